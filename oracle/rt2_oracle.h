@@ -1,0 +1,62 @@
+/* rt2_oracle.h — C API of the CPU oracle (TEST INFRASTRUCTURE, never shipped, never on the product
+ * path).  PARITY UNPINNED: the reference has no tests, golden vectors or CPU implementation of its
+ * shader math and cannot be built or run here (no Rust, no glslang, no Vulkan).
+ * This oracle is a hand restatement of the reference's GLSL, function by function, with every
+ * function citing the reference file:line it follows.  Only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs may load it.
+ */
+#ifndef RT2_ORACLE_H
+#define RT2_ORACLE_H
+#include "../include/rt2_abi.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct orc_scene orc_scene;
+
+/* flags for orc_render_* / orc_trace_primary */
+#define ORC_BRUTE_FORCE   1u   /* intersect by testing every triangle (no BVH)                    */
+#define ORC_TRIG_LIBM     2u   /* glibc sinf/cosf/atan2f/asinf instead of the pinned polynomials  */
+
+orc_scene* orc_scene_create(const rt2_scene_desc* scene);
+void       orc_scene_destroy(orc_scene* s);
+uint64_t   orc_scene_num_triangles(const orc_scene* s);
+
+/* setupPrimaryRay + trace with TMin 0.001 (refrence.rgen:26-27) for every pixel. */
+int orc_trace_primary(const orc_scene* s, const void* gconst, uint32_t width, uint32_t height,
+                      uint32_t flags, int threads, rt2_hit_record* out);
+
+/* K1 refrence.rgen::main for rows [row0,row1) (row1 = 0 => height).  diffuse_f16/specular_f16 are
+ * the rgba16f images (in/out: prior frame state when accumulation is on), diffuse_f32 the fp32
+ * shadow accumulator (may be NULL).  Returns the number of rays traced through *rays. */
+int orc_render_reference(const orc_scene* s, const void* gconst, uint32_t frame,
+                         uint32_t width, uint32_t height, uint32_t spp, uint32_t max_bounces,
+                         uint32_t row0, uint32_t row1, uint32_t flags, int threads,
+                         uint16_t* diffuse_f16, uint16_t* specular_f16, float* diffuse_f32,
+                         uint64_t* rays);
+
+/* ---- known-answer probes for pure functions ------------------------------------------------- */
+uint32_t orc_zcurve_to_linear(uint32_t x, uint32_t y);            /* RtxdiMath.hlsli:55-58 */
+void     orc_linear_to_zcurve(uint32_t i, uint32_t* x, uint32_t* y); /* RtxdiMath.hlsli:61-66 */
+uint32_t orc_jenkins_hash(uint32_t a);                            /* RtxdiMath.hlsli:69-79 */
+/* initRandomSampler(pixel, frame + 13*pass) then n draws (Helpers.glsl:13-64) */
+void     orc_rng_stream(uint32_t px, uint32_t py, uint32_t frame, uint32_t pass, uint32_t n,
+                        uint32_t* raw, float* uniform);
+uint16_t orc_f32_to_f16(float f);
+float    orc_f16_to_f32(uint16_t h);
+void     orc_sincos(float angle, uint32_t flags, float* s, float* c);
+/* watertight ray/triangle test (pinned; Vulkan leaves it to the driver). returns 1 on hit */
+int      orc_ray_triangle(const float o[3], const float d[3], float tmin, float tmax,
+                          const float v0[3], const float v1[3], const float v2[3],
+                          float* t, float* u, float* v);
+/* setupPrimaryRay (GBufferHelpers.glsl:12-27) */
+void     orc_primary_ray(const void* gconst, uint32_t px, uint32_t py, float origin[3], float dir[3]);
+/* RAB_GetSurfaceBrdfSample's cosine lobe (bridge :437-461) for given normal + 3 uniforms */
+void     orc_cos_hemisphere_dir(const float n[3], float r1, float r2, uint32_t flags, float dir[3]);
+/* texture(textures[idx], uv).rgb with the pinned LOD-0 filter (Hit.glsl:35-37) */
+void     orc_sample_texture(const orc_scene* s, uint32_t texture_index, float u, float v, float rgb[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,216 @@
+"""Host-side mirror of the reference's pass objects over the C ABI.
+
+Names and call order follow the reference's host (src/main.rs:661-700):
+    Renderer            <- Renderer::new                 (src/context.rs:120)
+    Model.from_scene    <- Model::from_gltf + TLAS       (src/model.rs:185, src/main.rs:153-191)
+    LightPasses         <- LightPasses::{new,update_uniform,execute}   (src/light_passes.rs:226,665,550)
+    PrepareLightsTasks  <- PrepareLightsTasks::execute   (src/prepare_lights.rs:172)
+    GenerateMipsPass    <- GenerateMipsPass::execute_mip_generation    (src/mip_pass.rs:122)
+    PostProcessPass     <- PostProcessPass::execute      (src/postprocess.rs:225)
+Every method is one call into librt2cuda.so; errors raise Rt2Error with rt2_last_error()
+(the reference's constructors return anyhow::Result / panic on unwrap).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _ffi
+from ._ffi import (Camera, GConst, HitRecord, LaunchParams, PlanarViewConstants, SceneDesc, Stats)
+
+# rt2_buffer ids (include/rt2_abi.h)
+BUF_DIFFUSE_F16, BUF_SPECULAR_F16, BUF_DIFFUSE_F32, BUF_HIT_IDS, BUF_OUTPUT_RGBA8 = 0, 1, 2, 3, 4
+BUF_LIGHT_INFO, BUF_GEOM_TO_LIGHT, BUF_LIGHT_TASKS = 5, 6, 7
+BUF_LOCAL_PDF_MIP0, BUF_ENV_PDF_MIP0 = 16, 48
+BUF_GBUFFER_DEPTH, BUF_GBUFFER_NORMALS, BUF_GBUFFER_GEO_NORMALS = 80, 81, 82
+BUF_GBUFFER_DIFFUSE_ALBEDO, BUF_GBUFFER_SPECULAR_ROUGH, BUF_GBUFFER_EMISSIVE = 83, 84, 85
+BUF_MOTION_VECTORS, BUF_DI_RESERVOIRS, BUF_GI_RESERVOIRS, BUF_SECONDARY_GBUFFER = 86, 87, 88, 89
+
+LAUNCH_TRIG_LIBDEVICE = 1
+
+SCENE_CORNELL, SCENE_HALL, SCENE_MANYLIGHT, SCENE_INSTANCED, SCENE_FURNACE, SCENE_RANDOM = 1, 2, 3, 5, 6, 7
+
+
+class Rt2Error(RuntimeError):
+    pass
+
+
+# ---- host library wrappers ------------------------------------------------------------------------------
+class Scene:
+    """A procedurally generated scene in the reference's upload layout (rt2h_scene_generate)."""
+
+    def __init__(self, kind: int, scale: float = 1.0, texture_size: int = 0, seed: int = 0):
+        self._h = _ffi.host_lib()
+        self._p = self._h.rt2h_scene_generate(kind, scale, texture_size, seed)
+        if not self._p:
+            raise Rt2Error(f"unknown scene kind {kind}")
+        self.kind = kind
+
+    @property
+    def desc(self) -> "C.POINTER(SceneDesc)":
+        return self._h.rt2h_scene_desc(self._p)
+
+    def camera(self, aspect_ratio: float = 0.0) -> Camera:
+        cam = Camera()
+        self._h.rt2h_scene_camera(self._p, aspect_ratio, C.byref(cam))
+        return cam
+
+    @property
+    def num_lights(self) -> int:
+        return self._h.rt2h_scene_num_lights(self._p)
+
+    @property
+    def num_triangles(self) -> int:
+        return self._h.rt2h_scene_num_triangles(self._p)
+
+    def close(self):
+        if self._p:
+            self._h.rt2h_scene_destroy(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def default_gconst(cam: Camera, width: int, height: int, num_lights: int = 0, env_size=(0, 0)) -> GConst:
+    """src/main.rs:237-400 defaults."""
+    g = GConst()
+    _ffi.host_lib().rt2h_default_gconst(C.byref(g), C.byref(cam), width, height, num_lights, env_size[0], env_size[1])
+    return g
+
+
+def advance_frame(g: GConst, cam: Camera, width: int, height: int, frame: int) -> None:
+    """src/main.rs:641-651."""
+    _ffi.host_lib().rt2h_advance_frame(C.byref(g), C.byref(cam), width, height, frame)
+
+
+def planar_view_constants(cam: Camera, width: int, height: int) -> PlanarViewConstants:
+    v = PlanarViewConstants()
+    _ffi.host_lib().rt2h_planar_view_constants(C.byref(cam), width, height, C.byref(v))
+    return v
+
+
+# ---- the CUDA context ---------------------------------------------------------------------------------------
+class Renderer:
+    """Owns one rt2_ctx (one CUDA device, one stream)."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _ffi.cuda_lib()
+        self._ctx = C.c_void_p()
+        rc = self._lib.rt2_create(device, C.byref(self._ctx))
+        if rc != 0:
+            msg = self._lib.rt2_last_error(None)
+            raise Rt2Error(f"rt2_create({device}) failed ({rc}): {msg.decode() if msg else ''}")
+        self.width = self.height = 0
+
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            msg = self._lib.rt2_last_error(self._ctx)
+            raise Rt2Error(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+    def set_stream(self, cuda_stream_handle: int):
+        self._check(self._lib.rt2_set_stream(self._ctx, C.c_void_p(cuda_stream_handle)), "rt2_set_stream")
+
+    def resize(self, width: int, height: int):
+        self._check(self._lib.rt2_resize(self._ctx, width, height), "rt2_resize")
+        self.width, self.height = width, height
+
+    def sync(self):
+        self._check(self._lib.rt2_sync(self._ctx), "rt2_sync")
+
+    def buffer_size(self, which: int) -> int:
+        return int(self._lib.rt2_buffer_size(self._ctx, which))
+
+    def read(self, which: int, dtype=np.uint8) -> np.ndarray:
+        n = self.buffer_size(which)
+        if n == 0:
+            raise Rt2Error(f"buffer {which} is not allocated")
+        out = np.empty(n, dtype=np.uint8)
+        self._check(self._lib.rt2_read(self._ctx, which, out.ctypes.data_as(C.c_void_p), n), "rt2_read")
+        return out.view(dtype)
+
+    def read_into(self, which: int, dst_ptr: int, nbytes: int):
+        self._check(self._lib.rt2_read(self._ctx, which, C.c_void_p(dst_ptr), nbytes), "rt2_read")
+
+    def write(self, which: int, arr: np.ndarray):
+        a = np.ascontiguousarray(arr)
+        self._check(self._lib.rt2_write(self._ctx, which, a.ctypes.data_as(C.c_void_p), a.nbytes), "rt2_write")
+
+    def copy_to_device(self, which: int, device_ptr: int, nbytes: int, row0: int = 0, row1: int = 0):
+        self._check(self._lib.rt2_copy_to_device(self._ctx, which, C.c_void_p(device_ptr), nbytes, row0, row1), "rt2_copy_to_device")
+
+    def stats(self) -> Stats:
+        s = Stats()
+        self._check(self._lib.rt2_get_stats(self._ctx, C.byref(s)), "rt2_get_stats")
+        return s
+
+    def close(self):
+        if getattr(self, "_ctx", None) and self._ctx.value:
+            self._lib.rt2_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Model:
+    """Model::from_gltf (uploads) + the BLAS/TLAS build, on the device."""
+
+    def __init__(self, ctx: Renderer, scene_desc):
+        self.ctx = ctx
+        ctx._check(ctx._lib.rt2_upload_scene(ctx._ctx, scene_desc), "rt2_upload_scene")
+        ctx._check(ctx._lib.rt2_build_accel(ctx._ctx), "rt2_build_accel")
+
+    @classmethod
+    def from_scene(cls, ctx: Renderer, scene: Scene) -> "Model":
+        return cls(ctx, scene.desc)
+
+
+class LightPasses:
+    def __init__(self, ctx: Renderer, width: int, height: int):
+        self.ctx = ctx
+        ctx.resize(width, height)
+
+    def update_uniform(self, g_const: GConst):
+        self.ctx._check(self.ctx._lib.rt2_set_constants(self.ctx._ctx, C.byref(g_const), C.sizeof(g_const)), "rt2_set_constants")
+
+    def execute(self, frame: int, params: LaunchParams | None = None):
+        p = C.byref(params) if params is not None else None
+        self.ctx._check(self.ctx._lib.rt2_render(self.ctx._ctx, frame & 0xFFFFFFFF, p), "rt2_render")
+
+    def trace_primary(self, params: LaunchParams | None = None):
+        p = C.byref(params) if params is not None else None
+        self.ctx._check(self.ctx._lib.rt2_trace_primary(self.ctx._ctx, p), "rt2_trace_primary")
+
+
+class PrepareLightsTasks:
+    def __init__(self, ctx: Renderer):
+        self.ctx = ctx
+
+    def execute(self):
+        self.ctx._check(self.ctx._lib.rt2_prepare_lights(self.ctx._ctx), "rt2_prepare_lights")
+
+
+class GenerateMipsPass:
+    LOCAL_LIGHTS, ENVIRONMENT = 0, 1
+
+    def __init__(self, ctx: Renderer, which: int):
+        self.ctx, self.which = ctx, which
+
+    def execute_mip_generation(self):
+        self.ctx._check(self.ctx._lib.rt2_generate_mips(self.ctx._ctx, self.which), "rt2_generate_mips")
+
+
+class PostProcessPass:
+    def __init__(self, ctx: Renderer):
+        self.ctx = ctx
+
+    def execute(self, frame: int):
+        self.ctx._check(self.ctx._lib.rt2_postprocess(self.ctx._ctx, frame & 0xFFFFFFFF), "rt2_postprocess")

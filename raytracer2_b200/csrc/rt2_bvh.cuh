@@ -1,0 +1,209 @@
+// rt2_bvh.cuh — compressed 8-wide BVH (CWBVH, after Ylitie/Karras/Laine 2017) node format and
+// stack traversal.  Replaces the driver BLAS/TLAS + traceRayEXT of the reference
+// (src/model.rs:379-459, src/main.rs:153-191, RtxdiApplicationBridge.glsl:74-81).
+//
+// 80-byte node, five 16-byte words:
+//   w0: p.x p.y p.z (fp32 grid origin) | ex ey ez imask (4 x u8; grid step = 2^e, imask bit s = slot s is an inner child)
+//   w1: child_base, tri_base, meta[8]   (meta: 0 empty | inner 001sssss with sssss = 24+slot | leaf ccc ooooo:
+//                                         ccc = unary triangle count, ooooo = first triangle relative to tri_base)
+//   w2: qlo.x[8] qlo.y[8]   w3: qlo.z[8] qhi.x[8]   w4: qhi.y[8] qhi.z[8]     (u8 grid coordinates per child)
+// Child box = [p + qlo*2^e, p + qhi*2^e].  The builder keeps >= 2^-10 grid steps of slack around
+// every child box and the slab test widens t by (1 +- 2^-18), so a ray the watertight triangle
+// test accepts is never culled by a quantised box (bit-exact hit ids vs brute force).
+//
+// Leaf triangles are stored pre-transformed (node matrix M*v, src/model.rs:193-212) as three
+// float4: (v0, geometryIndex) (v1, primitiveId) (v2, 0); ids ride in the .w lanes.
+#pragma once
+#include "rt2_math.cuh"
+
+namespace rt2 {
+
+struct __align__(16) Node8 {
+    float px, py, pz;
+    uint8_t ex, ey, ez, imask;
+    uint32_t child_base, tri_base;
+    uint8_t meta[8];
+    uint8_t qlox[8], qloy[8];
+    uint8_t qloz[8], qhix[8];
+    uint8_t qhiy[8], qhiz[8];
+};
+static_assert(sizeof(Node8) == 80, "CWBVH node must be 80 bytes");
+
+struct __align__(16) TriPos { float4 v0, v1, v2; };      // 48 bytes
+static_assert(sizeof(TriPos) == 48, "leaf triangle must be 48 bytes");
+
+#define RT2_SLAB_EPS 3.814697265625e-06f   /* 2^-18 */
+#define RT2_STACK_SIZE 48
+
+RT2_HD uint32_t rt2_popc(uint32_t x) {
+#ifdef __CUDA_ARCH__
+    return (uint32_t)__popc(x);
+#else
+    return (uint32_t)__builtin_popcount(x);
+#endif
+}
+RT2_HD uint32_t rt2_fhs(uint32_t x) {   // index of highest set bit (x != 0)
+#ifdef __CUDA_ARCH__
+    return 31u - (uint32_t)__clz((int)x);
+#else
+    return 31u - (uint32_t)__builtin_clz(x);
+#endif
+}
+RT2_HD uint32_t rt2_byte(uint32_t w, uint32_t i) { return (w >> (8u * i)) & 0xFFu; }
+RT2_HD uint4 ld16(const void* p) {
+#ifdef __CUDA_ARCH__
+    return __ldg(reinterpret_cast<const uint4*>(p));
+#else
+    return *reinterpret_cast<const uint4*>(p);
+#endif
+}
+RT2_HD float4 ld16f(const void* p) {
+#ifdef __CUDA_ARCH__
+    return __ldg(reinterpret_cast<const float4*>(p));
+#else
+    return *reinterpret_cast<const float4*>(p);
+#endif
+}
+// sign-extend each byte's msb over the byte: 0x80 -> 0xFF, else 0x00
+RT2_HD uint32_t sign_extend_s8x4(uint32_t x) {
+#ifdef __CUDA_ARCH__
+    return __byte_perm(x, 0u, 0xBA98u);
+#else
+    uint32_t r = 0;
+    for (int i = 0; i < 4; i++) if (x & (0x80u << (8 * i))) r |= 0xFFu << (8 * i);
+    return r;
+#endif
+}
+RT2_HD float byte_to_float(uint32_t w, uint32_t i) { return (float)rt2_byte(w, i); }
+
+struct TraceRay {
+    V3 o, d;
+    float tmin, tmax;
+};
+
+// Generic CWBVH stack traversal.  `leaf(slot)` is called for every leaf primitive whose (padded)
+// box the ray touches within [tmin, min(tmax, *t_limit)]; it may lower *t_limit (closest hit).
+template <class LeafFn>
+RT2_HD void cwbvh_traverse(const Node8* __restrict__ nodes, const TraceRay& ray, const float* t_limit, LeafFn&& leaf,
+                           uint32_t* node_visits = nullptr) {
+    // per-ray slab constants: near planes use idir*(1-eps), far planes idir*(1+eps)
+    const float idx = 1.0f / ray.d.x, idy = 1.0f / ray.d.y, idz = 1.0f / ray.d.z;
+    const float inx = idx * (1.0f - RT2_SLAB_EPS), iny = idy * (1.0f - RT2_SLAB_EPS), inz = idz * (1.0f - RT2_SLAB_EPS);
+    const float ifx = idx * (1.0f + RT2_SLAB_EPS), ify = idy * (1.0f + RT2_SLAB_EPS), ifz = idz * (1.0f + RT2_SLAB_EPS);
+    const bool negx = (f2u(ray.d.x) >> 31) != 0, negy = (f2u(ray.d.y) >> 31) != 0, negz = (f2u(ray.d.z) >> 31) != 0;
+    const uint32_t oct = (negx ? 1u : 0u) | (negy ? 2u : 0u) | (negz ? 4u : 0u);
+    const uint32_t oct_inv = 7u - oct;
+    const uint32_t oct_inv4 = oct_inv * 0x01010101u;
+
+    uint2 stack[RT2_STACK_SIZE];
+    int sp = 0;
+    uint2 ngroup = make_uint2(0u, 0x80000000u);
+
+    for (;;) {
+        uint2 tgroup;
+        if (ngroup.y > 0x00FFFFFFu) {
+            const uint32_t hits = ngroup.y;
+            const uint32_t imask = hits & 0xFFu;
+            const uint32_t bit = rt2_fhs(hits);
+            ngroup.y &= ~(1u << bit);
+            if (ngroup.y > 0x00FFFFFFu) { if (sp < RT2_STACK_SIZE) stack[sp++] = ngroup; }
+            const uint32_t slot = (bit - 24u) ^ oct_inv;
+            const uint32_t rel = rt2_popc(imask & ~(0xFFFFFFFFu << slot));
+            const Node8* np = nodes + (ngroup.x + rel);
+            if (node_visits) (*node_visits)++;
+            const uint4 n0 = ld16(np), n1 = ld16(reinterpret_cast<const uint4*>(np) + 1);
+            const uint4 n2 = ld16(reinterpret_cast<const uint4*>(np) + 2), n3 = ld16(reinterpret_cast<const uint4*>(np) + 3);
+            const uint4 n4 = ld16(reinterpret_cast<const uint4*>(np) + 4);
+            const float sx = u2f(rt2_byte(n0.w, 0) << 23), sy = u2f(rt2_byte(n0.w, 1) << 23), sz = u2f(rt2_byte(n0.w, 2) << 23);
+            const float ax = u2f(n0.x) - ray.o.x, ay = u2f(n0.y) - ray.o.y, az = u2f(n0.z) - ray.o.z;
+            // t = q * (s*idir) + (p-o)*idir ; s is a power of two so s*idir is exact
+            const float snx = sx * inx, sny = sy * iny, snz = sz * inz, sfx = sx * ifx, sfy = sy * ify, sfz = sz * ifz;
+            const float anx = ax * inx, any_ = ay * iny, anz = az * inz, afx = ax * ifx, afy = ay * ify, afz = az * ifz;
+            const float tfar_limit = fminf(*t_limit, ray.tmax);
+            uint32_t hitmask = 0;
+#pragma unroll
+            for (int half = 0; half < 2; half++) {
+                const uint32_t meta4 = half ? n1.w : n1.z;
+                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+                const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
+                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+                const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+                const uint32_t qnx = negx ? qhix : qlox, qfx = negx ? qlox : qhix;
+                const uint32_t qny = negy ? qhiy : qloy, qfy = negy ? qloy : qhiy;
+                const uint32_t qnz = negz ? qhiz : qloz, qfz = negz ? qloz : qhiz;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float tnx = rt2_fma(byte_to_float(qnx, j), snx, anx);
+                    const float tny = rt2_fma(byte_to_float(qny, j), sny, any_);
+                    const float tnz = rt2_fma(byte_to_float(qnz, j), snz, anz);
+                    const float tfx = rt2_fma(byte_to_float(qfx, j), sfx, afx);
+                    const float tfy = rt2_fma(byte_to_float(qfy, j), sfy, afy);
+                    const float tfz = rt2_fma(byte_to_float(qfz, j), sfz, afz);
+                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, ray.tmin));
+                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar_limit));
+                    if (tn <= tf) hitmask |= rt2_byte(child_bits4, j) << rt2_byte(bit_index4, j);
+                }
+            }
+            ngroup.x = n1.x;
+            ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
+            tgroup.x = n1.y;
+            tgroup.y = hitmask & 0x00FFFFFFu;
+        } else {
+            tgroup = ngroup;
+            ngroup = make_uint2(0u, 0u);
+        }
+        while (tgroup.y != 0u) {
+            const uint32_t ti = rt2_fhs(tgroup.y);
+            tgroup.y &= ~(1u << ti);
+            leaf(tgroup.x + ti);
+        }
+        if (ngroup.y <= 0x00FFFFFFu) {
+            if (sp == 0) break;
+            ngroup = stack[--sp];
+        }
+    }
+}
+
+// Closest hit over one triangle CWBVH.  `inst` is written into the hit record (0 for the
+// single-level case).  Caller initialises best.t = +inf and ids = ~0u.
+RT2_HD void cwbvh_closest_hit(const Node8* __restrict__ nodes, const TriPos* __restrict__ tris,
+                              const TraceRay& ray, uint32_t inst, Hit& best, uint32_t* slot_out, uint32_t* node_visits = nullptr) {
+    const RayShear sh = make_shear(ray.d);
+    cwbvh_traverse(nodes, ray, &best.t, [&](uint32_t slot) {
+        const TriPos* tp = tris + slot;
+        const float4 a = ld16f(&tp->v0), b = ld16f(&tp->v1), c = ld16f(&tp->v2);
+        float t, u, v;
+        if (ray_triangle(ray.o, sh, ray.tmin, ray.tmax, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
+            const uint32_t geom = f2u(a.w), prim = f2u(b.w);
+            if (hit_closer(t, inst, geom, prim, best)) {
+                best.t = t; best.u = u; best.v = v; best.inst = inst; best.geom = geom; best.prim = prim;
+                if (slot_out) *slot_out = slot;
+            }
+        }
+    }, node_visits);
+}
+
+// Instance record of the TLAS (A2 extension): world->object 3x4, object->world 3x4. 96 bytes.
+struct __align__(16) InstanceRec { float inv[12]; float fwd[12]; };
+
+// Two-level closest hit: TLAS leaves are instance slots; the ray is re-expressed in object space
+// (o' = inv*o, d' = inv*d, t unchanged) and the BLAS is traversed.
+RT2_HD void tlas_closest_hit(const Node8* __restrict__ tlas_nodes, const uint32_t* __restrict__ tlas_slot_to_inst,
+                             const InstanceRec* __restrict__ instances, const Node8* __restrict__ blas_nodes,
+                             const TriPos* __restrict__ tris, const TraceRay& ray, Hit& best, uint32_t* slot_out,
+                             uint32_t* node_visits = nullptr) {
+    cwbvh_traverse(tlas_nodes, ray, &best.t, [&](uint32_t slot) {
+        const uint32_t inst = tlas_slot_to_inst[slot];
+        const InstanceRec* ir = instances + inst;
+        float m[12];
+#pragma unroll
+        for (int k = 0; k < 3; k++) { float4 r = ld16f(ir->inv + 4 * k); m[4 * k] = r.x; m[4 * k + 1] = r.y; m[4 * k + 2] = r.z; m[4 * k + 3] = r.w; }
+        TraceRay lr;
+        lr.o = xform_point(m, ray.o); lr.d = xform_vector(m, ray.d); lr.tmin = ray.tmin; lr.tmax = ray.tmax;
+        cwbvh_closest_hit(blas_nodes, tris, lr, inst, best, slot_out, node_visits);
+    }, node_visits);
+}
+
+}  // namespace rt2

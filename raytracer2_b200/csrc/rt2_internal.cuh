@@ -1,0 +1,142 @@
+// rt2_internal.cuh — context object and cross-file declarations of librt2cuda.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/rt2_abi.h"
+#include "../../include/rt2_gconst.h"
+#include "rt2_bvh.cuh"
+
+namespace rt2 {
+
+struct LaunchCounter {
+    uint64_t n = 0;
+    void add(uint64_t k) { n += k; }
+};
+
+// One acceleration structure level.
+struct Accel {
+    Node8* nodes = nullptr;
+    TriPos* tris = nullptr;             // BLAS only: leaf triangles in slot order
+    uint32_t* slot_to_prim = nullptr;   // slot -> primitive id (BLAS: triangle in geometry order; TLAS: instance id)
+    uint32_t num_nodes = 0, num_prims = 0, depth = 0;
+    float box_lo[3] = {0, 0, 0}, box_hi[3] = {0, 0, 0};
+    void release() {
+        if (nodes) cudaFree(nodes);
+        if (tris) cudaFree(tris);
+        if (slot_to_prim) cudaFree(slot_to_prim);
+        nodes = nullptr; tris = nullptr; slot_to_prim = nullptr; num_nodes = num_prims = depth = 0;
+    }
+};
+
+// Per-triangle shading record in leaf (slot) order: what GetGeometryFromHit (Hit.glsl:2-42) gathers
+// through Indices[] and Vertices[] — same fp32 values, one indirection instead of three. 96 bytes.
+struct __align__(16) TriShade {
+    float n0[3], n1[3], n2[3];
+    float uv0[2], uv1[2], uv2[2];
+    float c0[3], c1[3], c2[3];
+};
+static_assert(sizeof(TriShade) == 96, "TriShade must be 96 bytes");
+
+// Per-geometry shading record (from GeometryInfo, src/model.rs:12-23). 112 bytes.
+struct __align__(16) GeomShade {
+    float transform[16];      // column-major; used for normalize(transform * vec4(n, 0)) (Hit.glsl:27)
+    float base_color[3];
+    int32_t texture;          // baseColorTextureIndex
+    float emission12[3];      // emission.xyz * 12.0 (Hit.glsl:41) — one fp32 multiply, done at upload
+    float metallic;
+    float emission[3];        // raw emission (prepare_lights)
+    float roughness;
+};
+static_assert(sizeof(GeomShade) == 112, "GeomShade must be 112 bytes");
+
+struct TextureRec { uint32_t offset; uint32_t width, height, filter; };   // offset in texels into the texel pool
+
+struct DeviceScene {
+    rt2_vertex* vertices = nullptr; uint64_t num_vertices = 0;
+    uint32_t* indices = nullptr; uint64_t num_indices = 0;
+    rt2_geometry_info* geoms = nullptr; uint32_t num_geoms = 0;
+    uint32_t* geom_tri_offset = nullptr;      // num_geoms + 1
+    GeomShade* geom_shade = nullptr;
+    uint32_t* texels = nullptr;               // RGBA8 pool
+    TextureRec* textures = nullptr; uint32_t num_textures = 0;
+    float* srgb_lut = nullptr;                // 256 floats
+    float4* sky = nullptr; uint32_t sky_w = 0, sky_h = 0;
+    InstanceRec* instances = nullptr; uint32_t num_instances = 0;   // 0 => single identity instance
+    uint32_t num_tris = 0;
+    uint32_t num_lights = 0;
+    TriShade* tri_shade = nullptr;            // slot order (after build)
+    Accel blas, tlas;
+    bool accel_built = false;
+    // host copies needed by host-side steps (prepare_lights scan, src/prepare_lights.rs:182-201)
+    std::vector<rt2_geometry_info> h_geoms;
+    std::vector<uint32_t> h_index_counts;
+};
+
+// Per-size resources (RenderResources::new, src/render_resources.rs:130-341)
+struct FrameBuffers {
+    uint32_t width = 0, height = 0;
+    ushort4* diffuse_f16 = nullptr;    // DiffuseLighting rgba16f
+    ushort4* specular_f16 = nullptr;   // SpecularLighting rgba16f
+    float4* diffuse_f32 = nullptr;     // fp32 shadow accumulator
+    rt2_hit_record* hit_ids = nullptr;
+    uchar4* output_rgba8 = nullptr;
+    // wavefront state (one slot per owned pixel)
+    uint32_t max_slots = 0;
+    float4 *st_ray0 = nullptr, *st_ray1 = nullptr, *st_acc = nullptr;
+    uint4* st_misc = nullptr;
+    float4* st_hit = nullptr;
+    uint32_t* st_hit_inst = nullptr;
+    uint32_t *queue0 = nullptr, *queue1 = nullptr;
+    uint32_t* counters = nullptr;      // [0..1] queue counts, [2] fetch head, [4..5] u64 rays, [6..7] u64 hits
+};
+
+}  // namespace rt2
+
+struct rt2_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    int num_sms = 0;
+    std::string last_error;
+    rt2::DeviceScene scene;
+    rt2::FrameBuffers fb;
+    rt2_gconst gconst{};
+    bool have_gconst = false;
+    rt2_gconst* d_gconst = nullptr;
+    rt2_stats stats{};
+    uint64_t device_bytes = 0;
+    // lights / pdf textures (K10/K12)
+    rt2_light_info* light_info = nullptr; uint32_t light_capacity = 0;
+    uint32_t* geom_to_light = nullptr;
+    rt2_prepare_lights_task* light_tasks = nullptr; uint32_t num_light_tasks = 0;
+    float* local_pdf = nullptr; uint32_t local_pdf_w = 0, local_pdf_h = 0, local_pdf_mips = 0;   // all mips, packed
+    uint16_t* env_pdf = nullptr; uint32_t env_pdf_w = 0, env_pdf_h = 0, env_pdf_mips = 0;        // r16f, packed mips
+};
+
+namespace rt2 {
+
+int fail(rt2_ctx* ctx, int code, const std::string& msg);
+#define RT2_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return rt2::fail((ctx), RT2_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
+
+// rt2_build.cu
+struct BuildInput;
+int build_blas(cudaStream_t st, const BuildInput& in, Accel* out, LaunchCounter* lc, std::string& err);
+int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, uint32_t n, Node8** nodes_out, uint32_t* num_nodes_out,
+                           uint32_t** out_prim_out, uint32_t* depth_out, LaunchCounter* lc, std::string& err);
+// rt2_scene.cu
+int scene_upload(rt2_ctx* ctx, const rt2_scene_desc* d);
+int scene_build_accel(rt2_ctx* ctx);
+void scene_release(rt2_ctx* ctx);
+// rt2_render.cu
+int frame_resize(rt2_ctx* ctx, uint32_t w, uint32_t h);
+void frame_release(rt2_ctx* ctx);
+int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp);   // K1
+int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp);
+
+}  // namespace rt2
