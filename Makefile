@@ -1,0 +1,26 @@
+# Builds every native piece in-tree: the CUDA product library, the C++ host library, the CPU oracle.
+NVCC ?= /usr/local/cuda/bin/nvcc
+CXX ?= g++
+CSRC := raytracer2_b200/csrc
+CU_SRCS := $(CSRC)/rt2_api.cu $(CSRC)/rt2_scene.cu $(CSRC)/rt2_build.cu $(CSRC)/rt2_render.cu $(wildcard $(CSRC)/rt2_passes*.cu) $(wildcard $(CSRC)/rt2_pass_*.cu)
+CU_HDRS := $(wildcard $(CSRC)/*.cuh) include/rt2_abi.h include/rt2_gconst.h
+# -fmad=false: no implicit FMA contraction (bit parity with the oracle); explicit __fmaf_rn where wanted.
+NVCCFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-ffp-contract=off,-Wall -Xptxas -v
+
+all: raytracer2_b200/librt2cuda.so raytracer2_b200/librt2host.so oracle
+
+raytracer2_b200/librt2cuda.so: $(CU_SRCS) $(CU_HDRS)
+	$(NVCC) $(NVCCFLAGS) -shared -o $@ $(CU_SRCS) 2> build_ptxas.log || (cat build_ptxas.log; exit 1)
+	@grep -E "error|warning" build_ptxas.log || true
+
+raytracer2_b200/librt2host.so: raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_host.h include/rt2_abi.h include/rt2_gconst.h
+	$(CXX) -O2 -std=c++17 -fPIC -Wall -Wextra -shared -o $@ raytracer2_b200/host/rt2_host.cpp
+
+oracle:
+	$(MAKE) -C oracle
+
+clean:
+	rm -f raytracer2_b200/librt2cuda.so raytracer2_b200/librt2host.so build_ptxas.log
+	$(MAKE) -C oracle clean
+
+.PHONY: all oracle clean

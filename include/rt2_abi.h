@@ -164,6 +164,7 @@ typedef struct rt2_launch_params {
 } rt2_launch_params;
 
 #define RT2_LAUNCH_TRIG_LIBDEVICE 1u  /* use CUDA sinf/cosf/atan2f/asinf instead of the pinned polynomials */
+#define RT2_LAUNCH_PROFILE        2u  /* bracket every kernel launch with CUDA events (rt2_stats.trace_ns/shade_ns) */
 
 /* Buffers readable with rt2_read (all row-major W x H unless noted). */
 enum rt2_buffer {
@@ -198,7 +199,10 @@ typedef struct rt2_stats {
     uint64_t bvh_nodes;        /* CWBVH nodes (BLAS + TLAS)                                    */
     uint64_t bvh_triangles;
     uint64_t device_bytes;     /* device memory owned by the context                          */
-    uint64_t _reserved;
+    uint64_t trace_ns;         /* with RT2_LAUNCH_PROFILE: summed CUDA-event time of the traversal kernel launches */
+    uint64_t shade_ns;         /* with RT2_LAUNCH_PROFILE: summed CUDA-event time of the shading kernel launches   */
+    uint64_t trace_launches;   /* with RT2_LAUNCH_PROFILE: traversal kernel launches that had rays to trace         */
+    uint64_t _reserved[2];
 } rt2_stats;
 
 typedef struct rt2_ctx rt2_ctx;

@@ -28,6 +28,7 @@ BUF_GBUFFER_DIFFUSE_ALBEDO, BUF_GBUFFER_SPECULAR_ROUGH, BUF_GBUFFER_EMISSIVE = 8
 BUF_MOTION_VECTORS, BUF_DI_RESERVOIRS, BUF_GI_RESERVOIRS, BUF_SECONDARY_GBUFFER = 86, 87, 88, 89
 
 LAUNCH_TRIG_LIBDEVICE = 1
+LAUNCH_PROFILE = 2
 
 SCENE_CORNELL, SCENE_HALL, SCENE_MANYLIGHT, SCENE_INSTANCED, SCENE_FURNACE, SCENE_RANDOM = 1, 2, 3, 5, 6, 7
 

@@ -93,7 +93,8 @@ struct FrameBuffers {
     float4* st_hit = nullptr;
     uint32_t* st_hit_inst = nullptr;
     uint32_t *queue0 = nullptr, *queue1 = nullptr;
-    uint32_t* counters = nullptr;      // [0..1] queue counts, [2] fetch head, [4..5] u64 rays, [6..7] u64 hits
+    uint32_t* counters = nullptr;      // [0..1] u64 rays, [2..3] u64 hits, then (count, head) per wavefront iteration
+    size_t counter_capacity = 0;
 };
 
 }  // namespace rt2
@@ -110,6 +111,10 @@ struct rt2_ctx {
     bool have_gconst = false;
     rt2_gconst* d_gconst = nullptr;
     rt2_stats stats{};
+    bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
+    uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
+    int trace_blocks_per_sm[2] = {1, 1};
+    std::vector<cudaEvent_t> prof_events;   // RT2_LAUNCH_PROFILE: 3 per wavefront iteration (before trace, after trace, after shade)
     uint64_t device_bytes = 0;
     // lights / pdf textures (K10/K12)
     rt2_light_info* light_info = nullptr; uint32_t light_capacity = 0;
@@ -138,5 +143,6 @@ int frame_resize(rt2_ctx* ctx, uint32_t w, uint32_t h);
 void frame_release(rt2_ctx* ctx);
 int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp);   // K1
 int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp);
+int render_init(rt2_ctx* ctx);
 
 }  // namespace rt2

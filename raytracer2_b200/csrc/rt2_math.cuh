@@ -8,6 +8,7 @@
 // Reference citations are relative to src/shaders/ of the reference tree.
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <math.h>
 #include <stdint.h>
 
