@@ -162,7 +162,11 @@ def main():
     g = rt.default_gconst(cam, W, H, sc.num_lights)
     g.refrence_mode = 1
     ctx = rt.Renderer(local_rank)
-    stream = torch.cuda.current_stream()
+    # a real (non-default) torch stream: the library, torch's events and NCCL all run on it, so
+    # torch.cuda.Event timing sees exactly the kernels librt2cuda launches
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     ctx.set_stream(stream.cuda_stream)
     rt.Model.from_scene(ctx, sc)
     lp = rt.LightPasses(ctx, W, H)

@@ -187,7 +187,13 @@ enum rt2_buffer {
     RT2_BUF_MOTION_VECTORS  = 86,  /* rgba32f                                                      */
     RT2_BUF_DI_RESERVOIRS   = 87,  /* rt2_packed_di_reservoir x arrayPitch x 2, block-linear       */
     RT2_BUF_GI_RESERVOIRS   = 88,  /* 32 B x arrayPitch x 2                                        */
-    RT2_BUF_SECONDARY_GBUFFER = 89 /* 48 B x W x H                                                 */
+    RT2_BUF_SECONDARY_GBUFFER = 89, /* 48 B x W x H                                                 */
+    /* acceleration-structure introspection (tests / tools) */
+    RT2_BUF_BLAS_NODES = 100,      /* 80-byte CWBVH nodes                                          */
+    RT2_BUF_BLAS_TRIS = 101,       /* 48-byte leaf triangles in slot order                         */
+    RT2_BUF_BLAS_SLOT_TO_PRIM = 102, /* uint32 slot -> triangle index in geometry order            */
+    RT2_BUF_TLAS_NODES = 103,
+    RT2_BUF_TLAS_SLOT_TO_INST = 104
 };
 
 /* Counters of the last rt2_render / rt2_trace_primary on this context. */

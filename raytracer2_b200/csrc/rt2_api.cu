@@ -137,6 +137,11 @@ static bool buffer_lookup(rt2_ctx* ctx, int which, void** ptr, size_t* bytes) {
         case RT2_BUF_DIFFUSE_F32: *ptr = f.diffuse_f32; *bytes = n * 16; return f.diffuse_f32 != nullptr;
         case RT2_BUF_HIT_IDS: *ptr = f.hit_ids; *bytes = n * sizeof(rt2_hit_record); return f.hit_ids != nullptr;
         case RT2_BUF_OUTPUT_RGBA8: *ptr = f.output_rgba8; *bytes = n * 4; return f.output_rgba8 != nullptr;
+        case RT2_BUF_BLAS_NODES: *ptr = ctx->scene.blas.nodes; *bytes = (size_t)ctx->scene.blas.num_nodes * sizeof(Node8); return ctx->scene.accel_built;
+        case RT2_BUF_BLAS_TRIS: *ptr = ctx->scene.blas.tris; *bytes = (size_t)ctx->scene.blas.num_prims * sizeof(TriPos); return ctx->scene.accel_built && ctx->scene.blas.num_prims;
+        case RT2_BUF_BLAS_SLOT_TO_PRIM: *ptr = ctx->scene.blas.slot_to_prim; *bytes = (size_t)ctx->scene.blas.num_prims * 4; return ctx->scene.accel_built && ctx->scene.blas.num_prims;
+        case RT2_BUF_TLAS_NODES: *ptr = ctx->scene.tlas.nodes; *bytes = (size_t)ctx->scene.tlas.num_nodes * sizeof(Node8); return ctx->scene.accel_built && ctx->scene.tlas.nodes;
+        case RT2_BUF_TLAS_SLOT_TO_INST: *ptr = ctx->scene.tlas.slot_to_prim; *bytes = (size_t)ctx->scene.tlas.num_prims * 4; return ctx->scene.accel_built && ctx->scene.tlas.nodes;
         default: return pass_buffer(ctx, which, ptr, bytes);
     }
 }

@@ -67,7 +67,10 @@ RT2_HD float4 ld16f(const void* p) {
 // sign-extend each byte's msb over the byte: 0x80 -> 0xFF, else 0x00
 RT2_HD uint32_t sign_extend_s8x4(uint32_t x) {
 #ifdef __CUDA_ARCH__
-    return __byte_perm(x, 0u, 0xBA98u);
+    // prmt selector nibbles 8..B = replicate the sign bit of byte 0..3 (__byte_perm masks that mode away)
+    uint32_t r;
+    asm("prmt.b32 %0, %1, 0, 0xBA98;" : "=r"(r) : "r"(x));
+    return r;
 #else
     uint32_t r = 0;
     for (int i = 0; i < 4; i++) if (x & (0x80u << (8 * i))) r |= 0xFFu << (8 * i);

@@ -181,3 +181,17 @@ void hostemu_trace_primary(void* p, const void* gconst, uint32_t w, uint32_t h, 
 }
 
 }  // extern "C"
+
+// traverse an externally supplied (device-built) single-level CWBVH on the CPU
+extern "C" void hostemu_trace_external(const void* nodes, const void* tris, const void* gconst, uint32_t w, uint32_t h, rt2_hit_record* out) {
+    rt2_gconst g; memcpy(&g, gconst, sizeof g);
+    for (uint32_t y = 0; y < h; y++) for (uint32_t x = 0; x < w; x++) {
+        TraceRay ray; primary_ray(g.view, x, y, &ray.o, &ray.d); ray.tmin = 0.001f; ray.tmax = 100000.0f;
+        Hit best; best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
+        cwbvh_closest_hit((const Node8*)nodes, (const TriPos*)tris, ray, 0u, best, nullptr, nullptr);
+        rt2_hit_record r; memset(&r, 0, sizeof r);
+        r.instance = best.inst; r.geometry = best.geom; r.primitive = best.prim;
+        if (best.geom != 0xFFFFFFFFu) { r.t = best.t; r.u = best.u; r.v = best.v; }
+        out[(size_t)y * w + x] = r;
+    }
+}
