@@ -84,20 +84,84 @@ struct TraceRay {
     float tmin, tmax;
 };
 
+// Per-ray slab constants: near planes use idir*(1-eps), far planes idir*(1+eps).
+struct RayPrep {
+    float ox, oy, oz;
+    float inx, iny, inz, ifx, ify, ifz;
+    uint32_t oct_inv;     // 7 - octant
+    bool negx, negy, negz;
+};
+RT2_HD RayPrep make_ray_prep(const V3& o, const V3& d) {
+    RayPrep r;
+    const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
+    r.ox = o.x; r.oy = o.y; r.oz = o.z;
+    r.inx = idx * (1.0f - RT2_SLAB_EPS); r.iny = idy * (1.0f - RT2_SLAB_EPS); r.inz = idz * (1.0f - RT2_SLAB_EPS);
+    r.ifx = idx * (1.0f + RT2_SLAB_EPS); r.ify = idy * (1.0f + RT2_SLAB_EPS); r.ifz = idz * (1.0f + RT2_SLAB_EPS);
+    r.negx = (f2u(d.x) >> 31) != 0; r.negy = (f2u(d.y) >> 31) != 0; r.negz = (f2u(d.z) >> 31) != 0;
+    r.oct_inv = 7u - ((r.negx ? 1u : 0u) | (r.negy ? 2u : 0u) | (r.negz ? 4u : 0u));
+    return r;
+}
+
+// One node step: pops the nearest-octant-first inner child of `ngroup` (which must have one),
+// pushes the remainder on the stack, tests the child's 8 boxes and returns the new inner-hit group in
+// `ngroup` and the triangle-hit group in `tgroup`.
+RT2_HD void cwbvh_node_step(const Node8* __restrict__ nodes, const RayPrep& rp, float tmin, float tfar_limit,
+                            uint2& ngroup, uint2& tgroup, uint2* stack, int& sp) {
+    const uint32_t hits = ngroup.y;
+    const uint32_t imask = hits & 0xFFu;
+    const uint32_t bit = rt2_fhs(hits);
+    ngroup.y &= ~(1u << bit);
+    if (ngroup.y > 0x00FFFFFFu) { if (sp < RT2_STACK_SIZE) stack[sp++] = ngroup; }
+    const uint32_t slot = (bit - 24u) ^ rp.oct_inv;
+    const uint32_t rel = rt2_popc(imask & ~(0xFFFFFFFFu << slot));
+    const Node8* np = nodes + (ngroup.x + rel);
+    const uint4 n0 = ld16(np), n1 = ld16(reinterpret_cast<const uint4*>(np) + 1);
+    const uint4 n2 = ld16(reinterpret_cast<const uint4*>(np) + 2), n3 = ld16(reinterpret_cast<const uint4*>(np) + 3);
+    const uint4 n4 = ld16(reinterpret_cast<const uint4*>(np) + 4);
+    const float sx = u2f(rt2_byte(n0.w, 0) << 23), sy = u2f(rt2_byte(n0.w, 1) << 23), sz = u2f(rt2_byte(n0.w, 2) << 23);
+    const float ax = u2f(n0.x) - rp.ox, ay = u2f(n0.y) - rp.oy, az = u2f(n0.z) - rp.oz;
+    // t = q * (s*idir) + (p-o)*idir ; s is a power of two so s*idir is exact
+    const float snx = sx * rp.inx, sny = sy * rp.iny, snz = sz * rp.inz, sfx = sx * rp.ifx, sfy = sy * rp.ify, sfz = sz * rp.ifz;
+    const float anx = ax * rp.inx, any_ = ay * rp.iny, anz = az * rp.inz, afx = ax * rp.ifx, afy = ay * rp.ify, afz = az * rp.ifz;
+    const uint32_t oct_inv4 = rp.oct_inv * 0x01010101u;
+    uint32_t hitmask = 0;
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const uint32_t meta4 = half ? n1.w : n1.z;
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+        const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
+        const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
+        const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
+        const uint32_t qnx = rp.negx ? qhix : qlox, qfx = rp.negx ? qlox : qhix;
+        const uint32_t qny = rp.negy ? qhiy : qloy, qfy = rp.negy ? qloy : qhiy;
+        const uint32_t qnz = rp.negz ? qhiz : qloz, qfz = rp.negz ? qloz : qhiz;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const float tnx = rt2_fma(byte_to_float(qnx, j), snx, anx);
+            const float tny = rt2_fma(byte_to_float(qny, j), sny, any_);
+            const float tnz = rt2_fma(byte_to_float(qnz, j), snz, anz);
+            const float tfx = rt2_fma(byte_to_float(qfx, j), sfx, afx);
+            const float tfy = rt2_fma(byte_to_float(qfy, j), sfy, afy);
+            const float tfz = rt2_fma(byte_to_float(qfz, j), sfz, afz);
+            const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+            const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar_limit));
+            if (tn <= tf) hitmask |= rt2_byte(child_bits4, j) << rt2_byte(bit_index4, j);
+        }
+    }
+    ngroup.x = n1.x;
+    ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
+    tgroup.x = n1.y;
+    tgroup.y = hitmask & 0x00FFFFFFu;
+}
+
 // Generic CWBVH stack traversal.  `leaf(slot)` is called for every leaf primitive whose (padded)
 // box the ray touches within [tmin, min(tmax, *t_limit)]; it may lower *t_limit (closest hit).
 template <class LeafFn>
 RT2_HD void cwbvh_traverse(const Node8* __restrict__ nodes, const TraceRay& ray, const float* t_limit, LeafFn&& leaf,
                            uint32_t* node_visits = nullptr) {
-    // per-ray slab constants: near planes use idir*(1-eps), far planes idir*(1+eps)
-    const float idx = 1.0f / ray.d.x, idy = 1.0f / ray.d.y, idz = 1.0f / ray.d.z;
-    const float inx = idx * (1.0f - RT2_SLAB_EPS), iny = idy * (1.0f - RT2_SLAB_EPS), inz = idz * (1.0f - RT2_SLAB_EPS);
-    const float ifx = idx * (1.0f + RT2_SLAB_EPS), ify = idy * (1.0f + RT2_SLAB_EPS), ifz = idz * (1.0f + RT2_SLAB_EPS);
-    const bool negx = (f2u(ray.d.x) >> 31) != 0, negy = (f2u(ray.d.y) >> 31) != 0, negz = (f2u(ray.d.z) >> 31) != 0;
-    const uint32_t oct = (negx ? 1u : 0u) | (negy ? 2u : 0u) | (negz ? 4u : 0u);
-    const uint32_t oct_inv = 7u - oct;
-    const uint32_t oct_inv4 = oct_inv * 0x01010101u;
-
+    const RayPrep rp = make_ray_prep(ray.o, ray.d);
     uint2 stack[RT2_STACK_SIZE];
     int sp = 0;
     uint2 ngroup = make_uint2(0u, 0x80000000u);
@@ -105,54 +169,8 @@ RT2_HD void cwbvh_traverse(const Node8* __restrict__ nodes, const TraceRay& ray,
     for (;;) {
         uint2 tgroup;
         if (ngroup.y > 0x00FFFFFFu) {
-            const uint32_t hits = ngroup.y;
-            const uint32_t imask = hits & 0xFFu;
-            const uint32_t bit = rt2_fhs(hits);
-            ngroup.y &= ~(1u << bit);
-            if (ngroup.y > 0x00FFFFFFu) { if (sp < RT2_STACK_SIZE) stack[sp++] = ngroup; }
-            const uint32_t slot = (bit - 24u) ^ oct_inv;
-            const uint32_t rel = rt2_popc(imask & ~(0xFFFFFFFFu << slot));
-            const Node8* np = nodes + (ngroup.x + rel);
             if (node_visits) (*node_visits)++;
-            const uint4 n0 = ld16(np), n1 = ld16(reinterpret_cast<const uint4*>(np) + 1);
-            const uint4 n2 = ld16(reinterpret_cast<const uint4*>(np) + 2), n3 = ld16(reinterpret_cast<const uint4*>(np) + 3);
-            const uint4 n4 = ld16(reinterpret_cast<const uint4*>(np) + 4);
-            const float sx = u2f(rt2_byte(n0.w, 0) << 23), sy = u2f(rt2_byte(n0.w, 1) << 23), sz = u2f(rt2_byte(n0.w, 2) << 23);
-            const float ax = u2f(n0.x) - ray.o.x, ay = u2f(n0.y) - ray.o.y, az = u2f(n0.z) - ray.o.z;
-            // t = q * (s*idir) + (p-o)*idir ; s is a power of two so s*idir is exact
-            const float snx = sx * inx, sny = sy * iny, snz = sz * inz, sfx = sx * ifx, sfy = sy * ify, sfz = sz * ifz;
-            const float anx = ax * inx, any_ = ay * iny, anz = az * inz, afx = ax * ifx, afy = ay * ify, afz = az * ifz;
-            const float tfar_limit = fminf(*t_limit, ray.tmax);
-            uint32_t hitmask = 0;
-#pragma unroll
-            for (int half = 0; half < 2; half++) {
-                const uint32_t meta4 = half ? n1.w : n1.z;
-                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
-                const uint32_t bit_index4 = (meta4 ^ (oct_inv4 & inner_mask4)) & 0x1F1F1F1Fu;
-                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlox = half ? n2.y : n2.x, qloy = half ? n2.w : n2.z, qloz = half ? n3.y : n3.x;
-                const uint32_t qhix = half ? n3.w : n3.z, qhiy = half ? n4.y : n4.x, qhiz = half ? n4.w : n4.z;
-                const uint32_t qnx = negx ? qhix : qlox, qfx = negx ? qlox : qhix;
-                const uint32_t qny = negy ? qhiy : qloy, qfy = negy ? qloy : qhiy;
-                const uint32_t qnz = negz ? qhiz : qloz, qfz = negz ? qloz : qhiz;
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const float tnx = rt2_fma(byte_to_float(qnx, j), snx, anx);
-                    const float tny = rt2_fma(byte_to_float(qny, j), sny, any_);
-                    const float tnz = rt2_fma(byte_to_float(qnz, j), snz, anz);
-                    const float tfx = rt2_fma(byte_to_float(qfx, j), sfx, afx);
-                    const float tfy = rt2_fma(byte_to_float(qfy, j), sfy, afy);
-                    const float tfz = rt2_fma(byte_to_float(qfz, j), sfz, afz);
-                    const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, ray.tmin));
-                    const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar_limit));
-                    if (tn <= tf) hitmask |= rt2_byte(child_bits4, j) << rt2_byte(bit_index4, j);
-                }
-            }
-            ngroup.x = n1.x;
-            ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
-            tgroup.x = n1.y;
-            tgroup.y = hitmask & 0x00FFFFFFu;
+            cwbvh_node_step(nodes, rp, ray.tmin, fminf(*t_limit, ray.tmax), ngroup, tgroup, stack, sp);
         } else {
             tgroup = ngroup;
             ngroup = make_uint2(0u, 0u);

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -114,6 +115,7 @@ struct rt2_ctx {
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
     int trace_blocks_per_sm[2] = {1, 1};
+    int trace_variant = 0;
     std::vector<cudaEvent_t> prof_events;   // RT2_LAUNCH_PROFILE: 3 per wavefront iteration (before trace, after trace, after shade)
     uint64_t device_bytes = 0;
     // lights / pdf textures (K10/K12)

@@ -78,6 +78,7 @@ __device__ __forceinline__ void setup_primary_ray(const rt2_planar_view_constant
 
 #define RT2_BACKGROUND_DEPTH 100000.0f   /* ShaderParameters.glsl:12 */
 #define RT2_K1_TMIN 0.001f               /* refrence.rgen:27 */
+#define RT2_DEFAULT_TRACE_VARIANT 5
 
 // texture(textures[idx], uv).rgb at implicit LOD 0 — Hit.glsl:35-37; R8G8B8A8_SRGB, REPEAT; pinned
 // filter identical to the oracle's sample_texture.
@@ -217,6 +218,93 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs a) {
             a.st_hit[slot] = make_float4(best.t, best.u, best.v, __uint_as_float(tri_slot));
             if (INSTANCED) a.st_hit_inst[slot] = best.inst;
         }
+    }
+}
+
+// Single-level traversal with dynamic ray fetch and triangle postponing (after Aila & Laine 2009 and
+// Ylitie et al. 2017): a warp keeps its lanes busy by refilling finished lanes from the queue once
+// enough lane-iterations have been lost, and a lane whose triangle group would run with fewer than
+// POSTPONE_PCT % of the warp's live lanes pushes it back and keeps walking nodes.  The closest hit is a
+// total order (hit_closer), so the result does not depend on any of this scheduling.
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY>
+__global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
+    const uint32_t count = *a.count;
+    const uint32_t lane = threadIdx.x & 31u;
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(a.stat_rays, (unsigned long long)count);
+    uint2 stack[RT2_STACK_SIZE];
+    int sp = 0;
+    bool active = false, exhausted = false;
+    uint32_t slot = 0, tri_slot = 0xFFFFFFFFu;
+    RayPrep rp = make_ray_prep(v3(0.f, 0.f, 0.f), v3(1.f, 1.f, 1.f));
+    RayShear sh = make_shear(v3(1.f, 1.f, 1.f));
+    Hit best; best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
+    uint2 ngroup = make_uint2(0u, 0u), tgroup = make_uint2(0u, 0u);
+    for (;;) {
+        const uint32_t need = __ballot_sync(0xFFFFFFFFu, !active);
+        if (!exhausted && (need == 0xFFFFFFFFu || (REFILL_MIN > 0 && __popc(need) >= REFILL_MIN))) {
+            const uint32_t n = __popc(need);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(a.head, n);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (!active) {
+                const uint32_t idx = base + __popc(need & ((1u << lane) - 1u));
+                if (idx < count) {
+                    slot = a.queue[idx];
+                    const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot];
+                    const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r0.w, r1.x, r1.y);
+                    rp = make_ray_prep(o, d);
+                    sh = make_shear(d);
+                    best.t = INFINITY; best.u = best.v = 0.f; best.geom = best.prim = 0xFFFFFFFFu;
+                    tri_slot = 0xFFFFFFFFu;
+                    sp = 0; ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
+                    active = true;
+                }
+            }
+            if (base + n >= count) exhausted = true;
+        }
+        const uint32_t act = __ballot_sync(0xFFFFFFFFu, active);
+        if (act == 0u) break;
+        int budget = CHECK_EVERY;
+        if (active) {
+            for (;;) {
+                if (ngroup.y > 0x00FFFFFFu) {
+                    cwbvh_node_step(a.blas_nodes, rp, RT2_K1_TMIN, fminf(best.t, RT2_BACKGROUND_DEPTH), ngroup, tgroup, stack, sp);
+                } else {
+                    tgroup = ngroup;
+                    ngroup = make_uint2(0u, 0u);
+                }
+                const int in_loop = __popc(__activemask());
+                while (tgroup.y != 0u) {
+                    if (POSTPONE_PCT > 0) {
+                        if (__popc(__activemask()) * 100 < in_loop * POSTPONE_PCT && sp < RT2_STACK_SIZE) { stack[sp++] = tgroup; break; }
+                    }
+                    const uint32_t ti = rt2_fhs(tgroup.y);
+                    tgroup.y &= ~(1u << ti);
+                    const uint32_t s = tgroup.x + ti;
+                    const TriPos* tp = a.tris + s;
+                    const float4 va = ld16f(&tp->v0), vb = ld16f(&tp->v1), vc = ld16f(&tp->v2);
+                    float t, u, v;
+                    if (ray_triangle(v3(rp.ox, rp.oy, rp.oz), sh, RT2_K1_TMIN, RT2_BACKGROUND_DEPTH, v3(va.x, va.y, va.z), v3(vb.x, vb.y, vb.z),
+                                     v3(vc.x, vc.y, vc.z), &t, &u, &v)) {
+                        const uint32_t geom = f2u(va.w), prim = f2u(vb.w);
+                        if (hit_closer(t, 0u, geom, prim, best)) {
+                            best.t = t; best.u = u; best.v = v; best.inst = 0u; best.geom = geom; best.prim = prim;
+                            tri_slot = s;
+                        }
+                    }
+                }
+                if (ngroup.y <= 0x00FFFFFFu) {
+                    if (sp == 0) {
+                        a.st_hit[slot] = make_float4(best.t, best.u, best.v, __uint_as_float(tri_slot));
+                        active = false;
+                        break;
+                    }
+                    ngroup = stack[--sp];
+                }
+                if (REFILL_MIN > 0 && !exhausted && --budget == 0) break;
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -404,6 +492,25 @@ static int ensure_counters(rt2_ctx* ctx, uint32_t iterations) {
     return RT2_OK;
 }
 
+// single-level trace variants (RT2_TRACE_VARIANT, read once per context: A/B runs on the GPU box)
+typedef void (*trace_kernel_t)(TraceArgs);
+static const trace_kernel_t g_trace_variants[] = {
+    k_trace<false>,            // 0: static 32-ray batches
+    k_trace_dyn<20, 0, 0>,     // 1: postponing 20 %, whole-warp refill only
+    k_trace_dyn<10, 0, 0>,     // 2
+    k_trace_dyn<30, 0, 0>,     // 3
+    k_trace_dyn<20, 8, 16>,    // 4: + refill when >= 8 lanes idle, checked every 16 iterations
+    k_trace_dyn<20, 4, 8>,     // 5
+    k_trace_dyn<20, 2, 4>,     // 6
+    k_trace_dyn<25, 4, 4>,     // 7
+    k_trace_dyn<15, 6, 8>,     // 8
+    k_trace_dyn<20, 4, 12>,    // 9
+};
+static const int g_num_trace_variants = (int)(sizeof(g_trace_variants) / sizeof(g_trace_variants[0]));
+static void launch_trace_single(rt2_ctx* ctx, const TraceArgs& t) {
+    g_trace_variants[ctx->trace_variant]<<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+}
+
 int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp) {
     int rc = check_ready(ctx); if (rc) return rc;
     FrameBuffers& f = ctx->fb;
@@ -461,7 +568,7 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
             if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], ctx->stream));
             t.queue = q[it & 1]; t.count = f.counters + 4 + 2 * it; t.head = f.counters + 5 + 2 * it;
             if (s.num_instances) k_trace<true><<<trace_blocks, 128, 0, ctx->stream>>>(t);
-            else k_trace<false><<<trace_blocks, 128, 0, ctx->stream>>>(t);
+            else launch_trace_single(ctx, t);
             if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], ctx->stream));
             a.queue_in = q[it & 1]; a.count_in = t.count; a.queue_out = q[(it + 1) & 1]; a.count_out = f.counters + 4 + 2 * (it + 1);
             k_k1_shade<<<shade_blocks, 256, 0, ctx->stream>>>(a);
@@ -479,7 +586,9 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
 
 int render_init(rt2_ctx* ctx) {
     int b0 = 0, b1 = 0;
-    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, k_trace<false>, 128, 0));
+    ctx->trace_variant = RT2_DEFAULT_TRACE_VARIANT;
+    if (const char* e = getenv("RT2_TRACE_VARIANT")) { int v = atoi(e); if (v >= 0 && v < g_num_trace_variants) ctx->trace_variant = v; }
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, g_trace_variants[ctx->trace_variant], 128, 0));
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<true>, 128, 0));
     ctx->trace_blocks_per_sm[0] = std::max(b0, 1); ctx->trace_blocks_per_sm[1] = std::max(b1, 1);
     return RT2_OK;
