@@ -43,8 +43,41 @@ def lib():
         L.orc_primary_ray.restype = None; L.orc_primary_ray.argtypes = [VP, u32, u32, VP, VP]
         L.orc_cos_hemisphere_dir.restype = None; L.orc_cos_hemisphere_dir.argtypes = [VP, f32, f32, u32, VP]
         L.orc_sample_texture.restype = None; L.orc_sample_texture.argtypes = [VP, u32, f32, f32, VP]
+        L.orc_prepare_lights.restype = C.c_int
+        L.orc_prepare_lights.argtypes = [VP, VP, C.POINTER(u32), VP, VP, u32, C.POINTER(u32), VP, u32, u32]
+        L.orc_generate_mips.restype = C.c_int; L.orc_generate_mips.argtypes = [VP, C.c_int, VP, u32, u32, u32]
+        L.orc_postprocess.restype = C.c_int; L.orc_postprocess.argtypes = [VP, VP, u32, u32] + [VP] * 8
+        L.orc_pack_r11g11b10.restype = u32; L.orc_pack_r11g11b10.argtypes = [VP]
+        L.orc_unpack_r11g11b10.restype = None; L.orc_unpack_r11g11b10.argtypes = [u32, VP]
+        L.orc_pack_rgba8_gamma.restype = u32; L.orc_pack_rgba8_gamma.argtypes = [VP]
+        L.orc_unpack_rgba8_gamma.restype = None; L.orc_unpack_rgba8_gamma.argtypes = [u32, VP]
+        L.orc_ndir_to_oct_unorm32.restype = u32; L.orc_ndir_to_oct_unorm32.argtypes = [VP]
+        L.orc_oct_unorm32_to_ndir.restype = None; L.orc_oct_unorm32_to_ndir.argtypes = [u32, VP]
+        L.orc_store_triangle_light.restype = None; L.orc_store_triangle_light.argtypes = [VP, VP, VP, VP, VP, C.POINTER(f32)]
+        L.orc_create_triangle_light.restype = None; L.orc_create_triangle_light.argtypes = [VP] * 6 + [C.POINTER(f32)]
+        L.orc_tonemap.restype = u32; L.orc_tonemap.argtypes = [VP]
         _lib = L
     return _lib
+
+
+def _f(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def mip_dims(w, h, mips):
+    return [(max(1, w >> k), max(1, h >> k)) for k in range(mips)]
+
+
+def split_mips(packed, w, h, mips):
+    out, off = [], 0
+    for mw, mh in mip_dims(w, h, mips):
+        out.append(packed[off:off + mw * mh].reshape(mh, mw)); off += mw * mh
+    return out
+
+
+class _SceneHead(C.Structure):   # leading fields of rt2_scene_desc (include/rt2_abi.h)
+    _fields_ = [("vertices", VP), ("num_vertices", u64), ("indices", VP), ("num_indices", u64),
+                ("geometries", VP), ("index_counts", VP), ("num_geometries", u32)]
 
 
 class OracleScene:
@@ -53,6 +86,7 @@ class OracleScene:
         self._p = self._L.orc_scene_create(C.cast(scene_desc_ptr, VP))
         if not self._p:
             raise RuntimeError("orc_scene_create failed")
+        self.num_geometries = int(C.cast(scene_desc_ptr, C.POINTER(_SceneHead)).contents.num_geometries)
 
     def close(self):
         if self._p:
@@ -82,3 +116,32 @@ class OracleScene:
                                           d32.ctypes.data_as(VP), C.byref(rays))
         assert rc == 0
         return d16, s16, d32, rays.value
+
+    # ---- K10 / K12 / K13 ---------------------------------------------------------------------------------
+    def prepare_lights(self, pdf_w=0, pdf_h=0):
+        """returns (tasks[n,4] u32, geom_to_light u32, lights[n,12] u32, pdf_mip0 f32 or None)"""
+        L = self._L
+        nt, nl = u32(0), u32(0)
+        assert L.orc_prepare_lights(self._p, None, C.byref(nt), None, None, 0, C.byref(nl), None, 0, 0) == 0
+        ng = self.num_geometries
+        tasks = np.zeros((max(ng, 1), 4), np.uint32); g2l = np.zeros(max(ng, 1), np.uint32)
+        lights = np.zeros((max(nl.value, 1), 12), np.uint32)
+        pdf = np.zeros((pdf_h, pdf_w), np.float32) if pdf_w and pdf_h else None
+        rc = L.orc_prepare_lights(self._p, tasks.ctypes.data_as(VP), C.byref(nt), g2l.ctypes.data_as(VP), lights.ctypes.data_as(VP),
+                                  lights.shape[0], C.byref(nl), pdf.ctypes.data_as(VP) if pdf is not None else None, pdf_w, pdf_h)
+        assert rc == 0
+        return tasks[:nt.value], g2l[:ng], lights[:nl.value], pdf
+
+    def generate_mips(self, which, packed, w, h, mips):
+        assert packed.flags["C_CONTIGUOUS"]
+        rc = self._L.orc_generate_mips(self._p, which, packed.ctypes.data_as(VP), w, h, mips)
+        assert rc == 0, rc
+        return packed
+
+    def postprocess(self, gconst, w, h, diffuse_f16, specular_f16=None, gb_depth=None, gb_albedo=None, gb_specrough=None, gb_emissive=None):
+        out = np.zeros((h, w, 4), np.uint8); mv = np.zeros((h, w, 4), np.float32)
+        p = lambda a: a.ctypes.data_as(VP) if a is not None else None
+        rc = self._L.orc_postprocess(self._p, C.cast(C.byref(gconst), VP), w, h, p(diffuse_f16), p(specular_f16), p(gb_depth), p(gb_albedo),
+                                     p(gb_specrough), p(gb_emissive), p(mv), p(out))
+        assert rc == 0, rc
+        return out, mv

@@ -863,3 +863,5 @@ void orc_sample_texture(const orc_scene* s, uint32_t ti, float u, float v, float
 }
 
 }  // extern "C"
+
+#include "rt2_oracle_passes.inc"

@@ -56,6 +56,34 @@ void     orc_cos_hemisphere_dir(const float n[3], float r1, float r2, uint32_t f
 /* texture(textures[idx], uv).rgb with the pinned LOD-0 filter (Hit.glsl:35-37) */
 void     orc_sample_texture(const orc_scene* s, uint32_t texture_index, float u, float v, float rgb[3]);
 
+/* ---- K10 prepare_lights (src/prepare_lights.rs:172-257 + prepare_lights.comp:40-126) ----------
+ * tasks / geom_to_light: capacity num_geometries; lights may be NULL to query counts only;
+ * pdf_mip0 (r32f, pdf_w x pdf_h, caller zero-fills) receives getPower() at the Z-curve texel. */
+int orc_prepare_lights(const orc_scene* s, rt2_prepare_lights_task* tasks, uint32_t* num_tasks, uint32_t* geom_to_light,
+                       rt2_light_info* lights, uint32_t light_capacity, uint32_t* num_lights,
+                       float* pdf_mip0, uint32_t pdf_w, uint32_t pdf_h);
+/* ---- K12 mip_pass (src/mip_pass.rs:122-186 + generate_mip_levels/mips.glsl) ----------------------
+ * packed = all mips back to back (mip k is max(1,w>>k) x max(1,h>>k)); which 0: r32f local-light
+ * PDF (mip 0 is the input), which 1: r16f environment PDF (mip 0 is written from the sky). */
+int orc_generate_mips(const orc_scene* s, int which, void* packed, uint32_t w, uint32_t h, uint32_t mips);
+/* ---- K13 postprocess (post_processing.comp:152-191) -------------------------------------------- */
+int orc_postprocess(const orc_scene* s, const void* gconst, uint32_t width, uint32_t height,
+                    const uint16_t* diffuse_f16, const uint16_t* specular_f16, const float* gb_depth,
+                    const uint32_t* gb_diffuse_albedo, const uint32_t* gb_specular_rough, const uint16_t* gb_emissive,
+                    float* motion_vectors, uint8_t* out_rgba8);
+/* codec / light KAT probes (packing.glsl, Helpers.glsl:251-332, PolymorphicLight.glsl:320-357) */
+uint32_t orc_pack_r11g11b10(const float rgb[3]);
+void     orc_unpack_r11g11b10(uint32_t p, float rgb[3]);
+uint32_t orc_pack_rgba8_gamma(const float c[4]);
+void     orc_unpack_rgba8_gamma(uint32_t p, float c[4]);
+uint32_t orc_ndir_to_oct_unorm32(const float n[3]);
+void     orc_oct_unorm32_to_ndir(uint32_t p, float n[3]);
+void     orc_store_triangle_light(const float base[3], const float edge1[3], const float edge2[3], const float radiance[3],
+                                  rt2_light_info* out, float* power);
+void     orc_create_triangle_light(const rt2_light_info* li, float base[3], float edge1[3], float edge2[3], float radiance[3],
+                                   float normal[3], float* area);
+uint32_t orc_tonemap(const float rgb[3]);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,7 +20,9 @@ int fail(rt2_ctx* ctx, int code, const std::string& msg) {
 int lights_prepare(rt2_ctx* ctx);
 int mips_generate(rt2_ctx* ctx, int which);
 int post_process(rt2_ctx* ctx, uint32_t frame);
-void passes_release(rt2_ctx* ctx);
+void passes_release(rt2_ctx* ctx);          // everything the passes own
+void passes_release_frame(rt2_ctx* ctx);    // per-size resources only
+void lights_release(rt2_ctx* ctx);          // per-scene light resources
 int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp);
 bool pass_buffer(rt2_ctx* ctx, int which, void** ptr, size_t* bytes);
 }  // namespace rt2
@@ -84,9 +86,9 @@ const char* rt2_last_error(rt2_ctx* ctx) {
     return copy.c_str();
 }
 
-int rt2_upload_scene(rt2_ctx* ctx, const rt2_scene_desc* scene) { RT2_GUARD(ctx); return scene_upload(ctx, scene); }
+int rt2_upload_scene(rt2_ctx* ctx, const rt2_scene_desc* scene) { RT2_GUARD(ctx); RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); lights_release(ctx); return scene_upload(ctx, scene); }
 int rt2_build_accel(rt2_ctx* ctx) { RT2_GUARD(ctx); return scene_build_accel(ctx); }
-int rt2_resize(rt2_ctx* ctx, uint32_t w, uint32_t h) { RT2_GUARD(ctx); passes_release(ctx); return frame_resize(ctx, w, h); }
+int rt2_resize(rt2_ctx* ctx, uint32_t w, uint32_t h) { RT2_GUARD(ctx); RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); passes_release_frame(ctx); return frame_resize(ctx, w, h); }
 
 int rt2_set_constants(rt2_ctx* ctx, const void* gconst, size_t nbytes) {
     RT2_GUARD(ctx);

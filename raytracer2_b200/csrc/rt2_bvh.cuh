@@ -93,7 +93,13 @@ struct RayPrep {
 };
 RT2_HD RayPrep make_ray_prep(const V3& o, const V3& d) {
     RayPrep r;
-    const float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
+    // |1/d| is capped at 2^60: a zero (or denormal-small) direction component would otherwise give inf and
+    // then NaN slab distances (0 * inf), which fminf/fmaxf drop — still conservative, but such a ray walks
+    // every node the other two axes admit (one ray in ~2^23 after a cosine bounce off an axis-aligned wall,
+    // costing milliseconds).  With the cap the slab test degenerates to "is the origin inside the slab".
+    const float cap = 1.152921504606846976e18f;
+    float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
+    idx = copysignf(fminf(fabsf(idx), cap), idx); idy = copysignf(fminf(fabsf(idy), cap), idy); idz = copysignf(fminf(fabsf(idz), cap), idz);
     r.ox = o.x; r.oy = o.y; r.oz = o.z;
     r.inx = idx * (1.0f - RT2_SLAB_EPS); r.iny = idy * (1.0f - RT2_SLAB_EPS); r.inz = idz * (1.0f - RT2_SLAB_EPS);
     r.ifx = idx * (1.0f + RT2_SLAB_EPS); r.ify = idy * (1.0f + RT2_SLAB_EPS); r.ifz = idz * (1.0f + RT2_SLAB_EPS);

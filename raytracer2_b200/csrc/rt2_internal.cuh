@@ -94,6 +94,18 @@ struct FrameBuffers {
     float4* st_hit = nullptr;
     uint32_t* st_hit_inst = nullptr;
     uint32_t *queue0 = nullptr, *queue1 = nullptr;
+    // ReSTIR-side per-size resources (RenderResources::new, src/render_resources.rs:48-101,191-206,287-317); allocated on first use
+    float* gb_depth[2] = {nullptr, nullptr};             // r32f, ping-pong by frame % 2 (src/light_passes.rs:565-577)
+    uint32_t* gb_normals[2] = {nullptr, nullptr};        // r32ui oct
+    uint32_t* gb_geo_normals[2] = {nullptr, nullptr};
+    uint32_t* gb_diffuse_albedo[2] = {nullptr, nullptr}; // R11G11B10
+    uint32_t* gb_specular_rough[2] = {nullptr, nullptr}; // RGBA8 gamma
+    ushort4* gb_emissive[2] = {nullptr, nullptr};        // rgba16f
+    float4* motion_vectors = nullptr;                    // rgba32f
+    rt2_packed_di_reservoir* di_reservoirs = nullptr;    // arrayPitch x 2
+    uint4* gi_reservoirs = nullptr;                      // 32 B x arrayPitch x 2
+    uint4* secondary_gbuffer = nullptr;                  // 48 B x W x H
+    uint32_t reservoir_block_row_pitch = 0, reservoir_array_pitch = 0;
     uint32_t* counters = nullptr;      // [0..1] u64 rays, [2..3] u64 hits, then (count, head) per wavefront iteration
     size_t counter_capacity = 0;
 };
@@ -122,6 +134,8 @@ struct rt2_ctx {
     rt2_light_info* light_info = nullptr; uint32_t light_capacity = 0;
     uint32_t* geom_to_light = nullptr;
     rt2_prepare_lights_task* light_tasks = nullptr; uint32_t num_light_tasks = 0;
+    bool lights_prepared = false;
+    uint32_t last_gbuffer_index = 0;     // frame % 2 of the last ReSTIR-mode render: which G-buffer set rt2_read returns
     float* local_pdf = nullptr; uint32_t local_pdf_w = 0, local_pdf_h = 0, local_pdf_mips = 0;   // all mips, packed
     uint16_t* env_pdf = nullptr; uint32_t env_pdf_w = 0, env_pdf_h = 0, env_pdf_mips = 0;        // r16f, packed mips
 };

@@ -1,0 +1,88 @@
+// rt2_passes_common.cu — resources shared by the light / G-buffer / reservoir / post passes and their
+// read-out through rt2_read (RenderResources, src/render_resources.rs:130-341).
+#include "rt2_internal.cuh"
+
+namespace rt2 {
+
+void lights_release(rt2_ctx* ctx);
+size_t mip_chain_texels(uint32_t w, uint32_t h, uint32_t mips);
+
+void passes_release_frame(rt2_ctx* ctx) {
+    FrameBuffers& f = ctx->fb;
+    for (int i = 0; i < 2; i++) {
+        void* ptrs[] = {f.gb_depth[i], f.gb_normals[i], f.gb_geo_normals[i], f.gb_diffuse_albedo[i], f.gb_specular_rough[i], f.gb_emissive[i]};
+        for (void* p : ptrs) if (p) cudaFree(p);
+        f.gb_depth[i] = nullptr; f.gb_normals[i] = f.gb_geo_normals[i] = f.gb_diffuse_albedo[i] = f.gb_specular_rough[i] = nullptr; f.gb_emissive[i] = nullptr;
+    }
+    void* ptrs[] = {f.motion_vectors, f.di_reservoirs, f.gi_reservoirs, f.secondary_gbuffer};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    f.motion_vectors = nullptr; f.di_reservoirs = nullptr; f.gi_reservoirs = nullptr; f.secondary_gbuffer = nullptr;
+    f.reservoir_block_row_pitch = f.reservoir_array_pitch = 0;
+}
+
+void passes_release(rt2_ctx* ctx) { passes_release_frame(ctx); lights_release(ctx); }
+
+template <class T>
+static cudaError_t zalloc(rt2_ctx* ctx, T** p, size_t n) {
+    cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T));
+    if (e == cudaSuccess) { ctx->device_bytes += std::max<size_t>(n, 1) * sizeof(T); e = cudaMemsetAsync(*p, 0, std::max<size_t>(n, 1) * sizeof(T), ctx->stream); }
+    return e;
+}
+
+// G-buffers x2, motion vectors, DI/GI reservoirs, secondary G-buffer — allocated on the first ReSTIR-mode render
+int restir_ensure_resources(rt2_ctx* ctx) {
+    FrameBuffers& f = ctx->fb;
+    if (!f.width) return fail(ctx, RT2_E_STATE, "no frame buffers: call rt2_resize first");
+    if (f.gb_depth[0]) return RT2_OK;
+    const size_t n = (size_t)f.width * f.height;
+    for (int i = 0; i < 2; i++) {
+        RT2_CUDA(ctx, zalloc(ctx, &f.gb_depth[i], n)); RT2_CUDA(ctx, zalloc(ctx, &f.gb_normals[i], n)); RT2_CUDA(ctx, zalloc(ctx, &f.gb_geo_normals[i], n));
+        RT2_CUDA(ctx, zalloc(ctx, &f.gb_diffuse_albedo[i], n)); RT2_CUDA(ctx, zalloc(ctx, &f.gb_specular_rough[i], n)); RT2_CUDA(ctx, zalloc(ctx, &f.gb_emissive[i], n));
+    }
+    RT2_CUDA(ctx, zalloc(ctx, &f.motion_vectors, n));
+    // src/light_passes.rs:718-731 calculate_reservoir_buffer_parameters (RTXDI_RESERVOIR_BLOCK_SIZE = 16)
+    const uint32_t wb = (f.width + 15u) / 16u, hb = (f.height + 15u) / 16u;
+    f.reservoir_block_row_pitch = wb * 256u; f.reservoir_array_pitch = f.reservoir_block_row_pitch * hb;
+    RT2_CUDA(ctx, zalloc(ctx, &f.di_reservoirs, (size_t)f.reservoir_array_pitch * 2));    // src/render_resources.rs:191-198
+    RT2_CUDA(ctx, zalloc(ctx, &f.gi_reservoirs, (size_t)f.reservoir_array_pitch * 2 * 2)); // 32 B each, :199-206
+    RT2_CUDA(ctx, zalloc(ctx, &f.secondary_gbuffer, n * 3));                               // 48 B each, :309-317
+    return RT2_OK;
+}
+
+bool pass_buffer(rt2_ctx* ctx, int which, void** ptr, size_t* bytes) {
+    const FrameBuffers& f = ctx->fb;
+    const size_t n = (size_t)f.width * f.height;
+    const uint32_t cur = ctx->last_gbuffer_index & 1u;
+    auto mip = [&](void* base, uint32_t w, uint32_t h, uint32_t mips, uint32_t k, size_t texel) -> bool {
+        if (!base || k >= mips) return false;
+        size_t off = 0;
+        for (uint32_t j = 0; j < k; j++) off += (size_t)std::max(1u, w >> j) * std::max(1u, h >> j);
+        *ptr = (char*)base + off * texel; *bytes = (size_t)std::max(1u, w >> k) * std::max(1u, h >> k) * texel;
+        return true;
+    };
+    if (which >= RT2_BUF_LOCAL_PDF_MIP0 && which < RT2_BUF_LOCAL_PDF_MIP0 + 32)
+        return mip(ctx->local_pdf, ctx->local_pdf_w, ctx->local_pdf_h, ctx->local_pdf_mips, (uint32_t)(which - RT2_BUF_LOCAL_PDF_MIP0), 4);
+    if (which >= RT2_BUF_ENV_PDF_MIP0 && which < RT2_BUF_ENV_PDF_MIP0 + 32)
+        return mip(ctx->env_pdf, ctx->env_pdf_w, ctx->env_pdf_h, ctx->env_pdf_mips, (uint32_t)(which - RT2_BUF_ENV_PDF_MIP0), 2);
+    switch (which) {
+        case RT2_BUF_LIGHT_INFO: *ptr = ctx->light_info; *bytes = (size_t)ctx->light_capacity * sizeof(rt2_light_info); return ctx->light_info && ctx->light_capacity;
+        case RT2_BUF_GEOM_TO_LIGHT: *ptr = ctx->geom_to_light; *bytes = (size_t)ctx->scene.num_geoms * 4; return ctx->geom_to_light && ctx->scene.num_geoms;
+        case RT2_BUF_LIGHT_TASKS: *ptr = ctx->light_tasks; *bytes = (size_t)ctx->num_light_tasks * sizeof(rt2_prepare_lights_task); return ctx->light_tasks && ctx->num_light_tasks;
+        case RT2_BUF_GBUFFER_DEPTH: *ptr = f.gb_depth[cur]; *bytes = n * 4; return f.gb_depth[cur] != nullptr;
+        case RT2_BUF_GBUFFER_NORMALS: *ptr = f.gb_normals[cur]; *bytes = n * 4; return f.gb_normals[cur] != nullptr;
+        case RT2_BUF_GBUFFER_GEO_NORMALS: *ptr = f.gb_geo_normals[cur]; *bytes = n * 4; return f.gb_geo_normals[cur] != nullptr;
+        case RT2_BUF_GBUFFER_DIFFUSE_ALBEDO: *ptr = f.gb_diffuse_albedo[cur]; *bytes = n * 4; return f.gb_diffuse_albedo[cur] != nullptr;
+        case RT2_BUF_GBUFFER_SPECULAR_ROUGH: *ptr = f.gb_specular_rough[cur]; *bytes = n * 4; return f.gb_specular_rough[cur] != nullptr;
+        case RT2_BUF_GBUFFER_EMISSIVE: *ptr = f.gb_emissive[cur]; *bytes = n * 8; return f.gb_emissive[cur] != nullptr;
+        case RT2_BUF_MOTION_VECTORS: *ptr = f.motion_vectors; *bytes = n * 16; return f.motion_vectors != nullptr;
+        case RT2_BUF_DI_RESERVOIRS: *ptr = f.di_reservoirs; *bytes = (size_t)f.reservoir_array_pitch * 2 * sizeof(rt2_packed_di_reservoir); return f.di_reservoirs != nullptr;
+        case RT2_BUF_GI_RESERVOIRS: *ptr = f.gi_reservoirs; *bytes = (size_t)f.reservoir_array_pitch * 2 * 32; return f.gi_reservoirs != nullptr;
+        case RT2_BUF_SECONDARY_GBUFFER: *ptr = f.secondary_gbuffer; *bytes = n * 48; return f.secondary_gbuffer != nullptr;
+        default: return false;
+    }
+}
+
+// temporary until rt2_passes_restir.cu lands
+int render_restir(rt2_ctx* ctx, uint32_t, const rt2_launch_params&) { return fail(ctx, RT2_E_STATE, "ReSTIR passes not built yet (set refrence_mode = 1)"); }
+
+}  // namespace rt2

@@ -200,3 +200,28 @@ def test_create_fails_loudly_without_a_device():
     with pytest.raises(rt.Rt2Error) as e:
         rt.Renderer(0)
     assert "no CPU fallback" in str(e.value) or "CUDA" in str(e.value)
+
+
+def test_axis_aligned_rays_do_not_walk_the_whole_tree(hostemu):
+    """A zero direction component used to give inf * 0 = NaN slab distances (dropped by fmin/fmax), which is
+    conservative but makes the ray visit every node the other axes admit: about one ray in 2^23 after a cosine
+    bounce off an axis-aligned wall, costing milliseconds each on the GPU.  With |1/d| capped the visit count
+    of exactly axis-aligned rays stays within 2x of the same rays tilted by 1e-6."""
+    sc = rt.Scene(rt.SCENE_HALL, 0.25, 16, 0)
+    hs = hostemu.hostemu_build(C.cast(sc.desc, C.c_void_p))
+    rng = np.random.default_rng(9)
+    n = 600
+    rays = np.zeros((n, 6), np.float32)
+    rays[:, 0] = rng.uniform(-19, 19, n); rays[:, 1] = rng.uniform(0.5, 11, n); rays[:, 2] = rng.uniform(-7, 7, n)
+    axes = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1]], np.float32)
+    rays[:, 3:] = axes[np.arange(n) % 6]
+    tilted = rays.copy()
+    tilted[:, 3:] += np.float32(1e-6)
+    out = np.zeros((n, 8), np.uint32); out2 = np.zeros((n, 8), np.uint32)
+    v_axis, v_tilt = C.c_uint64(0), C.c_uint64(0)
+    hostemu.hostemu_trace_rays(hs, rays.ctypes.data_as(C.c_void_p), n, 0.001, 1e5, out.ctypes.data_as(C.c_void_p), C.byref(v_axis))
+    hostemu.hostemu_trace_rays(hs, tilted.ctypes.data_as(C.c_void_p), n, 0.001, 1e5, out2.ctypes.data_as(C.c_void_p), C.byref(v_tilt))
+    hostemu.hostemu_destroy(hs)
+    assert v_axis.value <= 2 * v_tilt.value, (v_axis.value, v_tilt.value)
+    assert v_axis.value / n < 200
+    assert (out[:, 1] != 0xFFFFFFFF).mean() > 0.9      # closed hall: nearly every ray hits
