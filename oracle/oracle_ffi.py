@@ -56,6 +56,10 @@ def lib():
         L.orc_store_triangle_light.restype = None; L.orc_store_triangle_light.argtypes = [VP, VP, VP, VP, VP, C.POINTER(f32)]
         L.orc_create_triangle_light.restype = None; L.orc_create_triangle_light.argtypes = [VP] * 6 + [C.POINTER(f32)]
         L.orc_tonemap.restype = u32; L.orc_tonemap.argtypes = [VP]
+        L.orc_gbuffer.restype = C.c_int; L.orc_gbuffer.argtypes = [VP, VP, u32, u32, u32, C.c_int] + [VP] * 7 + [C.POINTER(u64)]
+        L.orc_di_fused_resampling.restype = C.c_int
+        L.orc_di_fused_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int] + [VP] * 5 + [VP, u32, VP, VP, u32, u32, u32, VP, VP, VP, C.POINTER(u64)]
+        L.orc_reservoir_position_to_pointer.restype = u32; L.orc_reservoir_position_to_pointer.argtypes = [u32] * 5
         _lib = L
     return _lib
 
@@ -145,3 +149,28 @@ class OracleScene:
                                      p(gb_specrough), p(gb_emissive), p(mv), p(out))
         assert rc == 0, rc
         return out, mv
+
+    # ---- K3 / K9 ---------------------------------------------------------------------------------------------
+    def gbuffer(self, gconst, w, h, flags=0, threads=0):
+        gb = {"depth": np.zeros((h, w), np.float32), "normals": np.zeros((h, w), np.uint32), "geo_normals": np.zeros((h, w), np.uint32),
+              "diffuse_albedo": np.zeros((h, w), np.uint32), "specular_rough": np.zeros((h, w), np.uint32),
+              "emissive": np.zeros((h, w, 4), np.uint16), "motion": np.zeros((h, w, 4), np.float32)}
+        rays = u64(0)
+        rc = self._L.orc_gbuffer(self._p, C.cast(C.byref(gconst), VP), w, h, flags, threads, *[gb[k].ctypes.data_as(VP) for k in
+                                 ("depth", "normals", "geo_normals", "diffuse_albedo", "specular_rough", "emissive", "motion")], C.byref(rays))
+        assert rc == 0, rc
+        return gb
+
+    def di_fused_resampling(self, gconst, frame, w, h, gb, lights, geom_to_light, pdf_packed, pdf_w, pdf_h, pdf_mips, array_pitch,
+                            diffuse_f16=None, specular_f16=None, flags=0, threads=0):
+        res = np.zeros((array_pitch * 2, 6), np.uint32)
+        d16 = np.zeros((h, w, 4), np.uint16) if diffuse_f16 is None else diffuse_f16
+        s16 = np.zeros((h, w, 4), np.uint16) if specular_f16 is None else specular_f16
+        rays = u64(0)
+        lights = np.ascontiguousarray(lights); geom_to_light = np.ascontiguousarray(geom_to_light); pdf_packed = np.ascontiguousarray(pdf_packed, np.float32)
+        rc = self._L.orc_di_fused_resampling(self._p, C.cast(C.byref(gconst), VP), frame, w, h, flags, threads,
+                                             *[np.ascontiguousarray(gb[k]).ctypes.data_as(VP) for k in ("depth", "normals", "geo_normals", "diffuse_albedo", "specular_rough")],
+                                             lights.ctypes.data_as(VP), len(lights), geom_to_light.ctypes.data_as(VP), pdf_packed.ctypes.data_as(VP), pdf_w, pdf_h, pdf_mips,
+                                             res.ctypes.data_as(VP), d16.ctypes.data_as(VP), s16.ctypes.data_as(VP), C.byref(rays))
+        assert rc == 0, rc
+        return res, d16, s16, rays.value

@@ -84,6 +84,21 @@ void     orc_create_triangle_light(const rt2_light_info* li, float base[3], floa
                                    float normal[3], float* area);
 uint32_t orc_tonemap(const float rgb[3]);
 
+/* ---- K3 g_buffer (lighting_passes/g_buffer.rgen:14-47); all images row-major W x H --------------- */
+int orc_gbuffer(const orc_scene* s, const void* gconst, uint32_t width, uint32_t height, uint32_t flags, int threads,
+                float* depth, uint32_t* normals, uint32_t* geo_normals, uint32_t* diffuse_albedo, uint32_t* specular_rough,
+                uint16_t* emissive_f16, float* motion_vectors, uint64_t* rays);
+/* ---- K9 di_fused_resampling (lighting_passes/di_fused_resampling.rgen:16-93): reads the G-buffer, the
+ * light list (K10) and the local-light PDF pyramid (K12, all mips packed), writes the packed DI
+ * reservoirs (block-linear, arrayPitch x 2) and the rgba16f lighting images (in/out). */
+int orc_di_fused_resampling(const orc_scene* s, const void* gconst, uint32_t frame, uint32_t width, uint32_t height, uint32_t flags, int threads,
+                            const float* gb_depth, const uint32_t* gb_normals, const uint32_t* gb_geo_normals, const uint32_t* gb_diffuse_albedo,
+                            const uint32_t* gb_specular_rough, const rt2_light_info* lights, uint32_t num_lights, const uint32_t* geom_to_light,
+                            const float* pdf_packed, uint32_t pdf_w, uint32_t pdf_h, uint32_t pdf_mips,
+                            rt2_packed_di_reservoir* reservoirs, uint16_t* diffuse_f16, uint16_t* specular_f16, uint64_t* rays);
+/* RTXDI_ReservoirPositionToPointer (rtxdi/RtxdiHelpers.hlsli:75-88) */
+uint32_t orc_reservoir_position_to_pointer(uint32_t block_row_pitch, uint32_t array_pitch, uint32_t x, uint32_t y, uint32_t array_index);
+
 #ifdef __cplusplus
 }
 #endif

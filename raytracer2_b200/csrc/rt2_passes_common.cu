@@ -82,7 +82,4 @@ bool pass_buffer(rt2_ctx* ctx, int which, void** ptr, size_t* bytes) {
     }
 }
 
-// temporary until rt2_passes_restir.cu lands
-int render_restir(rt2_ctx* ctx, uint32_t, const rt2_launch_params&) { return fail(ctx, RT2_E_STATE, "ReSTIR passes not built yet (set refrence_mode = 1)"); }
-
 }  // namespace rt2

@@ -1,0 +1,213 @@
+// rt2_restir.cuh — device restatement of the RTXDI application bridge and the reachable part of the
+// RTXDI SDK (SURVEY §8a rows G2, D1–D10): G-buffer surfaces, BRDF evaluation, triangle-light
+// sampling, DI reservoirs and the initial light sampling.  Citations are relative to src/shaders/ of
+// the reference tree ("bridge" = lighting_passes/RtxdiApplicationBridge.glsl).
+#pragma once
+#include "rt2_surface.cuh"
+#include "rt2_codec.cuh"
+
+namespace rt2 {
+
+#define RT2_MIN_ROUGHNESS 0.05f          /* common.glsl:3 */
+#define RT2_INVALID_LIGHT 0xFFFFFFFFu    /* rtxdi/RtxdiParameters.h:52 */
+
+// RAB_Surface, bridge :83-94
+struct Surface { V3 world_pos, view_dir; float view_depth; V3 normal, geo_normal, diffuse_albedo, specular_f0; float roughness, diffuse_probability; };
+// RAB_EmptySurface leaves everything but viewDepth uninitialised (bridge :161-166): pinned to zero
+__device__ __forceinline__ Surface empty_surface() {
+    Surface s;
+    s.world_pos = s.view_dir = s.normal = s.geo_normal = s.diffuse_albedo = s.specular_f0 = v3(0.f, 0.f, 0.f);
+    s.roughness = s.diffuse_probability = 0.f; s.view_depth = RT2_BACKGROUND_DEPTH;
+    return s;
+}
+struct GBufferRefs { const float* depth; const uint32_t* normals; const uint32_t* geo_normals; const uint32_t* diffuse_albedo; const uint32_t* specular_rough; };
+// GetGBufferSurface, bridge :296-323; viewDepthToWorldPos, GBufferHelpers.glsl:54-67
+__device__ __forceinline__ Surface gbuffer_surface(const GBufferRefs& gb, uint32_t width, int px, int py, const rt2_planar_view_constants& view) {
+    Surface s = empty_surface();
+    if ((float)px >= view.viewport_size[0] || (float)py >= view.viewport_size[1]) return s;
+    const size_t i = (size_t)py * width + (size_t)px;
+    s.view_depth = gb.depth[i];
+    if (s.view_depth == RT2_BACKGROUND_DEPTH) return s;
+    s.normal = oct_to_ndir_unorm32(gb.normals[i]);
+    s.geo_normal = oct_to_ndir_unorm32(gb.geo_normals[i]);
+    s.diffuse_albedo = unpack_r11g11b10(gb.diffuse_albedo[i]);
+    const float4 sr = unpack_rgba8_gamma(gb.specular_rough[i]);
+    s.specular_f0 = v3(sr.x, sr.y, sr.z); s.roughness = sr.w;
+    V3 o, d;
+    setup_primary_ray(view, (uint32_t)px, (uint32_t)py, &o, &d);
+    s.world_pos = o + d * s.view_depth;
+    s.view_dir = normalize3(o - s.world_pos);
+    s.diffuse_probability = 1.0f;                 // getSurfaceDiffuseProbability, bridge :131-138
+    return s;
+}
+
+// ---- BRDF: Helpers.glsl:182-239 with `#define square(a) a*a` (common.glsl:2) expanded literally (Q1) -----------
+__device__ __forceinline__ float ggx_d_literal(float alpha, float NoH) {
+    return alpha * alpha / (((RT2_RTXDI_PI * NoH * NoH * alpha * alpha) + (1 - NoH * NoH) * NoH * NoH * alpha * alpha) + (1 - NoH * NoH));
+}
+__device__ __forceinline__ float ggx_vndf_pdf(float roughness, V3 N, V3 V, V3 L) {
+    const V3 H = normalize3(L + V);
+    const float NoH = saturatef(dot3(N, H)), VoH = saturatef(dot3(V, H));
+    const float alpha = roughness * roughness;
+    const float D = ggx_d_literal(alpha, NoH);
+    return (VoH > 0.0f) ? D / (4.0f * VoH) : 0.0f;
+}
+__device__ __forceinline__ float g_smith_over_ndotv(float roughness, float NdotV, float NdotL) {
+    const float alpha = roughness * roughness;
+    const float g1 = NdotV * sqrtf(alpha * alpha + (1.0f - alpha * alpha) * NdotL * NdotL);
+    const float g2 = NdotL * sqrtf(alpha * alpha + (1.0f - alpha * alpha) * NdotV * NdotV);
+    return 2.0f * NdotL / (g1 + g2);
+}
+__device__ __forceinline__ V3 ggx_times_ndotl(V3 V, V3 L, V3 N, float roughness, V3 F0) {
+    const V3 H = normalize3(L + V);
+    const float NoL = saturatef(dot3(N, L)), VoH = saturatef(dot3(V, H)), NoV = saturatef(dot3(N, V)), NoH = saturatef(dot3(N, H));
+    if (NoL > 0) {
+        const float G = g_smith_over_ndotv(roughness, NoV, NoL);
+        const float alpha = roughness * roughness;
+        const float D = ggx_d_literal(alpha, NoH);
+        const float p = pow_pinned(fmaxf(1 - VoH, 0.f), 5.0f);            // Schlick_Fresnel
+        const V3 F = v3(F0.x + (1 - F0.x) * p, F0.y + (1 - F0.y) * p, F0.z + (1 - F0.z) * p);
+        return F * (D * G / 4);
+    }
+    return v3(0.f, 0.f, 0.f);
+}
+__device__ __forceinline__ float lambert(V3 normal, V3 light_incident) { return fmaxf(0.f, -dot3(normal, light_incident)) / RT2_RTXDI_PI; }
+// RAB_GetSurfaceBrdfPdf, bridge :463-470
+__device__ __forceinline__ float surface_brdf_pdf(const Surface& s, V3 dir) {
+    const float cos_theta = saturatef(dot3(s.normal, dir));
+    const float diffuse_pdf = cos_theta / RT2_RTXDI_PI;
+    const float specular_pdf = ggx_vndf_pdf(fmaxf(s.roughness, RT2_MIN_ROUGHNESS), s.normal, s.view_dir, dir);
+    return cos_theta > 0.f ? mixf(specular_pdf, diffuse_pdf, s.diffuse_probability) : 0.f;
+}
+// RAB_GetSurfaceBrdfSample, bridge :437-461 (diffuseProbability == 1: only the cosine lobe is reachable)
+__device__ __forceinline__ bool surface_brdf_sample(const Surface& s, Rng& rng, V3* dir) {
+    const float rx = rng_next(rng), ry = rng_next(rng), rz = rng_next(rng);
+    (void)rx;
+    *dir = tangent_to_world(s.normal, sample_cos_hemisphere(ry, rz, false));
+    return dot3(s.normal, *dir) > 0.f;
+}
+
+// ---- light samples: bridge :96-103, :478-525; PolymorphicLight.glsl:266-294 ------------------------------------
+struct LightSample { V3 position, normal, radiance; float solid_angle_pdf; uint32_t light_type; };
+__device__ __forceinline__ LightSample empty_light_sample() {
+    LightSample s; s.position = s.normal = s.radiance = v3(0.f, 0.f, 0.f); s.solid_angle_pdf = 0.f; s.light_type = 0u; return s;
+}
+__device__ __forceinline__ rt2_light_info load_light_info(const rt2_light_info* lights, uint32_t index) {
+    const uint4* p = reinterpret_cast<const uint4*>(lights + index);
+    const uint4 a = __ldg(p), b = __ldg(p + 1);      // uint4[2] holds only shaping data (unused for triangle lights)
+    rt2_light_info li;
+    li.center[0] = __uint_as_float(a.x); li.center[1] = __uint_as_float(a.y); li.center[2] = __uint_as_float(a.z); li.color_type_and_flags = a.w;
+    li.direction1 = b.x; li.direction2 = b.y; li.scalars = b.z; li.log_radiance = b.w;
+    li.ies_profile_index = li.primary_axis = li.cos_cone_angle_and_softness = li.padding = 0u;
+    return li;
+}
+__device__ __forceinline__ LightSample sample_polymorphic_light(const rt2_light_info& li, const Surface& surface, float uvx, float uvy) {
+    LightSample out = empty_light_sample();
+    out.light_type = (li.color_type_and_flags >> RT2_LIGHT_TYPE_SHIFT) & RT2_LIGHT_TYPE_MASK;
+    if (out.light_type != RT2_LIGHT_TRIANGLE) return out;
+    const TriangleLight self = create_triangle_light(li);
+    const float sqrtx = sqrtf(uvx);                                       // sampleTriangle, Helpers.glsl:66-74
+    const float by = sqrtx * (1 - uvy), bz = sqrtx * uvy;
+    out.position = (self.base + self.edge1 * by) + self.edge2 * bz;
+    out.normal = self.normal;
+    V3 L = out.position - surface.world_pos;                             // calcTriangleSolidAnglePdf
+    const float Ldist = length3(L);
+    L = L / Ldist;
+    const float area_pdf = 1.0f / self.surface_area;
+    const float cos_theta = clampf(dot3(L, neg3(out.normal)), 0.0f, 1.0f);
+    out.solid_angle_pdf = area_pdf * (Ldist * Ldist) / cos_theta;        // pdfAtoW
+    out.radiance = self.radiance;
+    if (out.solid_angle_pdf > 0) out.radiance = out.radiance * v3(1.0f, 1.0f, 1.0f);   // evaluateLightShaping with isSpot == 0
+    return out;
+}
+__device__ __forceinline__ float light_sample_target_pdf(const LightSample& ls, const Surface& s) {
+    if (ls.solid_angle_pdf <= 0) return 0;
+    const V3 L = normalize3(ls.position - s.world_pos);
+    if (dot3(L, s.geo_normal) <= 0) return 0;
+    const float d = lambert(s.normal, neg3(L));
+    const V3 sp = s.roughness == 0 ? v3(0.f, 0.f, 0.f) : ggx_times_ndotl(s.view_dir, L, s.normal, fmaxf(s.roughness, RT2_MIN_ROUGHNESS), s.specular_f0);
+    const V3 reflected = ls.radiance * (s.diffuse_albedo * d + sp);
+    return calc_luminance(reflected) / ls.solid_angle_pdf;
+}
+
+// ---- DI reservoirs: rtxdi/DIReservoir.hlsli:28-340 ----------------------------------------------------------------
+struct DIReservoir { uint32_t light_data, uv_data; float weight_sum, target_pdf, M; uint32_t packed_visibility; int sdx, sdy; uint32_t age; };
+__device__ __forceinline__ DIReservoir empty_di_reservoir() {
+    DIReservoir r; r.light_data = r.uv_data = 0u; r.weight_sum = r.target_pdf = r.M = 0.f; r.packed_visibility = 0u; r.sdx = r.sdy = 0; r.age = 0u; return r;
+}
+__device__ __forceinline__ bool di_valid(const DIReservoir& r) { return r.light_data != 0u; }
+__device__ __forceinline__ rt2_packed_di_reservoir pack_di_reservoir(const DIReservoir& r) {
+    const int cx = min(max(r.sdx, -127), 127), cy = min(max(r.sdy, -127), 127);
+    rt2_packed_di_reservoir d;
+    d.light_data = r.light_data; d.uv_data = r.uv_data;
+    d.m_visibility = r.packed_visibility | (min((uint32_t)r.M, 0x3fffu) << 18);
+    d.distance_age = ((uint32_t)cx & 0xffu) | (((uint32_t)cy & 0xffu) << 8) | (min(r.age, 0xffu) << 16);
+    d.target_pdf = r.target_pdf; d.weight = r.weight_sum;
+    return d;
+}
+// RTXDI_ReservoirPositionToPointer, rtxdi/RtxdiHelpers.hlsli:75-88 (16x16 block-linear)
+__device__ __forceinline__ uint32_t reservoir_pointer(uint32_t block_row_pitch, uint32_t array_pitch, uint32_t x, uint32_t y, uint32_t array_index) {
+    return array_index * array_pitch + (y / 16u) * block_row_pitch + (x / 16u) * 256u + (y % 16u) * 16u + (x % 16u);
+}
+__device__ __forceinline__ void di_store_visibility(DIReservoir& r, V3 vis, bool discard_if_invisible) {
+    r.packed_visibility = (uint32_t)(saturatef(vis.x) * 63.0f) | ((uint32_t)(saturatef(vis.y) * 63.0f) << 6) | ((uint32_t)(saturatef(vis.z) * 63.0f) << 12);
+    r.sdx = r.sdy = 0; r.age = 0u;
+    if (discard_if_invisible && vis.x == 0 && vis.y == 0 && vis.z == 0) { r.light_data = 0u; r.weight_sum = 0.f; }
+}
+__device__ __forceinline__ bool di_stream_sample(DIReservoir& r, uint32_t light_index, float uvx, float uvy, float random, float target_pdf, float inv_source_pdf) {
+    const float ris_weight = target_pdf * inv_source_pdf;
+    r.M += 1;
+    r.weight_sum += ris_weight;
+    const bool select = (random * r.weight_sum < ris_weight);
+    if (select) {
+        r.light_data = light_index | 0x80000000u;
+        r.uv_data = (uint32_t)(saturatef(uvx) * 65535.0f) | ((uint32_t)(saturatef(uvy) * 65535.0f) << 16);
+        r.target_pdf = target_pdf;
+    }
+    return select;
+}
+__device__ __forceinline__ bool di_combine(DIReservoir& r, const DIReservoir& n, float random, float target_pdf) {
+    const float ris_weight = target_pdf * (n.weight_sum * n.M);
+    r.M += n.M;
+    r.weight_sum += ris_weight;
+    const bool select = (random * r.weight_sum < ris_weight);
+    if (select) {
+        r.light_data = n.light_data; r.uv_data = n.uv_data; r.target_pdf = target_pdf;
+        r.packed_visibility = n.packed_visibility; r.sdx = n.sdx; r.sdy = n.sdy; r.age = n.age;
+    }
+    return select;
+}
+__device__ __forceinline__ void di_finalize(DIReservoir& r, float num, float den) {
+    const float denominator = r.target_pdf * den;
+    r.weight_sum = (denominator == 0.0f) ? 0.0f : (r.weight_sum * num) / denominator;
+}
+
+// ---- initial sampling: rtxdi/InitialSamplingFunctions.hlsli:50-115 -------------------------------------------------
+struct SampleParams { uint32_t num_local, num_infinite, num_env, num_brdf, num_mis; float local_mis_weight, env_mis_weight, brdf_mis_weight, brdf_cutoff, brdf_ray_min_t; };
+__device__ __forceinline__ SampleParams init_sample_params(uint32_t nl, uint32_t ni, uint32_t ne, uint32_t nb, float brdf_cutoff, float brdf_ray_min_t) {
+    SampleParams r;
+    r.num_local = nl; r.num_infinite = ni; r.num_env = ne; r.num_brdf = nb; r.num_mis = nl + ne + nb;
+    r.local_mis_weight = (float)nl / (float)r.num_mis; r.env_mis_weight = (float)ne / (float)r.num_mis; r.brdf_mis_weight = (float)nb / (float)r.num_mis;
+    r.brdf_cutoff = brdf_cutoff; r.brdf_ray_min_t = brdf_ray_min_t;
+    return r;
+}
+__device__ __forceinline__ float brdf_max_distance_from_pdf(float brdf_cutoff, float pdf) {
+    return brdf_cutoff > 0.f ? sqrtf((1.f / brdf_cutoff - 1.f) * pdf) : 3.402823466e+38F;
+}
+__device__ __forceinline__ float light_brdf_mis_weight(const Surface& s, const LightSample& ls, float light_selection_pdf, float light_mis_weight,
+                                                       bool is_environment_map, const SampleParams& sp) {
+    const float pdf = ls.solid_angle_pdf;
+    const bool analytic = ls.light_type != RT2_LIGHT_TRIANGLE && ls.light_type != 6u;   // RAB_IsAnalyticLightSample, bridge :544-548
+    if (sp.brdf_mis_weight == 0 || analytic || pdf <= 0 || isinf(pdf) || isnan(pdf)) return light_mis_weight * light_selection_pdf;
+    const V3 to_light = ls.position - s.world_pos;                        // RAB_GetLightDirDistance, bridge :527-542
+    const float light_distance = length3(to_light);
+    const V3 light_dir = to_light / light_distance;
+    float brdf_pdf = surface_brdf_pdf(s, light_dir);
+    const float max_distance = brdf_max_distance_from_pdf(sp.brdf_cutoff, brdf_pdf);
+    if (!is_environment_map && light_distance > max_distance) brdf_pdf = 0.f;
+    const float source_pdf_wrt_solid_angle = light_selection_pdf * pdf;
+    const float blended = light_mis_weight * source_pdf_wrt_solid_angle + sp.brdf_mis_weight * brdf_pdf;
+    return blended / pdf;
+}
+
+}  // namespace rt2

@@ -130,3 +130,110 @@ def test_postprocess_synthetic_radiance_sweep():
     diff = np.abs(out.astype(np.int32) - ref.astype(np.int32))
     assert diff.max() <= 1 and int((diff > 0).sum()) <= 4
     ctx.close()
+
+
+# ---- K3 g_buffer / K9 di_fused_resampling ---------------------------------------------------------------
+GB_KEYS = [("depth", rt.BUF_GBUFFER_DEPTH, np.float32, 1), ("normals", rt.BUF_GBUFFER_NORMALS, np.uint32, 1),
+           ("geo_normals", rt.BUF_GBUFFER_GEO_NORMALS, np.uint32, 1), ("diffuse_albedo", rt.BUF_GBUFFER_DIFFUSE_ALBEDO, np.uint32, 1),
+           ("specular_rough", rt.BUF_GBUFFER_SPECULAR_ROUGH, np.uint32, 1), ("emissive", rt.BUF_GBUFFER_EMISSIVE, np.uint16, 4),
+           ("motion", rt.BUF_MOTION_VECTORS, np.float32, 4)]
+
+
+def _restir_setup(kind, scale, w, h, tex=64):
+    sc, ctx = _setup(kind, scale, tex=tex)
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+    g.refrence_mode = 0; g.enable_restir_gi = 0; g.enable_restir_di = 0
+    lp = rt.LightPasses(ctx, w, h)
+    return sc, ctx, g, lp
+
+
+def _read_gbuffer(ctx, w, h):
+    return {k: (ctx.read(b, dt).reshape(h, w) if n == 1 else ctx.read(b, dt).reshape(h, w, n)) for k, b, dt, n in GB_KEYS}
+
+
+@pytest.mark.parametrize("kind,scale,w,h,brute", [
+    (rt.SCENE_CORNELL, 1.0, 512, 512, True), (rt.SCENE_HALL, 0.125, 320, 180, True), (rt.SCENE_HALL, 0.5, 480, 270, False),
+    (rt.SCENE_INSTANCED, 0.05, 320, 180, True), (rt.SCENE_MANYLIGHT, 0.1, 320, 180, True)])
+@pytest.mark.parametrize("frame", [1, 2])
+def test_gbuffer_bit_exact(kind, scale, w, h, brute, frame):
+    sc, ctx, g, lp = _restir_setup(kind, scale, w, h)
+    lp.update_uniform(g)
+    lp.execute(frame)
+    got = _read_gbuffer(ctx, w, h)
+    ref = O.OracleScene(sc.desc).gbuffer(g, w, h, flags=O.ORC_BRUTE_FORCE if brute else 0)
+    st = ctx.stats()
+    assert st.rays_traced == w * h and st.rays_hit == int((ref["depth"] != 100000.0).sum())
+    for k in ("depth", "normals", "geo_normals", "diffuse_albedo", "emissive", "motion"):
+        assert np.array_equal(got[k].view(np.uint32 if got[k].dtype.itemsize == 4 else np.uint16),
+                              ref[k].view(np.uint32 if ref[k].dtype.itemsize == 4 else np.uint16)), k
+    nbad = int((got["specular_rough"] != ref["specular_rough"]).sum())          # pow(x, 1/2.2) through binary64: <= 1e-6 of pixels may flip an LSB
+    assert nbad <= max(1, w * h // 1000000), nbad
+    assert (got["depth"] > 0).all()
+    ctx.close()
+
+
+def _di_run(kind, scale, w, h, frame, **di):
+    sc, ctx, g, lp = _restir_setup(kind, scale, w, h)
+    g.enable_restir_di = 1
+    isp = g.restir_di.initial_sampling_params
+    isp.num_primary_local_light_samples = di.get("local", 4); isp.num_primary_brdf_samples = di.get("brdf", 1)
+    isp.enable_initial_visibility = di.get("initial_vis", 0); isp.brdf_cutoff = di.get("cutoff", 0.0)
+    g.restir_di.shading_params.enable_final_visibility = di.get("final_vis", 0)
+    g.enable_accumulation = di.get("accumulate", 0); g.blend_factor = 0.25
+    rt.PrepareLightsTasks(ctx).execute()
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    lp.update_uniform(g)
+    if di.get("accumulate", 0):     # seed prior lighting so the accumulation branch reads something
+        rng = np.random.default_rng(4)
+        prior = np.zeros((h, w, 4), np.float16); prior[:, :, :3] = rng.random((h, w, 3))
+        ctx.write(rt.BUF_DIFFUSE_F16, prior.view(np.uint16)); ctx.write(rt.BUF_SPECULAR_F16, prior.view(np.uint16))
+    else:
+        prior = None
+    lp.execute(frame)
+    gb = _read_gbuffer(ctx, w, h)
+    pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
+    pdf = np.concatenate([m.ravel() for m in _read_mips(ctx, rt.BUF_LOCAL_PDF_MIP0, pw.value, ph.value, pm.value, np.float32)])
+    lights = ctx.read(rt.BUF_LIGHT_INFO, np.uint32).reshape(-1, 12)
+    g2l = ctx.read(rt.BUF_GEOM_TO_LIGHT, np.uint32)
+    pitch = g.restir_di.reservoir_buffer_params.reservoir_array_pitch
+    d_in = prior.view(np.uint16).copy() if prior is not None else None
+    s_in = prior.view(np.uint16).copy() if prior is not None else None
+    res, d16, s16, rays = O.OracleScene(sc.desc).di_fused_resampling(g, frame, w, h, gb, lights, g2l, pdf, pw.value, ph.value, pm.value, pitch,
+                                                                     diffuse_f16=d_in, specular_f16=s_in, flags=di.get("oflags", O.ORC_BRUTE_FORCE))
+    got_res = ctx.read(rt.BUF_DI_RESERVOIRS, np.uint32).reshape(-1, 6)
+    got_d = ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).reshape(h, w, 4)
+    got_s = ctx.read(rt.BUF_SPECULAR_F16, np.uint16).reshape(h, w, 4)
+    st = ctx.stats()
+    ctx.close()
+    return (got_res, got_d, got_s, st.rays_traced - w * h), (res, d16, s16, rays)
+
+
+@pytest.mark.parametrize("kind,scale,w,h,di", [
+    (rt.SCENE_CORNELL, 1.0, 512, 512, dict(local=4, brdf=1)),                      # BASELINE config 1 size
+    (rt.SCENE_CORNELL, 1.0, 256, 256, dict(local=0, brdf=1)),                      # the reference's default sample counts (src/main.rs:322-331)
+    (rt.SCENE_CORNELL, 1.0, 256, 256, dict(local=8, brdf=2, initial_vis=1, final_vis=1)),
+    (rt.SCENE_CORNELL, 1.0, 200, 120, dict(local=3, brdf=1, cutoff=0.1, final_vis=1, accumulate=1)),
+    (rt.SCENE_HALL, 0.125, 320, 180, dict(local=4, brdf=1, final_vis=1, oflags=0)),
+    (rt.SCENE_MANYLIGHT, 0.2, 320, 180, dict(local=8, brdf=1, initial_vis=1, oflags=0)),     # config 3 shape: many emissive triangles
+])
+def test_di_reservoir_sampling_bit_exact(kind, scale, w, h, di):
+    (res, d16, s16, rays), (rres, rd16, rs16, rrays) = _di_run(kind, scale, w, h, 1, **di)
+    nvalid = int((rres[:, 0] != 0).sum())
+    assert nvalid > 0 and rays == rrays
+    tol = max(2, w * h // 50000)     # log2/exp2/pow via binary64 may round a last bit differently in <= 2e-5 of pixels
+    bad = np.flatnonzero((res != rres).any(axis=1))
+    assert len(bad) <= tol, f"{len(bad)} reservoirs differ (of {nvalid} valid), first {bad[:4]}"
+    assert int((d16 != rd16).any(axis=2).sum()) <= tol and int((s16 != rs16).any(axis=2).sum()) <= tol
+    f = d16.view(np.float16)[:, :, :3].astype(np.float32)
+    assert np.isfinite(f).all() and f.max() > 0
+
+
+def test_di_needs_light_list():
+    sc, ctx, g, lp = _restir_setup(rt.SCENE_CORNELL, 1.0, 64, 64)
+    g.enable_restir_di = 1
+    g.restir_di.initial_sampling_params.num_primary_local_light_samples = 2
+    lp.update_uniform(g)
+    with pytest.raises(rt.Rt2Error):
+        lp.execute(1)               # rt2_prepare_lights has not run
+    ctx.close()
