@@ -173,28 +173,18 @@ def main():
     lp.update_uniform(g)
     params = rt.LaunchParams(spp=spp, max_bounces=BOUNCES, band_rows=BAND_ROWS if n_gpus > 1 else 0, band_rank=rank, band_world=n_gpus)
 
-    # band gather plumbing: each rank's rows packed contiguously -> all_gather -> (rank 0 could scatter back)
-    my_rows = [y for y in range(H) if n_gpus == 1 or (y // BAND_ROWS) % n_gpus == rank]
-    bands = []
-    y = 0
-    while y < H:
-        y1 = min(y + BAND_ROWS, H)
-        if n_gpus == 1 or (y // BAND_ROWS) % n_gpus == rank:
-            bands.append((y, y1))
-        y = y1
-    max_rows = max(len([yy for yy in range(H) if (yy // BAND_ROWS) % n_gpus == r]) for r in range(n_gpus))
-    send = torch.zeros(max_rows * W * 4, dtype=torch.float32, device="cuda")
-    recv = torch.zeros(n_gpus * max_rows * W * 4, dtype=torch.float32, device="cuda") if n_gpus > 1 else None
+    # band gather plumbing (raytracer2_b200/sharding.py): each rank's rows packed contiguously -> all_gather
+    from raytracer2_b200.sharding import BandPlan, gather_frame
+    plan = BandPlan(H, BAND_ROWS, n_gpus)
+    send = torch.zeros(plan.max_rows * W * 4, dtype=torch.float32, device="cuda")
+    recv = torch.zeros(n_gpus * plan.max_rows * W * 4, dtype=torch.float32, device="cuda") if n_gpus > 1 else None
 
     def step(frame):
         lp.execute(frame, params)
         if n_gpus > 1:
-            off = 0
-            for (y0, y1) in bands:
-                nb = (y1 - y0) * W * 16
-                ctx.copy_to_device(rt.BUF_DIFFUSE_F32, send.data_ptr() + off, nb, y0, y1)
-                off += nb
-            dist.all_gather_into_tensor(recv, send)
+            for (y0, y1, off) in plan.pack_offsets(rank):
+                ctx.copy_to_device(rt.BUF_DIFFUSE_F32, send.data_ptr() + off * W * 16, (y1 - y0) * W * 16, y0, y1)
+            gather_frame(plan, rank, send, recv, dist)
 
     for i in range(args.warmup):
         step(1 + i)
@@ -279,9 +269,12 @@ def main():
                          "whole_step": {"bytes_per_ray": B_RAY, "achieved": value * 1e6 / n_gpus * B_RAY / 1e9, "frac": value * 1e6 / n_gpus * B_RAY / 1e9 / peak}},
         }
         if n_gpus == 1 and not args.no_cpu_baseline:
-            v, crays, dt, cores, _ = cpu_oracle_run(1, BOUNCES)
+            v, crays, dt, cores, _ = cpu_oracle_run(1, BOUNCES)                 # probe: one sample per pixel
+            cspp = max(1, min(64, int(round(15.0 / max(dt, 1e-3)))))            # then ~15 s of CPU work on the same frame
+            if cspp > 1:
+                v, crays, dt, cores, _ = cpu_oracle_run(cspp, BOUNCES)
             line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "port",
-                                    "sample": f"same C2 scene and camera, {W}x{H}, 1 spp x {BOUNCES} bounces = {crays} rays in {dt:.1f} s (CPU oracle, {cores} threads)"}
+                                    "sample": f"same C2 scene and camera, {W}x{H}, {cspp} spp x {BOUNCES} bounces = {crays} rays in {dt:.1f} s (CPU oracle, {cores} threads)"}
         print(json.dumps(line), flush=True)
     ctx.close()
     if dist:
