@@ -77,7 +77,17 @@ RT2_HD uint32_t sign_extend_s8x4(uint32_t x) {
     return r;
 #endif
 }
-RT2_HD float byte_to_float(uint32_t w, uint32_t i) { return (float)rt2_byte(w, i); }
+// u8 -> f32.  I2F.U8 issues to the XU pipe (16 lanes/clk/SM, 63 % busy in profiles/r01b).  The prmt variant drops the
+// byte into the mantissa of 2^23 and subtracts 2^23 (exact, bit-identical) at the price of one more issue slot per
+// value; measured on B200 it LOSES 3 % on C2 (2142 vs 2212 Mrays/s): the kernel is issue/latency bound before it is
+// XU bound.  Kept behind RT2_BYTE_MAGIC for the record.
+RT2_HD float byte_to_float(uint32_t w, uint32_t i) {
+#if defined(__CUDA_ARCH__) && defined(RT2_BYTE_MAGIC)
+    return u2f(__byte_perm(w, 0x4B000000u, 0x7540u | i)) - 8388608.0f;
+#else
+    return (float)rt2_byte(w, i);
+#endif
+}
 
 struct TraceRay {
     V3 o, d;
