@@ -133,6 +133,31 @@ typedef struct rt2_packed_di_reservoir {
     float    weight;
 } rt2_packed_di_reservoir;
 
+/* src/shaders/rtxdi/ReSTIRGIParameters.h:17-30 `RTXDI_PackedGIReservoir`. 32 bytes. */
+typedef struct rt2_packed_gi_reservoir {
+    float    position[3];
+    uint32_t packed_misc_age_m;   /* M bits 0-7, age bits 8-15, misc bits 16-31 (GIReservoir.hlsli:52-61) */
+    uint32_t packed_radiance;     /* 32-bit LogLuv (RtxdiMath.hlsli:233-264) */
+    float    weight;
+    uint32_t packed_normal;       /* 2 x snorm16 octahedral (RtxdiMath.hlsli:184-196) */
+    float    unused;
+} rt2_packed_gi_reservoir;
+
+/* src/shaders/ShaderParameters.glsl:49-60 `SecondaryGBufferData`. 48 bytes; block-linear addressing like the reservoirs,
+ * arrayPitch entries (src/render_resources.rs:309-317). */
+typedef struct rt2_secondary_gbuffer_data {
+    float    world_pos[3];
+    uint32_t normal;                  /* octahedral unorm 2x16 */
+    uint32_t throughput_and_flags[2]; /* .x = throughput.rg fp16, .y = throughput.b fp16 | flags << 16 */
+    uint32_t diffuse_albedo;          /* R11G11B10_UFLOAT */
+    uint32_t specular_and_roughness;  /* R8G8B8A8 gamma */
+    float    emission[3];
+    float    pdf;
+} rt2_secondary_gbuffer_data;
+#define RT2_SECONDARY_IS_SPECULAR_RAY   1u   /* ShaderParameters.glsl:21-23 */
+#define RT2_SECONDARY_IS_DELTA_SURFACE  2u
+#define RT2_SECONDARY_IS_ENVIRONMENT    4u
+
 /* The 1424-byte `GConst` block (src/shader_params.rs:243-274 == GLSL `ResamplingConstants`,
  * src/shaders/ShaderParameters.glsl:62-92) is passed verbatim as bytes. */
 #define RT2_GCONST_SIZE 1424 /* SURVEY.md says 1456; summing src/shader_params.rs field by field gives 464 (PlanarViewConstants) and 1424 */

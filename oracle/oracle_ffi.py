@@ -60,6 +60,14 @@ def lib():
         L.orc_di_fused_resampling.restype = C.c_int
         L.orc_di_fused_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int] + [VP] * 5 + [VP, u32, VP, VP, u32, u32, u32, VP, VP, VP, C.POINTER(u64)]
         L.orc_reservoir_position_to_pointer.restype = u32; L.orc_reservoir_position_to_pointer.argtypes = [u32] * 5
+        L.orc_brdf_rays.restype = C.c_int; L.orc_brdf_rays.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int, VP, VP, VP, VP, C.POINTER(u64)]
+        L.orc_shade_secondary_surfaces.restype = C.c_int
+        L.orc_shade_secondary_surfaces.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int, VP, VP, VP, VP, VP, VP, C.POINTER(u64)]
+        L.orc_gi_final_shading.restype = C.c_int; L.orc_gi_final_shading.argtypes = [VP, VP, u32, u32, u32, C.c_int, VP, VP, VP, VP, VP, C.POINTER(u64)]
+        L.orc_encode_logluv.restype = u32; L.orc_encode_logluv.argtypes = [VP]
+        L.orc_decode_logluv.restype = None; L.orc_decode_logluv.argtypes = [u32, VP]
+        L.orc_encode_snorm_oct.restype = u32; L.orc_encode_snorm_oct.argtypes = [VP]
+        L.orc_decode_snorm_oct.restype = None; L.orc_decode_snorm_oct.argtypes = [u32, VP]
         _lib = L
     return _lib
 
@@ -82,6 +90,14 @@ def split_mips(packed, w, h, mips):
 class _SceneHead(C.Structure):   # leading fields of rt2_scene_desc (include/rt2_abi.h)
     _fields_ = [("vertices", VP), ("num_vertices", u64), ("indices", VP), ("num_indices", u64),
                 ("geometries", VP), ("index_counts", VP), ("num_geometries", u32)]
+
+
+class GBufferIn(C.Structure):   # orc_gbuffer_in
+    _fields_ = [(k, VP) for k in ("depth", "normals", "geo_normals", "diffuse_albedo", "specular_rough")]
+
+
+class LightIn(C.Structure):     # orc_light_in
+    _fields_ = [("lights", VP), ("num_lights", u32), ("geom_to_light", VP), ("pdf_packed", VP), ("pdf_w", u32), ("pdf_h", u32), ("pdf_mips", u32)]
 
 
 class OracleScene:
@@ -174,3 +190,59 @@ class OracleScene:
                                              res.ctypes.data_as(VP), d16.ctypes.data_as(VP), s16.ctypes.data_as(VP), C.byref(rays))
         assert rc == 0, rc
         return res, d16, s16, rays.value
+
+    # ---- the ReSTIR-GI chain K4 -> K5 -> K8 ----------------------------------------------------------------
+    @staticmethod
+    def _gb_in(gb):
+        keep = [np.ascontiguousarray(gb[k]) for k in ("depth", "normals", "geo_normals", "diffuse_albedo", "specular_rough")]
+        return GBufferIn(*[a.ctypes.data_as(VP) for a in keep]), keep
+
+    @staticmethod
+    def _light_in(lights, geom_to_light, pdf_packed, pdf_w, pdf_h, pdf_mips):
+        if lights is None:
+            return None, []
+        keep = [np.ascontiguousarray(lights), np.ascontiguousarray(geom_to_light), np.ascontiguousarray(pdf_packed, np.float32)]
+        return LightIn(keep[0].ctypes.data_as(VP), len(keep[0]), keep[1].ctypes.data_as(VP), keep[2].ctypes.data_as(VP), pdf_w, pdf_h, pdf_mips), keep
+
+    def brdf_rays(self, gconst, frame, w, h, gb, secondary, diffuse_f16, specular_f16, flags=0, threads=0):
+        """K4.  secondary: uint32 [arrayPitch, 12] (in/out); lighting images rgba16f as uint16 [h, w, 4] (in/out).  Returns rays."""
+        gin, keep = self._gb_in(gb)
+        rays = u64(0)
+        rc = self._L.orc_brdf_rays(self._p, C.cast(C.byref(gconst), VP), frame, w, h, flags, threads, C.byref(gin),
+                                   secondary.ctypes.data_as(VP), diffuse_f16.ctypes.data_as(VP), specular_f16.ctypes.data_as(VP), C.byref(rays))
+        assert rc == 0, rc
+        return rays.value
+
+    def shade_secondary_surfaces(self, gconst, frame, w, h, gb, secondary, gi_reservoirs, diffuse_f16, specular_f16,
+                                 lights=None, geom_to_light=None, pdf_packed=None, pdf_dims=(0, 0, 0), flags=0, threads=0):
+        """K5.  gi_reservoirs: uint32 [arrayPitch * 2, 8] (in/out)."""
+        gin, keep = self._gb_in(gb)
+        lin, keep2 = self._light_in(lights, geom_to_light, pdf_packed, *pdf_dims)
+        rays = u64(0)
+        rc = self._L.orc_shade_secondary_surfaces(self._p, C.cast(C.byref(gconst), VP), frame, w, h, flags, threads, C.byref(gin),
+                                                  C.byref(lin) if lin is not None else None, secondary.ctypes.data_as(VP), gi_reservoirs.ctypes.data_as(VP),
+                                                  diffuse_f16.ctypes.data_as(VP), specular_f16.ctypes.data_as(VP), C.byref(rays))
+        assert rc == 0, rc
+        return rays.value
+
+    def gi_final_shading(self, gconst, w, h, gb, secondary, gi_reservoirs, diffuse_f16, specular_f16, flags=0, threads=0):
+        """K8."""
+        gin, keep = self._gb_in(gb)
+        rays = u64(0)
+        rc = self._L.orc_gi_final_shading(self._p, C.cast(C.byref(gconst), VP), w, h, flags, threads, C.byref(gin),
+                                          secondary.ctypes.data_as(VP), gi_reservoirs.ctypes.data_as(VP),
+                                          diffuse_f16.ctypes.data_as(VP), specular_f16.ctypes.data_as(VP), C.byref(rays))
+        assert rc == 0, rc
+        return rays.value
+
+    def gi_chain(self, gconst, frame, w, h, gb, array_pitch, light_inputs=None, state=None, flags=0, threads=0):
+        """K4 -> K5 -> K8 on fresh (or carried-over `state`) buffers.  Returns dict(secondary, gi_reservoirs, diffuse, specular, rays)."""
+        st = state or {"secondary": np.zeros((array_pitch, 12), np.uint32), "gi_reservoirs": np.zeros((array_pitch * 2, 8), np.uint32),
+                       "diffuse": np.zeros((h, w, 4), np.uint16), "specular": np.zeros((h, w, 4), np.uint16)}
+        li = light_inputs or {}
+        r4 = self.brdf_rays(gconst, frame, w, h, gb, st["secondary"], st["diffuse"], st["specular"], flags, threads)
+        r5 = self.shade_secondary_surfaces(gconst, frame, w, h, gb, st["secondary"], st["gi_reservoirs"], st["diffuse"], st["specular"],
+                                           li.get("lights"), li.get("geom_to_light"), li.get("pdf_packed"), li.get("pdf_dims", (0, 0, 0)), flags, threads)
+        r8 = self.gi_final_shading(gconst, w, h, gb, st["secondary"], st["gi_reservoirs"], st["diffuse"], st["specular"], flags, threads)
+        st["rays"] = (r4, r5, r8)
+        return st

@@ -583,8 +583,9 @@ static void GetGeometryFromHit(const orc_scene& s, const Hit& h, V3* normal, V3*
 static V3 GetEnvironmentRadiance(const orc_scene& s, const GConstView& g, V3 dir) {
     if (g.environment != 1u || s.sky.empty()) return v3(0, 0, 0);
     const float PI_ = 3.1415926f;
-    float u = 0.5f + std::atan2(dir.z, dir.x) / (2.0f * PI_);
-    float v = 0.5f - std::asin(dir.y) / PI_;
+    // transcendental pin: binary64, rounded once (GLSL leaves atan / asin precision to the implementation)
+    float u = 0.5f + (float)std::atan2((double)dir.z, (double)dir.x) / (2.0f * PI_);
+    float v = 0.5f - (float)std::asin((double)dir.y) / PI_;
     const int W = (int)s.sky_w, H = (int)s.sky_h;
     float x = u * (float)W - 0.5f, y = v * (float)H - 0.5f;
     float fx = std::floor(x), fy = std::floor(y);
@@ -865,3 +866,4 @@ void orc_sample_texture(const orc_scene* s, uint32_t ti, float u, float v, float
 }  // extern "C"
 
 #include "rt2_oracle_passes.inc"
+#include "rt2_oracle_gi.inc"

@@ -99,6 +99,34 @@ int orc_di_fused_resampling(const orc_scene* s, const void* gconst, uint32_t fra
 /* RTXDI_ReservoirPositionToPointer (rtxdi/RtxdiHelpers.hlsli:75-88) */
 uint32_t orc_reservoir_position_to_pointer(uint32_t block_row_pitch, uint32_t array_pitch, uint32_t x, uint32_t y, uint32_t array_index);
 
+/* ---- the default ReSTIR-GI chain (src/light_passes.rs:621-659) -------------------------------
+ * G-buffer inputs as for K9.  `secondary` (arrayPitch entries, block-linear) and `gi_reservoirs` (arrayPitch x 2)
+ * persist between the passes and between frames, so they are in/out.  Light inputs may be null when
+ * enableRestirDI == 0 (K5 then traces one more cosine bounce instead of sampling the light list). */
+typedef struct orc_gbuffer_in {
+    const float* depth; const uint32_t* normals; const uint32_t* geo_normals; const uint32_t* diffuse_albedo; const uint32_t* specular_rough;
+} orc_gbuffer_in;
+typedef struct orc_light_in {
+    const rt2_light_info* lights; uint32_t num_lights; const uint32_t* geom_to_light;
+    const float* pdf_packed; uint32_t pdf_w, pdf_h, pdf_mips;
+} orc_light_in;
+/* K4 lighting_passes/brdf_rays.rgen:19-195 */
+int orc_brdf_rays(const orc_scene* s, const void* gconst, uint32_t frame, uint32_t width, uint32_t height, uint32_t flags, int threads,
+                  const orc_gbuffer_in* gb, rt2_secondary_gbuffer_data* secondary, uint16_t* diffuse_f16, uint16_t* specular_f16, uint64_t* rays);
+/* K5 lighting_passes/shade_secondary_surfaces.rgen:26-157 */
+int orc_shade_secondary_surfaces(const orc_scene* s, const void* gconst, uint32_t frame, uint32_t width, uint32_t height, uint32_t flags, int threads,
+                                 const orc_gbuffer_in* gb, const orc_light_in* li, rt2_secondary_gbuffer_data* secondary,
+                                 rt2_packed_gi_reservoir* gi_reservoirs, uint16_t* diffuse_f16, uint16_t* specular_f16, uint64_t* rays);
+/* K8 lighting_passes/gi_final_shading.rgen:43-101 */
+int orc_gi_final_shading(const orc_scene* s, const void* gconst, uint32_t width, uint32_t height, uint32_t flags, int threads,
+                         const orc_gbuffer_in* gb, const rt2_secondary_gbuffer_data* secondary, const rt2_packed_gi_reservoir* gi_reservoirs,
+                         uint16_t* diffuse_f16, uint16_t* specular_f16, uint64_t* rays);
+/* KAT probes: rtxdi/RtxdiMath.hlsli:129-296 */
+uint32_t orc_encode_logluv(const float rgb[3]);
+void orc_decode_logluv(uint32_t packed, float rgb[3]);
+uint32_t orc_encode_snorm_oct(const float n[3]);
+void orc_decode_snorm_oct(uint32_t packed, float n[3]);
+
 #ifdef __cplusplus
 }
 #endif

@@ -45,7 +45,7 @@ int restir_ensure_resources(rt2_ctx* ctx) {
     f.reservoir_block_row_pitch = wb * 256u; f.reservoir_array_pitch = f.reservoir_block_row_pitch * hb;
     RT2_CUDA(ctx, zalloc(ctx, &f.di_reservoirs, (size_t)f.reservoir_array_pitch * 2));    // src/render_resources.rs:191-198
     RT2_CUDA(ctx, zalloc(ctx, &f.gi_reservoirs, (size_t)f.reservoir_array_pitch * 2 * 2)); // 32 B each, :199-206
-    RT2_CUDA(ctx, zalloc(ctx, &f.secondary_gbuffer, n * 3));                               // 48 B each, :309-317
+    RT2_CUDA(ctx, zalloc(ctx, &f.secondary_gbuffer, (size_t)f.reservoir_array_pitch * 3)); // 48 B x arrayPitch (block-linear addressing), :309-317
     return RT2_OK;
 }
 
@@ -77,7 +77,7 @@ bool pass_buffer(rt2_ctx* ctx, int which, void** ptr, size_t* bytes) {
         case RT2_BUF_MOTION_VECTORS: *ptr = f.motion_vectors; *bytes = n * 16; return f.motion_vectors != nullptr;
         case RT2_BUF_DI_RESERVOIRS: *ptr = f.di_reservoirs; *bytes = (size_t)f.reservoir_array_pitch * 2 * sizeof(rt2_packed_di_reservoir); return f.di_reservoirs != nullptr;
         case RT2_BUF_GI_RESERVOIRS: *ptr = f.gi_reservoirs; *bytes = (size_t)f.reservoir_array_pitch * 2 * 32; return f.gi_reservoirs != nullptr;
-        case RT2_BUF_SECONDARY_GBUFFER: *ptr = f.secondary_gbuffer; *bytes = n * 48; return f.secondary_gbuffer != nullptr;
+        case RT2_BUF_SECONDARY_GBUFFER: *ptr = f.secondary_gbuffer; *bytes = (size_t)f.reservoir_array_pitch * 48; return f.secondary_gbuffer != nullptr;
         default: return false;
     }
 }

@@ -1,6 +1,7 @@
 // rt2_passes_restir.cu — the non-reference branch of LightPasses::execute (src/light_passes.rs:598-659):
 //   K3 g_buffer            lighting_passes/g_buffer.rgen:14-47
 //   K9 di_fused_resampling lighting_passes/di_fused_resampling.rgen:16-93 (reservoir light sampling)
+//   K4 brdf_rays / K5 shade_secondary_surfaces / K8 gi_final_shading (the default ReSTIR-GI chain)
 //
 // Both are one-thread-per-pixel kernels with the traversal inlined (8x4 pixel tiles per warp so the
 // primary / BRDF rays of a warp start coherent).  K3 is bound like the primary wavefront of K1
@@ -73,19 +74,15 @@ __global__ void __launch_bounds__(128) k_gbuffer(GBufferArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// K9
+// RTXDI_SampleLightsForSurface (rtxdi/InitialSamplingFunctions.hlsli:594-664) — shared by K9 and K5
 // ------------------------------------------------------------------------------------------------
-struct DIArgs {
-    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame;
-    GBufferRefs gb;
+struct LightRefs {
     const rt2_light_info* lights; const uint32_t* geom_to_light;
     const float* pdf; uint32_t pdf_w, pdf_h, pdf_last_offset;
-    rt2_packed_di_reservoir* reservoirs; ushort4* diffuse; ushort4* specular; float4* diffuse_f32;
-    unsigned long long* stat_rays; unsigned long long* stat_hits;
 };
 
 // RAB_EvaluateLocalLightSourcePdf, bridge :420-434 (Q14 pinned to texelFetch semantics)
-__device__ __forceinline__ float local_light_source_pdf(const DIArgs& a, uint32_t light_index) {
+__device__ __forceinline__ float local_light_source_pdf(const LightRefs& a, uint32_t light_index) {
     uint32_t x, y;
     linear_to_zcurve(light_index, x, y);
     const float texel = (x < a.pdf_w && y < a.pdf_h) ? __ldg(a.pdf + (size_t)y * a.pdf_w + x) : 0.f;
@@ -95,30 +92,17 @@ __device__ __forceinline__ float local_light_source_pdf(const DIArgs& a, uint32_
     return texel / sum;
 }
 
-__device__ __forceinline__ bool visibility_ray_miss(const DIArgs& a, const Surface& s, V3 sample_position, float offset, uint32_t* rays) {
+__device__ __forceinline__ bool visibility_ray_miss(const SceneRefs& sc, const Surface& s, V3 sample_position, float offset, uint32_t* rays) {
     const V3 L = sample_position - s.world_pos;                        // setupVisibilityRay, bridge :191-218
     const float tmax = fmaxf(offset, length3(L) - offset * 2);
     uint32_t slot;
-    const Hit h = trace_closest(a.sc, s.world_pos, normalize3(L), offset, tmax, &slot);
+    const Hit h = trace_closest(sc, s.world_pos, normalize3(L), offset, tmax, &slot);
     (*rays)++;
     return h.geom == 0xFFFFFFFFu;
 }
 
-__global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
-    uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
-    const rt2_gconst& g = *a.g;
-    const rt2_restirdi_params& di = g.restir_di;
-    uint32_t rays = 0, hits = 0;
-    uint32_t px = lx, py = ly;                                         // RTXDI_ReservoirPosToPixelPos, RtxdiHelpers.hlsli:52-61
-    const uint32_t field = g.runtime_params.active_checkerboard_field;
-    if (field != 0u) { px = lx << 1; px += ((py + field) & 1u); }
-    Rng rng = rng_init(px, py, a.frame, 1u);
-    const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
-    const SampleParams sp = init_sample_params(di.initial_sampling_params.num_primary_local_light_samples, di.initial_sampling_params.num_primary_infinite_light_samples,
-                                               di.initial_sampling_params.num_primary_environment_samples, di.initial_sampling_params.num_primary_brdf_samples,
-                                               di.initial_sampling_params.brdf_cutoff, 0.001f);
-    // ---- RTXDI_SampleLightsForSurface, InitialSamplingFunctions.hlsli:594-664 -----------------------------------
+__device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& sc, const LightRefs& lr, const rt2_gconst& g, Rng& rng, const Surface& surface,
+                                                              const SampleParams& sp, LightSample* o_light_sample, uint32_t& rays, uint32_t& hits) {
     const uint32_t first_local = g.light_buffer_params.local_light_buffer_region.first_light_index;
     const uint32_t num_local = g.light_buffer_params.local_light_buffer_region.num_lights;
     LightSample local_sample = empty_light_sample();
@@ -129,7 +113,7 @@ __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
             const float rnd = rng_next(rng);                           // UniformSampling.hlsli:14-25
             const float inv_source_pdf = (float)num_local;
             const uint32_t light_index = first_local + min((uint32_t)floorf(rnd * (float)num_local), num_local - 1u);
-            const rt2_light_info li = load_light_info(a.lights, light_index);
+            const rt2_light_info li = load_light_info(lr.lights, light_index);
             const float uvx = rng_next(rng), uvy = rng_next(rng);
             const LightSample cand = sample_polymorphic_light(li, surface, uvx, uvy);           // :131-156
             const float blended = light_brdf_mis_weight(surface, cand, 1.0f / inv_source_pdf, sp.local_mis_weight, false, sp);
@@ -158,11 +142,11 @@ __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
             const float brdf_pdf = surface_brdf_pdf(surface, sample_dir);
             const float max_distance = brdf_max_distance_from_pdf(sp.brdf_cutoff, brdf_pdf);
             uint32_t slot;                                             // RAB_TraceRayForLocalLight, bridge :629-669
-            const Hit h = trace_closest(a.sc, surface.world_pos, sample_dir, sp.brdf_ray_min_t, max_distance, &slot);
+            const Hit h = trace_closest(sc, surface.world_pos, sample_dir, sp.brdf_ray_min_t, max_distance, &slot);
             rays++;
             if (h.geom != 0xFFFFFFFFu) {
                 hits++;
-                uint32_t li = __ldg(a.geom_to_light + h.geom);         // getLightIndex, bridge :621-627
+                uint32_t li = __ldg(lr.geom_to_light + h.geom);        // getLightIndex, bridge :621-627
                 if (li != RT2_INVALID_LIGHT) li += h.prim;
                 light_index = li;
             }
@@ -170,14 +154,14 @@ __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
                 const float bx = 1 - h.u - h.v, bz = h.v;              // hitUVToBarycentric, randomFromBarycentric (Helpers.glsl:76-86)
                 const float sqrtx = 1 - bx;
                 rx = sqrtx * sqrtx; ry = bz / sqrtx;
-                cand = sample_polymorphic_light(load_light_info(a.lights, light_index), surface, rx, ry);
+                cand = sample_polymorphic_light(load_light_info(lr.lights, light_index), surface, rx, ry);
                 if (sp.brdf_cutoff > 0.f) {
                     const V3 to_light = cand.position - surface.world_pos;
                     const float light_distance = length3(to_light);
                     const float pdf2 = surface_brdf_pdf(surface, to_light / light_distance);
                     if (light_distance > brdf_max_distance_from_pdf(sp.brdf_cutoff, pdf2)) light_index = RT2_INVALID_LIGHT;
                 }
-                if (light_index != RT2_INVALID_LIGHT) light_source_pdf = local_light_source_pdf(a, light_index);
+                if (light_index != RT2_INVALID_LIGHT) light_source_pdf = local_light_source_pdf(lr, light_index);
             }
             // BRDF miss + environmentLightParams.lightPresent: the environment light (index lights + 1) is never written (Q7) -> absent
         }
@@ -196,34 +180,76 @@ __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
     const bool select_brdf = di_combine(reservoir, brdf_reservoir, rng_next(rng), brdf_reservoir.target_pdf);
     di_finalize(reservoir, 1.0f, 1.0f);
     reservoir.M = 1;
-    LightSample light_sample = select_brdf ? brdf_sample : (select_infinite ? infinite_sample : local_sample);
+    *o_light_sample = select_brdf ? brdf_sample : (select_infinite ? infinite_sample : local_sample);
+    return reservoir;
+}
+
+// ShadeSurfaceWithLightSample, ShadingHelpers.glsl:2-58.  Visibility reuse needs reservoir.age > 0 (DIReservoir.hlsli:186-189);
+// both callers hand in a freshly sampled reservoir (age 0), so the final-visibility ray is always traced.
+__device__ __forceinline__ void shade_surface_with_light_sample(const SceneRefs& sc, const rt2_gconst& g, DIReservoir& reservoir, const Surface& surface,
+                                                                LightSample light_sample, V3* diffuse, V3* specular, uint32_t& rays, uint32_t& hits) {
+    *diffuse = v3(0.f, 0.f, 0.f); *specular = v3(0.f, 0.f, 0.f);
+    if (light_sample.solid_angle_pdf <= 0) return;
+    const rt2_restirdi_params& di = g.restir_di;
+    if (di.shading_params.enable_final_visibility == 1u) {
+        const bool vis = visibility_ray_miss(sc, surface, light_sample.position, 0.01f, &rays);
+        if (!vis) hits++;
+        const V3 visibility = vis ? v3(1.f, 1.f, 1.f) : v3(0.f, 0.f, 0.f);
+        di_store_visibility(reservoir, visibility, di.temporal_resampling_params.discard_invisible_samples == 1u);
+        light_sample.radiance = light_sample.radiance * visibility;
+    }
+    light_sample.radiance = light_sample.radiance * (reservoir.weight_sum / light_sample.solid_angle_pdf);
+    if (light_sample.radiance.x > 0.0f || light_sample.radiance.y > 0.0f || light_sample.radiance.z > 0.0f) {
+        const SplitBrdf brdf = evaluate_brdf(surface, light_sample.position);
+        *diffuse = light_sample.radiance * brdf.demodulated_diffuse;
+        *specular = brdf.specular * light_sample.radiance;
+    }
+}
+
+__device__ __forceinline__ void launch_to_pixel(const rt2_gconst& g, uint32_t lx, uint32_t ly, uint32_t* px, uint32_t* py) {   // RtxdiHelpers.hlsli:52-61
+    const uint32_t field = g.runtime_params.active_checkerboard_field;
+    *px = lx; *py = ly;
+    if (field != 0u) { *px = lx << 1; *px += ((ly + field) & 1u); }
+}
+__device__ __forceinline__ void flush_ray_stats(unsigned long long* stat_rays, unsigned long long* stat_hits, uint32_t rays, uint32_t hits) {
+    const uint32_t am = __activemask();
+    const uint32_t wr = __reduce_add_sync(am, rays), wh = __reduce_add_sync(am, hits);
+    if ((threadIdx.x & 31u) == (uint32_t)(__ffs(am) - 1)) { atomicAdd(stat_rays, (unsigned long long)wr); atomicAdd(stat_hits, (unsigned long long)wh); }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K9
+// ------------------------------------------------------------------------------------------------
+struct DIArgs {
+    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame;
+    GBufferRefs gb;
+    LightRefs li;
+    rt2_packed_di_reservoir* reservoirs; ushort4* diffuse; ushort4* specular; float4* diffuse_f32;
+    unsigned long long* stat_rays; unsigned long long* stat_hits;
+};
+
+__global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const rt2_gconst& g = *a.g;
+    const rt2_restirdi_params& di = g.restir_di;
+    uint32_t rays = 0, hits = 0;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    Rng rng = rng_init(px, py, a.frame, 1u);
+    const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+    const SampleParams sp = init_sample_params(di.initial_sampling_params.num_primary_local_light_samples, di.initial_sampling_params.num_primary_infinite_light_samples,
+                                               di.initial_sampling_params.num_primary_environment_samples, di.initial_sampling_params.num_primary_brdf_samples,
+                                               di.initial_sampling_params.brdf_cutoff, 0.001f);
+    LightSample light_sample;
+    DIReservoir reservoir = sample_lights_for_surface(a.sc, a.li, g, rng, surface, sp, &light_sample, rays, hits);
     // ---- di_fused_resampling.rgen:42-48: initial visibility
     if (di.initial_sampling_params.enable_initial_visibility == 1u && di_valid(reservoir)) {
-        if (!visibility_ray_miss(a, surface, light_sample.position, 0.001f, &rays)) { hits++; di_store_visibility(reservoir, v3(0.f, 0.f, 0.f), true); }
+        if (!visibility_ray_miss(a.sc, surface, light_sample.position, 0.001f, &rays)) { hits++; di_store_visibility(reservoir, v3(0.f, 0.f, 0.f), true); }
     }
-    // ---- shading: ShadingHelpers.glsl:2-58, DemodulateSpecular Helpers.glsl:312-315
     V3 diffuse = v3(0.f, 0.f, 0.f), specular = v3(0.f, 0.f, 0.f);
     if (di_valid(reservoir)) {
-        if (!(light_sample.solid_angle_pdf <= 0)) {
-            if (di.shading_params.enable_final_visibility == 1u) {
-                // visibility reuse needs reservoir.age > 0 (DIReservoir.hlsli:186-189); this reservoir is fresh, so the ray is always traced
-                const bool vis = visibility_ray_miss(a, surface, light_sample.position, 0.01f, &rays);
-                if (!vis) hits++;
-                const V3 visibility = vis ? v3(1.f, 1.f, 1.f) : v3(0.f, 0.f, 0.f);
-                di_store_visibility(reservoir, visibility, di.temporal_resampling_params.discard_invisible_samples == 1u);
-                light_sample.radiance = light_sample.radiance * visibility;
-            }
-            light_sample.radiance = light_sample.radiance * (reservoir.weight_sum / light_sample.solid_angle_pdf);
-            if (light_sample.radiance.x > 0.0f || light_sample.radiance.y > 0.0f || light_sample.radiance.z > 0.0f) {
-                const V3 L = normalize3(light_sample.position - surface.world_pos);             // EvaluateBrdf, bridge :146-159
-                const float dd = lambert(surface.normal, neg3(L));
-                const V3 spec = surface.roughness == 0 ? v3(0.f, 0.f, 0.f)
-                                                       : ggx_times_ndotl(surface.view_dir, L, surface.normal, fmaxf(surface.roughness, RT2_MIN_ROUGHNESS), surface.specular_f0);
-                diffuse = light_sample.radiance * dd;
-                specular = spec * light_sample.radiance;
-            }
-        }
-        specular = v3(specular.x / fmaxf(0.01f, surface.specular_f0.x), specular.y / fmaxf(0.01f, surface.specular_f0.y), specular.z / fmaxf(0.01f, surface.specular_f0.z));
+        shade_surface_with_light_sample(a.sc, g, reservoir, surface, light_sample, &diffuse, &specular, rays, hits);
+        specular = demodulate_specular(surface.specular_f0, specular);
     }
     const uint32_t ptr = reservoir_pointer(di.reservoir_buffer_params.reservoir_block_row_pitch, di.reservoir_buffer_params.reservoir_array_pitch, lx, ly,
                                            di.buffer_indices.shading_input_buffer_index);
@@ -231,11 +257,249 @@ __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
     uint2* dst = reinterpret_cast<uint2*>(a.reservoirs + ptr);
     dst[0] = make_uint2(packed.light_data, packed.uv_data); dst[1] = make_uint2(packed.m_visibility, packed.distance_age);
     dst[2] = make_uint2(__float_as_uint(packed.target_pdf), __float_as_uint(packed.weight));
-    store_shading_output(g, (size_t)ly * a.width + lx, diffuse, specular, g.enable_restir_di == 1u, a.diffuse, a.specular, a.diffuse_f32);
-    // per-warp ray statistics
-    const uint32_t am = __activemask();
-    const uint32_t wr = __reduce_add_sync(am, rays), wh = __reduce_add_sync(am, hits);
-    if ((threadIdx.x & 31u) == (uint32_t)(__ffs(am) - 1)) { atomicAdd(a.stat_rays, (unsigned long long)wr); atomicAdd(a.stat_hits, (unsigned long long)wh); }
+    if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, diffuse, specular, g.enable_restir_di == 1u, a.diffuse, a.specular, a.diffuse_f32);   // imageStore outside the image is discarded
+    flush_ray_stats(a.stat_rays, a.stat_hits, rays, hits);
+}
+
+// ------------------------------------------------------------------------------------------------
+// The default ReSTIR-GI chain (src/light_passes.rs:621-659): K4 -> K5 -> K8.
+// One thread per launch index, 8x4 pixel tiles per warp.  K4 and K5 trace one incoherent ray each and are
+// bound like a bounce wavefront of K1; K8 only evaluates BRDFs (plus an optional visibility ray).  The
+// 48-byte secondary G-buffer record and the 32-byte GI reservoir move as 16-byte words.
+// ------------------------------------------------------------------------------------------------
+struct GIArgs {
+    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame;
+    GBufferRefs gb;
+    LightRefs li;
+    uint4* secondary;        // rt2_secondary_gbuffer_data: 3 x uint4 per entry
+    uint4* reservoirs;       // rt2_packed_gi_reservoir: 2 x uint4 per entry
+    ushort4* diffuse; ushort4* specular; float4* diffuse_f32;
+    unsigned long long* stat_rays; unsigned long long* stat_hits;
+};
+
+__device__ __forceinline__ V3 unpack_half3(uint32_t tx, uint32_t ty) {
+    return v3(f16_bits_to_f32((uint16_t)(tx & 0xffffu)), f16_bits_to_f32((uint16_t)(tx >> 16)), f16_bits_to_f32((uint16_t)(ty & 0xffffu)));
+}
+
+// K4 — lighting_passes/brdf_rays.rgen:19-195
+__global__ void __launch_bounds__(128) k_brdf_rays(GIArgs a) {
+    __shared__ float lut[256];
+    lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
+    __syncthreads();
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const rt2_gconst& g = *a.g;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+    uint32_t rays = 0, hits = 0;
+    if (surface.view_depth != RT2_BACKGROUND_DEPTH) {                  // RAB_IsSurfaceValid, bridge :346-349
+        Rng rng = rng_init(lx, ly, a.frame, 5u);
+        V3 tangent, bitangent; construct_onb(surface.normal, &tangent, &bitangent);        // branchlessONB, Helpers.glsl:271-278
+        const V3 cam = v3(g.view.camera_direction_or_position[0], g.view.camera_direction_or_position[1], g.view.camera_direction_or_position[2]);
+        const float depth = fmaxf(1.0f, 0.1f * length3(surface.world_pos - cam));
+        const float tmin = 0.001f * depth;
+        float tmax = RT2_BACKGROUND_DEPTH;
+        const float randx = rng_next(rng), randy = rng_next(rng);
+        const V3 V = normalize3(cam - surface.world_pos);
+        const bool is_delta = surface.roughness == 0;
+        bool is_specular_ray;
+        float specular_pdf, overall_pdf;
+        V3 brdf_over_pdf, dir;
+        {
+            const V3 Ve = v3(dot3(V, tangent), dot3(V, bitangent), dot3(V, surface.normal));
+            const V3 He = sample_ggx_vndf(Ve, surface.roughness, randx, randy);
+            const V3 H = is_delta ? surface.normal : normalize3((tangent * He.x + bitangent * He.y) + surface.normal * He.z);
+            const V3 specular_direction = reflect3(neg3(V), H);
+            const float HoV = saturatef(dot3(H, V)), NoV = saturatef(dot3(surface.normal, V));
+            const V3 F = schlick_fresnel(surface.specular_f0, HoV);
+            const float G1 = is_delta ? 1.0f : (NoV > 0) ? g1_smith(surface.roughness, NoV) : 0.f;
+            const V3 specular_brdf_over_pdf = F * G1;
+            const V3 local_direction = sample_cos_hemisphere(randx, randy, false);
+            const V3 diffuse_direction = (tangent * local_direction.x + bitangent * local_direction.y) + surface.normal * local_direction.z;
+            const float diffuse_brdf_over_pdf = 1.0f;
+            specular_pdf = saturatef(calc_luminance(specular_brdf_over_pdf) / calc_luminance(specular_brdf_over_pdf + surface.diffuse_albedo * diffuse_brdf_over_pdf));
+            is_specular_ray = rng_next(rng) < specular_pdf;
+            if (is_specular_ray) { dir = specular_direction; brdf_over_pdf = specular_brdf_over_pdf / specular_pdf; }
+            else { dir = diffuse_direction; const float d = diffuse_brdf_over_pdf / (1.0f - specular_pdf); brdf_over_pdf = v3(d, d, d); }
+            const float specular_lobe_pdf = ggx_vndf_pdf(surface.roughness, surface.normal, V, dir);
+            const float diffuse_lobe_pdf = saturatef(dot3(dir, surface.normal)) / RT2_RTXDI_PI;
+            overall_pdf = is_delta ? diffuse_lobe_pdf : mixf(diffuse_lobe_pdf, specular_lobe_pdf, specular_pdf);
+        }
+        if (dot3(surface.geo_normal, dir) <= 0.0f) { brdf_over_pdf = v3(0.f, 0.f, 0.f); tmax = 0.f; }
+        const V3 origin = surface.world_pos;
+        V3 radiance = v3(0.f, 0.f, 0.f);
+        Hit h; h.t = 0.f; h.u = h.v = 0.f; h.inst = 0u; h.geom = 0xFFFFFFFFu; h.prim = 0xFFFFFFFFu;
+        uint32_t tri_slot = 0;
+        if (tmin <= tmax) { h = trace_closest(a.sc, origin, dir, tmin, tmax, &tri_slot); rays++; }   // TMin > TMax: miss (oracle P2)
+        V3 sec_position, sec_normal, sec_albedo, sec_f0; float sec_roughness; bool sec_is_env;
+        const bool include_emissive = g.enable_restir_di == 0u || (is_specular_ray && is_delta);
+        if (h.geom != 0xFFFFFFFFu) {
+            hits++;
+            const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, h.inst, h.u, h.v);
+            if (include_emissive) radiance = radiance + sf.emission;
+            sec_position = origin + dir * h.t;
+            sec_normal = (dot3(sf.normal, dir) < 0) ? sf.normal : neg3(sf.normal);
+            sec_albedo = sf.color; sec_f0 = sf.specular_f0; sec_roughness = sf.roughness; sec_is_env = false;
+        } else {
+            if (include_emissive) radiance = radiance + environment_radiance(a.sc, g, dir);
+            sec_position = origin + dir * 1000.0f;                     // DISTANT_LIGHT_DISTANCE, PolymorphicLight.glsl:43
+            sec_normal = neg3(dir);
+            sec_albedo = v3(0.f, 0.f, 0.f); sec_f0 = v3(0.f, 0.f, 0.f); sec_roughness = 0.0f; sec_is_env = true;
+        }
+        if (g.enable_brdf_indirect == 1u) {
+            uint32_t fl = 0;
+            if (is_specular_ray) fl |= RT2_SECONDARY_IS_SPECULAR_RAY;
+            if (is_delta) fl |= RT2_SECONDARY_IS_DELTA_SURFACE;
+            if (sec_is_env) fl |= RT2_SECONDARY_IS_ENVIRONMENT;
+            const uint32_t ptr = reservoir_pointer(g.restir_gi.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_gi.reservoir_buffer_params.reservoir_array_pitch, lx, ly, 0u);
+            uint4* dst = a.secondary + 3 * (size_t)ptr;
+            dst[0] = make_uint4(__float_as_uint(sec_position.x), __float_as_uint(sec_position.y), __float_as_uint(sec_position.z), ndir_to_oct_unorm32(sec_normal));
+            dst[1] = make_uint4(pack_r16g16_float(brdf_over_pdf.x, brdf_over_pdf.y), pack_r16g16_float(brdf_over_pdf.z, 0.0f) | (fl << 16),
+                                pack_r11g11b10(sec_albedo), pack_rgba8_gamma(sec_f0.x, sec_f0.y, sec_f0.z, sec_roughness));
+            dst[2] = make_uint4(__float_as_uint(radiance.x), __float_as_uint(radiance.y), __float_as_uint(radiance.z), __float_as_uint(overall_pdf));
+            if (g.enable_restir_gi == 1u) radiance = v3(0.f, 0.f, 0.f);
+        }
+        if (radiance.x > 0.0f || radiance.y > 0.0f || radiance.z > 0.0f || g.enable_brdf_additive_blend == 0u) {
+            const V3 diffuse = is_specular_ray ? v3(0.f, 0.f, 0.f) : radiance * brdf_over_pdf;
+            V3 specular = is_specular_ray ? radiance * brdf_over_pdf : v3(0.f, 0.f, 0.f);
+            specular = demodulate_specular(surface.specular_f0, specular);
+            if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, diffuse, specular, false, a.diffuse, a.specular, a.diffuse_f32);
+        }
+    }
+    flush_ray_stats(a.stat_rays, a.stat_hits, rays, hits);
+}
+
+// K5 — lighting_passes/shade_secondary_surfaces.rgen:26-157
+__global__ void __launch_bounds__(128) k_shade_secondary(GIArgs a) {
+    __shared__ float lut[256];
+    lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
+    __syncthreads();
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const rt2_gconst& g = *a.g;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    uint32_t rays = 0, hits = 0;
+    Rng rng = rng_init(lx, ly, a.frame, 6u);
+    // sic: the secondary G-buffer is addressed with the DI pitches here (:35) and with the GI pitches in K4/K8
+    const uint32_t gbuffer_index = reservoir_pointer(g.restir_di.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_di.reservoir_buffer_params.reservoir_array_pitch, lx, ly, 0u);
+    const Surface primary = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+    uint4* sgp = a.secondary + 3 * (size_t)gbuffer_index;
+    const uint4 s0 = sgp[0], s1 = sgp[1], s2 = sgp[2];
+    const V3 throughput = unpack_half3(s1.x, s1.y);
+    const uint32_t flags = s1.y >> 16;
+    const bool valid_secondary = throughput.x != 0 || throughput.y != 0 || throughput.z != 0;
+    const bool is_specular_ray = (flags & RT2_SECONDARY_IS_SPECULAR_RAY) != 0u;
+    const bool is_delta = (flags & RT2_SECONDARY_IS_DELTA_SURFACE) != 0u;
+    const bool is_env = (flags & RT2_SECONDARY_IS_ENVIRONMENT) != 0u;
+    V3 radiance = v3(__uint_as_float(s2.x), __uint_as_float(s2.y), __uint_as_float(s2.z));
+    const float pdf = __uint_as_float(s2.w);
+    Surface sec = empty_surface();
+    sec.world_pos = v3(__uint_as_float(s0.x), __uint_as_float(s0.y), __uint_as_float(s0.z));
+    sec.view_depth = 1.0f;
+    sec.normal = oct_to_ndir_unorm32(s0.w);
+    sec.geo_normal = sec.normal;
+    sec.diffuse_albedo = unpack_r11g11b10(s1.z);
+    const float4 sr = unpack_rgba8_gamma(s1.w);
+    sec.specular_f0 = v3(sr.x, sr.y, sr.z);
+    sec.roughness = sr.w;
+    sec.diffuse_probability = 1.0f;
+    sec.view_dir = normalize3(primary.world_pos - sec.world_pos);
+    if (valid_secondary && !is_env && g.enable_restir_di == 1u) {
+        const SampleParams sp = init_sample_params(0u, 0u, 0u, 1u, 0.f, 0.001f);
+        LightSample light_sample;
+        DIReservoir reservoir = sample_lights_for_surface(a.sc, a.li, g, rng, sec, sp, &light_sample, rays, hits);
+        V3 indirect_diffuse, indirect_specular;
+        shade_surface_with_light_sample(a.sc, g, reservoir, sec, light_sample, &indirect_diffuse, &indirect_specular, rays, hits);
+        radiance = radiance + (indirect_diffuse * sec.diffuse_albedo + indirect_specular);
+        const float c_max_indirect_radiance = 100.0f;                  // firefly suppression, :113-116
+        const float lum = calc_luminance(radiance);
+        if (lum > c_max_indirect_radiance) radiance = radiance * (c_max_indirect_radiance / lum);
+    }
+    if (g.enable_restir_di == 0u) {                                    // :119-128: one more cosine bounce
+        V3 dir;
+        surface_brdf_sample(sec, rng, &dir);
+        uint32_t tri_slot;
+        const Hit h = trace_closest(a.sc, sec.world_pos, dir, 0.001f, 1000.0f, &tri_slot);
+        rays++;
+        V3 emission;
+        if (h.geom == 0xFFFFFFFFu) emission = environment_radiance(a.sc, g, dir);       // Q2 / oracle P4
+        else { hits++; emission = get_geometry_from_hit(a.sc, lut, tri_slot, h.inst, h.u, h.v).emission; }
+        radiance = radiance + emission * sec.diffuse_albedo;
+    }
+    GIReservoir reservoir = empty_gi_reservoir();
+    const bool output_shading_result = is_specular_ray && is_delta;
+    if (valid_secondary && !output_shading_result) reservoir = make_gi_reservoir(sec.world_pos, sec.normal, radiance, pdf);
+    const uint32_t rx = g.runtime_params.active_checkerboard_field != 0u ? (px >> 1) : px;     // RTXDI_PixelPosToReservoirPos
+    store_gi_reservoir(a.reservoirs, reservoir_pointer(g.restir_gi.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_gi.reservoir_buffer_params.reservoir_array_pitch,
+                                                       rx, py, g.restir_gi.buffer_indices.secondary_surface_restirdi_output_buffer_index), reservoir, 0u);
+    const V3 saved = output_shading_result ? v3(0.f, 0.f, 0.f) : radiance;                    // initial sample radiance for the MIS in K8
+    sgp[2] = make_uint4(__float_as_uint(saved.x), __float_as_uint(saved.y), __float_as_uint(saved.z), s2.w);
+    if (output_shading_result) {
+        const V3 specular = demodulate_specular(primary.specular_f0, radiance);              // is_specular_ray holds: diffuse = 0
+        if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, v3(0.f, 0.f, 0.f), specular, false, a.diffuse, a.specular, a.diffuse_f32);
+    }
+    flush_ray_stats(a.stat_rays, a.stat_hits, rays, hits);
+}
+
+// K8 — lighting_passes/gi_final_shading.rgen:18-101
+__device__ __forceinline__ float gi_mis_weight(const SplitBrdf& rough, const SplitBrdf& tru, V3 albedo) {
+    const float k_max = 1e4f;
+    V3 cr = albedo * rough.demodulated_diffuse + rough.specular;
+    V3 ct = albedo * tru.demodulated_diffuse + tru.specular;
+    cr = v3(clampf(cr.x, 1e-4f, k_max), clampf(cr.y, 1e-4f, k_max), clampf(cr.z, 1e-4f, k_max));
+    ct = v3(clampf(ct.x, 0.f, k_max), clampf(ct.y, 0.f, k_max), clampf(ct.z, 0.f, k_max));
+    const float w = saturatef(calc_luminance(ct) / calc_luminance(ct + cr));
+    return w * w * w;
+}
+
+__global__ void __launch_bounds__(128) k_gi_final_shading(GIArgs a) {
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const rt2_gconst& g = *a.g;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    uint32_t rays = 0, hits = 0;
+    const Surface primary = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+    const uint32_t rx = g.runtime_params.active_checkerboard_field != 0u ? (px >> 1) : px;
+    const uint32_t row_pitch = g.restir_gi.reservoir_buffer_params.reservoir_block_row_pitch, array_pitch = g.restir_gi.reservoir_buffer_params.reservoir_array_pitch;
+    // sic: reads the K5 output page, not finalShadingInputBufferIndex (:50)
+    const GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, g.restir_gi.buffer_indices.secondary_surface_restirdi_output_buffer_index));
+    V3 diffuse = v3(0.f, 0.f, 0.f), specular = v3(0.f, 0.f, 0.f);
+    if (reservoir.M != 0u) {
+        V3 radiance = reservoir.radiance * reservoir.weight_sum;
+        V3 visibility = v3(1.f, 1.f, 1.f);
+        if (g.restir_gi.final_shading_params.enable_final_visibility == 1u) {
+            const bool miss = visibility_ray_miss(a.sc, primary, reservoir.position, 0.001f, &rays);
+            if (!miss) hits++;
+            const float vis = miss ? 1.0f : 0.0f;
+            visibility = v3(vis, vis, vis);
+        }
+        radiance = radiance * visibility;
+        const SplitBrdf brdf = evaluate_brdf(primary, reservoir.position);
+        if (g.restir_gi.final_shading_params.enable_final_mis == 1u) {
+            const uint4* sgp = a.secondary + 3 * (size_t)reservoir_pointer(row_pitch, array_pitch, rx, py, 0u);       // LoadInitialSampleReservoir, :30-41
+            const uint4 s0 = sgp[0], s1 = sgp[1], s2 = sgp[2];
+            const V3 normal = oct_to_ndir_unorm32(s0.w);
+            const V3 throughput = unpack_half3(s1.x, s1.y);
+            const GIReservoir initial = make_gi_reservoir(v3(__uint_as_float(s0.x), __uint_as_float(s0.y), __uint_as_float(s0.z)), normal,
+                                                          v3(__uint_as_float(s2.x), __uint_as_float(s2.y), __uint_as_float(s2.z)) * throughput, __uint_as_float(s2.w));
+            const SplitBrdf brdf0 = evaluate_brdf(primary, initial.position);
+            Surface roughened = primary;
+            roughened.roughness = fmaxf(roughened.roughness, 0.3f);                          // kMISRoughness
+            const SplitBrdf rough_brdf = evaluate_brdf(roughened, reservoir.position);
+            const SplitBrdf rough_brdf0 = evaluate_brdf(roughened, initial.position);
+            const float final_weight = 1.0f - gi_mis_weight(rough_brdf, brdf, primary.diffuse_albedo);
+            const float initial_weight = gi_mis_weight(rough_brdf0, brdf0, primary.diffuse_albedo);
+            const V3 initial_radiance = initial.radiance * initial.weight_sum;
+            diffuse = radiance * brdf.demodulated_diffuse * final_weight + initial_radiance * brdf0.demodulated_diffuse * initial_weight;
+            specular = brdf.specular * radiance * final_weight + brdf0.specular * initial_radiance * initial_weight;
+        } else {
+            diffuse = radiance * brdf.demodulated_diffuse;
+            specular = brdf.specular * radiance;
+        }
+        specular = demodulate_specular(primary.specular_f0, specular);
+    }
+    if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, diffuse, specular, g.enable_restir_di == 0u, a.diffuse, a.specular, a.diffuse_f32);
+    flush_ray_stats(a.stat_rays, a.stat_hits, rays, hits);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -245,7 +509,8 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     if (!ctx->scene.accel_built) return fail(ctx, RT2_E_STATE, "no acceleration structure: call rt2_upload_scene + rt2_build_accel first");
     if (lp.band_world > 1u) return fail(ctx, RT2_E_INVALID, "row-band sharding is implemented for the reference path tracer only");
     const rt2_gconst& g = ctx->gconst;
-    if (g.enable_restir_gi == 1u) return fail(ctx, RT2_E_STATE, "the ReSTIR GI chain (brdf_rays / shade_secondary / gi_final_shading) is not built yet: set enable_restir_gi = 0");
+    if (g.enable_restir_gi == 1u && (g.enable_temporal_resampling == 1u || g.enable_spatial_resampling == 1u))
+        return fail(ctx, RT2_E_STATE, "GI temporal / spatial resampling (K6 / K7) is not built: clear enable_temporal_resampling and enable_spatial_resampling");
     int rc = restir_ensure_resources(ctx); if (rc) return rc;
     FrameBuffers& f = ctx->fb;
     // counters: [0..1] rays, [2..3] hits
@@ -260,43 +525,67 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     ctx->last_gbuffer_index = cur;
     const uint32_t tiles_x = (f.width + 7) / 8, tiles_y = (f.height + 3) / 4;
     const uint32_t padded = tiles_x * tiles_y * 32;
+    const uint32_t blocks = (padded + 127) / 128;
     uint64_t launches = 0;
-    // K3
-    GBufferArgs ga{};
-    ga.sc = make_scene_refs(ctx); ga.g = ctx->d_gconst; ga.width = f.width; ga.height = f.height;
-    ga.depth = f.gb_depth[cur]; ga.normals = f.gb_normals[cur]; ga.geo_normals = f.gb_geo_normals[cur]; ga.diffuse_albedo = f.gb_diffuse_albedo[cur];
-    ga.specular_rough = f.gb_specular_rough[cur]; ga.emissive = f.gb_emissive[cur]; ga.motion = f.motion_vectors; ga.stat_hits = stat_hits;
-    k_gbuffer<<<(padded + 127) / 128, 128, 0, ctx->stream>>>(ga); launches++;
-    uint64_t static_rays = (uint64_t)f.width * f.height;
-    // K9
+    auto pitches_ok = [&](const rt2_reservoir_buffer_params& p) {
+        return p.reservoir_array_pitch == f.reservoir_array_pitch && p.reservoir_block_row_pitch == f.reservoir_block_row_pitch;
+    };
+    // ---- validation of everything the enabled passes will index with -------------------------------------------
+    LightRefs lrefs{};
     if (g.enable_restir_di == 1u) {
         const uint32_t num_local = g.light_buffer_params.local_light_buffer_region.num_lights;
         if (g.light_buffer_params.infinite_light_buffer_region.num_lights != 0u) return fail(ctx, RT2_E_INVALID, "infinite lights have no producer in the reference (src/main.rs:375-380)");
         if (g.restir_di.initial_sampling_params.num_primary_environment_samples != 0u) return fail(ctx, RT2_E_INVALID, "environment RIS sampling is compiled out (RTXDI_ENABLE_PRESAMPLING 0)");
-        if (g.restir_di.reservoir_buffer_params.reservoir_array_pitch != f.reservoir_array_pitch || g.restir_di.reservoir_buffer_params.reservoir_block_row_pitch != f.reservoir_block_row_pitch)
-            return fail(ctx, RT2_E_INVALID, "GConst reservoir buffer parameters do not match the frame size (calculate_reservoir_buffer_parameters)");
+        if (!pitches_ok(g.restir_di.reservoir_buffer_params)) return fail(ctx, RT2_E_INVALID, "GConst reservoir buffer parameters do not match the frame size (calculate_reservoir_buffer_parameters)");
         if (g.restir_di.buffer_indices.shading_input_buffer_index > 1u) return fail(ctx, RT2_E_INVALID, "reservoir buffer index out of range");
         if (num_local) {
             if (!ctx->lights_prepared) return fail(ctx, RT2_E_STATE, "light list not built: call rt2_prepare_lights (+ rt2_generate_mips(0)) first");
             if (g.light_buffer_params.local_light_buffer_region.first_light_index + (uint64_t)num_local > ctx->light_capacity) return fail(ctx, RT2_E_INVALID, "local light region exceeds the light buffer");
         }
         if ((rc = lights_ensure_resources(ctx))) return rc;
+        lrefs.lights = ctx->light_info; lrefs.geom_to_light = ctx->geom_to_light;
+        lrefs.pdf = ctx->local_pdf; lrefs.pdf_w = ctx->local_pdf_w; lrefs.pdf_h = ctx->local_pdf_h;
+        const uint32_t m = std::max(ctx->local_pdf_w, ctx->local_pdf_h);
+        uint32_t last = 0; while ((2u << last) <= m) last++;           // floor(log2(m))
+        last = std::min(last, ctx->local_pdf_mips - 1);
+        uint32_t off = 0;
+        for (uint32_t k = 0; k < last; k++) off += std::max(1u, ctx->local_pdf_w >> k) * std::max(1u, ctx->local_pdf_h >> k);
+        lrefs.pdf_last_offset = off;
+    }
+    if (g.enable_restir_gi == 1u) {
+        if (!pitches_ok(g.restir_gi.reservoir_buffer_params) || !pitches_ok(g.restir_di.reservoir_buffer_params))   // K5 addresses the secondary G-buffer with the DI pitches
+            return fail(ctx, RT2_E_INVALID, "GConst reservoir buffer parameters do not match the frame size (calculate_reservoir_buffer_parameters)");
+        if (g.restir_gi.buffer_indices.secondary_surface_restirdi_output_buffer_index > 1u) return fail(ctx, RT2_E_INVALID, "GI reservoir buffer index out of range");
+        if (g.runtime_params.active_checkerboard_field > 2u) return fail(ctx, RT2_E_INVALID, "active_checkerboard_field must be 0, 1 or 2");
+    }
+    // ---- K3
+    GBufferArgs ga{};
+    ga.sc = make_scene_refs(ctx); ga.g = ctx->d_gconst; ga.width = f.width; ga.height = f.height;
+    ga.depth = f.gb_depth[cur]; ga.normals = f.gb_normals[cur]; ga.geo_normals = f.gb_geo_normals[cur]; ga.diffuse_albedo = f.gb_diffuse_albedo[cur];
+    ga.specular_rough = f.gb_specular_rough[cur]; ga.emissive = f.gb_emissive[cur]; ga.motion = f.motion_vectors; ga.stat_hits = stat_hits;
+    k_gbuffer<<<blocks, 128, 0, ctx->stream>>>(ga); launches++;
+    uint64_t static_rays = (uint64_t)f.width * f.height;
+    const GBufferRefs gbrefs{f.gb_depth[cur], f.gb_normals[cur], f.gb_geo_normals[cur], f.gb_diffuse_albedo[cur], f.gb_specular_rough[cur]};
+    // ---- K9
+    if (g.enable_restir_di == 1u) {
         DIArgs da{};
         da.sc = ga.sc; da.g = ctx->d_gconst; da.width = f.width; da.height = f.height; da.frame = frame;
-        da.gb = GBufferRefs{f.gb_depth[cur], f.gb_normals[cur], f.gb_geo_normals[cur], f.gb_diffuse_albedo[cur], f.gb_specular_rough[cur]};
-        da.lights = ctx->light_info; da.geom_to_light = ctx->geom_to_light;
-        da.pdf = ctx->local_pdf; da.pdf_w = ctx->local_pdf_w; da.pdf_h = ctx->local_pdf_h;
-        {
-            const uint32_t m = std::max(ctx->local_pdf_w, ctx->local_pdf_h);
-            uint32_t last = 0; while ((2u << last) <= m) last++;           // floor(log2(m))
-            last = std::min(last, ctx->local_pdf_mips - 1);
-            uint32_t off = 0;
-            for (uint32_t k = 0; k < last; k++) off += std::max(1u, ctx->local_pdf_w >> k) * std::max(1u, ctx->local_pdf_h >> k);
-            da.pdf_last_offset = off;
-        }
+        da.gb = gbrefs; da.li = lrefs;
         da.reservoirs = f.di_reservoirs; da.diffuse = f.diffuse_f16; da.specular = f.specular_f16; da.diffuse_f32 = f.diffuse_f32;
         da.stat_rays = stat_rays; da.stat_hits = stat_hits;
-        k_di_fused<<<(padded + 127) / 128, 128, 0, ctx->stream>>>(da); launches++;
+        k_di_fused<<<blocks, 128, 0, ctx->stream>>>(da); launches++;
+    }
+    // ---- K4 -> K5 -> K8 (stream order is the ALL_COMMANDS barrier of src/light_passes.rs:621-659)
+    if (g.enable_restir_gi == 1u) {
+        GIArgs gi{};
+        gi.sc = ga.sc; gi.g = ctx->d_gconst; gi.width = f.width; gi.height = f.height; gi.frame = frame;
+        gi.gb = gbrefs; gi.li = lrefs;
+        gi.secondary = f.secondary_gbuffer; gi.reservoirs = f.gi_reservoirs;
+        gi.diffuse = f.diffuse_f16; gi.specular = f.specular_f16; gi.diffuse_f32 = f.diffuse_f32;
+        gi.stat_rays = stat_rays; gi.stat_hits = stat_hits;
+        k_brdf_rays<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+        k_shade_secondary<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+        k_gi_final_shading<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
     }
     RT2_CUDA(ctx, cudaGetLastError());
     ctx->stats.kernel_launches = launches;

@@ -210,4 +210,129 @@ __device__ __forceinline__ float light_brdf_mis_weight(const Surface& s, const L
     return blended / pdf;
 }
 
+// ---- EvaluateBrdf (bridge :146-159), DemodulateSpecular (Helpers.glsl:312-315) ---------------------------------
+struct SplitBrdf { float demodulated_diffuse; V3 specular; };
+__device__ __forceinline__ SplitBrdf evaluate_brdf(const Surface& s, V3 sample_position) {
+    const V3 L = normalize3(sample_position - s.world_pos);
+    SplitBrdf b;
+    b.demodulated_diffuse = lambert(s.normal, neg3(L));
+    b.specular = s.roughness == 0 ? v3(0.f, 0.f, 0.f) : ggx_times_ndotl(s.view_dir, L, s.normal, fmaxf(s.roughness, RT2_MIN_ROUGHNESS), s.specular_f0);
+    return b;
+}
+__device__ __forceinline__ V3 demodulate_specular(V3 f0, V3 specular) {
+    return v3(specular.x / fmaxf(0.01f, f0.x), specular.y / fmaxf(0.01f, f0.y), specular.z / fmaxf(0.01f, f0.z));
+}
+__device__ __forceinline__ V3 schlick_fresnel(V3 F0, float VdotH) {                      // Helpers.glsl:199-202
+    const float p = pow_pinned(fmaxf(1 - VdotH, 0.f), 5.0f);
+    return v3(F0.x + (1 - F0.x) * p, F0.y + (1 - F0.y) * p, F0.z + (1 - F0.z) * p);
+}
+
+// ---- VNDF sampling pieces of K4: Helpers.glsl:281-310 ------------------------------------------------------------
+__device__ __forceinline__ V3 sample_ggx_vndf(V3 Ve, float roughness, float randx, float randy) {
+    const float alpha = roughness * roughness;
+    const V3 Vh = normalize3(v3(alpha * Ve.x, alpha * Ve.y, Ve.z));
+    const float lensq = Vh.x * Vh.x + Vh.y * Vh.y;
+    const V3 T1 = lensq > 0.0f ? v3(-Vh.y, Vh.x, 0.0f) / sqrtf(lensq) : v3(1.0f, 0.0f, 0.0f);
+    const V3 T2 = cross3(Vh, T1);
+    const float r = sqrtf(randx);
+    const float phi = 2.0f * RT2_RTXDI_PI * randy;
+    float sn, cs; sincos_pinned(phi, &sn, &cs);
+    const float t1 = r * cs;
+    float t2 = r * sn;
+    const float sv = 0.5f * (1.0f + Vh.z);
+    t2 = (1.0f - sv) * sqrtf(1.0f - t1 * t1) + sv * t2;
+    const V3 Nh = (T1 * t1 + T2 * t2) + Vh * sqrtf(fmaxf(0.0f, (1.0f - t1 * t1) - t2 * t2));
+    return v3(alpha * Nh.x, alpha * Nh.y, fmaxf(0.0f, Nh.z));
+}
+__device__ __forceinline__ float g1_smith(float roughness, float NdotL) {
+    const float alpha = roughness * roughness;
+    return 2.0f * NdotL / (NdotL + sqrtf(alpha * alpha + (1.0f - alpha * alpha) * NdotL * NdotL));
+}
+__device__ __forceinline__ V3 reflect3(V3 I, V3 N) { const float k = 2.0f * dot3(N, I); return I - N * k; }
+
+// ---- GI reservoir codecs: rtxdi/RtxdiMath.hlsli:129-296 (round() pinned to half-to-even, oracle P1) -------------
+__device__ __forceinline__ uint32_t pack_snorm2x16(float vx, float vy) {
+    if (isnan(vx) || isnan(vy)) { vx = 0.f; vy = 0.f; } else { vx = clampf(vx, -1.0f, 1.0f); vy = clampf(vy, -1.0f, 1.0f); }
+    const int ix = (int)rintf(vx * 32767.0f), iy = (int)rintf(vy * 32767.0f);
+    return ((uint32_t)ix & 0x0000ffffu) | ((uint32_t)iy << 16);
+}
+__device__ __forceinline__ uint32_t encode_snorm_oct(V3 n) {
+    const float inv = 1.0f / ((fabsf(n.x) + fabsf(n.y)) + fabsf(n.z));
+    float px = n.x * inv, py = n.y * inv;
+    if (n.z < 0.0f) {
+        const float qx = (1.0f - fabsf(py)) * (px >= 0.0f ? 1.0f : -1.0f);
+        const float qy = (1.0f - fabsf(px)) * (py >= 0.0f ? 1.0f : -1.0f);
+        px = qx; py = qy;
+    }
+    return pack_snorm2x16(px, py);
+}
+__device__ __forceinline__ V3 decode_snorm_oct(uint32_t packed) {
+    const int bx = (int)(packed << 16) >> 16, by = (int)packed >> 16;
+    const float px = fmaxf((float)bx / 32767.0f, -1.0f), py = fmaxf((float)by / 32767.0f, -1.0f);
+    V3 n = v3(px, py, (1.0f - fabsf(px)) - fabsf(py));
+    if (n.z < 0.0f) {
+        const float qx = (1.0f - fabsf(n.y)) * (n.x >= 0.0f ? 1.0f : -1.0f);
+        const float qy = (1.0f - fabsf(n.x)) * (n.y >= 0.0f ? 1.0f : -1.0f);
+        n.x = qx; n.y = qy;
+    }
+    return normalize3(n);
+}
+__device__ __forceinline__ uint32_t encode_logluv(V3 c) {
+    const float X = dot3(c, v3(0.4123907992659595f, 0.3575843393838780f, 0.1804807884018343f));
+    const float Y = dot3(c, v3(0.2126390058715104f, 0.7151686787677559f, 0.0721923153607337f));
+    const float Z = dot3(c, v3(0.0193308187155918f, 0.1191947797946259f, 0.9505321522496608f));
+    const float logY = 409.6f * (log2_pinned(Y) + 20.0f);
+    const float cl = clampf(logY, 0.0f, 16383.0f);
+    const uint32_t Le = isnan(cl) ? 0u : (uint32_t)cl;
+    if (Le == 0u) return 0u;
+    const float inv_denom = 1.0f / ((-2.0f * X + 12.0f * Y) + 3.0f * ((X + Y) + Z));
+    const float u = 4.0f * X * inv_denom, v = 9.0f * Y * inv_denom;
+    const float cu = clampf(820.0f * u, 0.0f, 511.0f), cv = clampf(820.0f * v, 0.0f, 511.0f);
+    const uint32_t ue = isnan(cu) ? 0u : (uint32_t)cu, ve = isnan(cv) ? 0u : (uint32_t)cv;
+    return (Le << 18) | (ue << 9) | ve;
+}
+__device__ __forceinline__ V3 decode_logluv(uint32_t packed) {
+    const uint32_t Le = packed >> 18;
+    if (Le == 0u) return v3(0.f, 0.f, 0.f);
+    const float logY = ((float)Le + 0.5f) / 409.6f - 20.0f;
+    const float Y = pow_pinned(2.0f, logY);
+    const uint32_t ue = (packed >> 9) & 0x1ffu, ve = packed & 0x1ffu;
+    const float u = ((float)ue + 0.5f) / 820.0f, v = ((float)ve + 0.5f) / 820.0f;
+    const float inv_denom = 1.0f / ((6.0f * u - 16.0f * v) + 12.0f);
+    const float x = 9.0f * u * inv_denom, y = 4.0f * v * inv_denom;
+    const float sc = Y / y;
+    const V3 XYZ = v3(sc * x, Y, sc * ((1.f - x) - y));
+    const float r = dot3(XYZ, v3(3.240969941904522f, -1.537383177570094f, -0.4986107602930032f));
+    const float g = dot3(XYZ, v3(-0.9692436362808803f, 1.875967501507721f, 0.04155505740717569f));
+    const float b = dot3(XYZ, v3(0.05563007969699373f, -0.2039769588889765f, 1.056971514242878f));
+    return v3(fmaxf(r, 0.0f), fmaxf(g, 0.0f), fmaxf(b, 0.0f));
+}
+
+// ---- GI reservoirs: rtxdi/GIReservoir.hlsli:29-185, GIResamplingFunctions.hlsli:97-111 ---------------------------
+struct GIReservoir { V3 position, normal, radiance; float weight_sum; uint32_t M, age; };
+__device__ __forceinline__ GIReservoir empty_gi_reservoir() {
+    GIReservoir r; r.position = r.normal = r.radiance = v3(0.f, 0.f, 0.f); r.weight_sum = 0.f; r.M = 0u; r.age = 0u; return r;
+}
+__device__ __forceinline__ GIReservoir make_gi_reservoir(V3 pos, V3 normal, V3 radiance, float pdf) {
+    GIReservoir r; r.position = pos; r.normal = normal; r.radiance = radiance;
+    r.weight_sum = pdf > 0.0f ? 1.0f / pdf : 0.0f; r.M = 1u; r.age = 0u;
+    return r;
+}
+// 32-byte packed form as two 16-byte words: {pos.xyz, misc_age_M}, {radiance, weight, normal, unused}
+__device__ __forceinline__ void store_gi_reservoir(uint4* buf, uint32_t ptr, const GIReservoir& r, uint32_t misc) {
+    const uint32_t mam = (misc & 0xffff0000u) | (min(r.age, 0xffu) << 8) | min(r.M, 0xffu);
+    buf[2 * (size_t)ptr] = make_uint4(__float_as_uint(r.position.x), __float_as_uint(r.position.y), __float_as_uint(r.position.z), mam);
+    buf[2 * (size_t)ptr + 1] = make_uint4(encode_logluv(r.radiance), __float_as_uint(r.weight_sum), encode_snorm_oct(r.normal), 0u);
+}
+__device__ __forceinline__ GIReservoir load_gi_reservoir(const uint4* buf, uint32_t ptr) {
+    const uint4 a = buf[2 * (size_t)ptr], b = buf[2 * (size_t)ptr + 1];
+    GIReservoir r;
+    r.position = v3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
+    r.normal = decode_snorm_oct(b.z);
+    r.radiance = decode_logluv(b.x);
+    r.weight_sum = __uint_as_float(b.y);
+    r.M = a.w & 0xffu; r.age = (a.w >> 8) & 0xffu;
+    return r;
+}
+
 }  // namespace rt2

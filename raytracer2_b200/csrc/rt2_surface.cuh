@@ -78,8 +78,9 @@ __device__ __forceinline__ V3 sample_texture(const uint32_t* __restrict__ texels
 __device__ __forceinline__ V3 environment_radiance(const SceneRefs& a, const rt2_gconst& g, V3 dir) {
     if (g.environment != 1u || a.sky == nullptr) return v3(0.f, 0.f, 0.f);
     const float PI_ = 3.1415926f;
-    const float u = 0.5f + atan2f(dir.z, dir.x) / (2.0f * PI_);
-    const float v = 0.5f - asinf(dir.y) / PI_;
+    // atan / asin follow the transcendental pin (binary64, rounded once), so the lookup is bit-identical to the oracle's
+    const float u = 0.5f + (float)atan2((double)dir.z, (double)dir.x) / (2.0f * PI_);
+    const float v = 0.5f - (float)asin((double)dir.y) / PI_;
     const int W = (int)a.sky_w, H = (int)a.sky_h;
     const float x = u * (float)W - 0.5f, y = v * (float)H - 0.5f;
     const float fx = floorf(x), fy = floorf(y);

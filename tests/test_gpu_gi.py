@@ -1,0 +1,133 @@
+"""GPU parity of the default ReSTIR-GI chain: K4 brdf_rays -> K5 shade_secondary_surfaces -> K8 gi_final_shading
+through the C ABI (rt2_render with refrence_mode 0, enable_restir_gi 1) against the CPU oracle on the same G-buffer.
+Compared bit for bit: the 48-byte secondary G-buffer, the packed 32-byte GI reservoirs (LogLuv radiance, snorm16
+octahedral normal) and both rgba16f lighting images.  Tolerance: log2/pow are evaluated in binary64 and rounded once
+on both sides, which can differ in the last bit for ~1e-5 of the inputs; such a pixel may differ, nothing else may."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import raytracer2_b200 as rt
+from oracle import oracle_ffi as O
+
+pytestmark = pytest.mark.gpu
+
+GB_KEYS = [("depth", rt.BUF_GBUFFER_DEPTH, np.float32, 1), ("normals", rt.BUF_GBUFFER_NORMALS, np.uint32, 1),
+           ("geo_normals", rt.BUF_GBUFFER_GEO_NORMALS, np.uint32, 1), ("diffuse_albedo", rt.BUF_GBUFFER_DIFFUSE_ALBEDO, np.uint32, 1),
+           ("specular_rough", rt.BUF_GBUFFER_SPECULAR_ROUGH, np.uint32, 1)]
+
+
+def _ctx(kind, scale, w, h, tex=64):
+    sc = rt.Scene(kind, scale, tex, 0)
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+    g.refrence_mode = 0
+    return sc, ctx, g, rt.LightPasses(ctx, w, h)
+
+
+def _read_gb(ctx, w, h):
+    return {k: ctx.read(b, dt).reshape(h, w) for k, b, dt, n in GB_KEYS}
+
+
+def _light_inputs(sc, ctx):
+    pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
+    mips = [ctx.read(rt.BUF_LOCAL_PDF_MIP0 + k, np.float32) for k in range(pm.value)]
+    return {"lights": ctx.read(rt.BUF_LIGHT_INFO, np.uint32).reshape(-1, 12), "geom_to_light": ctx.read(rt.BUF_GEOM_TO_LIGHT, np.uint32),
+            "pdf_packed": np.concatenate([m.ravel() for m in mips]), "pdf_dims": (pw.value, ph.value, pm.value)}
+
+
+def _run(kind, scale, w, h, frames=(1,), di=0, final_vis=0, mis=1, env=0, additive=1, oflags=O.ORC_BRUTE_FORCE, local=2, brdf=1):
+    sc, ctx, g, lp = _ctx(kind, scale, w, h)
+    g.enable_restir_gi = 1; g.enable_restir_di = di; g.environment = env; g.enable_brdf_additive_blend = additive
+    g.restir_gi.final_shading_params.enable_final_visibility = final_vis
+    g.restir_gi.final_shading_params.enable_final_mis = mis
+    g.restir_di.initial_sampling_params.num_primary_local_light_samples = local
+    g.restir_di.initial_sampling_params.num_primary_brdf_samples = brdf
+    g.restir_di.shading_params.enable_final_visibility = 1
+    if di:
+        rt.PrepareLightsTasks(ctx).execute()
+        rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    osc = O.OracleScene(sc.desc)
+    pitch = g.restir_gi.reservoir_buffer_params.reservoir_array_pitch
+    state = None
+    out = []
+    for frame in frames:
+        g.frame = frame
+        lp.update_uniform(g)
+        lp.execute(frame)
+        gb = _read_gb(ctx, w, h)
+        got = {"secondary": ctx.read(rt.BUF_SECONDARY_GBUFFER, np.uint32).reshape(-1, 12), "gi_reservoirs": ctx.read(rt.BUF_GI_RESERVOIRS, np.uint32).reshape(-1, 8),
+               "diffuse": ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).reshape(h, w, 4), "specular": ctx.read(rt.BUF_SPECULAR_F16, np.uint16).reshape(h, w, 4)}
+        st = ctx.stats()
+        li = _light_inputs(sc, ctx) if di else None
+        if state is None:
+            state = {"secondary": np.zeros((pitch, 12), np.uint32), "gi_reservoirs": np.zeros((pitch * 2, 8), np.uint32),
+                     "diffuse": np.zeros((h, w, 4), np.uint16), "specular": np.zeros((h, w, 4), np.uint16)}
+        rays_di = 0
+        if di:
+            _, _, _, rays_di = osc.di_fused_resampling(g, frame, w, h, gb, li["lights"], li["geom_to_light"], li["pdf_packed"], *li["pdf_dims"],
+                                                       g.restir_di.reservoir_buffer_params.reservoir_array_pitch,
+                                                       diffuse_f16=state["diffuse"], specular_f16=state["specular"], flags=oflags)
+        state = osc.gi_chain(g, frame, w, h, gb, pitch, light_inputs=li, state=state, flags=oflags)
+        out.append((got, {k: v.copy() for k, v in state.items() if k != "rays"}, st.rays_traced - w * h, rays_di + sum(state["rays"]), gb))
+    ctx.close()
+    return out
+
+
+def _check(got, ref, w, h, tol):
+    for key in ("secondary", "gi_reservoirs"):
+        assert got[key].shape == ref[key].shape
+        bad = np.flatnonzero((got[key] != ref[key]).any(axis=1))
+        assert len(bad) <= tol, f"{key}: {len(bad)} records differ, first {bad[:4]}: {got[key][bad[:1]]} vs {ref[key][bad[:1]]}"
+    for key in ("diffuse", "specular"):
+        nbad = int((got[key] != ref[key]).any(axis=2).sum())
+        assert nbad <= tol, f"{key}: {nbad} pixels differ"
+
+
+@pytest.mark.parametrize("kind,scale,w,h,kw", [
+    (rt.SCENE_CORNELL, 1.0, 512, 512, dict()),                                         # the reference's default frame (src/main.rs:388-399) at config 1 size
+    (rt.SCENE_CORNELL, 1.0, 200, 120, dict(mis=0, final_vis=1, additive=0)),
+    (rt.SCENE_HALL, 0.125, 320, 180, dict(final_vis=1, oflags=0)),
+    (rt.SCENE_INSTANCED, 0.05, 320, 180, dict(env=1, oflags=0)),                       # open scene under a sky: environment secondary surfaces
+    (rt.SCENE_CORNELL, 1.0, 256, 256, dict(di=1)),                                     # DI on: K5 samples the light list at the secondary hit
+    (rt.SCENE_MANYLIGHT, 0.2, 320, 180, dict(di=1, final_vis=1, oflags=0)),
+])
+def test_gi_chain_bit_exact(kind, scale, w, h, kw):
+    (got, ref, rays, rrays, gb), = _run(kind, scale, w, h, **kw)
+    tol = max(2, w * h // 50000)
+    _check(got, ref, w, h, tol)
+    assert rays == rrays
+    hit = gb["depth"] != 100000.0
+    valid = (ref["gi_reservoirs"][:, 3] & 0xff) != 0
+    assert hit.any() and valid.any()
+    d = got["diffuse"].view(np.float16)[:, :, :3].astype(np.float32)
+    assert np.isfinite(d).all() and d.max() > 0
+
+
+def test_gi_chain_state_carries_over_frames():
+    """The secondary G-buffer and the reservoirs persist: background pixels keep what an earlier frame left there."""
+    outs = _run(rt.SCENE_CORNELL, 1.0, 160, 96, frames=(1, 2, 3))
+    for (got, ref, rays, rrays, gb) in outs:
+        _check(got, ref, 160, 96, 2)
+        assert rays == rrays
+    assert not np.array_equal(outs[0][0]["gi_reservoirs"], outs[1][0]["gi_reservoirs"])
+
+
+def test_gi_default_frame_traces_three_rays_per_pixel_at_most():
+    """the default frame is K3 + K4 + K5 = 3 rays / pixel (K4 skips background pixels and below-horizon samples)."""
+    (got, ref, rays, rrays, gb), = _run(rt.SCENE_CORNELL, 1.0, 128, 128)
+    n = 128 * 128
+    hit = int((gb["depth"] != 100000.0).sum())
+    assert rays == rrays and n < rays <= n + hit           # K5 traces every launch index, K4 only valid surfaces
+
+
+def test_gi_rejects_unbuilt_resampling_passes():
+    sc, ctx, g, lp = _ctx(rt.SCENE_CORNELL, 1.0, 64, 64)
+    g.enable_restir_gi = 1; g.enable_temporal_resampling = 1
+    lp.update_uniform(g)
+    with pytest.raises(rt.Rt2Error):
+        lp.execute(1)
+    ctx.close()

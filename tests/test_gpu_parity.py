@@ -68,18 +68,21 @@ def test_reference_path_tracer_bit_exact(kind, scale, w, h, spp, bounces):
     ctx.close()
 
 
-def test_instanced_path_tracer_close_to_oracle():
-    """Environment lookups use atan2/asin (libdevice vs glibc): statistical bound instead of bit-exact."""
+def test_instanced_path_tracer_with_environment_bit_exact():
+    """Two-level traversal + environment lookups.  atan2/asin of the equirect mapping follow the transcendental pin
+    (binary64, rounded once) on both sides; a last-bit disagreement of the two binary64 libraries can only show where
+    the result sits within ~1e-16 of a binary32 rounding boundary, so at most a couple of pixels may differ."""
     w, h = 192, 108
     sc, g, ctx, lp = _gpu_setup(rt.SCENE_INSTANCED, 0.05, w, h)
     g.environment = 1
     lp.update_uniform(g)
     lp.execute(1, rt.LaunchParams(spp=8, max_bounces=3))
-    d32 = ctx.read(rt.BUF_DIFFUSE_F32, np.float32).reshape(h, w, 4)[:, :, :3].astype(np.float64)
-    r32 = O.OracleScene(sc.desc).render_reference(g, 1, w, h, spp=8, max_bounces=3)[2][:, :, :3].astype(np.float64)
-    rel_mse = np.mean((d32 - r32) ** 2) / np.mean(r32 ** 2)
-    assert rel_mse < 1e-3, rel_mse
-    assert (np.abs(d32 - r32) > 1e-3 * (1 + np.abs(r32))).mean() < 0.01
+    d32 = ctx.read(rt.BUF_DIFFUSE_F32, np.float32).reshape(h, w, 4)
+    r32, rays = O.OracleScene(sc.desc).render_reference(g, 1, w, h, spp=8, max_bounces=3)[2:4]
+    assert ctx.stats().rays_traced == rays
+    nbad = int((d32.view(np.uint32) != r32.view(np.uint32)).any(axis=2).sum())
+    assert nbad <= 2, f"{nbad} pixels differ"
+    assert np.allclose(d32, r32, rtol=1e-5, atol=1e-6)
     ctx.close()
 
 
