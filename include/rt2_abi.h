@@ -133,6 +133,8 @@ typedef struct rt2_packed_di_reservoir {
     float    weight;
 } rt2_packed_di_reservoir;
 
+#define RT2_NEIGHBOR_OFFSET_COUNT 8192u   /* src/main.rs:56 NEIGHBOR_OFFSET_COUNT */
+
 /* src/shaders/rtxdi/ReSTIRGIParameters.h:17-30 `RTXDI_PackedGIReservoir`. 32 bytes. */
 typedef struct rt2_packed_gi_reservoir {
     float    position[3];
@@ -212,7 +214,8 @@ enum rt2_buffer {
     RT2_BUF_MOTION_VECTORS  = 86,  /* rgba32f                                                      */
     RT2_BUF_DI_RESERVOIRS   = 87,  /* rt2_packed_di_reservoir x arrayPitch x 2, block-linear       */
     RT2_BUF_GI_RESERVOIRS   = 88,  /* 32 B x arrayPitch x 2                                        */
-    RT2_BUF_SECONDARY_GBUFFER = 89, /* 48 B x W x H                                                 */
+    RT2_BUF_SECONDARY_GBUFFER = 89, /* rt2_secondary_gbuffer_data (48 B) x arrayPitch, block-linear  */
+    RT2_BUF_NEIGHBOR_OFFSETS = 90,  /* K7 neighbour-offset table: RT2_NEIGHBOR_OFFSET_COUNT signed byte pairs */
     /* acceleration-structure introspection (tests / tools) */
     RT2_BUF_BLAS_NODES = 100,      /* 80-byte CWBVH nodes                                          */
     RT2_BUF_BLAS_TRIS = 101,       /* 48-byte leaf triangles in slot order                         */

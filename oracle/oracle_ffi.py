@@ -64,6 +64,11 @@ def lib():
         L.orc_shade_secondary_surfaces.restype = C.c_int
         L.orc_shade_secondary_surfaces.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int, VP, VP, VP, VP, VP, VP, C.POINTER(u64)]
         L.orc_gi_final_shading.restype = C.c_int; L.orc_gi_final_shading.argtypes = [VP, VP, u32, u32, u32, C.c_int, VP, VP, VP, VP, VP, C.POINTER(u64)]
+        L.orc_gi_temporal_resampling.restype = C.c_int
+        L.orc_gi_temporal_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int, VP, VP, VP, VP, C.POINTER(u64)]
+        L.orc_gi_spatial_resampling.restype = C.c_int
+        L.orc_gi_spatial_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int, VP, VP, u32, VP, C.POINTER(u64)]
+        L.orc_fill_neighbor_offset_buffer.restype = None; L.orc_fill_neighbor_offset_buffer.argtypes = [u32, VP]
         L.orc_encode_logluv.restype = u32; L.orc_encode_logluv.argtypes = [VP]
         L.orc_decode_logluv.restype = None; L.orc_decode_logluv.argtypes = [u32, VP]
         L.orc_encode_snorm_oct.restype = u32; L.orc_encode_snorm_oct.argtypes = [VP]
@@ -98,6 +103,12 @@ class GBufferIn(C.Structure):   # orc_gbuffer_in
 
 class LightIn(C.Structure):     # orc_light_in
     _fields_ = [("lights", VP), ("num_lights", u32), ("geom_to_light", VP), ("pdf_packed", VP), ("pdf_w", u32), ("pdf_h", u32), ("pdf_mips", u32)]
+
+
+def fill_neighbor_offset_buffer(count=8192):
+    out = np.zeros((count, 2), np.int8)
+    lib().orc_fill_neighbor_offset_buffer(count, out.ctypes.data_as(VP))
+    return out
 
 
 class OracleScene:
@@ -235,14 +246,41 @@ class OracleScene:
         assert rc == 0, rc
         return rays.value
 
-    def gi_chain(self, gconst, frame, w, h, gb, array_pitch, light_inputs=None, state=None, flags=0, threads=0):
-        """K4 -> K5 -> K8 on fresh (or carried-over `state`) buffers.  Returns dict(secondary, gi_reservoirs, diffuse, specular, rays)."""
+    def gi_temporal_resampling(self, gconst, frame, w, h, gb, gb_prev, motion, gi_reservoirs, flags=0, threads=0):
+        """K6.  motion: float32 [h, w, 4]; gi_reservoirs in/out."""
+        gin, keep = self._gb_in(gb)
+        gpv, keep2 = self._gb_in(gb_prev)
+        mv = np.ascontiguousarray(motion, np.float32)
+        rays = u64(0)
+        rc = self._L.orc_gi_temporal_resampling(self._p, C.cast(C.byref(gconst), VP), frame, w, h, flags, threads, C.byref(gin), C.byref(gpv),
+                                                mv.ctypes.data_as(VP), gi_reservoirs.ctypes.data_as(VP), C.byref(rays))
+        assert rc == 0, rc
+        return rays.value
+
+    def gi_spatial_resampling(self, gconst, frame, w, h, gb, neighbor_offsets, gi_reservoirs, flags=0, threads=0):
+        """K7.  neighbor_offsets: int8 [count, 2]."""
+        gin, keep = self._gb_in(gb)
+        no = np.ascontiguousarray(neighbor_offsets, np.int8)
+        rays = u64(0)
+        rc = self._L.orc_gi_spatial_resampling(self._p, C.cast(C.byref(gconst), VP), frame, w, h, flags, threads, C.byref(gin),
+                                               no.ctypes.data_as(VP), no.size // 2, gi_reservoirs.ctypes.data_as(VP), C.byref(rays))
+        assert rc == 0, rc
+        return rays.value
+
+    def gi_chain(self, gconst, frame, w, h, gb, array_pitch, light_inputs=None, state=None, flags=0, threads=0, gb_prev=None, motion=None, neighbor_offsets=None):
+        """K4 -> K5 -> [K6] -> [K7] -> K8 on fresh (or carried-over `state`) buffers, as LightPasses::execute orders them
+        (src/light_passes.rs:621-659).  Returns dict(secondary, gi_reservoirs, diffuse, specular, rays)."""
         st = state or {"secondary": np.zeros((array_pitch, 12), np.uint32), "gi_reservoirs": np.zeros((array_pitch * 2, 8), np.uint32),
                        "diffuse": np.zeros((h, w, 4), np.uint16), "specular": np.zeros((h, w, 4), np.uint16)}
         li = light_inputs or {}
         r4 = self.brdf_rays(gconst, frame, w, h, gb, st["secondary"], st["diffuse"], st["specular"], flags, threads)
         r5 = self.shade_secondary_surfaces(gconst, frame, w, h, gb, st["secondary"], st["gi_reservoirs"], st["diffuse"], st["specular"],
                                            li.get("lights"), li.get("geom_to_light"), li.get("pdf_packed"), li.get("pdf_dims", (0, 0, 0)), flags, threads)
+        r6 = r7 = 0
+        if gconst.enable_temporal_resampling == 1:
+            r6 = self.gi_temporal_resampling(gconst, frame, w, h, gb, gb_prev, motion, st["gi_reservoirs"], flags, threads)
+        if gconst.enable_spatial_resampling == 1:
+            r7 = self.gi_spatial_resampling(gconst, frame, w, h, gb, neighbor_offsets, st["gi_reservoirs"], flags, threads)
         r8 = self.gi_final_shading(gconst, w, h, gb, st["secondary"], st["gi_reservoirs"], st["diffuse"], st["specular"], flags, threads)
-        st["rays"] = (r4, r5, r8)
+        st["rays"] = (r4, r5, r6, r7, r8)
         return st

@@ -121,6 +121,19 @@ int orc_shade_secondary_surfaces(const orc_scene* s, const void* gconst, uint32_
 int orc_gi_final_shading(const orc_scene* s, const void* gconst, uint32_t width, uint32_t height, uint32_t flags, int threads,
                          const orc_gbuffer_in* gb, const rt2_secondary_gbuffer_data* secondary, const rt2_packed_gi_reservoir* gi_reservoirs,
                          uint16_t* diffuse_f16, uint16_t* specular_f16, uint64_t* rays);
+/* K6 lighting_passes/temporal_resampling.rgen + rtxdi/GIResamplingFunctions.hlsli:186-359.  gb_prev = last frame's G-buffer
+ * (interpreted through prevView); motion_vectors = rgba32f of K3.  Reads page temporalResamplingInputBufferIndex at
+ * reprojected neighbours, writes page temporalResamplingOutputBufferIndex. */
+int orc_gi_temporal_resampling(const orc_scene* s, const void* gconst, uint32_t frame, uint32_t width, uint32_t height, uint32_t flags, int threads,
+                               const orc_gbuffer_in* gb, const orc_gbuffer_in* gb_prev, const float* motion_vectors,
+                               rt2_packed_gi_reservoir* gi_reservoirs, uint64_t* rays);
+/* K7 lighting_passes/spatial_resampling.rgen + rtxdi/GIResamplingFunctions.hlsli:391-553.  neighbor_offsets: signed byte
+ * pairs (SURVEY Q11 pin), neighbor_offset_count entries. */
+int orc_gi_spatial_resampling(const orc_scene* s, const void* gconst, uint32_t frame, uint32_t width, uint32_t height, uint32_t flags, int threads,
+                              const orc_gbuffer_in* gb, const int8_t* neighbor_offsets, uint32_t neighbor_offset_count,
+                              rt2_packed_gi_reservoir* gi_reservoirs, uint64_t* rays);
+/* fill_neighbor_offset_buffer (src/light_passes.rs:671-698) with signed bytes; xy holds 2 * count bytes */
+void orc_fill_neighbor_offset_buffer(uint32_t neighbor_offset_count, int8_t* xy);
 /* KAT probes: rtxdi/RtxdiMath.hlsli:129-296 */
 uint32_t orc_encode_logluv(const float rgb[3]);
 void orc_decode_logluv(uint32_t packed, float rgb[3]);

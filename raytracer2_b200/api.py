@@ -26,6 +26,7 @@ BUF_LOCAL_PDF_MIP0, BUF_ENV_PDF_MIP0 = 16, 48
 BUF_GBUFFER_DEPTH, BUF_GBUFFER_NORMALS, BUF_GBUFFER_GEO_NORMALS = 80, 81, 82
 BUF_GBUFFER_DIFFUSE_ALBEDO, BUF_GBUFFER_SPECULAR_ROUGH, BUF_GBUFFER_EMISSIVE = 83, 84, 85
 BUF_MOTION_VECTORS, BUF_DI_RESERVOIRS, BUF_GI_RESERVOIRS, BUF_SECONDARY_GBUFFER = 86, 87, 88, 89
+BUF_NEIGHBOR_OFFSETS = 90
 
 BUF_BLAS_NODES, BUF_BLAS_TRIS, BUF_BLAS_SLOT_TO_PRIM, BUF_TLAS_NODES, BUF_TLAS_SLOT_TO_INST = 100, 101, 102, 103, 104
 

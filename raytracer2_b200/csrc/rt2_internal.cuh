@@ -104,7 +104,8 @@ struct FrameBuffers {
     float4* motion_vectors = nullptr;                    // rgba32f
     rt2_packed_di_reservoir* di_reservoirs = nullptr;    // arrayPitch x 2
     uint4* gi_reservoirs = nullptr;                      // 32 B x arrayPitch x 2
-    uint4* secondary_gbuffer = nullptr;                  // 48 B x W x H
+    uint4* secondary_gbuffer = nullptr;                  // 48 B x arrayPitch
+    char2* neighbor_offsets = nullptr;                   // RT2_NEIGHBOR_OFFSET_COUNT signed byte pairs (K7)
     uint32_t reservoir_block_row_pitch = 0, reservoir_array_pitch = 0;
     uint32_t* counters = nullptr;      // [0..1] u64 rays, [2..3] u64 hits, then (count, head) per wavefront iteration
     size_t counter_capacity = 0;

@@ -1,5 +1,6 @@
 // rt2_passes_common.cu — resources shared by the light / G-buffer / reservoir / post passes and their
 // read-out through rt2_read (RenderResources, src/render_resources.rs:130-341).
+#include <vector>
 #include "rt2_internal.cuh"
 
 namespace rt2 {
@@ -14,9 +15,9 @@ void passes_release_frame(rt2_ctx* ctx) {
         for (void* p : ptrs) if (p) cudaFree(p);
         f.gb_depth[i] = nullptr; f.gb_normals[i] = f.gb_geo_normals[i] = f.gb_diffuse_albedo[i] = f.gb_specular_rough[i] = nullptr; f.gb_emissive[i] = nullptr;
     }
-    void* ptrs[] = {f.motion_vectors, f.di_reservoirs, f.gi_reservoirs, f.secondary_gbuffer};
+    void* ptrs[] = {f.motion_vectors, f.di_reservoirs, f.gi_reservoirs, f.secondary_gbuffer, f.neighbor_offsets};
     for (void* p : ptrs) if (p) cudaFree(p);
-    f.motion_vectors = nullptr; f.di_reservoirs = nullptr; f.gi_reservoirs = nullptr; f.secondary_gbuffer = nullptr;
+    f.motion_vectors = nullptr; f.di_reservoirs = nullptr; f.gi_reservoirs = nullptr; f.secondary_gbuffer = nullptr; f.neighbor_offsets = nullptr;
     f.reservoir_block_row_pitch = f.reservoir_array_pitch = 0;
 }
 
@@ -45,6 +46,24 @@ int restir_ensure_resources(rt2_ctx* ctx) {
     f.reservoir_block_row_pitch = wb * 256u; f.reservoir_array_pitch = f.reservoir_block_row_pitch * hb;
     RT2_CUDA(ctx, zalloc(ctx, &f.di_reservoirs, (size_t)f.reservoir_array_pitch * 2));    // src/render_resources.rs:191-198
     RT2_CUDA(ctx, zalloc(ctx, &f.gi_reservoirs, (size_t)f.reservoir_array_pitch * 2 * 2)); // 32 B each, :199-206
+    {   // fill_neighbor_offset_buffer, src/light_passes.rs:671-698 (f32 arithmetic).  The reference stores `as u8` bytes and reads them as
+        // vec2; pinned to the RTXDI SDK's intent: signed bytes, decoded as SNORM8 by K7.
+        std::vector<signed char> tab; tab.reserve(RT2_NEIGHBOR_OFFSET_COUNT * 2);
+        const float phi2 = 1.0f / 1.3247179572447f;
+        float u = 0.5f, v = 0.5f;
+        while (tab.size() < (size_t)RT2_NEIGHBOR_OFFSET_COUNT * 2) {
+            u += phi2; v += phi2 * phi2;
+            if (u >= 1.0f) u -= 1.0f;
+            if (v >= 1.0f) v -= 1.0f;
+            const float r_sq = (u - 0.5f) * (u - 0.5f) + (v - 0.5f) * (v - 0.5f);
+            if (r_sq > 0.25f) continue;
+            tab.push_back((signed char)((u - 0.5f) * 250.0f));
+            tab.push_back((signed char)((v - 0.5f) * 250.0f));
+        }
+        RT2_CUDA(ctx, cudaMalloc((void**)&f.neighbor_offsets, tab.size())); ctx->device_bytes += tab.size();
+        RT2_CUDA(ctx, cudaMemcpyAsync(f.neighbor_offsets, tab.data(), tab.size(), cudaMemcpyHostToDevice, ctx->stream));
+        RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // `tab` is pageable host memory going out of scope
+    }
     RT2_CUDA(ctx, zalloc(ctx, &f.secondary_gbuffer, (size_t)f.reservoir_array_pitch * 3)); // 48 B x arrayPitch (block-linear addressing), :309-317
     return RT2_OK;
 }
@@ -77,6 +96,7 @@ bool pass_buffer(rt2_ctx* ctx, int which, void** ptr, size_t* bytes) {
         case RT2_BUF_MOTION_VECTORS: *ptr = f.motion_vectors; *bytes = n * 16; return f.motion_vectors != nullptr;
         case RT2_BUF_DI_RESERVOIRS: *ptr = f.di_reservoirs; *bytes = (size_t)f.reservoir_array_pitch * 2 * sizeof(rt2_packed_di_reservoir); return f.di_reservoirs != nullptr;
         case RT2_BUF_GI_RESERVOIRS: *ptr = f.gi_reservoirs; *bytes = (size_t)f.reservoir_array_pitch * 2 * 32; return f.gi_reservoirs != nullptr;
+        case RT2_BUF_NEIGHBOR_OFFSETS: *ptr = f.neighbor_offsets; *bytes = (size_t)RT2_NEIGHBOR_OFFSET_COUNT * 2; return f.neighbor_offsets != nullptr;
         case RT2_BUF_SECONDARY_GBUFFER: *ptr = f.secondary_gbuffer; *bytes = (size_t)f.reservoir_array_pitch * 48; return f.secondary_gbuffer != nullptr;
         default: return false;
     }

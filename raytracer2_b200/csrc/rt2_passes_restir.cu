@@ -503,14 +503,202 @@ __global__ void __launch_bounds__(128) k_gi_final_shading(GIArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// N2 — GI temporal (K6) and spatial (K7) resampling: lighting_passes/temporal_resampling.rgen,
+// spatial_resampling.rgen, rtxdi/GIResamplingFunctions.hlsli:186-553.  The first kernels with cross-pixel reads:
+// neighbours come from last frame's G-buffer / reservoir page (K6) or from this frame's (K7); the page a kernel
+// writes is never the page it gathers from (checked on the host), so stream order is the only dependency.
+// ------------------------------------------------------------------------------------------------
+struct GIResampleArgs {
+    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame;
+    GBufferRefs gb, gb_prev;
+    const float4* motion;
+    const char2* neighbor_offsets;     // signed byte pairs, SNORM8 (SURVEY Q11 pin)
+    uint4* reservoirs;
+    unsigned long long* stat_rays; unsigned long long* stat_hits;
+};
+
+__global__ void __launch_bounds__(128) k_gi_temporal(GIResampleArgs a) {
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const rt2_gconst& g = *a.g;
+    const rt2_restirgi_params& gi = g.restir_gi;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    uint32_t rays = 0, hits = 0;
+    Rng rng = rng_init(lx, ly, a.frame, 7u);
+    const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+    const uint32_t field = g.runtime_params.active_checkerboard_field;
+    const uint32_t rx = field != 0u ? (px >> 1) : px;
+    const uint32_t row_pitch = gi.reservoir_buffer_params.reservoir_block_row_pitch, array_pitch = gi.reservoir_buffer_params.reservoir_array_pitch;
+    GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, gi.buffer_indices.secondary_surface_restirdi_output_buffer_index));
+    V3 motion = v3(0.f, 0.f, 0.f);
+    if (px < a.width && py < a.height) { const float4 m = a.motion[(size_t)py * a.width + px]; motion = v3(m.x, m.y, m.z); }
+    {   // convertMotionVectorToPixelSpace, GBufferHelpers.glsl:69-80
+        const float cx = (float)(int)px + 0.5f, cy = (float)(int)py + 0.5f;
+        float ppx = cx + motion.x, ppy = cy + motion.y;
+        ppx *= g.prev_view.viewport_size[0] * g.view.viewport_size_inv[0];
+        ppy *= g.prev_view.viewport_size[1] * g.view.viewport_size_inv[1];
+        motion.x = ppx - cx; motion.y = ppy - cy;
+    }
+    if (surface.view_depth != RT2_BACKGROUND_DEPTH) {
+        const rt2_restirgi_temporal_params& tp = gi.temporal_resampling_params;
+        const float age_scale = (float)tp.max_reservoir_age * (0.5f + rng_next(rng) * 0.5f);
+        const uint32_t max_reservoir_age = isnan(age_scale) ? 0u : (uint32_t)age_scale;
+        const GIReservoir input = reservoir;
+        int prev_x = (int)rintf((float)px + motion.x), prev_y = (int)rintf((float)py + motion.y);
+        const float expected_prev_depth = surface.view_depth + motion.z;
+        const int radius = (field == 0u) ? 1 : 2;
+        GIReservoir temporal = empty_gi_reservoir();
+        bool found = false;
+        const int start_idx = (int)(rng_next(rng) * 8);
+        Surface temporal_surface = empty_surface();
+        const int temporal_sample_count = 5;
+        const int sample_count = temporal_sample_count + (tp.enable_fallback_sampling == 1u ? 1 : 0);
+        for (int i = 0; i < sample_count; i++) {
+            const bool is_first = i == 0, is_fallback = i == temporal_sample_count;
+            int ox = 0, oy = 0;
+            if (is_fallback) { prev_x = (int)px; prev_y = (int)py; }
+            else if (!is_first) temporal_resampling_offset(start_idx + i, radius, &ox, &oy);
+            int ix = prev_x + ox, iy = prev_y + oy;
+            if ((tp.enable_permutation_sampling == 1u && is_first) || is_fallback) apply_permutation_sampling(&ix, &iy, tp.uniform_random_number);
+            activate_checkerboard_pixel(&ix, &iy, true, field);
+            temporal_surface = gbuffer_surface(a.gb_prev, a.width, ix, iy, g.prev_view);
+            if (temporal_surface.view_depth == RT2_BACKGROUND_DEPTH) continue;
+            if (!is_fallback && !is_valid_neighbor(surface.normal, temporal_surface.normal, expected_prev_depth, temporal_surface.view_depth, tp.normal_threshold, tp.depth_threshold)) continue;
+            if (!materials_similar(surface, temporal_surface)) continue;
+            const uint32_t prx = field != 0u ? ((uint32_t)ix >> 1) : (uint32_t)ix;
+            temporal = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, prx, (uint32_t)iy, gi.buffer_indices.temporal_resampling_input_buffer_index));
+            if (temporal.M == 0u) continue;
+            found = true;
+            break;
+        }
+        GIReservoir cur = empty_gi_reservoir();
+        float selected_target_pdf = 0;
+        if (input.M != 0u) {
+            selected_target_pdf = gi_target_pdf(input.position, input.radiance, surface);
+            gi_combine(cur, input, 0.5f, selected_target_pdf);
+        }
+        if (found) {
+            float jacobian = gi_jacobian(surface.world_pos, temporal_surface.world_pos, temporal);
+            if (!validate_gi_jacobian(jacobian)) found = false;
+            temporal.weight_sum *= jacobian;
+            temporal.M = min(temporal.M, tp.max_history_length);
+            ++temporal.age;
+            if (temporal.age > max_reservoir_age) found = false;
+        }
+        bool selected_previous = false;
+        if (found) {
+            const float target_pdf = gi_target_pdf(temporal.position, temporal.radiance, surface);
+            selected_previous = gi_combine(cur, temporal, rng_next(rng), target_pdf);
+            if (selected_previous) selected_target_pdf = target_pdf;
+        }
+        if (tp.temporal_bias_correction_mode >= 1u) {                  // RTXDI_BIAS_CORRECTION_BASIC
+            float pi = selected_target_pdf;
+            float pi_sum = selected_target_pdf * (float)input.M;
+            if (cur.M != 0u && found) {
+                float temporal_p = gi_target_pdf(cur.position, cur.radiance, temporal_surface);
+                if (tp.temporal_bias_correction_mode == 3u && temporal_p > 0) {        // RAY_TRACED: bridge :708-711, current BVH
+                    if (!visibility_ray_miss(a.sc, temporal_surface, cur.position, 0.001f, &rays)) { hits++; temporal_p = 0; }
+                }
+                pi = selected_previous ? temporal_p : pi;
+                pi_sum += temporal_p * (float)temporal.M;
+            }
+            gi_finalize(cur, pi, pi_sum * selected_target_pdf);
+        } else {
+            gi_finalize(cur, 1.0f, selected_target_pdf * (float)cur.M);
+        }
+        reservoir = cur;
+    }
+    store_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, gi.buffer_indices.temporal_resampling_output_buffer_index), reservoir, 0u);
+    flush_ray_stats(a.stat_rays, a.stat_hits, rays, hits);
+}
+
+__device__ __forceinline__ void spatial_offset(const char2* table, int sample_idx, float radius, uint32_t mask, int* ox, int* oy) {   // :132-136
+    sample_idx &= (int)mask;
+    const char2 b = table[sample_idx];
+    const float fx = fmaxf((float)b.x / 127.0f, -1.0f), fy = fmaxf((float)b.y / 127.0f, -1.0f);
+    *ox = (int)(fx * radius); *oy = (int)(fy * radius);
+}
+
+__global__ void __launch_bounds__(128) k_gi_spatial(GIResampleArgs a) {
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const rt2_gconst& g = *a.g;
+    const rt2_restirgi_params& gi = g.restir_gi;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    uint32_t rays = 0, hits = 0;
+    Rng rng = rng_init(lx, ly, a.frame, 8u);
+    const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+    const uint32_t field = g.runtime_params.active_checkerboard_field, mask = g.runtime_params.neighbor_offset_mask;
+    const uint32_t rx = field != 0u ? (px >> 1) : px;
+    const uint32_t row_pitch = gi.reservoir_buffer_params.reservoir_block_row_pitch, array_pitch = gi.reservoir_buffer_params.reservoir_array_pitch;
+    const uint32_t src = gi.buffer_indices.spatial_resampling_input_buffer_index;
+    GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, src));
+    if (surface.view_depth != RT2_BACKGROUND_DEPTH) {
+        const rt2_restirgi_spatial_params& sp = gi.spatial_resampling_params;
+        const int num_samples = (int)sp.num_spatial_samples;
+        const GIReservoir input = reservoir;
+        GIReservoir cur = empty_gi_reservoir();
+        float selected_target_pdf = 0;
+        if (input.M != 0u) {
+            selected_target_pdf = gi_target_pdf(input.position, input.radiance, surface);
+            gi_combine(cur, input, 0.5f, selected_target_pdf);
+        }
+        uint32_t cached = 0;
+        int selected = -1;
+        const int start_idx = (int)(rng_next(rng) * (float)mask);
+        for (int i = 0; i < num_samples; ++i) {
+            int ox, oy; spatial_offset(a.neighbor_offsets, start_idx + i, sp.spatial_sampling_radius, mask, &ox, &oy);
+            int ix = (int)px + ox, iy = (int)py + oy;
+            clamp_sample_position_into_view(g, &ix, &iy);
+            activate_checkerboard_pixel(&ix, &iy, false, field);
+            const Surface ns = gbuffer_surface(a.gb, a.width, ix, iy, g.view);
+            if (!is_valid_neighbor(surface.normal, ns.normal, surface.view_depth, ns.view_depth, sp.spatial_normal_threshold, sp.spatial_depth_threshold)) continue;
+            if (!materials_similar(surface, ns)) continue;
+            const uint32_t nrx = field != 0u ? ((uint32_t)ix >> 1) : (uint32_t)ix;
+            const GIReservoir nr = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, nrx, (uint32_t)iy, src));
+            if (nr.M == 0u) continue;
+            float jacobian = gi_jacobian(surface.world_pos, ns.world_pos, nr);
+            const float target_pdf = gi_target_pdf(nr.position, nr.radiance, surface);
+            if (!validate_gi_jacobian(jacobian)) continue;
+            cached |= (1u << (uint32_t)i);
+            if (gi_combine(cur, nr, rng_next(rng), target_pdf * jacobian)) { selected = i; selected_target_pdf = target_pdf; }
+        }
+        if (sp.spatial_bias_correction_mode >= 1u) {
+            float pi = selected_target_pdf;
+            float pi_sum = selected_target_pdf * (float)input.M;
+            for (int i = 0; i < num_samples; ++i) {
+                if ((cached & (1u << (uint32_t)i)) == 0u) continue;
+                int ox, oy; spatial_offset(a.neighbor_offsets, start_idx + i, sp.spatial_sampling_radius, mask, &ox, &oy);
+                int ix = (int)px + ox, iy = (int)py + oy;
+                clamp_sample_position_into_view(g, &ix, &iy);
+                activate_checkerboard_pixel(&ix, &iy, false, field);
+                const Surface ns = gbuffer_surface(a.gb, a.width, ix, iy, g.view);
+                const uint32_t nrx = field != 0u ? ((uint32_t)ix >> 1) : (uint32_t)ix;
+                const uint4 head = a.reservoirs[2 * (size_t)reservoir_pointer(row_pitch, array_pitch, nrx, (uint32_t)iy, src)];   // only M is needed again
+                float ps = gi_target_pdf(cur.position, cur.radiance, ns);
+                if (sp.spatial_bias_correction_mode == 3u && ps > 0) {
+                    if (!visibility_ray_miss(a.sc, ns, cur.position, 0.001f, &rays)) { hits++; ps = 0; }
+                }
+                pi = selected == i ? ps : pi;
+                pi_sum += ps * (float)(head.w & 0xffu);
+            }
+            gi_finalize(cur, pi, selected_target_pdf * pi_sum);
+        } else {
+            gi_finalize(cur, 1.0f, (float)cur.M * selected_target_pdf);
+        }
+        reservoir = cur;
+    }
+    store_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, gi.buffer_indices.spatial_resampling_output_buffer_index), reservoir, 0u);
+    flush_ray_stats(a.stat_rays, a.stat_hits, rays, hits);
+}
+
+// ------------------------------------------------------------------------------------------------
 // host: LightPasses::execute, non-reference branch (src/light_passes.rs:598-659)
 // ------------------------------------------------------------------------------------------------
 int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     if (!ctx->scene.accel_built) return fail(ctx, RT2_E_STATE, "no acceleration structure: call rt2_upload_scene + rt2_build_accel first");
     if (lp.band_world > 1u) return fail(ctx, RT2_E_INVALID, "row-band sharding is implemented for the reference path tracer only");
     const rt2_gconst& g = ctx->gconst;
-    if (g.enable_restir_gi == 1u && (g.enable_temporal_resampling == 1u || g.enable_spatial_resampling == 1u))
-        return fail(ctx, RT2_E_STATE, "GI temporal / spatial resampling (K6 / K7) is not built: clear enable_temporal_resampling and enable_spatial_resampling");
     int rc = restir_ensure_resources(ctx); if (rc) return rc;
     FrameBuffers& f = ctx->fb;
     // counters: [0..1] rays, [2..3] hits
@@ -557,6 +745,19 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
             return fail(ctx, RT2_E_INVALID, "GConst reservoir buffer parameters do not match the frame size (calculate_reservoir_buffer_parameters)");
         if (g.restir_gi.buffer_indices.secondary_surface_restirdi_output_buffer_index > 1u) return fail(ctx, RT2_E_INVALID, "GI reservoir buffer index out of range");
         if (g.runtime_params.active_checkerboard_field > 2u) return fail(ctx, RT2_E_INVALID, "active_checkerboard_field must be 0, 1 or 2");
+        const rt2_restirgi_buffer_indices& bi = g.restir_gi.buffer_indices;
+        if (g.enable_temporal_resampling == 1u) {
+            if (bi.temporal_resampling_input_buffer_index > 1u || bi.temporal_resampling_output_buffer_index > 1u) return fail(ctx, RT2_E_INVALID, "GI reservoir buffer index out of range");
+            if (bi.temporal_resampling_input_buffer_index == bi.temporal_resampling_output_buffer_index)
+                return fail(ctx, RT2_E_INVALID, "temporal resampling would gather from the reservoir page it writes (a data race in the reference too)");
+        }
+        if (g.enable_spatial_resampling == 1u) {
+            if (bi.spatial_resampling_input_buffer_index > 1u || bi.spatial_resampling_output_buffer_index > 1u) return fail(ctx, RT2_E_INVALID, "GI reservoir buffer index out of range");
+            if (bi.spatial_resampling_input_buffer_index == bi.spatial_resampling_output_buffer_index)
+                return fail(ctx, RT2_E_INVALID, "spatial resampling would gather from the reservoir page it writes (a data race in the reference too)");
+            if (g.runtime_params.neighbor_offset_mask >= RT2_NEIGHBOR_OFFSET_COUNT) return fail(ctx, RT2_E_INVALID, "neighbor_offset_mask exceeds the neighbour-offset table (8192 entries, src/main.rs:56)");
+            if (g.restir_gi.spatial_resampling_params.num_spatial_samples > 32u) return fail(ctx, RT2_E_INVALID, "num_spatial_samples must be <= 32 (bit mask of accepted neighbours)");
+        }
     }
     // ---- K3
     GBufferArgs ga{};
@@ -585,6 +786,18 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         gi.stat_rays = stat_rays; gi.stat_hits = stat_hits;
         k_brdf_rays<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
         k_shade_secondary<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+        if (g.enable_temporal_resampling == 1u || g.enable_spatial_resampling == 1u) {
+            const uint32_t prev = cur ^ 1u;
+            GIResampleArgs ra{};
+            ra.sc = ga.sc; ra.g = ctx->d_gconst; ra.width = f.width; ra.height = f.height; ra.frame = frame;
+            ra.gb = gbrefs;
+            ra.gb_prev = GBufferRefs{f.gb_depth[prev], f.gb_normals[prev], f.gb_geo_normals[prev], f.gb_diffuse_albedo[prev], f.gb_specular_rough[prev]};
+            ra.motion = f.motion_vectors; ra.neighbor_offsets = f.neighbor_offsets; ra.reservoirs = f.gi_reservoirs;
+            ra.stat_rays = stat_rays; ra.stat_hits = stat_hits;
+            // the reference records K6 and K7 without a barrier between them (src/light_passes.rs:642-647); stream order = K6 then K7
+            if (g.enable_temporal_resampling == 1u) { k_gi_temporal<<<blocks, 128, 0, ctx->stream>>>(ra); launches++; }
+            if (g.enable_spatial_resampling == 1u) { k_gi_spatial<<<blocks, 128, 0, ctx->stream>>>(ra); launches++; }
+        }
         k_gi_final_shading<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
     }
     RT2_CUDA(ctx, cudaGetLastError());

@@ -25,6 +25,7 @@ struct GBufferRefs { const float* depth; const uint32_t* normals; const uint32_t
 __device__ __forceinline__ Surface gbuffer_surface(const GBufferRefs& gb, uint32_t width, int px, int py, const rt2_planar_view_constants& view) {
     Surface s = empty_surface();
     if ((float)px >= view.viewport_size[0] || (float)py >= view.viewport_size[1]) return s;
+    if (px < 0 || py < 0) return s;      // imageLoad outside the image: pinned to "invalid surface" (oracle pin, K6/K7 neighbours)
     const size_t i = (size_t)py * width + (size_t)px;
     s.view_depth = gb.depth[i];
     if (s.view_depth == RT2_BACKGROUND_DEPTH) return s;
@@ -333,6 +334,80 @@ __device__ __forceinline__ GIReservoir load_gi_reservoir(const uint4* buf, uint3
     r.weight_sum = __uint_as_float(b.y);
     r.M = a.w & 0xffu; r.age = (a.w >> 8) & 0xffu;
     return r;
+}
+
+// ---- GI resampling: rtxdi/GIResamplingFunctions.hlsli:25-136, RtxdiMath.hlsli:18-29,120-123, bridge :252-265,600-616,673-694
+__device__ __forceinline__ float rtxdi_luminance(V3 rgb) { return dot3(rgb, v3(0.2126f, 0.7152f, 0.0722f)); }
+__device__ __forceinline__ bool compare_relative_difference(float reference, float candidate, float threshold) {
+    return (threshold <= 0) || fabsf(reference - candidate) <= threshold * fmaxf(reference, candidate);
+}
+__device__ __forceinline__ bool is_valid_neighbor(V3 our_norm, V3 their_norm, float our_depth, float their_depth, float normal_threshold, float depth_threshold) {
+    return (dot3(their_norm, our_norm) >= normal_threshold) && compare_relative_difference(our_depth, their_depth, depth_threshold);
+}
+__device__ __forceinline__ bool materials_similar(const Surface& a, const Surface& b) {
+    if (!compare_relative_difference(a.roughness, b.roughness, 0.5f)) return false;
+    if (fabsf(calc_luminance(a.specular_f0) - calc_luminance(b.specular_f0)) > 0.25f) return false;
+    if (fabsf(calc_luminance(a.diffuse_albedo) - calc_luminance(b.diffuse_albedo)) > 0.25f) return false;
+    return true;
+}
+__device__ __forceinline__ bool validate_gi_jacobian(float& jacobian) {
+    if (jacobian > 10.0f || jacobian < 1 / 10.0f) return false;
+    jacobian = clampf(jacobian, 1 / 3.0f, 3.0f);
+    return true;
+}
+__device__ __forceinline__ float gi_target_pdf(V3 sample_position, V3 sample_radiance, const Surface& s) {
+    const SplitBrdf brdf = evaluate_brdf(s, sample_position);
+    return rtxdi_luminance(sample_radiance * (s.diffuse_albedo * brdf.demodulated_diffuse + brdf.specular));
+}
+__device__ __forceinline__ bool gi_combine(GIReservoir& r, const GIReservoir& n, float random, float target_pdf) {
+    const float ris_weight = target_pdf * n.weight_sum * (float)n.M;
+    r.M += n.M;
+    r.weight_sum += ris_weight;
+    const bool select = (random * r.weight_sum <= ris_weight);
+    if (select) { r.position = n.position; r.normal = n.normal; r.radiance = n.radiance; r.age = n.age; }
+    return select;
+}
+__device__ __forceinline__ void gi_finalize(GIReservoir& r, float num, float den) {
+    r.weight_sum = (den == 0.0f) ? 0.0f : (r.weight_sum * num) / den;
+}
+__device__ __forceinline__ void gi_partial_jacobian(V3 receiver_pos, V3 sample_pos, V3 sample_normal, float* distance, float* cosine) {
+    const V3 vec = receiver_pos - sample_pos;
+    *distance = length3(vec);
+    *cosine = saturatef(dot3(sample_normal, vec / *distance));
+}
+__device__ __forceinline__ float gi_jacobian(V3 receiver_pos, V3 neighbor_receiver_pos, const GIReservoir& n) {
+    float od, oc, nd, nc;
+    gi_partial_jacobian(receiver_pos, n.position, n.normal, &nd, &nc);
+    gi_partial_jacobian(neighbor_receiver_pos, n.position, n.normal, &od, &oc);
+    float j = (nc * od * od) / (oc * nd * nd);
+    if (isinf(j) || isnan(j)) j = 0;
+    return j;
+}
+__device__ __forceinline__ void temporal_resampling_offset(int sample_idx, int radius, int* ox, int* oy) {
+    sample_idx &= 7;
+    const int mask2 = sample_idx >> 1 & 0x01, mask4 = 1 - (sample_idx >> 2 & 0x01);
+    const int tmp0 = -1 + 2 * (sample_idx & 0x01), tmp1 = 1 - 2 * mask2, tmp2 = mask4 | mask2, tmp3 = mask4 | (1 - mask2);
+    *ox = tmp0 * tmp2 * radius; *oy = tmp0 * tmp1 * tmp3 * radius;
+}
+__device__ __forceinline__ void apply_permutation_sampling(int* x, int* y, uint32_t uniform_random_number) {       // RtxdiHelpers.hlsli:63-73
+    const int ox = (int)(uniform_random_number & 3u), oy = (int)((uniform_random_number >> 2) & 3u);
+    *x += ox; *y += oy; *x ^= 3; *y ^= 3; *x -= ox; *y -= oy;
+}
+__device__ __forceinline__ void activate_checkerboard_pixel(int* x, int* y, bool previous_frame, uint32_t field) {  // RtxdiHelpers.hlsli:16-43
+    if (field == 0u) return;
+    uint32_t ux = (uint32_t)*x;
+    const uint32_t uy = (uint32_t)*y;
+    if (((ux + uy + (previous_frame ? 1u : 0u)) & 1u) == (field & 1u)) return;
+    if (previous_frame) ux += (uint32_t)((int)field * 2 - 3);
+    else ux += (uy & 1u) != 0u ? 1u : 0xFFFFFFFFu;
+    *x = (int)ux;
+}
+__device__ __forceinline__ void clamp_sample_position_into_view(const rt2_gconst& g, int* x, int* y) {
+    const int width = (int)g.view.viewport_size[0], height = (int)g.view.viewport_size[1];
+    if (*x < 0) *x = -*x;
+    if (*y < 0) *y = -*y;
+    if (*x >= width) *x = 2 * width - *x - 1;
+    if (*y >= height) *y = 2 * height - *y - 1;
 }
 
 }  // namespace rt2

@@ -124,9 +124,75 @@ def test_gi_default_frame_traces_three_rays_per_pixel_at_most():
     assert rays == rrays and n < rays <= n + hit           # K5 traces every launch index, K4 only valid surfaces
 
 
-def test_gi_rejects_unbuilt_resampling_passes():
+# ---- N2: K6 temporal + K7 spatial resampling --------------------------------------------------------------------
+def _run_resampling(kind, scale, w, h, nframes, temporal=1, spatial=1, move=True, bias=2, nspatial=1, permutation=0, oflags=O.ORC_BRUTE_FORCE, final_vis=0):
+    sc = rt.Scene(kind, scale, 64, 0)
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    cam = sc.camera(w / h)
+    g = rt.default_gconst(cam, w, h, sc.num_lights)
+    g.refrence_mode = 0; g.enable_restir_gi = 1; g.enable_restir_di = 0
+    g.enable_temporal_resampling = temporal; g.enable_spatial_resampling = spatial
+    g.restir_gi.temporal_resampling_params.temporal_bias_correction_mode = bias
+    g.restir_gi.temporal_resampling_params.enable_permutation_sampling = permutation
+    g.restir_gi.spatial_resampling_params.spatial_bias_correction_mode = bias
+    g.restir_gi.spatial_resampling_params.num_spatial_samples = nspatial
+    g.restir_gi.final_shading_params.enable_final_visibility = final_vis
+    lp = rt.LightPasses(ctx, w, h)
+    osc = O.OracleScene(sc.desc)
+    pitch = g.restir_gi.reservoir_buffer_params.reservoir_array_pitch
+    offsets = O.fill_neighbor_offset_buffer(8192)
+    state = None
+    gb_prev = {k: np.zeros((h, w), dt) for k, b, dt, n in GB_KEYS}          # the product zero-fills both G-buffer sets at allocation
+    results = []
+    for frame in range(1, nframes + 1):
+        if move:
+            cam.position[0] += 0.02; cam.position[1] += 0.01                 # a slow dolly: sub-pixel to few-pixel motion vectors
+        rt.advance_frame(g, cam, w, h, frame)
+        lp.update_uniform(g)
+        lp.execute(frame)
+        gb = _read_gb(ctx, w, h)
+        motion = ctx.read(rt.BUF_MOTION_VECTORS, np.float32).reshape(h, w, 4)
+        got = {"secondary": ctx.read(rt.BUF_SECONDARY_GBUFFER, np.uint32).reshape(-1, 12), "gi_reservoirs": ctx.read(rt.BUF_GI_RESERVOIRS, np.uint32).reshape(-1, 8),
+               "diffuse": ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).reshape(h, w, 4), "specular": ctx.read(rt.BUF_SPECULAR_F16, np.uint16).reshape(h, w, 4)}
+        rays = ctx.stats().rays_traced - w * h
+        state = osc.gi_chain(g, frame, w, h, gb, pitch, state=state, flags=oflags, gb_prev=gb_prev, motion=motion, neighbor_offsets=offsets)
+        results.append((got, {k: v.copy() for k, v in state.items() if k != "rays"}, rays, sum(state["rays"]), motion))
+        # keep the oracle on the product's trajectory: a last-bit difference must not snowball through the history
+        for k in ("secondary", "gi_reservoirs", "diffuse", "specular"):
+            state[k] = got[k].copy()
+        gb_prev = gb
+    tab = ctx.read(rt.BUF_NEIGHBOR_OFFSETS, np.int8).reshape(-1, 2)
+    ctx.close()
+    return results, tab, offsets
+
+
+@pytest.mark.parametrize("kind,scale,w,h,kw", [
+    (rt.SCENE_CORNELL, 1.0, 256, 256, dict()),                                          # reference defaults with both passes on
+    (rt.SCENE_CORNELL, 1.0, 200, 120, dict(bias=3, nspatial=3, permutation=1, final_vis=1)),   # ray-traced bias correction: visibility rays in K6/K7
+    (rt.SCENE_CORNELL, 1.0, 160, 96, dict(bias=0, nspatial=4)),                         # 1/M normalisation
+    (rt.SCENE_HALL, 0.125, 320, 180, dict(nspatial=2, oflags=0)),
+    (rt.SCENE_CORNELL, 1.0, 160, 96, dict(spatial=0)),                                  # temporal alone: page 1 is never written, no history (src/main.rs:241-247)
+    (rt.SCENE_CORNELL, 1.0, 160, 96, dict(temporal=0, nspatial=3, move=False)),
+])
+def test_gi_resampling_bit_exact_over_frames(kind, scale, w, h, kw):
+    results, tab, offsets = _run_resampling(kind, scale, w, h, 4, **kw)
+    assert np.array_equal(tab, offsets)                                                 # neighbour-offset table (Q11 pin)
+    tol = max(2, w * h // 50000)
+    for (got, ref, rays, rrays, motion) in results:
+        _check(got, ref, w, h, tol)
+        assert abs(rays - rrays) <= tol                                                 # a pixel that differs may also trace differently
+    if kw.get("move", True):
+        assert np.abs(results[-1][4][:, :, :2]).max() > 0.05                           # the camera really moved
+    if kw.get("temporal", 1) and kw.get("spatial", 1):
+        M = results[-1][0]["gi_reservoirs"][:, 3] & 0xff
+        assert M.max() > 2                                                              # history was found and merged
+
+
+def test_gi_resampling_rejects_aliased_pages():
     sc, ctx, g, lp = _ctx(rt.SCENE_CORNELL, 1.0, 64, 64)
-    g.enable_restir_gi = 1; g.enable_temporal_resampling = 1
+    g.enable_restir_gi = 1; g.enable_spatial_resampling = 1
+    g.restir_gi.buffer_indices.spatial_resampling_output_buffer_index = g.restir_gi.buffer_indices.spatial_resampling_input_buffer_index
     lp.update_uniform(g)
     with pytest.raises(rt.Rt2Error):
         lp.execute(1)

@@ -250,7 +250,7 @@ def test_gi_default_frame_agrees_with_brute_force_path_tracer():
     assert g.enable_restir_gi == 1 and g.enable_restir_di == 0 and g.enable_brdf_indirect == 1     # src/main.rs:388-399
     d, s, st = _gi_frames(osc, g, w, h, gb, 96)
     hit = gb["depth"] != 100000.0
-    r4, r5, r8 = st["rays"]
+    r4, r5, r6, r7, r8 = st["rays"]
     assert 0 < r4 <= hit.sum() and r5 == w * h and r8 == 0               # K4 skips background + below-horizon; K5 traces every index; no final visibility
     gi = d * _albedo(gb, w, h)
     g.refrence_mode = 1
