@@ -214,7 +214,7 @@ enum rt2_buffer {
     RT2_BUF_MOTION_VECTORS  = 86,  /* rgba32f                                                      */
     RT2_BUF_DI_RESERVOIRS   = 87,  /* rt2_packed_di_reservoir x arrayPitch x 2, block-linear       */
     RT2_BUF_GI_RESERVOIRS   = 88,  /* 32 B x arrayPitch x 2                                        */
-    RT2_BUF_SECONDARY_GBUFFER = 89, /* rt2_secondary_gbuffer_data (48 B) x arrayPitch, block-linear  */
+    RT2_BUF_SECONDARY_GBUFFER = 89, /* 48-byte rt2_secondary_gbuffer_data x arrayPitch, block-linear */
     RT2_BUF_NEIGHBOR_OFFSETS = 90,  /* K7 neighbour-offset table: RT2_NEIGHBOR_OFFSET_COUNT signed byte pairs */
     /* acceleration-structure introspection (tests / tools) */
     RT2_BUF_BLAS_NODES = 100,      /* 80-byte CWBVH nodes                                          */
