@@ -42,6 +42,18 @@ def measured_peak_hbm():
         return 6650.0, "fallback"
 
 
+def ncu_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum per k_trace launch from the committed ncu --set full capture
+    (profiles/*_summary.json, same workload, N=1); None when no capture is committed."""
+    import glob
+    for p in sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r*_summary.json")), reverse=True):
+        try:
+            return json.load(open(p))["traffic_bytes_per_launch"]
+        except Exception:
+            continue
+    return None
+
+
 class ClockSampler:
     """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
 
@@ -263,7 +275,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 1424, "d2h_bytes_per_step": W * H * 8, "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None,
+                         "frac": achieved / peak, "traffic": ncu_traffic_bytes(),
                          "algorithmic_bytes_per_ray": B_TRAVERSE, "rays_per_launch": rays_per_launch, "avg_launch_ms": trace_ms / trace_launches,
                          "trace_share_of_step": trace_ms / (trace_ms + shade_ms) if trace_ms + shade_ms > 0 else None,
                          "whole_step": {"bytes_per_ray": B_RAY, "achieved": value * 1e6 / n_gpus * B_RAY / 1e9, "frac": value * 1e6 / n_gpus * B_RAY / 1e9 / peak}},
