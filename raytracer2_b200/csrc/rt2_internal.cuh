@@ -127,7 +127,7 @@ struct rt2_ctx {
     rt2_stats stats{};
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
-    int trace_blocks_per_sm[2] = {1, 1};
+    int trace_blocks_per_sm[3] = {1, 1, 1};             // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level
     int trace_variant = 0;
     std::vector<cudaEvent_t> prof_events;   // RT2_LAUNCH_PROFILE: 3 per wavefront iteration (before trace, after trace, after shade)
     uint64_t device_bytes = 0;

@@ -41,6 +41,7 @@ struct TraceArgs {
     const float4* st_ray0; const float4* st_ray1;
     float4* st_hit; uint32_t* st_hit_inst;
     const uint32_t* queue; const uint32_t* count; uint32_t* head;
+    uint32_t postpone_limit;     // triangle groups may be postponed onto the stack only below this depth: RT2_STACK_SIZE - tree depth
     unsigned long long* stat_rays;
 };
 
@@ -123,24 +124,31 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs a) {
     }
 }
 
-// Single-level traversal with dynamic ray fetch and triangle postponing (after Aila & Laine 2009 and
-// Ylitie et al. 2017): a warp keeps its lanes busy by refilling finished lanes from the queue once
-// enough lane-iterations have been lost, and a lane whose triangle group would run with fewer than
-// POSTPONE_PCT % of the warp's live lanes pushes it back and keeps walking nodes.  The closest hit is a
-// total order (hit_closer), so the result does not depend on any of this scheduling.
-template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY>
+// Ray-queue traversal with dynamic ray fetch and triangle postponing (after Aila & Laine 2009 and Ylitie et al.
+// 2017): a warp keeps its lanes busy by refilling finished lanes from the queue (checked every CHECK_EVERY
+// iterations once REFILL_MIN lanes are idle), and a lane whose triangle group would run with fewer than
+// POSTPONE_PCT % of the warp's live lanes pushes it back and keeps walking nodes.
+// INSTANCED: the TLAS and the BLAS are walked by ONE loop — a lane is either at the top level (inst == ~0) or
+// inside an instance; entering an instance pushes what is left of the TLAS groups, re-expresses the ray in object
+// space (o' = inv*o, d' = inv*d, t unchanged) and starts at the BLAS root; the instance is left when the stack
+// is back at the depth it was entered with.  Lanes at different levels share every node step.
+// GENERIC: rays carry their own [tmin, tmax] (ray0 = o|tmin, ray1 = d|tmax) instead of K1's constants.
+// The closest hit is a total order (hit_closer), so the result does not depend on any of this scheduling.
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED = false, bool GENERIC = false>
 __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
     const uint32_t count = *a.count;
     const uint32_t lane = threadIdx.x & 31u;
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(a.stat_rays, (unsigned long long)count);
     uint2 stack[RT2_STACK_SIZE];
-    int sp = 0;
+    int sp = 0, inst_sp = 0;
     bool active = false, exhausted = false;
-    uint32_t slot = 0, tri_slot = 0xFFFFFFFFu;
+    uint32_t slot = 0, tri_slot = 0xFFFFFFFFu, inst = 0xFFFFFFFFu;
+    float tmin = RT2_K1_TMIN, tmax = RT2_BACKGROUND_DEPTH;
     RayPrep rp = make_ray_prep(v3(0.f, 0.f, 0.f), v3(1.f, 1.f, 1.f));
     RayShear sh = make_shear(v3(1.f, 1.f, 1.f));
     Hit best; best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
     uint2 ngroup = make_uint2(0u, 0u), tgroup = make_uint2(0u, 0u);
+    const int postpone_limit = (int)a.postpone_limit;
     for (;;) {
         const uint32_t need = __ballot_sync(0xFFFFFFFFu, !active);
         if (!exhausted && (need == 0xFFFFFFFFu || (REFILL_MIN > 0 && __popc(need) >= REFILL_MIN))) {
@@ -153,12 +161,13 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
                 if (idx < count) {
                     slot = a.queue[idx];
                     const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot];
-                    const V3 o = v3(r0.x, r0.y, r0.z), d = v3(r0.w, r1.x, r1.y);
+                    const V3 o = v3(r0.x, r0.y, r0.z), d = GENERIC ? v3(r1.x, r1.y, r1.z) : v3(r0.w, r1.x, r1.y);
+                    if (GENERIC) { tmin = r0.w; tmax = r1.w; }
                     rp = make_ray_prep(o, d);
-                    sh = make_shear(d);
-                    best.t = INFINITY; best.u = best.v = 0.f; best.geom = best.prim = 0xFFFFFFFFu;
-                    tri_slot = 0xFFFFFFFFu;
-                    sp = 0; ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
+                    if (!INSTANCED) sh = make_shear(d);
+                    best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
+                    tri_slot = 0xFFFFFFFFu; inst = 0xFFFFFFFFu;
+                    sp = 0; inst_sp = 0; ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
                     active = true;
                 }
             }
@@ -170,34 +179,64 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
         if (active) {
             for (;;) {
                 if (ngroup.y > 0x00FFFFFFu) {
-                    cwbvh_node_step(a.blas_nodes, rp, RT2_K1_TMIN, fminf(best.t, RT2_BACKGROUND_DEPTH), ngroup, tgroup, stack, sp);
+                    const Node8* level = (INSTANCED && inst == 0xFFFFFFFFu) ? a.tlas_nodes : a.blas_nodes;
+                    cwbvh_node_step(level, rp, tmin, fminf(best.t, tmax), ngroup, tgroup, stack, sp);
                 } else {
                     tgroup = ngroup;
                     ngroup = make_uint2(0u, 0u);
                 }
-                const int in_loop = __popc(__activemask());
-                while (tgroup.y != 0u) {
-                    if (POSTPONE_PCT > 0) {
-                        if (__popc(__activemask()) * 100 < in_loop * POSTPONE_PCT && sp < RT2_STACK_SIZE) { stack[sp++] = tgroup; break; }
+                if (INSTANCED && inst == 0xFFFFFFFFu) {
+                    if (tgroup.y != 0u) {                              // TLAS leaves = instance slots: enter one, keep the rest for later
+                        const uint32_t ti = rt2_fhs(tgroup.y);
+                        tgroup.y &= ~(1u << ti);
+                        if (tgroup.y != 0u) stack[sp++] = tgroup;
+                        if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
+                        inst = __ldg(a.tlas_slot_to_inst + tgroup.x + ti);
+                        const InstanceRec* ir = a.instances + inst;
+                        float m[12];
+#pragma unroll
+                        for (int k = 0; k < 3; k++) { const float4 r = ld16f(ir->inv + 4 * k); m[4 * k] = r.x; m[4 * k + 1] = r.y; m[4 * k + 2] = r.z; m[4 * k + 3] = r.w; }
+                        const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot];
+                        const V3 o = xform_point(m, v3(r0.x, r0.y, r0.z)), d = xform_vector(m, GENERIC ? v3(r1.x, r1.y, r1.z) : v3(r0.w, r1.x, r1.y));
+                        rp = make_ray_prep(o, d);
+                        sh = make_shear(d);
+                        inst_sp = sp;
+                        ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
+                        if (REFILL_MIN > 0 && !exhausted && --budget == 0) break;
+                        continue;
                     }
-                    const uint32_t ti = rt2_fhs(tgroup.y);
-                    tgroup.y &= ~(1u << ti);
-                    const uint32_t s = tgroup.x + ti;
-                    const TriPos* tp = a.tris + s;
-                    const float4 va = ld16f(&tp->v0), vb = ld16f(&tp->v1), vc = ld16f(&tp->v2);
-                    float t, u, v;
-                    if (ray_triangle(v3(rp.ox, rp.oy, rp.oz), sh, RT2_K1_TMIN, RT2_BACKGROUND_DEPTH, v3(va.x, va.y, va.z), v3(vb.x, vb.y, vb.z),
-                                     v3(vc.x, vc.y, vc.z), &t, &u, &v)) {
-                        const uint32_t geom = f2u(va.w), prim = f2u(vb.w);
-                        if (hit_closer(t, 0u, geom, prim, best)) {
-                            best.t = t; best.u = u; best.v = v; best.inst = 0u; best.geom = geom; best.prim = prim;
-                            tri_slot = s;
+                } else {
+                    const int in_loop = __popc(__activemask());
+                    while (tgroup.y != 0u) {
+                        if (POSTPONE_PCT > 0) {
+                            if (__popc(__activemask()) * 100 < in_loop * POSTPONE_PCT && sp < postpone_limit) { stack[sp++] = tgroup; break; }
+                        }
+                        const uint32_t ti = rt2_fhs(tgroup.y);
+                        tgroup.y &= ~(1u << ti);
+                        const uint32_t s = tgroup.x + ti;
+                        const TriPos* tp = a.tris + s;
+                        const float4 va = ld16f(&tp->v0), vb = ld16f(&tp->v1), vc = ld16f(&tp->v2);
+                        float t, u, v;
+                        if (ray_triangle(v3(rp.ox, rp.oy, rp.oz), sh, tmin, tmax, v3(va.x, va.y, va.z), v3(vb.x, vb.y, vb.z),
+                                         v3(vc.x, vc.y, vc.z), &t, &u, &v)) {
+                            const uint32_t geom = f2u(va.w), prim = f2u(vb.w);
+                            const uint32_t hi = INSTANCED ? inst : 0u;
+                            if (hit_closer(t, hi, geom, prim, best)) {
+                                best.t = t; best.u = u; best.v = v; best.inst = hi; best.geom = geom; best.prim = prim;
+                                tri_slot = s;
+                            }
                         }
                     }
                 }
                 if (ngroup.y <= 0x00FFFFFFu) {
+                    if (INSTANCED && inst != 0xFFFFFFFFu && sp == inst_sp) {    // this instance is done: back to the top level, world-space ray
+                        inst = 0xFFFFFFFFu;
+                        const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot];
+                        rp = make_ray_prep(v3(r0.x, r0.y, r0.z), GENERIC ? v3(r1.x, r1.y, r1.z) : v3(r0.w, r1.x, r1.y));
+                    }
                     if (sp == 0) {
                         a.st_hit[slot] = make_float4(best.t, best.u, best.v, __uint_as_float(tri_slot));
+                        if (INSTANCED) a.st_hit_inst[slot] = best.inst;
                         active = false;
                         break;
                     }
@@ -359,6 +398,8 @@ static TraceArgs make_trace_args(rt2_ctx* ctx) {
     t.blas_nodes = s.blas.nodes; t.tris = s.blas.tris;
     t.tlas_nodes = s.tlas.nodes; t.tlas_slot_to_inst = s.tlas.slot_to_prim; t.instances = s.instances;
     t.st_ray0 = f.st_ray0; t.st_ray1 = f.st_ray1; t.st_hit = f.st_hit; t.st_hit_inst = f.st_hit_inst;
+    const uint32_t depth = s.blas.depth + (s.num_instances ? s.tlas.depth + 2u : 0u) + 2u;    // node groups a ray can have stacked at once
+    t.postpone_limit = depth < RT2_STACK_SIZE ? RT2_STACK_SIZE - depth : 0u;
     return t;
 }
 
@@ -448,7 +489,12 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
         for (uint32_t it = 0; it < iterations; it++) {
             if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], ctx->stream));
             t.queue = q[it & 1]; t.count = f.counters + 4 + 2 * it; t.head = f.counters + 5 + 2 * it;
-            if (s.num_instances) k_trace<true><<<trace_blocks, 128, 0, ctx->stream>>>(t);
+            if (s.num_instances) {
+                // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
+                const bool unified = ctx->trace_variant != 0 && s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE;
+                if (unified) k_trace_dyn<20, 4, 8, true><<<trace_blocks, 128, 0, ctx->stream>>>(t);
+                else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+            }
             else launch_trace_single(ctx, t);
             if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], ctx->stream));
             a.queue_in = q[it & 1]; a.count_in = t.count; a.queue_out = q[(it + 1) & 1]; a.count_out = f.counters + 4 + 2 * (it + 1);
@@ -470,8 +516,10 @@ int render_init(rt2_ctx* ctx) {
     ctx->trace_variant = RT2_DEFAULT_TRACE_VARIANT;
     if (const char* e = getenv("RT2_TRACE_VARIANT")) { int v = atoi(e); if (v >= 0 && v < g_num_trace_variants) ctx->trace_variant = v; }
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, g_trace_variants[ctx->trace_variant], 128, 0));
-    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<true>, 128, 0));
-    ctx->trace_blocks_per_sm[0] = std::max(b0, 1); ctx->trace_blocks_per_sm[1] = std::max(b1, 1);
+    int b2 = 0;
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace_dyn<20, 4, 8, true>, 128, 0));
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, k_trace<true>, 128, 0));
+    ctx->trace_blocks_per_sm[0] = std::max(b0, 1); ctx->trace_blocks_per_sm[1] = std::max(b1, 1); ctx->trace_blocks_per_sm[2] = std::max(b2, 1);
     return RT2_OK;
 }
 
