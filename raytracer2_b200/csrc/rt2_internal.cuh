@@ -129,6 +129,7 @@ struct rt2_ctx {
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
     int trace_blocks_per_sm[3] = {1, 1, 1};             // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level
     int trace_variant = 0;
+    bool gi_megakernels = false;                         // RT2_GI_MEGAKERNEL=1: K4/K5 with inlined traversal instead of the ray-queue kernel (A/B)
     std::vector<cudaEvent_t> prof_events;   // RT2_LAUNCH_PROFILE: 3 per wavefront iteration (before trace, after trace, after shade)
     uint64_t device_bytes = 0;
     // lights / pdf textures (K10/K12)

@@ -13,6 +13,7 @@ namespace rt2 {
 
 int restir_ensure_resources(rt2_ctx* ctx);
 int lights_ensure_resources(rt2_ctx* ctx);
+int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays);
 
 struct GBufferArgs {
     SceneRefs sc; const rt2_gconst* g; uint32_t width, height;
@@ -503,6 +504,211 @@ __global__ void __launch_bounds__(128) k_gi_final_shading(GIArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// Wavefront form of K4 and of K5's DI-off branch: generate the ray (all shader code up to trace()), hand the
+// incoherent rays to the shared ray-queue kernel (rt2_render.cu: postponing + lane refill, 2-3x the rate of a
+// traversal inlined in a megakernel), then finish the shader from the hit record.  Same arithmetic, same order:
+// the split is invisible in the outputs.  Per-pixel hand-over state lives in the path-state arrays of K1
+// (st_ray0/1 = ray, st_acc = BRDF/pdf, st_misc.x = flags), slot = launch index.
+// ------------------------------------------------------------------------------------------------
+struct GIWaveArgs {
+    GIArgs gi;
+    float4 *st_ray0, *st_ray1, *st_acc; uint4* st_misc; float4* st_hit; const uint32_t* st_hit_inst;
+    uint32_t* queue; uint32_t* count;
+};
+#define GIW_VALID 1u
+#define GIW_SPECULAR 2u
+#define GIW_DELTA 4u
+
+__global__ void __launch_bounds__(128) k_brdf_rays_gen(GIWaveArgs w) {
+    const GIArgs& a = w.gi;
+    uint32_t lx, ly;
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    bool traced = false;
+    uint32_t slot = 0;
+    if (inside) {
+        slot = ly * a.width + lx;
+        const rt2_gconst& g = *a.g;
+        uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+        const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+        uint32_t flags = 0u;
+        if (surface.view_depth != RT2_BACKGROUND_DEPTH) {              // RAB_IsSurfaceValid, bridge :346-349
+            Rng rng = rng_init(lx, ly, a.frame, 5u);
+            V3 tangent, bitangent; construct_onb(surface.normal, &tangent, &bitangent);
+            const V3 cam = v3(g.view.camera_direction_or_position[0], g.view.camera_direction_or_position[1], g.view.camera_direction_or_position[2]);
+            const float depth = fmaxf(1.0f, 0.1f * length3(surface.world_pos - cam));
+            const float tmin = 0.001f * depth;
+            float tmax = RT2_BACKGROUND_DEPTH;
+            const float randx = rng_next(rng), randy = rng_next(rng);
+            const V3 V = normalize3(cam - surface.world_pos);
+            const bool is_delta = surface.roughness == 0;
+            bool is_specular_ray;
+            float specular_pdf, overall_pdf;
+            V3 brdf_over_pdf, dir;
+            {
+                const V3 Ve = v3(dot3(V, tangent), dot3(V, bitangent), dot3(V, surface.normal));
+                const V3 He = sample_ggx_vndf(Ve, surface.roughness, randx, randy);
+                const V3 H = is_delta ? surface.normal : normalize3((tangent * He.x + bitangent * He.y) + surface.normal * He.z);
+                const V3 specular_direction = reflect3(neg3(V), H);
+                const float HoV = saturatef(dot3(H, V)), NoV = saturatef(dot3(surface.normal, V));
+                const V3 F = schlick_fresnel(surface.specular_f0, HoV);
+                const float G1 = is_delta ? 1.0f : (NoV > 0) ? g1_smith(surface.roughness, NoV) : 0.f;
+                const V3 specular_brdf_over_pdf = F * G1;
+                const V3 local_direction = sample_cos_hemisphere(randx, randy, false);
+                const V3 diffuse_direction = (tangent * local_direction.x + bitangent * local_direction.y) + surface.normal * local_direction.z;
+                const float diffuse_brdf_over_pdf = 1.0f;
+                specular_pdf = saturatef(calc_luminance(specular_brdf_over_pdf) / calc_luminance(specular_brdf_over_pdf + surface.diffuse_albedo * diffuse_brdf_over_pdf));
+                is_specular_ray = rng_next(rng) < specular_pdf;
+                if (is_specular_ray) { dir = specular_direction; brdf_over_pdf = specular_brdf_over_pdf / specular_pdf; }
+                else { dir = diffuse_direction; const float d = diffuse_brdf_over_pdf / (1.0f - specular_pdf); brdf_over_pdf = v3(d, d, d); }
+                const float specular_lobe_pdf = ggx_vndf_pdf(surface.roughness, surface.normal, V, dir);
+                const float diffuse_lobe_pdf = saturatef(dot3(dir, surface.normal)) / RT2_RTXDI_PI;
+                overall_pdf = is_delta ? diffuse_lobe_pdf : mixf(diffuse_lobe_pdf, specular_lobe_pdf, specular_pdf);
+            }
+            if (dot3(surface.geo_normal, dir) <= 0.0f) { brdf_over_pdf = v3(0.f, 0.f, 0.f); tmax = 0.f; }
+            flags = GIW_VALID | (is_specular_ray ? GIW_SPECULAR : 0u) | (is_delta ? GIW_DELTA : 0u);
+            w.st_ray0[slot] = make_float4(surface.world_pos.x, surface.world_pos.y, surface.world_pos.z, tmin);
+            w.st_ray1[slot] = make_float4(dir.x, dir.y, dir.z, tmax);
+            w.st_acc[slot] = make_float4(brdf_over_pdf.x, brdf_over_pdf.y, brdf_over_pdf.z, overall_pdf);
+            traced = tmin <= tmax;                                     // TMin > TMax: miss without a ray (oracle P2)
+            if (!traced) w.st_hit[slot] = make_float4(INFINITY, 0.f, 0.f, __uint_as_float(0xFFFFFFFFu));
+        }
+        w.st_misc[slot] = make_uint4(flags, 0u, 0u, 0u);
+    }
+    warp_append(traced, slot, w.queue, w.count);
+}
+
+__global__ void __launch_bounds__(128) k_brdf_rays_shade(GIWaveArgs w) {
+    const GIArgs& a = w.gi;
+    __shared__ float lut[256];
+    lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
+    __syncthreads();
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const uint32_t slot = ly * a.width + lx;
+    const uint32_t flags = w.st_misc[slot].x;
+    uint32_t hits = 0;
+    if (flags & GIW_VALID) {
+        const rt2_gconst& g = *a.g;
+        uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+        const bool is_specular_ray = (flags & GIW_SPECULAR) != 0u, is_delta = (flags & GIW_DELTA) != 0u;
+        const float4 r0 = w.st_ray0[slot], r1 = w.st_ray1[slot], ac = w.st_acc[slot], h = w.st_hit[slot];
+        const V3 origin = v3(r0.x, r0.y, r0.z), dir = v3(r1.x, r1.y, r1.z);
+        const V3 brdf_over_pdf = v3(ac.x, ac.y, ac.z);
+        const float overall_pdf = ac.w;
+        const uint32_t tri_slot = __float_as_uint(h.w);
+        V3 radiance = v3(0.f, 0.f, 0.f);
+        V3 sec_position, sec_normal, sec_albedo, sec_f0; float sec_roughness; bool sec_is_env;
+        const bool include_emissive = g.enable_restir_di == 0u || (is_specular_ray && is_delta);
+        if (tri_slot != 0xFFFFFFFFu) {
+            hits++;
+            const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? w.st_hit_inst[slot] : 0u, h.y, h.z);
+            if (include_emissive) radiance = radiance + sf.emission;
+            sec_position = origin + dir * h.x;
+            sec_normal = (dot3(sf.normal, dir) < 0) ? sf.normal : neg3(sf.normal);
+            sec_albedo = sf.color; sec_f0 = sf.specular_f0; sec_roughness = sf.roughness; sec_is_env = false;
+        } else {
+            if (include_emissive) radiance = radiance + environment_radiance(a.sc, g, dir);
+            sec_position = origin + dir * 1000.0f;                     // DISTANT_LIGHT_DISTANCE, PolymorphicLight.glsl:43
+            sec_normal = neg3(dir);
+            sec_albedo = v3(0.f, 0.f, 0.f); sec_f0 = v3(0.f, 0.f, 0.f); sec_roughness = 0.0f; sec_is_env = true;
+        }
+        if (g.enable_brdf_indirect == 1u) {
+            uint32_t fl = 0;
+            if (is_specular_ray) fl |= RT2_SECONDARY_IS_SPECULAR_RAY;
+            if (is_delta) fl |= RT2_SECONDARY_IS_DELTA_SURFACE;
+            if (sec_is_env) fl |= RT2_SECONDARY_IS_ENVIRONMENT;
+            const uint32_t ptr = reservoir_pointer(g.restir_gi.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_gi.reservoir_buffer_params.reservoir_array_pitch, lx, ly, 0u);
+            uint4* dst = a.secondary + 3 * (size_t)ptr;
+            dst[0] = make_uint4(__float_as_uint(sec_position.x), __float_as_uint(sec_position.y), __float_as_uint(sec_position.z), ndir_to_oct_unorm32(sec_normal));
+            dst[1] = make_uint4(pack_r16g16_float(brdf_over_pdf.x, brdf_over_pdf.y), pack_r16g16_float(brdf_over_pdf.z, 0.0f) | (fl << 16),
+                                pack_r11g11b10(sec_albedo), pack_rgba8_gamma(sec_f0.x, sec_f0.y, sec_f0.z, sec_roughness));
+            dst[2] = make_uint4(__float_as_uint(radiance.x), __float_as_uint(radiance.y), __float_as_uint(radiance.z), __float_as_uint(overall_pdf));
+            if (g.enable_restir_gi == 1u) radiance = v3(0.f, 0.f, 0.f);
+        }
+        if (radiance.x > 0.0f || radiance.y > 0.0f || radiance.z > 0.0f || g.enable_brdf_additive_blend == 0u) {
+            const V3 diffuse = is_specular_ray ? v3(0.f, 0.f, 0.f) : radiance * brdf_over_pdf;
+            V3 specular = is_specular_ray ? radiance * brdf_over_pdf : v3(0.f, 0.f, 0.f);
+            V3 f0 = v3(0.f, 0.f, 0.f);                                 // the primary surface's specularF0 is all the shading tail needs
+            if ((float)px < g.view.viewport_size[0] && (float)py < g.view.viewport_size[1]) { const float4 sr = unpack_rgba8_gamma(a.gb.specular_rough[(size_t)py * a.width + px]); f0 = v3(sr.x, sr.y, sr.z); }
+            specular = demodulate_specular(f0, specular);
+            if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, diffuse, specular, false, a.diffuse, a.specular, a.diffuse_f32);
+        }
+    }
+    flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
+}
+
+// K5, DI off (shade_secondary_surfaces.rgen:119-128 is then the only ray): every launch index traces one cosine bounce
+// from its secondary surface.
+__global__ void __launch_bounds__(128) k_shade_secondary_gen(GIWaveArgs w) {
+    const GIArgs& a = w.gi;
+    uint32_t lx, ly;
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    uint32_t slot = 0;
+    if (inside) {
+        slot = ly * a.width + lx;
+        const rt2_gconst& g = *a.g;
+        Rng rng = rng_init(lx, ly, a.frame, 6u);
+        const uint32_t gbuffer_index = reservoir_pointer(g.restir_di.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_di.reservoir_buffer_params.reservoir_array_pitch, lx, ly, 0u);
+        const uint4 s0 = a.secondary[3 * (size_t)gbuffer_index];
+        Surface sec = empty_surface();                                 // surface_brdf_sample only reads the normal
+        sec.normal = oct_to_ndir_unorm32(s0.w);
+        V3 dir;
+        surface_brdf_sample(sec, rng, &dir);
+        w.st_ray0[slot] = make_float4(__uint_as_float(s0.x), __uint_as_float(s0.y), __uint_as_float(s0.z), 0.001f);
+        w.st_ray1[slot] = make_float4(dir.x, dir.y, dir.z, 1000.0f);
+    }
+    warp_append(inside, slot, w.queue, w.count);
+}
+
+__global__ void __launch_bounds__(128) k_shade_secondary_shade(GIWaveArgs w) {
+    const GIArgs& a = w.gi;
+    __shared__ float lut[256];
+    lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
+    __syncthreads();
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const uint32_t slot = ly * a.width + lx;
+    const rt2_gconst& g = *a.g;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    uint32_t hits = 0;
+    const uint32_t gbuffer_index = reservoir_pointer(g.restir_di.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_di.reservoir_buffer_params.reservoir_array_pitch, lx, ly, 0u);
+    uint4* sgp = a.secondary + 3 * (size_t)gbuffer_index;
+    const uint4 s0 = sgp[0], s1 = sgp[1], s2 = sgp[2];
+    const V3 throughput = unpack_half3(s1.x, s1.y);
+    const uint32_t flags = s1.y >> 16;
+    const bool valid_secondary = throughput.x != 0 || throughput.y != 0 || throughput.z != 0;
+    const bool is_specular_ray = (flags & RT2_SECONDARY_IS_SPECULAR_RAY) != 0u;
+    const bool is_delta = (flags & RT2_SECONDARY_IS_DELTA_SURFACE) != 0u;
+    V3 radiance = v3(__uint_as_float(s2.x), __uint_as_float(s2.y), __uint_as_float(s2.z));
+    const float pdf = __uint_as_float(s2.w);
+    const V3 sec_world_pos = v3(__uint_as_float(s0.x), __uint_as_float(s0.y), __uint_as_float(s0.z));
+    const V3 sec_normal = oct_to_ndir_unorm32(s0.w);
+    const V3 sec_albedo = unpack_r11g11b10(s1.z);
+    {
+        const float4 h = w.st_hit[slot];
+        const uint32_t tri_slot = __float_as_uint(h.w);
+        V3 emission;
+        if (tri_slot == 0xFFFFFFFFu) { const float4 r1 = w.st_ray1[slot]; emission = environment_radiance(a.sc, g, v3(r1.x, r1.y, r1.z)); }   // Q2 / oracle P4
+        else { hits++; emission = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? w.st_hit_inst[slot] : 0u, h.y, h.z).emission; }
+        radiance = radiance + emission * sec_albedo;
+    }
+    GIReservoir reservoir = empty_gi_reservoir();
+    const bool output_shading_result = is_specular_ray && is_delta;
+    if (valid_secondary && !output_shading_result) reservoir = make_gi_reservoir(sec_world_pos, sec_normal, radiance, pdf);
+    const uint32_t rx = g.runtime_params.active_checkerboard_field != 0u ? (px >> 1) : px;
+    store_gi_reservoir(a.reservoirs, reservoir_pointer(g.restir_gi.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_gi.reservoir_buffer_params.reservoir_array_pitch,
+                                                       rx, py, g.restir_gi.buffer_indices.secondary_surface_restirdi_output_buffer_index), reservoir, 0u);
+    const V3 saved = output_shading_result ? v3(0.f, 0.f, 0.f) : radiance;
+    sgp[2] = make_uint4(__float_as_uint(saved.x), __float_as_uint(saved.y), __float_as_uint(saved.z), s2.w);
+    if (output_shading_result) {
+        const Surface primary = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+        const V3 specular = demodulate_specular(primary.specular_f0, radiance);
+        if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, v3(0.f, 0.f, 0.f), specular, false, a.diffuse, a.specular, a.diffuse_f32);
+    }
+    flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
+}
+
+// ------------------------------------------------------------------------------------------------
 // N2 — GI temporal (K6) and spatial (K7) resampling: lighting_passes/temporal_resampling.rgen,
 // spatial_resampling.rgen, rtxdi/GIResamplingFunctions.hlsli:186-553.  The first kernels with cross-pixel reads:
 // neighbours come from last frame's G-buffer / reservoir page (K6) or from this frame's (K7); the page a kernel
@@ -706,7 +912,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         if (f.counters) { RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(f.counters); f.counters = nullptr; }
         RT2_CUDA(ctx, cudaMalloc((void**)&f.counters, 8 * 4)); f.counter_capacity = 8;
     }
-    RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, 16, ctx->stream));
+    RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, 32, ctx->stream));
     unsigned long long* stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
     unsigned long long* stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
     const uint32_t cur = frame & 1u;                   // ping-pong, src/light_passes.rs:565-577
@@ -784,8 +990,26 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         gi.secondary = f.secondary_gbuffer; gi.reservoirs = f.gi_reservoirs;
         gi.diffuse = f.diffuse_f16; gi.specular = f.specular_f16; gi.diffuse_f32 = f.diffuse_f32;
         gi.stat_rays = stat_rays; gi.stat_hits = stat_hits;
-        k_brdf_rays<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
-        k_shade_secondary<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+        if (ctx->gi_megakernels) {
+            k_brdf_rays<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+            k_shade_secondary<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+        } else {
+            // generate -> shared ray-queue kernel -> finish; queue counters: [4] count, [5] head for K4, [6], [7] for K5
+            GIWaveArgs wa{};
+            wa.gi = gi; wa.st_ray0 = f.st_ray0; wa.st_ray1 = f.st_ray1; wa.st_acc = f.st_acc; wa.st_misc = f.st_misc; wa.st_hit = f.st_hit; wa.st_hit_inst = f.st_hit_inst;
+            wa.queue = f.queue0; wa.count = f.counters + 4;
+            k_brdf_rays_gen<<<blocks, 128, 0, ctx->stream>>>(wa);
+            if ((rc = trace_queue_generic(ctx, wa.queue, wa.count, f.counters + 5, stat_rays))) return rc;
+            k_brdf_rays_shade<<<blocks, 128, 0, ctx->stream>>>(wa); launches += 3;
+            if (g.enable_restir_di == 1u) {                            // K5 chains a BRDF ray and a visibility ray through the light sampler: stays one kernel
+                k_shade_secondary<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+            } else {
+                wa.queue = f.queue1; wa.count = f.counters + 6;
+                k_shade_secondary_gen<<<blocks, 128, 0, ctx->stream>>>(wa);
+                if ((rc = trace_queue_generic(ctx, wa.queue, wa.count, f.counters + 7, stat_rays))) return rc;
+                k_shade_secondary_shade<<<blocks, 128, 0, ctx->stream>>>(wa); launches += 3;
+            }
+        }
         if (g.enable_temporal_resampling == 1u || g.enable_spatial_resampling == 1u) {
             const uint32_t prev = cur ^ 1u;
             GIResampleArgs ra{};

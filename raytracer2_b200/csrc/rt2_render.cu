@@ -58,19 +58,6 @@ struct ShadeArgs {
     unsigned long long* stat_hits;
 };
 
-// one atomicAdd per warp: ballot + popc compaction of the lanes that stay alive
-__device__ __forceinline__ void warp_append(bool alive, uint32_t slot, uint32_t* queue_out, uint32_t* count_out) {
-    __syncwarp();
-    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);   // every lane of the warp calls this
-    if (mask == 0u) return;
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t leader = __ffs(mask) - 1u;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(count_out, __popc(mask));
-    base = __shfl_sync(0xFFFFFFFFu, base, leader);
-    if (alive) queue_out[base + __popc(mask & ((1u << lane) - 1u))] = slot;
-}
-
 // ------------------------------------------------------------------------------------------------
 // kernels
 // ------------------------------------------------------------------------------------------------
@@ -97,7 +84,7 @@ __global__ void __launch_bounds__(256) k_k1_init(ShadeArgs a, uint32_t padded) {
     warp_append(alive, slot, a.queue_out, a.count_out);
 }
 
-template <bool INSTANCED>
+template <bool INSTANCED, bool GENERIC = false>
 __global__ void __launch_bounds__(128) k_trace(TraceArgs a) {
     const uint32_t count = *a.count;
     const uint32_t lane = threadIdx.x & 31u;
@@ -112,8 +99,8 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs a) {
             const uint32_t slot = a.queue[idx];
             const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot];
             TraceRay ray;
-            ray.o = v3(r0.x, r0.y, r0.z); ray.d = v3(r0.w, r1.x, r1.y);
-            ray.tmin = RT2_K1_TMIN; ray.tmax = RT2_BACKGROUND_DEPTH;
+            ray.o = v3(r0.x, r0.y, r0.z); ray.d = GENERIC ? v3(r1.x, r1.y, r1.z) : v3(r0.w, r1.x, r1.y);
+            ray.tmin = GENERIC ? r0.w : RT2_K1_TMIN; ray.tmax = GENERIC ? r1.w : RT2_BACKGROUND_DEPTH;
             Hit best; best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
             uint32_t tri_slot = 0xFFFFFFFFu;
             if (INSTANCED) tlas_closest_hit(a.tlas_nodes, a.tlas_slot_to_inst, a.instances, a.blas_nodes, a.tris, ray, best, &tri_slot);
@@ -511,9 +498,26 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
     return RT2_OK;
 }
 
+// Traces a queue of GENERIC rays (st_ray0 = o|tmin, st_ray1 = d|tmax, slot = pixel-linear index) into st_hit / st_hit_inst:
+// the ReSTIR passes hand their incoherent rays to the same postponing/refilling kernel the path tracer uses.
+int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays) {
+    const DeviceScene& s = ctx->scene;
+    TraceArgs t = make_trace_args(ctx);
+    t.queue = queue; t.count = count; t.head = head; t.stat_rays = stat_rays;
+    if (s.num_instances) {
+        if (s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE) k_trace_dyn<20, 4, 8, true, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        else k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+    } else {
+        k_trace_dyn<20, 4, 8, false, true><<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+    }
+    RT2_CUDA(ctx, cudaGetLastError());
+    return RT2_OK;
+}
+
 int render_init(rt2_ctx* ctx) {
     int b0 = 0, b1 = 0;
     ctx->trace_variant = RT2_DEFAULT_TRACE_VARIANT;
+    if (const char* e = getenv("RT2_GI_MEGAKERNEL")) ctx->gi_megakernels = atoi(e) != 0;
     if (const char* e = getenv("RT2_TRACE_VARIANT")) { int v = atoi(e); if (v >= 0 && v < g_num_trace_variants) ctx->trace_variant = v; }
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, g_trace_variants[ctx->trace_variant], 128, 0));
     int b2 = 0;

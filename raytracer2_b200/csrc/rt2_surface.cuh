@@ -166,4 +166,18 @@ __device__ __forceinline__ SurfaceFetch get_geometry_from_hit(const SceneRefs& s
     return f;
 }
 
+// one atomicAdd per warp: ballot + popc compaction of the lanes that stay alive
+__device__ __forceinline__ void warp_append(bool alive, uint32_t slot, uint32_t* queue_out, uint32_t* count_out) {
+    __syncwarp();
+    const uint32_t mask = __ballot_sync(0xFFFFFFFFu, alive);   // every lane of the warp calls this
+    if (mask == 0u) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t leader = __ffs(mask) - 1u;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(count_out, __popc(mask));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (alive) queue_out[base + __popc(mask & ((1u << lane) - 1u))] = slot;
+}
+
+
 }  // namespace rt2
