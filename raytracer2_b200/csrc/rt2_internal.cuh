@@ -105,6 +105,7 @@ struct FrameBuffers {
     rt2_packed_di_reservoir* di_reservoirs = nullptr;    // arrayPitch x 2
     uint4* gi_reservoirs = nullptr;                      // 32 B x arrayPitch x 2
     uint4* secondary_gbuffer = nullptr;                  // 48 B x arrayPitch
+    uint4* di_state = nullptr;                           // 5 planes x W x H: sampler state parked between the wavefront stages of K9
     char2* neighbor_offsets = nullptr;                   // RT2_NEIGHBOR_OFFSET_COUNT signed byte pairs (K7)
     uint32_t reservoir_block_row_pitch = 0, reservoir_array_pitch = 0;
     uint32_t* counters = nullptr;      // [0..1] u64 rays, [2..3] u64 hits, then (count, head) per wavefront iteration

@@ -15,9 +15,9 @@ void passes_release_frame(rt2_ctx* ctx) {
         for (void* p : ptrs) if (p) cudaFree(p);
         f.gb_depth[i] = nullptr; f.gb_normals[i] = f.gb_geo_normals[i] = f.gb_diffuse_albedo[i] = f.gb_specular_rough[i] = nullptr; f.gb_emissive[i] = nullptr;
     }
-    void* ptrs[] = {f.motion_vectors, f.di_reservoirs, f.gi_reservoirs, f.secondary_gbuffer, f.neighbor_offsets};
+    void* ptrs[] = {f.motion_vectors, f.di_reservoirs, f.gi_reservoirs, f.secondary_gbuffer, f.neighbor_offsets, f.di_state};
     for (void* p : ptrs) if (p) cudaFree(p);
-    f.motion_vectors = nullptr; f.di_reservoirs = nullptr; f.gi_reservoirs = nullptr; f.secondary_gbuffer = nullptr; f.neighbor_offsets = nullptr;
+    f.motion_vectors = nullptr; f.di_reservoirs = nullptr; f.gi_reservoirs = nullptr; f.secondary_gbuffer = nullptr; f.neighbor_offsets = nullptr; f.di_state = nullptr;
     f.reservoir_block_row_pitch = f.reservoir_array_pitch = 0;
 }
 
@@ -64,6 +64,7 @@ int restir_ensure_resources(rt2_ctx* ctx) {
         RT2_CUDA(ctx, cudaMemcpyAsync(f.neighbor_offsets, tab.data(), tab.size(), cudaMemcpyHostToDevice, ctx->stream));
         RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // `tab` is pageable host memory going out of scope
     }
+    RT2_CUDA(ctx, zalloc(ctx, &f.di_state, n * 5));                                        // K9 wavefront hand-over state, 80 B per pixel
     RT2_CUDA(ctx, zalloc(ctx, &f.secondary_gbuffer, (size_t)f.reservoir_array_pitch * 3)); // 48 B x arrayPitch (block-linear addressing), :309-317
     return RT2_OK;
 }

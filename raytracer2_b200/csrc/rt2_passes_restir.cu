@@ -102,13 +102,16 @@ __device__ __forceinline__ bool visibility_ray_miss(const SceneRefs& sc, const S
     return h.geom == 0xFFFFFFFFu;
 }
 
-__device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& sc, const LightRefs& lr, const rt2_gconst& g, Rng& rng, const Surface& surface,
-                                                              const SampleParams& sp, LightSample* o_light_sample, uint32_t& rays, uint32_t& hits) {
+// The sampler in three pieces, so that the megakernel form (trace inlined between them) and the wavefront form of K9
+// (ray-queue kernel between them) run the very same arithmetic.
+// (1) RTXDI_SampleLocalLights{,Internal}, :264-343 (uniform selection)
+__device__ __forceinline__ void sl_local_lights(const LightRefs& lr, const rt2_gconst& g, Rng& rng, const Surface& surface, const SampleParams& sp,
+                                                DIReservoir* local_reservoir, LightSample* local_sample) {
     const uint32_t first_local = g.light_buffer_params.local_light_buffer_region.first_light_index;
     const uint32_t num_local = g.light_buffer_params.local_light_buffer_region.num_lights;
-    LightSample local_sample = empty_light_sample();
-    DIReservoir local_reservoir = empty_di_reservoir();
-    if (num_local != 0u && sp.num_local != 0u) {                       // RTXDI_SampleLocalLights{,Internal}, :264-343 (uniform selection)
+    *local_sample = empty_light_sample();
+    *local_reservoir = empty_di_reservoir();
+    if (num_local != 0u && sp.num_local != 0u) {
         DIReservoir state = empty_di_reservoir();
         for (uint32_t i = 0; i < sp.num_local; i++) {
             const float rnd = rng_next(rng);                           // UniformSampling.hlsli:14-25
@@ -121,60 +124,63 @@ __device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& s
             const float target_pdf = light_sample_target_pdf(cand, surface);
             const float ris_rnd = rng_next(rng);
             if (blended == 0) continue;
-            if (di_stream_sample(state, light_index, uvx, uvy, ris_rnd, target_pdf, 1.0f / blended)) local_sample = cand;
+            if (di_stream_sample(state, light_index, uvx, uvy, ris_rnd, target_pdf, 1.0f / blended)) *local_sample = cand;
         }
         di_finalize(state, 1.0f, (float)sp.num_mis);
         state.M = 1;
-        local_reservoir = state;
+        *local_reservoir = state;
     }
-    // RTXDI_SampleInfiniteLights: the infinite region is always empty (src/main.rs:375-380; rejected on the host otherwise)
-    const LightSample infinite_sample = empty_light_sample();
-    const DIReservoir infinite_reservoir = empty_di_reservoir();
-    // ---- RTXDI_SampleBrdf, :507-591
-    LightSample brdf_sample = empty_light_sample();
-    DIReservoir brdf_reservoir = empty_di_reservoir();
-    for (uint32_t i = 0; i < sp.num_brdf; ++i) {
-        float light_source_pdf = 0;
-        V3 sample_dir = v3(0.f, 0.f, 0.f);
-        uint32_t light_index = RT2_INVALID_LIGHT;
-        float rx = 0, ry = 0;
-        LightSample cand = empty_light_sample();
-        if (surface_brdf_sample(surface, rng, &sample_dir)) {
-            const float brdf_pdf = surface_brdf_pdf(surface, sample_dir);
-            const float max_distance = brdf_max_distance_from_pdf(sp.brdf_cutoff, brdf_pdf);
-            uint32_t slot;                                             // RAB_TraceRayForLocalLight, bridge :629-669
-            const Hit h = trace_closest(sc, surface.world_pos, sample_dir, sp.brdf_ray_min_t, max_distance, &slot);
-            rays++;
-            if (h.geom != 0xFFFFFFFFu) {
-                hits++;
-                uint32_t li = __ldg(lr.geom_to_light + h.geom);        // getLightIndex, bridge :621-627
-                if (li != RT2_INVALID_LIGHT) li += h.prim;
-                light_index = li;
-            }
-            if (light_index != RT2_INVALID_LIGHT) {
-                const float bx = 1 - h.u - h.v, bz = h.v;              // hitUVToBarycentric, randomFromBarycentric (Helpers.glsl:76-86)
-                const float sqrtx = 1 - bx;
-                rx = sqrtx * sqrtx; ry = bz / sqrtx;
-                cand = sample_polymorphic_light(load_light_info(lr.lights, light_index), surface, rx, ry);
-                if (sp.brdf_cutoff > 0.f) {
-                    const V3 to_light = cand.position - surface.world_pos;
-                    const float light_distance = length3(to_light);
-                    const float pdf2 = surface_brdf_pdf(surface, to_light / light_distance);
-                    if (light_distance > brdf_max_distance_from_pdf(sp.brdf_cutoff, pdf2)) light_index = RT2_INVALID_LIGHT;
-                }
-                if (light_index != RT2_INVALID_LIGHT) light_source_pdf = local_light_source_pdf(lr, light_index);
-            }
-            // BRDF miss + environmentLightParams.lightPresent: the environment light (index lights + 1) is never written (Q7) -> absent
+}
+// (2) RTXDI_SampleBrdf, :507-591, one iteration: the ray ...
+struct BrdfProbe { bool sampled; V3 dir; float max_distance; };
+__device__ __forceinline__ BrdfProbe sl_brdf_ray(const Surface& surface, Rng& rng, const SampleParams& sp) {
+    BrdfProbe p; p.dir = v3(0.f, 0.f, 0.f); p.max_distance = 0.f;
+    p.sampled = surface_brdf_sample(surface, rng, &p.dir);
+    if (p.sampled) p.max_distance = brdf_max_distance_from_pdf(sp.brdf_cutoff, surface_brdf_pdf(surface, p.dir));
+    return p;
+}
+// ... and what follows its hit (RAB_TraceRayForLocalLight, bridge :629-669): geom == ~0u is a miss
+__device__ __forceinline__ void sl_brdf_hit(const LightRefs& lr, Rng& rng, const Surface& surface, const SampleParams& sp, bool sampled,
+                                            uint32_t geom, uint32_t prim, float hu, float hv, DIReservoir* brdf_reservoir, LightSample* brdf_sample) {
+    float light_source_pdf = 0;
+    uint32_t light_index = RT2_INVALID_LIGHT;
+    float rx = 0, ry = 0;
+    LightSample cand = empty_light_sample();
+    if (sampled) {
+        if (geom != 0xFFFFFFFFu) {
+            uint32_t li = __ldg(lr.geom_to_light + geom);              // getLightIndex, bridge :621-627
+            if (li != RT2_INVALID_LIGHT) li += prim;
+            light_index = li;
         }
-        if (light_source_pdf == 0) continue;
-        const float target_pdf = light_sample_target_pdf(cand, surface);
-        const float blended = light_brdf_mis_weight(surface, cand, light_source_pdf, sp.local_mis_weight, false, sp);
-        const float ris_rnd = rng_next(rng);
-        if (di_stream_sample(brdf_reservoir, light_index, rx, ry, ris_rnd, target_pdf, 1.0f / blended)) brdf_sample = cand;
+        if (light_index != RT2_INVALID_LIGHT) {
+            const float bx = 1 - hu - hv, bz = hv;                     // hitUVToBarycentric, randomFromBarycentric (Helpers.glsl:76-86)
+            const float sqrtx = 1 - bx;
+            rx = sqrtx * sqrtx; ry = bz / sqrtx;
+            cand = sample_polymorphic_light(load_light_info(lr.lights, light_index), surface, rx, ry);
+            if (sp.brdf_cutoff > 0.f) {
+                const V3 to_light = cand.position - surface.world_pos;
+                const float light_distance = length3(to_light);
+                const float pdf2 = surface_brdf_pdf(surface, to_light / light_distance);
+                if (light_distance > brdf_max_distance_from_pdf(sp.brdf_cutoff, pdf2)) light_index = RT2_INVALID_LIGHT;
+            }
+            if (light_index != RT2_INVALID_LIGHT) light_source_pdf = local_light_source_pdf(lr, light_index);
+        }
+        // BRDF miss + environmentLightParams.lightPresent: the environment light (index lights + 1) is never written (Q7) -> absent
     }
+    if (light_source_pdf == 0) return;
+    const float target_pdf = light_sample_target_pdf(cand, surface);
+    const float blended = light_brdf_mis_weight(surface, cand, light_source_pdf, sp.local_mis_weight, false, sp);
+    const float ris_rnd = rng_next(rng);
+    if (di_stream_sample(*brdf_reservoir, light_index, rx, ry, ris_rnd, target_pdf, 1.0f / blended)) *brdf_sample = cand;
+}
+// (3) finalize the BRDF reservoir and combine, :586-590, 637-663.  The infinite-light region is always empty
+// (src/main.rs:375-380; rejected on the host otherwise), so its reservoir and sample are the empty ones.
+__device__ __forceinline__ DIReservoir sl_combine(Rng& rng, const SampleParams& sp, const DIReservoir& local_reservoir, const LightSample& local_sample,
+                                                  DIReservoir brdf_reservoir, const LightSample& brdf_sample, LightSample* o_light_sample) {
     di_finalize(brdf_reservoir, 1.0f, (float)sp.num_mis);
     brdf_reservoir.M = 1;
-    // ---- combine, :637-663
+    const LightSample infinite_sample = empty_light_sample();
+    const DIReservoir infinite_reservoir = empty_di_reservoir();
     DIReservoir reservoir = empty_di_reservoir();
     di_combine(reservoir, local_reservoir, 0.5f, local_reservoir.target_pdf);
     const bool select_infinite = di_combine(reservoir, infinite_reservoir, rng_next(rng), infinite_reservoir.target_pdf);
@@ -183,6 +189,26 @@ __device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& s
     reservoir.M = 1;
     *o_light_sample = select_brdf ? brdf_sample : (select_infinite ? infinite_sample : local_sample);
     return reservoir;
+}
+
+__device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& sc, const LightRefs& lr, const rt2_gconst& g, Rng& rng, const Surface& surface,
+                                                              const SampleParams& sp, LightSample* o_light_sample, uint32_t& rays, uint32_t& hits) {
+    LightSample local_sample; DIReservoir local_reservoir;
+    sl_local_lights(lr, g, rng, surface, sp, &local_reservoir, &local_sample);
+    LightSample brdf_sample = empty_light_sample();
+    DIReservoir brdf_reservoir = empty_di_reservoir();
+    for (uint32_t i = 0; i < sp.num_brdf; ++i) {
+        const BrdfProbe p = sl_brdf_ray(surface, rng, sp);
+        Hit h; h.geom = h.prim = 0xFFFFFFFFu; h.u = h.v = 0.f;
+        if (p.sampled) {
+            uint32_t slot;
+            h = trace_closest(sc, surface.world_pos, p.dir, sp.brdf_ray_min_t, p.max_distance, &slot);
+            rays++;
+            if (h.geom != 0xFFFFFFFFu) hits++;
+        }
+        sl_brdf_hit(lr, rng, surface, sp, p.sampled, h.geom, h.prim, h.u, h.v, &brdf_reservoir, &brdf_sample);
+    }
+    return sl_combine(rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, o_light_sample);
 }
 
 // ShadeSurfaceWithLightSample, ShadingHelpers.glsl:2-58.  Visibility reuse needs reservoir.age > 0 (DIReservoir.hlsli:186-189);
@@ -260,6 +286,203 @@ __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
     dst[2] = make_uint2(__float_as_uint(packed.target_pdf), __float_as_uint(packed.weight));
     if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, diffuse, specular, g.enable_restir_di == 1u, a.diffuse, a.specular, a.diffuse_f32);   // imageStore outside the image is discarded
     flush_ray_stats(a.stat_rays, a.stat_hits, rays, hits);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Wavefront form of K9 (numPrimaryBrdfSamples <= 1, the reference's setting): the BRDF ray and the one or two
+// visibility rays go through the shared ray-queue kernel; the sampler state (reservoir, chosen light sample, RNG
+// position: 80 bytes) is parked in five uint4 planes between the stages.
+//   A  local-light RIS + BRDF direction          -> ray queue
+//   B  BRDF hit -> light, combine                -> initial-visibility ray (if enabled, else final-visibility ray)
+//   C  apply initial visibility                  -> final-visibility ray          (only if initial visibility is on)
+//   D  apply final visibility, shade, store
+// ------------------------------------------------------------------------------------------------
+struct DIWaveArgs {
+    DIArgs di;
+    float4 *st_ray0, *st_ray1; float4* st_hit; const uint32_t* st_hit_inst;
+    uint4* state; uint32_t plane;          // 5 planes of `plane` uint4 each
+    uint32_t* queue; uint32_t* count;
+};
+__device__ __forceinline__ void di_state_store(const DIWaveArgs& w, uint32_t slot, const DIReservoir& r, const LightSample& ls, uint32_t rng_index, uint32_t flags) {
+    w.state[slot] = make_uint4(r.light_data, r.uv_data, __float_as_uint(r.weight_sum), __float_as_uint(r.target_pdf));
+    w.state[(size_t)w.plane + slot] = make_uint4(__float_as_uint(r.M), r.packed_visibility, (uint32_t)r.sdx, (uint32_t)r.sdy);
+    w.state[2 * (size_t)w.plane + slot] = make_uint4(r.age, rng_index, flags, ls.light_type);
+    w.state[3 * (size_t)w.plane + slot] = make_uint4(__float_as_uint(ls.position.x), __float_as_uint(ls.position.y), __float_as_uint(ls.position.z), __float_as_uint(ls.solid_angle_pdf));
+    w.state[4 * (size_t)w.plane + slot] = make_uint4(__float_as_uint(ls.radiance.x), __float_as_uint(ls.radiance.y), __float_as_uint(ls.radiance.z), 0u);
+}
+__device__ __forceinline__ void di_state_load(const DIWaveArgs& w, uint32_t slot, DIReservoir* r, LightSample* ls, uint32_t* rng_index, uint32_t* flags) {
+    const uint4 a = w.state[slot], b = w.state[(size_t)w.plane + slot], c = w.state[2 * (size_t)w.plane + slot];
+    const uint4 d = w.state[3 * (size_t)w.plane + slot], e = w.state[4 * (size_t)w.plane + slot];
+    r->light_data = a.x; r->uv_data = a.y; r->weight_sum = __uint_as_float(a.z); r->target_pdf = __uint_as_float(a.w);
+    r->M = __uint_as_float(b.x); r->packed_visibility = b.y; r->sdx = (int)b.z; r->sdy = (int)b.w;
+    r->age = c.x; *rng_index = c.y; *flags = c.z;
+    *ls = empty_light_sample();                                        // the normal is not needed past sample_polymorphic_light
+    ls->light_type = c.w;
+    ls->position = v3(__uint_as_float(d.x), __uint_as_float(d.y), __uint_as_float(d.z)); ls->solid_angle_pdf = __uint_as_float(d.w);
+    ls->radiance = v3(__uint_as_float(e.x), __uint_as_float(e.y), __uint_as_float(e.z));
+}
+__device__ __forceinline__ SampleParams di_sample_params(const rt2_restirdi_params& di) {
+    return init_sample_params(di.initial_sampling_params.num_primary_local_light_samples, di.initial_sampling_params.num_primary_infinite_light_samples,
+                              di.initial_sampling_params.num_primary_environment_samples, di.initial_sampling_params.num_primary_brdf_samples,
+                              di.initial_sampling_params.brdf_cutoff, 0.001f);
+}
+// setupVisibilityRay, bridge :191-218
+__device__ __forceinline__ void write_visibility_ray(const DIWaveArgs& w, uint32_t slot, const Surface& s, V3 sample_position, float offset) {
+    const V3 L = sample_position - s.world_pos;
+    const float tmax = fmaxf(offset, length3(L) - offset * 2);
+    const V3 d = normalize3(L);
+    w.st_ray0[slot] = make_float4(s.world_pos.x, s.world_pos.y, s.world_pos.z, offset);
+    w.st_ray1[slot] = make_float4(d.x, d.y, d.z, tmax);
+}
+#define DIW_BRDF_SAMPLED 1u
+#define DIW_RAY_PENDING 2u
+
+__global__ void __launch_bounds__(128) k_di_stage_a(DIWaveArgs w) {
+    const DIArgs& a = w.di;
+    uint32_t lx, ly;
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    bool traced = false;
+    uint32_t slot = 0;
+    if (inside) {
+        slot = ly * a.width + lx;
+        const rt2_gconst& g = *a.g;
+        uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+        Rng rng = rng_init(px, py, a.frame, 1u);
+        const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+        const SampleParams sp = di_sample_params(g.restir_di);
+        LightSample local_sample; DIReservoir local_reservoir;
+        sl_local_lights(a.li, g, rng, surface, sp, &local_reservoir, &local_sample);
+        uint32_t flags = 0u;
+        if (sp.num_brdf != 0u) {
+            const BrdfProbe p = sl_brdf_ray(surface, rng, sp);
+            if (p.sampled) {
+                flags |= DIW_BRDF_SAMPLED;
+                w.st_ray0[slot] = make_float4(surface.world_pos.x, surface.world_pos.y, surface.world_pos.z, sp.brdf_ray_min_t);
+                w.st_ray1[slot] = make_float4(p.dir.x, p.dir.y, p.dir.z, p.max_distance);
+                traced = true;
+            }
+        }
+        di_state_store(w, slot, local_reservoir, local_sample, rng.index, flags);
+    }
+    warp_append(traced, slot, w.queue, w.count);
+}
+
+// B: finish the sampler; queue the first visibility ray that is due
+__global__ void __launch_bounds__(128) k_di_stage_b(DIWaveArgs w, uint32_t* queue_out, uint32_t* count_out) {
+    const DIArgs& a = w.di;
+    uint32_t lx, ly;
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    bool traced = false;
+    uint32_t slot = 0, hits = 0;
+    if (inside) {
+        slot = ly * a.width + lx;
+        const rt2_gconst& g = *a.g;
+        const rt2_restirdi_params& di = g.restir_di;
+        uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+        const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+        const SampleParams sp = di_sample_params(di);
+        DIReservoir local_reservoir; LightSample local_sample; uint32_t flags;
+        Rng rng = rng_init(px, py, a.frame, 1u);
+        di_state_load(w, slot, &local_reservoir, &local_sample, &rng.index, &flags);
+        LightSample brdf_sample = empty_light_sample();
+        DIReservoir brdf_reservoir = empty_di_reservoir();
+        if (sp.num_brdf != 0u) {
+            const bool sampled = (flags & DIW_BRDF_SAMPLED) != 0u;
+            uint32_t geom = 0xFFFFFFFFu, prim = 0xFFFFFFFFu; float hu = 0.f, hv = 0.f;
+            if (sampled) {
+                const float4 h = w.st_hit[slot];
+                const uint32_t tri_slot = __float_as_uint(h.w);
+                if (tri_slot != 0xFFFFFFFFu) {
+                    hits++;
+                    const TriPos* tp = a.sc.tris + tri_slot;
+                    geom = f2u(ld16f(&tp->v0).w); prim = f2u(ld16f(&tp->v1).w); hu = h.y; hv = h.z;
+                }
+            }
+            sl_brdf_hit(a.li, rng, surface, sp, sampled, geom, prim, hu, hv, &brdf_reservoir, &brdf_sample);
+        }
+        LightSample light_sample;
+        DIReservoir reservoir = sl_combine(rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, &light_sample);
+        flags = 0u;
+        if (di_valid(reservoir)) {
+            if (di.initial_sampling_params.enable_initial_visibility == 1u) { write_visibility_ray(w, slot, surface, light_sample.position, 0.001f); traced = true; }
+            else if (!(light_sample.solid_angle_pdf <= 0) && di.shading_params.enable_final_visibility == 1u) { write_visibility_ray(w, slot, surface, light_sample.position, 0.01f); traced = true; }
+        }
+        if (traced) flags |= DIW_RAY_PENDING;
+        di_state_store(w, slot, reservoir, light_sample, rng.index, flags);
+    }
+    warp_append(traced, slot, queue_out, count_out);
+    flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
+}
+
+// C (only when initial visibility is on): di_fused_resampling.rgen:42-48, then queue the final-visibility ray
+__global__ void __launch_bounds__(128) k_di_stage_c(DIWaveArgs w, uint32_t* queue_out, uint32_t* count_out) {
+    const DIArgs& a = w.di;
+    uint32_t lx, ly;
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    bool traced = false;
+    uint32_t slot = 0, hits = 0;
+    if (inside) {
+        slot = ly * a.width + lx;
+        const rt2_gconst& g = *a.g;
+        const rt2_restirdi_params& di = g.restir_di;
+        uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+        DIReservoir reservoir; LightSample light_sample; uint32_t flags, rng_index;
+        di_state_load(w, slot, &reservoir, &light_sample, &rng_index, &flags);
+        if (flags & DIW_RAY_PENDING) {
+            if (__float_as_uint(w.st_hit[slot].w) != 0xFFFFFFFFu) { hits++; di_store_visibility(reservoir, v3(0.f, 0.f, 0.f), true); }
+        }
+        flags = 0u;
+        if (di_valid(reservoir) && !(light_sample.solid_angle_pdf <= 0) && di.shading_params.enable_final_visibility == 1u) {
+            const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+            write_visibility_ray(w, slot, surface, light_sample.position, 0.01f);
+            traced = true; flags |= DIW_RAY_PENDING;
+        }
+        di_state_store(w, slot, reservoir, light_sample, rng_index, flags);
+    }
+    warp_append(traced, slot, queue_out, count_out);
+    flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
+}
+
+// D: ShadeSurfaceWithLightSample with the traced final visibility, DemodulateSpecular, stores (di_fused_resampling.rgen:50-92)
+__global__ void __launch_bounds__(128) k_di_stage_d(DIWaveArgs w, uint32_t final_ray_was_queued) {
+    const DIArgs& a = w.di;
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const uint32_t slot = ly * a.width + lx;
+    const rt2_gconst& g = *a.g;
+    const rt2_restirdi_params& di = g.restir_di;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    uint32_t hits = 0;
+    DIReservoir reservoir; LightSample light_sample; uint32_t flags, rng_index;
+    di_state_load(w, slot, &reservoir, &light_sample, &rng_index, &flags);
+    const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+    V3 diffuse = v3(0.f, 0.f, 0.f), specular = v3(0.f, 0.f, 0.f);
+    if (di_valid(reservoir)) {
+        if (!(light_sample.solid_angle_pdf <= 0)) {
+            if (di.shading_params.enable_final_visibility == 1u) {
+                const bool vis = !(final_ray_was_queued && (flags & DIW_RAY_PENDING) && __float_as_uint(w.st_hit[slot].w) != 0xFFFFFFFFu);
+                if (!vis) hits++;
+                const V3 visibility = vis ? v3(1.f, 1.f, 1.f) : v3(0.f, 0.f, 0.f);
+                di_store_visibility(reservoir, visibility, di.temporal_resampling_params.discard_invisible_samples == 1u);
+                light_sample.radiance = light_sample.radiance * visibility;
+            }
+            light_sample.radiance = light_sample.radiance * (reservoir.weight_sum / light_sample.solid_angle_pdf);
+            if (light_sample.radiance.x > 0.0f || light_sample.radiance.y > 0.0f || light_sample.radiance.z > 0.0f) {
+                const SplitBrdf brdf = evaluate_brdf(surface, light_sample.position);
+                diffuse = light_sample.radiance * brdf.demodulated_diffuse;
+                specular = brdf.specular * light_sample.radiance;
+            }
+        }
+        specular = demodulate_specular(surface.specular_f0, specular);
+    }
+    const uint32_t ptr = reservoir_pointer(di.reservoir_buffer_params.reservoir_block_row_pitch, di.reservoir_buffer_params.reservoir_array_pitch, lx, ly,
+                                           di.buffer_indices.shading_input_buffer_index);
+    const rt2_packed_di_reservoir packed = pack_di_reservoir(reservoir);
+    uint2* dst = reinterpret_cast<uint2*>(a.reservoirs + ptr);
+    dst[0] = make_uint2(packed.light_data, packed.uv_data); dst[1] = make_uint2(packed.m_visibility, packed.distance_age);
+    dst[2] = make_uint2(__float_as_uint(packed.target_pdf), __float_as_uint(packed.weight));
+    if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, diffuse, specular, g.enable_restir_di == 1u, a.diffuse, a.specular, a.diffuse_f32);
+    flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -908,11 +1131,11 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     int rc = restir_ensure_resources(ctx); if (rc) return rc;
     FrameBuffers& f = ctx->fb;
     // counters: [0..1] rays, [2..3] hits
-    if (f.counter_capacity < 8) {
+    if (f.counter_capacity < 16) {
         if (f.counters) { RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(f.counters); f.counters = nullptr; }
-        RT2_CUDA(ctx, cudaMalloc((void**)&f.counters, 8 * 4)); f.counter_capacity = 8;
+        RT2_CUDA(ctx, cudaMalloc((void**)&f.counters, 16 * 4)); f.counter_capacity = 16;
     }
-    RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, 32, ctx->stream));
+    RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, 64, ctx->stream));
     unsigned long long* stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
     unsigned long long* stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
     const uint32_t cur = frame & 1u;                   // ping-pong, src/light_passes.rs:565-577
@@ -980,7 +1203,29 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         da.gb = gbrefs; da.li = lrefs;
         da.reservoirs = f.di_reservoirs; da.diffuse = f.diffuse_f16; da.specular = f.specular_f16; da.diffuse_f32 = f.diffuse_f32;
         da.stat_rays = stat_rays; da.stat_hits = stat_hits;
-        k_di_fused<<<blocks, 128, 0, ctx->stream>>>(da); launches++;
+        if (ctx->gi_megakernels || g.restir_di.initial_sampling_params.num_primary_brdf_samples > 1u) {
+            k_di_fused<<<blocks, 128, 0, ctx->stream>>>(da); launches++;
+        } else {
+            // counters: [8],[9] BRDF rays, [10],[11] first visibility stage, [12],[13] second
+            DIWaveArgs dw{};
+            dw.di = da; dw.st_ray0 = f.st_ray0; dw.st_ray1 = f.st_ray1; dw.st_hit = f.st_hit; dw.st_hit_inst = f.st_hit_inst;
+            dw.state = f.di_state; dw.plane = (uint32_t)((size_t)f.width * f.height);
+            dw.queue = f.queue0; dw.count = f.counters + 8;
+            const bool initial_vis = g.restir_di.initial_sampling_params.enable_initial_visibility == 1u;
+            const bool final_vis = g.restir_di.shading_params.enable_final_visibility == 1u;
+            k_di_stage_a<<<blocks, 128, 0, ctx->stream>>>(dw); launches++;
+            if (g.restir_di.initial_sampling_params.num_primary_brdf_samples != 0u) {
+                if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 8, f.counters + 9, stat_rays))) return rc;
+                launches++;
+            }
+            k_di_stage_b<<<blocks, 128, 0, ctx->stream>>>(dw, f.queue1, f.counters + 10); launches++;
+            if (initial_vis || final_vis) { if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 10, f.counters + 11, stat_rays))) return rc; launches++; }
+            if (initial_vis) {
+                k_di_stage_c<<<blocks, 128, 0, ctx->stream>>>(dw, f.queue0, f.counters + 12); launches++;
+                if (final_vis) { if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 12, f.counters + 13, stat_rays))) return rc; launches++; }
+            }
+            k_di_stage_d<<<blocks, 128, 0, ctx->stream>>>(dw, final_vis ? 1u : 0u); launches++;
+        }
     }
     // ---- K4 -> K5 -> K8 (stream order is the ALL_COMMANDS barrier of src/light_passes.rs:621-659)
     if (g.enable_restir_gi == 1u) {
