@@ -301,6 +301,7 @@ struct DIWaveArgs {
     DIArgs di;
     float4 *st_ray0, *st_ray1; float4* st_hit; const uint32_t* st_hit_inst;
     uint4* state; uint32_t plane;          // 5 planes of `plane` uint4 each
+    const uint4* secondary;                // K5 (DI on): sample at the secondary surface instead of the G-buffer surface
     uint32_t* queue; uint32_t* count;
 };
 __device__ __forceinline__ void di_state_store(const DIWaveArgs& w, uint32_t slot, const DIReservoir& r, const LightSample& ls, uint32_t rng_index, uint32_t flags) {
@@ -336,7 +337,42 @@ __device__ __forceinline__ void write_visibility_ray(const DIWaveArgs& w, uint32
 }
 #define DIW_BRDF_SAMPLED 1u
 #define DIW_RAY_PENDING 2u
+#define DIW_ACTIVE 4u
 
+// The surface a stage works on.  SEC = false: K9, the G-buffer surface of the pixel.  SEC = true: K5 with DI on
+// (shade_secondary_surfaces.rgen:48-64), the secondary surface unpacked from SecondaryGBufferData; only valid,
+// non-environment secondary surfaces sample lights.
+template <bool SEC>
+__device__ __forceinline__ Surface di_stage_surface(const DIWaveArgs& w, const rt2_gconst& g, uint32_t lx, uint32_t ly, uint32_t px, uint32_t py, bool* active) {
+    const DIArgs& a = w.di;
+    if (!SEC) { *active = true; return gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view); }
+    const uint32_t gbuffer_index = reservoir_pointer(g.restir_di.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_di.reservoir_buffer_params.reservoir_array_pitch, lx, ly, 0u);
+    const uint4* sgp = w.secondary + 3 * (size_t)gbuffer_index;
+    const uint4 s0 = sgp[0], s1 = sgp[1];
+    const float tx = f16_bits_to_f32((uint16_t)(s1.x & 0xffffu)), ty = f16_bits_to_f32((uint16_t)(s1.x >> 16)), tz = f16_bits_to_f32((uint16_t)(s1.y & 0xffffu));
+    const uint32_t flags = s1.y >> 16;
+    *active = (tx != 0 || ty != 0 || tz != 0) && (flags & RT2_SECONDARY_IS_ENVIRONMENT) == 0u;
+    Surface sec = empty_surface();
+    if (!*active) return sec;
+    const Surface primary = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+    sec.world_pos = v3(__uint_as_float(s0.x), __uint_as_float(s0.y), __uint_as_float(s0.z));
+    sec.view_depth = 1.0f;
+    sec.normal = oct_to_ndir_unorm32(s0.w);
+    sec.geo_normal = sec.normal;
+    sec.diffuse_albedo = unpack_r11g11b10(s1.z);
+    const float4 sr = unpack_rgba8_gamma(s1.w);
+    sec.specular_f0 = v3(sr.x, sr.y, sr.z);
+    sec.roughness = sr.w;
+    sec.diffuse_probability = 1.0f;
+    sec.view_dir = normalize3(primary.world_pos - sec.world_pos);
+    return sec;
+}
+template <bool SEC>
+__device__ __forceinline__ SampleParams di_stage_params(const rt2_restirdi_params& di) {
+    return SEC ? init_sample_params(0u, 0u, 0u, 1u, 0.f, 0.001f) : di_sample_params(di);
+}
+
+template <bool SEC>
 __global__ void __launch_bounds__(128) k_di_stage_a(DIWaveArgs w) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
@@ -347,13 +383,14 @@ __global__ void __launch_bounds__(128) k_di_stage_a(DIWaveArgs w) {
         slot = ly * a.width + lx;
         const rt2_gconst& g = *a.g;
         uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
-        Rng rng = rng_init(px, py, a.frame, 1u);
-        const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
-        const SampleParams sp = di_sample_params(g.restir_di);
-        LightSample local_sample; DIReservoir local_reservoir;
-        sl_local_lights(a.li, g, rng, surface, sp, &local_reservoir, &local_sample);
-        uint32_t flags = 0u;
-        if (sp.num_brdf != 0u) {
+        Rng rng = SEC ? rng_init(lx, ly, a.frame, 6u) : rng_init(px, py, a.frame, 1u);
+        bool active;
+        const Surface surface = di_stage_surface<SEC>(w, g, lx, ly, px, py, &active);
+        const SampleParams sp = di_stage_params<SEC>(g.restir_di);
+        LightSample local_sample = empty_light_sample(); DIReservoir local_reservoir = empty_di_reservoir();
+        if (active) sl_local_lights(a.li, g, rng, surface, sp, &local_reservoir, &local_sample);
+        uint32_t flags = active ? DIW_ACTIVE : 0u;
+        if (active && sp.num_brdf != 0u) {
             const BrdfProbe p = sl_brdf_ray(surface, rng, sp);
             if (p.sampled) {
                 flags |= DIW_BRDF_SAMPLED;
@@ -368,6 +405,7 @@ __global__ void __launch_bounds__(128) k_di_stage_a(DIWaveArgs w) {
 }
 
 // B: finish the sampler; queue the first visibility ray that is due
+template <bool SEC>
 __global__ void __launch_bounds__(128) k_di_stage_b(DIWaveArgs w, uint32_t* queue_out, uint32_t* count_out) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
@@ -379,11 +417,13 @@ __global__ void __launch_bounds__(128) k_di_stage_b(DIWaveArgs w, uint32_t* queu
         const rt2_gconst& g = *a.g;
         const rt2_restirdi_params& di = g.restir_di;
         uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
-        const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
-        const SampleParams sp = di_sample_params(di);
+        bool active;
+        const Surface surface = di_stage_surface<SEC>(w, g, lx, ly, px, py, &active);
+        const SampleParams sp = di_stage_params<SEC>(di);
         DIReservoir local_reservoir; LightSample local_sample; uint32_t flags;
-        Rng rng = rng_init(px, py, a.frame, 1u);
+        Rng rng = SEC ? rng_init(lx, ly, a.frame, 6u) : rng_init(px, py, a.frame, 1u);
         di_state_load(w, slot, &local_reservoir, &local_sample, &rng.index, &flags);
+        if (active) {
         LightSample brdf_sample = empty_light_sample();
         DIReservoir brdf_reservoir = empty_di_reservoir();
         if (sp.num_brdf != 0u) {
@@ -402,13 +442,15 @@ __global__ void __launch_bounds__(128) k_di_stage_b(DIWaveArgs w, uint32_t* queu
         }
         LightSample light_sample;
         DIReservoir reservoir = sl_combine(rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, &light_sample);
-        flags = 0u;
-        if (di_valid(reservoir)) {
-            if (di.initial_sampling_params.enable_initial_visibility == 1u) { write_visibility_ray(w, slot, surface, light_sample.position, 0.001f); traced = true; }
+        flags = DIW_ACTIVE;
+        // K9 runs the initial-visibility test of di_fused_resampling.rgen:42-48 first; K5 shades with enableVisibilityReuse false and has none
+        if (di_valid(reservoir) || SEC) {
+            if (!SEC && di.initial_sampling_params.enable_initial_visibility == 1u) { write_visibility_ray(w, slot, surface, light_sample.position, 0.001f); traced = true; }
             else if (!(light_sample.solid_angle_pdf <= 0) && di.shading_params.enable_final_visibility == 1u) { write_visibility_ray(w, slot, surface, light_sample.position, 0.01f); traced = true; }
         }
         if (traced) flags |= DIW_RAY_PENDING;
         di_state_store(w, slot, reservoir, light_sample, rng.index, flags);
+        }
     }
     warp_append(traced, slot, queue_out, count_out);
     flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
@@ -931,6 +973,70 @@ __global__ void __launch_bounds__(128) k_shade_secondary_shade(GIWaveArgs w) {
     flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
 }
 
+// K5 with DI on, last stage (shade_secondary_surfaces.rgen:105-156): shade the secondary surface with the sampled light
+// (visibility from the ray-queue kernel), firefly clamp, initial GI reservoir, MIS radiance hand-over.
+__global__ void __launch_bounds__(128) k_shade_secondary_stage_d(DIWaveArgs w, GIArgs a) {
+    uint32_t lx, ly;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    const uint32_t slot = ly * a.width + lx;
+    const rt2_gconst& g = *a.g;
+    const rt2_restirdi_params& di = g.restir_di;
+    uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
+    uint32_t hits = 0;
+    const uint32_t gbuffer_index = reservoir_pointer(di.reservoir_buffer_params.reservoir_block_row_pitch, di.reservoir_buffer_params.reservoir_array_pitch, lx, ly, 0u);
+    uint4* sgp = a.secondary + 3 * (size_t)gbuffer_index;
+    const uint4 s0 = sgp[0], s1 = sgp[1], s2 = sgp[2];
+    const V3 throughput = unpack_half3(s1.x, s1.y);
+    const uint32_t sflags = s1.y >> 16;
+    const bool valid_secondary = throughput.x != 0 || throughput.y != 0 || throughput.z != 0;
+    const bool is_specular_ray = (sflags & RT2_SECONDARY_IS_SPECULAR_RAY) != 0u;
+    const bool is_delta = (sflags & RT2_SECONDARY_IS_DELTA_SURFACE) != 0u;
+    V3 radiance = v3(__uint_as_float(s2.x), __uint_as_float(s2.y), __uint_as_float(s2.z));
+    const float pdf = __uint_as_float(s2.w);
+    const V3 sec_world_pos = v3(__uint_as_float(s0.x), __uint_as_float(s0.y), __uint_as_float(s0.z));
+    const V3 sec_normal = oct_to_ndir_unorm32(s0.w);
+    DIReservoir reservoir; LightSample light_sample; uint32_t flags, rng_index;
+    di_state_load(w, slot, &reservoir, &light_sample, &rng_index, &flags);
+    if (flags & DIW_ACTIVE) {
+        bool active;
+        const Surface sec = di_stage_surface<true>(w, g, lx, ly, px, py, &active);
+        V3 indirect_diffuse = v3(0.f, 0.f, 0.f), indirect_specular = v3(0.f, 0.f, 0.f);
+        if (!(light_sample.solid_angle_pdf <= 0)) {                    // ShadeSurfaceWithLightSample, ShadingHelpers.glsl:2-58
+            if (di.shading_params.enable_final_visibility == 1u) {
+                const bool vis = !((flags & DIW_RAY_PENDING) && __float_as_uint(w.st_hit[slot].w) != 0xFFFFFFFFu);
+                if (!vis) hits++;
+                const V3 visibility = vis ? v3(1.f, 1.f, 1.f) : v3(0.f, 0.f, 0.f);
+                di_store_visibility(reservoir, visibility, di.temporal_resampling_params.discard_invisible_samples == 1u);
+                light_sample.radiance = light_sample.radiance * visibility;
+            }
+            light_sample.radiance = light_sample.radiance * (reservoir.weight_sum / light_sample.solid_angle_pdf);
+            if (light_sample.radiance.x > 0.0f || light_sample.radiance.y > 0.0f || light_sample.radiance.z > 0.0f) {
+                const SplitBrdf brdf = evaluate_brdf(sec, light_sample.position);
+                indirect_diffuse = light_sample.radiance * brdf.demodulated_diffuse;
+                indirect_specular = brdf.specular * light_sample.radiance;
+            }
+        }
+        radiance = radiance + (indirect_diffuse * sec.diffuse_albedo + indirect_specular);
+        const float c_max_indirect_radiance = 100.0f;                  // firefly suppression, :113-116
+        const float lum = calc_luminance(radiance);
+        if (lum > c_max_indirect_radiance) radiance = radiance * (c_max_indirect_radiance / lum);
+    }
+    GIReservoir gi_reservoir = empty_gi_reservoir();
+    const bool output_shading_result = is_specular_ray && is_delta;
+    if (valid_secondary && !output_shading_result) gi_reservoir = make_gi_reservoir(sec_world_pos, sec_normal, radiance, pdf);
+    const uint32_t rx = g.runtime_params.active_checkerboard_field != 0u ? (px >> 1) : px;
+    store_gi_reservoir(a.reservoirs, reservoir_pointer(g.restir_gi.reservoir_buffer_params.reservoir_block_row_pitch, g.restir_gi.reservoir_buffer_params.reservoir_array_pitch,
+                                                       rx, py, g.restir_gi.buffer_indices.secondary_surface_restirdi_output_buffer_index), gi_reservoir, 0u);
+    const V3 saved = output_shading_result ? v3(0.f, 0.f, 0.f) : radiance;
+    sgp[2] = make_uint4(__float_as_uint(saved.x), __float_as_uint(saved.y), __float_as_uint(saved.z), s2.w);
+    if (output_shading_result) {
+        const Surface primary = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
+        const V3 specular = demodulate_specular(primary.specular_f0, radiance);
+        if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, v3(0.f, 0.f, 0.f), specular, false, a.diffuse, a.specular, a.diffuse_f32);
+    }
+    flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
+}
+
 // ------------------------------------------------------------------------------------------------
 // N2 — GI temporal (K6) and spatial (K7) resampling: lighting_passes/temporal_resampling.rgen,
 // spatial_resampling.rgen, rtxdi/GIResamplingFunctions.hlsli:186-553.  The first kernels with cross-pixel reads:
@@ -1213,12 +1319,12 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
             dw.queue = f.queue0; dw.count = f.counters + 8;
             const bool initial_vis = g.restir_di.initial_sampling_params.enable_initial_visibility == 1u;
             const bool final_vis = g.restir_di.shading_params.enable_final_visibility == 1u;
-            k_di_stage_a<<<blocks, 128, 0, ctx->stream>>>(dw); launches++;
+            k_di_stage_a<false><<<blocks, 128, 0, ctx->stream>>>(dw); launches++;
             if (g.restir_di.initial_sampling_params.num_primary_brdf_samples != 0u) {
                 if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 8, f.counters + 9, stat_rays))) return rc;
                 launches++;
             }
-            k_di_stage_b<<<blocks, 128, 0, ctx->stream>>>(dw, f.queue1, f.counters + 10); launches++;
+            k_di_stage_b<false><<<blocks, 128, 0, ctx->stream>>>(dw, f.queue1, f.counters + 10); launches++;
             if (initial_vis || final_vis) { if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 10, f.counters + 11, stat_rays))) return rc; launches++; }
             if (initial_vis) {
                 k_di_stage_c<<<blocks, 128, 0, ctx->stream>>>(dw, f.queue0, f.counters + 12); launches++;
@@ -1246,8 +1352,21 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
             k_brdf_rays_gen<<<blocks, 128, 0, ctx->stream>>>(wa);
             if ((rc = trace_queue_generic(ctx, wa.queue, wa.count, f.counters + 5, stat_rays))) return rc;
             k_brdf_rays_shade<<<blocks, 128, 0, ctx->stream>>>(wa); launches += 3;
-            if (g.enable_restir_di == 1u) {                            // K5 chains a BRDF ray and a visibility ray through the light sampler: stays one kernel
-                k_shade_secondary<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+            if (g.enable_restir_di == 1u) {                            // K5 samples the light list at the secondary surface: the K9 stages, pointed at SecondaryGBufferData
+                DIWaveArgs dw{};
+                dw.di.sc = gi.sc; dw.di.g = gi.g; dw.di.width = gi.width; dw.di.height = gi.height; dw.di.frame = gi.frame; dw.di.gb = gi.gb; dw.di.li = gi.li;
+                dw.di.stat_rays = stat_rays; dw.di.stat_hits = stat_hits;
+                dw.st_ray0 = f.st_ray0; dw.st_ray1 = f.st_ray1; dw.st_hit = f.st_hit; dw.st_hit_inst = f.st_hit_inst;
+                dw.state = f.di_state; dw.plane = (uint32_t)((size_t)f.width * f.height); dw.secondary = f.secondary_gbuffer;
+                dw.queue = f.queue1; dw.count = f.counters + 6;
+                k_di_stage_a<true><<<blocks, 128, 0, ctx->stream>>>(dw);
+                if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 6, f.counters + 7, stat_rays))) return rc;
+                k_di_stage_b<true><<<blocks, 128, 0, ctx->stream>>>(dw, f.queue0, f.counters + 14); launches += 3;
+                if (g.restir_di.shading_params.enable_final_visibility == 1u) {
+                    if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 14, f.counters + 15, stat_rays))) return rc;
+                    launches++;
+                }
+                k_shade_secondary_stage_d<<<blocks, 128, 0, ctx->stream>>>(dw, gi); launches++;
             } else {
                 wa.queue = f.queue1; wa.count = f.counters + 6;
                 k_shade_secondary_gen<<<blocks, 128, 0, ctx->stream>>>(wa);
