@@ -216,6 +216,8 @@ enum rt2_buffer {
     RT2_BUF_GI_RESERVOIRS   = 88,  /* 32 B x arrayPitch x 2                                        */
     RT2_BUF_SECONDARY_GBUFFER = 89, /* 48-byte rt2_secondary_gbuffer_data x arrayPitch, block-linear */
     RT2_BUF_NEIGHBOR_OFFSETS = 90,  /* K7 neighbour-offset table: RT2_NEIGHBOR_OFFSET_COUNT signed byte pairs */
+    RT2_BUF_RIS = 91,               /* K11: uint2 per RIS entry (light index | COMPACT bit or packed uv, asuint(1/pdf)) */
+    RT2_BUF_RIS_LIGHT_DATA = 92,    /* K11: two uint4 per RIS entry, the compact light record (PolymorphicLight.glsl:95-112) */
     /* acceleration-structure introspection (tests / tools) */
     RT2_BUF_BLAS_NODES = 100,      /* 80-byte CWBVH nodes                                          */
     RT2_BUF_BLAS_TRIS = 101,       /* 48-byte leaf triangles in slot order                         */
@@ -271,6 +273,10 @@ int  rt2_prepare_lights(rt2_ctx* ctx);
 /* GenerateMipsPass::execute_mip_generation (src/mip_pass.rs:122-186) + generate_mip_levels/mips.glsl
  * (K12).  which: 0 = local-light PDF texture, 1 = environment PDF texture. */
 int  rt2_generate_mips(rt2_ctx* ctx, int which);
+/* LightPasses::execute_presampeling (src/light_passes.rs:510-548) + lighting_passes/presample_{locallights,environment}.comp
+ * (K11): 128 tiles x 1024 samples drawn through the PDF mip pyramid into the RIS buffer.  which: 0 = local lights (after
+ * rt2_prepare_lights + rt2_generate_mips(0)), 1 = environment map (after rt2_generate_mips(1)).  `frame` seeds the sampler. */
+int  rt2_presample(rt2_ctx* ctx, uint32_t frame, int which);
 /* LightPasses::execute (src/light_passes.rs:550-663).  `frame` is the push constant
  * (light_passes.rs:581-585: low 32 bits of the u64 frame counter, first frame = 1).  Dispatches on
  * GConst.refrence_mode / enable_restir_di / enable_restir_gi exactly like the reference. */

@@ -69,6 +69,7 @@ def lib():
         L.orc_gi_spatial_resampling.restype = C.c_int
         L.orc_gi_spatial_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int, VP, VP, u32, VP, C.POINTER(u64)]
         L.orc_fill_neighbor_offset_buffer.restype = None; L.orc_fill_neighbor_offset_buffer.argtypes = [u32, VP]
+        L.orc_presample.restype = C.c_int; L.orc_presample.argtypes = [VP, u32, C.c_int, VP, u32, u32, u32, VP, u32, VP, VP]
         L.orc_encode_logluv.restype = u32; L.orc_encode_logluv.argtypes = [VP]
         L.orc_decode_logluv.restype = None; L.orc_decode_logluv.argtypes = [u32, VP]
         L.orc_encode_snorm_oct.restype = u32; L.orc_encode_snorm_oct.argtypes = [VP]
@@ -103,6 +104,19 @@ class GBufferIn(C.Structure):   # orc_gbuffer_in
 
 class LightIn(C.Structure):     # orc_light_in
     _fields_ = [("lights", VP), ("num_lights", u32), ("geom_to_light", VP), ("pdf_packed", VP), ("pdf_w", u32), ("pdf_h", u32), ("pdf_mips", u32)]
+
+
+def presample(gconst, frame, which, pdf_packed, w, h, mips, lights=None, ris=None, ris_light_data=None, entries=2 * 128 * 1024):
+    """K11.  Returns (ris uint32 [entries, 2], ris_light_data uint32 [entries, 8]); pass the arrays back in to fill the other segment."""
+    ris = np.zeros((entries, 2), np.uint32) if ris is None else ris
+    data = np.zeros((entries, 8), np.uint32) if ris_light_data is None else ris_light_data
+    pdf = np.ascontiguousarray(pdf_packed)
+    li = np.ascontiguousarray(lights) if lights is not None else None
+    rc = lib().orc_presample(C.cast(C.byref(gconst), VP), frame, which, pdf.ctypes.data_as(VP), w, h, mips,
+                             li.ctypes.data_as(VP) if li is not None else None, len(li) if li is not None else 0,
+                             ris.ctypes.data_as(VP), data.ctypes.data_as(VP))
+    assert rc == 0, rc
+    return ris, data
 
 
 def fill_neighbor_offset_buffer(count=8192):

@@ -134,6 +134,11 @@ int orc_gi_spatial_resampling(const orc_scene* s, const void* gconst, uint32_t f
                               rt2_packed_gi_reservoir* gi_reservoirs, uint64_t* rays);
 /* fill_neighbor_offset_buffer (src/light_passes.rs:671-698) with signed bytes; xy holds 2 * count bytes */
 void orc_fill_neighbor_offset_buffer(uint32_t neighbor_offset_count, int8_t* xy);
+/* K11 lighting_passes/presample_{locallights,environment}.comp + rtxdi/PresamplingFunctions.hlsli:30-162.  which 0: local
+ * lights (pdf_packed = r32f pyramid), 1: environment (r16f pyramid).  ris: uint2 per entry, both segments; ris_light_data:
+ * 2 x uvec4 per entry (local lights only).  Writes the reference's fixed 128 x 1024 grid. */
+int orc_presample(const void* gconst, uint32_t frame, int which, const void* pdf_packed, uint32_t w, uint32_t h, uint32_t mips,
+                  const rt2_light_info* lights, uint32_t num_lights, uint32_t* ris, uint32_t* ris_light_data);
 /* KAT probes: rtxdi/RtxdiMath.hlsli:129-296 */
 uint32_t orc_encode_logluv(const float rgb[3]);
 void orc_decode_logluv(uint32_t packed, float rgb[3]);

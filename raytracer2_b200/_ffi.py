@@ -202,6 +202,7 @@ ABI_SYMBOLS = {
     "rt2_set_constants": (C.c_int, [VP, VP, C.c_size_t]),
     "rt2_prepare_lights": (C.c_int, [VP]),
     "rt2_generate_mips": (C.c_int, [VP, C.c_int]),
+    "rt2_presample": (C.c_int, [VP, u32, C.c_int]),
     "rt2_render": (C.c_int, [VP, u32, C.POINTER(LaunchParams)]),
     "rt2_trace_primary": (C.c_int, [VP, C.POINTER(LaunchParams)]),
     "rt2_postprocess": (C.c_int, [VP, u32]),

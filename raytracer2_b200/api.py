@@ -27,6 +27,7 @@ BUF_GBUFFER_DEPTH, BUF_GBUFFER_NORMALS, BUF_GBUFFER_GEO_NORMALS = 80, 81, 82
 BUF_GBUFFER_DIFFUSE_ALBEDO, BUF_GBUFFER_SPECULAR_ROUGH, BUF_GBUFFER_EMISSIVE = 83, 84, 85
 BUF_MOTION_VECTORS, BUF_DI_RESERVOIRS, BUF_GI_RESERVOIRS, BUF_SECONDARY_GBUFFER = 86, 87, 88, 89
 BUF_NEIGHBOR_OFFSETS = 90
+BUF_RIS, BUF_RIS_LIGHT_DATA = 91, 92
 
 BUF_BLAS_NODES, BUF_BLAS_TRIS, BUF_BLAS_SLOT_TO_PRIM, BUF_TLAS_NODES, BUF_TLAS_SLOT_TO_INST = 100, 101, 102, 103, 104
 
@@ -188,6 +189,15 @@ class LightPasses:
     def execute(self, frame: int, params: LaunchParams | None = None):
         p = C.byref(params) if params is not None else None
         self.ctx._check(self.ctx._lib.rt2_render(self.ctx._ctx, frame & 0xFFFFFFFF, p), "rt2_render")
+
+    def execute_presampeling(self, frame: int, skybox_changed: bool) -> bool:
+        """src/light_passes.rs:510-548 (K11, spelling as in the reference): local-light presampling every frame, the
+        environment map only when the sky box changed; returns the reference's `skybox_dirty` follow-up value."""
+        self.ctx._check(self.ctx._lib.rt2_presample(self.ctx._ctx, frame & 0xFFFFFFFF, 0), "rt2_presample")
+        if skybox_changed:
+            self.ctx._check(self.ctx._lib.rt2_presample(self.ctx._ctx, frame & 0xFFFFFFFF, 1), "rt2_presample")
+            return False
+        return True
 
     def trace_primary(self, params: LaunchParams | None = None):
         p = C.byref(params) if params is not None else None

@@ -23,6 +23,7 @@ int post_process(rt2_ctx* ctx, uint32_t frame);
 void passes_release(rt2_ctx* ctx);          // everything the passes own
 void passes_release_frame(rt2_ctx* ctx);    // per-size resources only
 void lights_release(rt2_ctx* ctx);          // per-scene light resources
+int presample(rt2_ctx* ctx, uint32_t frame, int which);
 int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp);
 bool pass_buffer(rt2_ctx* ctx, int which, void** ptr, size_t* bytes);
 }  // namespace rt2
@@ -105,6 +106,7 @@ int rt2_set_constants(rt2_ctx* ctx, const void* gconst, size_t nbytes) {
 int rt2_prepare_lights(rt2_ctx* ctx) { RT2_GUARD(ctx); return lights_prepare(ctx); }
 int rt2_generate_mips(rt2_ctx* ctx, int which) { RT2_GUARD(ctx); return mips_generate(ctx, which); }
 int rt2_postprocess(rt2_ctx* ctx, uint32_t frame) { RT2_GUARD(ctx); return post_process(ctx, frame); }
+int rt2_presample(rt2_ctx* ctx, uint32_t frame, int which) { RT2_GUARD(ctx); return presample(ctx, frame, which); }
 
 int rt2_render(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params* params) {
     RT2_GUARD(ctx);

@@ -140,6 +140,7 @@ struct rt2_ctx {
     bool lights_prepared = false;
     uint32_t last_gbuffer_index = 0;     // frame % 2 of the last ReSTIR-mode render: which G-buffer set rt2_read returns
     float* local_pdf = nullptr; uint32_t local_pdf_w = 0, local_pdf_h = 0, local_pdf_mips = 0;   // all mips, packed
+    uint2* ris_buffer = nullptr; uint4* ris_light_data = nullptr; uint64_t ris_entries = 0; uint32_t* presample_error = nullptr;   // K11 outputs
     uint16_t* env_pdf = nullptr; uint32_t env_pdf_w = 0, env_pdf_h = 0, env_pdf_mips = 0;        // r16f, packed mips
 };
 

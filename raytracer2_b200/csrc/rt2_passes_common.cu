@@ -97,6 +97,8 @@ bool pass_buffer(rt2_ctx* ctx, int which, void** ptr, size_t* bytes) {
         case RT2_BUF_MOTION_VECTORS: *ptr = f.motion_vectors; *bytes = n * 16; return f.motion_vectors != nullptr;
         case RT2_BUF_DI_RESERVOIRS: *ptr = f.di_reservoirs; *bytes = (size_t)f.reservoir_array_pitch * 2 * sizeof(rt2_packed_di_reservoir); return f.di_reservoirs != nullptr;
         case RT2_BUF_GI_RESERVOIRS: *ptr = f.gi_reservoirs; *bytes = (size_t)f.reservoir_array_pitch * 2 * 32; return f.gi_reservoirs != nullptr;
+        case RT2_BUF_RIS: *ptr = ctx->ris_buffer; *bytes = (size_t)ctx->ris_entries * 8; return ctx->ris_buffer != nullptr;
+        case RT2_BUF_RIS_LIGHT_DATA: *ptr = ctx->ris_light_data; *bytes = (size_t)ctx->ris_entries * 32; return ctx->ris_light_data != nullptr;
         case RT2_BUF_NEIGHBOR_OFFSETS: *ptr = f.neighbor_offsets; *bytes = (size_t)RT2_NEIGHBOR_OFFSET_COUNT * 2; return f.neighbor_offsets != nullptr;
         case RT2_BUF_SECONDARY_GBUFFER: *ptr = f.secondary_gbuffer; *bytes = (size_t)f.reservoir_array_pitch * 48; return f.secondary_gbuffer != nullptr;
         default: return false;

@@ -71,7 +71,9 @@ __global__ void __launch_bounds__(256) k_prepare_lights(const rt2_prepare_lights
     if (x < pdf_w && y < pdf_h) pdf_mip0[(size_t)y * pdf_w + x] = light_power(li);
 }
 
+void presample_release(rt2_ctx* ctx);
 void lights_release(rt2_ctx* ctx) {
+    presample_release(ctx);
     void* ptrs[] = {ctx->light_info, ctx->geom_to_light, ctx->light_tasks, ctx->local_pdf, ctx->env_pdf};
     for (void* p : ptrs) if (p) cudaFree(p);
     ctx->light_info = nullptr; ctx->geom_to_light = nullptr; ctx->light_tasks = nullptr; ctx->local_pdf = nullptr; ctx->env_pdf = nullptr;

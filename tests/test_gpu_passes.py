@@ -237,3 +237,58 @@ def test_di_needs_light_list():
     with pytest.raises(rt.Rt2Error):
         lp.execute(1)               # rt2_prepare_lights has not run
     ctx.close()
+
+
+# ---- K11 presampling ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind,scale", [(rt.SCENE_CORNELL, 1.0), (rt.SCENE_MANYLIGHT, 0.3), (rt.SCENE_MANYLIGHT, 1.0)])
+def test_presample_local_lights_bit_exact(kind, scale):
+    sc, ctx = _setup(kind, scale)
+    g = rt.default_gconst(sc.camera(16 / 9), 320, 180, sc.num_lights)
+    lp = rt.LightPasses(ctx, 320, 180)
+    lp.update_uniform(g)
+    rt.PrepareLightsTasks(ctx).execute()
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    assert lp.execute_presampeling(7, False) is True               # src/light_passes.rs:543-547
+    ris = ctx.read(rt.BUF_RIS, np.uint32).reshape(-1, 2)
+    data = ctx.read(rt.BUF_RIS_LIGHT_DATA, np.uint32).reshape(-1, 8)
+    pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
+    pdf = np.concatenate([m.ravel() for m in _read_mips(ctx, rt.BUF_LOCAL_PDF_MIP0, pw.value, ph.value, pm.value, np.float32)])
+    lights = ctx.read(rt.BUF_LIGHT_INFO, np.uint32).reshape(-1, 12)
+    rris, rdata = O.presample(g, 7, 0, pdf, pw.value, ph.value, pm.value, lights, entries=len(ris))
+    assert len(ris) == 128 * 1024
+    assert np.array_equal(ris, rris) and np.array_equal(data, rdata)
+    assert (ris[:, 1].view(np.float32) > 0).all()
+    ctx.close()
+
+
+def test_presample_environment_bit_exact():
+    sc, ctx = _setup(rt.SCENE_INSTANCED, 0.125)
+    d = sc.desc.contents
+    w, h = d.sky_width, d.sky_height
+    g = rt.default_gconst(sc.camera(16 / 9), 320, 180, sc.num_lights, env_size=(w, h))
+    lp = rt.LightPasses(ctx, 320, 180)
+    lp.update_uniform(g)
+    rt.PrepareLightsTasks(ctx).execute()
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.ENVIRONMENT).execute_mip_generation()
+    assert lp.execute_presampeling(2, True) is False
+    ris = ctx.read(rt.BUF_RIS, np.uint32).reshape(-1, 2)
+    mips = int(math.ceil(math.log2(max(w, h)))) + 1
+    env = np.concatenate([m.ravel() for m in _read_mips(ctx, rt.BUF_ENV_PDF_MIP0, w, h, mips, np.uint16)])
+    off = g.environment_light_risbuffer_segment_params.buffer_offset
+    rris, _ = O.presample(g, 2, 1, env, w, h, mips, entries=len(ris))
+    assert len(ris) == 2 * 128 * 1024
+    assert np.array_equal(ris[off:], rris[off:])
+    assert (ris[off:, 1].view(np.float32) > 0).all()
+    ctx.close()
+
+
+def test_presample_needs_its_inputs():
+    sc, ctx = _setup(rt.SCENE_CORNELL, 1.0)
+    g = rt.default_gconst(sc.camera(1.0), 64, 64, sc.num_lights)
+    lp = rt.LightPasses(ctx, 64, 64)
+    lp.update_uniform(g)
+    with pytest.raises(rt.Rt2Error):
+        lp.execute_presampeling(1, False)          # K10 / K12 have not run
+    ctx.close()

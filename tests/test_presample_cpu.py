@@ -1,0 +1,101 @@
+"""CPU checks of the oracle's K11 presampling (rtxdi/PresamplingFunctions.hlsli:30-162): the hierarchical descent through the
+PDF mip pyramid must draw light i with probability power_i / sum(power) and report exactly that probability's inverse."""
+import ctypes as C
+
+import numpy as np
+
+import raytracer2_b200 as rt
+from oracle import oracle_ffi as O
+
+
+def _local_inputs(kind, scale):
+    sc = rt.Scene(kind, scale, 16, 0)
+    g = rt.default_gconst(sc.camera(1.0), 64, 64, sc.num_lights)
+    osc = O.OracleScene(sc.desc)
+    pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
+    tasks, g2l, lights, pdf0 = osc.prepare_lights(pw.value, ph.value)
+    packed = np.zeros(sum(a * b for a, b in O.mip_dims(pw.value, ph.value, pm.value)), np.float32)
+    packed[:pw.value * ph.value] = pdf0.ravel()
+    osc.generate_mips(0, packed, pw.value, ph.value, pm.value)
+    return sc, g, lights, pdf0, packed, (pw.value, ph.value, pm.value)
+
+
+def test_local_light_presampling_follows_the_power_distribution():
+    sc, g, lights, pdf0, packed, (w, h, m) = _local_inputs(rt.SCENE_MANYLIGHT, 0.3)
+    assert g.local_lights_risbuffer_segment_params.tile_size == 1024 and g.local_lights_risbuffer_segment_params.tile_count == 128   # src/main.rs:305-310
+    ris, data = O.presample(g, 3, 0, packed, w, h, m, lights)
+    seg = ris[:128 * 1024]
+    idx = seg[:, 0]
+    inv = seg[:, 1].view(np.float32)
+    assert (idx >> 31 == 1).all()                                   # every K10 light packs compactly (no spot shaping)
+    li = idx & 0x7fffffff
+    n = len(lights)
+    assert li.max() < n and (inv > 0).all()
+    # light i sits at Z-curve texel i, whose mip-0 value is its power
+    L = O.lib()
+    power = np.zeros(n)
+    x, y = C.c_uint32(), C.c_uint32()
+    for i in range(n):
+        L.orc_linear_to_zcurve(i, C.byref(x), C.byref(y)); power[i] = pdf0[y.value, x.value]
+    p = power / power.sum()
+    # the reported inverse pdf is the product of the per-level choices == 1 / p_i (up to fp32 rounding through <= 13 levels)
+    assert np.allclose(1.0 / inv.astype(np.float64), p[li], rtol=2e-5)
+    # and the empirical histogram matches p (chi-square-ish bound on 131072 draws)
+    counts = np.bincount(li, minlength=n)
+    expect = p * len(li)
+    big = expect > 20
+    z = (counts[big] - expect[big]) / np.sqrt(expect[big])
+    assert np.abs(z).max() < 6 and abs(z.mean()) < 0.3
+    assert (counts[power == 0] == 0).all()
+    # the compact record is the light itself
+    sel = np.arange(0, len(seg), 997)
+    for k in sel:
+        assert np.array_equal(data[k, 0:3], lights[li[k], 0:3]) and data[k, 3] == lights[li[k], 3]
+        assert np.array_equal(data[k, 4:8], lights[li[k], 4:8])
+    # a different frame draws different samples; the same frame the same
+    ris2, _ = O.presample(g, 3, 0, packed, w, h, m, lights)
+    ris3, _ = O.presample(g, 4, 0, packed, w, h, m, lights)
+    assert np.array_equal(ris, ris2) and not np.array_equal(ris, ris3)
+    assert not ris[128 * 1024:].any()                               # the environment segment is untouched
+
+
+def test_single_light_and_empty_pyramids():
+    sc, g, lights, pdf0, packed, (w, h, m) = _local_inputs(rt.SCENE_CORNELL, 1.0)
+    ris, data = O.presample(g, 1, 0, packed, w, h, m, lights)
+    li = ris[:128 * 1024, 0] & 0x7fffffff
+    assert set(np.unique(li)) <= set(range(len(lights))) and len(lights) == sc.num_lights
+    # all-zero pyramid: nothing found -> (firstLightIndex, 0) entries, no compact bit
+    zero = np.zeros_like(packed)
+    ris0, _ = O.presample(g, 1, 0, zero, w, h, m, lights)
+    assert (ris0[:128 * 1024, 1] == 0).all() and (ris0[:128 * 1024, 0] >> 31 == 0).all()
+
+
+def test_environment_presampling_importance_samples_the_sky():
+    sc = rt.Scene(rt.SCENE_INSTANCED, 0.125, 16, 0)         # 512 x 256 sky: the descent doubles the position per level, so it needs a power-of-two pyramid
+    d = sc.desc.contents
+    w, h = d.sky_width, d.sky_height
+    assert (w, h) == (512, 256)
+    g = rt.default_gconst(sc.camera(1.0), 64, 64, sc.num_lights, env_size=(w, h))
+    osc = O.OracleScene(sc.desc)
+    import math
+    mips = int(math.ceil(math.log2(max(w, h)))) + 1
+    packed = np.zeros(sum(a * b for a, b in O.mip_dims(w, h, mips)), np.uint16)
+    osc.generate_mips(1, packed, w, h, mips)
+    ris, _ = O.presample(g, 2, 1, packed, w, h, mips)
+    off = g.environment_light_risbuffer_segment_params.buffer_offset
+    assert off == 128 * 1024 and not ris[:off].any()                # src/main.rs:299-304
+    seg = ris[off:off + 128 * 1024]
+    inv = seg[:, 1].view(np.float32)
+    assert (inv > 0).all()
+    u = (seg[:, 0] & 0xffff) / 65535.0; v = (seg[:, 0] >> 16) / 65535.0
+    tx = np.minimum((u * w).astype(int), w - 1); ty = np.minimum((v * h).astype(int), h - 1)
+    pdf0 = packed[:w * h].view(np.float16).astype(np.float64).reshape(h, w)
+    # texels are drawn in proportion to their mip-0 weight: compare row marginals (rows are wide enough to have counts)
+    rows = np.bincount(ty, minlength=h) / len(ty)
+    want = pdf0.sum(axis=1) / pdf0.sum()
+    assert np.abs(rows - want).max() < 0.01
+    # 1 / inv == texel probability (the pyramid is r16f, so only to half precision)
+    p = pdf0 / pdf0.sum()
+    rel = np.abs(1.0 / inv.astype(np.float64) - p[ty, tx]) / p[ty, tx]
+    assert np.median(rel) < 2e-3 and (rel < 0.03).mean() > 0.99      # uv is quantised to 16 bits: a sample on a texel edge can decode into the neighbour
