@@ -26,7 +26,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 W, H, SPP, BOUNCES = 1920, 1080, 4, 4
-BAND_ROWS = 16
+BAND_ROWS = 8
 TRIS = 262144
 # algorithmic bytes per ray, SURVEY.md §8(d): B_ray = 80*D + 96 + h*(12+192+128+16*tex), D = ceil(log8(T/2)) = 6
 B_TRAVERSE = 80 * 6 + 96          # k_trace's share: 576 B/ray
@@ -194,8 +194,7 @@ def main():
     def step(frame):
         lp.execute(frame, params)
         if n_gpus > 1:
-            for (y0, y1, off) in plan.pack_offsets(rank):
-                ctx.copy_to_device(rt.BUF_DIFFUSE_F32, send.data_ptr() + off * W * 16, (y1 - y0) * W * 16, y0, y1)
+            ctx.pack_bands(rt.BUF_DIFFUSE_F32, send.data_ptr(), plan.rows(rank) * W * 16, BAND_ROWS, rank, n_gpus)
             gather_frame(plan, rank, send, recv, dist)
 
     for i in range(args.warmup):

@@ -296,6 +296,10 @@ int  rt2_read(rt2_ctx* ctx, int which, void* dst, size_t nbytes);      /* device
  * buffer; pass 0,0 for the whole buffer. */
 int  rt2_copy_to_device(rt2_ctx* ctx, int which, void* device_dst, size_t nbytes,
                         uint32_t row0, uint32_t row1);
+/* all row bands of one rank (band b of `band_rows` rows belongs to rank b mod band_world, as in rt2_launch_params) packed
+ * back to back into caller-owned device memory, in frame order — the send buffer of the NCCL band gather. */
+int  rt2_pack_bands(rt2_ctx* ctx, int which, void* device_dst, size_t nbytes,
+                    uint32_t band_rows, uint32_t band_rank, uint32_t band_world);
 /* host -> device write into a context buffer (used to scatter gathered bands back, and by tests
  * to seed accumulation state). */
 int  rt2_write(rt2_ctx* ctx, int which, const void* src, size_t nbytes);

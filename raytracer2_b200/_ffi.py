@@ -210,6 +210,7 @@ ABI_SYMBOLS = {
     "rt2_buffer_size": (C.c_size_t, [VP, C.c_int]),
     "rt2_read": (C.c_int, [VP, C.c_int, VP, C.c_size_t]),
     "rt2_copy_to_device": (C.c_int, [VP, C.c_int, VP, C.c_size_t, u32, u32]),
+    "rt2_pack_bands": (C.c_int, [VP, C.c_int, VP, C.c_size_t, u32, u32, u32]),
     "rt2_write": (C.c_int, [VP, C.c_int, VP, C.c_size_t]),
     "rt2_get_stats": (C.c_int, [VP, C.POINTER(Stats)]),
 }

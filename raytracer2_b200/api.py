@@ -148,6 +148,9 @@ class Renderer:
     def copy_to_device(self, which: int, device_ptr: int, nbytes: int, row0: int = 0, row1: int = 0):
         self._check(self._lib.rt2_copy_to_device(self._ctx, which, C.c_void_p(device_ptr), nbytes, row0, row1), "rt2_copy_to_device")
 
+    def pack_bands(self, which: int, device_ptr: int, nbytes: int, band_rows: int, band_rank: int, band_world: int):
+        self._check(self._lib.rt2_pack_bands(self._ctx, which, C.c_void_p(device_ptr), nbytes, band_rows, band_rank, band_world), "rt2_pack_bands")
+
     def stats(self) -> Stats:
         s = Stats()
         self._check(self._lib.rt2_get_stats(self._ctx, C.byref(s)), "rt2_get_stats")

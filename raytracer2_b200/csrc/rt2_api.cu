@@ -67,6 +67,8 @@ int rt2_destroy(rt2_ctx* ctx) {
     scene_release(ctx); frame_release(ctx); passes_release(ctx);
     for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
     if (ctx->d_gconst) cudaFree(ctx->d_gconst);
+    for (uint32_t c = 0; c < RT2_MAX_CHAINS; c++) { if (ctx->chain_streams[c]) cudaStreamDestroy(ctx->chain_streams[c]); if (ctx->chain_join[c]) cudaEventDestroy(ctx->chain_join[c]); }
+    if (ctx->chain_fork) cudaEventDestroy(ctx->chain_fork);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
     return RT2_OK;
@@ -181,6 +183,35 @@ int rt2_copy_to_device(rt2_ctx* ctx, int which, void* device_dst, size_t nbytes,
     }
     if (nbytes != len) return fail(ctx, RT2_E_INVALID, "size mismatch: range is " + std::to_string(len) + " bytes");
     RT2_CUDA(ctx, cudaMemcpyAsync(device_dst, (const char*)p + off, len, cudaMemcpyDeviceToDevice, ctx->stream));
+    return RT2_OK;
+}
+
+// All row bands of one rank (band b -> rank b mod world) packed back to back into caller-owned device memory:
+// one strided copy for the full-height bands plus one for a ragged last band, instead of a copy per band.
+int rt2_pack_bands(rt2_ctx* ctx, int which, void* device_dst, size_t nbytes, uint32_t band_rows, uint32_t band_rank, uint32_t band_world) {
+    RT2_GUARD(ctx);
+    void* p; size_t b = 0;
+    if (!device_dst) return fail(ctx, RT2_E_INVALID, "device_dst is NULL");
+    if (which > RT2_BUF_OUTPUT_RGBA8) return fail(ctx, RT2_E_INVALID, "rt2_pack_bands: not a W x H frame buffer");
+    if (!buffer_lookup(ctx, which, &p, &b)) return fail(ctx, RT2_E_STATE, "buffer not allocated");
+    if (band_rows == 0 || band_world == 0 || band_rank >= band_world) return fail(ctx, RT2_E_INVALID, "bad band parameters");
+    const uint32_t H = ctx->fb.height;
+    const size_t row_bytes = b / H;
+    const uint32_t num_bands = (H + band_rows - 1) / band_rows;
+    uint32_t mine = 0, full = 0, last_rows = 0;
+    for (uint32_t band = band_rank; band < num_bands; band += band_world) {
+        const uint32_t rows = std::min(band_rows, H - band * band_rows);
+        if (rows == band_rows) full++; else last_rows = rows;      // only the last band of the frame can be ragged
+        mine++;
+    }
+    const size_t need = ((size_t)full * band_rows + last_rows) * row_bytes;
+    if (nbytes != need) return fail(ctx, RT2_E_INVALID, "size mismatch: this rank's bands are " + std::to_string(need) + " bytes");
+    const char* src = (const char*)p + (size_t)band_rank * band_rows * row_bytes;
+    if (full) RT2_CUDA(ctx, cudaMemcpy2DAsync(device_dst, (size_t)band_rows * row_bytes, src, (size_t)band_rows * band_world * row_bytes,
+                                             (size_t)band_rows * row_bytes, full, cudaMemcpyDeviceToDevice, ctx->stream));
+    if (last_rows) RT2_CUDA(ctx, cudaMemcpyAsync((char*)device_dst + (size_t)full * band_rows * row_bytes, src + (size_t)full * band_rows * band_world * row_bytes,
+                                                 (size_t)last_rows * row_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    (void)mine;
     return RT2_OK;
 }
 

@@ -130,6 +130,8 @@ struct rt2_ctx {
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
     int trace_blocks_per_sm[3] = {1, 1, 1};             // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level
     int trace_variant = 0;
+    uint32_t chains = 0;                                 // wavefront chains of the path tracer; 0 = by frame size (RT2_CHAINS overrides)
+    cudaStream_t chain_streams[8] = {}; cudaEvent_t chain_join[8] = {}; cudaEvent_t chain_fork = nullptr;
     bool gi_megakernels = false;                         // RT2_GI_MEGAKERNEL=1: K4/K5 with inlined traversal instead of the ray-queue kernel (A/B)
     std::vector<cudaEvent_t> prof_events;   // RT2_LAUNCH_PROFILE: 3 per wavefront iteration (before trace, after trace, after shade)
     uint64_t device_bytes = 0;
@@ -147,6 +149,7 @@ struct rt2_ctx {
 namespace rt2 {
 
 int fail(rt2_ctx* ctx, int code, const std::string& msg);
+#define RT2_MAX_CHAINS 8u
 #define RT2_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return rt2::fail((ctx), RT2_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); } while (0)
 
 // rt2_build.cu

@@ -63,8 +63,8 @@ struct ShadeArgs {
 // ------------------------------------------------------------------------------------------------
 // refrence.rgen:21-27: rng = RAB_InitRandomSampler(pixel, 1); first primary ray.  Threads are laid out
 // as 8x4 pixel tiles per warp so primary rays of a warp are coherent.
-__global__ void __launch_bounds__(256) k_k1_init(ShadeArgs a, uint32_t padded) {
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) k_k1_init(ShadeArgs a, uint32_t first, uint32_t padded) {
+    const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;    // [first, padded): the tile range of one wavefront chain
     if (i >= padded) return;
     const uint32_t tiles_x = (a.band.width + 7u) >> 3;
     const uint32_t tile = i >> 5, within = i & 31u;
@@ -393,7 +393,7 @@ static TraceArgs make_trace_args(rt2_ctx* ctx) {
 // counters layout: [0..1] u64 rays, [2..3] u64 hits, then per iteration it: count at 4 + 2*it, head at 5 + 2*it
 static int ensure_counters(rt2_ctx* ctx, uint32_t iterations) {
     FrameBuffers& f = ctx->fb;
-    const size_t need = 4 + 2 * ((size_t)iterations + 2);
+    const size_t need = 4 + RT2_MAX_CHAINS * 2 * ((size_t)iterations + 2);     // per chain and iteration: count, head
     if (f.counter_capacity < need) {
         if (f.counters) { RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(f.counters); f.counters = nullptr; }
         RT2_CUDA(ctx, cudaMalloc((void**)&f.counters, need * 4));
@@ -418,9 +418,6 @@ static const trace_kernel_t g_trace_variants[] = {
     k_trace_dyn<20, 4, 12>,    // 9
 };
 static const int g_num_trace_variants = (int)(sizeof(g_trace_variants) / sizeof(g_trace_variants[0]));
-static void launch_trace_single(rt2_ctx* ctx, const TraceArgs& t) {
-    g_trace_variants[ctx->trace_variant]<<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
-}
 
 int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp) {
     int rc = check_ready(ctx); if (rc) return rc;
@@ -463,31 +460,60 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
     a.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
     TraceArgs t = make_trace_args(ctx);
     t.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
-    uint32_t* q[2] = {f.queue0, f.queue1};
     if (padded) {
-        a.queue_out = q[0]; a.count_out = f.counters + 4;
-        k_k1_init<<<(padded + 255) / 256, 256, 0, ctx->stream>>>(a, padded); launches++;
-        const int trace_blocks = ctx->trace_blocks_per_sm[s.num_instances ? 1 : 0] * ctx->num_sms;
-        const int shade_blocks = ctx->num_sms * 8;
+        const int shade_blocks_full = ctx->num_sms * 8;
         const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
         for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
         ctx->prof_events.clear();
         if (profile) { ctx->prof_events.resize((size_t)iterations * 3); for (auto& e : ctx->prof_events) RT2_CUDA(ctx, cudaEventCreate(&e)); }
-        for (uint32_t it = 0; it < iterations; it++) {
-            if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], ctx->stream));
-            t.queue = q[it & 1]; t.count = f.counters + 4 + 2 * it; t.head = f.counters + 5 + 2 * it;
-            if (s.num_instances) {
-                // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
-                const bool unified = ctx->trace_variant != 0 && s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE;
-                if (unified) k_trace_dyn<20, 4, 8, true><<<trace_blocks, 128, 0, ctx->stream>>>(t);
-                else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        // Wavefront chains: the pixels of the frame are independent, so the tile range is cut into `chains` contiguous parts,
+        // each running its own init -> (trace -> shade) x iterations sequence on its own stream with its own queues and
+        // counters.  While one chain's trace kernel drains its last long rays (a ~45 us tail per launch that does not
+        // shrink with the wavefront), the other chains' kernels fill the SMs.  Per-kernel event timing (LAUNCH_PROFILE)
+        // needs serial kernels, so it runs one chain.
+        // measured on C2 (profiles/r01c): 2 chains +4 % at 2 M pixels, 4 chains +13 % at 260 k pixels (one of 8 ranks)
+        const uint32_t auto_chains = (uint64_t)band.width * band.local_rows >= (1u << 20) ? 2u : 4u;
+        uint32_t chains = profile ? 1u : std::max(1u, std::min(ctx->chains ? ctx->chains : auto_chains, RT2_MAX_CHAINS));
+        uint32_t per = ((padded + chains - 1) / chains + 255u) & ~255u;
+        while (chains > 1u && (uint64_t)per * (chains - 1) >= padded) { chains--; per = ((padded + chains - 1) / chains + 255u) & ~255u; }
+        if (chains > 1u) {
+            if (!ctx->chain_fork) { RT2_CUDA(ctx, cudaEventCreateWithFlags(&ctx->chain_fork, cudaEventDisableTiming)); }
+            for (uint32_t c = 1; c < chains; c++) {
+                if (!ctx->chain_streams[c]) {
+                    RT2_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->chain_streams[c], cudaStreamNonBlocking));
+                    RT2_CUDA(ctx, cudaEventCreateWithFlags(&ctx->chain_join[c], cudaEventDisableTiming));
+                }
             }
-            else launch_trace_single(ctx, t);
-            if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], ctx->stream));
-            a.queue_in = q[it & 1]; a.count_in = t.count; a.queue_out = q[(it + 1) & 1]; a.count_out = f.counters + 4 + 2 * (it + 1);
-            k_k1_shade<<<shade_blocks, 256, 0, ctx->stream>>>(a);
-            if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 2], ctx->stream));
-            launches += 2;
+            RT2_CUDA(ctx, cudaEventRecord(ctx->chain_fork, ctx->stream));
+        }
+        const size_t counter_stride = 2 * ((size_t)iterations + 2);
+        for (uint32_t c = 0; c < chains; c++) {
+            cudaStream_t st = c == 0 ? ctx->stream : ctx->chain_streams[c];
+            if (c != 0) RT2_CUDA(ctx, cudaStreamWaitEvent(st, ctx->chain_fork, 0));
+            const uint32_t first = c * per, end = std::min(padded, first + per);
+            uint32_t* cnt = f.counters + 4 + c * counter_stride;
+            uint32_t* q[2] = {f.queue0 + first, f.queue1 + first};
+            const int shade_blocks = std::max(1, std::min(shade_blocks_full, (int)((end - first + 255u) / 256u)));
+            a.queue_out = q[0]; a.count_out = cnt;
+            k_k1_init<<<(end - first + 255) / 256, 256, 0, st>>>(a, first, end); launches++;
+            for (uint32_t it = 0; it < iterations; it++) {
+                if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], st));
+                t.queue = q[it & 1]; t.count = cnt + 2 * it; t.head = cnt + 2 * it + 1;
+                if (s.num_instances) {
+                    // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
+                    const bool unified = ctx->trace_variant != 0 && s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE;
+                    if (unified) k_trace_dyn<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, st>>>(t);
+                    else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, st>>>(t);
+                } else {
+                    g_trace_variants[ctx->trace_variant]<<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, st>>>(t);
+                }
+                if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], st));
+                a.queue_in = q[it & 1]; a.count_in = t.count; a.queue_out = q[(it + 1) & 1]; a.count_out = cnt + 2 * (it + 1);
+                k_k1_shade<<<shade_blocks, 256, 0, st>>>(a);
+                if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 2], st));
+                launches += 2;
+            }
+            if (c != 0) { RT2_CUDA(ctx, cudaEventRecord(ctx->chain_join[c], st)); RT2_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->chain_join[c], 0)); }
         }
     }
     RT2_CUDA(ctx, cudaGetLastError());
@@ -518,6 +544,7 @@ int render_init(rt2_ctx* ctx) {
     int b0 = 0, b1 = 0;
     ctx->trace_variant = RT2_DEFAULT_TRACE_VARIANT;
     if (const char* e = getenv("RT2_GI_MEGAKERNEL")) ctx->gi_megakernels = atoi(e) != 0;
+    if (const char* e = getenv("RT2_CHAINS")) { int v = atoi(e); if (v >= 1) ctx->chains = (uint32_t)v; }
     if (const char* e = getenv("RT2_TRACE_VARIANT")) { int v = atoi(e); if (v >= 0 && v < g_num_trace_variants) ctx->trace_variant = v; }
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, g_trace_variants[ctx->trace_variant], 128, 0));
     int b2 = 0;

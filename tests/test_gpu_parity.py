@@ -5,6 +5,7 @@ import ctypes as C
 
 import numpy as np
 import pytest
+import torch
 
 import raytracer2_b200 as rt
 from oracle import oracle_ffi as O
@@ -126,8 +127,37 @@ def test_row_band_sharding_is_bit_identical_to_single_context():
             assert not part[other].any(), "a rank wrote rows it does not own"
             merged[rows] = part[rows]
             rays += ctx.stats().rays_traced
+            # rt2_pack_bands: this rank's bands back to back, in frame order, in one call
+            send = torch.zeros(len(rows) * w * 4, dtype=torch.float32, device="cuda")
+            ctx.pack_bands(rt.BUF_DIFFUSE_F32, send.data_ptr(), send.numel() * 4, 16, rank, world)
+            ctx.sync()
+            assert np.array_equal(send.cpu().numpy().reshape(len(rows), w, 4).view(np.uint32), part[rows].view(np.uint32))
+            with pytest.raises(rt.Rt2Error):
+                ctx.pack_bands(rt.BUF_DIFFUSE_F32, send.data_ptr(), send.numel() * 4 - 16, 16, rank, world)
         assert np.array_equal(merged.view(np.uint32), full.view(np.uint32))
         assert rays == rays_full
+    ctx.close()
+
+
+@pytest.mark.parametrize("band_rows,world", [(8, 8), (4, 5), (1, 2)])
+def test_pack_bands_matches_band_plan(band_rows, world):
+    """The packed send buffer of every rank, scattered with sharding.BandPlan, rebuilds the frame (the NCCL gather's layout)."""
+    from raytracer2_b200.sharding import BandPlan
+    w, h = 96, 77
+    sc, g, ctx, lp = _gpu_setup(rt.SCENE_CORNELL, 1, w, h)
+    lp.execute(5, rt.LaunchParams(spp=1, max_bounces=2))
+    full = ctx.read(rt.BUF_DIFFUSE_F32, np.float32).reshape(h, w, 4).copy()
+    plan = BandPlan(h, band_rows, world)
+    out = np.zeros_like(full)
+    for rank in range(world):
+        n = plan.rows(rank)
+        send = torch.zeros(max(n, 1) * w * 4, dtype=torch.float32, device="cuda")
+        ctx.pack_bands(rt.BUF_DIFFUSE_F32, send.data_ptr(), n * w * 16, band_rows, rank, world)
+        ctx.sync()
+        packed = send.cpu().numpy().reshape(-1, w, 4)
+        for (y0, y1, off) in plan.pack_offsets(rank):
+            out[y0:y1] = packed[off:off + (y1 - y0)]
+    assert np.array_equal(out.view(np.uint32), full.view(np.uint32))
     ctx.close()
 
 
