@@ -191,6 +191,9 @@ typedef struct rt2_launch_params {
 } rt2_launch_params;
 
 #define RT2_LAUNCH_TRIG_LIBDEVICE 1u  /* use CUDA sinf/cosf/atan2f/asinf instead of the pinned polynomials */
+#define RT2_LAUNCH_PRESAMPLING    4u  /* ReSTIR light sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1 (the reference ships 0,
+                                       * RtxdiApplicationBridge.glsl:12): local_light_sampling_mode 1 = POWER_RIS draws from the tiles
+                                       * rt2_presample(…, 0) filled (InitialSamplingFunctions.hlsli:241-254) */
 #define RT2_LAUNCH_PROFILE        2u  /* bracket every kernel launch with CUDA events (rt2_stats.trace_ns/shade_ns) */
 
 /* Buffers readable with rt2_read (all row-major W x H unless noted). */

@@ -12,6 +12,7 @@ LIB_PATH = os.path.join(_HERE, "librt2oracle.so")
 
 ORC_BRUTE_FORCE = 1
 ORC_TRIG_LIBM = 2
+ORC_PRESAMPLING = 4   # sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1 (POWER_RIS tiles of K11)
 
 u32, u64, f32 = C.c_uint32, C.c_uint64, C.c_float
 VP = C.c_void_p
@@ -58,7 +59,7 @@ def lib():
         L.orc_tonemap.restype = u32; L.orc_tonemap.argtypes = [VP]
         L.orc_gbuffer.restype = C.c_int; L.orc_gbuffer.argtypes = [VP, VP, u32, u32, u32, C.c_int] + [VP] * 7 + [C.POINTER(u64)]
         L.orc_di_fused_resampling.restype = C.c_int
-        L.orc_di_fused_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int] + [VP] * 5 + [VP, u32, VP, VP, u32, u32, u32, VP, VP, VP, C.POINTER(u64)]
+        L.orc_di_fused_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int] + [VP] * 5 + [VP, u32, VP, VP, u32, u32, u32, VP, VP, VP, C.POINTER(u64), VP, VP, u64]
         L.orc_reservoir_position_to_pointer.restype = u32; L.orc_reservoir_position_to_pointer.argtypes = [u32] * 5
         L.orc_brdf_rays.restype = C.c_int; L.orc_brdf_rays.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int, VP, VP, VP, VP, C.POINTER(u64)]
         L.orc_shade_secondary_surfaces.restype = C.c_int
@@ -103,7 +104,8 @@ class GBufferIn(C.Structure):   # orc_gbuffer_in
 
 
 class LightIn(C.Structure):     # orc_light_in
-    _fields_ = [("lights", VP), ("num_lights", u32), ("geom_to_light", VP), ("pdf_packed", VP), ("pdf_w", u32), ("pdf_h", u32), ("pdf_mips", u32)]
+    _fields_ = [("lights", VP), ("num_lights", u32), ("geom_to_light", VP), ("pdf_packed", VP), ("pdf_w", u32), ("pdf_h", u32), ("pdf_mips", u32),
+                ("ris", VP), ("ris_light_data", VP), ("ris_entries", u64)]
 
 
 def presample(gconst, frame, which, pdf_packed, w, h, mips, lights=None, ris=None, ris_light_data=None, entries=2 * 128 * 1024):
@@ -203,7 +205,8 @@ class OracleScene:
         return gb
 
     def di_fused_resampling(self, gconst, frame, w, h, gb, lights, geom_to_light, pdf_packed, pdf_w, pdf_h, pdf_mips, array_pitch,
-                            diffuse_f16=None, specular_f16=None, flags=0, threads=0):
+                            diffuse_f16=None, specular_f16=None, flags=0, threads=0, ris=None, ris_light_data=None):
+        """K9.  ris / ris_light_data: K11's outputs (presample()), read with flags & ORC_PRESAMPLING and local_light_sampling_mode 1."""
         res = np.zeros((array_pitch * 2, 6), np.uint32)
         d16 = np.zeros((h, w, 4), np.uint16) if diffuse_f16 is None else diffuse_f16
         s16 = np.zeros((h, w, 4), np.uint16) if specular_f16 is None else specular_f16
@@ -212,7 +215,9 @@ class OracleScene:
         rc = self._L.orc_di_fused_resampling(self._p, C.cast(C.byref(gconst), VP), frame, w, h, flags, threads,
                                              *[np.ascontiguousarray(gb[k]).ctypes.data_as(VP) for k in ("depth", "normals", "geo_normals", "diffuse_albedo", "specular_rough")],
                                              lights.ctypes.data_as(VP), len(lights), geom_to_light.ctypes.data_as(VP), pdf_packed.ctypes.data_as(VP), pdf_w, pdf_h, pdf_mips,
-                                             res.ctypes.data_as(VP), d16.ctypes.data_as(VP), s16.ctypes.data_as(VP), C.byref(rays))
+                                             res.ctypes.data_as(VP), d16.ctypes.data_as(VP), s16.ctypes.data_as(VP), C.byref(rays),
+                                             ris.ctypes.data_as(VP) if ris is not None else None,
+                                             ris_light_data.ctypes.data_as(VP) if ris_light_data is not None else None, u64(len(ris) if ris is not None else 0))
         assert rc == 0, rc
         return res, d16, s16, rays.value
 
@@ -223,11 +228,13 @@ class OracleScene:
         return GBufferIn(*[a.ctypes.data_as(VP) for a in keep]), keep
 
     @staticmethod
-    def _light_in(lights, geom_to_light, pdf_packed, pdf_w, pdf_h, pdf_mips):
+    def _light_in(lights, geom_to_light, pdf_packed, pdf_w, pdf_h, pdf_mips, ris=None, ris_light_data=None):
         if lights is None:
             return None, []
-        keep = [np.ascontiguousarray(lights), np.ascontiguousarray(geom_to_light), np.ascontiguousarray(pdf_packed, np.float32)]
-        return LightIn(keep[0].ctypes.data_as(VP), len(keep[0]), keep[1].ctypes.data_as(VP), keep[2].ctypes.data_as(VP), pdf_w, pdf_h, pdf_mips), keep
+        keep = [np.ascontiguousarray(lights), np.ascontiguousarray(geom_to_light), np.ascontiguousarray(pdf_packed, np.float32), ris, ris_light_data]
+        return LightIn(keep[0].ctypes.data_as(VP), len(keep[0]), keep[1].ctypes.data_as(VP), keep[2].ctypes.data_as(VP), pdf_w, pdf_h, pdf_mips,
+                       ris.ctypes.data_as(VP) if ris is not None else None, ris_light_data.ctypes.data_as(VP) if ris_light_data is not None else None,
+                       len(ris) if ris is not None else 0), keep
 
     def brdf_rays(self, gconst, frame, w, h, gb, secondary, diffuse_f16, specular_f16, flags=0, threads=0):
         """K4.  secondary: uint32 [arrayPitch, 12] (in/out); lighting images rgba16f as uint16 [h, w, 4] (in/out).  Returns rays."""
@@ -239,10 +246,10 @@ class OracleScene:
         return rays.value
 
     def shade_secondary_surfaces(self, gconst, frame, w, h, gb, secondary, gi_reservoirs, diffuse_f16, specular_f16,
-                                 lights=None, geom_to_light=None, pdf_packed=None, pdf_dims=(0, 0, 0), flags=0, threads=0):
+                                 lights=None, geom_to_light=None, pdf_packed=None, pdf_dims=(0, 0, 0), flags=0, threads=0, ris=None, ris_light_data=None):
         """K5.  gi_reservoirs: uint32 [arrayPitch * 2, 8] (in/out)."""
         gin, keep = self._gb_in(gb)
-        lin, keep2 = self._light_in(lights, geom_to_light, pdf_packed, *pdf_dims)
+        lin, keep2 = self._light_in(lights, geom_to_light, pdf_packed, *pdf_dims, ris=ris, ris_light_data=ris_light_data)
         rays = u64(0)
         rc = self._L.orc_shade_secondary_surfaces(self._p, C.cast(C.byref(gconst), VP), frame, w, h, flags, threads, C.byref(gin),
                                                   C.byref(lin) if lin is not None else None, secondary.ctypes.data_as(VP), gi_reservoirs.ctypes.data_as(VP),
@@ -289,7 +296,8 @@ class OracleScene:
         li = light_inputs or {}
         r4 = self.brdf_rays(gconst, frame, w, h, gb, st["secondary"], st["diffuse"], st["specular"], flags, threads)
         r5 = self.shade_secondary_surfaces(gconst, frame, w, h, gb, st["secondary"], st["gi_reservoirs"], st["diffuse"], st["specular"],
-                                           li.get("lights"), li.get("geom_to_light"), li.get("pdf_packed"), li.get("pdf_dims", (0, 0, 0)), flags, threads)
+                                           li.get("lights"), li.get("geom_to_light"), li.get("pdf_packed"), li.get("pdf_dims", (0, 0, 0)), flags, threads,
+                                           li.get("ris"), li.get("ris_light_data"))
         r6 = r7 = 0
         if gconst.enable_temporal_resampling == 1:
             r6 = self.gi_temporal_resampling(gconst, frame, w, h, gb, gb_prev, motion, st["gi_reservoirs"], flags, threads)

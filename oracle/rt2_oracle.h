@@ -16,6 +16,7 @@ typedef struct orc_scene orc_scene;
 
 /* flags for orc_render_* / orc_trace_primary */
 #define ORC_BRUTE_FORCE   1u   /* intersect by testing every triangle (no BVH)                    */
+#define ORC_PRESAMPLING   4u   /* light sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1: POWER_RIS tiles of K11 */
 #define ORC_TRIG_LIBM     2u   /* glibc sinf/cosf/atan2f/asinf instead of the pinned polynomials  */
 
 orc_scene* orc_scene_create(const rt2_scene_desc* scene);
@@ -95,7 +96,8 @@ int orc_di_fused_resampling(const orc_scene* s, const void* gconst, uint32_t fra
                             const float* gb_depth, const uint32_t* gb_normals, const uint32_t* gb_geo_normals, const uint32_t* gb_diffuse_albedo,
                             const uint32_t* gb_specular_rough, const rt2_light_info* lights, uint32_t num_lights, const uint32_t* geom_to_light,
                             const float* pdf_packed, uint32_t pdf_w, uint32_t pdf_h, uint32_t pdf_mips,
-                            rt2_packed_di_reservoir* reservoirs, uint16_t* diffuse_f16, uint16_t* specular_f16, uint64_t* rays);
+                            rt2_packed_di_reservoir* reservoirs, uint16_t* diffuse_f16, uint16_t* specular_f16, uint64_t* rays,
+                            const uint32_t* ris, const uint32_t* ris_light_data, uint64_t ris_entries);
 /* RTXDI_ReservoirPositionToPointer (rtxdi/RtxdiHelpers.hlsli:75-88) */
 uint32_t orc_reservoir_position_to_pointer(uint32_t block_row_pitch, uint32_t array_pitch, uint32_t x, uint32_t y, uint32_t array_index);
 
@@ -109,6 +111,7 @@ typedef struct orc_gbuffer_in {
 typedef struct orc_light_in {
     const rt2_light_info* lights; uint32_t num_lights; const uint32_t* geom_to_light;
     const float* pdf_packed; uint32_t pdf_w, pdf_h, pdf_mips;
+    const uint32_t* ris; const uint32_t* ris_light_data; uint64_t ris_entries;   /* K11 outputs, read with ORC_PRESAMPLING + POWER_RIS */
 } orc_light_in;
 /* K4 lighting_passes/brdf_rays.rgen:19-195 */
 int orc_brdf_rays(const orc_scene* s, const void* gconst, uint32_t frame, uint32_t width, uint32_t height, uint32_t flags, int threads,

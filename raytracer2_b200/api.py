@@ -33,6 +33,7 @@ BUF_BLAS_NODES, BUF_BLAS_TRIS, BUF_BLAS_SLOT_TO_PRIM, BUF_TLAS_NODES, BUF_TLAS_S
 
 LAUNCH_TRIG_LIBDEVICE = 1
 LAUNCH_PROFILE = 2
+LAUNCH_PRESAMPLING = 4   # light sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1: POWER_RIS reads K11's tiles
 
 SCENE_CORNELL, SCENE_HALL, SCENE_MANYLIGHT, SCENE_INSTANCED, SCENE_FURNACE, SCENE_RANDOM = 1, 2, 3, 5, 6, 7
 

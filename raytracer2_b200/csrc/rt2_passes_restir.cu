@@ -80,6 +80,8 @@ __global__ void __launch_bounds__(128) k_gbuffer(GBufferArgs a) {
 struct LightRefs {
     const rt2_light_info* lights; const uint32_t* geom_to_light;
     const float* pdf; uint32_t pdf_w, pdf_h, pdf_last_offset;
+    // RT2_LAUNCH_PRESAMPLING: the sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1; K11's tiles for POWER_RIS
+    uint32_t presampling; const uint2* ris; const uint4* ris_light_data;
 };
 
 // RAB_EvaluateLocalLightSourcePdf, bridge :420-434 (Q14 pinned to texelFetch semantics)
@@ -105,7 +107,10 @@ __device__ __forceinline__ bool visibility_ray_miss(const SceneRefs& sc, const S
 // The sampler in three pieces, so that the megakernel form (trace inlined between them) and the wavefront form of K9
 // (ray-queue kernel between them) run the very same arithmetic.
 // (1) RTXDI_SampleLocalLights{,Internal}, :264-343 (uniform selection)
-__device__ __forceinline__ void sl_local_lights(const LightRefs& lr, const rt2_gconst& g, Rng& rng, const Surface& surface, const SampleParams& sp,
+// With lr.presampling and localLightSamplingMode == POWER_RIS the lights come from one of K11's tiles, chosen by the tile-coherent
+// generator (:241-254, LocalLightSelection.hlsli:43-94, RISBuffer.hlsli:22-45); tile_x/tile_y = launch pixel / RTXDI_TILE_SIZE_IN_PIXELS.
+__device__ __forceinline__ void sl_local_lights(const LightRefs& lr, const rt2_gconst& g, Rng& rng, uint32_t tile_x, uint32_t tile_y, uint32_t frame,
+                                                const Surface& surface, const SampleParams& sp,
                                                 DIReservoir* local_reservoir, LightSample* local_sample) {
     const uint32_t first_local = g.light_buffer_params.local_light_buffer_region.first_light_index;
     const uint32_t num_local = g.light_buffer_params.local_light_buffer_region.num_lights;
@@ -113,11 +118,33 @@ __device__ __forceinline__ void sl_local_lights(const LightRefs& lr, const rt2_g
     *local_reservoir = empty_di_reservoir();
     if (num_local != 0u && sp.num_local != 0u) {
         DIReservoir state = empty_di_reservoir();
+        const bool ris_mode = lr.presampling != 0u && g.restir_di.initial_sampling_params.local_light_sampling_mode == 1u;
+        uint32_t tile_offset = 0, tile_size = 0;
+        if (ris_mode) {                                                // RTXDI_RandomlySelectRISTile
+            const rt2_ris_buffer_segment_params& seg = g.local_lights_risbuffer_segment_params;
+            Rng tile_rng = rng_init(tile_x, tile_y, frame, 1u);
+            const uint32_t tile_index = (uint32_t)(rng_next(tile_rng) * (float)seg.tile_count);
+            tile_offset = tile_index * seg.tile_size + seg.buffer_offset;
+            tile_size = seg.tile_size;
+        }
         for (uint32_t i = 0; i < sp.num_local; i++) {
-            const float rnd = rng_next(rng);                           // UniformSampling.hlsli:14-25
-            const float inv_source_pdf = (float)num_local;
-            const uint32_t light_index = first_local + min((uint32_t)floorf(rnd * (float)num_local), num_local - 1u);
-            const rt2_light_info li = load_light_info(lr.lights, light_index);
+            const float rnd = rng_next(rng);
+            float inv_source_pdf;
+            uint32_t light_index;
+            rt2_light_info li;
+            if (ris_mode) {                                            // RTXDI_RandomlySelectLocalLightFromRISTile
+                const uint32_t ptr = min((uint32_t)floorf(rnd * (float)tile_size), tile_size - 1u) + tile_offset;
+                const uint2 tile_data = __ldg(lr.ris + ptr);
+                light_index = tile_data.x & 0x7FFFFFFFu;               // RTXDI_LIGHT_INDEX_MASK
+                inv_source_pdf = __uint_as_float(tile_data.y);
+                // RTXDI_LIGHT_COMPACT_BIT: the 32-byte record K11 parked next to the tile entry (RAB_LoadCompactLightInfo, bridge :562-568)
+                li = (tile_data.x & 0x80000000u) ? load_light_info(reinterpret_cast<const rt2_light_info*>(lr.ris_light_data), 0u, ptr)
+                                                 : load_light_info(lr.lights, light_index);
+            } else {                                                   // UniformSampling.hlsli:14-25
+                inv_source_pdf = (float)num_local;
+                light_index = first_local + min((uint32_t)floorf(rnd * (float)num_local), num_local - 1u);
+                li = load_light_info(lr.lights, light_index);
+            }
             const float uvx = rng_next(rng), uvy = rng_next(rng);
             const LightSample cand = sample_polymorphic_light(li, surface, uvx, uvy);           // :131-156
             const float blended = light_brdf_mis_weight(surface, cand, 1.0f / inv_source_pdf, sp.local_mis_weight, false, sp);
@@ -175,7 +202,7 @@ __device__ __forceinline__ void sl_brdf_hit(const LightRefs& lr, Rng& rng, const
 }
 // (3) finalize the BRDF reservoir and combine, :586-590, 637-663.  The infinite-light region is always empty
 // (src/main.rs:375-380; rejected on the host otherwise), so its reservoir and sample are the empty ones.
-__device__ __forceinline__ DIReservoir sl_combine(Rng& rng, const SampleParams& sp, const DIReservoir& local_reservoir, const LightSample& local_sample,
+__device__ __forceinline__ DIReservoir sl_combine(const LightRefs& lr, Rng& rng, const SampleParams& sp, const DIReservoir& local_reservoir, const LightSample& local_sample,
                                                   DIReservoir brdf_reservoir, const LightSample& brdf_sample, LightSample* o_light_sample) {
     di_finalize(brdf_reservoir, 1.0f, (float)sp.num_mis);
     brdf_reservoir.M = 1;
@@ -184,6 +211,8 @@ __device__ __forceinline__ DIReservoir sl_combine(Rng& rng, const SampleParams& 
     DIReservoir reservoir = empty_di_reservoir();
     di_combine(reservoir, local_reservoir, 0.5f, local_reservoir.target_pdf);
     const bool select_infinite = di_combine(reservoir, infinite_reservoir, rng_next(rng), infinite_reservoir.target_pdf);
+    // :641-643 — with presampling compiled in the (always empty, Q7) environment reservoir is combined too: one more draw
+    if (lr.presampling != 0u) { const DIReservoir env = empty_di_reservoir(); di_combine(reservoir, env, rng_next(rng), env.target_pdf); }
     const bool select_brdf = di_combine(reservoir, brdf_reservoir, rng_next(rng), brdf_reservoir.target_pdf);
     di_finalize(reservoir, 1.0f, 1.0f);
     reservoir.M = 1;
@@ -191,10 +220,11 @@ __device__ __forceinline__ DIReservoir sl_combine(Rng& rng, const SampleParams& 
     return reservoir;
 }
 
-__device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& sc, const LightRefs& lr, const rt2_gconst& g, Rng& rng, const Surface& surface,
+__device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& sc, const LightRefs& lr, const rt2_gconst& g, Rng& rng,
+                                                              uint32_t tile_x, uint32_t tile_y, uint32_t frame, const Surface& surface,
                                                               const SampleParams& sp, LightSample* o_light_sample, uint32_t& rays, uint32_t& hits) {
     LightSample local_sample; DIReservoir local_reservoir;
-    sl_local_lights(lr, g, rng, surface, sp, &local_reservoir, &local_sample);
+    sl_local_lights(lr, g, rng, tile_x, tile_y, frame, surface, sp, &local_reservoir, &local_sample);
     LightSample brdf_sample = empty_light_sample();
     DIReservoir brdf_reservoir = empty_di_reservoir();
     for (uint32_t i = 0; i < sp.num_brdf; ++i) {
@@ -208,7 +238,7 @@ __device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& s
         }
         sl_brdf_hit(lr, rng, surface, sp, p.sampled, h.geom, h.prim, h.u, h.v, &brdf_reservoir, &brdf_sample);
     }
-    return sl_combine(rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, o_light_sample);
+    return sl_combine(lr, rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, o_light_sample);
 }
 
 // ShadeSurfaceWithLightSample, ShadingHelpers.glsl:2-58.  Visibility reuse needs reservoir.age > 0 (DIReservoir.hlsli:186-189);
@@ -268,7 +298,7 @@ __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
                                                di.initial_sampling_params.num_primary_environment_samples, di.initial_sampling_params.num_primary_brdf_samples,
                                                di.initial_sampling_params.brdf_cutoff, 0.001f);
     LightSample light_sample;
-    DIReservoir reservoir = sample_lights_for_surface(a.sc, a.li, g, rng, surface, sp, &light_sample, rays, hits);
+    DIReservoir reservoir = sample_lights_for_surface(a.sc, a.li, g, rng, px >> 4, py >> 4, a.frame, surface, sp, &light_sample, rays, hits);
     // ---- di_fused_resampling.rgen:42-48: initial visibility
     if (di.initial_sampling_params.enable_initial_visibility == 1u && di_valid(reservoir)) {
         if (!visibility_ray_miss(a.sc, surface, light_sample.position, 0.001f, &rays)) { hits++; di_store_visibility(reservoir, v3(0.f, 0.f, 0.f), true); }
@@ -388,7 +418,7 @@ __global__ void __launch_bounds__(128) k_di_stage_a(DIWaveArgs w) {
         const Surface surface = di_stage_surface<SEC>(w, g, lx, ly, px, py, &active);
         const SampleParams sp = di_stage_params<SEC>(g.restir_di);
         LightSample local_sample = empty_light_sample(); DIReservoir local_reservoir = empty_di_reservoir();
-        if (active) sl_local_lights(a.li, g, rng, surface, sp, &local_reservoir, &local_sample);
+        if (active) sl_local_lights(a.li, g, rng, (SEC ? lx : px) >> 4, (SEC ? ly : py) >> 4, a.frame, surface, sp, &local_reservoir, &local_sample);
         uint32_t flags = active ? DIW_ACTIVE : 0u;
         if (active && sp.num_brdf != 0u) {
             const BrdfProbe p = sl_brdf_ray(surface, rng, sp);
@@ -441,7 +471,7 @@ __global__ void __launch_bounds__(128) k_di_stage_b(DIWaveArgs w, uint32_t* queu
             sl_brdf_hit(a.li, rng, surface, sp, sampled, geom, prim, hu, hv, &brdf_reservoir, &brdf_sample);
         }
         LightSample light_sample;
-        DIReservoir reservoir = sl_combine(rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, &light_sample);
+        DIReservoir reservoir = sl_combine(a.li, rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, &light_sample);
         flags = DIW_ACTIVE;
         // K9 runs the initial-visibility test of di_fused_resampling.rgen:42-48 first; K5 shades with enableVisibilityReuse false and has none
         if (di_valid(reservoir) || SEC) {
@@ -673,7 +703,7 @@ __global__ void __launch_bounds__(128) k_shade_secondary(GIArgs a) {
     if (valid_secondary && !is_env && g.enable_restir_di == 1u) {
         const SampleParams sp = init_sample_params(0u, 0u, 0u, 1u, 0.f, 0.001f);
         LightSample light_sample;
-        DIReservoir reservoir = sample_lights_for_surface(a.sc, a.li, g, rng, sec, sp, &light_sample, rays, hits);
+        DIReservoir reservoir = sample_lights_for_surface(a.sc, a.li, g, rng, lx >> 4, ly >> 4, a.frame, sec, sp, &light_sample, rays, hits);
         V3 indirect_diffuse, indirect_specular;
         shade_surface_with_light_sample(a.sc, g, reservoir, sec, light_sample, &indirect_diffuse, &indirect_specular, rays, hits);
         radiance = radiance + (indirect_diffuse * sec.diffuse_albedo + indirect_specular);
@@ -1274,6 +1304,18 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         uint32_t off = 0;
         for (uint32_t k = 0; k < last; k++) off += std::max(1u, ctx->local_pdf_w >> k) * std::max(1u, ctx->local_pdf_h >> k);
         lrefs.pdf_last_offset = off;
+        if (lp.flags & RT2_LAUNCH_PRESAMPLING) {
+            lrefs.presampling = 1u;
+            const uint32_t mode = g.restir_di.initial_sampling_params.local_light_sampling_mode;
+            if (mode > 1u) return fail(ctx, RT2_E_INVALID, "local_light_sampling_mode 2 (ReGIR) is compiled out of the reference (RTXDI_REGIR_MODE disabled)");
+            if (mode == 1u) {
+                const rt2_ris_buffer_segment_params& seg = g.local_lights_risbuffer_segment_params;
+                if (!ctx->ris_buffer || !ctx->ris_light_data) return fail(ctx, RT2_E_STATE, "POWER_RIS light sampling needs the presampled tiles: call rt2_presample(ctx, frame, 0) first");
+                if (seg.tile_size == 0u || seg.tile_count == 0u || (uint64_t)seg.buffer_offset + (uint64_t)seg.tile_size * seg.tile_count > ctx->ris_entries)
+                    return fail(ctx, RT2_E_INVALID, "local-light RIS segment exceeds the RIS buffer");
+                lrefs.ris = ctx->ris_buffer; lrefs.ris_light_data = ctx->ris_light_data;
+            }
+        }
     }
     if (g.enable_restir_gi == 1u) {
         if (!pitches_ok(g.restir_gi.reservoir_buffer_params) || !pitches_ok(g.restir_di.reservoir_buffer_params))   // K5 addresses the secondary G-buffer with the DI pitches

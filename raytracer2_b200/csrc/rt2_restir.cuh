@@ -93,8 +93,10 @@ struct LightSample { V3 position, normal, radiance; float solid_angle_pdf; uint3
 __device__ __forceinline__ LightSample empty_light_sample() {
     LightSample s; s.position = s.normal = s.radiance = v3(0.f, 0.f, 0.f); s.solid_angle_pdf = 0.f; s.light_type = 0u; return s;
 }
-__device__ __forceinline__ rt2_light_info load_light_info(const rt2_light_info* lights, uint32_t index) {
-    const uint4* p = reinterpret_cast<const uint4*>(lights + index);
+// a light-buffer entry (48 B apart), or — with compact_index — one of K11's compact records (32 B apart, `lights` = their base)
+__device__ __forceinline__ rt2_light_info load_light_info(const rt2_light_info* lights, uint32_t index, uint32_t compact_index = 0xFFFFFFFFu) {
+    const uint4* p = compact_index != 0xFFFFFFFFu ? reinterpret_cast<const uint4*>(lights) + 2 * (size_t)compact_index
+                                                  : reinterpret_cast<const uint4*>(lights + index);
     const uint4 a = __ldg(p), b = __ldg(p + 1);      // uint4[2] holds only shaping data (unused for triangle lights)
     rt2_light_info li;
     li.center[0] = __uint_as_float(a.x); li.center[1] = __uint_as_float(a.y); li.center[2] = __uint_as_float(a.z); li.color_type_and_flags = a.w;

@@ -182,14 +182,21 @@ def _di_run(kind, scale, w, h, frame, **di):
     g.enable_accumulation = di.get("accumulate", 0); g.blend_factor = 0.25
     rt.PrepareLightsTasks(ctx).execute()
     rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    isp.local_light_sampling_mode = di.get("mode", 0)
     lp.update_uniform(g)
+    presampling = di.get("presampling", False)
+    ris = ris_data = None
+    if presampling:                 # K11 fills the tiles the POWER_RIS sampler draws from (its own parity: test_presample_local_lights_bit_exact)
+        lp.execute_presampeling(frame, False)
+        ris = ctx.read(rt.BUF_RIS, np.uint32).reshape(-1, 2)
+        ris_data = ctx.read(rt.BUF_RIS_LIGHT_DATA, np.uint32).reshape(-1, 8)
     if di.get("accumulate", 0):     # seed prior lighting so the accumulation branch reads something
         rng = np.random.default_rng(4)
         prior = np.zeros((h, w, 4), np.float16); prior[:, :, :3] = rng.random((h, w, 3))
         ctx.write(rt.BUF_DIFFUSE_F16, prior.view(np.uint16)); ctx.write(rt.BUF_SPECULAR_F16, prior.view(np.uint16))
     else:
         prior = None
-    lp.execute(frame)
+    lp.execute(frame, rt.LaunchParams(flags=rt.LAUNCH_PRESAMPLING) if presampling else None)
     gb = _read_gbuffer(ctx, w, h)
     pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
     rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
@@ -197,10 +204,11 @@ def _di_run(kind, scale, w, h, frame, **di):
     lights = ctx.read(rt.BUF_LIGHT_INFO, np.uint32).reshape(-1, 12)
     g2l = ctx.read(rt.BUF_GEOM_TO_LIGHT, np.uint32)
     pitch = g.restir_di.reservoir_buffer_params.reservoir_array_pitch
+    oflags = di.get("oflags", O.ORC_BRUTE_FORCE) | (O.ORC_PRESAMPLING if presampling else 0)
     d_in = prior.view(np.uint16).copy() if prior is not None else None
     s_in = prior.view(np.uint16).copy() if prior is not None else None
     res, d16, s16, rays = O.OracleScene(sc.desc).di_fused_resampling(g, frame, w, h, gb, lights, g2l, pdf, pw.value, ph.value, pm.value, pitch,
-                                                                     diffuse_f16=d_in, specular_f16=s_in, flags=di.get("oflags", O.ORC_BRUTE_FORCE))
+                                                                     diffuse_f16=d_in, specular_f16=s_in, flags=oflags, ris=ris, ris_light_data=ris_data)
     got_res = ctx.read(rt.BUF_DI_RESERVOIRS, np.uint32).reshape(-1, 6)
     got_d = ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).reshape(h, w, 4)
     got_s = ctx.read(rt.BUF_SPECULAR_F16, np.uint16).reshape(h, w, 4)
@@ -227,6 +235,45 @@ def test_di_reservoir_sampling_bit_exact(kind, scale, w, h, di):
     assert int((d16 != rd16).any(axis=2).sum()) <= tol and int((s16 != rs16).any(axis=2).sum()) <= tol
     f = d16.view(np.float16)[:, :, :3].astype(np.float32)
     assert np.isfinite(f).all() and f.max() > 0
+
+
+@pytest.mark.parametrize("kind,scale,w,h,di", [
+    (rt.SCENE_CORNELL, 1.0, 256, 256, dict(local=4, brdf=1, presampling=True, mode=1)),
+    (rt.SCENE_MANYLIGHT, 0.2, 320, 180, dict(local=8, brdf=1, initial_vis=1, final_vis=1, oflags=0, presampling=True, mode=1)),
+    (rt.SCENE_MANYLIGHT, 0.2, 320, 180, dict(local=8, brdf=1, oflags=0, presampling=True, mode=0)),   # uniform selection, but the environment combine draw shifts the RNG
+    (rt.SCENE_MANYLIGHT, 0.2, 200, 120, dict(local=2, brdf=2, final_vis=1, oflags=0, presampling=True, mode=1)),  # 2 BRDF samples: megakernel form
+])
+def test_di_power_ris_sampling_bit_exact(kind, scale, w, h, di):
+    """the light sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1 — POWER_RIS local lights drawn from K11's tiles."""
+    (res, d16, s16, rays), (rres, rd16, rs16, rrays) = _di_run(kind, scale, w, h, 3, **di)
+    nvalid = int((rres[:, 0] != 0).sum())
+    assert nvalid > 0 and rays == rrays
+    tol = max(2, w * h // 50000)
+    bad = np.flatnonzero((res != rres).any(axis=1))
+    assert len(bad) <= tol, f"{len(bad)} reservoirs differ (of {nvalid} valid), first {bad[:4]}"
+    assert int((d16 != rd16).any(axis=2).sum()) <= tol and int((s16 != rs16).any(axis=2).sum()) <= tol
+    # the presampled branch really ran: the same frame without it selects different lights
+    (res0, _, _, _), _ = _di_run(kind, scale, w, h, 3, **{**di, "presampling": False, "mode": 0})
+    ndiff = int((res0[:, 0] != res[:, 0]).sum())
+    assert ndiff > (nvalid // 4 if di["mode"] == 1 else 0)      # mode 0: only the environment combine's extra draw differs
+
+
+def test_power_ris_needs_presampled_tiles():
+    sc, ctx, g, lp = _restir_setup(rt.SCENE_CORNELL, 1.0, 64, 64)
+    g.enable_restir_di = 1
+    g.restir_di.initial_sampling_params.num_primary_local_light_samples = 2
+    g.restir_di.initial_sampling_params.local_light_sampling_mode = 1
+    rt.PrepareLightsTasks(ctx).execute()
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    lp.update_uniform(g)
+    lp.execute(1)                                                   # the reference's build: the mode is ignored (presampling compiled out)
+    with pytest.raises(rt.Rt2Error):
+        lp.execute(1, rt.LaunchParams(flags=rt.LAUNCH_PRESAMPLING))   # rt2_presample has not run
+    g.restir_di.initial_sampling_params.local_light_sampling_mode = 2
+    lp.update_uniform(g)
+    with pytest.raises(rt.Rt2Error):
+        lp.execute(1, rt.LaunchParams(flags=rt.LAUNCH_PRESAMPLING))   # ReGIR is compiled out
+    ctx.close()
 
 
 def test_di_needs_light_list():
