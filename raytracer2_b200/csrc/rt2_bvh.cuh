@@ -82,7 +82,9 @@ RT2_HD uint32_t sign_extend_s8x4(uint32_t x) {
 // value; measured on B200 it LOSES 3 % on C2 (2142 vs 2212 Mrays/s): the kernel is issue/latency bound before it is
 // XU bound.  Kept behind RT2_BYTE_MAGIC for the record.
 RT2_HD float byte_to_float(uint32_t w, uint32_t i) {
-#if defined(__CUDA_ARCH__) && defined(RT2_BYTE_MAGIC)
+#if defined(__CUDA_ARCH__) && defined(RT2_NODE_TEST_FOLDED)
+    return u2f(__byte_perm(w, 0x4B000000u, 0x7540u | i));          // 2^23 + q: cwbvh_node_step folds the 2^23 into its offsets
+#elif defined(__CUDA_ARCH__) && defined(RT2_BYTE_MAGIC)
     return u2f(__byte_perm(w, 0x4B000000u, 0x7540u | i)) - 8388608.0f;
 #else
     return (float)rt2_byte(w, i);
@@ -138,7 +140,21 @@ RT2_HD void cwbvh_node_step(const Node8* __restrict__ nodes, const RayPrep& rp, 
     const float ax = u2f(n0.x) - rp.ox, ay = u2f(n0.y) - rp.oy, az = u2f(n0.z) - rp.oz;
     // t = q * (s*idir) + (p-o)*idir ; s is a power of two so s*idir is exact
     const float snx = sx * rp.inx, sny = sy * rp.iny, snz = sz * rp.inz, sfx = sx * rp.ifx, sfy = sy * rp.ify, sfz = sz * rp.ifz;
-    const float anx = ax * rp.inx, any_ = ay * rp.iny, anz = az * rp.inz, afx = ax * rp.ifx, afy = ay * rp.ify, afz = az * rp.ifz;
+    float anx = ax * rp.inx, any_ = ay * rp.iny, anz = az * rp.inz, afx = ax * rp.ifx, afy = ay * rp.ify, afz = az * rp.ifz;
+#if defined(__CUDA_ARCH__) && defined(RT2_NODE_TEST_FOLDED)
+    // EXPERIMENT, off by default (measured −7 % on C2, 2147 vs 2305 Mrays/s: the 48 prmt per node land on the ALU pipe, which
+    // FMNMX/LOP3/SEL already keep 47 % busy, while I2F.U8 runs beside it on the otherwise idle XU pipe).
+    // Dequantisation without the XU pipe (I2F.U8 runs at 16 lanes/clk/SM and was the busiest pipe of k_trace, 63 % in
+    // profiles/r01b): prmt drops the byte q into the mantissa of 2^23, giving the float 2^23 + q, and the 2^23 is taken
+    // out of the per-node offset instead of out of every value:  q*s + a == (2^23 + q)*s + (a - 2^23*s).
+    // a - 2^23*s is rounded once (fma), to <= half a grid cell |s| — so the offset also moves each near plane one cell
+    // earlier and each far plane one cell later (constants 2^23 +- 1, exact in binary32).  The box test stays conservative;
+    // it is no longer the oracle's arithmetic, which is fine: the closest hit is a total order, independent of which
+    // superfluous nodes are visited.  The CPU build of this header keeps the exact form.
+    anx = rt2_fma(snx, rp.negx ? -8388607.0f : -8388609.0f, anx); afx = rt2_fma(sfx, rp.negx ? -8388609.0f : -8388607.0f, afx);
+    any_ = rt2_fma(sny, rp.negy ? -8388607.0f : -8388609.0f, any_); afy = rt2_fma(sfy, rp.negy ? -8388609.0f : -8388607.0f, afy);
+    anz = rt2_fma(snz, rp.negz ? -8388607.0f : -8388609.0f, anz); afz = rt2_fma(sfz, rp.negz ? -8388609.0f : -8388607.0f, afz);
+#endif
     const uint32_t oct_inv4 = rp.oct_inv * 0x01010101u;
     uint32_t hitmask = 0;
 #pragma unroll

@@ -471,8 +471,9 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
         // counters.  While one chain's trace kernel drains its last long rays (a ~45 us tail per launch that does not
         // shrink with the wavefront), the other chains' kernels fill the SMs.  Per-kernel event timing (LAUNCH_PROFILE)
         // needs serial kernels, so it runs one chain.
-        // measured on C2 (profiles/r01c): 2 chains +4 % at 2 M pixels, 4 chains +13 % at 260 k pixels (one of 8 ranks)
-        const uint32_t auto_chains = (uint64_t)band.width * band.local_rows >= (1u << 20) ? 2u : 4u;
+        // measured (profiles/r01c): C2 2 chains +4 % at 2 M pixels, 4 chains +13 % at 260 k pixels (one of 8 ranks); a scene whose
+        // trace launches last only microseconds (C1, 32 triangles) is launch-rate bound and loses 10-25 % to the extra launches
+        const uint32_t auto_chains = s.num_tris < 4096u ? 1u : ((uint64_t)band.width * band.local_rows >= (1u << 20) ? 2u : 4u);
         uint32_t chains = profile ? 1u : std::max(1u, std::min(ctx->chains ? ctx->chains : auto_chains, RT2_MAX_CHAINS));
         uint32_t per = ((padded + chains - 1) / chains + 255u) & ~255u;
         while (chains > 1u && (uint64_t)per * (chains - 1) >= padded) { chains--; per = ((padded + chains - 1) / chains + 255u) & ~255u; }
