@@ -13,8 +13,8 @@ raytracer2_b200/librt2cuda.so: $(CU_SRCS) $(CU_HDRS)
 	$(NVCC) $(NVCCFLAGS) -shared -o $@ $(CU_SRCS) 2> build_ptxas.log || (cat build_ptxas.log; exit 1)
 	@grep -E "error|warning" build_ptxas.log || true
 
-raytracer2_b200/librt2host.so: raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_host.h include/rt2_abi.h include/rt2_gconst.h
-	$(CXX) -O2 -std=c++17 -fPIC -Wall -Wextra -shared -o $@ raytracer2_b200/host/rt2_host.cpp
+raytracer2_b200/librt2host.so: raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp raytracer2_b200/host/rt2_host.h raytracer2_b200/host/rt2_ingest.h include/rt2_abi.h include/rt2_gconst.h
+	$(CXX) -O2 -std=c++17 -fPIC -Wall -Wextra -shared -o $@ raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp -lz
 
 oracle:
 	$(MAKE) -C oracle

@@ -33,6 +33,7 @@ BUF_BLAS_NODES, BUF_BLAS_TRIS, BUF_BLAS_SLOT_TO_PRIM, BUF_TLAS_NODES, BUF_TLAS_S
 
 LAUNCH_TRIG_LIBDEVICE = 1
 LAUNCH_PROFILE = 2
+FILTER_NEAREST, FILTER_LINEAR = 0, 1   # rt2_sampler_desc (src/model.rs:165-183)
 LAUNCH_PRESAMPLING = 4   # light sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1: POWER_RIS reads K11's tiles
 
 SCENE_CORNELL, SCENE_HALL, SCENE_MANYLIGHT, SCENE_INSTANCED, SCENE_FURNACE, SCENE_RANDOM = 1, 2, 3, 5, 6, 7
@@ -40,6 +41,20 @@ SCENE_CORNELL, SCENE_HALL, SCENE_MANYLIGHT, SCENE_INSTANCED, SCENE_FURNACE, SCEN
 
 class Rt2Error(RuntimeError):
     pass
+
+
+def load_exr(path: str):
+    """RGBA32F numpy array [h, w, 4] (DynamicImage::to_rgba32f of image::open, src/context.rs:1476)."""
+    h = _ffi.host_lib()
+    w_, h_ = C.c_uint32(), C.c_uint32()
+    err = C.create_string_buffer(512)
+    p = h.rt2h_load_exr(path.encode(), C.byref(w_), C.byref(h_), err, len(err))
+    if not p:
+        raise Rt2Error(f"cannot load {path}: {err.value.decode(errors='replace')}")
+    try:
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(h_.value, w_.value, 4)).copy()
+    finally:
+        h.rt2h_free(p)
 
 
 # ---- host library wrappers ------------------------------------------------------------------------------
@@ -52,6 +67,18 @@ class Scene:
         if not self._p:
             raise Rt2Error(f"unknown scene kind {kind}")
         self.kind = kind
+
+    @classmethod
+    def from_gltf(cls, path: str, sky_exr: str | None = None) -> "Scene":
+        """gltf::load_file + image::open of the sky box (src/main.rs:62-63) through the C++ readers (rt2h_scene_load_gltf)."""
+        self = cls.__new__(cls)
+        self._h = _ffi.host_lib()
+        err = C.create_string_buffer(512)
+        self._p = self._h.rt2h_scene_load_gltf(path.encode(), sky_exr.encode() if sky_exr else None, err, len(err))
+        if not self._p:
+            raise Rt2Error(f"cannot load {path}: {err.value.decode(errors='replace')}")
+        self.kind = 0
+        return self
 
     @property
     def desc(self) -> "C.POINTER(SceneDesc)":

@@ -1,11 +1,16 @@
 // rt2_host.cpp — host-side mirror of the reference's CPU arithmetic for the path + procedural
 // scene generators.  See rt2_host.h.  No CUDA here; pure C++17.
 #include "rt2_host.h"
+#include "rt2_ingest.h"
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
+#include <memory>
+#include <string>
 #include <vector>
 
 namespace {
@@ -634,6 +639,38 @@ rt2h_scene* rt2h_scene_generate(int kind, float scale, uint32_t texture_size, ui
     s->finish();
     return s;
 }
+static void set_err(char* err, size_t err_len, const std::string& m) {
+    if (err && err_len) { std::snprintf(err, err_len, "%s", m.c_str()); }
+}
+rt2h_scene* rt2h_scene_load_gltf(const char* gltf_path, const char* sky_exr_path, char* err, size_t err_len) {
+    if (!gltf_path) { set_err(err, err_len, "gltf_path is NULL"); return nullptr; }
+    rt2ingest::GltfModel m;
+    std::string e;
+    if (!rt2ingest::load_gltf(gltf_path, m, e)) { set_err(err, err_len, e); return nullptr; }
+    std::unique_ptr<rt2h_scene> s(new rt2h_scene());
+    s->kind = 0;
+    s->verts = std::move(m.vertices); s->idx = std::move(m.indices);
+    s->geoms = std::move(m.geometries); s->index_counts = std::move(m.index_counts);
+    s->image_data = std::move(m.image_rgba8);
+    for (size_t i = 0; i < s->image_data.size(); i++) s->images.push_back({s->image_data[i].data(), m.image_w[i], m.image_h[i]});
+    s->samplers = std::move(m.samplers); s->textures = std::move(m.textures);
+    if (sky_exr_path && !rt2ingest::load_exr(sky_exr_path, s->sky, s->sky_w, s->sky_h, e)) { set_err(err, err_len, e); return nullptr; }
+    const float pos[3] = {0.0f, 0.0f, 10.0f}, dir[3] = {0.0f, 0.0f, 1.0f};      // src/main.rs:114-121
+    rt2h_camera_new(&s->cam, pos, dir, 65.0f, 1920.0f / 1080.0f, 0.1f, 1000.0f);
+    s->finish();
+    return s.release();
+}
+float* rt2h_load_exr(const char* path, uint32_t* width, uint32_t* height, char* err, size_t err_len) {
+    std::vector<float> px; uint32_t w = 0, h = 0; std::string e;
+    if (!path || !rt2ingest::load_exr(path, px, w, h, e)) { set_err(err, err_len, path ? e : "path is NULL"); return nullptr; }
+    float* out = (float*)std::malloc(px.size() * sizeof(float));
+    if (!out) { set_err(err, err_len, "out of memory"); return nullptr; }
+    std::memcpy(out, px.data(), px.size() * sizeof(float));
+    if (width) *width = w;
+    if (height) *height = h;
+    return out;
+}
+void rt2h_free(void* p) { std::free(p); }
 void rt2h_scene_destroy(rt2h_scene* s) { delete s; }
 const rt2_scene_desc* rt2h_scene_desc(const rt2h_scene* s) { return s ? &s->desc : nullptr; }
 void rt2h_scene_camera(const rt2h_scene* s, float aspect_ratio, rt2h_camera* out) { *out = s->cam; if (aspect_ratio > 0) out->aspect_ratio = aspect_ratio; }

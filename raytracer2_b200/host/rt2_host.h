@@ -10,6 +10,7 @@
 #define RT2_HOST_H
 #include "../../include/rt2_abi.h"
 #include "../../include/rt2_gconst.h"
+#include <stddef.h>
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -61,6 +62,14 @@ enum rt2h_scene_kind {
 /* `scale` shrinks the big scenes for tests: triangle counts scale ~ scale^2 (1.0 = BASELINE size);
  * texture_size 0 => default (512 for HALL). */
 rt2h_scene* rt2h_scene_generate(int kind, float scale, uint32_t texture_size, uint64_t seed);
+/* SURVEY §8f N4 — the reference's asset path: gltf::load_file("./src/models/box.glb") (src/main.rs:62, src/gltf/mod.rs:50-168)
+ * and image::open("./src/models/skybox2.exr") -> to_rgba32f (src/main.rs:63, src/context.rs:1476), flattened into the
+ * upload layout Model::from_gltf consumes.  gltf_path: .glb or .gltf; sky_exr_path may be NULL.  The camera is the
+ * reference's start-up camera (src/main.rs:114-121).  Returns NULL and writes a message into err (if given) on failure. */
+rt2h_scene* rt2h_scene_load_gltf(const char* gltf_path, const char* sky_exr_path, char* err, size_t err_len);
+/* the EXR reader alone: RGBA32F rows, top to bottom; caller frees with rt2h_free */
+float*      rt2h_load_exr(const char* path, uint32_t* width, uint32_t* height, char* err, size_t err_len);
+void        rt2h_free(void* p);
 void        rt2h_scene_destroy(rt2h_scene* s);
 const rt2_scene_desc* rt2h_scene_desc(const rt2h_scene* s);
 /* recommended camera for the scene */

@@ -390,7 +390,7 @@ void expand_to_rgba8(const std::vector<uint8_t>& px, uint32_t channels, std::vec
     for (size_t i = 0; i < n; i++) {
         const uint8_t* s = px.data() + i * channels;
         uint8_t* o = out.data() + i * 4;
-        o[0] = s[0]; o[1] = channels >= 2 && channels != 4 ? (channels >= 2 ? s[1] : 0) : (channels == 4 ? s[1] : 0);
+        o[0] = s[0]; o[1] = channels >= 2 ? s[1] : 0;
         o[2] = channels >= 3 ? s[2] : 0; o[3] = channels == 4 ? s[3] : 255;
     }
 }
@@ -528,3 +528,139 @@ bool load_gltf(const std::string& path, GltfModel& out, std::string& err) {
         if (g.base_color_texture_index >= (int32_t)out.textures.size()) { err = "glTF: material texture index out of range"; return false; }
     return true;
 }
+
+// ------------------------------------------------------------------------------------------------
+// OpenEXR, single-part scan-line files (openexr.com "OpenEXR File Layout")
+// ------------------------------------------------------------------------------------------------
+namespace {
+float half_to_float(uint16_t h) {
+    const uint32_t sign = (uint32_t)(h & 0x8000u) << 16, e = (h >> 10) & 0x1Fu, m = h & 0x3FFu;
+    uint32_t bits;
+    if (e == 0) {
+        if (m == 0) bits = sign;
+        else { int s = 0; uint32_t mm = m; while (!(mm & 0x400u)) { mm <<= 1; s++; } bits = sign | ((uint32_t)(113 - s) << 23) | ((mm & 0x3FFu) << 13); }
+    } else if (e == 31) bits = sign | 0x7F800000u | (m << 13);
+    else bits = sign | ((e + 112u) << 23) | (m << 13);
+    float f; std::memcpy(&f, &bits, 4); return f;
+}
+
+struct ExrChannel { std::string name; int type; };   // 0 UINT, 1 HALF, 2 FLOAT
+
+// undo the ZIP/RLE block post-processing: delta predictor, then de-interleave of the two halves
+void exr_unpredict_reorder(std::vector<uint8_t>& buf, std::vector<uint8_t>& tmp) {
+    const size_t n = buf.size();
+    for (size_t i = 1; i < n; i++) buf[i] = (uint8_t)(buf[i - 1] + buf[i] - 128);
+    tmp.resize(n);
+    const size_t half = (n + 1) / 2;
+    for (size_t i = 0, a = 0, b = half; i < n; ) { tmp[i++] = buf[a++]; if (i < n) tmp[i++] = buf[b++]; }
+    buf.swap(tmp);
+}
+bool exr_rle_decode(const uint8_t* src, size_t n, std::vector<uint8_t>& out, size_t expected) {
+    out.clear(); out.reserve(expected);
+    size_t i = 0;
+    while (i < n) {
+        const int c = (int8_t)src[i++];
+        if (c < 0) { const size_t len = (size_t)(-c); if (i + len > n) return false; out.insert(out.end(), src + i, src + i + len); i += len; }
+        else { if (i >= n) return false; out.insert(out.end(), (size_t)c + 1, src[i++]); }
+        if (out.size() > expected) return false;
+    }
+    return out.size() == expected;
+}
+}  // namespace
+
+bool load_exr(const std::string& path, std::vector<float>& rgba, uint32_t& w, uint32_t& h, std::string& err) {
+    std::vector<uint8_t> f;
+    if (!read_file(path, f, err)) return false;
+    if (f.size() < 8 || f[0] != 0x76 || f[1] != 0x2F || f[2] != 0x31 || f[3] != 0x01) { err = "not an OpenEXR file"; return false; }
+    uint32_t version; std::memcpy(&version, f.data() + 4, 4);
+    if ((version & 0xFFu) != 2 || (version & 0x1A00u)) { err = "EXR: tiled, deep and multi-part files are not supported"; return false; }
+    size_t pos = 8;
+    std::vector<ExrChannel> channels;
+    int compression = -1, line_order = 0;
+    int32_t dw[4] = {0, 0, -1, -1};
+    auto cstr = [&](std::string& s) { s.clear(); while (pos < f.size() && f[pos]) s.push_back((char)f[pos++]); if (pos >= f.size()) return false; pos++; return true; };
+    for (;;) {
+        std::string name, type;
+        if (!cstr(name)) { err = "EXR: truncated header"; return false; }
+        if (name.empty()) break;
+        if (!cstr(type) || pos + 4 > f.size()) { err = "EXR: truncated header"; return false; }
+        uint32_t size; std::memcpy(&size, f.data() + pos, 4); pos += 4;
+        if (pos + size > f.size()) { err = "EXR: truncated attribute"; return false; }
+        const uint8_t* v = f.data() + pos;
+        if (name == "channels") {
+            size_t p = 0;
+            while (p < size && v[p]) {
+                ExrChannel c;
+                while (p < size && v[p]) c.name.push_back((char)v[p++]);
+                p++;
+                if (p + 16 > size) { err = "EXR: bad channel list"; return false; }
+                int32_t t, xs, ys; std::memcpy(&t, v + p, 4); std::memcpy(&xs, v + p + 8, 4); std::memcpy(&ys, v + p + 12, 4);
+                if (xs != 1 || ys != 1) { err = "EXR: subsampled channels are not supported"; return false; }
+                c.type = t; p += 16;
+                channels.push_back(c);
+            }
+        } else if (name == "compression" && size >= 1) compression = v[0];
+        else if (name == "dataWindow" && size >= 16) std::memcpy(dw, v, 16);
+        else if (name == "lineOrder" && size >= 1) line_order = v[0];
+        pos += size;
+    }
+    (void)line_order;   // the offset table is indexed by block number in increasing-y order for both INCREASING_Y and DECREASING_Y
+    if (channels.empty() || dw[2] < dw[0] || dw[3] < dw[1]) { err = "EXR: missing channels or dataWindow"; return false; }
+    int lines_per_block;
+    switch (compression) {
+        case 0: case 1: case 2: lines_per_block = 1; break;     // NONE, RLE, ZIPS
+        case 3: lines_per_block = 16; break;                    // ZIP
+        default: err = "EXR: compression " + std::to_string(compression) + " is not supported (NONE, RLE, ZIPS, ZIP only)"; return false;
+    }
+    w = (uint32_t)(dw[2] - dw[0] + 1); h = (uint32_t)(dw[3] - dw[1] + 1);
+    if ((uint64_t)w * h > (1ull << 28)) { err = "EXR: image too large"; return false; }
+    size_t bytes_per_line = 0;
+    for (const auto& c : channels) { if (c.type < 0 || c.type > 2) { err = "EXR: bad pixel type"; return false; } bytes_per_line += (size_t)w * (c.type == 1 ? 2 : 4); }
+    // destination component of each channel: R,G,B,A by name; a lone luminance channel Y feeds R, G and B
+    std::vector<int> dest(channels.size(), -1);
+    bool have_alpha = false, have_rgb = false;
+    for (size_t i = 0; i < channels.size(); i++) {
+        const std::string& n = channels[i].name;
+        if (n == "R") { dest[i] = 0; have_rgb = true; } else if (n == "G") { dest[i] = 1; have_rgb = true; } else if (n == "B") { dest[i] = 2; have_rgb = true; }
+        else if (n == "A") { dest[i] = 3; have_alpha = true; }
+    }
+    if (!have_rgb) for (size_t i = 0; i < channels.size(); i++) if (channels[i].name == "Y") dest[i] = 4;
+    const uint32_t blocks = (h + (uint32_t)lines_per_block - 1) / (uint32_t)lines_per_block;
+    if (pos + (size_t)blocks * 8 > f.size()) { err = "EXR: truncated offset table"; return false; }
+    const size_t table = pos;
+    rgba.assign((size_t)w * h * 4, 0.0f);
+    if (!have_alpha) for (size_t i = 0; i < (size_t)w * h; i++) rgba[i * 4 + 3] = 1.0f;
+    std::vector<uint8_t> block, tmp;
+    for (uint32_t b = 0; b < blocks; b++) {
+        uint64_t off; std::memcpy(&off, f.data() + table + (size_t)b * 8, 8);
+        if (off + 8 > f.size()) { err = "EXR: block offset out of range"; return false; }
+        int32_t y0, size; std::memcpy(&y0, f.data() + off, 4); std::memcpy(&size, f.data() + off + 4, 4);
+        if (size < 0 || off + 8 + (uint64_t)size > f.size() || y0 < dw[1] || y0 > dw[3]) { err = "EXR: bad block header"; return false; }
+        const uint32_t row0 = (uint32_t)(y0 - dw[1]);
+        const uint32_t rows = std::min<uint32_t>((uint32_t)lines_per_block, h - row0);
+        const size_t expected = bytes_per_line * rows;
+        const uint8_t* src = f.data() + off + 8;
+        if ((size_t)size == expected) block.assign(src, src + size);       // stored raw (also when compression did not shrink the block)
+        else if (compression == 2 || compression == 3) { if (!zlib_inflate(src, (size_t)size, block, expected, err)) return false; exr_unpredict_reorder(block, tmp); }
+        else if (compression == 1) { if (!exr_rle_decode(src, (size_t)size, block, expected)) { err = "EXR: bad RLE block"; return false; } exr_unpredict_reorder(block, tmp); }
+        else { err = "EXR: block size mismatch"; return false; }
+        const uint8_t* p = block.data();
+        for (uint32_t r = 0; r < rows; r++) {
+            float* dst_row = rgba.data() + (size_t)(row0 + r) * w * 4;
+            for (size_t c = 0; c < channels.size(); c++) {                  // within a scan line: channels in file (alphabetical) order, each contiguous
+                const int t = channels[c].type, d = dest[c];
+                for (uint32_t x = 0; x < w; x++) {
+                    float v;
+                    if (t == 1) { uint16_t hv; std::memcpy(&hv, p, 2); p += 2; v = half_to_float(hv); }
+                    else if (t == 2) { std::memcpy(&v, p, 4); p += 4; }
+                    else { uint32_t u; std::memcpy(&u, p, 4); p += 4; v = (float)u; }
+                    if (d >= 0 && d < 4) dst_row[(size_t)x * 4 + d] = v;
+                    else if (d == 4) { dst_row[(size_t)x * 4] = dst_row[(size_t)x * 4 + 1] = dst_row[(size_t)x * 4 + 2] = v; }
+                }
+            }
+        }
+    }
+    return true;
+}
+
+}  // namespace rt2ingest

@@ -2,6 +2,7 @@
 written here straight from the shader sources (the reference ships no vectors of its own),
 plus the host-side helpers of src/light_passes.rs:671-731 against hand-evaluated values."""
 import ctypes as C
+import os
 import math
 import struct
 
@@ -205,3 +206,39 @@ def test_camera_matrices_are_consistent():
     O.lib().orc_primary_ray(C.cast(C.byref(g), C.c_void_p), 256, 256, o, d)
     assert tuple(o) == (0.0, 0.0, pytest.approx(3.4))
     assert d[2] < -0.99
+
+
+def test_rt2_sys_declares_the_abi():
+    """bindings/rt2-sys/src/lib.rs (the Rust -sys crate of SURVEY §8f N4) cannot be compiled here (no cargo): check it against
+    include/rt2_abi.h textually — same function set, same argument counts, same buffer ids, flags and struct sizes."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "rt2_abi.h")).read()
+    rs = open(os.path.join(root, "bindings", "rt2-sys", "src", "lib.rs")).read()
+    code = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    c_fns = {m.group(1): (0 if m.group(2).strip() == "void" else m.group(2).count(",") + 1)
+             for m in re.finditer(r"\b(rt2_[a-z_0-9]+)\s*\(([^)]*)\)\s*;", code)}
+    rs_fns = {m.group(1): (0 if not m.group(2).strip() else m.group(2).count(":"))
+              for m in re.finditer(r"pub fn (rt2_[a-z_0-9]+)\(([^)]*)\)", rs)}
+    assert c_fns == rs_fns, set(c_fns.items()) ^ set(rs_fns.items())
+    c_bufs = {m.group(1): int(m.group(2)) for m in re.finditer(r"\b(RT2_BUF_[A-Z0-9_]+)\s*=\s*(\d+)", code)}
+    rs_bufs = {m.group(1): int(m.group(2)) for m in re.finditer(r"pub const (RT2_BUF_[A-Z0-9_]+): c_int = (\d+);", rs)}
+    assert c_bufs == rs_bufs
+    c_defs = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define (RT2_(?:LAUNCH|SECONDARY|FILTER|E)_[A-Z_]+|RT2_OK|RT2_ABI_VERSION|RT2_GCONST_SIZE)\s+(-?\d+)u?\b", code)}
+    rs_defs = {m.group(1): int(m.group(2)) for m in re.finditer(r"pub const (RT2_[A-Z_]+): (?:u32|c_int|usize) = (-?\d+);", rs) if not m.group(1).startswith("RT2_BUF_")}
+    rs_defs.pop("RT2_NEIGHBOR_OFFSET_COUNT", None)
+    assert c_defs == rs_defs, set(c_defs.items()) ^ set(rs_defs.items())
+    sizes = {m.group(1): int(m.group(2)) for m in re.finditer(r"size_of::<(rt2_[a-z_]+)>\(\) == (\d+)", rs)}
+    ct = {"rt2_vertex": _ffi.Vertex, "rt2_geometry_info": _ffi.GeometryInfo, "rt2_hit_record": _ffi.HitRecord, "rt2_launch_params": _ffi.LaunchParams,
+          "rt2_stats": _ffi.Stats}
+    for name, t in ct.items():
+        assert sizes[name] == C.sizeof(t), name
+    assert sizes["rt2_light_info"] == 48 and sizes["rt2_packed_di_reservoir"] == 24 and sizes["rt2_packed_gi_reservoir"] == 32 and sizes["rt2_secondary_gbuffer_data"] == 48
+    # every struct field of the header appears, in order, in the Rust struct of the same name
+    for sm in re.finditer(r"typedef struct (rt2_[a-z_]+) \{(.*?)\} \1;", code, flags=re.S):
+        name, body = sm.group(1), sm.group(2)
+        c_fields = [re.sub(r"\[.*", "", f.strip().split()[-1].lstrip("*")) for f in body.split(";") if f.strip()]
+        rm = re.search(r"pub struct %s \{(.*?)\n\}" % name, rs, flags=re.S)
+        assert rm, name
+        rs_fields = re.findall(r"pub ([a-z_0-9]+):", rm.group(1))
+        assert c_fields == rs_fields, (name, c_fields, rs_fields)
