@@ -121,6 +121,8 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs a) {
 // is back at the depth it was entered with.  Lanes at different levels share every node step.
 // GENERIC: rays carry their own [tmin, tmax] (ray0 = o|tmin, ray1 = d|tmax) instead of K1's constants.
 // The closest hit is a total order (hit_closer), so the result does not depend on any of this scheduling.
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED = false, bool GENERIC = false>
 __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
     const uint32_t count = *a.count;
@@ -168,6 +170,14 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
                 if (ngroup.y > 0x00FFFFFFu) {
                     const Node8* level = (INSTANCED && inst == 0xFFFFFFFFu) ? a.tlas_nodes : a.blas_nodes;
                     cwbvh_node_step(level, rp, tmin, fminf(best.t, tmax), ngroup, tgroup, stack, sp);
+#ifdef RT2_TRACE_PREFETCH_NODE   // measured -3.4 % on C2 (the address arithmetic costs more than the latency it hides): off
+                    // the node this lane visits next is known now; its 80 bytes are wanted only after the triangle phase
+                    if (ngroup.y > 0x00FFFFFFu) {
+                        const uint32_t nslot = (rt2_fhs(ngroup.y) - 24u) ^ rp.oct_inv;
+                        const uint32_t nrel = rt2_popc((ngroup.y & 0xFFu) & ~(0xFFFFFFFFu << nslot));
+                        prefetch_l1(level + (ngroup.x + nrel));
+                    }
+#endif
                 } else {
                     tgroup = ngroup;
                     ngroup = make_uint2(0u, 0u);
@@ -196,7 +206,10 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
                     const int in_loop = __popc(__activemask());
                     while (tgroup.y != 0u) {
                         if (POSTPONE_PCT > 0) {
-                            if (__popc(__activemask()) * 100 < in_loop * POSTPONE_PCT && sp < postpone_limit) { stack[sp++] = tgroup; break; }
+                            if (__popc(__activemask()) * 100 < in_loop * POSTPONE_PCT && sp < postpone_limit) {
+                                prefetch_l1(a.tris + (tgroup.x + rt2_fhs(tgroup.y)));      // postponed: by the time it is tested it sits in L1 (+0.5-1 %)
+                                stack[sp++] = tgroup; break;
+                            }
                         }
                         const uint32_t ti = rt2_fhs(tgroup.y);
                         tgroup.y &= ~(1u << ti);
