@@ -484,9 +484,10 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
         // counters.  While one chain's trace kernel drains its last long rays (a ~45 us tail per launch that does not
         // shrink with the wavefront), the other chains' kernels fill the SMs.  Per-kernel event timing (LAUNCH_PROFILE)
         // needs serial kernels, so it runs one chain.
-        // measured (profiles/r01c): C2 2 chains +4 % at 2 M pixels, 4 chains +13 % at 260 k pixels (one of 8 ranks); a scene whose
-        // trace launches last only microseconds (C1, 32 triangles) is launch-rate bound and loses 10-25 % to the extra launches
-        const uint32_t auto_chains = s.num_tris < 4096u ? 1u : ((uint64_t)band.width * band.local_rows >= (1u << 20) ? 2u : 4u);
+        // measured on C2 (tools_band_probe.py, Mrays/s for 1 / 2 / 4 chains): 2.07 M pixels 2231 / 2322 / 2232, 1.04 M 2083 / 2156 / 2029,
+        // 518 k 1856 / 1899 / 1884, 259 k (one of 8 ranks) 1488 / 1662 / 1754; a scene whose trace launches last only
+        // microseconds (C1, 32 triangles) is launch-rate bound and loses 10-25 % to the extra launches
+        const uint32_t auto_chains = s.num_tris < 4096u ? 1u : ((uint64_t)band.width * band.local_rows >= 400000u ? 2u : 4u);
         uint32_t chains = profile ? 1u : std::max(1u, std::min(ctx->chains ? ctx->chains : auto_chains, RT2_MAX_CHAINS));
         uint32_t per = ((padded + chains - 1) / chains + 255u) & ~255u;
         while (chains > 1u && (uint64_t)per * (chains - 1) >= padded) { chains--; per = ((padded + chains - 1) / chains + 255u) & ~255u; }
@@ -501,18 +502,26 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
             RT2_CUDA(ctx, cudaEventRecord(ctx->chain_fork, ctx->stream));
         }
         const size_t counter_stride = 2 * ((size_t)iterations + 2);
+        // Launches are enqueued iteration by iteration across the chains (not chain by chain), so that all chains advance
+        // together and finish together instead of the last chain running alone at the end of the frame.
+        struct Chain { cudaStream_t st; uint32_t first, end; uint32_t* cnt; uint32_t* q[2]; int shade_blocks; } ch[RT2_MAX_CHAINS];
         for (uint32_t c = 0; c < chains; c++) {
-            cudaStream_t st = c == 0 ? ctx->stream : ctx->chain_streams[c];
-            if (c != 0) RT2_CUDA(ctx, cudaStreamWaitEvent(st, ctx->chain_fork, 0));
-            const uint32_t first = c * per, end = std::min(padded, first + per);
-            uint32_t* cnt = f.counters + 4 + c * counter_stride;
-            uint32_t* q[2] = {f.queue0 + first, f.queue1 + first};
-            const int shade_blocks = std::max(1, std::min(shade_blocks_full, (int)((end - first + 255u) / 256u)));
-            a.queue_out = q[0]; a.count_out = cnt;
-            k_k1_init<<<(end - first + 255) / 256, 256, 0, st>>>(a, first, end); launches++;
-            for (uint32_t it = 0; it < iterations; it++) {
+            Chain& k = ch[c];
+            k.st = c == 0 ? ctx->stream : ctx->chain_streams[c];
+            if (c != 0) RT2_CUDA(ctx, cudaStreamWaitEvent(k.st, ctx->chain_fork, 0));
+            k.first = c * per; k.end = std::min(padded, k.first + per);
+            k.cnt = f.counters + 4 + c * counter_stride;
+            k.q[0] = f.queue0 + k.first; k.q[1] = f.queue1 + k.first;
+            k.shade_blocks = std::max(1, std::min(shade_blocks_full, (int)((k.end - k.first + 255u) / 256u)));
+            a.queue_out = k.q[0]; a.count_out = k.cnt;
+            k_k1_init<<<(k.end - k.first + 255) / 256, 256, 0, k.st>>>(a, k.first, k.end); launches++;
+        }
+        for (uint32_t it = 0; it < iterations; it++) {
+            for (uint32_t c = 0; c < chains; c++) {
+                const Chain& k = ch[c];
+                cudaStream_t st = k.st;
                 if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], st));
-                t.queue = q[it & 1]; t.count = cnt + 2 * it; t.head = cnt + 2 * it + 1;
+                t.queue = k.q[it & 1]; t.count = k.cnt + 2 * it; t.head = k.cnt + 2 * it + 1;
                 if (s.num_instances) {
                     // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
                     const bool unified = ctx->trace_variant != 0 && s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE;
@@ -522,13 +531,13 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
                     g_trace_variants[ctx->trace_variant]<<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, st>>>(t);
                 }
                 if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], st));
-                a.queue_in = q[it & 1]; a.count_in = t.count; a.queue_out = q[(it + 1) & 1]; a.count_out = cnt + 2 * (it + 1);
-                k_k1_shade<<<shade_blocks, 256, 0, st>>>(a);
+                a.queue_in = k.q[it & 1]; a.count_in = t.count; a.queue_out = k.q[(it + 1) & 1]; a.count_out = k.cnt + 2 * (it + 1);
+                k_k1_shade<<<k.shade_blocks, 256, 0, st>>>(a);
                 if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 2], st));
                 launches += 2;
             }
-            if (c != 0) { RT2_CUDA(ctx, cudaEventRecord(ctx->chain_join[c], st)); RT2_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->chain_join[c], 0)); }
         }
+        for (uint32_t c = 1; c < chains; c++) { RT2_CUDA(ctx, cudaEventRecord(ctx->chain_join[c], ch[c].st)); RT2_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->chain_join[c], 0)); }
     }
     RT2_CUDA(ctx, cudaGetLastError());
     ctx->stats.kernel_launches = launches;
