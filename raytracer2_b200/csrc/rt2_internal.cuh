@@ -130,6 +130,7 @@ struct rt2_ctx {
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
     int trace_blocks_per_sm[3] = {1, 1, 1};             // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level
     int trace_variant = 0;
+    uint32_t rays_per_lane = 0; bool rays_per_lane_set = false;   // cap of the persistent trace grid for small wavefronts (RT2_RAYS_PER_LANE overrides the rule)
     uint32_t chains = 0;                                 // wavefront chains of the path tracer; 0 = by frame size (RT2_CHAINS overrides)
     cudaStream_t chain_streams[8] = {}; cudaEvent_t chain_join[8] = {}; cudaEvent_t chain_fork = nullptr;
     bool gi_megakernels = false;                         // RT2_GI_MEGAKERNEL=1: K4/K5 with inlined traversal instead of the ray-queue kernel (A/B)

@@ -484,10 +484,19 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
         // counters.  While one chain's trace kernel drains its last long rays (a ~45 us tail per launch that does not
         // shrink with the wavefront), the other chains' kernels fill the SMs.  Per-kernel event timing (LAUNCH_PROFILE)
         // needs serial kernels, so it runs one chain.
-        // measured on C2 (tools_band_probe.py, Mrays/s for 1 / 2 / 4 chains): 2.07 M pixels 2231 / 2322 / 2232, 1.04 M 2083 / 2156 / 2029,
-        // 518 k 1856 / 1899 / 1884, 259 k (one of 8 ranks) 1488 / 1662 / 1754; a scene whose trace launches last only
-        // microseconds (C1, 32 triangles) is launch-rate bound and loses 10-25 % to the extra launches
-        const uint32_t auto_chains = s.num_tris < 4096u ? 1u : ((uint64_t)band.width * band.local_rows >= 400000u ? 2u : 4u);
+        // Small wavefronts (one rank's share of a sharded frame) also get a smaller persistent grid per chain: lane refill only
+        // works while the queue is longer than the grid, so each chain launches about rays / (128 * rays_per_lane) blocks and the
+        // chains together, not each alone, fill the resident block slots.
+        // Measured on C2 (profiles/r01c_chain_sweep.txt, Mrays/s per GPU, 1 chain / 2 chains full grid / 8 chains capped grid):
+        // 2.07 M pixels 2231 / 2322 / 2184, 1.04 M 2083 / 2165 / 2121, 691 k - / 1991 / 2060, 518 k 1856 / 1899 / 2014,
+        // 346 k - / 1773 / 1882, 259 k (one of 8 ranks) 1488 / 1662 / 1752.  A scene whose trace launches last only microseconds
+        // (C1, 32 triangles) is launch-rate bound and loses 10-25 % to the extra launches: one chain.
+        const uint64_t pixels = (uint64_t)band.width * band.local_rows;
+        const int full_blocks = ctx->trace_blocks_per_sm[s.num_instances ? 1 : 0] * ctx->num_sms;
+        const bool small_wave = pixels < 900000u;
+        const uint32_t auto_chains = s.num_tris < 4096u ? 1u : (small_wave ? 8u : 2u);
+        const uint32_t rays_per_lane = ctx->rays_per_lane_set ? ctx->rays_per_lane
+                                     : (small_wave && s.num_tris >= 4096u ? std::max<uint32_t>(1u, (uint32_t)(pixels / ((uint64_t)full_blocks * 128u))) : 0u);
         uint32_t chains = profile ? 1u : std::max(1u, std::min(ctx->chains ? ctx->chains : auto_chains, RT2_MAX_CHAINS));
         uint32_t per = ((padded + chains - 1) / chains + 255u) & ~255u;
         while (chains > 1u && (uint64_t)per * (chains - 1) >= padded) { chains--; per = ((padded + chains - 1) / chains + 255u) & ~255u; }
@@ -504,7 +513,7 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
         const size_t counter_stride = 2 * ((size_t)iterations + 2);
         // Launches are enqueued iteration by iteration across the chains (not chain by chain), so that all chains advance
         // together and finish together instead of the last chain running alone at the end of the frame.
-        struct Chain { cudaStream_t st; uint32_t first, end; uint32_t* cnt; uint32_t* q[2]; int shade_blocks; } ch[RT2_MAX_CHAINS];
+        struct Chain { cudaStream_t st; uint32_t first, end; uint32_t* cnt; uint32_t* q[2]; int shade_blocks, trace_blocks; } ch[RT2_MAX_CHAINS];
         for (uint32_t c = 0; c < chains; c++) {
             Chain& k = ch[c];
             k.st = c == 0 ? ctx->stream : ctx->chain_streams[c];
@@ -513,6 +522,10 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
             k.cnt = f.counters + 4 + c * counter_stride;
             k.q[0] = f.queue0 + k.first; k.q[1] = f.queue1 + k.first;
             k.shade_blocks = std::max(1, std::min(shade_blocks_full, (int)((k.end - k.first + 255u) / 256u)));
+            // persistent grid: every resident slot, unless the chain is so small that each lane would get fewer than
+            // rays_per_lane rays — lane refill needs a queue longer than the grid (RT2_RAYS_PER_LANE, 0 = always the full grid)
+            k.trace_blocks = full_blocks;
+            if (rays_per_lane && !profile) k.trace_blocks = std::max(ctx->num_sms, std::min(full_blocks, (int)((k.end - k.first) / (128u * rays_per_lane)) + 1));
             a.queue_out = k.q[0]; a.count_out = k.cnt;
             k_k1_init<<<(k.end - k.first + 255) / 256, 256, 0, k.st>>>(a, k.first, k.end); launches++;
         }
@@ -525,10 +538,10 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
                 if (s.num_instances) {
                     // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
                     const bool unified = ctx->trace_variant != 0 && s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE;
-                    if (unified) k_trace_dyn<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, st>>>(t);
+                    if (unified) k_trace_dyn<20, 4, 8, true><<<k.trace_blocks, 128, 0, st>>>(t);
                     else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, st>>>(t);
                 } else {
-                    g_trace_variants[ctx->trace_variant]<<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, st>>>(t);
+                    g_trace_variants[ctx->trace_variant]<<<k.trace_blocks, 128, 0, st>>>(t);
                 }
                 if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], st));
                 a.queue_in = k.q[it & 1]; a.count_in = t.count; a.queue_out = k.q[(it + 1) & 1]; a.count_out = k.cnt + 2 * (it + 1);
@@ -567,6 +580,7 @@ int render_init(rt2_ctx* ctx) {
     int b0 = 0, b1 = 0;
     ctx->trace_variant = RT2_DEFAULT_TRACE_VARIANT;
     if (const char* e = getenv("RT2_GI_MEGAKERNEL")) ctx->gi_megakernels = atoi(e) != 0;
+    if (const char* e = getenv("RT2_RAYS_PER_LANE")) { int v = atoi(e); if (v >= 0 && v <= 64) { ctx->rays_per_lane = (uint32_t)v; ctx->rays_per_lane_set = true; } }
     if (const char* e = getenv("RT2_CHAINS")) { int v = atoi(e); if (v >= 1) ctx->chains = (uint32_t)v; }
     if (const char* e = getenv("RT2_TRACE_VARIANT")) { int v = atoi(e); if (v >= 0 && v < g_num_trace_variants) ctx->trace_variant = v; }
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, g_trace_variants[ctx->trace_variant], 128, 0));

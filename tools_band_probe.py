@@ -5,7 +5,7 @@ import raytracer2_b200 as rt
 W, H = 1920, 1080
 sc = rt.Scene(rt.SCENE_HALL, 1.0, 512, 0)
 g = rt.default_gconst(sc.camera(W / H), W, H, sc.num_lights); g.refrence_mode = 1
-for chains in [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "0,1,2,4,6,8").split(",")]:
+for chains in [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "0").split(",")]:
     if chains: os.environ["RT2_CHAINS"] = str(chains)
     else: os.environ.pop("RT2_CHAINS", None)
     ctx = rt.Renderer(0)
