@@ -10,8 +10,8 @@ A step is one rt2_render of the whole 1080p frame.  With N ranks the frame is sp
 16-row bands, every rank traces 4 spp x N (so per-GPU work is fixed: weak scaling), and
 the fp32 bands are all-gathered with NCCL over NVLink inside the timed region.
 `value` is device-timed with inputs resident; `e2e` goes through the C ABI with host buffers:
-rt2_set_constants (host -> device) + rt2_render + rt2_read of the rgba16f accumulation image into
-pinned host memory, every step.
+rt2_set_constants (pinned host -> device) + rt2_render + rt2_read_async of the rgba16f accumulation image into
+pinned host memory, every step, two frames in flight (the transfer of frame n overlaps the render of frame n+1).
 """
 import argparse
 import ctypes as C
@@ -231,9 +231,13 @@ def main():
     trace_ms, shade_ms, trace_launches = pst.trace_ns / 1e6, pst.shade_ns / 1e6, max(1, pst.trace_launches)
 
     # ---- e2e through the C ABI with host buffers --------------------------------------------------------------
-    host_out = torch.empty(W * H * 4, dtype=torch.float16).pin_memory()
+    # Two frames in flight, as the reference's swapchain loop has (src/context.rs:30,639-694): frame n's image travels to
+    # pinned host memory on the context's copy stream (rt2_read_async) while frame n+1 renders; every step still uploads its
+    # GConst from pinned staging and reads its result back, and the timed region ends only after the last transfer landed.
+    host_out = [torch.empty(W * H * 4, dtype=torch.float16).pin_memory() for _ in range(2)]
     for i in range(2):
-        lp.update_uniform(g); step(200 + i); ctx.read_into(rt.BUF_DIFFUSE_F16, host_out.data_ptr(), W * H * 8)
+        lp.update_uniform(g); step(200 + i); ctx.read_into_async(rt.BUF_DIFFUSE_F16, host_out[i & 1].data_ptr(), W * H * 8)
+    ctx.sync()
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
@@ -241,10 +245,12 @@ def main():
     e0.record()
     for i in range(args.steps):
         g.frame = 300 + i
-        lp.update_uniform(g)                                                   # host -> device, 1424 B
+        lp.update_uniform(g)                                                                  # pinned host -> device, 1424 B
         step(300 + i)
-        ctx.read_into(rt.BUF_DIFFUSE_F16, host_out.data_ptr(), W * H * 8)      # device -> pinned host, syncs
+        ctx.read_into_async(rt.BUF_DIFFUSE_F16, host_out[i & 1].data_ptr(), W * H * 8)        # device -> pinned host
+    ctx.read_fence()                                                                          # e1 waits for every transfer
     e1.record()
+    ctx.sync()
     torch.cuda.synchronize()
     e2e_ms = e0.elapsed_time(e1)
 

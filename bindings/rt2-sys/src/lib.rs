@@ -258,6 +258,8 @@ extern "C" {
     pub fn rt2_sync(ctx: *mut rt2_ctx) -> c_int;
     pub fn rt2_buffer_size(ctx: *mut rt2_ctx, which: c_int) -> usize;
     pub fn rt2_read(ctx: *mut rt2_ctx, which: c_int, dst: *mut c_void, nbytes: usize) -> c_int;
+    pub fn rt2_read_async(ctx: *mut rt2_ctx, which: c_int, dst: *mut c_void, nbytes: usize) -> c_int;
+    pub fn rt2_read_fence(ctx: *mut rt2_ctx) -> c_int;
     pub fn rt2_copy_to_device(ctx: *mut rt2_ctx, which: c_int, device_dst: *mut c_void, nbytes: usize, row0: u32, row1: u32) -> c_int;
     pub fn rt2_pack_bands(ctx: *mut rt2_ctx, which: c_int, device_dst: *mut c_void, nbytes: usize, band_rows: u32, band_rank: u32, band_world: u32) -> c_int;
     pub fn rt2_write(ctx: *mut rt2_ctx, which: c_int, src: *const c_void, nbytes: usize) -> c_int;

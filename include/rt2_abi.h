@@ -294,6 +294,13 @@ int  rt2_postprocess(rt2_ctx* ctx, uint32_t frame);
 int  rt2_sync(rt2_ctx* ctx);
 size_t rt2_buffer_size(rt2_ctx* ctx, int which);                       /* bytes, 0 if absent      */
 int  rt2_read(rt2_ctx* ctx, int which, void* dst, size_t nbytes);      /* device -> host, syncs   */
+/* Frame-in-flight read (the reference presents one swapchain image while it records the next, src/context.rs:30,
+ * 639-694): snapshots the buffer on the context's stream and sends the snapshot to `dst` (pinned host memory for a
+ * truly asynchronous transfer) on the context's copy stream, so the next rt2_render overlaps the PCIe transfer.
+ * Up to two reads are in flight; `dst` is valid after rt2_sync.  rt2_read_fence makes later work on the context's
+ * stream (e.g. a timing event) wait for the reads issued so far without blocking the host. */
+int  rt2_read_async(rt2_ctx* ctx, int which, void* dst, size_t nbytes);
+int  rt2_read_fence(rt2_ctx* ctx);
 /* device -> device copy on the context's stream into caller-owned device memory (used to hand
  * row bands to NCCL without a host round trip). `row0,row1` select rows [row0,row1) of a W x H
  * buffer; pass 0,0 for the whole buffer. */

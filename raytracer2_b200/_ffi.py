@@ -210,6 +210,8 @@ ABI_SYMBOLS = {
     "rt2_sync": (C.c_int, [VP]),
     "rt2_buffer_size": (C.c_size_t, [VP, C.c_int]),
     "rt2_read": (C.c_int, [VP, C.c_int, VP, C.c_size_t]),
+    "rt2_read_async": (C.c_int, [VP, C.c_int, VP, C.c_size_t]),
+    "rt2_read_fence": (C.c_int, [VP]),
     "rt2_copy_to_device": (C.c_int, [VP, C.c_int, VP, C.c_size_t, u32, u32]),
     "rt2_pack_bands": (C.c_int, [VP, C.c_int, VP, C.c_size_t, u32, u32, u32]),
     "rt2_write": (C.c_int, [VP, C.c_int, VP, C.c_size_t]),

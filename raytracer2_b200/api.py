@@ -169,6 +169,13 @@ class Renderer:
     def read_into(self, which: int, dst_ptr: int, nbytes: int):
         self._check(self._lib.rt2_read(self._ctx, which, C.c_void_p(dst_ptr), nbytes), "rt2_read")
 
+    def read_into_async(self, which: int, dst_ptr: int, nbytes: int):
+        """Frame-in-flight read into (pinned) host memory; valid after sync().  See rt2_read_async."""
+        self._check(self._lib.rt2_read_async(self._ctx, which, C.c_void_p(dst_ptr), nbytes), "rt2_read_async")
+
+    def read_fence(self):
+        self._check(self._lib.rt2_read_fence(self._ctx), "rt2_read_fence")
+
     def write(self, which: int, arr: np.ndarray):
         a = np.ascontiguousarray(arr)
         self._check(self._lib.rt2_write(self._ctx, which, a.ctypes.data_as(C.c_void_p), a.nbytes), "rt2_write")

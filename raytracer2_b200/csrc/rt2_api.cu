@@ -54,8 +54,16 @@ int rt2_create(int cuda_device, rt2_ctx** out) {
     if ((e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess) { delete ctx; return fail(nullptr, RT2_E_CUDA, cudaGetErrorString(e)); }
     ctx->stream = ctx->own_stream;
     if ((e = cudaMalloc((void**)&ctx->d_gconst, sizeof(rt2_gconst))) != cudaSuccess) { cudaStreamDestroy(ctx->own_stream); delete ctx; return fail(nullptr, RT2_E_CUDA, cudaGetErrorString(e)); }
+    for (int i = 0; i < RT2_FRAMES_IN_FLIGHT && e == cudaSuccess; i++) {
+        if ((e = cudaEventCreateWithFlags(&ctx->gconst_done[i], cudaEventDisableTiming)) != cudaSuccess) break;
+        if ((e = cudaEventCreateWithFlags(&ctx->snap_ready[i], cudaEventDisableTiming)) != cudaSuccess) break;
+        e = cudaEventCreateWithFlags(&ctx->read_done[i], cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaHostAlloc((void**)&ctx->h_gconst_ring, RT2_FRAMES_IN_FLIGHT * sizeof(rt2_gconst), cudaHostAllocDefault);
+    if (e != cudaSuccess) { std::string m = cudaGetErrorString(e); rt2_destroy(ctx); return fail(nullptr, RT2_E_CUDA, m); }
     int rc = render_init(ctx);
-    if (rc != RT2_OK) { std::string m = ctx->last_error; cudaFree(ctx->d_gconst); cudaStreamDestroy(ctx->own_stream); delete ctx; return fail(nullptr, rc, m); }
+    if (rc != RT2_OK) { std::string m = ctx->last_error; rt2_destroy(ctx); return fail(nullptr, rc, m); }
     *out = ctx;
     return RT2_OK;
 }
@@ -64,6 +72,14 @@ int rt2_destroy(rt2_ctx* ctx) {
     if (!ctx) return RT2_E_INVALID;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    for (int i = 0; i < RT2_FRAMES_IN_FLIGHT; i++) {
+        if (ctx->gconst_done[i]) cudaEventDestroy(ctx->gconst_done[i]);
+        if (ctx->snap_ready[i]) cudaEventDestroy(ctx->snap_ready[i]);
+        if (ctx->read_done[i]) cudaEventDestroy(ctx->read_done[i]);
+        if (ctx->snap[i]) cudaFree(ctx->snap[i]);
+    }
+    if (ctx->h_gconst_ring) cudaFreeHost(ctx->h_gconst_ring);
     scene_release(ctx); frame_release(ctx); passes_release(ctx);
     for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
     if (ctx->d_gconst) cudaFree(ctx->d_gconst);
@@ -97,10 +113,14 @@ int rt2_set_constants(rt2_ctx* ctx, const void* gconst, size_t nbytes) {
     RT2_GUARD(ctx);
     if (!gconst || nbytes != RT2_GCONST_SIZE) return fail(ctx, RT2_E_INVALID, "GConst must be exactly 1424 bytes");
     memcpy(&ctx->gconst, gconst, RT2_GCONST_SIZE);
-    // stream-ordered copy from the context-owned host copy (replaces the UBO upload, light_passes.rs:665-668);
-    // sync so that a second rt2_set_constants cannot overwrite the staging copy in flight
-    RT2_CUDA(ctx, cudaMemcpyAsync(ctx->d_gconst, &ctx->gconst, RT2_GCONST_SIZE, cudaMemcpyHostToDevice, ctx->stream));
-    RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    // stream-ordered copy from a context-owned pinned staging slot (replaces the UBO upload, light_passes.rs:665-668).
+    // The slots form a ring, one per frame in flight: the call waits only for the copy that last used its slot, so the
+    // host can record frame n+1 while frame n still renders (the reference's per-swapchain-image command buffers).
+    const uint32_t slot = ctx->gconst_next++ % RT2_FRAMES_IN_FLIGHT;
+    RT2_CUDA(ctx, cudaEventSynchronize(ctx->gconst_done[slot]));
+    memcpy(&ctx->h_gconst_ring[slot], gconst, RT2_GCONST_SIZE);
+    RT2_CUDA(ctx, cudaMemcpyAsync(ctx->d_gconst, &ctx->h_gconst_ring[slot], RT2_GCONST_SIZE, cudaMemcpyHostToDevice, ctx->stream));
+    RT2_CUDA(ctx, cudaEventRecord(ctx->gconst_done[slot], ctx->stream));
     ctx->have_gconst = true;
     return RT2_OK;
 }
@@ -130,6 +150,7 @@ int rt2_trace_primary(rt2_ctx* ctx, const rt2_launch_params* params) {
 int rt2_sync(rt2_ctx* ctx) {
     RT2_GUARD(ctx);
     RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->reads_pending) { RT2_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream)); ctx->reads_pending = false; }
     RT2_CUDA(ctx, cudaGetLastError());
     return RT2_OK;
 }
@@ -166,6 +187,39 @@ int rt2_read(rt2_ctx* ctx, int which, void* dst, size_t nbytes) {
     if (nbytes != b) return fail(ctx, RT2_E_INVALID, "size mismatch: buffer is " + std::to_string(b) + " bytes");
     RT2_CUDA(ctx, cudaMemcpyAsync(dst, p, b, cudaMemcpyDeviceToHost, ctx->stream));
     RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT2_OK;
+}
+
+// Frame-in-flight read: the buffer is snapshotted on the context's stream (device -> device, microseconds) and the
+// snapshot travels to the host on the context's copy stream, so the next rt2_render overlaps the PCIe transfer.
+int rt2_read_async(rt2_ctx* ctx, int which, void* dst, size_t nbytes) {
+    RT2_GUARD(ctx);
+    void* p; size_t b = 0;
+    if (!dst) return fail(ctx, RT2_E_INVALID, "dst is NULL");
+    if (!buffer_lookup(ctx, which, &p, &b)) return fail(ctx, RT2_E_STATE, "buffer not allocated");
+    if (nbytes != b) return fail(ctx, RT2_E_INVALID, "size mismatch: buffer is " + std::to_string(b) + " bytes");
+    const uint32_t i = ctx->snap_next++ % RT2_FRAMES_IN_FLIGHT;
+    RT2_CUDA(ctx, cudaEventSynchronize(ctx->read_done[i]));          // the transfer that last used this snapshot (two reads ago)
+    if (ctx->snap_bytes[i] < b) {
+        if (ctx->snap[i]) { RT2_CUDA(ctx, cudaFree(ctx->snap[i])); ctx->device_bytes -= ctx->snap_bytes[i]; ctx->snap[i] = nullptr; ctx->snap_bytes[i] = 0; }
+        if (cudaMalloc(&ctx->snap[i], b) != cudaSuccess) { cudaGetLastError(); return fail(ctx, RT2_E_OOM, "out of device memory for the read snapshot"); }
+        ctx->snap_bytes[i] = b; ctx->device_bytes += b;
+    }
+    RT2_CUDA(ctx, cudaMemcpyAsync(ctx->snap[i], p, b, cudaMemcpyDeviceToDevice, ctx->stream));
+    RT2_CUDA(ctx, cudaEventRecord(ctx->snap_ready[i], ctx->stream));
+    RT2_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->snap_ready[i], 0));
+    RT2_CUDA(ctx, cudaMemcpyAsync(dst, ctx->snap[i], b, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    RT2_CUDA(ctx, cudaEventRecord(ctx->read_done[i], ctx->copy_stream));
+    ctx->reads_pending = true;
+    return RT2_OK;
+}
+
+// Orders everything enqueued on the context's stream after this call behind the asynchronous reads issued so far
+// (an event recorded on the stream afterwards then also covers their transfers).  Does not block the host.
+int rt2_read_fence(rt2_ctx* ctx) {
+    RT2_GUARD(ctx);
+    if (!ctx->reads_pending) return RT2_OK;
+    for (int i = 0; i < RT2_FRAMES_IN_FLIGHT; i++) RT2_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->read_done[i], 0));
     return RT2_OK;
 }
 

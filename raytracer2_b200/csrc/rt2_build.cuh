@@ -91,7 +91,9 @@ RT2_HD float box_half_area(float lx, float ly, float lz, float hx, float hy, flo
 
 // 4a. PLOC nearest-neighbour search for cluster position i (radius R). Distance = half area of the
 // union box; ties are broken by (min index, max index) so the globally best pair is always mutual.
+#ifndef RT2_PLOC_RADIUS
 #define RT2_PLOC_RADIUS 16
+#endif
 RT2_HD uint32_t ploc_nearest(const Bvh2& b, const uint32_t* clusters, uint32_t n, uint32_t i) {
     const uint32_t ci = clusters[i];
     const float4 li = b.lo[ci], hi_ = b.hi[ci];
@@ -134,7 +136,9 @@ RT2_HD uint32_t ploc_merge(const Bvh2& b, uint32_t* clusters, const uint32_t* ne
 }
 
 // ---- 5. collapse -------------------------------------------------------------------------------------------
+#ifndef RT2_LEAF_MAX
 #define RT2_LEAF_MAX 3u
+#endif
 
 struct CollapseCtx {
     Bvh2 bvh2;

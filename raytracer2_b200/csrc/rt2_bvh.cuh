@@ -82,14 +82,27 @@ RT2_HD uint32_t sign_extend_s8x4(uint32_t x) {
 // value; measured on B200 it LOSES 3 % on C2 (2142 vs 2212 Mrays/s): the kernel is issue/latency bound before it is
 // XU bound.  Kept behind RT2_BYTE_MAGIC for the record.
 RT2_HD float byte_to_float(uint32_t w, uint32_t i) {
-#if defined(__CUDA_ARCH__) && defined(RT2_NODE_TEST_FOLDED)
-    return u2f(__byte_perm(w, 0x4B000000u, 0x7540u | i));          // 2^23 + q: cwbvh_node_step folds the 2^23 into its offsets
-#elif defined(__CUDA_ARCH__) && defined(RT2_BYTE_MAGIC)
+#if defined(__CUDA_ARCH__) && defined(RT2_BYTE_MAGIC)
     return u2f(__byte_perm(w, 0x4B000000u, 0x7540u | i)) - 8388608.0f;
 #else
     return (float)rt2_byte(w, i);
 #endif
 }
+// 2^23 + q through the byte permute unit (ALU pipe) instead of I2F.U8 (XU pipe); cwbvh_node_step folds the 2^23 into
+// the plane offset of the planes it dequantises this way (RT2_NODE_FOLD_MASK).
+RT2_HD float byte_to_float_biased(uint32_t w, uint32_t i) {
+#ifdef __CUDA_ARCH__
+    return u2f(__byte_perm(w, 0x4B000000u, 0x7540u | i));
+#else
+    return u2f(0x4B000000u | rt2_byte(w, i));
+#endif
+}
+// Which of the six slab planes (bit 0..2 = near x,y,z; bit 3..5 = far x,y,z) are dequantised with the folded 2^23 form
+// on the device.  0 = all through I2F.U8 (the oracle's arithmetic), 63 = none.  Measured on B200, C2 (gpurun A/B, Mrays/s):
+// 0: 2318 | 9 (x near+far): 2346 | 5, 6: 2340 | 36, 7, 13, 3: 2322-2334 | 1: 2312 | 27: 2190 | 56: 2182 | 63: 2147.
+#ifndef RT2_NODE_FOLD_MASK
+#define RT2_NODE_FOLD_MASK 9
+#endif
 
 struct TraceRay {
     V3 o, d;
@@ -141,19 +154,25 @@ RT2_HD void cwbvh_node_step(const Node8* __restrict__ nodes, const RayPrep& rp, 
     // t = q * (s*idir) + (p-o)*idir ; s is a power of two so s*idir is exact
     const float snx = sx * rp.inx, sny = sy * rp.iny, snz = sz * rp.inz, sfx = sx * rp.ifx, sfy = sy * rp.ify, sfz = sz * rp.ifz;
     float anx = ax * rp.inx, any_ = ay * rp.iny, anz = az * rp.inz, afx = ax * rp.ifx, afy = ay * rp.ify, afz = az * rp.ifz;
-#if defined(__CUDA_ARCH__) && defined(RT2_NODE_TEST_FOLDED)
-    // EXPERIMENT, off by default (measured −7 % on C2, 2147 vs 2305 Mrays/s: the 48 prmt per node land on the ALU pipe, which
-    // FMNMX/LOP3/SEL already keep 47 % busy, while I2F.U8 runs beside it on the otherwise idle XU pipe).
-    // Dequantisation without the XU pipe (I2F.U8 runs at 16 lanes/clk/SM and was the busiest pipe of k_trace, 63 % in
-    // profiles/r01b): prmt drops the byte q into the mantissa of 2^23, giving the float 2^23 + q, and the 2^23 is taken
-    // out of the per-node offset instead of out of every value:  q*s + a == (2^23 + q)*s + (a - 2^23*s).
-    // a - 2^23*s is rounded once (fma), to <= half a grid cell |s| — so the offset also moves each near plane one cell
-    // earlier and each far plane one cell later (constants 2^23 +- 1, exact in binary32).  The box test stays conservative;
-    // it is no longer the oracle's arithmetic, which is fine: the closest hit is a total order, independent of which
+#if defined(__CUDA_ARCH__)
+    // Dequantisation split between the XU pipe (I2F.U8, 16 lanes/clk/SM: the busiest pipe of k_trace, 60 % in profiles/r01c)
+    // and the ALU pipe: for the planes in RT2_NODE_FOLD_MASK, prmt drops the byte q into the mantissa of 2^23, giving the
+    // float 2^23 + q, and the 2^23 is taken out of the per-node offset instead of out of every value:
+    //     q*s + a == (2^23 + q)*s + (a - 2^23*s).
+    // a - 2^23*s is rounded once (fma), to <= half a grid cell |s| — so the offset also moves a near plane one cell earlier
+    // and a far plane one cell later (constants 2^23 +- 1, exact in binary32).  The box test stays conservative; for those
+    // planes it is no longer the oracle's arithmetic, which is fine: the closest hit is a total order, independent of which
     // superfluous nodes are visited.  The CPU build of this header keeps the exact form.
-    anx = rt2_fma(snx, rp.negx ? -8388607.0f : -8388609.0f, anx); afx = rt2_fma(sfx, rp.negx ? -8388609.0f : -8388607.0f, afx);
-    any_ = rt2_fma(sny, rp.negy ? -8388607.0f : -8388609.0f, any_); afy = rt2_fma(sfy, rp.negy ? -8388609.0f : -8388607.0f, afy);
-    anz = rt2_fma(snz, rp.negz ? -8388607.0f : -8388609.0f, anz); afz = rt2_fma(sfz, rp.negz ? -8388609.0f : -8388607.0f, afz);
+    // All six planes folded measured -7 % on C2 (the 48 prmt land on the ALU pipe that FMNMX/LOP3/SEL already keep 46 % busy).
+    if (RT2_NODE_FOLD_MASK & 1) anx = rt2_fma(snx, rp.negx ? -8388607.0f : -8388609.0f, anx);
+    if (RT2_NODE_FOLD_MASK & 2) any_ = rt2_fma(sny, rp.negy ? -8388607.0f : -8388609.0f, any_);
+    if (RT2_NODE_FOLD_MASK & 4) anz = rt2_fma(snz, rp.negz ? -8388607.0f : -8388609.0f, anz);
+    if (RT2_NODE_FOLD_MASK & 8) afx = rt2_fma(sfx, rp.negx ? -8388609.0f : -8388607.0f, afx);
+    if (RT2_NODE_FOLD_MASK & 16) afy = rt2_fma(sfy, rp.negy ? -8388609.0f : -8388607.0f, afy);
+    if (RT2_NODE_FOLD_MASK & 32) afz = rt2_fma(sfz, rp.negz ? -8388609.0f : -8388607.0f, afz);
+#define RT2_DQ(bit, w, j) ((RT2_NODE_FOLD_MASK & (bit)) ? byte_to_float_biased(w, j) : byte_to_float(w, j))
+#else
+#define RT2_DQ(bit, w, j) byte_to_float(w, j)
 #endif
     const uint32_t oct_inv4 = rp.oct_inv * 0x01010101u;
     uint32_t hitmask = 0;
@@ -171,17 +190,18 @@ RT2_HD void cwbvh_node_step(const Node8* __restrict__ nodes, const RayPrep& rp, 
         const uint32_t qnz = rp.negz ? qhiz : qloz, qfz = rp.negz ? qloz : qhiz;
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-            const float tnx = rt2_fma(byte_to_float(qnx, j), snx, anx);
-            const float tny = rt2_fma(byte_to_float(qny, j), sny, any_);
-            const float tnz = rt2_fma(byte_to_float(qnz, j), snz, anz);
-            const float tfx = rt2_fma(byte_to_float(qfx, j), sfx, afx);
-            const float tfy = rt2_fma(byte_to_float(qfy, j), sfy, afy);
-            const float tfz = rt2_fma(byte_to_float(qfz, j), sfz, afz);
+            const float tnx = rt2_fma(RT2_DQ(1, qnx, j), snx, anx);
+            const float tny = rt2_fma(RT2_DQ(2, qny, j), sny, any_);
+            const float tnz = rt2_fma(RT2_DQ(4, qnz, j), snz, anz);
+            const float tfx = rt2_fma(RT2_DQ(8, qfx, j), sfx, afx);
+            const float tfy = rt2_fma(RT2_DQ(16, qfy, j), sfy, afy);
+            const float tfz = rt2_fma(RT2_DQ(32, qfz, j), sfz, afz);
             const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
             const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tfar_limit));
             if (tn <= tf) hitmask |= rt2_byte(child_bits4, j) << rt2_byte(bit_index4, j);
         }
     }
+#undef RT2_DQ
     ngroup.x = n1.x;
     ngroup.y = (hitmask & 0xFF000000u) | (n0.w >> 24);
     tgroup.x = n1.y;

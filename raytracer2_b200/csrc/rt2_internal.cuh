@@ -114,6 +114,7 @@ struct FrameBuffers {
 
 }  // namespace rt2
 
+#define RT2_FRAMES_IN_FLIGHT 2
 struct rt2_ctx {
     int device = 0;
     cudaStream_t own_stream = nullptr;
@@ -125,6 +126,12 @@ struct rt2_ctx {
     rt2_gconst gconst{};
     bool have_gconst = false;
     rt2_gconst* d_gconst = nullptr;
+    // frames in flight (the reference keeps swapchain images + one command buffer per image in flight, src/context.rs:30,639-694):
+    // a ring of pinned staging copies for rt2_set_constants, and rt2_read_async's device snapshots + copy stream
+    rt2_gconst* h_gconst_ring = nullptr; cudaEvent_t gconst_done[RT2_FRAMES_IN_FLIGHT] = {}; uint32_t gconst_next = 0;
+    cudaStream_t copy_stream = nullptr;
+    void* snap[RT2_FRAMES_IN_FLIGHT] = {}; size_t snap_bytes[RT2_FRAMES_IN_FLIGHT] = {};
+    cudaEvent_t snap_ready[RT2_FRAMES_IN_FLIGHT] = {}, read_done[RT2_FRAMES_IN_FLIGHT] = {}; uint32_t snap_next = 0; bool reads_pending = false;
     rt2_stats stats{};
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)

@@ -122,6 +122,23 @@ __global__ void __launch_bounds__(128) k_trace(TraceArgs a) {
 // GENERIC: rays carry their own [tmin, tmax] (ray0 = o|tmin, ray1 = d|tmax) instead of K1's constants.
 // The closest hit is a total order (hit_closer), so the result does not depend on any of this scheduling.
 __device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+// leaf triangles are touched once per ray: loaded without allocating an L1 line so that the L1 keeps BVH nodes (RT2_TRI_NOALLOC)
+__device__ __forceinline__ float4 ld16f_stream(const void* p) {
+#ifdef RT2_TRI_NOALLOC
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+#else
+    return ld16f(p);
+#endif
+}
+#ifdef RT2_RAY_STREAM
+#define RT2_LDRAY(p) __ldcs(p)
+#define RT2_STHIT(p, v) __stcs((p), (v))
+#else
+#define RT2_LDRAY(p) (*(p))
+#define RT2_STHIT(p, v) (*(p) = (v))
+#endif
 
 template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED = false, bool GENERIC = false>
 __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
@@ -149,7 +166,7 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
                 const uint32_t idx = base + __popc(need & ((1u << lane) - 1u));
                 if (idx < count) {
                     slot = a.queue[idx];
-                    const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot];
+                    const float4 r0 = RT2_LDRAY(a.st_ray0 + slot), r1 = RT2_LDRAY(a.st_ray1 + slot);
                     const V3 o = v3(r0.x, r0.y, r0.z), d = GENERIC ? v3(r1.x, r1.y, r1.z) : v3(r0.w, r1.x, r1.y);
                     if (GENERIC) { tmin = r0.w; tmax = r1.w; }
                     rp = make_ray_prep(o, d);
@@ -207,7 +224,9 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
                     while (tgroup.y != 0u) {
                         if (POSTPONE_PCT > 0) {
                             if (__popc(__activemask()) * 100 < in_loop * POSTPONE_PCT && sp < postpone_limit) {
-                                prefetch_l1(a.tris + (tgroup.x + rt2_fhs(tgroup.y)));      // postponed: by the time it is tested it sits in L1 (+0.5-1 %)
+#ifndef RT2_TRI_NOALLOC
+                                prefetch_l1(a.tris + (tgroup.x + rt2_fhs(tgroup.y)));
+#endif      // postponed: by the time it is tested it sits in L1 (+0.5-1 %)
                                 stack[sp++] = tgroup; break;
                             }
                         }
@@ -215,7 +234,7 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
                         tgroup.y &= ~(1u << ti);
                         const uint32_t s = tgroup.x + ti;
                         const TriPos* tp = a.tris + s;
-                        const float4 va = ld16f(&tp->v0), vb = ld16f(&tp->v1), vc = ld16f(&tp->v2);
+                        const float4 va = ld16f_stream(&tp->v0), vb = ld16f_stream(&tp->v1), vc = ld16f_stream(&tp->v2);
                         float t, u, v;
                         if (ray_triangle(v3(rp.ox, rp.oy, rp.oz), sh, tmin, tmax, v3(va.x, va.y, va.z), v3(vb.x, vb.y, vb.z),
                                          v3(vc.x, vc.y, vc.z), &t, &u, &v)) {
@@ -235,7 +254,7 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
                         rp = make_ray_prep(v3(r0.x, r0.y, r0.z), GENERIC ? v3(r1.x, r1.y, r1.z) : v3(r0.w, r1.x, r1.y));
                     }
                     if (sp == 0) {
-                        a.st_hit[slot] = make_float4(best.t, best.u, best.v, __uint_as_float(tri_slot));
+                        RT2_STHIT(a.st_hit + slot, make_float4(best.t, best.u, best.v, __uint_as_float(tri_slot)));
                         if (INSTANCED) a.st_hit_inst[slot] = best.inst;
                         active = false;
                         break;

@@ -263,3 +263,37 @@ def test_full_size_image_is_independent_of_the_schedule(monkeypatch):
         assert r == rays and np.array_equal(got, ref), env
     got, r = render({}, bands=8)
     assert r == rays and np.array_equal(got, ref)
+
+
+def test_read_async_two_frames_in_flight_matches_blocking_read():
+    """rt2_read_async (device snapshot + copy stream) returns what rt2_read returns, with two reads in flight while the
+    next frames render, and rt2_set_constants no longer waits for the stream (pinned staging ring)."""
+    import torch
+    w, h = 96, 64
+    sc = rt.Scene(rt.SCENE_CORNELL)
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+    g.refrence_mode = 1
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, w, h)
+    n = w * h * 8
+    bufs = [torch.empty(n, dtype=torch.uint8).pin_memory() for _ in range(4)]
+    want = []
+    for f in range(4):
+        g.frame = 1 + f
+        lp.update_uniform(g)
+        lp.execute(1 + f, rt.LaunchParams(spp=1 + f, max_bounces=2))
+        want.append(ctx.read(rt.BUF_DIFFUSE_F16, np.uint8).copy())
+    for f in range(4):                       # same frames again, never syncing between them
+        g.frame = 1 + f
+        lp.update_uniform(g)
+        lp.execute(1 + f, rt.LaunchParams(spp=1 + f, max_bounces=2))
+        ctx.read_into_async(rt.BUF_DIFFUSE_F16, bufs[f].data_ptr(), n)
+    ctx.read_fence()
+    ctx.sync()
+    for f in range(4):
+        assert np.array_equal(bufs[f].numpy(), want[f]), f"frame {f}"
+    assert not np.array_equal(want[0], want[3])
+    with pytest.raises(rt.Rt2Error):
+        ctx.read_into_async(rt.BUF_DIFFUSE_F16, bufs[0].data_ptr(), n - 8)
+    ctx.close()
