@@ -50,6 +50,18 @@ RT2_HD float dot3(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
 RT2_HD V3 normalize3(V3 v) { return v / sqrtf(dot3(v, v)); }
 RT2_HD float saturatef(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
 RT2_HD float comp(const V3& v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+// comp() as two SELs.  In the triangle loop of k_trace nvcc turned the nine comp() calls of ray_triangle into seven
+// branch diamonds (64 of the loop's 158 SASS instructions, run at 6-7 active lanes); selp keeps them straight-line.
+RT2_HD float comp_sel(const V3& v, int k) {
+#ifdef __CUDA_ARCH__
+    float r;
+    asm("{\n\t.reg .pred p0, p1;\n\t.reg .f32 t;\n\tsetp.eq.s32 p0, %4, 0;\n\tsetp.eq.s32 p1, %4, 1;\n\t"
+        "selp.f32 t, %2, %3, p1;\n\tselp.f32 %0, %1, t, p0;\n\t}" : "=f"(r) : "f"(v.x), "f"(v.y), "f"(v.z), "r"(k));
+    return r;
+#else
+    return comp(v, k);
+#endif
+}
 
 // GLSL `M * v` for column-major M (m[c*4+r]); pinned order ((c0*x + c1*y) + c2*z) + c3*w
 RT2_HD void mat4_mul_vec4(const float* m, float x, float y, float z, float w, float out[4]) {
@@ -192,13 +204,13 @@ RT2_HD RayShear make_shear(V3 d) {
 RT2_HD bool ray_triangle(V3 o, const RayShear& s, float tmin, float tmax, V3 p0, V3 p1, V3 p2,
                          float* t_out, float* u_out, float* v_out) {
     V3 A = p0 - o, B = p1 - o, C = p2 - o;
-    float Akz = comp(A, s.kz), Bkz = comp(B, s.kz), Ckz = comp(C, s.kz);
-    float Ax = rt2_fma(-s.Sx, Akz, comp(A, s.kx));
-    float Ay = rt2_fma(-s.Sy, Akz, comp(A, s.ky));
-    float Bx = rt2_fma(-s.Sx, Bkz, comp(B, s.kx));
-    float By = rt2_fma(-s.Sy, Bkz, comp(B, s.ky));
-    float Cx = rt2_fma(-s.Sx, Ckz, comp(C, s.kx));
-    float Cy = rt2_fma(-s.Sy, Ckz, comp(C, s.ky));
+    float Akz = comp_sel(A, s.kz), Bkz = comp_sel(B, s.kz), Ckz = comp_sel(C, s.kz);
+    float Ax = rt2_fma(-s.Sx, Akz, comp_sel(A, s.kx));
+    float Ay = rt2_fma(-s.Sy, Akz, comp_sel(A, s.ky));
+    float Bx = rt2_fma(-s.Sx, Bkz, comp_sel(B, s.kx));
+    float By = rt2_fma(-s.Sy, Bkz, comp_sel(B, s.ky));
+    float Cx = rt2_fma(-s.Sx, Ckz, comp_sel(C, s.kx));
+    float Cy = rt2_fma(-s.Sy, Ckz, comp_sel(C, s.ky));
     float U = Cx * By - Cy * Bx;      // two roundings per product: keeps edge functions antisymmetric
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;

@@ -448,6 +448,11 @@ static const trace_kernel_t g_trace_variants[] = {
     k_trace_dyn<25, 4, 4>,     // 7
     k_trace_dyn<15, 6, 8>,     // 8
     k_trace_dyn<20, 4, 12>,    // 9
+    k_trace_dyn<30, 4, 8>,     // 10
+    k_trace_dyn<40, 4, 8>,     // 11
+    k_trace_dyn<12, 4, 8>,     // 12
+    k_trace_dyn<20, 6, 6>,     // 13
+    k_trace_dyn<20, 3, 6>,     // 14
 };
 static const int g_num_trace_variants = (int)(sizeof(g_trace_variants) / sizeof(g_trace_variants[0]));
 
