@@ -269,19 +269,27 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
 }
 
 // refrence.rgen:28-46 for one traced ray of each queued slot
-__global__ void __launch_bounds__(256) k_k1_shade(ShadeArgs a) {
+// 4 blocks of 256 threads per SM (64 registers): the kernel waits on dependent gathers (state -> shading record -> texels),
+// so resident warps buy bandwidth; measured 1 / 3 / 4 / 5 blocks: 2488 / 2486 / 2532 / 2501 Mrays/s on C2 (5 spills).
+#ifndef RT2_SHADE_MIN_BLOCKS
+#define RT2_SHADE_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_k1_shade(ShadeArgs a) {
     __shared__ float lut[256];
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x];
     __syncthreads();
     const uint32_t count = *a.count_in;
     const uint32_t stride = gridDim.x * blockDim.x;
     // all lanes of a warp iterate together (warp_append uses warp collectives)
-    for (uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; i0 < count; i0 += stride) {
+    // the queue entry of the next iteration is fetched one iteration ahead: one dependent memory round trip less per ray
+    uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u;
+    uint32_t slot_ahead = i0 + (threadIdx.x & 31u) < count ? a.queue_in[i0 + (threadIdx.x & 31u)] : 0u;
+    for (; i0 < count; i0 += stride) {
         const uint32_t i = i0 + (threadIdx.x & 31u);
         bool alive = false;
-        uint32_t slot = 0;
+        uint32_t slot = slot_ahead;
+        if (i + stride < count) slot_ahead = a.queue_in[i + stride];
         if (i < count) {
-            slot = a.queue_in[i];
             const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot], ac = a.st_acc[slot];
             const uint4 misc = a.st_misc[slot];
             const float4 h = a.st_hit[slot];
