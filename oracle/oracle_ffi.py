@@ -28,6 +28,8 @@ def lib():
         L.orc_scene_create.restype = VP; L.orc_scene_create.argtypes = [VP]
         L.orc_scene_destroy.restype = None; L.orc_scene_destroy.argtypes = [VP]
         L.orc_scene_num_triangles.restype = u64; L.orc_scene_num_triangles.argtypes = [VP]
+        L.orc_trace_rays.restype = C.c_int
+        L.orc_trace_rays.argtypes = [VP, VP, u32, u32, VP]
         L.orc_trace_primary.restype = C.c_int
         L.orc_trace_primary.argtypes = [VP, VP, u32, u32, u32, C.c_int, VP]
         L.orc_render_reference.restype = C.c_int
@@ -150,6 +152,13 @@ class OracleScene:
         out = np.zeros((height, width, 8), dtype=np.uint32)
         rc = self._L.orc_trace_primary(self._p, C.cast(C.byref(gconst), VP), width, height, flags, threads, out.ctypes.data_as(VP))
         assert rc == 0
+        return out
+
+    def trace_rays(self, rays, flags=0):
+        """rays [n, 8] float32 = (o.xyz, tmin, d.xyz, tmax) -> hit records [n, 8] uint32 views"""
+        r = np.ascontiguousarray(rays, np.float32)
+        out = np.zeros((r.shape[0], 8), np.uint32)
+        assert self._L.orc_trace_rays(self._p, r.ctypes.data_as(VP), r.shape[0], flags, out.ctypes.data_as(VP)) == 0
         return out
 
     def render_reference(self, gconst, frame, width, height, spp=0, max_bounces=0, row0=0, row1=0, flags=0, threads=0,

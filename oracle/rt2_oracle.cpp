@@ -766,7 +766,18 @@ orc_scene* orc_scene_create(const rt2_scene_desc* d) {
         }
     }
     std::vector<Box> boxes(s->tris.size());
-    for (size_t i = 0; i < s->tris.size(); i++) { Box b = empty_box(); grow(b, s->tris[i].p0); grow(b, s->tris[i].p1); grow(b, s->tris[i].p2); boxes[i] = b; }
+    for (size_t i = 0; i < s->tris.size(); i++) {
+        Box b = empty_box(); grow(b, s->tris[i].p0); grow(b, s->tris[i].p1); grow(b, s->tris[i].p2);
+        // The BVH has to be conservative with respect to ray_triangle, whose sheared coordinates carry an absolute error of
+        // about |vertex| * 2^-23: a ray leaving a 1e4-unit triangle is reported to hit that triangle again at t ~ 1e-3 (just above
+        // TMin), outside its exact box.  Pad every triangle box on all axes by its largest coordinate * 2^-16
+        // (tests/test_adversarial_geometry.py found the miss; the brute-force path is the definition).
+        const float m = std::fmax(std::fmax(std::fmax(std::fabs(b.lo.x), std::fabs(b.hi.x)), std::fmax(std::fabs(b.lo.y), std::fabs(b.hi.y))),
+                                  std::fmax(std::fabs(b.lo.z), std::fabs(b.hi.z)));
+        const float pad = m * 1.52587890625e-05f;
+        b.lo = b.lo - v3(pad, pad, pad); b.hi = b.hi + v3(pad, pad, pad);
+        boxes[i] = b;
+    }
     s->blas.build(boxes, 4);
     if (d->num_instances > 0 && d->instance_transforms) {
         s->instanced = true;
@@ -810,6 +821,21 @@ int orc_trace_primary(const orc_scene* s, const void* gconst, uint32_t width, ui
             if (h.geom != 0xFFFFFFFFu) { r.t = h.t; r.u = h.u; r.v = h.v; }
         }
     });
+    return 0;
+}
+
+// arbitrary rays (test utility): rays[i] = {o.xyz, tmin, d.xyz, tmax}
+int orc_trace_rays(const orc_scene* s, const float* rays, uint32_t n, uint32_t flags, rt2_hit_record* out) {
+    if (!s || !rays || !out) return -1;
+    const bool brute = (flags & ORC_BRUTE_FORCE) != 0;
+    for (uint32_t i = 0; i < n; i++) {
+        const float* r8 = rays + (size_t)i * 8;
+        Hit h = trace(*s, v3(r8[0], r8[1], r8[2]), v3(r8[4], r8[5], r8[6]), r8[3], r8[7], brute);
+        rt2_hit_record& r = out[i];
+        std::memset(&r, 0, sizeof r);
+        r.instance = h.inst; r.geometry = h.geom; r.primitive = h.prim;
+        if (h.geom != 0xFFFFFFFFu) { r.t = h.t; r.u = h.u; r.v = h.v; }
+    }
     return 0;
 }
 

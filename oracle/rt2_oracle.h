@@ -24,6 +24,8 @@ void       orc_scene_destroy(orc_scene* s);
 uint64_t   orc_scene_num_triangles(const orc_scene* s);
 
 /* setupPrimaryRay + trace with TMin 0.001 (refrence.rgen:26-27) for every pixel. */
+/* arbitrary rays, rays[i] = {o.xyz, tmin, d.xyz, tmax} (test utility) */
+int orc_trace_rays(const orc_scene* s, const float* rays, uint32_t n, uint32_t flags, rt2_hit_record* out);
 int orc_trace_primary(const orc_scene* s, const void* gconst, uint32_t width, uint32_t height,
                       uint32_t flags, int threads, rt2_hit_record* out);
 
