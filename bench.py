@@ -173,7 +173,9 @@ def run_reference_arm(args, rank, world):
     line = {"impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt / max(args.steps, 1) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"C2 hall {TRIS} tris 64 textures {W}x{H} {BOUNCES} bounces (CPU oracle, SAH BVH2, std::thread; the reference itself has no CPU path and cannot run on this box)"},
+            "config": {"workload": f"C2 procedural hall {sc.num_triangles} tris, 64 sRGB textures 512^2, {W}x{H}, {BOUNCES} bounces, {SPP} spp per GPU (spp={SPP * max(args.gpus, 1)})",
+                       "arm": "CPU oracle (SAH BVH2, std::thread over rows): the reference itself is Rust + GLSL on Vulkan ray tracing, has no CPU path and cannot run on this box; each step is a bounded sample of the workload, 1 spp of the same frame",
+                       "rays_per_step": rays_total // max(args.steps, 1)},
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
