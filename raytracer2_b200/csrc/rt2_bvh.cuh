@@ -116,22 +116,27 @@ struct RayPrep {
     uint32_t oct_inv;     // 7 - octant
     bool negx, negy, negz;
 };
-RT2_HD RayPrep make_ray_prep(const V3& o, const V3& d) {
-    RayPrep r;
-    // |1/d| is capped at 2^60: a zero (or denormal-small) direction component would otherwise give inf and
-    // then NaN slab distances (0 * inf), which fminf/fmaxf drop — still conservative, but such a ray walks
-    // every node the other two axes admit (one ray in ~2^23 after a cosine bounce off an axis-aligned wall,
-    // costing milliseconds).  With the cap the slab test degenerates to "is the origin inside the slab".
+// 1/d with |1/d| capped at 2^60: a zero (or denormal-small) direction component would otherwise give inf and
+// then NaN slab distances (0 * inf), which fminf/fmaxf drop — still conservative, but such a ray walks
+// every node the other two axes admit (one ray in ~2^23 after a cosine bounce off an axis-aligned wall,
+// costing milliseconds).  With the cap the slab test degenerates to "is the origin inside the slab".
+RT2_HD V3 ray_inv_dir(const V3& d) {
     const float cap = 1.152921504606846976e18f;
     float idx = 1.0f / d.x, idy = 1.0f / d.y, idz = 1.0f / d.z;
-    idx = copysignf(fminf(fabsf(idx), cap), idx); idy = copysignf(fminf(fabsf(idy), cap), idy); idz = copysignf(fminf(fabsf(idz), cap), idz);
+    return v3(copysignf(fminf(fabsf(idx), cap), idx), copysignf(fminf(fabsf(idy), cap), idy), copysignf(fminf(fabsf(idz), cap), idz));
+}
+// The sign of 1/d is the sign of d (1/-0 = -inf), so the octant comes from the reciprocal alone: a kernel that keeps
+// ray_inv_dir(d) rebuilds RayPrep with six multiplies instead of three divisions (the instanced walk does, per instance exit).
+RT2_HD RayPrep ray_prep_from_inv(const V3& o, const V3& id) {
+    RayPrep r;
     r.ox = o.x; r.oy = o.y; r.oz = o.z;
-    r.inx = idx * (1.0f - RT2_SLAB_EPS); r.iny = idy * (1.0f - RT2_SLAB_EPS); r.inz = idz * (1.0f - RT2_SLAB_EPS);
-    r.ifx = idx * (1.0f + RT2_SLAB_EPS); r.ify = idy * (1.0f + RT2_SLAB_EPS); r.ifz = idz * (1.0f + RT2_SLAB_EPS);
-    r.negx = (f2u(d.x) >> 31) != 0; r.negy = (f2u(d.y) >> 31) != 0; r.negz = (f2u(d.z) >> 31) != 0;
+    r.inx = id.x * (1.0f - RT2_SLAB_EPS); r.iny = id.y * (1.0f - RT2_SLAB_EPS); r.inz = id.z * (1.0f - RT2_SLAB_EPS);
+    r.ifx = id.x * (1.0f + RT2_SLAB_EPS); r.ify = id.y * (1.0f + RT2_SLAB_EPS); r.ifz = id.z * (1.0f + RT2_SLAB_EPS);
+    r.negx = (f2u(id.x) >> 31) != 0; r.negy = (f2u(id.y) >> 31) != 0; r.negz = (f2u(id.z) >> 31) != 0;
     r.oct_inv = 7u - ((r.negx ? 1u : 0u) | (r.negy ? 2u : 0u) | (r.negz ? 4u : 0u));
     return r;
 }
+RT2_HD RayPrep make_ray_prep(const V3& o, const V3& d) { return ray_prep_from_inv(o, ray_inv_dir(d)); }
 
 // One node step: pops the nearest-octant-first inner child of `ngroup` (which must have one),
 // pushes the remainder on the stack, tests the child's 8 boxes and returns the new inner-hit group in
