@@ -231,17 +231,32 @@ def main():
     # band gather plumbing (raytracer2_b200/sharding.py): each rank's rows packed contiguously -> all_gather
     from raytracer2_b200.sharding import BandPlan, gather_frame
     plan = BandPlan(H, BAND_ROWS, n_gpus)
-    send = torch.zeros(plan.max_rows * W * 4, dtype=torch.float32, device="cuda")
-    recv = torch.zeros(n_gpus * plan.max_rows * W * 4, dtype=torch.float32, device="cuda") if n_gpus > 1 else None
+    # two send/recv pairs: the gather of frame n (NCCL's own stream) overlaps the render of frame n+1; a pair is reused only
+    # after the collective that last used it has completed (handle.wait() = a stream-level wait, the host never blocks)
+    send = [torch.zeros(plan.max_rows * W * 4, dtype=torch.float32, device="cuda") for _ in range(2)]
+    recv = [torch.zeros(n_gpus * plan.max_rows * W * 4, dtype=torch.float32, device="cuda") if n_gpus > 1 else None for _ in range(2)]
+    pending = [None, None]
+    step_no = [0]
 
     def step(frame):
         lp.execute(frame, params)
         if n_gpus > 1:
-            ctx.pack_bands(rt.BUF_DIFFUSE_F32, send.data_ptr(), plan.rows(rank) * W * 16, BAND_ROWS, rank, n_gpus)
-            gather_frame(plan, rank, send, recv, dist)
+            b = step_no[0] & 1
+            step_no[0] += 1
+            if pending[b] is not None:
+                pending[b].wait()
+            ctx.pack_bands(rt.BUF_DIFFUSE_F32, send[b].data_ptr(), plan.rows(rank) * W * 16, BAND_ROWS, rank, n_gpus)
+            pending[b] = gather_frame(plan, rank, send[b], recv[b], dist, async_op=True)
+
+    def drain():
+        for b in range(2):
+            if pending[b] is not None:
+                pending[b].wait()
+                pending[b] = None
 
     for i in range(args.warmup):
         step(1 + i)
+    drain()
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
@@ -255,6 +270,7 @@ def main():
     ev0.record()
     for i in range(args.steps):
         step(100 + i)
+    drain()                 # every gather has landed before the end event
     ev1.record()
     torch.cuda.synchronize()
     ms = ev0.elapsed_time(ev1)
@@ -280,6 +296,7 @@ def main():
     host_out = [torch.empty(W * H * 4, dtype=torch.float16).pin_memory() for _ in range(2)]
     for i in range(2):
         lp.update_uniform(g); step(200 + i); ctx.read_into_async(rt.BUF_DIFFUSE_F16, host_out[i & 1].data_ptr(), W * H * 8)
+    drain()
     ctx.sync()
     torch.cuda.synchronize()
     if dist:
@@ -291,6 +308,7 @@ def main():
         lp.update_uniform(g)                                                                  # pinned host -> device, 1424 B
         step(300 + i)
         ctx.read_into_async(rt.BUF_DIFFUSE_F16, host_out[i & 1].data_ptr(), W * H * 8)        # device -> pinned host
+    drain()
     ctx.read_fence()                                                                          # e1 waits for every transfer
     e1.record()
     ctx.sync()

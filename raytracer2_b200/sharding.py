@@ -86,15 +86,17 @@ def unpack_gathered(plan: BandPlan, gathered, frame):
     return frame
 
 
-def gather_frame(plan: BandPlan, rank: int, send, recv, dist):
+def gather_frame(plan: BandPlan, rank: int, send, recv, dist, async_op: bool = False):
     """All-gather every rank's packed bands (`send`: [max_rows, ...]) into `recv` ([world*max_rows, ...]).
-    `dist` is torch.distributed (NCCL on the GPU box, gloo in the CPU tests)."""
+    `dist` is torch.distributed (NCCL on the GPU box, gloo in the CPU tests).  With async_op the collective's work handle is
+    returned instead of `recv`: the caller's stream does not wait for the gather (and so not for the slowest rank) until it
+    calls handle.wait() — used with double-buffered send/recv to let the gather of frame n overlap the render of frame n+1."""
     if plan.world == 1:
         recv.copy_(send)
-        return recv
+        return None if async_op else recv
     if dist.get_backend() == "gloo":                 # gloo has no all_gather_into_tensor
         chunks = list(recv.view(plan.world, -1).unbind(0))
-        dist.all_gather(chunks, send.reshape(-1))
+        h = dist.all_gather(chunks, send.reshape(-1), async_op=async_op)
     else:
-        dist.all_gather_into_tensor(recv.view(-1), send.reshape(-1))
-    return recv
+        h = dist.all_gather_into_tensor(recv.view(-1), send.reshape(-1), async_op=async_op)
+    return h if async_op else recv

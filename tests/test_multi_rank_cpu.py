@@ -82,6 +82,10 @@ def _rank_main(rank, world, port, w, h, band_rows, q):
         pack_bands(plan, rank, torch.from_numpy(d32), send)
         recv = torch.full((world * plan.max_rows, w, 4), float("nan"))
         gather_frame(plan, rank, send, recv, dist)
+        recv2 = torch.full((world * plan.max_rows, w, 4), float("nan"))      # the double-buffered form bench.py uses: handle, wait later
+        handle = gather_frame(plan, rank, send, recv2, dist, async_op=True)
+        handle.wait()
+        assert torch.equal(recv2.view(torch.int32), recv.view(torch.int32))
         t = torch.tensor([float(rays)], dtype=torch.float64)
         dist.all_reduce(t)                                          # whole-job ray count, as bench.py sums it
         tm = torch.tensor([float(rank + 1)]); dist.all_reduce(tm, op=dist.ReduceOp.MAX)   # max-over-ranks timing path
