@@ -297,3 +297,37 @@ def test_read_async_two_frames_in_flight_matches_blocking_read():
     with pytest.raises(rt.Rt2Error):
         ctx.read_into_async(rt.BUF_DIFFUSE_F16, bufs[0].data_ptr(), n - 8)
     ctx.close()
+
+
+def test_constants_ring_keeps_every_frames_gconst_without_syncing():
+    """rt2_set_constants stages GConst in a ring of pinned slots and never waits for the stream: six back-to-back frames with
+    six different cameras (more than the ring holds) must each render with their own constants."""
+    import torch
+    w, h = 96, 64
+    sc = rt.Scene(rt.SCENE_CORNELL)
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, w, h)
+    n = w * h * 8
+
+    def gconst(k):
+        cam = sc.camera(w / h)
+        cam.position[0] = 0.15 * k - 0.3
+        cam.position[1] = 0.05 * k
+        g = rt.default_gconst(cam, w, h, sc.num_lights)
+        g.refrence_mode = 1
+        return g
+
+    want = []
+    for k in range(6):
+        lp.update_uniform(gconst(k)); lp.execute(5, rt.LaunchParams(spp=1, max_bounces=2))
+        want.append(ctx.read(rt.BUF_DIFFUSE_F16, np.uint8).copy())
+    assert len({w_.tobytes() for w_ in want}) == 6
+    bufs = [torch.empty(n, dtype=torch.uint8).pin_memory() for _ in range(6)]
+    for k in range(6):
+        lp.update_uniform(gconst(k)); lp.execute(5, rt.LaunchParams(spp=1, max_bounces=2))
+        ctx.read_into_async(rt.BUF_DIFFUSE_F16, bufs[k].data_ptr(), n)
+    ctx.sync()
+    for k in range(6):
+        assert np.array_equal(bufs[k].numpy(), want[k]), f"frame {k}"
+    ctx.close()
