@@ -45,7 +45,11 @@ __device__ __forceinline__ bool tile_pixel(uint32_t i, uint32_t width, uint32_t 
     return *x < width && *y < height;
 }
 
-__global__ void __launch_bounds__(128) k_gbuffer(GBufferArgs a) {
+// 6 blocks/SM (80 registers instead of 96): default ReSTIR-GI frame 2.91 -> 2.84 ms together with K8 (profiles/r01d_ab_gi_regs.txt)
+#ifndef RT2_GBUF_BLOCKS
+#define RT2_GBUF_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(128, RT2_GBUF_BLOCKS) k_gbuffer(GBufferArgs a) {
     __shared__ float lut[256];
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
     __syncthreads();
@@ -748,7 +752,11 @@ __device__ __forceinline__ float gi_mis_weight(const SplitBrdf& rough, const Spl
     return w * w * w;
 }
 
-__global__ void __launch_bounds__(128) k_gi_final_shading(GIArgs a) {
+// 6 blocks/SM (80 registers instead of 128)
+#ifndef RT2_K8_BLOCKS
+#define RT2_K8_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(128, RT2_K8_BLOCKS) k_gi_final_shading(GIArgs a) {
     uint32_t lx, ly;
     if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
