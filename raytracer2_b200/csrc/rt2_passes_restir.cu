@@ -45,6 +45,14 @@ __device__ __forceinline__ bool tile_pixel(uint32_t i, uint32_t width, uint32_t 
     return *x < width && *y < height;
 }
 
+// Register caps measured on the ReSTIR frames (profiles/r01d_ab_gi_regs.txt): K9 stages a/b at 8 blocks/SM (64 registers, DI-only frame
+// 3.14 -> 3.01 ms), K6/K7 at 6 blocks/SM (80 registers, GI + temporal + spatial 3.91 -> 3.79 ms).
+#ifndef RT2_DI_BLOCKS
+#define RT2_DI_BLOCKS 8
+#endif
+#ifndef RT2_GIRS_BLOCKS
+#define RT2_GIRS_BLOCKS 6
+#endif
 // 6 blocks/SM (80 registers instead of 96): default ReSTIR-GI frame 2.91 -> 2.84 ms together with K8 (profiles/r01d_ab_gi_regs.txt)
 #ifndef RT2_GBUF_BLOCKS
 #define RT2_GBUF_BLOCKS 6
@@ -407,7 +415,7 @@ __device__ __forceinline__ SampleParams di_stage_params(const rt2_restirdi_param
 }
 
 template <bool SEC>
-__global__ void __launch_bounds__(128) k_di_stage_a(DIWaveArgs w) {
+__global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_a(DIWaveArgs w) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
     const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
@@ -440,7 +448,7 @@ __global__ void __launch_bounds__(128) k_di_stage_a(DIWaveArgs w) {
 
 // B: finish the sampler; queue the first visibility ray that is due
 template <bool SEC>
-__global__ void __launch_bounds__(128) k_di_stage_b(DIWaveArgs w, uint32_t* queue_out, uint32_t* count_out) {
+__global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_b(DIWaveArgs w, uint32_t* queue_out, uint32_t* count_out) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
     const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
@@ -1090,7 +1098,7 @@ struct GIResampleArgs {
     unsigned long long* stat_rays; unsigned long long* stat_hits;
 };
 
-__global__ void __launch_bounds__(128) k_gi_temporal(GIResampleArgs a) {
+__global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_temporal(GIResampleArgs a) {
     uint32_t lx, ly;
     if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
@@ -1192,7 +1200,7 @@ __device__ __forceinline__ void spatial_offset(const char2* table, int sample_id
     *ox = (int)(fx * radius); *oy = (int)(fy * radius);
 }
 
-__global__ void __launch_bounds__(128) k_gi_spatial(GIResampleArgs a) {
+__global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_spatial(GIResampleArgs a) {
     uint32_t lx, ly;
     if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
