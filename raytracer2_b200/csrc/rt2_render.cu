@@ -140,8 +140,8 @@ __device__ __forceinline__ float4 ld16f_stream(const void* p) {
 #define RT2_STHIT(p, v) (*(p) = (v))
 #endif
 
-template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED = false, bool GENERIC = false>
-__global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED, bool GENERIC>
+__device__ __forceinline__ void trace_dyn_body(const TraceArgs& a) {
     const uint32_t count = *a.count;
     const uint32_t lane = threadIdx.x & 31u;
     if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(a.stat_rays, (unsigned long long)count);
@@ -276,6 +276,13 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) {
         __syncwarp();
     }
 }
+
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED = false, bool GENERIC = false>
+__global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, INSTANCED, GENERIC>(a); }
+// The two-level walk at 6 blocks/SM (80 registers; ptxas picks 96 = 5 blocks on its own): C5 619 -> 659 Mrays/s.  A separate
+// entry point because __launch_bounds__(128, n) on the single-level kernels changes their code (C2 -0.4 % at n = 7).
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false>
+__global__ void __launch_bounds__(128, 6) k_trace_dyn_tlas(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, true, GENERIC>(a); }
 
 // refrence.rgen:28-46 for one traced ray of each queued slot
 // 4 blocks of 256 threads per SM (64 registers): the kernel waits on dependent gathers (state -> shading record -> texels),
@@ -579,7 +586,7 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
                 if (s.num_instances) {
                     // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
                     const bool unified = ctx->trace_variant != 0 && s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE;
-                    if (unified) k_trace_dyn<20, 4, 8, true><<<k.trace_blocks, 128, 0, st>>>(t);
+                    if (unified) k_trace_dyn_tlas<20, 4, 8><<<k.trace_blocks, 128, 0, st>>>(t);
                     else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, st>>>(t);
                 } else {
                     g_trace_variants[ctx->trace_variant]<<<k.trace_blocks, 128, 0, st>>>(t);
@@ -608,7 +615,7 @@ int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* cou
     TraceArgs t = make_trace_args(ctx);
     t.queue = queue; t.count = count; t.head = head; t.stat_rays = stat_rays;
     if (s.num_instances) {
-        if (s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE) k_trace_dyn<20, 4, 8, true, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        if (s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE) k_trace_dyn_tlas<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
         else k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
     } else {
         k_trace_dyn<20, 4, 8, false, true><<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
@@ -626,7 +633,7 @@ int render_init(rt2_ctx* ctx) {
     if (const char* e = getenv("RT2_TRACE_VARIANT")) { int v = atoi(e); if (v >= 0 && v < g_num_trace_variants) ctx->trace_variant = v; }
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, g_trace_variants[ctx->trace_variant], 128, 0));
     int b2 = 0;
-    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace_dyn<20, 4, 8, true>, 128, 0));
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace_dyn_tlas<20, 4, 8>, 128, 0));
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, k_trace<true>, 128, 0));
     ctx->trace_blocks_per_sm[0] = std::max(b0, 1); ctx->trace_blocks_per_sm[1] = std::max(b1, 1); ctx->trace_blocks_per_sm[2] = std::max(b2, 1);
     return RT2_OK;
