@@ -542,9 +542,10 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
         const uint64_t pixels = (uint64_t)band.width * band.local_rows;
         const int full_blocks = ctx->trace_blocks_per_sm[s.num_instances ? 1 : 0] * ctx->num_sms;
         const bool small_wave = pixels < 900000u;
-        const uint32_t auto_chains = s.num_tris < 4096u ? 1u : (small_wave ? 8u : 2u);
+        const bool tiny_scene = s.num_tris < 4096u && !s.num_instances;      // an instanced scene's BLAS may be small; its trace launches are not
+        const uint32_t auto_chains = tiny_scene ? 1u : (small_wave ? 8u : 2u);
         const uint32_t rays_per_lane = ctx->rays_per_lane_set ? ctx->rays_per_lane
-                                     : (small_wave && s.num_tris >= 4096u ? std::max<uint32_t>(1u, (uint32_t)(pixels / ((uint64_t)full_blocks * 128u))) : 0u);
+                                     : (small_wave && !tiny_scene ? std::max<uint32_t>(1u, (uint32_t)(pixels / ((uint64_t)full_blocks * 128u))) : 0u);
         uint32_t chains = profile ? 1u : std::max(1u, std::min(ctx->chains ? ctx->chains : auto_chains, RT2_MAX_CHAINS));
         uint32_t per = ((padded + chains - 1) / chains + 255u) & ~255u;
         while (chains > 1u && (uint64_t)per * (chains - 1) >= padded) { chains--; per = ((padded + chains - 1) / chains + 255u) & ~255u; }
