@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# RT2_CUDA_LIB: an alternative build of the same library (kernel A/B experiments, tools_gpu_ab.sh); never a different backend
+# RT2_CUDA_LIB: an alternative build of the same library (kernel A/B experiments, tools/gpu_ab.sh); never a different backend
 CUDA_LIB_PATH = os.environ.get("RT2_CUDA_LIB") or os.path.join(_HERE, "librt2cuda.so")
 HOST_LIB_PATH = os.path.join(_HERE, "librt2host.so")
 

@@ -1,7 +1,7 @@
 """Row-band sharding of one frame over the ranks of one node.
 
 The reference renders a frame on one Vulkan device; its ray-gen launches are per-pixel independent
-(src/shaders/reference_mode/reference_mode.rgen:20-40: the seed is a function of the pixel and the
+(src/shaders/lighting_passes/refrence.rgen:18-47: the seed is a function of the pixel and the
 frame only), so the frame splits by rows with no exchange step inside the pass.  A rank owns every
 `world`-th band of `band_rows` rows (interleaved so that sky/floor imbalance spreads evenly); the scene
 and acceleration structure are replicated.  The only collective is the gather of the finished bands.

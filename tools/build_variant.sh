@@ -1,5 +1,5 @@
 #!/bin/bash
-# build an alternative librt2cuda into gpurun_variants/<name>.so with extra nvcc flags: ./tools_build_variant.sh name -DFOO ...
+# build an alternative librt2cuda into gpurun_variants/<name>.so with extra nvcc flags: ./tools/build_variant.sh name -DFOO ...
 name=$1; shift
 mkdir -p gpurun_variants
 CSRC=raytracer2_b200/csrc

@@ -4,6 +4,7 @@ accumulation (enable_accumulation=1, blend_factor = 1/frame: src/main.rs:551-554
 (a) once per frame and (b) once after the last frame — both timed.  Run alone (N=1) or under torch.distributed.run.
 Rank 0 prints one JSON object.  With --check the gathered image is compared bit for bit against a whole-frame render
 of the same 16 frames on rank 0."""
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
 import argparse, json, os
 import numpy as np, torch
 import raytracer2_b200 as rt

@@ -3,6 +3,7 @@ sky on, 1080p, 4 spp x 4 bounces, K12 (environment PDF mips) once, then per fram
 NCCL gather of the RGBA8 bands (sharded K13 + gather of RGBA8).  STRONG scaling: the frame is fixed.  Run alone (N=1)
 or under torch.distributed.run; rank 0 prints one JSON object.  --check compares the gathered RGBA8 image bit for bit with a
 whole-frame render on rank 0."""
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
 import argparse, json, os
 import numpy as np, torch
 import raytracer2_b200 as rt

@@ -1,5 +1,6 @@
 """BASELINE.md result table: device throughput of configs C1, C3, C4 (1 GPU share), C5 with the CPU oracle timed on a
 bounded sample of the same workload.  Prints one JSON object.  (C2 is bench.py's own line.)"""
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
 import json, os, sys, time
 import numpy as np, torch
 import raytracer2_b200 as rt

@@ -1,4 +1,5 @@
 """where does the e2e step go? (host timers around each C-ABI call)"""
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
 import time, torch, numpy as np
 import raytracer2_b200 as rt
 W, H = 1920, 1080

@@ -1,4 +1,5 @@
 """per-frame device time of K1 on C2 for a range of frame indices (looking for slow frames)"""
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
 import sys, torch, numpy as np
 import raytracer2_b200 as rt
 W, H = 1920, 1080

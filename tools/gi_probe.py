@@ -1,4 +1,5 @@
 """device time of the ReSTIR frame variants on C2 at 1080p: default GI chain, + temporal/spatial, + DI (not the bench metric)"""
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
 import json, torch
 import raytracer2_b200 as rt
 W, H = 1920, 1080

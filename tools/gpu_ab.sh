@@ -1,5 +1,5 @@
 #!/bin/bash
-# A/B of alternative builds of librt2cuda (gpurun_variants/*.so, made by tools_build_variant.sh): short bench per build, default first and last
+# A/B of alternative builds of librt2cuda (gpurun_variants/*.so, made by tools/build_variant.sh): short bench per build, default first and last
 mkdir -p gpurun_out
 run() { RT2_CUDA_LIB=$1 timeout 300 python bench.py --steps 8 --warmup 3 --no-cpu-baseline 2>&1 | tail -1 | python -c "
 import json,sys

@@ -1,6 +1,6 @@
 """GPU diagnostics: device-built BVH vs CPU-emulated build; device traversal vs CPU traversal of the same BVH."""
 import ctypes as C, sys, os, subprocess
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import raytracer2_b200 as rt
 from oracle import oracle_ffi as O

@@ -12,7 +12,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
 echo "ncu list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_trace -s 20 -c 3 -o gpurun_out/prof_trace $CMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
-CMD2="python tools_gi_probe.py"
+CMD2="python tools/gi_probe.py"
 export PYTHONPATH=.
 timeout 300 $CMD2 > gpurun_out/gi_plain.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_di_stage|k_brdf_rays|k_shade_secondary|k_gi_|k_trace|k_gbuffer' -s 40 -c 16 -o gpurun_out/prof_restir $CMD2 > gpurun_out/ncu_full3.log 2>&1

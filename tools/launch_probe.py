@@ -1,4 +1,5 @@
 """host enqueue time of rt2_render vs its device time for one rank's share of an N-way sharded 1080p frame (is the wavefront loop launch-bound?)"""
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
 import time, torch
 import raytracer2_b200 as rt
 W, H = 1920, 1080

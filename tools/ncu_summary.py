@@ -1,6 +1,7 @@
 """Summarise an .ncu-rep (ncu --set full) into profiles/: the raw per-launch CSV and a small JSON of the metrics DESIGN.md cites.
-usage: python tools_ncu_summary.py gpurun_out/prof_trace.ncu-rep profiles/r01c_k_trace  "note"
+usage: python tools/ncu_summary.py gpurun_out/prof_trace.ncu-rep profiles/r01c_k_trace  "note"
 """
+import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
 import csv, io, json, subprocess, sys
 
 rep, out, note = sys.argv[1], sys.argv[2], (sys.argv[3] if len(sys.argv) > 3 else "")

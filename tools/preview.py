@@ -1,6 +1,6 @@
 """Render previews through the C ABI and save them as PNG (gpurun_out/)."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import raytracer2_b200 as rt
 from PIL import Image

@@ -11,7 +11,7 @@ import json; d=json.load(open('gpurun_out/scale_bench_n$n.json')); print('bench 
 done
 for n in 1 2 4 8; do
   port=$((port+1))
-  if [ $n = 1 ]; then PYTHONPATH=. timeout 300 python tools_c4_probe.py 2>/dev/null | tail -1 > gpurun_out/scale_c4_n$n.json
-  else PYTHONPATH=. timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port tools_c4_probe.py --check 2>/dev/null | tail -1 > gpurun_out/scale_c4_n$n.json; fi
+  if [ $n = 1 ]; then PYTHONPATH=. timeout 300 python tools/c4_probe.py 2>/dev/null | tail -1 > gpurun_out/scale_c4_n$n.json
+  else PYTHONPATH=. timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port tools/c4_probe.py --check 2>/dev/null | tail -1 > gpurun_out/scale_c4_n$n.json; fi
   echo "c4 N=$n $(cut -c1-400 gpurun_out/scale_c4_n$n.json)"
 done
