@@ -9,9 +9,18 @@ NVCCFLAGS := $(EXTRA_NVCCFLAGS) -gencode arch=compute_100a,code=sm_100a -O3 -std
 
 all: raytracer2_b200/librt2cuda.so raytracer2_b200/librt2host.so oracle
 
-raytracer2_b200/librt2cuda.so: $(CU_SRCS) $(CU_HDRS)
-	$(NVCC) $(NVCCFLAGS) -shared -o $@ $(CU_SRCS) 2> build_ptxas.log || (cat build_ptxas.log; exit 1)
-	@grep -E "error|warning" build_ptxas.log || true
+# one object per translation unit (no relocatable device code: no kernel calls across files), so `make -j` builds in parallel and
+# an edit recompiles one file; every unit's ptxas -v output is kept in build/<unit>.ptxas.log and joined into build_ptxas.log
+OBJDIR := build/$(if $(EXTRA_NVCCFLAGS),variant,default)
+CU_OBJS := $(patsubst $(CSRC)/%.cu,$(OBJDIR)/%.o,$(CU_SRCS))
+$(OBJDIR)/%.o: $(CSRC)/%.cu $(CU_HDRS)
+	@mkdir -p $(OBJDIR)
+	$(NVCC) $(NVCCFLAGS) -Wno-deprecated-gpu-targets -Xcompiler -Wno-unknown-pragmas -c -o $@ $< 2> $(OBJDIR)/$*.ptxas.log || (cat $(OBJDIR)/$*.ptxas.log; exit 1)
+	@grep -E "error|warning" $(OBJDIR)/$*.ptxas.log || true
+
+raytracer2_b200/librt2cuda.so: $(CU_OBJS)
+	$(NVCC) -shared -o $@ $(CU_OBJS) $(LDLIBS_CUDA)
+	@cat $(sort $(wildcard $(OBJDIR)/*.ptxas.log)) > build_ptxas.log
 
 raytracer2_b200/librt2host.so: raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp raytracer2_b200/host/rt2_host.h raytracer2_b200/host/rt2_ingest.h include/rt2_abi.h include/rt2_gconst.h
 	$(CXX) -O2 -std=c++17 -fPIC -Wall -Wextra -shared -o $@ raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp -lz
@@ -20,7 +29,7 @@ oracle:
 	$(MAKE) -C oracle
 
 clean:
-	rm -f raytracer2_b200/librt2cuda.so raytracer2_b200/librt2host.so build_ptxas.log
+	rm -rf raytracer2_b200/librt2cuda.so raytracer2_b200/librt2host.so build_ptxas.log build
 	$(MAKE) -C oracle clean
 
 .PHONY: all oracle clean

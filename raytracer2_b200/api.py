@@ -116,6 +116,16 @@ def default_gconst(cam: Camera, width: int, height: int, num_lights: int = 0, en
     return g
 
 
+def overhead_camera(scene: "Scene", aspect_ratio: float, height: float = 60.0) -> Camera:
+    """A second camera for the instanced field (BASELINE config C5): above the centre looking down (the generator's own camera
+    looks across the field and sees mostly sky).  The view direction is -direction (the projection keeps w = +z_view,
+    src/camera.rs:99-123), and UP = (0,-1,0) forbids an exactly vertical axis, hence the slight tilt."""
+    cam = Camera()
+    pos, d = (C.c_float * 3)(0.0, height, 0.0), (C.c_float * 3)(0.15, 1.0, 0.1)
+    _ffi.host_lib().rt2h_camera_new(C.byref(cam), pos, d, 65.0, aspect_ratio, 0.1, 1000.0)
+    return cam
+
+
 def advance_frame(g: GConst, cam: Camera, width: int, height: int, frame: int) -> None:
     """src/main.rs:641-651."""
     _ffi.host_lib().rt2h_advance_frame(C.byref(g), C.byref(cam), width, height, frame)

@@ -211,8 +211,10 @@ __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a) {
                     if (tgroup.y != 0u) {                              // TLAS leaves = instance slots: enter one, keep the rest for later
                         const uint32_t ti = rt2_fhs(tgroup.y);
                         tgroup.y &= ~(1u << ti);
-                        if (tgroup.y != 0u) stack[sp++] = tgroup;
-                        if (ngroup.y > 0x00FFFFFFu) stack[sp++] = ngroup;
+                        // each TLAS level can leave two entries (instance remnant + inner remainder): the launch gate
+                        // (unified_walk_fits) sizes for that, the bounds checks keep a malformed tree from corrupting local memory
+                        if (tgroup.y != 0u && sp < RT2_STACK_SIZE) stack[sp++] = tgroup;
+                        if (ngroup.y > 0x00FFFFFFu && sp < RT2_STACK_SIZE) stack[sp++] = ngroup;
                         inst = __ldg(a.tlas_slot_to_inst + tgroup.x + ti);
                         const InstanceRec* ir = a.instances + inst;
                         float m[12];
@@ -422,9 +424,20 @@ int frame_resize(rt2_ctx* ctx, uint32_t w, uint32_t h) {
     RT2_CUDA(ctx, dev_alloc(ctx, &f.st_misc, n));
     RT2_CUDA(ctx, dev_alloc(ctx, &f.st_hit, n));
     RT2_CUDA(ctx, dev_alloc(ctx, &f.st_hit_inst, n));
-    RT2_CUDA(ctx, dev_alloc(ctx, &f.queue0, n));
-    RT2_CUDA(ctx, dev_alloc(ctx, &f.queue1, n));
+    // queues are indexed in the padded 8x4-tile lane range: a wavefront chain's window starts at its first padded lane, so
+    // dead lanes of earlier chains shift later windows past w*h when w is not a multiple of 8 (or rows of 4)
+    const size_t padded = (size_t)((w + 7u) / 8u) * ((h + 3u) / 4u) * 32u;
+    RT2_CUDA(ctx, dev_alloc(ctx, &f.queue0, padded));
+    RT2_CUDA(ctx, dev_alloc(ctx, &f.queue1, padded));
     f.counter_capacity = 0;
+    return RT2_OK;
+}
+
+static int check_band(rt2_ctx* ctx, const rt2_launch_params& lp) {
+    if (lp.band_world > 1u) {
+        if (lp.band_rows == 0u) return fail(ctx, RT2_E_INVALID, "band_world > 1 needs band_rows > 0");
+        if (lp.band_rank >= lp.band_world) return fail(ctx, RT2_E_INVALID, "band_rank must be < band_world");
+    }
     return RT2_OK;
 }
 
@@ -441,7 +454,7 @@ static TraceArgs make_trace_args(rt2_ctx* ctx) {
     t.blas_nodes = s.blas.nodes; t.tris = s.blas.tris;
     t.tlas_nodes = s.tlas.nodes; t.tlas_slot_to_inst = s.tlas.slot_to_prim; t.instances = s.instances;
     t.st_ray0 = f.st_ray0; t.st_ray1 = f.st_ray1; t.st_hit = f.st_hit; t.st_hit_inst = f.st_hit_inst;
-    const uint32_t depth = s.blas.depth + (s.num_instances ? s.tlas.depth + 2u : 0u) + 2u;    // node groups a ray can have stacked at once
+    const uint32_t depth = s.blas.depth + (s.num_instances ? 2u * s.tlas.depth + 2u : 0u) + 2u;    // node groups a ray can have stacked at once
     t.postpone_limit = depth < RT2_STACK_SIZE ? RT2_STACK_SIZE - depth : 0u;
     return t;
 }
@@ -460,6 +473,9 @@ static int ensure_counters(rt2_ctx* ctx, uint32_t iterations) {
 }
 
 // single-level trace variants (RT2_TRACE_VARIANT, read once per context: A/B runs on the GPU box)
+// one-loop TLAS/BLAS walk: a TLAS level can hold two stack entries (instance remnant + inner remainder), a BLAS level one
+static bool unified_walk_fits(const DeviceScene& s) { return 2u * s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE; }
+
 typedef void (*trace_kernel_t)(TraceArgs);
 static const trace_kernel_t g_trace_variants[] = {
     k_trace<false>,            // 0: static 32-ray batches
@@ -482,6 +498,7 @@ static const int g_num_trace_variants = (int)(sizeof(g_trace_variants) / sizeof(
 
 int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp) {
     int rc = check_ready(ctx); if (rc) return rc;
+    if ((rc = check_band(ctx, lp))) return rc;
     FrameBuffers& f = ctx->fb;
     if ((rc = ensure_counters(ctx, 0))) return rc;
     const Band band = make_band(f.width, f.height, lp);
@@ -503,6 +520,7 @@ int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp) {
 
 int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     int rc = check_ready(ctx); if (rc) return rc;
+    if ((rc = check_band(ctx, lp))) return rc;
     FrameBuffers& f = ctx->fb; const DeviceScene& s = ctx->scene;
     const uint32_t spp = lp.spp ? lp.spp : 12u;                    // refrence.rgen:17
     const uint32_t bounces = lp.max_bounces ? lp.max_bounces : 5u; // refrence.rgen:16
@@ -586,7 +604,7 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
                 t.queue = k.q[it & 1]; t.count = k.cnt + 2 * it; t.head = k.cnt + 2 * it + 1;
                 if (s.num_instances) {
                     // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
-                    const bool unified = ctx->trace_variant != 0 && s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE;
+                    const bool unified = ctx->trace_variant != 0 && unified_walk_fits(s);
                     if (unified) k_trace_dyn_tlas<20, 4, 8><<<k.trace_blocks, 128, 0, st>>>(t);
                     else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, st>>>(t);
                 } else {
@@ -616,7 +634,7 @@ int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* cou
     TraceArgs t = make_trace_args(ctx);
     t.queue = queue; t.count = count; t.head = head; t.stat_rays = stat_rays;
     if (s.num_instances) {
-        if (s.tlas.depth + s.blas.depth + 6u <= RT2_STACK_SIZE) k_trace_dyn_tlas<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        if (unified_walk_fits(s)) k_trace_dyn_tlas<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
         else k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
     } else {
         k_trace_dyn<20, 4, 8, false, true><<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, ctx->stream>>>(t);

@@ -302,6 +302,7 @@ bool get_accessor(const Doc& d, long index, Accessor& a, std::string& err) {
     const JVal& j = accs->arr[(size_t)index];
     if (j.has("sparse")) { err = "glTF: sparse accessors are not supported"; return false; }
     a.component = (uint32_t)j.integer("componentType", 0);
+    if (j.integer("count", 0) < 0 || j.integer("byteOffset", 0) < 0) { err = "glTF: negative accessor count / byteOffset"; return false; }
     a.count = (size_t)j.integer("count", 0);
     a.normalized = j.get("normalized") && j.get("normalized")->b;
     const std::string type = j.string("type");
@@ -314,12 +315,14 @@ bool get_accessor(const Doc& d, long index, Accessor& a, std::string& err) {
     const JVal& bv = bvs->arr[(size_t)bv_index];
     const long buf = bv.integer("buffer", -1);
     if (buf < 0 || (size_t)buf >= d.buffers.size()) { err = "glTF: buffer index out of range"; return false; }
+    if (bv.integer("byteOffset", 0) < 0 || bv.integer("byteStride", 0) < 0) { err = "glTF: negative buffer view byteOffset / byteStride"; return false; }
     const size_t off = (size_t)bv.integer("byteOffset", 0) + (size_t)j.integer("byteOffset", 0);
     const size_t elem = cs * a.ncomp;
     a.stride = (size_t)bv.integer("byteStride", 0);
     if (a.stride == 0) a.stride = elem;
     const std::vector<uint8_t>& b = d.buffers[(size_t)buf];
-    if (a.count && off + (a.count - 1) * a.stride + elem > b.size()) { err = "glTF: accessor reads past the end of its buffer"; return false; }
+    // overflow-safe form of off + (count-1)*stride + elem <= size
+    if (a.count && (off > b.size() || elem > b.size() - off || (a.count - 1) > (b.size() - off - elem) / a.stride)) { err = "glTF: accessor reads past the end of its buffer"; return false; }
     a.base = b.data() + off;
     return true;
 }
@@ -633,9 +636,9 @@ bool load_exr(const std::string& path, std::vector<float>& rgba, uint32_t& w, ui
     std::vector<uint8_t> block, tmp;
     for (uint32_t b = 0; b < blocks; b++) {
         uint64_t off; std::memcpy(&off, f.data() + table + (size_t)b * 8, 8);
-        if (off + 8 > f.size()) { err = "EXR: block offset out of range"; return false; }
+        if (f.size() < 8 || off > f.size() - 8) { err = "EXR: block offset out of range"; return false; }
         int32_t y0, size; std::memcpy(&y0, f.data() + off, 4); std::memcpy(&size, f.data() + off + 4, 4);
-        if (size < 0 || off + 8 + (uint64_t)size > f.size() || y0 < dw[1] || y0 > dw[3]) { err = "EXR: bad block header"; return false; }
+        if (size < 0 || (uint64_t)size > f.size() - 8 - off || y0 < dw[1] || y0 > dw[3]) { err = "EXR: bad block header"; return false; }
         const uint32_t row0 = (uint32_t)(y0 - dw[1]);
         const uint32_t rows = std::min<uint32_t>((uint32_t)lines_per_block, h - row0);
         const size_t expected = bytes_per_line * rows;
