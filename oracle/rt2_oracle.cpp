@@ -257,6 +257,15 @@ static inline bool ray_triangle(V3 o, const RayShear& s, float tmin, float tmax,
     float U = Cx * By - Cy * Bx;
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
+    // Woop / Benthin / Wald 2013, section 3.3: an edge function that comes out exactly zero is recomputed in binary64 (the
+    // fp32 products are exact there, the difference is rounded once).  Without this a triangle seen edge-on from hundreds of
+    // units away can cancel two edge functions to +-0 and be "hit" by a ray that passes nowhere near it (found by the
+    // full-size brute-force comparison on the instanced field).
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+    }
     if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
     float det = (U + V) + W;
     if (det == 0.0f) return false;

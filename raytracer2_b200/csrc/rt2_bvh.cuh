@@ -284,4 +284,41 @@ RT2_HD void tlas_closest_hit(const Node8* __restrict__ tlas_nodes, const uint32_
     }, node_visits);
 }
 
+// Flattened instancing (B200: 180 GB of HBM makes the memory a non-issue): ONE CWBVH over the world-space boxes of every
+// (instance, triangle) pair, so a ray walks a single tree with the world-space ray — no instance entry / exit, no per-instance
+// BLAS descent, lanes of a warp stay at comparable depths.  A leaf slot names its pair (FlatLeaf) and the triangle is tested in
+// the instance's object space with the ray re-expressed exactly as the two-level walk does (o' = inv*o, d' = inv*d, t
+// unchanged), so the accepted hits — and (t, u, v) — are the same; the closest hit is a total order, hence the same image.
+// The object-space ray is cached per lane while consecutive leaves belong to the same instance.
+struct FlatLeaf { uint32_t inst, tri; };      // tri = BLAS leaf slot (index into the object-space TriPos array)
+
+RT2_HD void flat_closest_hit(const Node8* __restrict__ nodes, const FlatLeaf* __restrict__ leaves, const InstanceRec* __restrict__ instances,
+                             const TriPos* __restrict__ tris, const TraceRay& ray, Hit& best, uint32_t* slot_out, uint32_t* node_visits = nullptr) {
+    uint32_t cur = 0xFFFFFFFFu;
+    V3 oo = ray.o;
+    RayShear sh = make_shear(ray.d);
+    cwbvh_traverse(nodes, ray, &best.t, [&](uint32_t slot) {
+        const FlatLeaf lf = leaves[slot];
+        if (lf.inst != cur) {
+            cur = lf.inst;
+            const InstanceRec* ir = instances + cur;
+            float m[12];
+#pragma unroll
+            for (int k = 0; k < 3; k++) { float4 r = ld16f(ir->inv + 4 * k); m[4 * k] = r.x; m[4 * k + 1] = r.y; m[4 * k + 2] = r.z; m[4 * k + 3] = r.w; }
+            oo = xform_point(m, ray.o);
+            sh = make_shear(xform_vector(m, ray.d));
+        }
+        const TriPos* tp = tris + lf.tri;
+        const float4 a = ld16f(&tp->v0), b = ld16f(&tp->v1), c = ld16f(&tp->v2);
+        float t, u, v;
+        if (ray_triangle(oo, sh, ray.tmin, ray.tmax, v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), &t, &u, &v)) {
+            const uint32_t geom = f2u(a.w), prim = f2u(b.w);
+            if (hit_closer(t, cur, geom, prim, best)) {
+                best.t = t; best.u = u; best.v = v; best.inst = cur; best.geom = geom; best.prim = prim;
+                if (slot_out) *slot_out = lf.tri;
+            }
+        }
+    }, node_visits);
+}
+
 }  // namespace rt2

@@ -73,6 +73,7 @@ struct DeviceScene {
     uint32_t num_lights = 0;
     TriShade* tri_shade = nullptr;            // slot order (after build)
     Accel blas, tlas;
+    Accel flat; FlatLeaf* flat_leaf = nullptr;   // flattened instancing: one CWBVH over every (instance, triangle) pair (nodes + leaf records); empty when not built
     bool accel_built = false;
     // host copies needed by host-side steps (prepare_lights scan, src/prepare_lights.rs:182-201)
     std::vector<rt2_geometry_info> h_geoms;
@@ -94,6 +95,7 @@ struct FrameBuffers {
     float4* st_hit = nullptr;
     uint32_t* st_hit_inst = nullptr;
     uint32_t *queue0 = nullptr, *queue1 = nullptr;
+    uint32_t* warp_pop = nullptr; size_t warp_pop_cap = 0;   // k_path_warp: warp-private slot queues (num_warps x P)
     // ReSTIR-side per-size resources (RenderResources::new, src/render_resources.rs:48-101,191-206,287-317); allocated on first use
     float* gb_depth[2] = {nullptr, nullptr};             // r32f, ping-pong by frame % 2 (src/light_passes.rs:565-577)
     uint32_t* gb_normals[2] = {nullptr, nullptr};        // r32ui oct
@@ -135,8 +137,11 @@ struct rt2_ctx {
     rt2_stats stats{};
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
-    int trace_blocks_per_sm[3] = {1, 1, 1};             // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level
+    int trace_blocks_per_sm[4] = {1, 1, 1, 1};          // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level, [3] flattened instancing
+    bool use_flat = true;                                // trace instanced scenes through the flattened tree when it was built (RT2_USE_FLAT=0: two-level walk)
     int trace_variant = 0;
+    int path_mode = 0;                                   // K1 schedule: 0 = one launch per bounce (wavefront chains), 1 = warp-local wavefronts in one persistent launch (RT2_PATH_MODE)
+    int path_blocks_per_sm[3] = {1, 1, 1}; int warp_blocks_per_sm = 0; uint32_t warp_paths = 0;   // k_path_warp occupancy; RT2_WARP_BLOCKS / RT2_WARP_P overrides
     uint32_t rays_per_lane = 0; bool rays_per_lane_set = false;   // cap of the persistent trace grid for small wavefronts (RT2_RAYS_PER_LANE overrides the rule)
     uint32_t chains = 0;                                 // wavefront chains of the path tracer; 0 = by frame size (RT2_CHAINS overrides)
     cudaStream_t chain_streams[8] = {}; cudaEvent_t chain_join[8] = {}; cudaEvent_t chain_fork = nullptr;

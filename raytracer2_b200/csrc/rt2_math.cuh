@@ -214,6 +214,14 @@ RT2_HD bool ray_triangle(V3 o, const RayShear& s, float tmin, float tmax, V3 p0,
     float U = Cx * By - Cy * Bx;      // two roundings per product: keeps edge functions antisymmetric
     float V = Ax * Cy - Ay * Cx;
     float W = Bx * Ay - By * Ax;
+    // an edge function that is exactly zero is recomputed in binary64 (Woop / Benthin / Wald 2013, section 3.3; same rule as the
+    // oracle): fp32 products are exact in binary64 and the difference is rounded once, so the sign is the true one.  Rare on
+    // the device (a BVH only offers triangles the ray passes close to), so the branch costs one compare on the common path.
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+    }
     if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;
     float det = (U + V) + W;
     if (det == 0.0f) return false;

@@ -38,6 +38,7 @@ static Band make_band(uint32_t w, uint32_t h, const rt2_launch_params& lp) {
 struct TraceArgs {
     const Node8* blas_nodes; const TriPos* tris;
     const Node8* tlas_nodes; const uint32_t* tlas_slot_to_inst; const InstanceRec* instances;
+    const Node8* flat_nodes; const FlatLeaf* flat_leaf;      // flattened instancing (rt2_bvh.cuh), null when not built
     const float4* st_ray0; const float4* st_ray1;
     float4* st_hit; uint32_t* st_hit_inst;
     const uint32_t* queue; const uint32_t* count; uint32_t* head;
@@ -140,11 +141,17 @@ __device__ __forceinline__ float4 ld16f_stream(const void* p) {
 #define RT2_STHIT(p, v) (*(p) = (v))
 #endif
 
-template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED, bool GENERIC>
-__device__ __forceinline__ void trace_dyn_body(const TraceArgs& a) {
-    const uint32_t count = *a.count;
+// LOCALQ: the queue belongs to this warp alone (k_path_warp): `queue`/`count` are passed in and the head is a warp-uniform
+// register instead of a global atomic.
+// FLAT (with INSTANCED = false): one tree over every (instance, triangle) pair walked with the world-space ray; the lane re-expresses
+// its ray in an instance's object space only when a leaf of another instance comes up (rt2_bvh.cuh, flat_closest_hit).
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED, bool GENERIC, bool LOCALQ = false, bool FLAT = false>
+__device__ __forceinline__ void trace_dyn_body(const TraceArgs& a, const uint32_t* lq = nullptr, uint32_t lcount = 0u) {
+    const uint32_t count = LOCALQ ? lcount : *a.count;
+    const uint32_t* queue = LOCALQ ? lq : a.queue;      // no __restrict__: a warp-local queue was written earlier in this kernel
     const uint32_t lane = threadIdx.x & 31u;
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(a.stat_rays, (unsigned long long)count);
+    uint32_t lhead = 0u;
+    if (!LOCALQ && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(a.stat_rays, (unsigned long long)count);
     uint2 stack[RT2_STACK_SIZE];
     int sp = 0, inst_sp = 0;
     bool active = false, exhausted = false;
@@ -162,23 +169,27 @@ __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a) {
     V3 world_id = v3(1.f, 1.f, 1.f);
     V3 dobj = v3(1.f, 1.f, 1.f);
     bool sh_pending = false;
+    V3 oobj = v3(0.f, 0.f, 0.f);              // FLAT: origin in the object space of instance `inst`
     for (;;) {
         const uint32_t need = __ballot_sync(0xFFFFFFFFu, !active);
         if (!exhausted && (need == 0xFFFFFFFFu || (REFILL_MIN > 0 && __popc(need) >= REFILL_MIN))) {
             const uint32_t n = __popc(need);
             uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(a.head, n);
-            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            if (LOCALQ) { base = lhead; lhead += n; }
+            else {
+                if (lane == 0) base = atomicAdd(a.head, n);
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            }
             if (!active) {
                 const uint32_t idx = base + __popc(need & ((1u << lane) - 1u));
                 if (idx < count) {
-                    slot = a.queue[idx];
+                    slot = queue[idx];
                     const float4 r0 = RT2_LDRAY(a.st_ray0 + slot), r1 = RT2_LDRAY(a.st_ray1 + slot);
                     const V3 o = v3(r0.x, r0.y, r0.z), d = GENERIC ? v3(r1.x, r1.y, r1.z) : v3(r0.w, r1.x, r1.y);
                     if (GENERIC) { tmin = r0.w; tmax = r1.w; }
                     if (INSTANCED) { world_id = ray_inv_dir(d); rp = ray_prep_from_inv(o, world_id); }
                     else rp = make_ray_prep(o, d);
-                    if (!INSTANCED) sh = make_shear(d);
+                    if (!INSTANCED && !FLAT) sh = make_shear(d);
                     best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
                     tri_slot = 0xFFFFFFFFu; inst = 0xFFFFFFFFu;
                     sp = 0; inst_sp = 0; ngroup = make_uint2(0u, 0x80000000u); tgroup = make_uint2(0u, 0u);
@@ -193,7 +204,7 @@ __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a) {
         if (active) {
             for (;;) {
                 if (ngroup.y > 0x00FFFFFFu) {
-                    const Node8* level = (INSTANCED && inst == 0xFFFFFFFFu) ? a.tlas_nodes : a.blas_nodes;
+                    const Node8* level = FLAT ? a.flat_nodes : ((INSTANCED && inst == 0xFFFFFFFFu) ? a.tlas_nodes : a.blas_nodes);
                     cwbvh_node_step(level, rp, tmin, fminf(best.t, tmax), ngroup, tgroup, stack, sp);
 #ifdef RT2_TRACE_PREFETCH_NODE   // measured -3.4 % on C2 (the address arithmetic costs more than the latency it hides): off
                     // the node this lane visits next is known now; its 80 bytes are wanted only after the triangle phase
@@ -235,22 +246,37 @@ __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a) {
                         if (POSTPONE_PCT > 0) {
                             if (__popc(__activemask()) * 100 < in_loop * POSTPONE_PCT && sp < postpone_limit) {
 #ifndef RT2_TRI_NOALLOC
-                                prefetch_l1(a.tris + (tgroup.x + rt2_fhs(tgroup.y)));
+                                if (FLAT) prefetch_l1(a.flat_leaf + (tgroup.x + rt2_fhs(tgroup.y)));
+                                else prefetch_l1(a.tris + (tgroup.x + rt2_fhs(tgroup.y)));
 #endif      // postponed: by the time it is tested it sits in L1 (+0.5-1 %)
                                 stack[sp++] = tgroup; break;
                             }
                         }
                         const uint32_t ti = rt2_fhs(tgroup.y);
                         tgroup.y &= ~(1u << ti);
-                        const uint32_t s = tgroup.x + ti;
+                        uint32_t s = tgroup.x + ti;
+                        if (FLAT) {
+                            const uint2 lf = __ldg(reinterpret_cast<const uint2*>(a.flat_leaf) + s);
+                            s = lf.y;
+                            if (lf.x != inst) {            // another instance: object-space origin + shear constants for it
+                                inst = lf.x;
+                                const InstanceRec* ir = a.instances + inst;
+                                float m[12];
+#pragma unroll
+                                for (int k = 0; k < 3; k++) { const float4 r = ld16f(ir->inv + 4 * k); m[4 * k] = r.x; m[4 * k + 1] = r.y; m[4 * k + 2] = r.z; m[4 * k + 3] = r.w; }
+                                const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot];
+                                oobj = xform_point(m, v3(r0.x, r0.y, r0.z));
+                                sh = make_shear(xform_vector(m, GENERIC ? v3(r1.x, r1.y, r1.z) : v3(r0.w, r1.x, r1.y)));
+                            }
+                        }
                         const TriPos* tp = a.tris + s;
                         const float4 va = ld16f_stream(&tp->v0), vb = ld16f_stream(&tp->v1), vc = ld16f_stream(&tp->v2);
                         if (INSTANCED && sh_pending) { sh = make_shear(dobj); sh_pending = false; }
                         float t, u, v;
-                        if (ray_triangle(v3(rp.ox, rp.oy, rp.oz), sh, tmin, tmax, v3(va.x, va.y, va.z), v3(vb.x, vb.y, vb.z),
+                        if (ray_triangle(FLAT ? oobj : v3(rp.ox, rp.oy, rp.oz), sh, tmin, tmax, v3(va.x, va.y, va.z), v3(vb.x, vb.y, vb.z),
                                          v3(vc.x, vc.y, vc.z), &t, &u, &v)) {
                             const uint32_t geom = f2u(va.w), prim = f2u(vb.w);
-                            const uint32_t hi = INSTANCED ? inst : 0u;
+                            const uint32_t hi = (INSTANCED || FLAT) ? inst : 0u;
                             if (hit_closer(t, hi, geom, prim, best)) {
                                 best.t = t; best.u = u; best.v = v; best.inst = hi; best.geom = geom; best.prim = prim;
                                 tri_slot = s;
@@ -266,7 +292,7 @@ __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a) {
                     }
                     if (sp == 0) {
                         RT2_STHIT(a.st_hit + slot, make_float4(best.t, best.u, best.v, __uint_as_float(tri_slot)));
-                        if (INSTANCED) a.st_hit_inst[slot] = best.inst;
+                        if (INSTANCED || FLAT) a.st_hit_inst[slot] = best.inst;
                         active = false;
                         break;
                     }
@@ -285,8 +311,70 @@ __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) { trace_dyn_body
 // entry point because __launch_bounds__(128, n) on the single-level kernels changes their code (C2 -0.4 % at n = 7).
 template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false>
 __global__ void __launch_bounds__(128, 6) k_trace_dyn_tlas(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, true, GENERIC>(a); }
+// flattened instancing: single-level walk over the (instance, triangle) tree
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false>
+__global__ void __launch_bounds__(128) k_trace_dyn_flat(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, false, GENERIC, false, true>(a); }
 
-// refrence.rgen:28-46 for one traced ray of each queued slot
+// refrence.rgen:28-46 for the path in `slot` whose ray just came back (hit record in st_hit): emission / throughput update,
+// cosine-lobe sample, path regeneration.  Returns true while the pixel still has rays to trace (state written back), false when
+// its last sample finished (radiance stored).
+__device__ __forceinline__ bool k1_shade_step(const ShadeArgs& a, const float* lut, uint32_t slot, uint32_t* hits) {
+    const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot], ac = a.st_acc[slot];
+    const uint4 misc = a.st_misc[slot];
+    const float4 h = a.st_hit[slot];
+    const uint32_t x = slot % a.band.width, ly = slot / a.band.width;
+    const uint32_t y = band_local_to_global(a.band, ly);
+    V3 o = v3(r0.x, r0.y, r0.z), d = v3(r0.w, r1.x, r1.y);
+    V3 thr = v3(r1.z, r1.w, ac.x), rad = v3(ac.y, ac.z, ac.w);
+    Rng rng; rng.index = misc.x; rng.seed = jenkins_hash(zcurve_to_linear(x, y)) + (a.frame + 13u);
+    uint32_t sample = misc.y & 0xFFFFu, bounce = misc.y >> 16;
+    const uint32_t tri_slot = __float_as_uint(h.w);
+    bool next_sample;
+    if (tri_slot == 0xFFFFFFFFu) {                         // refrence.rgen:32-36
+        const V3 emission = environment_radiance(a.sc, *a.g, d);
+        rad = rad + thr * emission;
+        next_sample = true;
+    } else {
+        (*hits)++;
+        const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? a.st_hit_inst[slot] : 0u, h.y, h.z);
+        const V3 n = sf.normal, color = sf.color;
+        rad = rad + thr * sf.emission;                          // refrence.rgen:38
+        thr = thr * color;                                   // refrence.rgen:39
+        // RAB_GetSurfaceBrdfSample, bridge :437-461 (diffuseProbability == 1: cosine lobe only)
+        const float rx = rng_next(rng), ry = rng_next(rng), rz = rng_next(rng);
+        (void)rx;
+        const V3 hvec = sample_cos_hemisphere(ry, rz, (a.flags & RT2_LAUNCH_TRIG_LIBDEVICE) != 0u);
+        const V3 world_pos = o + d * h.x;                    // Hit.glsl:67
+        d = tangent_to_world(n, hvec);
+        o = world_pos;                                       // refrence.rgen:42
+        bounce++;
+        next_sample = bounce >= a.max_bounces;
+    }
+    if (next_sample) {
+        sample++; bounce = 0;
+        if (sample >= a.spp) {
+            // refrence.rgen:46
+            const float inv = (float)a.spp;
+            store_shading_output(*a.g, (size_t)y * a.band.width + x, v3(rad.x / inv, rad.y / inv, rad.z / inv), v3(0.f, 0.f, 0.f), true,
+                                 a.diffuse_f16, a.specular_f16, a.diffuse_f32);
+            return false;
+        }
+        thr = v3(1.f, 1.f, 1.f);
+        setup_primary_ray(a.g->view, x, y, &o, &d);
+    }
+    a.st_ray0[slot] = make_float4(o.x, o.y, o.z, d.x);
+    a.st_ray1[slot] = make_float4(d.y, d.z, thr.x, thr.y);
+    a.st_acc[slot] = make_float4(thr.z, rad.x, rad.y, rad.z);
+    a.st_misc[slot] = make_uint4(rng.index, sample | (bounce << 16), 0u, 0u);
+    return true;
+}
+
+// warp-aggregated counter flush (every lane of the warp calls this)
+__device__ __forceinline__ void warp_flush_counter(unsigned long long* dst, uint32_t v) {
+    const uint32_t sum = __reduce_add_sync(0xFFFFFFFFu, v);
+    if ((threadIdx.x & 31u) == 0u && sum) atomicAdd(dst, (unsigned long long)sum);
+}
+
 // 4 blocks of 256 threads per SM (64 registers): the kernel waits on dependent gathers (state -> shading record -> texels),
 // so resident warps buy bandwidth; measured 1 / 3 / 4 / 5 blocks: 2488 / 2486 / 2532 / 2501 Mrays/s on C2 (5 spills).
 #ifndef RT2_SHADE_MIN_BLOCKS
@@ -298,6 +386,7 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_k1_shade(ShadeArg
     __syncthreads();
     const uint32_t count = *a.count_in;
     const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t hits = 0;
     // all lanes of a warp iterate together (warp_append uses warp collectives)
     // the queue entry of the next iteration is fetched one iteration ahead: one dependent memory round trip less per ray
     uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u;
@@ -305,66 +394,101 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_k1_shade(ShadeArg
     for (; i0 < count; i0 += stride) {
         const uint32_t i = i0 + (threadIdx.x & 31u);
         bool alive = false;
-        uint32_t slot = slot_ahead;
+        const uint32_t slot = slot_ahead;
         if (i + stride < count) slot_ahead = a.queue_in[i + stride];
-        if (i < count) {
-            const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot], ac = a.st_acc[slot];
-            const uint4 misc = a.st_misc[slot];
-            const float4 h = a.st_hit[slot];
-            const uint32_t x = slot % a.band.width, ly = slot / a.band.width;
-            const uint32_t y = band_local_to_global(a.band, ly);
-            V3 o = v3(r0.x, r0.y, r0.z), d = v3(r0.w, r1.x, r1.y);
-            V3 thr = v3(r1.z, r1.w, ac.x), rad = v3(ac.y, ac.z, ac.w);
-            Rng rng; rng.index = misc.x; rng.seed = jenkins_hash(zcurve_to_linear(x, y)) + (a.frame + 13u);
-            uint32_t sample = misc.y & 0xFFFFu, bounce = misc.y >> 16;
-            const uint32_t tri_slot = __float_as_uint(h.w);
-            bool next_sample;
-            if (tri_slot == 0xFFFFFFFFu) {                         // refrence.rgen:32-36
-                const V3 emission = environment_radiance(a.sc, *a.g, d);
-                rad = rad + thr * emission;
-                next_sample = true;
-            } else {
-                const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? a.st_hit_inst[slot] : 0u, h.y, h.z);
-                const V3 n = sf.normal, color = sf.color;
-                rad = rad + thr * sf.emission;                          // refrence.rgen:38
-                thr = thr * color;                                   // refrence.rgen:39
-                // RAB_GetSurfaceBrdfSample, bridge :437-461 (diffuseProbability == 1: cosine lobe only)
-                const float rx = rng_next(rng), ry = rng_next(rng), rz = rng_next(rng);
-                (void)rx;
-                const V3 hvec = sample_cos_hemisphere(ry, rz, (a.flags & RT2_LAUNCH_TRIG_LIBDEVICE) != 0u);
-                const V3 world_pos = o + d * h.x;                    // Hit.glsl:67
-                d = tangent_to_world(n, hvec);
-                o = world_pos;                                       // refrence.rgen:42
-                bounce++;
-                next_sample = bounce >= a.max_bounces;
-            }
-            alive = true;
-            if (next_sample) {
-                sample++; bounce = 0;
-                if (sample >= a.spp) {
-                    // refrence.rgen:46
-                    const float inv = (float)a.spp;
-                    store_shading_output(*a.g, (size_t)y * a.band.width + x, v3(rad.x / inv, rad.y / inv, rad.z / inv), v3(0.f, 0.f, 0.f), true,
-                                         a.diffuse_f16, a.specular_f16, a.diffuse_f32);
-                    alive = false;
-                } else {
-                    thr = v3(1.f, 1.f, 1.f);
-                    setup_primary_ray(a.g->view, x, y, &o, &d);
-                }
-            }
-            if (alive) {
-                a.st_ray0[slot] = make_float4(o.x, o.y, o.z, d.x);
-                a.st_ray1[slot] = make_float4(d.y, d.z, thr.x, thr.y);
-                a.st_acc[slot] = make_float4(thr.z, rad.x, rad.y, rad.z);
-                a.st_misc[slot] = make_uint4(rng.index, sample | (bounce << 16), 0u, 0u);
-            }
-        }
+        if (i < count) alive = k1_shade_step(a, lut, slot, &hits);
         warp_append(alive, slot, a.queue_out, a.count_out);
     }
+    warp_flush_counter(a.stat_hits, hits);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Warp-local wavefronts: the whole frame in ONE persistent launch.
+// Every warp owns a population of up to P paths (slots in its private queue).  It alternates between a shade phase — the
+// k_k1_shade body over its population, 32 paths at a time at full lane width, finished pixels replaced by new ones pulled from
+// a global pixel counter — and a trace phase, the postponing / lane-refilling traversal loop over the same queue.  No kernel
+// boundary and no grid-wide barrier per bounce: a warp's tail (its last long rays) overlaps other warps' phases instead of
+// idling the GPU, and a warp that shades (latency bound) shares its SM with warps that traverse (issue bound).  Traversal
+// state is scoped to the trace phase, so the register budget is max(trace, shade), not the sum.  The image is bit-identical
+// to the launch-per-bounce form: same per-pixel state machine, closest hit = total order, RNG keyed on pixel + frame.
+// ------------------------------------------------------------------------------------------------
+struct WarpPathArgs {
+    uint32_t* pop;            // num_warps x P slot queue, warp-private rows
+    uint32_t P;               // population per warp (multiple of 32)
+    uint32_t* pixel_head;     // next unclaimed padded lane of [first, end)
+    uint32_t first, end;
+};
+
+template <bool INSTANCED, bool FLAT>
+__device__ __forceinline__ void path_warp_body(const TraceArgs& t, const ShadeArgs& a, const WarpPathArgs& w, const float* lut) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    uint32_t* q = w.pop + (size_t)warp * w.P;
+    const uint32_t tiles_x = (a.band.width + 7u) >> 3;
+    uint32_t n = 0, rays = 0, hits = 0;
+    bool exhausted = false;
+    for (;;) {
+        // ---- shade phase: every path of the population has a hit record waiting --------------------------------
+        uint32_t wr = 0;
+        for (uint32_t i0 = 0; i0 < n; i0 += 32u) {
+            const uint32_t i = i0 + lane;
+            bool alive = false;
+            uint32_t slot = 0;
+            if (i < n) { slot = q[i]; alive = k1_shade_step(a, lut, slot, &hits); }
+            const uint32_t m = __ballot_sync(0xFFFFFFFFu, alive);      // also orders this batch's queue reads before its writes
+            if (alive) q[wr + __popc(m & ((1u << lane) - 1u))] = slot;
+            wr += __popc(m);
+        }
+        // finished pixels are replaced: pull padded lanes (8x4 tiles, so a fresh batch of 32 is one coherent tile)
+        while (!exhausted && wr < w.P) {
+            const uint32_t want = min(32u, w.P - wr);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(w.pixel_head, want);
+            base = __shfl_sync(0xFFFFFFFFu, base, 0);
+            const uint32_t i = w.first + base + lane;
+            bool alive = false;
+            uint32_t slot = 0;
+            if (lane < want && i < w.end) {
+                const uint32_t tile = i >> 5, within = i & 31u;
+                const uint32_t x = (tile % tiles_x) * 8u + (within & 7u), ly = (tile / tiles_x) * 4u + (within >> 3);
+                if (x < a.band.width && ly < a.band.local_rows) {
+                    alive = true;
+                    slot = ly * a.band.width + x;
+                    V3 o, d;
+                    setup_primary_ray(a.g->view, x, band_local_to_global(a.band, ly), &o, &d);
+                    a.st_ray0[slot] = make_float4(o.x, o.y, o.z, d.x);
+                    a.st_ray1[slot] = make_float4(d.y, d.z, 1.0f, 1.0f);
+                    a.st_acc[slot] = make_float4(1.0f, 0.0f, 0.0f, 0.0f);
+                    a.st_misc[slot] = make_uint4(1u, 0u, 0u, 0u);
+                }
+            }
+            const uint32_t m = __ballot_sync(0xFFFFFFFFu, alive);
+            if (alive) q[wr + __popc(m & ((1u << lane) - 1u))] = slot;
+            wr += __popc(m);
+            if (w.first + base + want >= w.end) exhausted = true;
+        }
+        n = wr;
+        if (n == 0u) break;
+        __syncwarp();          // queue + path state written by other lanes of this warp are visible from here on
+        // ---- trace phase ------------------------------------------------------------------------------------------
+        trace_dyn_body<20, 4, 8, INSTANCED, false, true, FLAT>(t, q, n);
+        rays += n;
+        __syncwarp();
+    }
+    if (lane == 0) { if (rays) atomicAdd(t.stat_rays, (unsigned long long)rays); }
+    warp_flush_counter(a.stat_hits, hits);
+}
+
+template <bool INSTANCED, bool FLAT = false>
+__global__ void __launch_bounds__(128) k_path_warp(TraceArgs t, ShadeArgs a, WarpPathArgs w) {
+    __shared__ float lut[256];
+    lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
+    __syncthreads();
+    path_warp_body<INSTANCED, FLAT>(t, a, w, lut);
 }
 
 // primary visibility probe: one thread per pixel, 8x4 tiles per warp
-template <bool INSTANCED>
+template <bool INSTANCED, bool FLAT = false>
 __global__ void __launch_bounds__(128) k_primary(TraceArgs a, Band band, const rt2_gconst* g, rt2_hit_record* out, uint32_t padded,
                                                  unsigned long long* stat_hits) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -378,7 +502,8 @@ __global__ void __launch_bounds__(128) k_primary(TraceArgs a, Band band, const r
     setup_primary_ray(g->view, x, y, &ray.o, &ray.d);
     ray.tmin = RT2_K1_TMIN; ray.tmax = RT2_BACKGROUND_DEPTH;
     Hit best; best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
-    if (INSTANCED) tlas_closest_hit(a.tlas_nodes, a.tlas_slot_to_inst, a.instances, a.blas_nodes, a.tris, ray, best, nullptr);
+    if (FLAT) flat_closest_hit(a.flat_nodes, a.flat_leaf, a.instances, a.tris, ray, best, nullptr);
+    else if (INSTANCED) tlas_closest_hit(a.tlas_nodes, a.tlas_slot_to_inst, a.instances, a.blas_nodes, a.tris, ray, best, nullptr);
     else cwbvh_closest_hit(a.blas_nodes, a.tris, ray, 0u, best, nullptr);
     rt2_hit_record r;
     r.instance = best.inst; r.geometry = best.geom; r.primitive = best.prim;
@@ -401,7 +526,7 @@ static cudaError_t dev_alloc(rt2_ctx* ctx, T** p, size_t n) {
 void frame_release(rt2_ctx* ctx) {
     FrameBuffers& f = ctx->fb;
     void* ptrs[] = {f.diffuse_f16, f.specular_f16, f.diffuse_f32, f.hit_ids, f.output_rgba8, f.st_ray0, f.st_ray1, f.st_acc, f.st_misc,
-                    f.st_hit, f.st_hit_inst, f.queue0, f.queue1, f.counters};
+                    f.st_hit, f.st_hit_inst, f.queue0, f.queue1, f.counters, f.warp_pop};
     for (void* p : ptrs) if (p) cudaFree(p);
     f = FrameBuffers();
 }
@@ -453,7 +578,10 @@ static TraceArgs make_trace_args(rt2_ctx* ctx) {
     TraceArgs t{};
     t.blas_nodes = s.blas.nodes; t.tris = s.blas.tris;
     t.tlas_nodes = s.tlas.nodes; t.tlas_slot_to_inst = s.tlas.slot_to_prim; t.instances = s.instances;
+    const bool flat = s.flat.nodes && ctx->use_flat;
+    t.flat_nodes = flat ? s.flat.nodes : nullptr; t.flat_leaf = flat ? s.flat_leaf : nullptr;
     t.st_ray0 = f.st_ray0; t.st_ray1 = f.st_ray1; t.st_hit = f.st_hit; t.st_hit_inst = f.st_hit_inst;
+    if (flat) { const uint32_t d = s.flat.depth + 2u; t.postpone_limit = d < RT2_STACK_SIZE ? RT2_STACK_SIZE - d : 0u; return t; }
     const uint32_t depth = s.blas.depth + (s.num_instances ? 2u * s.tlas.depth + 2u : 0u) + 2u;    // node groups a ray can have stacked at once
     t.postpone_limit = depth < RT2_STACK_SIZE ? RT2_STACK_SIZE - depth : 0u;
     return t;
@@ -507,7 +635,8 @@ int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp) {
     TraceArgs t = make_trace_args(ctx);
     unsigned long long* hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
     if (padded) {
-        if (ctx->scene.num_instances) k_primary<true><<<(padded + 127) / 128, 128, 0, ctx->stream>>>(t, band, ctx->d_gconst, f.hit_ids, padded, hits);
+        if (ctx->scene.flat.nodes && ctx->use_flat) k_primary<false, true><<<(padded + 127) / 128, 128, 0, ctx->stream>>>(t, band, ctx->d_gconst, f.hit_ids, padded, hits);
+        else if (ctx->scene.num_instances) k_primary<true><<<(padded + 127) / 128, 128, 0, ctx->stream>>>(t, band, ctx->d_gconst, f.hit_ids, padded, hits);
         else k_primary<false><<<(padded + 127) / 128, 128, 0, ctx->stream>>>(t, band, ctx->d_gconst, f.hit_ids, padded, hits);
     }
     RT2_CUDA(ctx, cudaGetLastError());
@@ -544,7 +673,7 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
         const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
         for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
         ctx->prof_events.clear();
-        if (profile) { ctx->prof_events.resize((size_t)iterations * 3); for (auto& e : ctx->prof_events) RT2_CUDA(ctx, cudaEventCreate(&e)); }
+        if (profile) { ctx->prof_events.resize(ctx->path_mode == 1 ? 3 : (size_t)iterations * 3); for (auto& e : ctx->prof_events) RT2_CUDA(ctx, cudaEventCreate(&e)); }
         // Wavefront chains: the pixels of the frame are independent, so the tile range is cut into `chains` contiguous parts,
         // each running its own init -> (trace -> shade) x iterations sequence on its own stream with its own queues and
         // counters.  While one chain's trace kernel drains its last long rays (a ~45 us tail per launch that does not
@@ -558,7 +687,41 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
         // 346 k - / 1773 / 1882, 259 k (one of 8 ranks) 1488 / 1662 / 1752.  A scene whose trace launches last only microseconds
         // (C1, 32 triangles) is launch-rate bound and loses 10-25 % to the extra launches: one chain.
         const uint64_t pixels = (uint64_t)band.width * band.local_rows;
-        const int full_blocks = ctx->trace_blocks_per_sm[s.num_instances ? 1 : 0] * ctx->num_sms;
+        const bool flat = s.flat.nodes && ctx->use_flat;
+        if (ctx->path_mode == 1 && (!s.num_instances || flat || unified_walk_fits(s))) {
+            // warp-local wavefronts: one persistent launch for the whole frame (see k_path_warp)
+            const int occ = ctx->path_blocks_per_sm[flat ? 2 : (s.num_instances ? 1 : 0)];
+            const int bps = ctx->warp_blocks_per_sm ? std::min(ctx->warp_blocks_per_sm, occ) : occ;
+            int blocks = bps * ctx->num_sms;
+            uint32_t P = ctx->warp_paths;
+            if (!P) {
+                // population per warp: 8 rays per lane when the frame is large enough, never below 2 per lane — a small frame
+                // (one rank's bands) runs on fewer blocks instead
+                const uint64_t per_warp = pixels / ((uint64_t)blocks * 4u);
+                P = (uint32_t)std::min<uint64_t>(256u, std::max<uint64_t>(64u, per_warp & ~31ull));
+                if (per_warp < 64u) blocks = std::max(ctx->num_sms, (int)std::min<uint64_t>((uint64_t)blocks, pixels / (64u * 4u) + 1u));
+            }
+            P = std::max(32u, P & ~31u);
+            const size_t need = (size_t)blocks * 4u * P;
+            if (f.warp_pop_cap < need) {
+                if (f.warp_pop) { RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(f.warp_pop); f.warp_pop = nullptr; f.warp_pop_cap = 0; }
+                RT2_CUDA(ctx, cudaMalloc((void**)&f.warp_pop, need * 4));
+                f.warp_pop_cap = need; ctx->device_bytes += need * 4;
+            }
+            WarpPathArgs w{f.warp_pop, P, f.counters + 4, 0u, padded};
+            if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[0], ctx->stream));
+            if (flat) k_path_warp<false, true><<<blocks, 128, 0, ctx->stream>>>(t, a, w);
+            else if (s.num_instances) k_path_warp<true><<<blocks, 128, 0, ctx->stream>>>(t, a, w);
+            else k_path_warp<false><<<blocks, 128, 0, ctx->stream>>>(t, a, w);
+            if (profile) { RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[1], ctx->stream)); RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[2], ctx->stream)); }
+            RT2_CUDA(ctx, cudaGetLastError());
+            ctx->stats.kernel_launches = 1;
+            ctx->stats.wavefront_iterations = iterations;
+            ctx->stats_from_counters = true;
+            ctx->pending_rays_static = 0;
+            return RT2_OK;
+        }
+        const int full_blocks = ctx->trace_blocks_per_sm[flat ? 3 : (s.num_instances ? 1 : 0)] * ctx->num_sms;
         const bool small_wave = pixels < 900000u;
         const bool tiny_scene = s.num_tris < 4096u && !s.num_instances;      // an instanced scene's BLAS may be small; its trace launches are not
         const uint32_t auto_chains = tiny_scene ? 1u : (small_wave ? 8u : 2u);
@@ -602,7 +765,9 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
                 cudaStream_t st = k.st;
                 if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], st));
                 t.queue = k.q[it & 1]; t.count = k.cnt + 2 * it; t.head = k.cnt + 2 * it + 1;
-                if (s.num_instances) {
+                if (flat) {
+                    k_trace_dyn_flat<20, 4, 8><<<k.trace_blocks, 128, 0, st>>>(t);
+                } else if (s.num_instances) {
                     // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
                     const bool unified = ctx->trace_variant != 0 && unified_walk_fits(s);
                     if (unified) k_trace_dyn_tlas<20, 4, 8><<<k.trace_blocks, 128, 0, st>>>(t);
@@ -633,7 +798,9 @@ int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* cou
     const DeviceScene& s = ctx->scene;
     TraceArgs t = make_trace_args(ctx);
     t.queue = queue; t.count = count; t.head = head; t.stat_rays = stat_rays;
-    if (s.num_instances) {
+    if (t.flat_nodes) {
+        k_trace_dyn_flat<20, 4, 8, true><<<ctx->trace_blocks_per_sm[3] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+    } else if (s.num_instances) {
         if (unified_walk_fits(s)) k_trace_dyn_tlas<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
         else k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
     } else {
@@ -654,6 +821,17 @@ int render_init(rt2_ctx* ctx) {
     int b2 = 0;
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace_dyn_tlas<20, 4, 8>, 128, 0));
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, k_trace<true>, 128, 0));
+    if (const char* e = getenv("RT2_PATH_MODE")) ctx->path_mode = atoi(e);
+    if (const char* e = getenv("RT2_WARP_P")) { int v = atoi(e); if (v >= 32 && v <= 4096) ctx->warp_paths = (uint32_t)v; }
+    if (const char* e = getenv("RT2_WARP_BLOCKS")) { int v = atoi(e); if (v >= 1 && v <= 16) ctx->warp_blocks_per_sm = v; }
+    int p0 = 0, p1 = 0, p2 = 0, b3 = 0;
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p0, k_path_warp<false>, 128, 0));
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p1, k_path_warp<true>, 128, 0));
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2, k_path_warp<false, true>, 128, 0));
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, k_trace_dyn_flat<20, 4, 8>, 128, 0));
+    ctx->path_blocks_per_sm[0] = std::max(p0, 1); ctx->path_blocks_per_sm[1] = std::max(p1, 1); ctx->path_blocks_per_sm[2] = std::max(p2, 1);
+    ctx->trace_blocks_per_sm[3] = std::max(b3, 1);
+    if (const char* e = getenv("RT2_USE_FLAT")) ctx->use_flat = atoi(e) != 0;
     ctx->trace_blocks_per_sm[0] = std::max(b0, 1); ctx->trace_blocks_per_sm[1] = std::max(b1, 1); ctx->trace_blocks_per_sm[2] = std::max(b2, 1);
     return RT2_OK;
 }

@@ -42,6 +42,29 @@ __global__ void k_instance_boxes(const InstanceRec* __restrict__ inst, uint32_t 
     hi[i] = make_float4(h.x + e.x, h.y + e.y, h.z + e.z, 0.f);
 }
 
+// Flattened instancing: world-space box of (instance i / T, BLAS leaf slot i % T), padded like the instance boxes — the box is a
+// culling aid only (the triangle is tested in object space) and must never be tighter than what that test can accept.
+__global__ void k_flat_boxes(const InstanceRec* __restrict__ inst, const TriPos* __restrict__ tris, uint32_t T, uint64_t n, float4* lo, float4* hi) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t in = (uint32_t)(i / T), s = (uint32_t)(i % T);
+    const float* m = inst[in].fwd;
+    const TriPos t = tris[s];
+    const V3 a = xform_point(m, v3(t.v0.x, t.v0.y, t.v0.z)), b = xform_point(m, v3(t.v1.x, t.v1.y, t.v1.z)), c = xform_point(m, v3(t.v2.x, t.v2.y, t.v2.z));
+    const V3 l = v3(fminf(a.x, fminf(b.x, c.x)), fminf(a.y, fminf(b.y, c.y)), fminf(a.z, fminf(b.z, c.z)));
+    const V3 h = v3(fmaxf(a.x, fmaxf(b.x, c.x)), fmaxf(a.y, fmaxf(b.y, c.y)), fmaxf(a.z, fmaxf(b.z, c.z)));
+    V3 e = (h - l) * 1e-4f + v3(1e-6f, 1e-6f, 1e-6f);
+    e = e + v3(fmaxf(fabsf(l.x), fabsf(h.x)), fmaxf(fabsf(l.y), fabsf(h.y)), fmaxf(fabsf(l.z), fabsf(h.z))) * 1.9073486328125e-06f;   // 2^-19
+    lo[i] = make_float4(l.x - e.x, l.y - e.y, l.z - e.z, 0.f);
+    hi[i] = make_float4(h.x + e.x, h.y + e.y, h.z + e.z, 0.f);
+}
+__global__ void k_flat_leaves(const uint32_t* __restrict__ out_prim, uint32_t T, uint64_t n, FlatLeaf* leaves) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t p = out_prim[i];
+    leaves[i] = FlatLeaf{p / T, p % T};
+}
+
 // inverse of an affine 3x4 in double (adjugate / determinant), rounded to float — the same formula,
 // in the same order, as the oracle's invert_affine (host code; compiled with -ffp-contract=off).
 static void invert_affine(const float* m, float* out) {
@@ -71,7 +94,8 @@ void scene_release(rt2_ctx* ctx) {
     DeviceScene& s = ctx->scene;
     void* ptrs[] = {s.vertices, s.indices, s.geoms, s.geom_tri_offset, s.geom_shade, s.texels, s.textures, s.srgb_lut, s.sky, s.instances, s.tri_shade};
     for (void* p : ptrs) if (p) cudaFree(p);
-    s.blas.release(); s.tlas.release();
+    s.blas.release(); s.tlas.release(); s.flat.release();
+    if (s.flat_leaf) cudaFree(s.flat_leaf);
     s = DeviceScene();
 }
 
@@ -164,7 +188,8 @@ int scene_upload(rt2_ctx* ctx, const rt2_scene_desc* d) {
 int scene_build_accel(rt2_ctx* ctx) {
     DeviceScene& s = ctx->scene;
     if (!s.geom_tri_offset) return fail(ctx, RT2_E_STATE, "rt2_build_accel before rt2_upload_scene");
-    s.blas.release(); s.tlas.release();
+    s.blas.release(); s.tlas.release(); s.flat.release();
+    if (s.flat_leaf) { cudaFree(s.flat_leaf); s.flat_leaf = nullptr; }
     if (s.tri_shade) { cudaFree(s.tri_shade); s.tri_shade = nullptr; }
     s.accel_built = false;
     LaunchCounter lc;
@@ -185,12 +210,40 @@ int scene_build_accel(rt2_ctx* ctx) {
         cudaFree(lo); cudaFree(hi);
         if (rc != RT2_OK) return fail(ctx, rc, "TLAS build: " + err);
         s.tlas.num_prims = s.num_instances;
+        // Flattened instancing when it fits: n = instances x triangles primitives cost ~40 B each when built (80-byte node per ~3.7
+        // primitives + 8-byte leaf record) and ~300 B each of build scratch.  RT2_FLATTEN=0 keeps the two-level walk only,
+        // RT2_FLATTEN=1 forces the attempt; the default takes it when the scratch fits in half of the free device memory.
+        const uint64_t n_flat = (uint64_t)s.num_instances * s.num_tris;
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        int want = n_flat > 0 && n_flat < 0x7FFFFFF0ull && n_flat * 320ull < free_b / 2 ? 1 : 0;
+        if (const char* e = getenv("RT2_FLATTEN")) want = atoi(e) != 0 && n_flat > 0 && n_flat < 0x7FFFFFF0ull;
+        if (want) {
+            RT2_CUDA(ctx, cudaMalloc((void**)&lo, n_flat * 16));
+            RT2_CUDA(ctx, cudaMalloc((void**)&hi, n_flat * 16));
+            k_flat_boxes<<<(uint32_t)((n_flat + 255) / 256), 256, 0, ctx->stream>>>(s.instances, s.blas.tris, s.num_tris, n_flat, lo, hi);
+            lc.add(1);
+            Node8* nodes = nullptr; uint32_t* out_prim = nullptr; uint32_t num_nodes = 0, depth = 0;
+            rc = build_cwbvh_from_boxes(ctx->stream, lo, hi, (uint32_t)n_flat, &nodes, &num_nodes, &out_prim, &depth, &lc, err);
+            cudaFree(lo); cudaFree(hi);
+            if (rc != RT2_OK) return fail(ctx, rc, "flattened-instance BVH build: " + err);
+            // the builder sizes the node array for the worst case (n + 1): keep only what was used
+            RT2_CUDA(ctx, cudaMalloc((void**)&s.flat.nodes, (size_t)num_nodes * sizeof(Node8)));
+            RT2_CUDA(ctx, cudaMemcpyAsync(s.flat.nodes, nodes, (size_t)num_nodes * sizeof(Node8), cudaMemcpyDeviceToDevice, ctx->stream));
+            RT2_CUDA(ctx, cudaMalloc((void**)&s.flat_leaf, n_flat * sizeof(FlatLeaf)));
+            k_flat_leaves<<<(uint32_t)((n_flat + 255) / 256), 256, 0, ctx->stream>>>(out_prim, s.num_tris, n_flat, s.flat_leaf);
+            lc.add(1);
+            RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            cudaFree(nodes); cudaFree(out_prim);
+            s.flat.num_nodes = num_nodes; s.flat.num_prims = (uint32_t)n_flat; s.flat.depth = depth;
+            ctx->device_bytes += (size_t)num_nodes * sizeof(Node8) + n_flat * sizeof(FlatLeaf);
+        }
     }
     RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     RT2_CUDA(ctx, cudaGetLastError());
     s.accel_built = true;
     ctx->stats.kernel_launches = lc.n;
-    ctx->stats.bvh_nodes = (uint64_t)s.blas.num_nodes + s.tlas.num_nodes;
+    ctx->stats.bvh_nodes = (uint64_t)s.blas.num_nodes + s.tlas.num_nodes + s.flat.num_nodes;
     ctx->stats.bvh_triangles = s.num_tris;
     return RT2_OK;
 }

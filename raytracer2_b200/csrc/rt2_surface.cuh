@@ -11,6 +11,7 @@ struct SceneRefs {
     const Node8* blas_nodes; const TriPos* tris;
     const Node8* tlas_nodes; const uint32_t* tlas_slot_to_inst;
     const InstanceRec* instances;            // non-null => instanced (two-level traversal)
+    const Node8* flat_nodes; const FlatLeaf* flat_leaf;   // non-null => flattened instancing: one tree over (instance, triangle) pairs
     const TriShade* tri_shade; const GeomShade* geom_shade;
     const uint32_t* texels; const TextureRec* textures; const float* srgb_lut;
     const float4* sky; uint32_t sky_w, sky_h;
@@ -20,6 +21,7 @@ inline SceneRefs make_scene_refs(const rt2_ctx* ctx) {
     SceneRefs r{};
     r.blas_nodes = s.blas.nodes; r.tris = s.blas.tris; r.tlas_nodes = s.tlas.nodes; r.tlas_slot_to_inst = s.tlas.slot_to_prim;
     r.instances = s.num_instances ? s.instances : nullptr;
+    if (s.flat.nodes && ctx->use_flat) { r.flat_nodes = s.flat.nodes; r.flat_leaf = s.flat_leaf; }
     r.tri_shade = s.tri_shade; r.geom_shade = s.geom_shade;
     r.texels = s.texels; r.textures = s.textures; r.srgb_lut = s.srgb_lut; r.sky = s.sky; r.sky_w = s.sky_w; r.sky_h = s.sky_h;
     return r;
@@ -129,7 +131,8 @@ __device__ __forceinline__ Hit trace_closest(const SceneRefs& sc, V3 o, V3 d, fl
     TraceRay ray; ray.o = o; ray.d = d; ray.tmin = tmin; ray.tmax = tmax;
     Hit best; best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
     *tri_slot = 0xFFFFFFFFu;
-    if (sc.instances) tlas_closest_hit(sc.tlas_nodes, sc.tlas_slot_to_inst, sc.instances, sc.blas_nodes, sc.tris, ray, best, tri_slot);
+    if (sc.flat_nodes) flat_closest_hit(sc.flat_nodes, sc.flat_leaf, sc.instances, sc.tris, ray, best, tri_slot);
+    else if (sc.instances) tlas_closest_hit(sc.tlas_nodes, sc.tlas_slot_to_inst, sc.instances, sc.blas_nodes, sc.tris, ray, best, tri_slot);
     else cwbvh_closest_hit(sc.blas_nodes, sc.tris, ray, 0u, best, tri_slot);
     return best;
 }

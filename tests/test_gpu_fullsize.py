@@ -112,7 +112,7 @@ def test_c3_full_size_light_passes():
     nbad = int((got_res != res).any(axis=1).sum())
     assert nbad <= tol, f"{nbad} packed DI reservoirs differ"
     assert int((got_d != d16).any(axis=2).sum()) <= tol
-    assert int((res[:, 0] != 0).sum()) > W * H // 2
+    assert int((res[:, 0] != 0).sum()) > W * H // 8          # a quarter of the pixels see a light through the towers
     ctx.close()
 
 
@@ -172,11 +172,11 @@ def test_c5_full_size_instanced_frame(camera):
         assert hit_fraction > 0.9, hit_fraction
     _brute_force_band(osc, g, hits, 800, 801, step=8)        # 240 rays x 20.48 M instanced triangles
     lp.execute(1, rt.LaunchParams(spp=4, max_bounces=4))
+    rays = ctx.stats().rays_traced
     rt.PostProcessPass(ctx).execute(1)
     d32 = ctx.read(rt.BUF_DIFFUSE_F32, np.float32).reshape(H, W, 4)
     d16 = ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).reshape(H, W, 4)
     out = ctx.read(rt.BUF_OUTPUT_RGBA8, np.uint8).reshape(H, W, 4)
-    rays = ctx.stats().rays_traced
     r16, _, r32, rrays = osc.render_reference(g, 1, W, H, spp=4, max_bounces=4)
     assert rays == rrays
     nbad = int((d32.view(np.uint32) != r32.view(np.uint32)).any(axis=2).sum())
