@@ -2,7 +2,7 @@
 NVCC ?= /usr/local/cuda/bin/nvcc
 CXX ?= g++
 CSRC := raytracer2_b200/csrc
-CU_SRCS := $(CSRC)/rt2_api.cu $(CSRC)/rt2_scene.cu $(CSRC)/rt2_build.cu $(CSRC)/rt2_render.cu $(wildcard $(CSRC)/rt2_passes*.cu) $(wildcard $(CSRC)/rt2_pass_*.cu)
+CU_SRCS := $(CSRC)/rt2_api.cu $(CSRC)/rt2_scene.cu $(CSRC)/rt2_build.cu $(CSRC)/rt2_render.cu $(CSRC)/rt2_noalloc.cu $(wildcard $(CSRC)/rt2_passes*.cu) $(wildcard $(CSRC)/rt2_pass_*.cu)
 CU_HDRS := $(wildcard $(CSRC)/*.cuh) include/rt2_abi.h include/rt2_gconst.h
 # -fmad=false: no implicit FMA contraction (bit parity with the oracle); explicit __fmaf_rn where wanted.
 NVCCFLAGS := $(EXTRA_NVCCFLAGS) -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-ffp-contract=off,-Wall -Xptxas -v

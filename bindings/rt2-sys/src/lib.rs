@@ -254,6 +254,8 @@ extern "C" {
     pub fn rt2_presample(ctx: *mut rt2_ctx, frame: u32, which: c_int) -> c_int;
     pub fn rt2_render(ctx: *mut rt2_ctx, frame: u32, params: *const rt2_launch_params) -> c_int;
     pub fn rt2_trace_primary(ctx: *mut rt2_ctx, params: *const rt2_launch_params) -> c_int;
+    /// No counterpart in the reference: allocates nothing, static scratch, at most 2^23 padded pixels.
+    pub fn rt2_trace_primary_noalloc(ctx: *mut rt2_ctx, params: *const rt2_launch_params, device_hits_out: *mut c_void, nbytes: usize, device_hit_count_out: *mut u64) -> c_int;
     pub fn rt2_postprocess(ctx: *mut rt2_ctx, frame: u32) -> c_int;
     pub fn rt2_sync(ctx: *mut rt2_ctx) -> c_int;
     pub fn rt2_buffer_size(ctx: *mut rt2_ctx, which: c_int) -> usize;

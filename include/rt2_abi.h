@@ -287,6 +287,18 @@ int  rt2_render(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params* params);
 /* Primary visibility only (setupPrimaryRay + trace, GBufferHelpers.glsl:12-27, bridge :74-81,
  * with K1's TMin = 0.001): fills RT2_BUF_HIT_IDS.  Parity probe; no reference pass of its own. */
 int  rt2_trace_primary(rt2_ctx* ctx, const rt2_launch_params* params);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).  Same result as rt2_trace_primary —
+ * one rt2_hit_record per owned pixel, row-major W x H of the last rt2_resize — but written to CALLER-owned device memory
+ * `device_hits_out` (`nbytes` must be W*H*32; rows of other band ranks are left untouched) and, if `device_hit_count_out` is
+ * not NULL, the number of hits to that caller-owned device word.  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * host synchronisation): the kernel's scratch is a static device array inside the library, about 1 MiB per GPU, held by
+ * every GPU that loads the library until the process exits.  Limit: at most 2^23 = 8 388 608 padded pixels
+ * (ceil(W/8)*ceil(rows/4)*32 — 3840x2160 fits); larger frames return RT2_E_INVALID.  All calls on one device share the
+ * scratch: calls on one stream are ordered and safe, calls whose kernels overlap on the GPU race.  rt2_get_stats is not
+ * updated.  Runs on the context's stream like every other pass. */
+int  rt2_trace_primary_noalloc(rt2_ctx* ctx, const rt2_launch_params* params, void* device_hits_out, size_t nbytes,
+                               uint64_t* device_hit_count_out);
 /* PostProcessPass::execute (src/postprocess.rs:225-307) + post_processing.comp:152-191 (K13) */
 int  rt2_postprocess(rt2_ctx* ctx, uint32_t frame);
 

@@ -206,6 +206,7 @@ ABI_SYMBOLS = {
     "rt2_presample": (C.c_int, [VP, u32, C.c_int]),
     "rt2_render": (C.c_int, [VP, u32, C.POINTER(LaunchParams)]),
     "rt2_trace_primary": (C.c_int, [VP, C.POINTER(LaunchParams)]),
+    "rt2_trace_primary_noalloc": (C.c_int, [VP, C.POINTER(LaunchParams), VP, C.c_size_t, VP]),
     "rt2_postprocess": (C.c_int, [VP, u32]),
     "rt2_sync": (C.c_int, [VP]),
     "rt2_buffer_size": (C.c_size_t, [VP, C.c_int]),

@@ -252,6 +252,14 @@ class LightPasses:
         self.ctx._check(self.ctx._lib.rt2_trace_primary(self.ctx._ctx, p), "rt2_trace_primary")
 
 
+def trace_primary_noalloc(ctx: "Renderer", device_hits_ptr: int, nbytes: int, device_hit_count_ptr: int = 0, params: LaunchParams | None = None):
+    """rt2_trace_primary_noalloc: primary visibility into caller-owned device memory, allocating nothing (static scratch in the
+    library, at most 2^23 padded pixels).  No counterpart in the reference."""
+    p = C.byref(params) if params is not None else None
+    ctx._check(ctx._lib.rt2_trace_primary_noalloc(ctx._ctx, p, C.c_void_p(device_hits_ptr), nbytes, C.c_void_p(device_hit_count_ptr or None)),
+               "rt2_trace_primary_noalloc")
+
+
 class PrepareLightsTasks:
     def __init__(self, ctx: Renderer):
         self.ctx = ctx

@@ -63,6 +63,7 @@ int rt2_create(int cuda_device, rt2_ctx** out) {
     if (e == cudaSuccess) e = cudaHostAlloc((void**)&ctx->h_gconst_ring, RT2_FRAMES_IN_FLIGHT * sizeof(rt2_gconst), cudaHostAllocDefault);
     if (e != cudaSuccess) { std::string m = cudaGetErrorString(e); rt2_destroy(ctx); return fail(nullptr, RT2_E_CUDA, m); }
     int rc = render_init(ctx);
+    if (rc == RT2_OK) rc = noalloc_init(ctx);
     if (rc != RT2_OK) { std::string m = ctx->last_error; rt2_destroy(ctx); return fail(nullptr, rc, m); }
     *out = ctx;
     return RT2_OK;

@@ -180,5 +180,7 @@ void frame_release(rt2_ctx* ctx);
 int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp);   // K1
 int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp);
 int render_init(rt2_ctx* ctx);
+// rt2_noalloc.cu
+int noalloc_init(rt2_ctx* ctx);                    // resolves the static scratch's device address, once per device (cudaGetSymbolAddress)
 
 }  // namespace rt2
