@@ -256,6 +256,8 @@ def main():
 
     for i in range(args.warmup):
         step(1 + i)
+        ctx.sync()          # warm-up frames complete one by one: the library picks its sample schedule from the previous frame's
+                            # miss statistics and allocates the speculative path buffers on the first frame that uses them
     drain()
     torch.cuda.synchronize()
     if dist:

@@ -81,6 +81,8 @@ int rt2_destroy(rt2_ctx* ctx) {
         if (ctx->snap[i]) cudaFree(ctx->snap[i]);
     }
     if (ctx->h_gconst_ring) cudaFreeHost(ctx->h_gconst_ring);
+    if (ctx->h_k1_stats) cudaFreeHost(ctx->h_k1_stats);
+    if (ctx->k1_stats_ready) cudaEventDestroy(ctx->k1_stats_ready);
     scene_release(ctx); frame_release(ctx); passes_release(ctx);
     for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
     if (ctx->d_gconst) cudaFree(ctx->d_gconst);

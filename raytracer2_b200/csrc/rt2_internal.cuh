@@ -95,6 +95,13 @@ struct FrameBuffers {
     float4* st_hit = nullptr;
     uint32_t* st_hit_inst = nullptr;
     uint32_t *queue0 = nullptr, *queue1 = nullptr;
+    // speculative sample parallelism (render_reference_spec): one path per (pixel, sample); allocated on first use, grow-only
+    struct Spec {
+        float4 *ray0 = nullptr, *ray1 = nullptr, *hit = nullptr, *contrib = nullptr, *px_rad = nullptr;
+        uint4* misc = nullptr; uint32_t *hit_inst = nullptr, *queue0 = nullptr, *queue1 = nullptr, *pending0 = nullptr, *pending1 = nullptr, *counters = nullptr, *start_index = nullptr;
+        uint8_t* nhits = nullptr; uint2* px_prog = nullptr;
+        size_t cap_paths = 0, cap_contrib = 0, cap_pixels = 0, cap_counters = 0;
+    } spec;
     uint32_t* warp_pop = nullptr; size_t warp_pop_cap = 0;   // k_path_warp: warp-private slot queues (num_warps x P)
     // ReSTIR-side per-size resources (RenderResources::new, src/render_resources.rs:48-101,191-206,287-317); allocated on first use
     float* gb_depth[2] = {nullptr, nullptr};             // r32f, ping-pong by frame % 2 (src/light_passes.rs:565-577)
@@ -140,6 +147,10 @@ struct rt2_ctx {
     int trace_blocks_per_sm[4] = {1, 1, 1, 1};          // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level, [3] flattened instancing
     bool use_flat = true;                                // trace instanced scenes through the flattened tree when it was built (RT2_USE_FLAT=0: two-level walk)
     int trace_variant = 0;
+    // K1 sample schedule: speculate = -1 auto (from the previous frame's miss statistics, read back without a sync), 0 never, 1 whenever
+    // the paths fit (RT2_SPECULATE); spec_rounds = prediction fix-up rounds before the candidate round (RT2_SPEC_ROUNDS)
+    int speculate = -1; bool spec_auto = false; int spec_rounds = 1;
+    unsigned long long* h_k1_stats = nullptr; cudaEvent_t k1_stats_ready = nullptr; bool k1_stats_pending = false; uint64_t k1_stats_paths = 0;
     int path_mode = 0;                                   // K1 schedule: 0 = one launch per bounce (wavefront chains), 1 = warp-local wavefronts in one persistent launch (RT2_PATH_MODE)
     int path_blocks_per_sm[3] = {1, 1, 1}; int warp_blocks_per_sm = 0; uint32_t warp_paths = 0;   // k_path_warp occupancy; RT2_WARP_BLOCKS / RT2_WARP_P overrides
     uint32_t rays_per_lane = 0; bool rays_per_lane_set = false;   // cap of the persistent trace grid for small wavefronts (RT2_RAYS_PER_LANE overrides the rule)

@@ -375,6 +375,25 @@ __device__ __forceinline__ void warp_flush_counter(unsigned long long* dst, uint
     if ((threadIdx.x & 31u) == 0u && sum) atomicAdd(dst, (unsigned long long)sum);
 }
 
+// Queue append with ONE global atomic per block instead of one per warp: a wavefront of 8 M paths makes 260 k same-address
+// atomics per launch with warp_append, which serialise in the L2.  Every thread of the block calls this the same number of times;
+// `s_off` is 2 x 9 words of shared memory (double-buffered by `parity`, so one barrier pair per call is enough).
+__device__ __forceinline__ uint32_t block_append_index(bool alive, uint32_t* count_out, uint32_t* s_off, uint32_t parity) {
+    uint32_t* o = s_off + parity * 9u;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, alive);
+    if (lane == 0u) o[warp] = (uint32_t)__popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0u) {
+        uint32_t total = 0;
+        for (uint32_t w = 0; w < nwarps; w++) total += o[w];
+        uint32_t base = total ? atomicAdd(count_out, total) : 0u;
+        for (uint32_t w = 0; w < nwarps; w++) { const uint32_t c = o[w]; o[w] = base; base += c; }
+    }
+    __syncthreads();
+    return o[warp] + (uint32_t)__popc(m & ((1u << lane) - 1u));
+}
+
 // 4 blocks of 256 threads per SM (64 registers): the kernel waits on dependent gathers (state -> shading record -> texels),
 // so resident warps buy bandwidth; measured 1 / 3 / 4 / 5 blocks: 2488 / 2486 / 2532 / 2501 Mrays/s on C2 (5 spills).
 #ifndef RT2_SHADE_MIN_BLOCKS
@@ -384,20 +403,22 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_k1_shade(ShadeArg
     __shared__ float lut[256];
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x];
     __syncthreads();
+    __shared__ uint32_t s_off[18];
     const uint32_t count = *a.count_in;
     const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t hits = 0;
-    // all lanes of a warp iterate together (warp_append uses warp collectives)
+    uint32_t hits = 0, parity = 0;
+    // all threads of a block iterate together (block_append_index uses block barriers)
     // the queue entry of the next iteration is fetched one iteration ahead: one dependent memory round trip less per ray
-    uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u;
-    uint32_t slot_ahead = i0 + (threadIdx.x & 31u) < count ? a.queue_in[i0 + (threadIdx.x & 31u)] : 0u;
-    for (; i0 < count; i0 += stride) {
-        const uint32_t i = i0 + (threadIdx.x & 31u);
+    uint32_t b0 = blockIdx.x * blockDim.x;
+    uint32_t slot_ahead = b0 + threadIdx.x < count ? a.queue_in[b0 + threadIdx.x] : 0u;
+    for (; b0 < count; b0 += stride, parity ^= 1u) {
+        const uint32_t i = b0 + threadIdx.x;
         bool alive = false;
         const uint32_t slot = slot_ahead;
         if (i + stride < count) slot_ahead = a.queue_in[i + stride];
         if (i < count) alive = k1_shade_step(a, lut, slot, &hits);
-        warp_append(alive, slot, a.queue_out, a.count_out);
+        const uint32_t at = block_append_index(alive, a.count_out, s_off, parity);
+        if (alive) a.queue_out[at] = slot;
     }
     warp_flush_counter(a.stat_hits, hits);
 }
@@ -417,6 +438,9 @@ struct WarpPathArgs {
     uint32_t P;               // population per warp (multiple of 32)
     uint32_t* pixel_head;     // next unclaimed padded lane of [first, end)
     uint32_t first, end;
+    // list mode (the speculative renderer's fallback): pixels come from `list` (*list_count slots) and resume at the sample, RNG
+    // position and radiance recorded in px_prog / px_rad instead of starting fresh
+    const uint32_t* list; const uint32_t* list_count; const uint2* px_prog; const float4* px_rad;
 };
 
 template <bool INSTANCED, bool FLAT>
@@ -448,6 +472,27 @@ __device__ __forceinline__ void path_warp_body(const TraceArgs& t, const ShadeAr
             const uint32_t i = w.first + base + lane;
             bool alive = false;
             uint32_t slot = 0;
+            if (w.list) {
+                const uint32_t n_list = *w.list_count;
+                if (lane < want && base + lane < n_list) {
+                    alive = true;
+                    slot = w.list[base + lane];
+                    const uint32_t x = slot % a.band.width, ly = slot / a.band.width;
+                    const uint2 pr = w.px_prog[slot];
+                    const float4 rd = w.px_rad[slot];
+                    V3 o, d;
+                    setup_primary_ray(a.g->view, x, band_local_to_global(a.band, ly), &o, &d);
+                    a.st_ray0[slot] = make_float4(o.x, o.y, o.z, d.x);
+                    a.st_ray1[slot] = make_float4(d.y, d.z, 1.0f, 1.0f);
+                    a.st_acc[slot] = make_float4(1.0f, rd.x, rd.y, rd.z);
+                    a.st_misc[slot] = make_uint4(pr.y, pr.x, 0u, 0u);
+                }
+                const uint32_t m = __ballot_sync(0xFFFFFFFFu, alive);
+                if (alive) q[wr + __popc(m & ((1u << lane) - 1u))] = slot;
+                wr += __popc(m);
+                if (base + want >= n_list) exhausted = true;
+                continue;
+            }
             if (lane < want && i < w.end) {
                 const uint32_t tile = i >> 5, within = i & 31u;
                 const uint32_t x = (tile % tiles_x) * 8u + (within & 7u), ly = (tile / tiles_x) * 4u + (within >> 3);
@@ -485,6 +530,263 @@ __global__ void __launch_bounds__(128) k_path_warp(TraceArgs t, ShadeArgs a, War
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
     __syncthreads();
     path_warp_body<INSTANCED, FLAT>(t, a, w, lut);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Speculative sample parallelism (B200: 180 GB of HBM holds every sample of every pixel as a path of its own).
+// The shader runs a pixel's samples one after the other on ONE RNG stream (refrence.rgen:21-46): sample s starts at stream
+// position 1 + 3 * (hits of samples 0..s-1), three draws per hit.  A sample that never misses takes exactly max_bounces hits, so
+// in a closed scene the start position of every sample is known in advance: all spp samples of all pixels are traced as
+// independent paths — spp x more rays per wavefront, max_bounces wavefront iterations per frame instead of spp x max_bounces —
+// each path recording its per-bounce radiance contributions thr * emission.  k_spec_reduce then walks a pixel's samples in
+// order, adds the contributions in the shader's order (fp32 addition is not associative: same order => same bits) and stops
+// at the first sample that ended on a miss: the samples after it started from a wrong stream position and are traced again
+// (fix-up rounds over the pending pixels, then k_path_warp's list mode, which finishes whatever is left sequentially).
+// Only valid samples are counted as rays.  The image is bit-identical to the sequential form.
+// ------------------------------------------------------------------------------------------------
+struct SpecArgs {
+    Band band;
+    const rt2_gconst* g;
+    uint32_t frame, spp, max_bounces, flags;
+    SceneRefs sc;
+    float4 *ray0, *ray1; uint4* misc;                 // per path: o|d.x, d.yz|thr.xy, {rng index, bounce, pixel_slot * spp + sample, thr.z}
+    const float4* hit; const uint32_t* hit_inst;
+    float4* contrib;                                  // per (pixel, sample, bounce): thr * emission of that event
+    uint8_t* nhits;                                   // per (pixel, sample): hits | 0x80 if the sample ended on a miss
+    uint32_t* start_index;                            // per (pixel, sample): the RNG position the sample's path was started from
+    // candidate round: misc.z / contrib / nhits are indexed by (pending-list position, candidate) = k * cand_K + m instead of
+    // (pixel, sample), and the pixel is cand_list[k]
+    const uint32_t* cand_list; uint32_t cand_K;
+    uint2* px_prog; float4* px_rad;                   // per pixel: {next sample, RNG position}, radiance summed so far
+    ushort4* diffuse_f16; ushort4* specular_f16; float4* diffuse_f32;
+    unsigned long long *stat_rays, *stat_hits;
+};
+
+// pixel slot of list entry k: round 0 walks the padded 8x4-tile lanes [first, first + lanes), later rounds a pending list
+template <bool IMPLICIT>
+__device__ __forceinline__ bool spec_pixel(const SpecArgs& a, const uint32_t* list, uint32_t first, uint32_t k, uint32_t* slot) {
+    if (!IMPLICIT) { *slot = list[k]; return true; }
+    const uint32_t i = first + k;
+    const uint32_t tiles_x = (a.band.width + 7u) >> 3;
+    const uint32_t tile = i >> 5, within = i & 31u;
+    const uint32_t x = (tile % tiles_x) * 8u + (within & 7u), ly = (tile / tiles_x) * 4u + (within >> 3);
+    *slot = ly * a.band.width + x;
+    return x < a.band.width && ly < a.band.local_rows;
+}
+
+// One path per (pending pixel, remaining sample) from a speculated RNG position: the pixel's position + 3 x the predicted hits of
+// the samples in between.  Round 0 predicts max_bounces hits per sample (a path that never misses); a fix-up round predicts what
+// the previous round observed for that sample — its path came from a wrong position, but what makes a sample short is mostly
+// geometry (a primary ray that leaves through a crack misses whatever the random numbers are).
+template <bool IMPLICIT>
+__global__ void __launch_bounds__(256) k_spec_gen(SpecArgs a, const uint32_t* list, const uint32_t* list_count, uint32_t first, uint32_t lanes,
+                                                  uint32_t* queue_out, uint32_t* count_out, uint32_t path_base) {
+    const uint32_t n_list = IMPLICIT ? lanes : *list_count;
+    const uint64_t n_items = (uint64_t)n_list * a.spp;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    __shared__ uint32_t s_off[18];
+    uint32_t parity = 0;
+    for (uint64_t b0 = (uint64_t)blockIdx.x * blockDim.x; b0 < n_items; b0 += stride, parity ^= 1u) {
+        const uint64_t i = b0 + threadIdx.x;
+        bool alive = false;
+        uint32_t slot = 0, sample = 0, index = 0, x = 0, ly = 0;
+        if (i < n_items) {
+            const uint32_t k = (uint32_t)(i / a.spp), j = (uint32_t)(i % a.spp);
+            if (spec_pixel<IMPLICIT>(a, list, first, k, &slot)) {
+                uint2 pr = make_uint2(0u, 1u);                 // refrence.rgen:21: a fresh pixel starts sample 0 at position 1
+                if (IMPLICIT) { if (j == 0u) { a.px_prog[slot] = pr; a.px_rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f); } }
+                else pr = a.px_prog[slot];
+                sample = pr.x + j;
+                if (sample < a.spp) {
+                    alive = true; x = slot % a.band.width; ly = slot / a.band.width;
+                    uint32_t predicted = a.max_bounces * j;
+                    if (!IMPLICIT) { predicted = 0; for (uint32_t q = 0; q < j; q++) predicted += a.nhits[slot * a.spp + pr.x + q] & 0x7Fu; }
+                    index = pr.y + 3u * predicted;
+                }
+            }
+        }
+        const uint32_t p = block_append_index(alive, count_out, s_off, parity);
+        if (alive) {
+            V3 o, d;
+            setup_primary_ray(a.g->view, x, band_local_to_global(a.band, ly), &o, &d);
+            a.ray0[path_base + p] = make_float4(o.x, o.y, o.z, d.x);
+            a.ray1[path_base + p] = make_float4(d.y, d.z, 1.0f, 1.0f);
+            a.misc[path_base + p] = make_uint4(index, 0u, slot * a.spp + sample, __float_as_uint(1.0f));
+            a.start_index[slot * a.spp + sample] = index;
+            queue_out[p] = path_base + p;
+        }
+    }
+}
+
+// refrence.rgen:28-42 for one traced ray of each queued path; a path is one sample and ends with it
+__global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_spec_shade(SpecArgs a, const uint32_t* queue_in, const uint32_t* count_in,
+                                                                          uint32_t* queue_out, uint32_t* count_out) {
+    __shared__ float lut[256];
+    lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x];
+    __syncthreads();
+    __shared__ uint32_t s_off[18];
+    const uint32_t count = *count_in;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t b0 = blockIdx.x * blockDim.x, parity = 0;
+    uint32_t p_ahead = b0 + threadIdx.x < count ? queue_in[b0 + threadIdx.x] : 0u;
+    for (; b0 < count; b0 += stride, parity ^= 1u) {
+        const uint32_t i = b0 + threadIdx.x;
+        bool alive = false;
+        const uint32_t p = p_ahead;
+        if (i + stride < count) p_ahead = queue_in[i + stride];
+        if (i < count) {
+            const float4 r0 = a.ray0[p], r1 = a.ray1[p];
+            const uint4 misc = a.misc[p];
+            const float4 h = a.hit[p];
+            const uint32_t ps = misc.z, slot = a.cand_list ? a.cand_list[ps / a.cand_K] : ps / a.spp;
+            const uint32_t x = slot % a.band.width, y = band_local_to_global(a.band, slot / a.band.width);
+            V3 o = v3(r0.x, r0.y, r0.z), d = v3(r0.w, r1.x, r1.y);
+            V3 thr = v3(r1.z, r1.w, __uint_as_float(misc.w));
+            Rng rng; rng.index = misc.x; rng.seed = jenkins_hash(zcurve_to_linear(x, y)) + (a.frame + 13u);
+            uint32_t bounce = misc.y;
+            const uint32_t tri_slot = __float_as_uint(h.w);
+            float4* c = a.contrib + ((size_t)ps * a.max_bounces + bounce);
+            if (tri_slot == 0xFFFFFFFFu) {                         // refrence.rgen:32-36
+                const V3 e = thr * environment_radiance(a.sc, *a.g, d);
+                *c = make_float4(e.x, e.y, e.z, 0.f);
+                a.nhits[ps] = (uint8_t)(bounce | 0x80u);
+            } else {
+                const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? a.hit_inst[p] : 0u, h.y, h.z);
+                const V3 e = thr * sf.emission;                    // refrence.rgen:38
+                *c = make_float4(e.x, e.y, e.z, 0.f);
+                thr = thr * sf.color;                              // refrence.rgen:39
+                const float rx = rng_next(rng), ry = rng_next(rng), rz = rng_next(rng);
+                (void)rx;
+                const V3 hvec = sample_cos_hemisphere(ry, rz, (a.flags & RT2_LAUNCH_TRIG_LIBDEVICE) != 0u);
+                const V3 world_pos = o + d * h.x;                  // Hit.glsl:67
+                d = tangent_to_world(sf.normal, hvec);
+                o = world_pos;                                     // refrence.rgen:42
+                bounce++;
+                if (bounce >= a.max_bounces) a.nhits[ps] = (uint8_t)bounce;
+                else {
+                    alive = true;
+                    a.ray0[p] = make_float4(o.x, o.y, o.z, d.x);
+                    a.ray1[p] = make_float4(d.y, d.z, thr.x, thr.y);
+                    a.misc[p] = make_uint4(rng.index, bounce, ps, __float_as_uint(thr.z));
+                }
+            }
+        }
+        const uint32_t at = block_append_index(alive, count_out, s_off, parity);
+        if (alive) queue_out[at] = p;
+    }
+}
+
+// per pending pixel: contributions of its valid samples added in the shader's order.  A sample is valid iff its path was started
+// from the position the stream really has there (1 + 3 x hits of the samples before it); the first sample that was not sends
+// the pixel to the next round's list.  The first pending sample is always valid, so every round makes progress.  refrence.rgen:46 when done.
+template <bool IMPLICIT>
+__global__ void __launch_bounds__(256) k_spec_reduce(SpecArgs a, const uint32_t* list, const uint32_t* list_count, uint32_t first, uint32_t lanes,
+                                                     uint32_t* pending_out, uint32_t* pending_count) {
+    const uint32_t n_list = IMPLICIT ? lanes : *list_count;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t rays = 0, hits = 0;
+    for (uint32_t k0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; k0 < n_list; k0 += stride) {
+        const uint32_t k = k0 + (threadIdx.x & 31u);
+        bool pending = false;
+        uint32_t slot = 0;
+        if (k < n_list && spec_pixel<IMPLICIT>(a, list, first, k, &slot)) {
+            const uint2 pr = a.px_prog[slot];
+            const float4 r4 = a.px_rad[slot];
+            V3 rad = v3(r4.x, r4.y, r4.z);
+            uint32_t sample = pr.x, index = pr.y;
+            while (sample < a.spp) {
+                const uint32_t ps = slot * a.spp + sample;
+                if (a.start_index[ps] != index) break;
+                const uint32_t nh = a.nhits[ps], h = nh & 0x7Fu, missed = nh >> 7;
+                const float4* c = a.contrib + (size_t)ps * a.max_bounces;
+                for (uint32_t b = 0; b < h + missed; b++) { const float4 e = c[b]; rad = rad + v3(e.x, e.y, e.z); }
+                index += 3u * h; rays += h + missed; hits += h;
+                sample++;
+            }
+            a.px_prog[slot] = make_uint2(sample, index);
+            a.px_rad[slot] = make_float4(rad.x, rad.y, rad.z, 0.f);
+            if (sample >= a.spp) {
+                const uint32_t x = slot % a.band.width, y = band_local_to_global(a.band, slot / a.band.width);
+                const float inv = (float)a.spp;
+                store_shading_output(*a.g, (size_t)y * a.band.width + x, v3(rad.x / inv, rad.y / inv, rad.z / inv), v3(0.f, 0.f, 0.f), true,
+                                     a.diffuse_f16, a.specular_f16, a.diffuse_f32);
+            } else pending = true;
+        }
+        warp_append(pending, slot, pending_out, pending_count);
+    }
+    warp_flush_counter(a.stat_rays, rays);
+    warp_flush_counter(a.stat_hits, hits);
+}
+
+// Candidate round, for the pixels no prediction settles (next to a crack a bounce ray leaks at random: with 32 samples such a
+// pixel mispredicts again and again, and finishing it one dependent ray after the other is a ~4 ms latency chain).  The path of a
+// sample is a function of (pixel, start position) only — the primary ray has no jitter (Q12) and the stream is keyed on pixel +
+// frame — and the remaining samples can only start at idx0 + 3 m, m = 0 .. max_bounces x (remaining - 1).  So ALL those
+// candidate paths are traced in one parallel round, and k_spec_reduce_cand walks the chain m -> m + hits(m) in order.
+__global__ void __launch_bounds__(256) k_spec_gen_cand(SpecArgs a, const uint32_t* list, const uint32_t* list_count, uint32_t max_pixels,
+                                                       uint32_t* queue_out, uint32_t* count_out) {
+    __shared__ uint32_t s_off[18];
+    const uint32_t n_list = min(*list_count, max_pixels);
+    const uint64_t n_items = (uint64_t)n_list * a.cand_K;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    uint32_t parity = 0;
+    for (uint64_t b0 = (uint64_t)blockIdx.x * blockDim.x; b0 < n_items; b0 += stride, parity ^= 1u) {
+        const uint64_t i = b0 + threadIdx.x;
+        bool alive = false;
+        uint32_t slot = 0, index = 0;
+        if (i < n_items) {
+            const uint32_t k = (uint32_t)(i / a.cand_K), m = (uint32_t)(i % a.cand_K);
+            slot = list[k];
+            const uint2 pr = a.px_prog[slot];
+            if (pr.x < a.spp && m <= a.max_bounces * (a.spp - pr.x - 1u)) { alive = true; index = pr.y + 3u * m; }
+        }
+        const uint32_t p = block_append_index(alive, count_out, s_off, parity);
+        if (alive) {
+            V3 o, d;
+            setup_primary_ray(a.g->view, slot % a.band.width, band_local_to_global(a.band, slot / a.band.width), &o, &d);
+            a.ray0[p] = make_float4(o.x, o.y, o.z, d.x);
+            a.ray1[p] = make_float4(d.y, d.z, 1.0f, 1.0f);
+            a.misc[p] = make_uint4(index, 0u, (uint32_t)i, __float_as_uint(1.0f));
+            queue_out[p] = p;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_spec_reduce_cand(SpecArgs a, const uint32_t* list, const uint32_t* list_count, uint32_t max_pixels,
+                                                          uint32_t* overflow_out, uint32_t* overflow_count) {
+    const uint32_t n_all = *list_count;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t rays = 0, hits = 0;
+    for (uint32_t k0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; k0 < n_all; k0 += stride) {
+        const uint32_t k = k0 + (threadIdx.x & 31u);
+        bool overflow = false;
+        uint32_t slot = 0;
+        if (k < n_all) {
+            slot = list[k];
+            if (k >= max_pixels) overflow = true;                 // more pending pixels than candidate storage: sequential fallback
+            else {
+                const uint2 pr = a.px_prog[slot];
+                const float4 r4 = a.px_rad[slot];
+                V3 rad = v3(r4.x, r4.y, r4.z);
+                uint32_t m = 0;
+                for (uint32_t sample = pr.x; sample < a.spp; sample++) {
+                    const size_t cps = (size_t)k * a.cand_K + m;
+                    const uint32_t nh = a.nhits[cps], h = nh & 0x7Fu, missed = nh >> 7;
+                    const float4* c = a.contrib + cps * a.max_bounces;
+                    for (uint32_t b = 0; b < h + missed; b++) { const float4 e = c[b]; rad = rad + v3(e.x, e.y, e.z); }
+                    m += h; rays += h + missed; hits += h;
+                }
+                a.px_prog[slot] = make_uint2(a.spp, pr.y + 3u * m);
+                const uint32_t x = slot % a.band.width, y = band_local_to_global(a.band, slot / a.band.width);
+                const float inv = (float)a.spp;
+                store_shading_output(*a.g, (size_t)y * a.band.width + x, v3(rad.x / inv, rad.y / inv, rad.z / inv), v3(0.f, 0.f, 0.f), true,
+                                     a.diffuse_f16, a.specular_f16, a.diffuse_f32);
+            }
+        }
+        warp_append(overflow, slot, overflow_out, overflow_count);
+    }
+    warp_flush_counter(a.stat_rays, rays);
+    warp_flush_counter(a.stat_hits, hits);
 }
 
 // primary visibility probe: one thread per pixel, 8x4 tiles per warp
@@ -526,7 +828,9 @@ static cudaError_t dev_alloc(rt2_ctx* ctx, T** p, size_t n) {
 void frame_release(rt2_ctx* ctx) {
     FrameBuffers& f = ctx->fb;
     void* ptrs[] = {f.diffuse_f16, f.specular_f16, f.diffuse_f32, f.hit_ids, f.output_rgba8, f.st_ray0, f.st_ray1, f.st_acc, f.st_misc,
-                    f.st_hit, f.st_hit_inst, f.queue0, f.queue1, f.counters, f.warp_pop};
+                    f.st_hit, f.st_hit_inst, f.queue0, f.queue1, f.counters, f.warp_pop,
+                    f.spec.ray0, f.spec.ray1, f.spec.hit, f.spec.contrib, f.spec.px_rad, f.spec.misc, f.spec.hit_inst, f.spec.queue0, f.spec.queue1,
+                    f.spec.pending0, f.spec.pending1, f.spec.counters, f.spec.nhits, f.spec.px_prog, f.spec.start_index};
     for (void* p : ptrs) if (p) cudaFree(p);
     f = FrameBuffers();
 }
@@ -647,7 +951,7 @@ int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp) {
     return RT2_OK;
 }
 
-int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
+static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     int rc = check_ready(ctx); if (rc) return rc;
     if ((rc = check_band(ctx, lp))) return rc;
     FrameBuffers& f = ctx->fb; const DeviceScene& s = ctx->scene;
@@ -792,6 +1096,201 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
     return RT2_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// speculative sample parallelism: host side
+// ------------------------------------------------------------------------------------------------
+static void launch_trace_kernel(rt2_ctx* ctx, const TraceArgs& t, bool flat, int blocks, cudaStream_t st) {
+    const DeviceScene& s = ctx->scene;
+    if (flat) k_trace_dyn_flat<20, 4, 8><<<blocks, 128, 0, st>>>(t);
+    else if (s.num_instances) {
+        if (ctx->trace_variant != 0 && unified_walk_fits(s)) k_trace_dyn_tlas<20, 4, 8><<<blocks, 128, 0, st>>>(t);
+        else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, st>>>(t);
+    } else g_trace_variants[ctx->trace_variant]<<<blocks, 128, 0, st>>>(t);
+}
+
+template <class T>
+static cudaError_t spec_grow(rt2_ctx* ctx, T** p, size_t n) {
+    if (*p) { cudaFree(*p); *p = nullptr; }
+    cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(n, 1) * sizeof(T));
+    if (e == cudaSuccess) ctx->device_bytes += std::max<size_t>(n, 1) * sizeof(T);
+    return e;
+}
+
+static bool spec_eligible(rt2_ctx* ctx, const Band& band, uint32_t spp, uint32_t bounces) {
+    const DeviceScene& s = ctx->scene;
+    const uint64_t paths = (uint64_t)band.width * band.local_rows * spp;
+    if (spp < 2u || bounces > 127u || paths == 0 || paths > (64ull << 20)) return false;
+    if (paths * (16ull * 4 + 4 + 8 + 1 + 16ull * bounces) > (24ull << 30)) return false;
+    if (s.num_instances && !(s.flat.nodes && ctx->use_flat) && !unified_walk_fits(s)) return false;     // the fallback needs the one-loop walk
+    return true;
+}
+
+static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp, uint32_t spp, uint32_t bounces) {
+    FrameBuffers& f = ctx->fb; const DeviceScene& s = ctx->scene;
+    FrameBuffers::Spec& sp = f.spec;
+    int rc;
+    if ((rc = ensure_counters(ctx, 0))) return rc;
+    const Band band = make_band(f.width, f.height, lp);
+    const uint32_t tiles_x = (band.width + 7) / 8, tiles_y = (band.local_rows + 3) / 4;
+    const uint32_t padded = tiles_x * tiles_y * 32;
+    const size_t band_pixels = (size_t)band.width * band.local_rows;
+    const size_t paths = band_pixels * spp, contribs = paths * bounces;
+    const uint32_t rounds = 1u + (uint32_t)std::max(0, ctx->spec_rounds);
+    const uint32_t RB = 2u * (bounces + 1u) + 2u;                 // per round: (count, head) x (bounces + 1), pending count, pad
+    const size_t n_counters = 8 + (size_t)(rounds + 1u) * RB;      // + the candidate round
+    const bool flat = s.flat.nodes && ctx->use_flat;
+    const int fb_blocks = ctx->num_sms;                            // fallback kernel: one block of 4 warps per SM
+    const uint32_t fb_P = 64u;
+    // grow-only buffers (first speculative frame of a size allocates; steady state allocates nothing)
+    if (sp.cap_paths < paths || sp.cap_contrib < contribs || sp.cap_pixels < band_pixels || sp.cap_counters < n_counters ||
+        f.warp_pop_cap < (size_t)fb_blocks * 4u * fb_P) {
+        RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (sp.cap_paths < paths) {
+            RT2_CUDA(ctx, spec_grow(ctx, &sp.ray0, paths)); RT2_CUDA(ctx, spec_grow(ctx, &sp.ray1, paths)); RT2_CUDA(ctx, spec_grow(ctx, &sp.hit, paths));
+            RT2_CUDA(ctx, spec_grow(ctx, &sp.misc, paths)); RT2_CUDA(ctx, spec_grow(ctx, &sp.hit_inst, paths));
+            RT2_CUDA(ctx, spec_grow(ctx, &sp.queue0, paths)); RT2_CUDA(ctx, spec_grow(ctx, &sp.queue1, paths)); RT2_CUDA(ctx, spec_grow(ctx, &sp.nhits, paths));
+            RT2_CUDA(ctx, spec_grow(ctx, &sp.start_index, paths));
+            sp.cap_paths = paths;
+        }
+        if (sp.cap_contrib < contribs) { RT2_CUDA(ctx, spec_grow(ctx, &sp.contrib, contribs)); sp.cap_contrib = contribs; }
+        if (sp.cap_pixels < band_pixels) {
+            RT2_CUDA(ctx, spec_grow(ctx, &sp.px_rad, band_pixels)); RT2_CUDA(ctx, spec_grow(ctx, &sp.px_prog, band_pixels));
+            RT2_CUDA(ctx, spec_grow(ctx, &sp.pending0, band_pixels)); RT2_CUDA(ctx, spec_grow(ctx, &sp.pending1, band_pixels));
+            sp.cap_pixels = band_pixels;
+        }
+        if (sp.cap_counters < n_counters) { RT2_CUDA(ctx, spec_grow(ctx, &sp.counters, n_counters)); sp.cap_counters = n_counters; }
+        if (f.warp_pop_cap < (size_t)fb_blocks * 4u * fb_P) {
+            if (f.warp_pop) cudaFree(f.warp_pop);
+            f.warp_pop = nullptr; f.warp_pop_cap = 0;
+            RT2_CUDA(ctx, cudaMalloc((void**)&f.warp_pop, (size_t)fb_blocks * 4u * fb_P * 4u));
+            f.warp_pop_cap = (size_t)fb_blocks * 4u * fb_P; ctx->device_bytes += f.warp_pop_cap * 4;
+        }
+    }
+    cudaStream_t st = ctx->stream;
+    RT2_CUDA(ctx, cudaMemsetAsync(sp.counters, 0, n_counters * 4, st));
+    uint64_t launches = 0;
+    if (padded) {
+        SpecArgs a{};
+        a.band = band; a.g = ctx->d_gconst; a.frame = frame; a.spp = spp; a.max_bounces = bounces; a.flags = lp.flags;
+        a.sc = make_scene_refs(ctx);
+        a.ray0 = sp.ray0; a.ray1 = sp.ray1; a.misc = sp.misc; a.hit = sp.hit; a.hit_inst = sp.hit_inst;
+        a.contrib = sp.contrib; a.nhits = sp.nhits; a.start_index = sp.start_index; a.px_prog = sp.px_prog; a.px_rad = sp.px_rad;
+        a.diffuse_f16 = f.diffuse_f16; a.specular_f16 = f.specular_f16; a.diffuse_f32 = f.diffuse_f32;
+        a.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);           // valid samples only (k_spec_reduce)
+        a.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
+        TraceArgs t = make_trace_args(ctx);
+        t.st_ray0 = sp.ray0; t.st_ray1 = sp.ray1; t.st_hit = sp.hit; t.st_hit_inst = sp.hit_inst;
+        t.stat_rays = reinterpret_cast<unsigned long long*>(sp.counters);          // every ray traced, speculation losses included (diagnostic)
+        const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
+        for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
+        ctx->prof_events.clear();
+        if (profile) { ctx->prof_events.resize((size_t)bounces * 3); for (auto& e : ctx->prof_events) RT2_CUDA(ctx, cudaEventCreate(&e)); }
+        const int full_trace = ctx->trace_blocks_per_sm[flat ? 3 : (s.num_instances ? 1 : 0)] * ctx->num_sms;
+        const int full_shade = ctx->num_sms * 8;
+        uint32_t* q[2] = {sp.queue0, sp.queue1};
+        uint32_t* pend[2] = {sp.pending0, sp.pending1};
+        for (uint32_t r = 0; r < rounds; r++) {
+            uint32_t* cnt = sp.counters + 8 + (size_t)r * RB;
+            const uint32_t* list = r ? pend[(r - 1) & 1] : nullptr;
+            const uint32_t* list_count = r ? sp.counters + 8 + (size_t)(r - 1) * RB + (RB - 2) : nullptr;
+            // fix-up rounds are small (the pixels that saw a miss): a fraction of the grid, every kernel is grid-stride / persistent
+            const int gen_blocks = r ? ctx->num_sms * 2 : (int)std::min<uint64_t>((uint64_t)ctx->num_sms * 16, ((uint64_t)padded * spp + 255) / 256);
+            const int trace_blocks = r ? ctx->num_sms : full_trace;
+            const int shade_blocks = r ? ctx->num_sms : (int)std::min<uint64_t>((uint64_t)full_shade, (paths + 255) / 256);
+            if (r == 0) k_spec_gen<true><<<gen_blocks, 256, 0, st>>>(a, nullptr, nullptr, 0u, padded, q[0], cnt, 0u);
+            else k_spec_gen<false><<<gen_blocks, 256, 0, st>>>(a, list, list_count, 0u, 0u, q[0], cnt, 0u);
+            launches++;
+            for (uint32_t it = 0; it < bounces; it++) {
+                if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], st));
+                t.queue = q[it & 1]; t.count = cnt + 2 * it; t.head = cnt + 2 * it + 1;
+                launch_trace_kernel(ctx, t, flat, trace_blocks, st);
+                if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], st));
+                k_spec_shade<<<shade_blocks, 256, 0, st>>>(a, q[it & 1], cnt + 2 * it, q[(it + 1) & 1], cnt + 2 * (it + 1));
+                if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 2], st));
+                launches += 2;
+            }
+            if (r == 0) k_spec_reduce<true><<<std::max(1, std::min(ctx->num_sms * 8, (int)((padded + 255) / 256))), 256, 0, st>>>(a, nullptr, nullptr, 0u, padded, pend[0], cnt + (RB - 2));
+            else k_spec_reduce<false><<<ctx->num_sms, 256, 0, st>>>(a, list, list_count, 0u, 0u, pend[r & 1], cnt + (RB - 2));
+            launches++;
+        }
+        // candidate round over what is still pending; the path arrays are free again and hold cap_paths / K pixels' candidates
+        const uint32_t* pend_list = pend[(rounds - 1) & 1];
+        const uint32_t* pend_count = sp.counters + 8 + (size_t)(rounds - 1) * RB + (RB - 2);
+        uint32_t* overflow_list = pend[rounds & 1];
+        uint32_t* ccnt = sp.counters + 8 + (size_t)rounds * RB;
+        {
+            const uint32_t K = bounces * (spp - 1u) + 1u;
+            const uint32_t max_pixels = (uint32_t)std::min<size_t>(paths / K, 0x7FFFFFFFu / K);
+            SpecArgs ca = a;
+            ca.cand_list = pend_list; ca.cand_K = K;
+            k_spec_gen_cand<<<ctx->num_sms * 2, 256, 0, st>>>(ca, pend_list, pend_count, max_pixels, q[0], ccnt);
+            launches++;
+            for (uint32_t it = 0; it < bounces; it++) {
+                t.queue = q[it & 1]; t.count = ccnt + 2 * it; t.head = ccnt + 2 * it + 1;
+                launch_trace_kernel(ctx, t, flat, ctx->num_sms * 2, st);
+                k_spec_shade<<<ctx->num_sms, 256, 0, st>>>(ca, q[it & 1], ccnt + 2 * it, q[(it + 1) & 1], ccnt + 2 * (it + 1));
+                launches += 2;
+            }
+            k_spec_reduce_cand<<<ctx->num_sms, 256, 0, st>>>(ca, pend_list, pend_count, max_pixels, overflow_list, ccnt + (RB - 2));
+            launches++;
+        }
+        // pixels beyond the candidate storage (a frame where speculation was the wrong choice) finish sequentially in one persistent launch
+        ShadeArgs sa{};
+        sa.band = band; sa.g = ctx->d_gconst; sa.frame = frame; sa.spp = spp; sa.max_bounces = bounces; sa.flags = lp.flags;
+        sa.sc = a.sc;
+        sa.st_ray0 = f.st_ray0; sa.st_ray1 = f.st_ray1; sa.st_acc = f.st_acc; sa.st_misc = f.st_misc; sa.st_hit = f.st_hit; sa.st_hit_inst = f.st_hit_inst;
+        sa.diffuse_f16 = f.diffuse_f16; sa.specular_f16 = f.specular_f16; sa.diffuse_f32 = f.diffuse_f32;
+        sa.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
+        TraceArgs ts = make_trace_args(ctx);
+        ts.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
+        WarpPathArgs w{f.warp_pop, fb_P, sp.counters + 2, 0u, 0u, overflow_list, ccnt + (RB - 2), sp.px_prog, sp.px_rad};
+        if (flat) k_path_warp<false, true><<<fb_blocks, 128, 0, st>>>(ts, sa, w);
+        else if (s.num_instances) k_path_warp<true><<<fb_blocks, 128, 0, st>>>(ts, sa, w);
+        else k_path_warp<false><<<fb_blocks, 128, 0, st>>>(ts, sa, w);
+        launches++;
+    }
+    RT2_CUDA(ctx, cudaGetLastError());
+    ctx->stats.kernel_launches = launches;
+    ctx->stats.wavefront_iterations = (uint64_t)(rounds + 1u) * bounces;
+    ctx->stats_from_counters = true;
+    ctx->pending_rays_static = 0;
+    return RT2_OK;
+}
+
+// K1 entry: picks the sample schedule, then leaves the frame's (rays, hits) where the next call can read them without a sync
+int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
+    int rc = check_ready(ctx); if (rc) return rc;
+    if ((rc = check_band(ctx, lp))) return rc;
+    const uint32_t spp = lp.spp ? lp.spp : 12u;                    // refrence.rgen:17
+    const uint32_t bounces = lp.max_bounces ? lp.max_bounces : 5u; // refrence.rgen:16
+    if (spp > 65535u || bounces > 65535u || (uint64_t)spp * bounces > (1u << 22)) return fail(ctx, RT2_E_INVALID, "spp x bounces too large");
+    const Band band = make_band(ctx->fb.width, ctx->fb.height, lp);
+    // auto: speculate when fewer than 2 % of the previous frame's samples ended on a miss (each costs its pixel a fix-up round)
+    if (ctx->k1_stats_pending && cudaEventQuery(ctx->k1_stats_ready) == cudaSuccess) {
+        ctx->k1_stats_pending = false;
+        const unsigned long long rays = ctx->h_k1_stats[0], hits = ctx->h_k1_stats[1];
+        if (ctx->k1_stats_paths) ctx->spec_auto = (double)(rays - hits) < 0.02 * (double)ctx->k1_stats_paths;
+    }
+    cudaGetLastError();
+    const bool want = ctx->speculate > 0 || (ctx->speculate < 0 && ctx->spec_auto);
+    const bool spec = want && ctx->path_mode == 0 && spec_eligible(ctx, band, spp, bounces);
+    rc = spec ? render_reference_spec(ctx, frame, lp, spp, bounces) : render_reference_seq(ctx, frame, lp);
+    if (rc != RT2_OK) return rc;
+    if (ctx->speculate < 0) {
+        if (!ctx->h_k1_stats) {
+            RT2_CUDA(ctx, cudaHostAlloc((void**)&ctx->h_k1_stats, 32, cudaHostAllocDefault));
+            RT2_CUDA(ctx, cudaEventCreateWithFlags(&ctx->k1_stats_ready, cudaEventDisableTiming));
+        }
+        if (!ctx->k1_stats_pending) {          // one read-back in flight: the pinned words are rewritten only after the host consumed them
+            RT2_CUDA(ctx, cudaMemcpyAsync(ctx->h_k1_stats, ctx->fb.counters, 16, cudaMemcpyDeviceToHost, ctx->stream));
+            RT2_CUDA(ctx, cudaEventRecord(ctx->k1_stats_ready, ctx->stream));
+            ctx->k1_stats_pending = true;
+            ctx->k1_stats_paths = (uint64_t)band.width * band.local_rows * spp;
+        }
+    }
+    return RT2_OK;
+}
+
 // Traces a queue of GENERIC rays (st_ray0 = o|tmin, st_ray1 = d|tmax, slot = pixel-linear index) into st_hit / st_hit_inst:
 // the ReSTIR passes hand their incoherent rays to the same postponing/refilling kernel the path tracer uses.
 int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays) {
@@ -821,6 +1320,8 @@ int render_init(rt2_ctx* ctx) {
     int b2 = 0;
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace_dyn_tlas<20, 4, 8>, 128, 0));
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, k_trace<true>, 128, 0));
+    if (const char* e = getenv("RT2_SPECULATE")) ctx->speculate = atoi(e);
+    if (const char* e = getenv("RT2_SPEC_ROUNDS")) { int v = atoi(e); if (v >= 0 && v <= 16) ctx->spec_rounds = v; }
     if (const char* e = getenv("RT2_PATH_MODE")) ctx->path_mode = atoi(e);
     if (const char* e = getenv("RT2_WARP_P")) { int v = atoi(e); if (v >= 32 && v <= 4096) ctx->warp_paths = (uint32_t)v; }
     if (const char* e = getenv("RT2_WARP_BLOCKS")) { int v = atoi(e); if (v >= 1 && v <= 16) ctx->warp_blocks_per_sm = v; }

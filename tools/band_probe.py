@@ -16,7 +16,7 @@ for chains in [int(x) for x in (sys.argv[1] if len(sys.argv) > 1 else "0").split
     row = []
     for n in (1, 2, 4, 8):
         p = rt.LaunchParams(spp=4 * n, max_bounces=4, band_rows=8 if n > 1 else 0, band_rank=0, band_world=n)
-        for i in range(3): lp.execute(1 + i, p)
+        for i in range(4): lp.execute(1 + i, p); ctx.sync()
         ctx.sync()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
