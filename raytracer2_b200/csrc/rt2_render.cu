@@ -557,6 +557,7 @@ struct SpecArgs {
     // candidate round: misc.z / contrib / nhits are indexed by (pending-list position, candidate) = k * cand_K + m instead of
     // (pixel, sample), and the pixel is cand_list[k]
     const uint32_t* cand_list; uint32_t cand_K;
+    uint32_t path_base;                               // first path / candidate slot of this wavefront chain's region
     uint2* px_prog; float4* px_rad;                   // per pixel: {next sample, RNG position}, radiance summed so far
     ushort4* diffuse_f16; ushort4* specular_f16; float4* diffuse_f32;
     unsigned long long *stat_rays, *stat_hits;
@@ -638,7 +639,7 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_spec_shade(SpecAr
             const float4 r0 = a.ray0[p], r1 = a.ray1[p];
             const uint4 misc = a.misc[p];
             const float4 h = a.hit[p];
-            const uint32_t ps = misc.z, slot = a.cand_list ? a.cand_list[ps / a.cand_K] : ps / a.spp;
+            const uint32_t ps = misc.z, slot = a.cand_list ? a.cand_list[(ps - a.path_base) / a.cand_K] : ps / a.spp;
             const uint32_t x = slot % a.band.width, y = band_local_to_global(a.band, slot / a.band.width);
             V3 o = v3(r0.x, r0.y, r0.z), d = v3(r0.w, r1.x, r1.y);
             V3 thr = v3(r1.z, r1.w, __uint_as_float(misc.w));
@@ -744,10 +745,10 @@ __global__ void __launch_bounds__(256) k_spec_gen_cand(SpecArgs a, const uint32_
         if (alive) {
             V3 o, d;
             setup_primary_ray(a.g->view, slot % a.band.width, band_local_to_global(a.band, slot / a.band.width), &o, &d);
-            a.ray0[p] = make_float4(o.x, o.y, o.z, d.x);
-            a.ray1[p] = make_float4(d.y, d.z, 1.0f, 1.0f);
-            a.misc[p] = make_uint4(index, 0u, (uint32_t)i, __float_as_uint(1.0f));
-            queue_out[p] = p;
+            a.ray0[a.path_base + p] = make_float4(o.x, o.y, o.z, d.x);
+            a.ray1[a.path_base + p] = make_float4(d.y, d.z, 1.0f, 1.0f);
+            a.misc[a.path_base + p] = make_uint4(index, 0u, a.path_base + (uint32_t)i, __float_as_uint(1.0f));
+            queue_out[p] = a.path_base + p;
         }
     }
 }
@@ -770,7 +771,7 @@ __global__ void __launch_bounds__(256) k_spec_reduce_cand(SpecArgs a, const uint
                 V3 rad = v3(r4.x, r4.y, r4.z);
                 uint32_t m = 0;
                 for (uint32_t sample = pr.x; sample < a.spp; sample++) {
-                    const size_t cps = (size_t)k * a.cand_K + m;
+                    const size_t cps = (size_t)a.path_base + (size_t)k * a.cand_K + m;
                     const uint32_t nh = a.nhits[cps], h = nh & 0x7Fu, missed = nh >> 7;
                     const float4* c = a.contrib + cps * a.max_bounces;
                     for (uint32_t b = 0; b < h + missed; b++) { const float4 e = c[b]; rad = rad + v3(e.x, e.y, e.z); }
@@ -1137,13 +1138,18 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
     const size_t paths = band_pixels * spp, contribs = paths * bounces;
     const uint32_t rounds = 1u + (uint32_t)std::max(0, ctx->spec_rounds);
     const uint32_t RB = 2u * (bounces + 1u) + 2u;                 // per round: (count, head) x (bounces + 1), pending count, pad
-    const size_t n_counters = 8 + (size_t)(rounds + 1u) * RB;      // + the candidate round
+    const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
+    // two wavefront chains once a chain still gets >= 1 M paths (measured like the sequential form's rule); RT2_CHAINS overrides
+    uint32_t nch = profile ? 1u : (ctx->chains ? std::min(ctx->chains, RT2_MAX_CHAINS) : (paths >= (2u << 20) ? 2u : 1u));
+    nch = std::max(1u, std::min(nch, tiles_y ? tiles_y : 1u));
+    const size_t CB = 8 + (size_t)(rounds + 1u) * RB;             // per chain: traced (u64), fallback head, pad; rounds + the candidate round
+    const size_t n_counters = CB * nch;
     const bool flat = s.flat.nodes && ctx->use_flat;
     const int fb_blocks = ctx->num_sms;                            // fallback kernel: one block of 4 warps per SM
     const uint32_t fb_P = 64u;
     // grow-only buffers (first speculative frame of a size allocates; steady state allocates nothing)
     if (sp.cap_paths < paths || sp.cap_contrib < contribs || sp.cap_pixels < band_pixels || sp.cap_counters < n_counters ||
-        f.warp_pop_cap < (size_t)fb_blocks * 4u * fb_P) {
+        f.warp_pop_cap < (size_t)fb_blocks * 4u * fb_P * RT2_MAX_CHAINS) {
         RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         if (sp.cap_paths < paths) {
             RT2_CUDA(ctx, spec_grow(ctx, &sp.ray0, paths)); RT2_CUDA(ctx, spec_grow(ctx, &sp.ray1, paths)); RT2_CUDA(ctx, spec_grow(ctx, &sp.hit, paths));
@@ -1159,15 +1165,14 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
             sp.cap_pixels = band_pixels;
         }
         if (sp.cap_counters < n_counters) { RT2_CUDA(ctx, spec_grow(ctx, &sp.counters, n_counters)); sp.cap_counters = n_counters; }
-        if (f.warp_pop_cap < (size_t)fb_blocks * 4u * fb_P) {
+        if (f.warp_pop_cap < (size_t)fb_blocks * 4u * fb_P * RT2_MAX_CHAINS) {
             if (f.warp_pop) cudaFree(f.warp_pop);
             f.warp_pop = nullptr; f.warp_pop_cap = 0;
-            RT2_CUDA(ctx, cudaMalloc((void**)&f.warp_pop, (size_t)fb_blocks * 4u * fb_P * 4u));
-            f.warp_pop_cap = (size_t)fb_blocks * 4u * fb_P; ctx->device_bytes += f.warp_pop_cap * 4;
+            RT2_CUDA(ctx, cudaMalloc((void**)&f.warp_pop, (size_t)fb_blocks * 4u * fb_P * RT2_MAX_CHAINS * 4u));
+            f.warp_pop_cap = (size_t)fb_blocks * 4u * fb_P * RT2_MAX_CHAINS; ctx->device_bytes += f.warp_pop_cap * 4;
         }
     }
-    cudaStream_t st = ctx->stream;
-    RT2_CUDA(ctx, cudaMemsetAsync(sp.counters, 0, n_counters * 4, st));
+    RT2_CUDA(ctx, cudaMemsetAsync(sp.counters, 0, n_counters * 4, ctx->stream));
     uint64_t launches = 0;
     if (padded) {
         SpecArgs a{};
@@ -1180,61 +1185,77 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
         a.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
         TraceArgs t = make_trace_args(ctx);
         t.st_ray0 = sp.ray0; t.st_ray1 = sp.ray1; t.st_hit = sp.hit; t.st_hit_inst = sp.hit_inst;
-        t.stat_rays = reinterpret_cast<unsigned long long*>(sp.counters);          // every ray traced, speculation losses included (diagnostic)
-        const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
         for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
         ctx->prof_events.clear();
         if (profile) { ctx->prof_events.resize((size_t)bounces * 3); for (auto& e : ctx->prof_events) RT2_CUDA(ctx, cudaEventCreate(&e)); }
         const int full_trace = ctx->trace_blocks_per_sm[flat ? 3 : (s.num_instances ? 1 : 0)] * ctx->num_sms;
         const int full_shade = ctx->num_sms * 8;
-        uint32_t* q[2] = {sp.queue0, sp.queue1};
-        uint32_t* pend[2] = {sp.pending0, sp.pending1};
+        if (nch > 1u) {
+            if (!ctx->chain_fork) { RT2_CUDA(ctx, cudaEventCreateWithFlags(&ctx->chain_fork, cudaEventDisableTiming)); }
+            for (uint32_t c = 1; c < nch; c++) {
+                if (!ctx->chain_streams[c]) {
+                    RT2_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->chain_streams[c], cudaStreamNonBlocking));
+                    RT2_CUDA(ctx, cudaEventCreateWithFlags(&ctx->chain_join[c], cudaEventDisableTiming));
+                }
+            }
+            RT2_CUDA(ctx, cudaEventRecord(ctx->chain_fork, ctx->stream));
+        }
+        // Wavefront chains: the frame is cut at tile-row boundaries, so a chain owns the pixel slots [slot_lo, slot_hi) and with
+        // them the regions [slot_lo * spp, slot_hi * spp) of the path, contribution and candidate arrays, its own queues, pending
+        // lists and counters; one chain's trace tail overlaps the other's work.
+        struct Chain {
+            cudaStream_t st; uint32_t first, lanes, base; size_t cap_paths; uint32_t* cnt; uint32_t* q[2]; uint32_t* pend[2];
+        } ch[RT2_MAX_CHAINS];
+        for (uint32_t c = 0; c < nch; c++) {
+            Chain& k = ch[c];
+            const uint32_t tr0 = (uint32_t)((uint64_t)tiles_y * c / nch), tr1 = (uint32_t)((uint64_t)tiles_y * (c + 1) / nch);
+            const uint32_t row0 = std::min(band.local_rows, tr0 * 4u), row1 = std::min(band.local_rows, tr1 * 4u);
+            k.st = c == 0 ? ctx->stream : ctx->chain_streams[c];
+            if (c != 0) RT2_CUDA(ctx, cudaStreamWaitEvent(k.st, ctx->chain_fork, 0));
+            k.first = tr0 * tiles_x * 32u; k.lanes = (tr1 - tr0) * tiles_x * 32u;
+            k.base = row0 * band.width * spp; k.cap_paths = (size_t)(row1 - row0) * band.width * spp;
+            k.cnt = sp.counters + (size_t)c * CB;
+            k.q[0] = sp.queue0 + k.base; k.q[1] = sp.queue1 + k.base;
+            k.pend[0] = sp.pending0 + (size_t)row0 * band.width; k.pend[1] = sp.pending1 + (size_t)row0 * band.width;
+        }
+        auto round_counters = [&](const Chain& k, uint32_t r) { return k.cnt + 8 + (size_t)r * RB; };
         for (uint32_t r = 0; r < rounds; r++) {
-            uint32_t* cnt = sp.counters + 8 + (size_t)r * RB;
-            const uint32_t* list = r ? pend[(r - 1) & 1] : nullptr;
-            const uint32_t* list_count = r ? sp.counters + 8 + (size_t)(r - 1) * RB + (RB - 2) : nullptr;
             // fix-up rounds are small (the pixels that saw a miss): a fraction of the grid, every kernel is grid-stride / persistent
-            const int gen_blocks = r ? ctx->num_sms * 2 : (int)std::min<uint64_t>((uint64_t)ctx->num_sms * 16, ((uint64_t)padded * spp + 255) / 256);
-            const int trace_blocks = r ? ctx->num_sms : full_trace;
-            const int shade_blocks = r ? ctx->num_sms : (int)std::min<uint64_t>((uint64_t)full_shade, (paths + 255) / 256);
-            if (r == 0) k_spec_gen<true><<<gen_blocks, 256, 0, st>>>(a, nullptr, nullptr, 0u, padded, q[0], cnt, 0u);
-            else k_spec_gen<false><<<gen_blocks, 256, 0, st>>>(a, list, list_count, 0u, 0u, q[0], cnt, 0u);
-            launches++;
-            for (uint32_t it = 0; it < bounces; it++) {
-                if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], st));
-                t.queue = q[it & 1]; t.count = cnt + 2 * it; t.head = cnt + 2 * it + 1;
-                launch_trace_kernel(ctx, t, flat, trace_blocks, st);
-                if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], st));
-                k_spec_shade<<<shade_blocks, 256, 0, st>>>(a, q[it & 1], cnt + 2 * it, q[(it + 1) & 1], cnt + 2 * (it + 1));
-                if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 2], st));
-                launches += 2;
+            for (uint32_t c = 0; c < nch; c++) {
+                const Chain& k = ch[c];
+                uint32_t* cnt = round_counters(k, r);
+                const int gen_blocks = r ? ctx->num_sms * 2 : (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctx->num_sms * 16, ((uint64_t)k.lanes * spp + 255) / 256));
+                SpecArgs ca = a; ca.path_base = k.base;
+                if (r == 0) k_spec_gen<true><<<gen_blocks, 256, 0, k.st>>>(ca, nullptr, nullptr, k.first, k.lanes, k.q[0], cnt, k.base);
+                else k_spec_gen<false><<<gen_blocks, 256, 0, k.st>>>(ca, k.pend[(r - 1) & 1], round_counters(k, r - 1) + (RB - 2), 0u, 0u, k.q[0], cnt, k.base);
+                launches++;
             }
-            if (r == 0) k_spec_reduce<true><<<std::max(1, std::min(ctx->num_sms * 8, (int)((padded + 255) / 256))), 256, 0, st>>>(a, nullptr, nullptr, 0u, padded, pend[0], cnt + (RB - 2));
-            else k_spec_reduce<false><<<ctx->num_sms, 256, 0, st>>>(a, list, list_count, 0u, 0u, pend[r & 1], cnt + (RB - 2));
-            launches++;
-        }
-        // candidate round over what is still pending; the path arrays are free again and hold cap_paths / K pixels' candidates
-        const uint32_t* pend_list = pend[(rounds - 1) & 1];
-        const uint32_t* pend_count = sp.counters + 8 + (size_t)(rounds - 1) * RB + (RB - 2);
-        uint32_t* overflow_list = pend[rounds & 1];
-        uint32_t* ccnt = sp.counters + 8 + (size_t)rounds * RB;
-        {
-            const uint32_t K = bounces * (spp - 1u) + 1u;
-            const uint32_t max_pixels = (uint32_t)std::min<size_t>(paths / K, 0x7FFFFFFFu / K);
-            SpecArgs ca = a;
-            ca.cand_list = pend_list; ca.cand_K = K;
-            k_spec_gen_cand<<<ctx->num_sms * 2, 256, 0, st>>>(ca, pend_list, pend_count, max_pixels, q[0], ccnt);
-            launches++;
             for (uint32_t it = 0; it < bounces; it++) {
-                t.queue = q[it & 1]; t.count = ccnt + 2 * it; t.head = ccnt + 2 * it + 1;
-                launch_trace_kernel(ctx, t, flat, ctx->num_sms * 2, st);
-                k_spec_shade<<<ctx->num_sms, 256, 0, st>>>(ca, q[it & 1], ccnt + 2 * it, q[(it + 1) & 1], ccnt + 2 * (it + 1));
-                launches += 2;
+                for (uint32_t c = 0; c < nch; c++) {
+                    const Chain& k = ch[c];
+                    uint32_t* cnt = round_counters(k, r);
+                    const int trace_blocks = r ? ctx->num_sms : full_trace;
+                    const int shade_blocks = r ? ctx->num_sms : (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)full_shade, (k.cap_paths + 255) / 256));
+                    if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], k.st));
+                    t.queue = k.q[it & 1]; t.count = cnt + 2 * it; t.head = cnt + 2 * it + 1;
+                    t.stat_rays = reinterpret_cast<unsigned long long*>(k.cnt);          // every ray traced, speculation losses included (diagnostic)
+                    launch_trace_kernel(ctx, t, flat, trace_blocks, k.st);
+                    if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], k.st));
+                    k_spec_shade<<<shade_blocks, 256, 0, k.st>>>(a, k.q[it & 1], cnt + 2 * it, k.q[(it + 1) & 1], cnt + 2 * (it + 1));
+                    if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 2], k.st));
+                    launches += 2;
+                }
             }
-            k_spec_reduce_cand<<<ctx->num_sms, 256, 0, st>>>(ca, pend_list, pend_count, max_pixels, overflow_list, ccnt + (RB - 2));
-            launches++;
+            for (uint32_t c = 0; c < nch; c++) {
+                const Chain& k = ch[c];
+                uint32_t* cnt = round_counters(k, r);
+                if (r == 0) k_spec_reduce<true><<<std::max(1, std::min(ctx->num_sms * 8, (int)((k.lanes + 255) / 256))), 256, 0, k.st>>>(a, nullptr, nullptr, k.first, k.lanes, k.pend[0], cnt + (RB - 2));
+                else k_spec_reduce<false><<<ctx->num_sms, 256, 0, k.st>>>(a, k.pend[(r - 1) & 1], round_counters(k, r - 1) + (RB - 2), 0u, 0u, k.pend[r & 1], cnt + (RB - 2));
+                launches++;
+            }
         }
-        // pixels beyond the candidate storage (a frame where speculation was the wrong choice) finish sequentially in one persistent launch
+        // candidate round over what is still pending; the chain's path region is free again and holds cap_paths / K pixels' candidates.
+        // Pixels beyond that (a frame where speculation was the wrong choice) finish sequentially in one persistent launch.
         ShadeArgs sa{};
         sa.band = band; sa.g = ctx->d_gconst; sa.frame = frame; sa.spp = spp; sa.max_bounces = bounces; sa.flags = lp.flags;
         sa.sc = a.sc;
@@ -1243,11 +1264,34 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
         sa.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
         TraceArgs ts = make_trace_args(ctx);
         ts.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
-        WarpPathArgs w{f.warp_pop, fb_P, sp.counters + 2, 0u, 0u, overflow_list, ccnt + (RB - 2), sp.px_prog, sp.px_rad};
-        if (flat) k_path_warp<false, true><<<fb_blocks, 128, 0, st>>>(ts, sa, w);
-        else if (s.num_instances) k_path_warp<true><<<fb_blocks, 128, 0, st>>>(ts, sa, w);
-        else k_path_warp<false><<<fb_blocks, 128, 0, st>>>(ts, sa, w);
-        launches++;
+        const uint32_t K = bounces * (spp - 1u) + 1u;
+        for (uint32_t c = 0; c < nch; c++) {
+            const Chain& k = ch[c];
+            const uint32_t* pend_list = k.pend[(rounds - 1) & 1];
+            const uint32_t* pend_count = round_counters(k, rounds - 1) + (RB - 2);
+            uint32_t* overflow_list = k.pend[rounds & 1];
+            uint32_t* ccnt = round_counters(k, rounds);
+            const uint32_t max_pixels = (uint32_t)std::min<size_t>(k.cap_paths / K, 0x7FFFFFFFu / K);
+            SpecArgs ca = a;
+            ca.cand_list = pend_list; ca.cand_K = K; ca.path_base = k.base;
+            k_spec_gen_cand<<<ctx->num_sms * 2, 256, 0, k.st>>>(ca, pend_list, pend_count, max_pixels, k.q[0], ccnt);
+            launches++;
+            for (uint32_t it = 0; it < bounces; it++) {
+                t.queue = k.q[it & 1]; t.count = ccnt + 2 * it; t.head = ccnt + 2 * it + 1;
+                t.stat_rays = reinterpret_cast<unsigned long long*>(k.cnt);
+                launch_trace_kernel(ctx, t, flat, ctx->num_sms * 2, k.st);
+                k_spec_shade<<<ctx->num_sms, 256, 0, k.st>>>(ca, k.q[it & 1], ccnt + 2 * it, k.q[(it + 1) & 1], ccnt + 2 * (it + 1));
+                launches += 2;
+            }
+            k_spec_reduce_cand<<<ctx->num_sms, 256, 0, k.st>>>(ca, pend_list, pend_count, max_pixels, overflow_list, ccnt + (RB - 2));
+            launches++;
+            WarpPathArgs w{f.warp_pop + (size_t)c * fb_blocks * 4u * fb_P, fb_P, k.cnt + 2, 0u, 0u, overflow_list, ccnt + (RB - 2), sp.px_prog, sp.px_rad};
+            if (flat) k_path_warp<false, true><<<fb_blocks, 128, 0, k.st>>>(ts, sa, w);
+            else if (s.num_instances) k_path_warp<true><<<fb_blocks, 128, 0, k.st>>>(ts, sa, w);
+            else k_path_warp<false><<<fb_blocks, 128, 0, k.st>>>(ts, sa, w);
+            launches++;
+        }
+        for (uint32_t c = 1; c < nch; c++) { RT2_CUDA(ctx, cudaEventRecord(ctx->chain_join[c], ch[c].st)); RT2_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->chain_join[c], 0)); }
     }
     RT2_CUDA(ctx, cudaGetLastError());
     ctx->stats.kernel_launches = launches;

@@ -58,6 +58,22 @@ def test_speculative_samples_bit_exact(monkeypatch, kind, scale, w, h, spp, boun
     ctx.close()
 
 
+@pytest.mark.parametrize("chains", [2, 3, 8])
+def test_speculative_wavefront_chains_bit_exact(monkeypatch, chains):
+    """The frame cut into wavefront chains at tile-row boundaries (own streams, queues, pending lists, candidate regions)."""
+    monkeypatch.setenv("RT2_CHAINS", str(chains))
+    w, h, spp, bounces = 201, 77, 5, 3
+    sc, g, ctx, lp = _setup(monkeypatch, rt.SCENE_CORNELL if chains == 3 else rt.SCENE_HALL, 1.0 if chains == 3 else 0.125, w, h)
+    lp.execute(2, rt.LaunchParams(spp=spp, max_bounces=bounces))
+    st = ctx.stats()
+    d32 = ctx.read(rt.BUF_DIFFUSE_F32, np.uint32).reshape(h, w, 4)
+    _, _, r32, rays = O.OracleScene(sc.desc).render_reference(g, 2, w, h, spp=spp, max_bounces=bounces)
+    assert st.kernel_launches == chains * (3 * (2 + 2 * bounces) + 1)
+    assert st.rays_traced == rays
+    assert np.array_equal(d32, r32.view(np.uint32))
+    ctx.close()
+
+
 def test_speculative_bands_and_accumulation_bit_exact(monkeypatch):
     """Three accumulated frames, each rendered as 3 interleaved band ranks on one context: equals the oracle's whole frames."""
     w, h = 200, 150

@@ -7,7 +7,7 @@ tail -5 gpurun_out/pytest_spec1.log | cut -c1-300
 {
 echo "== sequential (RT2_SPECULATE=0)"; RT2_SPECULATE=0 timeout 300 python tools/band_probe.py 0
 echo "== speculative (RT2_SPECULATE=1)"; RT2_SPECULATE=1 timeout 300 python tools/band_probe.py 0
-echo "== auto"; timeout 300 python tools/band_probe.py 0
+echo "== speculative, chains 1,2,3,4"; RT2_SPECULATE=1 timeout 600 python tools/band_probe.py 1,2,3,4
 } > gpurun_out/spec_sweep2.txt 2>&1
 cat gpurun_out/spec_sweep2.txt
 timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench.log 2>&1; tail -1 gpurun_out/bench.log | cut -c1-330
