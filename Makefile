@@ -2,7 +2,7 @@
 NVCC ?= /usr/local/cuda/bin/nvcc
 CXX ?= g++
 CSRC := raytracer2_b200/csrc
-CU_SRCS := $(CSRC)/rt2_api.cu $(CSRC)/rt2_scene.cu $(CSRC)/rt2_build.cu $(CSRC)/rt2_render.cu $(CSRC)/rt2_noalloc.cu $(wildcard $(CSRC)/rt2_passes*.cu) $(wildcard $(CSRC)/rt2_pass_*.cu)
+CU_SRCS := $(CSRC)/rt2_api.cu $(CSRC)/rt2_scene.cu $(CSRC)/rt2_build.cu $(CSRC)/rt2_render.cu $(CSRC)/rt2_noalloc.cu $(CSRC)/rt2_group.cu $(wildcard $(CSRC)/rt2_passes*.cu) $(wildcard $(CSRC)/rt2_pass_*.cu)
 CU_HDRS := $(wildcard $(CSRC)/*.cuh) include/rt2_abi.h include/rt2_gconst.h
 # -fmad=false: no implicit FMA contraction (bit parity with the oracle); explicit __fmaf_rn where wanted.
 NVCCFLAGS := $(EXTRA_NVCCFLAGS) -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-ffp-contract=off,-Wall -Xptxas -v
@@ -19,7 +19,7 @@ $(OBJDIR)/%.o: $(CSRC)/%.cu $(CU_HDRS)
 	@grep -E "error|warning" $(OBJDIR)/$*.ptxas.log || true
 
 raytracer2_b200/librt2cuda.so: $(CU_OBJS)
-	$(NVCC) -shared -o $@ $(CU_OBJS) $(LDLIBS_CUDA)
+	$(NVCC) -shared -o $@ $(CU_OBJS) $(LDLIBS_CUDA) -ldl
 	@cat $(sort $(wildcard $(OBJDIR)/*.ptxas.log)) > build_ptxas.log
 
 raytracer2_b200/librt2host.so: raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp raytracer2_b200/host/rt2_host.h raytracer2_b200/host/rt2_ingest.h include/rt2_abi.h include/rt2_gconst.h

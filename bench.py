@@ -6,12 +6,14 @@ procedural Sponza-scale hall, 262 144 triangles, 64 textured materials, 1920x108
   python bench.py --gpus N --steps K --warmup W          (N>1: launched by torchrun, one rank per GPU)
   python bench.py --impl reference ...                   (CPU oracle on the host cores; see below)
 
-A step is one rt2_render of the whole 1080p frame.  With N ranks the frame is split into interleaved
-16-row bands, every rank traces 4 spp x N (so per-GPU work is fixed: weak scaling), and
-the fp32 bands are all-gathered with NCCL over NVLink inside the timed region.
+A step is one rt2_group_render of the whole 1080p frame.  With N ranks the frame is split into interleaved
+8-row bands, every rank traces 4 spp x N (so per-GPU work is fixed: weak scaling); the band plan,
+the NCCL all-gather of the rgba16f bands and the un-permute into the assembled frame all happen inside
+librt2cuda.so (rt2_group_*), inside the timed region.
 `value` is device-timed with inputs resident; `e2e` goes through the C ABI with host buffers:
-rt2_set_constants (pinned host -> device) + rt2_render + rt2_read_async of the rgba16f accumulation image into
-pinned host memory, every step, two frames in flight (the transfer of frame n overlaps the render of frame n+1).
+rt2_group_set_constants (pinned host -> device) + rt2_group_render + rt2_group_read_async of the ASSEMBLED rgba16f frame into
+pinned host memory on rank 0, every step, two frames in flight (the transfer of frame n overlaps the render of frame n+1).
+`extra` (N = 1): short timed runs of BASELINE configs C1, C3, C5 and the default ReSTIR-GI frame, plus the small passes.
 """
 import argparse
 import ctypes as C
@@ -42,16 +44,18 @@ def measured_peak_hbm():
         return 6650.0, "fallback"
 
 
-def ncu_traffic_bytes():
-    """dram__bytes_read.sum + dram__bytes_write.sum per k_trace launch from the committed ncu --set full capture
-    (profiles/*_summary.json, same workload, N=1); None when no capture is committed."""
+def ncu_summary():
+    """The newest committed ncu --set full summary of k_trace (profiles/r*_k_trace_summary.json, same workload, N=1): DRAM traffic per
+    launch and the counters of the bound that actually binds (issue slots, lanes per instruction).  {} when none is committed."""
     import glob
-    for p in sorted(glob.glob(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r*_summary.json")), reverse=True):
+    for p in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_k_trace_summary.json")), reverse=True):
         try:
-            return json.load(open(p))["traffic_bytes_per_launch"]
+            d = json.load(open(p))
+            d["source"] = os.path.relpath(p, ROOT)
+            return d
         except Exception:
             continue
-    return None
+    return {}
 
 
 class ClockSampler:
@@ -182,6 +186,128 @@ def run_reference_arm(args, rank, world):
     return 0
 
 
+def run_extra(rt, torch, device):
+    """Short timed runs of the other BASELINE configs on one GPU (rank 0, N = 1), so they are driver-visible and not builder-only
+    claims: C1, C3 (K10 + K12 + K11 once, K3 + K9 per frame), C5 (K12-env once, K1 + K13 per frame, both cameras), the default
+    ReSTIR-GI frame on C2, and the small passes with their own algorithmic bytes.  B_ray uses the MEASURED hit
+    fraction rays_hit / rays_traced."""
+    import ctypes as C
+    peak, _ = measured_peak_hbm()
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+
+    def timed(fn, n, warm=3):
+        for i in range(warm):
+            fn(1 + i)
+        torch.cuda.synchronize()
+        sampler = ClockSampler(device); sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n):
+            fn(10 + i)
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n, sampler.stop()
+
+    def entry(name, ms, st, depth_bytes, shade_bytes, clocks, note=""):
+        h = st.rays_hit / max(st.rays_traced, 1)
+        b_ray = depth_bytes + 96 + h * shade_bytes
+        mrays = st.rays_traced / ms / 1e3
+        return {"workload": name, "ms_per_frame": ms, "Mrays_s": mrays, "rays_per_frame": st.rays_traced, "hit_fraction": h, "B_ray": b_ray,
+                "roofline_frac_hbm_nominal": mrays * 1e6 * b_ray / 1e9 / peak, "kernel_launches": st.kernel_launches, "clocks": clocks, "note": note}
+
+    def small(name, us, units, bytes_per_unit, unit_name):
+        gbs = units * bytes_per_unit / (us * 1e-6) / 1e9 if us > 0 else 0.0
+        return {"kernel": name, "us": us, unit_name: units, "bytes_per_unit": bytes_per_unit, "achieved_GBs": gbs, "frac_of_hbm": gbs / peak}
+
+    def once_us(fn, reps=5):
+        fn(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps * 1e3
+
+    out, passes = {}, []
+    # ---- C1: Cornell 32 tris, 512x512, 1 spp, 2 bounces ------------------------------------------------------------------
+    sc = rt.Scene(rt.SCENE_CORNELL)
+    ctx = rt.Renderer(device); ctx.set_stream(stream.cuda_stream)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, 512, 512)
+    g = rt.default_gconst(sc.camera(1.0), 512, 512, sc.num_lights); g.refrence_mode = 1
+    lp.update_uniform(g)
+    p = rt.LaunchParams(spp=1, max_bounces=2)
+    ms, clk = timed(lambda f: (lp.execute(f, p), ctx.sync() if f < 10 else None), 50)
+    out["C1"] = entry("Cornell 32 tris, 512x512, 1 spp x 2 bounces (K1)", ms, ctx.stats(), 80 * 2, 332, clk, "launch-bound: 5 kernel launches of a few microseconds each")
+    ctx.close()
+    # ---- C3: many lights, 1 M tris, 10 k emissive triangles, 1080p -------------------------------------------------------
+    sc = rt.Scene(rt.SCENE_MANYLIGHT, 1.0, 64, 0)
+    ctx = rt.Renderer(device); ctx.set_stream(stream.cuda_stream)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, W, H)
+    g = rt.default_gconst(sc.camera(W / H), W, H, sc.num_lights)
+    g.refrence_mode = 0; g.enable_restir_gi = 0; g.enable_restir_di = 1
+    isp = g.restir_di.initial_sampling_params
+    isp.num_primary_local_light_samples = 8; isp.num_primary_brdf_samples = 1; isp.enable_initial_visibility = 1
+    g.restir_di.shading_params.enable_final_visibility = 1
+    lp.update_uniform(g)
+    k10, k12 = rt.PrepareLightsTasks(ctx), rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS)
+    k10.execute(); k12.execute_mip_generation()
+    pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
+    passes.append(small("K10 prepare_lights (C3, 10 000 lights)", once_us(k10.execute), sc.num_lights, 380, "lights"))
+    passes.append(small("K12 mip_pass local-light PDF (C3)", once_us(k12.execute_mip_generation), pw.value * ph.value, 16.0 / 3.0, "texels"))
+    passes.append(small("K11 presample local lights (C3, 128 x 1024 RIS entries)", once_us(lambda: lp.execute_presampeling(3, False)), 128 * 1024, 40, "entries"))
+    ms, clk = timed(lambda f: (lp.execute(f), ctx.sync() if f < 10 else None), 10)
+    out["C3"] = entry("many-light 1 M tris / 10 000 lights, 1080p, K3 + K9 (8 local + 1 BRDF candidates, initial + final visibility)", ms, ctx.stats(), 80 * 7, 332, clk)
+    ctx.close()
+    # ---- C5: 10 000 instances x 2048 tris, sky on, K12-env once, K1 + K13 per frame ---------------------------------------
+    sc = rt.Scene(rt.SCENE_INSTANCED, 1.0, 64, 0)
+    d = sc.desc.contents
+    ctx = rt.Renderer(device); ctx.set_stream(stream.cuda_stream)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, W, H)
+    post = rt.PostProcessPass(ctx)
+    k12e = rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.ENVIRONMENT)
+    p = rt.LaunchParams(spp=4, max_bounces=4)
+    for cam_name, cam in (("C5", sc.camera(W / H)), ("C5_overhead", rt.overhead_camera(sc, W / H))):
+        g = rt.default_gconst(cam, W, H, sc.num_lights, env_size=(d.sky_width, d.sky_height))
+        g.refrence_mode = 1; g.environment = 1
+        lp.update_uniform(g)
+        if cam_name == "C5":
+            passes.append(small("K12 mip_pass environment PDF (C5, 2048x1024 r16f)", once_us(k12e.execute_mip_generation), d.sky_width * d.sky_height, 16 + 2 * 4.0 / 3.0, "texels"))
+
+        def frame(f):
+            lp.execute(f, p)
+            post.execute(f)
+            if f < 10:
+                ctx.sync()
+        ms, clk = timed(frame, 10)
+        lp.execute(99, p); ctx.sync()
+        out[cam_name] = entry(f"instanced 10 000 x 2048 tris (flattened: one CWBVH over 20.5 M instance-triangles), sky on, 1080p, 4 spp x 4 bounces, K1 + K13; camera = {cam_name}",
+                              ms, ctx.stats(), 80 * (5 + 4) + 64, 332, clk)
+    passes.append(small("K13 postprocess (reference mode, 1080p)", once_us(lambda: post.execute(1)), W * H, 12, "pixels"))
+    ctx.close()
+    # ---- the default ReSTIR-GI frame (K3 -> K4 -> K5 -> K8) on C2 -------------------------------------------------------
+    sc = rt.Scene(rt.SCENE_HALL, 1.0, 512, 0)
+    cam = sc.camera(W / H)
+    ctx = rt.Renderer(device); ctx.set_stream(stream.cuda_stream)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, W, H)
+    rt.PrepareLightsTasks(ctx).execute()
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    g = rt.default_gconst(cam, W, H, sc.num_lights)
+
+    def gi(f):
+        rt.advance_frame(g, cam, W, H, f); lp.update_uniform(g); lp.execute(f)
+    ms, clk = timed(gi, 10)
+    out["restir_gi_default_frame"] = entry("C2 scene, 1080p, the application's default frame (src/main.rs:391-394): K3 g_buffer -> K4 brdf_rays -> K5 shade_secondary -> K8 gi_final",
+                                           ms, ctx.stats(), 80 * 6, 348, clk)
+    ctx.close()
+    out["small_passes"] = passes
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -190,6 +316,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--scale", type=float, default=1.0, help="scene scale (1.0 = BASELINE size); for quick checks only")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra configs (C1, C3, C5, ReSTIR-GI frame, small passes)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -205,10 +332,15 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the path has no CPU fallback (use --impl reference for the CPU oracle)")
     torch.cuda.set_device(local_rank)
     dist = None
+    uid = None
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # the library owns the data-path communicator: rank 0 makes the NCCL id, the host distributes it (plumbing only)
+        box = [rt.Group.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        uid = box[0]
     n_gpus = world
     spp = SPP * n_gpus     # fixed 4 spp of work per GPU
 
@@ -216,90 +348,71 @@ def main():
     cam = sc.camera(W / H)
     g = rt.default_gconst(cam, W, H, sc.num_lights)
     g.refrence_mode = 1
-    ctx = rt.Renderer(local_rank)
-    # a real (non-default) torch stream: the library, torch's events and NCCL all run on it, so
-    # torch.cuda.Event timing sees exactly the kernels librt2cuda launches
+    grp = rt.Group.from_rank(local_rank, rank, world, uid)
+    ctx = grp.ctx(0)
+    # a real (non-default) torch stream: the library and torch's events run on it, so torch.cuda.Event timing sees exactly the
+    # kernels librt2cuda launches; the gather runs on the group's own communication stream and is joined by wait_gather()
     stream = torch.cuda.Stream()
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
     ctx.set_stream(stream.cuda_stream)
-    rt.Model.from_scene(ctx, sc)
-    lp = rt.LightPasses(ctx, W, H)
-    lp.update_uniform(g)
-    params = rt.LaunchParams(spp=spp, max_bounces=BOUNCES, band_rows=BAND_ROWS if n_gpus > 1 else 0, band_rank=rank, band_world=n_gpus)
-
-    # band gather plumbing (raytracer2_b200/sharding.py): each rank's rows packed contiguously -> all_gather
-    from raytracer2_b200.sharding import BandPlan, gather_frame
-    plan = BandPlan(H, BAND_ROWS, n_gpus)
-    # two send/recv pairs: the gather of frame n (NCCL's own stream) overlaps the render of frame n+1; a pair is reused only
-    # after the collective that last used it has completed (handle.wait() = a stream-level wait, the host never blocks)
-    send = [torch.zeros(plan.max_rows * W * 4, dtype=torch.float32, device="cuda") for _ in range(2)]
-    recv = [torch.zeros(n_gpus * plan.max_rows * W * 4, dtype=torch.float32, device="cuda") if n_gpus > 1 else None for _ in range(2)]
-    pending = [None, None]
-    step_no = [0]
+    grp.upload_scene(sc.desc)
+    grp.resize(W, H)
+    grp.update_uniform(g)
+    params = rt.LaunchParams(spp=spp, max_bounces=BOUNCES)
+    GATHER = rt.BUF_DIFFUSE_F16          # DiffuseLighting rgba16f, the image the reference's passes write (render_resources.rs:294-300)
+    frame_bytes = W * H * 8
 
     def step(frame):
-        lp.execute(frame, params)
-        if n_gpus > 1:
-            b = step_no[0] & 1
-            step_no[0] += 1
-            if pending[b] is not None:
-                pending[b].wait()
-            ctx.pack_bands(rt.BUF_DIFFUSE_F32, send[b].data_ptr(), plan.rows(rank) * W * 16, BAND_ROWS, rank, n_gpus)
-            pending[b] = gather_frame(plan, rank, send[b], recv[b], dist, async_op=True)
-
-    def drain():
-        for b in range(2):
-            if pending[b] is not None:
-                pending[b].wait()
-                pending[b] = None
+        grp.execute(frame, params, gather=GATHER)     # render this rank's bands + pack + ncclAllGather + un-permute
 
     for i in range(args.warmup):
         step(1 + i)
-        ctx.sync()          # warm-up frames complete one by one: the library picks its sample schedule from the previous frame's
+        grp.sync()          # warm-up frames complete one by one: the library picks its sample schedule from the previous frame's
                             # miss statistics and allocates the speculative path buffers on the first frame that uses them
-    drain()
-    torch.cuda.synchronize()
-    if dist:
-        dist.barrier()
     torch.cuda.synchronize()
     sampler = ClockSampler(local_rank)
     if rank == 0:
-        sampler.start()
+        sampler.start()     # before the barrier: NVML start-up takes ~100 ms on rank 0, and a rank that enters the timed region early
+                            # only waits for the others in its first all-gather
+    if dist:
+        dist.barrier()
+    torch.cuda.synchronize()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    rays = 0
-    launches = 0
     ev0.record()
     for i in range(args.steps):
         step(100 + i)
-    drain()                 # every gather has landed before the end event
+    grp.wait_gather()       # the end event waits for every gather + un-permute on the communication stream
     ev1.record()
     torch.cuda.synchronize()
+    grp.sync()
     ms = ev0.elapsed_time(ev1)
     st = ctx.stats()
     rays_per_step = st.rays_traced
-    launches = st.kernel_launches * args.steps
+    hits_per_step = st.rays_hit
+    launches = (st.kernel_launches + (1 if world > 1 else 0)) * args.steps       # + the un-permute kernel
     if dist:
         dist.barrier()
     torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
 
     # per-kernel time of the dominant kernel (k_trace): one profiled step with CUDA events around each launch
-    prof = rt.LaunchParams(spp=spp, max_bounces=BOUNCES, band_rows=params.band_rows, band_rank=rank, band_world=n_gpus, flags=rt.LAUNCH_PROFILE)
-    lp.execute(500, prof)
-    ctx.sync()
+    prof = rt.LaunchParams(spp=spp, max_bounces=BOUNCES, flags=rt.LAUNCH_PROFILE)
+    grp.execute(500, prof, gather=-1)
+    grp.sync()
     pst = ctx.stats()
     trace_ms, shade_ms, trace_launches = pst.trace_ns / 1e6, pst.shade_ns / 1e6, max(1, pst.trace_launches)
 
     # ---- e2e through the C ABI with host buffers --------------------------------------------------------------
-    # Two frames in flight, as the reference's swapchain loop has (src/context.rs:30,639-694): frame n's image travels to
-    # pinned host memory on the context's copy stream (rt2_read_async) while frame n+1 renders; every step still uploads its
-    # GConst from pinned staging and reads its result back, and the timed region ends only after the last transfer landed.
+    # Two frames in flight, as the reference's swapchain loop has (src/context.rs:30,639-694): the ASSEMBLED frame n travels to
+    # pinned host memory on the communication stream (rt2_group_read_async) while frame n+1 renders; every step uploads its
+    # GConst from pinned staging, and the timed region ends only after the last transfer landed.
     host_out = [torch.empty(W * H * 4, dtype=torch.float16).pin_memory() for _ in range(2)]
     for i in range(2):
-        lp.update_uniform(g); step(200 + i); ctx.read_into_async(rt.BUF_DIFFUSE_F16, host_out[i & 1].data_ptr(), W * H * 8)
-    drain()
-    ctx.sync()
+        grp.update_uniform(g); step(200 + i)
+        if rank == 0:
+            grp.read_into_async(host_out[i & 1].data_ptr(), frame_bytes)
+    grp.sync()
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
@@ -307,45 +420,56 @@ def main():
     e0.record()
     for i in range(args.steps):
         g.frame = 300 + i
-        lp.update_uniform(g)                                                                  # pinned host -> device, 1424 B
+        grp.update_uniform(g)                                                   # pinned host -> device, 1424 B
         step(300 + i)
-        ctx.read_into_async(rt.BUF_DIFFUSE_F16, host_out[i & 1].data_ptr(), W * H * 8)        # device -> pinned host
-    drain()
-    ctx.read_fence()                                                                          # e1 waits for every transfer
+        if rank == 0:
+            grp.read_into_async(host_out[i & 1].data_ptr(), frame_bytes)        # assembled frame, device -> pinned host
+    grp.wait_gather()                                                           # e1 waits for every gather and transfer
     e1.record()
-    ctx.sync()
+    grp.sync()
     torch.cuda.synchronize()
     e2e_ms = e0.elapsed_time(e1)
+    frame_ok = bool(torch.isfinite(host_out[(args.steps - 1) & 1].float()).all().item()) and float(host_out[(args.steps - 1) & 1].float().abs().sum()) > 0 if rank == 0 else True
 
-    t = torch.tensor([ms, e2e_ms, float(rays_per_step), float(launches), trace_ms, shade_ms], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms, e2e_ms, float(rays_per_step), float(launches), trace_ms, shade_ms, float(hits_per_step)], dtype=torch.float64, device="cuda")
     if dist:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         ms, e2e_ms = tmax[0].item(), tmax[1].item()
-        total_rays_step, launches = tsum[2].item(), int(tsum[3].item())
+        total_rays_step, launches, total_hits_step = tsum[2].item(), int(tsum[3].item()), tsum[6].item()
     else:
-        total_rays_step = float(rays_per_step)
+        total_rays_step, total_hits_step = float(rays_per_step), float(hits_per_step)
     value = total_rays_step * args.steps / (ms * 1e-3) / 1e6
     e2e_value = total_rays_step * args.steps / (e2e_ms * 1e-3) / 1e6
     if rank == 0:
         peak, peak_kind = measured_peak_hbm()
         rays_per_launch = rays_per_step / trace_launches
         achieved = rays_per_launch * B_TRAVERSE / (trace_ms / trace_launches * 1e-3) / 1e9
+        ncu = ncu_summary()
+        k0 = (ncu.get("launches") or [{}])[0]
+        traffic = ncu.get("traffic_bytes_per_launch")
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"C2 procedural hall {sc.num_triangles} tris, 64 sRGB textures 512^2, {W}x{H}, {BOUNCES} bounces, {SPP} spp per GPU (spp={spp})",
-                       "sharding": "whole frame" if n_gpus == 1 else f"{BAND_ROWS}-row bands interleaved over {n_gpus} ranks, scene replicated, NCCL all_gather of fp32 bands per step",
-                       "l2": "no flush: working set (BVH+triangles+shading records+textures+path state ~270 MB) exceeds the 126 MB L2",
-                       "rays_per_step": total_rays_step},
+                       "sharding": "whole frame (rt2_group of one)" if n_gpus == 1 else f"{BAND_ROWS}-row bands interleaved over {n_gpus} ranks, scene replicated; band plan + ncclAllGather of the rgba16f bands + un-permute inside librt2cuda.so (rt2_group_*), every step",
+                       "schedule": "speculative sample parallelism (every sample of a pixel is its own path; validated + summed in shader order), 2 wavefront chains" if st.sample_schedule == 1 else "one launch pair per (sample, bounce), wavefront chains",
+                       "l2": "no flush: working set (BVH+triangles+shading records+textures+path state ~1 GB) exceeds the 126 MB L2",
+                       "rays_per_step": total_rays_step, "hit_fraction": total_hits_step / max(total_rays_step, 1.0)},
             "clocks": clocks,
-            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 1424, "d2h_bytes_per_step": W * H * 8, "ms_per_step": e2e_ms / args.steps},
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 1424, "d2h_bytes_per_step": frame_bytes, "ms_per_step": e2e_ms / args.steps,
+                    "delivers": "assembled W x H rgba16f frame in pinned host memory on rank 0 (gather + un-permute + D2H inside the timed region)", "frame_finite_nonzero": frame_ok},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": "k_trace", "achieved": achieved, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": ncu_traffic_bytes(),
+                         "frac": achieved / peak, "traffic": traffic,
                          "algorithmic_bytes_per_ray": B_TRAVERSE, "rays_per_launch": rays_per_launch, "avg_launch_ms": trace_ms / trace_launches,
                          "trace_share_of_step": trace_ms / (trace_ms + shade_ms) if trace_ms + shade_ms > 0 else None,
+                         "dram_traffic_over_algorithmic": (traffic / (k0.get("rays", 0) * B_TRAVERSE)) if traffic and k0.get("rays") else None,
+                         # the bound that actually binds (the BVH is L2-resident, DRAM runs at a few % of peak): instruction issue
+                         "issue": {"issue_active_pct": k0.get("issue_active_pct"), "lanes_per_inst": k0.get("threads_per_inst"),
+                                   "warp_insts_per_ray": (k0.get("inst_executed") / k0["rays"]) if k0.get("inst_executed") and k0.get("rays") else None,
+                                   "source": ncu.get("source")},
                          "whole_step": {"bytes_per_ray": B_RAY, "achieved": value * 1e6 / n_gpus * B_RAY / 1e9, "frac": value * 1e6 / n_gpus * B_RAY / 1e9 / peak}},
         }
         if n_gpus == 1 and not args.no_cpu_baseline:
@@ -354,9 +478,16 @@ def main():
             if cspp > 1:
                 v, crays, dt, cores, _ = cpu_oracle_run(cspp, BOUNCES)
             line["cpu_baseline"] = {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "port",
-                                    "sample": f"same C2 scene and camera, {W}x{H}, {cspp} spp x {BOUNCES} bounces = {crays} rays in {dt:.1f} s (CPU oracle, {cores} threads)"}
+                                    "sample": f"same C2 scene and camera, {W}x{H}, {cspp} spp x {BOUNCES} bounces = {crays} rays in {dt:.1f} s (CPU oracle, {cores} threads)",
+                                    "gpu_over_cpu": {"e2e": e2e_value / v, "device": value / v, "cpu_threads": cores}}
+    grp.close()
+    if rank == 0:
+        if n_gpus == 1 and not args.no_extra:
+            try:
+                line["extra"] = run_extra(rt, torch, local_rank)
+            except Exception as e:          # the headline line must survive a failure of the extras
+                line["extra"] = {"error": f"{type(e).__name__}: {e}"}
         print(json.dumps(line), flush=True)
-    ctx.close()
     if dist:
         dist.destroy_process_group()
     return 0

@@ -231,13 +231,21 @@ pub struct rt2_stats {
     pub trace_ns: u64,
     pub shade_ns: u64,
     pub trace_launches: u64,
-    pub _reserved: [u64; 2],
+    pub sample_schedule: u64,
+    pub _reserved: [u64; 1],
 }
 
 #[repr(C)]
 pub struct rt2_ctx {
     _private: [u8; 0],
 }
+/// Opaque multi-GPU group (include/rt2_abi.h, "multi-GPU").
+#[repr(C)]
+pub struct rt2_group {
+    _private: [u8; 0],
+}
+pub const RT2_GROUP_BAND_ROWS_ROWS: u64 = 8;
+pub const RT2_UNIQUE_ID_BYTES_LEN: u64 = 128;
 
 extern "C" {
     pub fn rt2_abi_version() -> c_int;
@@ -266,6 +274,30 @@ extern "C" {
     pub fn rt2_pack_bands(ctx: *mut rt2_ctx, which: c_int, device_dst: *mut c_void, nbytes: usize, band_rows: u32, band_rank: u32, band_world: u32) -> c_int;
     pub fn rt2_write(ctx: *mut rt2_ctx, which: c_int, src: *const c_void, nbytes: usize) -> c_int;
     pub fn rt2_get_stats(ctx: *mut rt2_ctx, out: *mut rt2_stats) -> c_int;
+
+    // multi-GPU: one frame over the GPUs of one node (band plan + NCCL gather + un-permute inside the library)
+    pub fn rt2_group_create(cuda_devices: *const c_int, n: c_int, out: *mut *mut rt2_group) -> c_int;
+    pub fn rt2_group_unique_id(id128: *mut c_void) -> c_int;
+    pub fn rt2_group_create_rank(cuda_device: c_int, rank: c_int, world: c_int, id128: *const c_void, out: *mut *mut rt2_group) -> c_int;
+    pub fn rt2_group_destroy(g: *mut rt2_group) -> c_int;
+    pub fn rt2_group_last_error(g: *mut rt2_group) -> *const c_char;
+    pub fn rt2_group_world(g: *mut rt2_group) -> c_int;
+    pub fn rt2_group_local_count(g: *mut rt2_group) -> c_int;
+    pub fn rt2_group_ctx(g: *mut rt2_group, local_index: c_int) -> *mut rt2_ctx;
+    pub fn rt2_group_upload_scene(g: *mut rt2_group, scene: *const rt2_scene_desc) -> c_int;
+    pub fn rt2_group_build_accel(g: *mut rt2_group) -> c_int;
+    pub fn rt2_group_resize(g: *mut rt2_group, width: u32, height: u32) -> c_int;
+    pub fn rt2_group_set_constants(g: *mut rt2_group, gconst: *const c_void, nbytes: usize) -> c_int;
+    pub fn rt2_group_prepare_lights(g: *mut rt2_group) -> c_int;
+    pub fn rt2_group_generate_mips(g: *mut rt2_group, which: c_int) -> c_int;
+    pub fn rt2_group_render(g: *mut rt2_group, frame: u32, params: *const rt2_launch_params, gather_which: c_int) -> c_int;
+    pub fn rt2_group_gather(g: *mut rt2_group, which: c_int) -> c_int;
+    pub fn rt2_group_postprocess(g: *mut rt2_group, frame: u32) -> c_int;
+    pub fn rt2_group_read(g: *mut rt2_group, dst: *mut c_void, nbytes: usize) -> c_int;
+    pub fn rt2_group_read_async(g: *mut rt2_group, dst: *mut c_void, nbytes: usize) -> c_int;
+    pub fn rt2_group_assembled(g: *mut rt2_group, local_index: c_int, nbytes: *mut usize) -> *mut c_void;
+    pub fn rt2_group_wait_gather(g: *mut rt2_group) -> c_int;
+    pub fn rt2_group_sync(g: *mut rt2_group) -> c_int;
 }
 
 // Layout checks that `cargo build` evaluates at compile time; the same numbers are asserted against the C header by the

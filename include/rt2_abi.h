@@ -241,7 +241,8 @@ typedef struct rt2_stats {
     uint64_t trace_ns;         /* with RT2_LAUNCH_PROFILE: summed CUDA-event time of the traversal kernel launches */
     uint64_t shade_ns;         /* with RT2_LAUNCH_PROFILE: summed CUDA-event time of the shading kernel launches   */
     uint64_t trace_launches;   /* with RT2_LAUNCH_PROFILE: traversal kernel launches that had rays to trace         */
-    uint64_t _reserved[2];
+    uint64_t sample_schedule;  /* K1: 0 = one launch pair per (sample, bounce); 1 = speculative sample parallelism (every sample its own path) */
+    uint64_t _reserved[1];
 } rt2_stats;
 
 typedef struct rt2_ctx rt2_ctx;
@@ -326,6 +327,53 @@ int  rt2_pack_bands(rt2_ctx* ctx, int which, void* device_dst, size_t nbytes,
  * to seed accumulation state). */
 int  rt2_write(rt2_ctx* ctx, int which, const void* src, size_t nbytes);
 int  rt2_get_stats(rt2_ctx* ctx, rt2_stats* out);
+
+/* ---- multi-GPU: one frame over the GPUs of one node -----------------------------
+ * The reference renders on ONE Vulkan device (src/context.rs:120, one queue, src/context.rs:639-694); the group generalises
+ * its frame loop (src/main.rs:661-700) to N GPUs: the scene and acceleration structure are replicated, the frame is split into
+ * interleaved bands of RT2_GROUP_BAND_ROWS rows (band b -> rank b mod N; the RNG is keyed on absolute pixel + frame,
+ * src/shaders/Helpers.glsl:13-23, so the N-GPU image equals the 1-GPU image bit for bit), every rank renders its bands and
+ * the library all-gathers them with NCCL over NVLink on its own stream and un-permutes them into an assembled W x H frame on
+ * every rank.  Two ways to build a group:
+ *   rt2_group_create       one process drives n devices (a Rust host needs no launcher);
+ *   rt2_group_create_rank  one process per GPU (torchrun / MPI): rank 0 calls rt2_group_unique_id, the host distributes the
+ *                          128 bytes by its own means, every rank passes them in.
+ * NCCL (libnccl.so.2) is resolved with dlopen when a group is created, so the library loads — and single-GPU contexts work —
+ * without it.  A group is not thread-safe; calls enqueue work and return. */
+typedef struct rt2_group rt2_group;
+#define RT2_GROUP_BAND_ROWS 8u
+#define RT2_UNIQUE_ID_BYTES 128
+int  rt2_group_create(const int* cuda_devices, int n, rt2_group** out);
+int  rt2_group_unique_id(void* id128);
+int  rt2_group_create_rank(int cuda_device, int rank, int world, const void* id128, rt2_group** out);
+int  rt2_group_destroy(rt2_group* g);
+const char* rt2_group_last_error(rt2_group* g);
+int  rt2_group_world(rt2_group* g);                    /* ranks in the frame split                                  */
+int  rt2_group_local_count(rt2_group* g);              /* contexts this process owns (n, or 1 per process)          */
+rt2_ctx* rt2_group_ctx(rt2_group* g, int local_index); /* for per-context calls (rt2_get_stats, rt2_read of a buffer) */
+/* Model::from_gltf + TLAS on every GPU (src/model.rs:185-476, src/main.rs:153-191) */
+int  rt2_group_upload_scene(rt2_group* g, const rt2_scene_desc* scene);
+int  rt2_group_build_accel(rt2_group* g);
+int  rt2_group_resize(rt2_group* g, uint32_t width, uint32_t height);          /* RenderResources::new, src/render_resources.rs:130 */
+int  rt2_group_set_constants(rt2_group* g, const void* gconst, size_t nbytes); /* LightPasses::update_uniform, src/light_passes.rs:665 */
+int  rt2_group_prepare_lights(rt2_group* g);                                   /* replicated: K10 is tiny (src/prepare_lights.rs:172) */
+int  rt2_group_generate_mips(rt2_group* g, int which);                         /* replicated: K12 (src/mip_pass.rs:122)              */
+/* LightPasses::execute (src/light_passes.rs:550-663) on every rank's bands (params->band_* are filled in by the group), then,
+ * if gather_which >= 0 (an rt2_buffer id of a W x H frame buffer, e.g. RT2_BUF_DIFFUSE_F32), pack + ncclAllGather +
+ * un-permute of that buffer on the group's communication stream: the gather of frame n overlaps the render of frame n + 1. */
+int  rt2_group_render(rt2_group* g, uint32_t frame, const rt2_launch_params* params, int gather_which);
+/* the gather step alone (e.g. RT2_BUF_OUTPUT_RGBA8 after rt2_group_postprocess: sharded K13 + gather of RGBA8) */
+int  rt2_group_gather(rt2_group* g, int which);
+/* PostProcessPass::execute (src/postprocess.rs:225-307) on every rank (its own bands' pixels are the valid ones) */
+int  rt2_group_postprocess(rt2_group* g, uint32_t frame);
+/* the assembled frame of the last gathered rt2_group_render, from local context 0: blocking / frame-in-flight (see rt2_read_async) */
+int  rt2_group_read(rt2_group* g, void* dst, size_t nbytes);
+int  rt2_group_read_async(rt2_group* g, void* dst, size_t nbytes);
+/* device pointer of the assembled frame on local context `local_index` (valid after rt2_group_sync / on the render stream after
+ * rt2_group_wait_gather) */
+void* rt2_group_assembled(rt2_group* g, int local_index, size_t* nbytes);
+int  rt2_group_wait_gather(rt2_group* g);   /* later work on every context's stream waits for the gathers issued so far (no host block) */
+int  rt2_group_sync(rt2_group* g);
 
 #ifdef __cplusplus
 }

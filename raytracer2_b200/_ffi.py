@@ -64,7 +64,7 @@ class LaunchParams(C.Structure):
 
 
 class Stats(C.Structure):
-    _fields_ = _fields("rays_traced rays_hit kernel_launches wavefront_iterations bvh_nodes bvh_triangles device_bytes trace_ns shade_ns trace_launches _r0 _r1", u64)
+    _fields_ = _fields("rays_traced rays_hit kernel_launches wavefront_iterations bvh_nodes bvh_triangles device_bytes trace_ns shade_ns trace_launches sample_schedule _r1", u64)
 
 
 # ---- GConst (include/rt2_gconst.h; src/shader_params.rs) ----------------------------------------------
@@ -217,6 +217,29 @@ ABI_SYMBOLS = {
     "rt2_pack_bands": (C.c_int, [VP, C.c_int, VP, C.c_size_t, u32, u32, u32]),
     "rt2_write": (C.c_int, [VP, C.c_int, VP, C.c_size_t]),
     "rt2_get_stats": (C.c_int, [VP, C.POINTER(Stats)]),
+    # multi-GPU group (rt2_group.cu)
+    "rt2_group_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(VP)]),
+    "rt2_group_unique_id": (C.c_int, [VP]),
+    "rt2_group_create_rank": (C.c_int, [C.c_int, C.c_int, C.c_int, VP, C.POINTER(VP)]),
+    "rt2_group_destroy": (C.c_int, [VP]),
+    "rt2_group_last_error": (C.c_char_p, [VP]),
+    "rt2_group_world": (C.c_int, [VP]),
+    "rt2_group_local_count": (C.c_int, [VP]),
+    "rt2_group_ctx": (VP, [VP, C.c_int]),
+    "rt2_group_upload_scene": (C.c_int, [VP, C.POINTER(SceneDesc)]),
+    "rt2_group_build_accel": (C.c_int, [VP]),
+    "rt2_group_resize": (C.c_int, [VP, u32, u32]),
+    "rt2_group_set_constants": (C.c_int, [VP, VP, C.c_size_t]),
+    "rt2_group_prepare_lights": (C.c_int, [VP]),
+    "rt2_group_generate_mips": (C.c_int, [VP, C.c_int]),
+    "rt2_group_render": (C.c_int, [VP, u32, C.POINTER(LaunchParams), C.c_int]),
+    "rt2_group_gather": (C.c_int, [VP, C.c_int]),
+    "rt2_group_postprocess": (C.c_int, [VP, u32]),
+    "rt2_group_read": (C.c_int, [VP, VP, C.c_size_t]),
+    "rt2_group_read_async": (C.c_int, [VP, VP, C.c_size_t]),
+    "rt2_group_assembled": (VP, [VP, C.c_int, C.POINTER(C.c_size_t)]),
+    "rt2_group_wait_gather": (C.c_int, [VP]),
+    "rt2_group_sync": (C.c_int, [VP]),
 }
 
 HOST_SYMBOLS = {

@@ -203,8 +203,128 @@ class Renderer:
 
     def close(self):
         if getattr(self, "_ctx", None) and self._ctx.value:
-            self._lib.rt2_destroy(self._ctx)
+            if not getattr(self, "_borrowed", False):      # contexts of a Group belong to the group
+                self._lib.rt2_destroy(self._ctx)
             self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Group:
+    """rt2_group: one frame over the GPUs of one node behind the C ABI — band plan, NCCL all-gather and the un-permute into the
+    assembled frame all happen inside librt2cuda.so.  Group(devices=[0, 1, ...]) drives n devices from this process;
+    Group.from_rank(device, rank, world, unique_id) is the one-process-per-GPU form (unique_id from Group.unique_id() on rank 0,
+    distributed by the host's own means, e.g. torch.distributed.broadcast_object_list)."""
+
+    def __init__(self, devices=None, _handle=None):
+        self._lib = _ffi.cuda_lib()
+        self._g = C.c_void_p()
+        if _handle is not None:
+            self._g = _handle
+        else:
+            arr = (C.c_int * len(devices))(*devices)
+            rc = self._lib.rt2_group_create(arr, len(devices), C.byref(self._g))
+            if rc != 0:
+                raise Rt2Error(f"rt2_group_create failed ({rc}): {(self._lib.rt2_group_last_error(None) or b'').decode()}")
+        self.width = self.height = 0
+
+    @staticmethod
+    def unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        lib = _ffi.cuda_lib()
+        rc = lib.rt2_group_unique_id(buf)
+        if rc != 0:
+            raise Rt2Error(f"rt2_group_unique_id failed ({rc}): {(lib.rt2_group_last_error(None) or b'').decode()}")
+        return buf.raw
+
+    @classmethod
+    def from_rank(cls, device: int, rank: int, world: int, unique_id: bytes | None) -> "Group":
+        lib = _ffi.cuda_lib()
+        h = C.c_void_p()
+        idbuf = C.create_string_buffer(unique_id, 128) if unique_id is not None else None
+        rc = lib.rt2_group_create_rank(device, rank, world, idbuf, C.byref(h))
+        if rc != 0:
+            raise Rt2Error(f"rt2_group_create_rank failed ({rc}): {(lib.rt2_group_last_error(None) or b'').decode()}")
+        return cls(_handle=h)
+
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            raise Rt2Error(f"{what} failed ({rc}): {(self._lib.rt2_group_last_error(self._g) or b'').decode()}")
+
+    @property
+    def world(self) -> int:
+        return self._lib.rt2_group_world(self._g)
+
+    @property
+    def local_count(self) -> int:
+        return self._lib.rt2_group_local_count(self._g)
+
+    def ctx(self, i: int = 0) -> "Renderer":
+        """A non-owning Renderer view of local context i (stats, per-context reads, set_stream)."""
+        r = Renderer.__new__(Renderer)
+        r._lib = self._lib
+        r._ctx = C.c_void_p(self._lib.rt2_group_ctx(self._g, i))
+        r._borrowed = True
+        r.width, r.height = self.width, self.height
+        return r
+
+    def upload_scene(self, scene_desc):
+        self._check(self._lib.rt2_group_upload_scene(self._g, scene_desc), "rt2_group_upload_scene")
+        self._check(self._lib.rt2_group_build_accel(self._g), "rt2_group_build_accel")
+
+    def resize(self, width: int, height: int):
+        self._check(self._lib.rt2_group_resize(self._g, width, height), "rt2_group_resize")
+        self.width, self.height = width, height
+
+    def update_uniform(self, g_const: GConst):
+        self._check(self._lib.rt2_group_set_constants(self._g, C.byref(g_const), C.sizeof(g_const)), "rt2_group_set_constants")
+
+    def prepare_lights(self):
+        self._check(self._lib.rt2_group_prepare_lights(self._g), "rt2_group_prepare_lights")
+
+    def generate_mips(self, which: int):
+        self._check(self._lib.rt2_group_generate_mips(self._g, which), "rt2_group_generate_mips")
+
+    def execute(self, frame: int, params: LaunchParams | None = None, gather: int = BUF_DIFFUSE_F32):
+        p = C.byref(params) if params is not None else None
+        self._check(self._lib.rt2_group_render(self._g, frame & 0xFFFFFFFF, p, gather), "rt2_group_render")
+
+    def postprocess(self, frame: int):
+        self._check(self._lib.rt2_group_postprocess(self._g, frame & 0xFFFFFFFF), "rt2_group_postprocess")
+
+    def gather(self, which: int):
+        self._check(self._lib.rt2_group_gather(self._g, which), "rt2_group_gather")
+
+    def read(self, dtype=np.uint8) -> np.ndarray:
+        n = C.c_size_t(0)
+        if not self._lib.rt2_group_assembled(self._g, 0, C.byref(n)):
+            raise Rt2Error("no gathered frame")
+        out = np.empty(n.value, dtype=np.uint8)
+        self._check(self._lib.rt2_group_read(self._g, out.ctypes.data_as(C.c_void_p), n.value), "rt2_group_read")
+        return out.view(dtype)
+
+    def read_into_async(self, dst_ptr: int, nbytes: int):
+        self._check(self._lib.rt2_group_read_async(self._g, C.c_void_p(dst_ptr), nbytes), "rt2_group_read_async")
+
+    def assembled_ptr(self, i: int = 0):
+        n = C.c_size_t(0)
+        p = self._lib.rt2_group_assembled(self._g, i, C.byref(n))
+        return p, n.value
+
+    def wait_gather(self):
+        self._check(self._lib.rt2_group_wait_gather(self._g), "rt2_group_wait_gather")
+
+    def sync(self):
+        self._check(self._lib.rt2_group_sync(self._g), "rt2_group_sync")
+
+    def close(self):
+        if getattr(self, "_g", None) and self._g.value:
+            self._lib.rt2_group_destroy(self._g)
+            self._g = C.c_void_p()
 
     def __del__(self):
         try:

@@ -1320,6 +1320,7 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
     const bool spec = want && ctx->path_mode == 0 && spec_eligible(ctx, band, spp, bounces);
     rc = spec ? render_reference_spec(ctx, frame, lp, spp, bounces) : render_reference_seq(ctx, frame, lp);
     if (rc != RT2_OK) return rc;
+    ctx->stats.sample_schedule = spec ? 1u : 0u;
     if (ctx->speculate < 0) {
         if (!ctx->h_k1_stats) {
             RT2_CUDA(ctx, cudaHostAlloc((void**)&ctx->h_k1_stats, 32, cudaHostAllocDefault));

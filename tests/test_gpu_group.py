@@ -1,0 +1,175 @@
+"""rt2_group_* (include/rt2_abi.h "multi-GPU"): the band plan, the NCCL all-gather and the un-permute into the
+assembled frame inside librt2cuda.so.  The N-GPU frame must equal the 1-GPU frame bit for bit (the RNG is keyed on absolute
+pixel + frame, Helpers.glsl:13-23).  Tests with more than one device skip on a one-GPU box (run them with gpurun --gpus 2)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import raytracer2_b200 as rt
+
+pytestmark = pytest.mark.gpu
+
+
+def _scene(kind=rt.SCENE_HALL, scale=0.125, w=200, h=150):
+    sc = rt.Scene(kind, scale, 32, 0)
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+    g.refrence_mode = 1
+    return sc, g
+
+
+def _single(sc, g, w, h, frames, params, which=rt.BUF_DIFFUSE_F32, dtype=np.uint32, post=False):
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, w, h)
+    out, rays = [], []
+    for f in frames:
+        g.frame = f
+        lp.update_uniform(g)
+        lp.execute(f, params)
+        if post:
+            rt.PostProcessPass(ctx).execute(f)
+        out.append(ctx.read(which, dtype).copy())
+        rays.append(ctx.stats().rays_traced)
+    ctx.close()
+    return out, rays
+
+
+def _group_frames(grp, sc, g, w, h, frames, params):
+    grp.upload_scene(sc.desc)
+    grp.resize(w, h)
+    out, rays = [], []
+    for f in frames:
+        g.frame = f
+        grp.update_uniform(g)
+        grp.execute(f, params)                     # render every rank's bands + gather RT2_BUF_DIFFUSE_F32
+        out.append(grp.read(np.uint32).copy())
+        rays.append(sum(grp.ctx(i).stats().rays_traced for i in range(grp.local_count)))
+    return out, rays
+
+
+def test_group_of_one_matches_a_plain_context():
+    w, h = 200, 150
+    sc, g = _scene(w=w, h=h)
+    p = rt.LaunchParams(spp=2, max_bounces=3)
+    want, rays = _single(sc, g, w, h, [1, 2, 3], p)
+    grp = rt.Group([0])
+    assert grp.world == 1 and grp.local_count == 1
+    got, grays = _group_frames(grp, sc, g, w, h, [1, 2, 3], p)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    assert grays == rays
+    # frame-in-flight read of the assembled frame + the device pointer of the assembled frame
+    host = torch.empty(w * h * 4, dtype=torch.int32).pin_memory()
+    grp.read_into_async(host.data_ptr(), w * h * 16)
+    grp.sync()
+    assert np.array_equal(host.numpy().view(np.uint32), want[-1])
+    ptr, n = grp.assembled_ptr(0)
+    assert ptr and n == w * h * 16
+    with pytest.raises(rt.Rt2Error):
+        grp.read_into_async(host.data_ptr(), w * h * 16 - 16)
+    grp.close()
+
+
+def test_group_error_paths():
+    with pytest.raises(rt.Rt2Error):
+        rt.Group([0, 0])                        # a device twice
+    with pytest.raises(rt.Rt2Error):
+        rt.Group([999])
+    grp = rt.Group([0])
+    with pytest.raises(rt.Rt2Error):
+        grp.execute(1)                          # before resize / scene
+    with pytest.raises(rt.Rt2Error):
+        grp.read()
+    grp.close()
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("w,h", [(200, 150), (1920, 1080)])
+def test_single_process_group_equals_one_gpu_bit_for_bit(n, w, h):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+    sc, g = _scene(scale=0.125 if w < 1000 else 0.5, w=w, h=h)
+    p = rt.LaunchParams(spp=4, max_bounces=3)
+    frames = [1, 2, 3, 4]                      # frames 2.. run the speculative schedule (auto policy) on every rank
+    want, rays = _single(sc, g, w, h, frames, p)
+    grp = rt.Group(list(range(n)))
+    assert grp.world == n and grp.local_count == n
+    got, grays = _group_frames(grp, sc, g, w, h, frames, p)
+    for f, (a, b) in enumerate(zip(got, want)):
+        assert np.array_equal(a, b), f"frame {frames[f]}: {int((a != b).sum())} words differ"
+    assert grays == rays
+    # every rank holds the assembled frame
+    for i in range(n):
+        ptr, nbytes = grp.assembled_ptr(i)
+        with torch.cuda.device(i):
+            t = torch.empty(nbytes // 4, dtype=torch.int32, device=f"cuda:{i}")
+            grp.sync()
+            assert C.CDLL("libcudart.so.12").cudaMemcpy(C.c_void_p(t.data_ptr()), C.c_void_p(ptr), C.c_size_t(nbytes), 3) == 0
+            assert np.array_equal(t.cpu().numpy().view(np.uint32), want[-1]), f"rank {i}"
+    grp.close()
+
+
+def test_group_gathers_tonemapped_rgba8_bands():
+    """K1 -> K13 on every rank's bands, RGBA8 bands gathered (sharded K13 + gather of RGBA8, BASELINE config C5's shape)."""
+    n = 2
+    if torch.cuda.device_count() < n:
+        pytest.skip("needs 2 GPUs")
+    w, h = 320, 180
+    sc = rt.Scene(rt.SCENE_INSTANCED, 0.05, 32, 0)
+    d = sc.desc.contents
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights, env_size=(d.sky_width, d.sky_height))
+    g.refrence_mode = 1; g.environment = 1
+    p = rt.LaunchParams(spp=2, max_bounces=3)
+    want, _ = _single(sc, g, w, h, [1], p, which=rt.BUF_OUTPUT_RGBA8, dtype=np.uint8, post=True)
+    grp = rt.Group([0, 1])
+    grp.upload_scene(sc.desc); grp.resize(w, h); grp.update_uniform(g)
+    grp.generate_mips(rt.GenerateMipsPass.ENVIRONMENT)
+    grp.execute(1, p, gather=-1)
+    grp.postprocess(1)
+    grp.gather(rt.BUF_OUTPUT_RGBA8)
+    assert np.array_equal(grp.read(np.uint8), want[0])
+    grp.close()
+
+
+def _rank_worker(rank, world, uid, w, h, q):
+    import numpy as np
+    import raytracer2_b200 as rt
+    sc = rt.Scene(rt.SCENE_HALL, 0.125, 32, 0)
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+    g.refrence_mode = 1
+    grp = rt.Group.from_rank(rank, rank, world, uid)
+    grp.upload_scene(sc.desc); grp.resize(w, h)
+    out = None
+    for f in (1, 2, 3):
+        g.frame = f
+        grp.update_uniform(g)
+        grp.execute(f, rt.LaunchParams(spp=4, max_bounces=3))
+        out = grp.read(np.uint32).copy()
+    q.put((rank, out.tobytes(), grp.ctx(0).stats().rays_traced))
+    grp.close()
+
+
+def test_one_process_per_gpu_group_equals_one_gpu_bit_for_bit():
+    n = 2
+    if torch.cuda.device_count() < n:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    w, h = 200, 150
+    sc, g = _scene(w=w, h=h)
+    want, rays = _single(sc, g, w, h, [1, 2, 3], rt.LaunchParams(spp=4, max_bounces=3))
+    uid = rt.Group.unique_id()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_rank_worker, args=(r, n, uid, w, h, q)) for r in range(n)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=300) for _ in range(n)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, buf, _ in res:
+        assert np.array_equal(np.frombuffer(buf, np.uint32), want[-1]), f"rank {rank}"
+    assert sum(r[2] for r in res) == rays[-1]

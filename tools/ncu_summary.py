@@ -5,6 +5,7 @@ import os as _os, sys as _sys; _sys.path.insert(0, _os.path.dirname(_os.path.dir
 import csv, io, json, subprocess, sys
 
 rep, out, note = sys.argv[1], sys.argv[2], (sys.argv[3] if len(sys.argv) > 3 else "")
+rays_per_launch = float(sys.argv[4]) if len(sys.argv) > 4 else None      # rays one captured launch traces (from the same run's stats)
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
 open(out + "_full_raw.csv", "w").write(raw)
 rows = list(csv.reader(io.StringIO(raw)))
@@ -43,10 +44,14 @@ for r in data:
         "xu_pipe_pct": num(r, "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"),
         "lsu_pipe_pct": num(r, "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
         "regs_per_thread": num(r, "launch__registers_per_thread"),
+        "inst_executed": num(r, "smsp__inst_executed.sum"),
+        "rays": rays_per_launch,
         "achieved_occupancy_pct": num(r, "sm__warps_active.avg.pct_of_peak_sustained_active"),
         "local_ld_st_sectors": (num(r, "l1tex__t_sectors_pipe_lsu_mem_local_op_ld.sum") or 0) + (num(r, "l1tex__t_sectors_pipe_lsu_mem_local_op_st.sum") or 0),
     })
-json.dump({"source": rep.split("/")[-1] + " (ncu --set full --clock-control none --import-source on)", "note": note, "launches": launches},
+big = [l["dram_bytes"] for l in launches if l["dram_bytes"]]
+json.dump({"source": rep.split("/")[-1] + " (ncu --set full --clock-control none --import-source on)", "note": note, "launches": launches,
+           "traffic_bytes_per_launch": (sum(big) / len(big)) if big else None},
           open(out + "_summary.json", "w"), indent=1)
 for l in launches:
     print(l["kernel"][:60].ljust(60), l["duration_us"], "us  dram MB", round(l["dram_bytes"] / 1e6, 1), " thr/inst", l["threads_per_inst"], " issue", l["issue_active_pct"],
