@@ -15,8 +15,11 @@ int restir_ensure_resources(rt2_ctx* ctx);
 int lights_ensure_resources(rt2_ctx* ctx);
 int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays);
 
+// interleaved row bands (the same rule as rt2_render.cu's Band): the passes below are per-pixel independent, every buffer
+// stays full-frame and addressed by absolute pixel, a rank just visits its own rows
+struct BandRef { uint32_t band_rows, rank, world, local_rows; };
 struct GBufferArgs {
-    SceneRefs sc; const rt2_gconst* g; uint32_t width, height;
+    SceneRefs sc; const rt2_gconst* g; uint32_t width, height; BandRef band;
     float* depth; uint32_t* normals; uint32_t* geo_normals; uint32_t* diffuse_albedo; uint32_t* specular_rough; ushort4* emissive; float4* motion;
     unsigned long long* stat_hits;
 };
@@ -38,11 +41,13 @@ __device__ __forceinline__ V3 get_motion_vector(const rt2_planar_view_constants&
     return m;
 }
 
-__device__ __forceinline__ bool tile_pixel(uint32_t i, uint32_t width, uint32_t height, uint32_t* x, uint32_t* y) {
+__device__ __forceinline__ bool tile_pixel(uint32_t i, uint32_t width, const BandRef& b, uint32_t* x, uint32_t* y) {
     const uint32_t tiles_x = (width + 7u) >> 3;
     const uint32_t tile = i >> 5, within = i & 31u;
-    *x = (tile % tiles_x) * 8u + (within & 7u); *y = (tile / tiles_x) * 4u + (within >> 3);
-    return *x < width && *y < height;
+    const uint32_t ly = (tile / tiles_x) * 4u + (within >> 3);
+    *x = (tile % tiles_x) * 8u + (within & 7u);
+    *y = b.world <= 1u ? ly : ((ly / b.band_rows) * b.world + b.rank) * b.band_rows + (ly % b.band_rows);
+    return *x < width && ly < b.local_rows;
 }
 
 // Register caps measured on the ReSTIR frames (profiles/r01d_ab_gi_regs.txt): K9 stages a/b at 8 blocks/SM (64 registers, DI-only frame
@@ -62,7 +67,7 @@ __global__ void __launch_bounds__(128, RT2_GBUF_BLOCKS) k_gbuffer(GBufferArgs a)
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
     __syncthreads();
     uint32_t x, y;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &x, &y)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &x, &y)) return;
     const size_t i = (size_t)y * a.width + x;
     const rt2_gconst& g = *a.g;
     V3 o, d;
@@ -290,7 +295,7 @@ __device__ __forceinline__ void flush_ray_stats(unsigned long long* stat_rays, u
 // K9
 // ------------------------------------------------------------------------------------------------
 struct DIArgs {
-    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame;
+    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame; BandRef band;
     GBufferRefs gb;
     LightRefs li;
     rt2_packed_di_reservoir* reservoirs; ushort4* diffuse; ushort4* specular; float4* diffuse_f32;
@@ -299,7 +304,7 @@ struct DIArgs {
 
 __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
     const rt2_restirdi_params& di = g.restir_di;
     uint32_t rays = 0, hits = 0;
@@ -418,7 +423,7 @@ template <bool SEC>
 __global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_a(DIWaveArgs w) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
-    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly);
     bool traced = false;
     uint32_t slot = 0;
     if (inside) {
@@ -451,7 +456,7 @@ template <bool SEC>
 __global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_b(DIWaveArgs w, uint32_t* queue_out, uint32_t* count_out) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
-    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly);
     bool traced = false;
     uint32_t slot = 0, hits = 0;
     if (inside) {
@@ -502,7 +507,7 @@ __global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_b(DIWaveArgs w,
 __global__ void __launch_bounds__(128) k_di_stage_c(DIWaveArgs w, uint32_t* queue_out, uint32_t* count_out) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
-    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly);
     bool traced = false;
     uint32_t slot = 0, hits = 0;
     if (inside) {
@@ -531,7 +536,7 @@ __global__ void __launch_bounds__(128) k_di_stage_c(DIWaveArgs w, uint32_t* queu
 __global__ void __launch_bounds__(128) k_di_stage_d(DIWaveArgs w, uint32_t final_ray_was_queued) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const uint32_t slot = ly * a.width + lx;
     const rt2_gconst& g = *a.g;
     const rt2_restirdi_params& di = g.restir_di;
@@ -576,7 +581,7 @@ __global__ void __launch_bounds__(128) k_di_stage_d(DIWaveArgs w, uint32_t final
 // 48-byte secondary G-buffer record and the 32-byte GI reservoir move as 16-byte words.
 // ------------------------------------------------------------------------------------------------
 struct GIArgs {
-    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame;
+    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame; BandRef band;
     GBufferRefs gb;
     LightRefs li;
     uint4* secondary;        // rt2_secondary_gbuffer_data: 3 x uint4 per entry
@@ -595,7 +600,7 @@ __global__ void __launch_bounds__(128) k_brdf_rays(GIArgs a) {
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
     __syncthreads();
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
     uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
     const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
@@ -683,7 +688,7 @@ __global__ void __launch_bounds__(128) k_shade_secondary(GIArgs a) {
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
     __syncthreads();
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
     uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
     uint32_t rays = 0, hits = 0;
@@ -766,7 +771,7 @@ __device__ __forceinline__ float gi_mis_weight(const SplitBrdf& rough, const Spl
 #endif
 __global__ void __launch_bounds__(128, RT2_K8_BLOCKS) k_gi_final_shading(GIArgs a) {
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
     uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
     uint32_t rays = 0, hits = 0;
@@ -833,7 +838,7 @@ struct GIWaveArgs {
 __global__ void __launch_bounds__(128) k_brdf_rays_gen(GIWaveArgs w) {
     const GIArgs& a = w.gi;
     uint32_t lx, ly;
-    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly);
     bool traced = false;
     uint32_t slot = 0;
     if (inside) {
@@ -894,7 +899,7 @@ __global__ void __launch_bounds__(128) k_brdf_rays_shade(GIWaveArgs w) {
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
     __syncthreads();
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const uint32_t slot = ly * a.width + lx;
     const uint32_t flags = w.st_misc[slot].x;
     uint32_t hits = 0;
@@ -953,7 +958,7 @@ __global__ void __launch_bounds__(128) k_brdf_rays_shade(GIWaveArgs w) {
 __global__ void __launch_bounds__(128) k_shade_secondary_gen(GIWaveArgs w) {
     const GIArgs& a = w.gi;
     uint32_t lx, ly;
-    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly);
+    const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly);
     uint32_t slot = 0;
     if (inside) {
         slot = ly * a.width + lx;
@@ -977,7 +982,7 @@ __global__ void __launch_bounds__(128) k_shade_secondary_shade(GIWaveArgs w) {
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x]; lut[threadIdx.x + 128] = a.sc.srgb_lut[threadIdx.x + 128];
     __syncthreads();
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const uint32_t slot = ly * a.width + lx;
     const rt2_gconst& g = *a.g;
     uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
@@ -1023,7 +1028,7 @@ __global__ void __launch_bounds__(128) k_shade_secondary_shade(GIWaveArgs w) {
 // (visibility from the ray-queue kernel), firefly clamp, initial GI reservoir, MIS radiance hand-over.
 __global__ void __launch_bounds__(128) k_shade_secondary_stage_d(DIWaveArgs w, GIArgs a) {
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const uint32_t slot = ly * a.width + lx;
     const rt2_gconst& g = *a.g;
     const rt2_restirdi_params& di = g.restir_di;
@@ -1090,7 +1095,7 @@ __global__ void __launch_bounds__(128) k_shade_secondary_stage_d(DIWaveArgs w, G
 // writes is never the page it gathers from (checked on the host), so stream order is the only dependency.
 // ------------------------------------------------------------------------------------------------
 struct GIResampleArgs {
-    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame;
+    SceneRefs sc; const rt2_gconst* g; uint32_t width, height, frame; BandRef band;
     GBufferRefs gb, gb_prev;
     const float4* motion;
     const char2* neighbor_offsets;     // signed byte pairs, SNORM8 (SURVEY Q11 pin)
@@ -1100,7 +1105,7 @@ struct GIResampleArgs {
 
 __global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_temporal(GIResampleArgs a) {
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
     const rt2_restirgi_params& gi = g.restir_gi;
     uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
@@ -1202,7 +1207,7 @@ __device__ __forceinline__ void spatial_offset(const char2* table, int sample_id
 
 __global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_spatial(GIResampleArgs a) {
     uint32_t lx, ly;
-    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.height, &lx, &ly)) return;
+    if (!tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly)) return;
     const rt2_gconst& g = *a.g;
     const rt2_restirgi_params& gi = g.restir_gi;
     uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
@@ -1278,8 +1283,14 @@ __global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_spatial(GIResampleA
 // ------------------------------------------------------------------------------------------------
 int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     if (!ctx->scene.accel_built) return fail(ctx, RT2_E_STATE, "no acceleration structure: call rt2_upload_scene + rt2_build_accel first");
-    if (lp.band_world > 1u) return fail(ctx, RT2_E_INVALID, "row-band sharding is implemented for the reference path tracer only");
     const rt2_gconst& g = ctx->gconst;
+    if (lp.band_world > 1u) {
+        if (lp.band_rows == 0u || lp.band_rank >= lp.band_world) return fail(ctx, RT2_E_INVALID, "bad band parameters");
+        // K3 / K9 / K4 / K5 / K8 are per-pixel independent and shard by rows with no exchange; K6 / K7 read their
+        // neighbours' G-buffer and reservoirs across band edges and would need a halo exchange between the ranks
+        if (g.enable_restir_gi == 1u && (g.enable_temporal_resampling == 1u || g.enable_spatial_resampling == 1u))
+            return fail(ctx, RT2_E_INVALID, "GI temporal / spatial resampling reads neighbouring rows: not available with row-band sharding (no halo exchange)");
+    }
     int rc = restir_ensure_resources(ctx); if (rc) return rc;
     FrameBuffers& f = ctx->fb;
     // counters: [0..1] rays, [2..3] hits
@@ -1292,9 +1303,16 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     unsigned long long* stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
     const uint32_t cur = frame & 1u;                   // ping-pong, src/light_passes.rs:565-577
     ctx->last_gbuffer_index = cur;
-    const uint32_t tiles_x = (f.width + 7) / 8, tiles_y = (f.height + 3) / 4;
+    BandRef band{lp.band_rows, lp.band_rank, lp.band_world, f.height};
+    if (band.world <= 1u || band.band_rows == 0u) { band.world = 1; band.rank = 0; band.band_rows = f.height; }
+    else {
+        uint32_t rows = 0;
+        for (uint32_t y0 = band.rank * band.band_rows; y0 < f.height; y0 += band.world * band.band_rows) rows += std::min(band.band_rows, f.height - y0);
+        band.local_rows = rows;
+    }
+    const uint32_t tiles_x = (f.width + 7) / 8, tiles_y = (band.local_rows + 3) / 4;
     const uint32_t padded = tiles_x * tiles_y * 32;
-    const uint32_t blocks = (padded + 127) / 128;
+    const uint32_t blocks = std::max(1u, (padded + 127) / 128);
     uint64_t launches = 0;
     auto pitches_ok = [&](const rt2_reservoir_buffer_params& p) {
         return p.reservoir_array_pitch == f.reservoir_array_pitch && p.reservoir_block_row_pitch == f.reservoir_block_row_pitch;
@@ -1354,16 +1372,16 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     }
     // ---- K3
     GBufferArgs ga{};
-    ga.sc = make_scene_refs(ctx); ga.g = ctx->d_gconst; ga.width = f.width; ga.height = f.height;
+    ga.sc = make_scene_refs(ctx); ga.g = ctx->d_gconst; ga.width = f.width; ga.height = f.height; ga.band = band;
     ga.depth = f.gb_depth[cur]; ga.normals = f.gb_normals[cur]; ga.geo_normals = f.gb_geo_normals[cur]; ga.diffuse_albedo = f.gb_diffuse_albedo[cur];
     ga.specular_rough = f.gb_specular_rough[cur]; ga.emissive = f.gb_emissive[cur]; ga.motion = f.motion_vectors; ga.stat_hits = stat_hits;
     k_gbuffer<<<blocks, 128, 0, ctx->stream>>>(ga); launches++;
-    uint64_t static_rays = (uint64_t)f.width * f.height;
+    uint64_t static_rays = (uint64_t)f.width * band.local_rows;      // K3: one primary ray per owned pixel
     const GBufferRefs gbrefs{f.gb_depth[cur], f.gb_normals[cur], f.gb_geo_normals[cur], f.gb_diffuse_albedo[cur], f.gb_specular_rough[cur]};
     // ---- K9
     if (g.enable_restir_di == 1u) {
         DIArgs da{};
-        da.sc = ga.sc; da.g = ctx->d_gconst; da.width = f.width; da.height = f.height; da.frame = frame;
+        da.sc = ga.sc; da.g = ctx->d_gconst; da.width = f.width; da.height = f.height; da.frame = frame; da.band = band;
         da.gb = gbrefs; da.li = lrefs;
         da.reservoirs = f.di_reservoirs; da.diffuse = f.diffuse_f16; da.specular = f.specular_f16; da.diffuse_f32 = f.diffuse_f32;
         da.stat_rays = stat_rays; da.stat_hits = stat_hits;
@@ -1394,7 +1412,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     // ---- K4 -> K5 -> K8 (stream order is the ALL_COMMANDS barrier of src/light_passes.rs:621-659)
     if (g.enable_restir_gi == 1u) {
         GIArgs gi{};
-        gi.sc = ga.sc; gi.g = ctx->d_gconst; gi.width = f.width; gi.height = f.height; gi.frame = frame;
+        gi.sc = ga.sc; gi.g = ctx->d_gconst; gi.width = f.width; gi.height = f.height; gi.frame = frame; gi.band = band;
         gi.gb = gbrefs; gi.li = lrefs;
         gi.secondary = f.secondary_gbuffer; gi.reservoirs = f.gi_reservoirs;
         gi.diffuse = f.diffuse_f16; gi.specular = f.specular_f16; gi.diffuse_f32 = f.diffuse_f32;
@@ -1412,7 +1430,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
             k_brdf_rays_shade<<<blocks, 128, 0, ctx->stream>>>(wa); launches += 3;
             if (g.enable_restir_di == 1u) {                            // K5 samples the light list at the secondary surface: the K9 stages, pointed at SecondaryGBufferData
                 DIWaveArgs dw{};
-                dw.di.sc = gi.sc; dw.di.g = gi.g; dw.di.width = gi.width; dw.di.height = gi.height; dw.di.frame = gi.frame; dw.di.gb = gi.gb; dw.di.li = gi.li;
+                dw.di.sc = gi.sc; dw.di.g = gi.g; dw.di.width = gi.width; dw.di.height = gi.height; dw.di.frame = gi.frame; dw.di.band = band; dw.di.gb = gi.gb; dw.di.li = gi.li;
                 dw.di.stat_rays = stat_rays; dw.di.stat_hits = stat_hits;
                 dw.st_ray0 = f.st_ray0; dw.st_ray1 = f.st_ray1; dw.st_hit = f.st_hit; dw.st_hit_inst = f.st_hit_inst;
                 dw.state = f.di_state; dw.plane = (uint32_t)((size_t)f.width * f.height); dw.secondary = f.secondary_gbuffer;
@@ -1435,7 +1453,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         if (g.enable_temporal_resampling == 1u || g.enable_spatial_resampling == 1u) {
             const uint32_t prev = cur ^ 1u;
             GIResampleArgs ra{};
-            ra.sc = ga.sc; ra.g = ctx->d_gconst; ra.width = f.width; ra.height = f.height; ra.frame = frame;
+            ra.sc = ga.sc; ra.g = ctx->d_gconst; ra.width = f.width; ra.height = f.height; ra.frame = frame; ra.band = band;
             ra.gb = gbrefs;
             ra.gb_prev = GBufferRefs{f.gb_depth[prev], f.gb_normals[prev], f.gb_geo_normals[prev], f.gb_diffuse_albedo[prev], f.gb_specular_rough[prev]};
             ra.motion = f.motion_vectors; ra.neighbor_offsets = f.neighbor_offsets; ra.reservoirs = f.gi_reservoirs;

@@ -197,3 +197,67 @@ def test_gi_resampling_rejects_aliased_pages():
     with pytest.raises(rt.Rt2Error):
         lp.execute(1)
     ctx.close()
+
+
+# ---- row-band sharding of the per-pixel ReSTIR passes (K3 / K9 / K4 / K5 / K8 shard with no exchange) ---------------
+@pytest.mark.parametrize("kind,scale,mode", [
+    (rt.SCENE_HALL, 0.125, dict(gi=1, di=0)),                # the default frame K3 -> K4 -> K5 -> K8
+    (rt.SCENE_HALL, 0.125, dict(gi=0, di=1)),                # K3 -> K9
+    (rt.SCENE_CORNELL, 1.0, dict(gi=1, di=1)),               # K9 + the DI branch inside K5
+    (rt.SCENE_INSTANCED, 0.05, dict(gi=1, di=0, env=1)),     # flattened instancing + sky
+])
+def test_restir_frames_shard_by_row_bands_bit_identically(kind, scale, mode):
+    """Every rank renders its interleaved bands into the full-frame buffers of one context: after all ranks ran, the lighting
+    images, G-buffer and packed reservoirs equal the whole-frame render bit for bit, and the ray counts add up."""
+    w, h = 200, 150
+    sc = rt.Scene(kind, scale, 32, 0)
+    cam = sc.camera(w / h)
+    d = sc.desc.contents
+    g = rt.default_gconst(cam, w, h, sc.num_lights, env_size=(d.sky_width, d.sky_height))
+    g.refrence_mode = 0; g.enable_restir_gi = mode["gi"]; g.enable_restir_di = mode["di"]; g.environment = mode.get("env", 0)
+    isp = g.restir_di.initial_sampling_params
+    isp.num_primary_local_light_samples = 4; isp.num_primary_brdf_samples = 1; isp.enable_initial_visibility = 1
+    g.restir_di.shading_params.enable_final_visibility = 1
+    bufs = [rt.BUF_DIFFUSE_F16, rt.BUF_SPECULAR_F16, rt.BUF_GBUFFER_DEPTH, rt.BUF_GBUFFER_NORMALS, rt.BUF_GBUFFER_DIFFUSE_ALBEDO, rt.BUF_GBUFFER_EMISSIVE]
+    if mode["gi"]:
+        bufs += [rt.BUF_GI_RESERVOIRS, rt.BUF_SECONDARY_GBUFFER]
+    if mode["di"]:
+        bufs += [rt.BUF_DI_RESERVOIRS]
+
+    def run(world, band_rows):
+        ctx = rt.Renderer(0)
+        rt.Model.from_scene(ctx, sc)
+        lp = rt.LightPasses(ctx, w, h)
+        rt.PrepareLightsTasks(ctx).execute()
+        rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+        rays = 0
+        for frame in (1, 2):
+            rt.advance_frame(g, cam, w, h, frame)
+            lp.update_uniform(g)
+            for rank in range(world):
+                lp.execute(frame, rt.LaunchParams(band_rows=band_rows if world > 1 else 0, band_rank=rank, band_world=world))
+                rays += ctx.stats().rays_traced
+        out = {b: ctx.read(b, np.uint8).copy() for b in bufs}
+        ctx.close()
+        return out, rays
+
+    want, rays = run(1, 0)
+    for world, band_rows in ((2, 8), (3, 16), (5, 4)):
+        got, r = run(world, band_rows)
+        assert r == rays, (world, r, rays)
+        for b in bufs:
+            assert np.array_equal(got[b], want[b]), f"buffer {b} differs with {world} ranks of {band_rows}-row bands"
+
+
+def test_resampling_is_rejected_under_row_band_sharding():
+    sc = rt.Scene(rt.SCENE_CORNELL)
+    g = rt.default_gconst(sc.camera(1.0), 64, 64, sc.num_lights)
+    g.refrence_mode = 0; g.enable_restir_gi = 1; g.enable_spatial_resampling = 1
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, 64, 64)
+    lp.update_uniform(g)
+    lp.execute(1)                                   # whole frame: fine
+    with pytest.raises(rt.Rt2Error, match="halo"):
+        lp.execute(1, rt.LaunchParams(band_rows=8, band_rank=0, band_world=2))
+    ctx.close()
