@@ -22,8 +22,8 @@ raytracer2_b200/librt2cuda.so: $(CU_OBJS)
 	$(NVCC) -shared -o $@ $(CU_OBJS) $(LDLIBS_CUDA) -ldl
 	@cat $(sort $(wildcard $(OBJDIR)/*.ptxas.log)) > build_ptxas.log
 
-raytracer2_b200/librt2host.so: raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp raytracer2_b200/host/rt2_host.h raytracer2_b200/host/rt2_ingest.h include/rt2_abi.h include/rt2_gconst.h
-	$(CXX) -O2 -std=c++17 -fPIC -Wall -Wextra -shared -o $@ raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp -lz
+raytracer2_b200/librt2host.so: raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp raytracer2_b200/host/rt2_ingest_codecs.cpp raytracer2_b200/host/rt2_host.h raytracer2_b200/host/rt2_ingest.h include/rt2_abi.h include/rt2_gconst.h
+	$(CXX) -O2 -std=c++17 -fPIC -Wall -Wextra -shared -o $@ raytracer2_b200/host/rt2_host.cpp raytracer2_b200/host/rt2_ingest.cpp raytracer2_b200/host/rt2_ingest_codecs.cpp -lz
 
 oracle:
 	$(MAKE) -C oracle

@@ -255,6 +255,7 @@ HOST_SYMBOLS = {
     "rt2h_scene_generate": (VP, [C.c_int, f32, u32, u64]),
     "rt2h_scene_load_gltf": (VP, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
     "rt2h_load_exr": (VP, [C.c_char_p, C.POINTER(u32), C.POINTER(u32), C.c_char_p, C.c_size_t]),
+    "rt2h_decode_image": (VP, [C.c_char_p, C.c_size_t, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), C.c_char_p, C.c_size_t]),
     "rt2h_free": (None, [VP]),
     "rt2h_scene_destroy": (None, [VP]),
     "rt2h_scene_desc": (C.POINTER(SceneDesc), [VP]),

@@ -670,6 +670,19 @@ float* rt2h_load_exr(const char* path, uint32_t* width, uint32_t* height, char* 
     if (height) *height = h;
     return out;
 }
+uint8_t* rt2h_decode_image(const uint8_t* data, size_t size, uint32_t* width, uint32_t* height, uint32_t* channels, char* err, size_t err_len) {
+    std::vector<uint8_t> px; uint32_t w = 0, h = 0, ch = 0; std::string e;
+    if (!data || size < 4) { set_err(err, err_len, "no image data"); return nullptr; }
+    const bool jpeg = data[0] == 0xFF && data[1] == 0xD8;
+    if (!(jpeg ? rt2ingest::decode_jpeg(data, size, px, w, h, ch, e) : rt2ingest::decode_png(data, size, px, w, h, ch, e))) { set_err(err, err_len, e); return nullptr; }
+    uint8_t* out = (uint8_t*)std::malloc(px.size() ? px.size() : 1);
+    if (!out) { set_err(err, err_len, "out of memory"); return nullptr; }
+    std::memcpy(out, px.data(), px.size());
+    if (width) *width = w;
+    if (height) *height = h;
+    if (channels) *channels = ch;
+    return out;
+}
 void rt2h_free(void* p) { std::free(p); }
 void rt2h_scene_destroy(rt2h_scene* s) { delete s; }
 const rt2_scene_desc* rt2h_scene_desc(const rt2h_scene* s) { return s ? &s->desc : nullptr; }

@@ -69,6 +69,9 @@ rt2h_scene* rt2h_scene_generate(int kind, float scale, uint32_t texture_size, ui
 rt2h_scene* rt2h_scene_load_gltf(const char* gltf_path, const char* sky_exr_path, char* err, size_t err_len);
 /* the EXR reader alone: RGBA32F rows, top to bottom; caller frees with rt2h_free */
 float*      rt2h_load_exr(const char* path, uint32_t* width, uint32_t* height, char* err, size_t err_len);
+/* the image decoders alone (PNG or baseline JPEG, by magic bytes): `channels` x 8-bit samples as the `image` crate reports them
+ * (src/gltf/image.rs:57-109 expands them to RGBA8); caller frees with rt2h_free */
+uint8_t*    rt2h_decode_image(const uint8_t* data, size_t size, uint32_t* width, uint32_t* height, uint32_t* channels, char* err, size_t err_len);
 void        rt2h_free(void* p);
 void        rt2h_scene_destroy(rt2h_scene* s);
 const rt2_scene_desc* rt2h_scene_desc(const rt2h_scene* s);

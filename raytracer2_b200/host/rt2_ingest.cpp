@@ -510,8 +510,8 @@ bool load_gltf(const std::string& path, GltfModel& out, std::string& err) {
             bytes.assign(d.buffers[(size_t)buf].begin() + (long)off, d.buffers[(size_t)buf].begin() + (long)(off + len));
         }
         std::vector<uint8_t> px; uint32_t w = 0, h = 0, ch = 0;
-        if (bytes.size() >= 3 && bytes[0] == 0xFF && bytes[1] == 0xD8) { err = "glTF: JPEG images are not supported by this reader (PNG only)"; return false; }
-        if (!decode_png(bytes.data(), bytes.size(), px, w, h, ch, err)) return false;
+        if (bytes.size() >= 3 && bytes[0] == 0xFF && bytes[1] == 0xD8) { if (!decode_jpeg(bytes.data(), bytes.size(), px, w, h, ch, err)) return false; }
+        else if (!decode_png(bytes.data(), bytes.size(), px, w, h, ch, err)) return false;
         out.image_rgba8.emplace_back();
         expand_to_rgba8(px, ch, out.image_rgba8.back());
         out.image_w.push_back(w); out.image_h.push_back(h);
@@ -613,7 +613,8 @@ bool load_exr(const std::string& path, std::vector<float>& rgba, uint32_t& w, ui
     switch (compression) {
         case 0: case 1: case 2: lines_per_block = 1; break;     // NONE, RLE, ZIPS
         case 3: lines_per_block = 16; break;                    // ZIP
-        default: err = "EXR: compression " + std::to_string(compression) + " is not supported (NONE, RLE, ZIPS, ZIP only)"; return false;
+        case 4: lines_per_block = 32; break;                    // PIZ (the OpenEXR default for photographs)
+        default: err = "EXR: compression " + std::to_string(compression) + " is not supported (NONE, RLE, ZIPS, ZIP, PIZ only; not PXR24 / B44 / DWA)"; return false;
     }
     w = (uint32_t)(dw[2] - dw[0] + 1); h = (uint32_t)(dw[3] - dw[1] + 1);
     if ((uint64_t)w * h > (1ull << 28)) { err = "EXR: image too large"; return false; }
@@ -646,6 +647,11 @@ bool load_exr(const std::string& path, std::vector<float>& rgba, uint32_t& w, ui
         if ((size_t)size == expected) block.assign(src, src + size);       // stored raw (also when compression did not shrink the block)
         else if (compression == 2 || compression == 3) { if (!zlib_inflate(src, (size_t)size, block, expected, err)) return false; exr_unpredict_reorder(block, tmp); }
         else if (compression == 1) { if (!exr_rle_decode(src, (size_t)size, block, expected)) { err = "EXR: bad RLE block"; return false; } exr_unpredict_reorder(block, tmp); }
+        else if (compression == 4) {
+            std::vector<int> words; for (const auto& c : channels) words.push_back(c.type == 1 ? 1 : 2);
+            if (!exr_piz_decode(src, (size_t)size, words, w, rows, block, err)) return false;
+            if (block.size() != expected) { err = "EXR: PIZ block decodes to the wrong size"; return false; }
+        }
         else { err = "EXR: block size mismatch"; return false; }
         const uint8_t* p = block.data();
         for (uint32_t r = 0; r < rows; r++) {
