@@ -246,10 +246,10 @@ def test_exr_sky_box_reader(tmp_path, compression, dtype, alpha):
 def test_exr_rejections_and_scene_with_sky(tmp_path):
     ch = {n: np.full((8, 8), v, np.float16) for n, v in (("R", 1.0), ("G", 2.0), ("B", 3.0))}
     good = write_exr(ch, 3)
-    bad = bytearray(good); k = bad.index(b"compression\0compression\0") + len(b"compression\0compression\0") + 4; bad[k] = 4     # PIZ
-    (tmp_path / "piz.exr").write_bytes(bytes(bad))
-    with pytest.raises(rt.Rt2Error, match="compression 4"):
-        rt.load_exr(str(tmp_path / "piz.exr"))
+    bad = bytearray(good); k = bad.index(b"compression\0compression\0") + len(b"compression\0compression\0") + 4; bad[k] = 5     # PXR24 (PIZ = 4 is read since round 2: test_ingest_independent_cpu.py)
+    (tmp_path / "pxr24.exr").write_bytes(bytes(bad))
+    with pytest.raises(rt.Rt2Error, match="compression 5"):
+        rt.load_exr(str(tmp_path / "pxr24.exr"))
     (tmp_path / "junk.exr").write_bytes(b"not an exr file at all")
     with pytest.raises(rt.Rt2Error, match="OpenEXR"):
         rt.load_exr(str(tmp_path / "junk.exr"))
