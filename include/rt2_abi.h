@@ -203,7 +203,7 @@ enum rt2_buffer {
     RT2_BUF_DIFFUSE_F32   = 2,  /* fp32 shadow of DiffuseLighting (rgba32f, 16 B/px), SURVEY §7.3#7 */
     RT2_BUF_HIT_IDS       = 3,  /* rt2_hit_record per pixel                                        */
     RT2_BUF_OUTPUT_RGBA8  = 4,  /* post-process output, 4 B/px (replaces the swapchain image)      */
-    RT2_BUF_LIGHT_INFO    = 5,  /* rt2_light_info x nLights (t_LightDataBuffer)                    */
+    RT2_BUF_LIGHT_INFO    = 5,  /* rt2_light_info x nLights (t_LightDataBuffer); with a sky: + a zero record and the environment light at nLights + 1 (src/main.rs:383) */
     RT2_BUF_GEOM_TO_LIGHT = 6,  /* uint32 x nGeometries (GeometryInstanceToLight)                  */
     RT2_BUF_LIGHT_TASKS   = 7,  /* rt2_prepare_lights_task x nTasks                                */
     RT2_BUF_LOCAL_PDF_MIP0 = 16, /* +k = mip k of the local-light PDF texture (r32f)               */

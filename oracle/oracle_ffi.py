@@ -19,6 +19,10 @@ VP = C.c_void_p
 _lib = None
 
 
+class OracleError(AssertionError):
+    """a negative return code of an orc_* call (args[0]); an AssertionError, as the wrappers' asserts raise"""
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -61,7 +65,7 @@ def lib():
         L.orc_tonemap.restype = u32; L.orc_tonemap.argtypes = [VP]
         L.orc_gbuffer.restype = C.c_int; L.orc_gbuffer.argtypes = [VP, VP, u32, u32, u32, C.c_int] + [VP] * 7 + [C.POINTER(u64)]
         L.orc_di_fused_resampling.restype = C.c_int
-        L.orc_di_fused_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int] + [VP] * 5 + [VP, u32, VP, VP, u32, u32, u32, VP, VP, VP, C.POINTER(u64), VP, VP, u64]
+        L.orc_di_fused_resampling.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int] + [VP] * 5 + [VP, u32, VP, VP, u32, u32, u32, VP, VP, VP, C.POINTER(u64), VP, VP, u64, VP, u32, u32, u32]
         L.orc_reservoir_position_to_pointer.restype = u32; L.orc_reservoir_position_to_pointer.argtypes = [u32] * 5
         L.orc_brdf_rays.restype = C.c_int; L.orc_brdf_rays.argtypes = [VP, VP, u32, u32, u32, u32, C.c_int, VP, VP, VP, VP, C.POINTER(u64)]
         L.orc_shade_secondary_surfaces.restype = C.c_int
@@ -107,7 +111,7 @@ class GBufferIn(C.Structure):   # orc_gbuffer_in
 
 class LightIn(C.Structure):     # orc_light_in
     _fields_ = [("lights", VP), ("num_lights", u32), ("geom_to_light", VP), ("pdf_packed", VP), ("pdf_w", u32), ("pdf_h", u32), ("pdf_mips", u32),
-                ("ris", VP), ("ris_light_data", VP), ("ris_entries", u64)]
+                ("ris", VP), ("ris_light_data", VP), ("ris_entries", u64), ("env_pdf_packed", VP), ("env_w", u32), ("env_h", u32), ("env_mips", u32)]
 
 
 def presample(gconst, frame, which, pdf_packed, w, h, mips, lights=None, ris=None, ris_light_data=None, entries=2 * 128 * 1024):
@@ -174,19 +178,22 @@ class OracleScene:
         return d16, s16, d32, rays.value
 
     # ---- K10 / K12 / K13 ---------------------------------------------------------------------------------
-    def prepare_lights(self, pdf_w=0, pdf_h=0):
-        """returns (tasks[n,4] u32, geom_to_light u32, lights[n,12] u32, pdf_mip0 f32 or None)"""
+    def prepare_lights(self, pdf_w=0, pdf_h=0, env=False):
+        """returns (tasks[n,4] u32, geom_to_light u32, lights[n,12] u32, pdf_mip0 f32 or None).  env: size the light buffer for
+        lights + 2 records, so that the environment light lands at index lights + 1 (scenes with a sky; SURVEY Q7 pinned to intent)."""
         L = self._L
         nt, nl = u32(0), u32(0)
         assert L.orc_prepare_lights(self._p, None, C.byref(nt), None, None, 0, C.byref(nl), None, 0, 0) == 0
         ng = self.num_geometries
         tasks = np.zeros((max(ng, 1), 4), np.uint32); g2l = np.zeros(max(ng, 1), np.uint32)
-        lights = np.zeros((max(nl.value, 1), 12), np.uint32)
+        lights = np.zeros((max(nl.value, 1) + (2 if env else 0), 12), np.uint32)
+        if env:
+            lights = lights[:nl.value + 2]
         pdf = np.zeros((pdf_h, pdf_w), np.float32) if pdf_w and pdf_h else None
         rc = L.orc_prepare_lights(self._p, tasks.ctypes.data_as(VP), C.byref(nt), g2l.ctypes.data_as(VP), lights.ctypes.data_as(VP),
                                   lights.shape[0], C.byref(nl), pdf.ctypes.data_as(VP) if pdf is not None else None, pdf_w, pdf_h)
         assert rc == 0
-        return tasks[:nt.value], g2l[:ng], lights[:nl.value], pdf
+        return tasks[:nt.value], g2l[:ng], lights[:nl.value + (2 if env else 0)], pdf
 
     def generate_mips(self, which, packed, w, h, mips):
         assert packed.flags["C_CONTIGUOUS"]
@@ -214,8 +221,9 @@ class OracleScene:
         return gb
 
     def di_fused_resampling(self, gconst, frame, w, h, gb, lights, geom_to_light, pdf_packed, pdf_w, pdf_h, pdf_mips, array_pitch,
-                            diffuse_f16=None, specular_f16=None, flags=0, threads=0, ris=None, ris_light_data=None):
-        """K9.  ris / ris_light_data: K11's outputs (presample()), read with flags & ORC_PRESAMPLING and local_light_sampling_mode 1."""
+                            diffuse_f16=None, specular_f16=None, flags=0, threads=0, ris=None, ris_light_data=None, env_pdf=None, env_dims=(0, 0, 0)):
+        """K9.  ris / ris_light_data: K11's outputs (presample()), read with flags & ORC_PRESAMPLING and local_light_sampling_mode 1.
+        env_pdf / env_dims = (w, h, mips): K12's r16f environment pyramid (uint16, packed), read with ORC_PRESAMPLING + an environment light."""
         res = np.zeros((array_pitch * 2, 6), np.uint32)
         d16 = np.zeros((h, w, 4), np.uint16) if diffuse_f16 is None else diffuse_f16
         s16 = np.zeros((h, w, 4), np.uint16) if specular_f16 is None else specular_f16
@@ -226,8 +234,10 @@ class OracleScene:
                                              lights.ctypes.data_as(VP), len(lights), geom_to_light.ctypes.data_as(VP), pdf_packed.ctypes.data_as(VP), pdf_w, pdf_h, pdf_mips,
                                              res.ctypes.data_as(VP), d16.ctypes.data_as(VP), s16.ctypes.data_as(VP), C.byref(rays),
                                              ris.ctypes.data_as(VP) if ris is not None else None,
-                                             ris_light_data.ctypes.data_as(VP) if ris_light_data is not None else None, u64(len(ris) if ris is not None else 0))
-        assert rc == 0, rc
+                                             ris_light_data.ctypes.data_as(VP) if ris_light_data is not None else None, u64(len(ris) if ris is not None else 0),
+                                             env_pdf.ctypes.data_as(VP) if env_pdf is not None else None, *env_dims)
+        if rc != 0:
+            raise OracleError(rc)
         return res, d16, s16, rays.value
 
     # ---- the ReSTIR-GI chain K4 -> K5 -> K8 ----------------------------------------------------------------
@@ -237,13 +247,13 @@ class OracleScene:
         return GBufferIn(*[a.ctypes.data_as(VP) for a in keep]), keep
 
     @staticmethod
-    def _light_in(lights, geom_to_light, pdf_packed, pdf_w, pdf_h, pdf_mips, ris=None, ris_light_data=None):
+    def _light_in(lights, geom_to_light, pdf_packed, pdf_w, pdf_h, pdf_mips, ris=None, ris_light_data=None, env_pdf=None, env_dims=(0, 0, 0)):
         if lights is None:
             return None, []
-        keep = [np.ascontiguousarray(lights), np.ascontiguousarray(geom_to_light), np.ascontiguousarray(pdf_packed, np.float32), ris, ris_light_data]
+        keep = [np.ascontiguousarray(lights), np.ascontiguousarray(geom_to_light), np.ascontiguousarray(pdf_packed, np.float32), ris, ris_light_data, env_pdf]
         return LightIn(keep[0].ctypes.data_as(VP), len(keep[0]), keep[1].ctypes.data_as(VP), keep[2].ctypes.data_as(VP), pdf_w, pdf_h, pdf_mips,
                        ris.ctypes.data_as(VP) if ris is not None else None, ris_light_data.ctypes.data_as(VP) if ris_light_data is not None else None,
-                       len(ris) if ris is not None else 0), keep
+                       len(ris) if ris is not None else 0, env_pdf.ctypes.data_as(VP) if env_pdf is not None else None, *env_dims), keep
 
     def brdf_rays(self, gconst, frame, w, h, gb, secondary, diffuse_f16, specular_f16, flags=0, threads=0):
         """K4.  secondary: uint32 [arrayPitch, 12] (in/out); lighting images rgba16f as uint16 [h, w, 4] (in/out).  Returns rays."""
@@ -255,10 +265,11 @@ class OracleScene:
         return rays.value
 
     def shade_secondary_surfaces(self, gconst, frame, w, h, gb, secondary, gi_reservoirs, diffuse_f16, specular_f16,
-                                 lights=None, geom_to_light=None, pdf_packed=None, pdf_dims=(0, 0, 0), flags=0, threads=0, ris=None, ris_light_data=None):
+                                 lights=None, geom_to_light=None, pdf_packed=None, pdf_dims=(0, 0, 0), flags=0, threads=0, ris=None, ris_light_data=None,
+                                 env_pdf=None, env_dims=(0, 0, 0)):
         """K5.  gi_reservoirs: uint32 [arrayPitch * 2, 8] (in/out)."""
         gin, keep = self._gb_in(gb)
-        lin, keep2 = self._light_in(lights, geom_to_light, pdf_packed, *pdf_dims, ris=ris, ris_light_data=ris_light_data)
+        lin, keep2 = self._light_in(lights, geom_to_light, pdf_packed, *pdf_dims, ris=ris, ris_light_data=ris_light_data, env_pdf=env_pdf, env_dims=env_dims)
         rays = u64(0)
         rc = self._L.orc_shade_secondary_surfaces(self._p, C.cast(C.byref(gconst), VP), frame, w, h, flags, threads, C.byref(gin),
                                                   C.byref(lin) if lin is not None else None, secondary.ctypes.data_as(VP), gi_reservoirs.ctypes.data_as(VP),
@@ -306,7 +317,7 @@ class OracleScene:
         r4 = self.brdf_rays(gconst, frame, w, h, gb, st["secondary"], st["diffuse"], st["specular"], flags, threads)
         r5 = self.shade_secondary_surfaces(gconst, frame, w, h, gb, st["secondary"], st["gi_reservoirs"], st["diffuse"], st["specular"],
                                            li.get("lights"), li.get("geom_to_light"), li.get("pdf_packed"), li.get("pdf_dims", (0, 0, 0)), flags, threads,
-                                           li.get("ris"), li.get("ris_light_data"))
+                                           li.get("ris"), li.get("ris_light_data"), li.get("env_pdf"), li.get("env_dims", (0, 0, 0)))
         r6 = r7 = 0
         if gconst.enable_temporal_resampling == 1:
             r6 = self.gi_temporal_resampling(gconst, frame, w, h, gb, gb_prev, motion, st["gi_reservoirs"], flags, threads)

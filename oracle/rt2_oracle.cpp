@@ -589,12 +589,15 @@ static void GetGeometryFromHit(const orc_scene& s, const Hit& h, V3* normal, V3*
 // sampler: LINEAR, CLAMP_TO_BORDER black, normalised coords (src/main.rs:123-138 builds the
 // unnormalised one for the mip pass; the SkyBox binding of the lighting passes uses the default).
 // ------------------------------------------------------------------------------------------------
-static V3 GetEnvironmentRadiance(const orc_scene& s, const GConstView& g, V3 dir) {
-    if (g.environment != 1u || s.sky.empty()) return v3(0, 0, 0);
+// directionToEquirectUV, Helpers.glsl:242-248
+static void directionToEquirectUV(V3 dir, float* u, float* v) {
     const float PI_ = 3.1415926f;
     // transcendental pin: binary64, rounded once (GLSL leaves atan / asin precision to the implementation)
-    float u = 0.5f + (float)std::atan2((double)dir.z, (double)dir.x) / (2.0f * PI_);
-    float v = 0.5f - (float)std::asin((double)dir.y) / PI_;
+    *u = 0.5f + (float)std::atan2((double)dir.z, (double)dir.x) / (2.0f * PI_);
+    *v = 0.5f - (float)std::asin((double)dir.y) / PI_;
+}
+// texture(SkyBox, uv).rgb / textureLod(SkyBox, uv, 0).rgb (ray-generation shaders have no derivatives: LOD 0 either way)
+static V3 sample_sky(const orc_scene& s, float u, float v) {
     const int W = (int)s.sky_w, H = (int)s.sky_h;
     float x = u * (float)W - 0.5f, y = v * (float)H - 0.5f;
     float fx = std::floor(x), fy = std::floor(y);
@@ -609,6 +612,11 @@ static V3 GetEnvironmentRadiance(const orc_scene& s, const GConstView& g, V3 dir
     float ia = 1.0f - a, ib = 1.0f - b;
     V3 top = t00 * ia + t10 * a, bot = t01 * ia + t11 * a;
     return top * ib + bot * b;
+}
+static V3 GetEnvironmentRadiance(const orc_scene& s, const GConstView& g, V3 dir) {
+    if (g.environment != 1u || s.sky.empty()) return v3(0, 0, 0);
+    float u, v; directionToEquirectUV(dir, &u, &v);
+    return sample_sky(s, u, v);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -65,6 +65,9 @@ void     orc_sample_texture(const orc_scene* s, uint32_t texture_index, float u,
 int orc_prepare_lights(const orc_scene* s, rt2_prepare_lights_task* tasks, uint32_t* num_tasks, uint32_t* geom_to_light,
                        rt2_light_info* lights, uint32_t light_capacity, uint32_t* num_lights,
                        float* pdf_mip0, uint32_t pdf_w, uint32_t pdf_h);
+/* The environment light record (PolymorphicLight.glsl:359-424) orc_prepare_lights writes at index num_lights + 1 when
+ * light_capacity >= num_lights + 2 and the scene has a sky (SURVEY Q7 pinned to intent; read only with ORC_PRESAMPLING). */
+void orc_environment_light_info(uint32_t tex_w, uint32_t tex_h, rt2_light_info* out);
 /* ---- K12 mip_pass (src/mip_pass.rs:122-186 + generate_mip_levels/mips.glsl) ----------------------
  * packed = all mips back to back (mip k is max(1,w>>k) x max(1,h>>k)); which 0: r32f local-light
  * PDF (mip 0 is the input), which 1: r16f environment PDF (mip 0 is written from the sky). */
@@ -99,7 +102,8 @@ int orc_di_fused_resampling(const orc_scene* s, const void* gconst, uint32_t fra
                             const uint32_t* gb_specular_rough, const rt2_light_info* lights, uint32_t num_lights, const uint32_t* geom_to_light,
                             const float* pdf_packed, uint32_t pdf_w, uint32_t pdf_h, uint32_t pdf_mips,
                             rt2_packed_di_reservoir* reservoirs, uint16_t* diffuse_f16, uint16_t* specular_f16, uint64_t* rays,
-                            const uint32_t* ris, const uint32_t* ris_light_data, uint64_t ris_entries);
+                            const uint32_t* ris, const uint32_t* ris_light_data, uint64_t ris_entries,
+                            const void* env_pdf_packed, uint32_t env_w, uint32_t env_h, uint32_t env_mips);
 /* RTXDI_ReservoirPositionToPointer (rtxdi/RtxdiHelpers.hlsli:75-88) */
 uint32_t orc_reservoir_position_to_pointer(uint32_t block_row_pitch, uint32_t array_pitch, uint32_t x, uint32_t y, uint32_t array_index);
 
@@ -114,6 +118,7 @@ typedef struct orc_light_in {
     const rt2_light_info* lights; uint32_t num_lights; const uint32_t* geom_to_light;
     const float* pdf_packed; uint32_t pdf_w, pdf_h, pdf_mips;
     const uint32_t* ris; const uint32_t* ris_light_data; uint64_t ris_entries;   /* K11 outputs, read with ORC_PRESAMPLING + POWER_RIS */
+    const void* env_pdf_packed; uint32_t env_w, env_h, env_mips;                  /* K12's r16f environment pyramid (ORC_PRESAMPLING + an environment light) */
 } orc_light_in;
 /* K4 lighting_passes/brdf_rays.rgen:19-195 */
 int orc_brdf_rays(const orc_scene* s, const void* gconst, uint32_t frame, uint32_t width, uint32_t height, uint32_t flags, int threads,

@@ -261,6 +261,7 @@ HOST_SYMBOLS = {
     "rt2h_scene_desc": (C.POINTER(SceneDesc), [VP]),
     "rt2h_scene_camera": (None, [VP, f32, C.POINTER(Camera)]),
     "rt2h_scene_num_lights": (u32, [VP]),
+    "rt2h_scene_add_procedural_sky": (None, [VP, u32]),
     "rt2h_scene_num_triangles": (u64, [VP]),
 }
 

@@ -89,6 +89,11 @@ class Scene:
         self._h.rt2h_scene_camera(self._p, aspect_ratio, C.byref(cam))
         return cam
 
+    def add_sky(self, width: int = 512) -> "Scene":
+        """Attach the procedural sky box (width x width/2) to a scene generated without one; call before uploading."""
+        self._h.rt2h_scene_add_procedural_sky(self._p, width)
+        return self
+
     @property
     def num_lights(self) -> int:
         return self._h.rt2h_scene_num_lights(self._p)

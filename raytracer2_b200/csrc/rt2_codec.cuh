@@ -113,6 +113,29 @@ __device__ __forceinline__ rt2_light_info store_triangle_light(const TriangleLig
     li.color_type_and_flags |= RT2_LIGHT_TRIANGLE << RT2_LIGHT_TYPE_SHIFT;
     return li;
 }
+// EnvironmentLight, :359-424.  The reference names one at index lights + 1 (src/main.rs:381-386) and never writes it;
+// K10 writes this record there (pinned to intent, read only with RT2_LAUNCH_PRESAMPLING): radianceScale 1 through packLightColor,
+// importance sampled, texture = the SkyBox binding, size = the environment PDF texture's.  rotation = 0.25 turns reconciles
+// equirectUVToDirection's azimuth (u + 0.25) * 2pi (Helpers.glsl:336) with the u = 0.5 + atan2(z, x) / 2pi every sky lookup
+// uses (Helpers.glsl:244) — see oracle/rt2_oracle_passes.inc StoreEnvironmentLight.
+#define RT2_LIGHT_ENVIRONMENT 6u
+__device__ __forceinline__ rt2_light_info store_environment_light(uint32_t tex_w, uint32_t tex_h) {
+    rt2_light_info li;
+    li.center[0] = li.center[1] = li.center[2] = 0.f;
+    li.color_type_and_flags = 0u; li.log_radiance = 0u; li.ies_profile_index = 0u; li.primary_axis = 0u;
+    li.cos_cone_angle_and_softness = 0u; li.padding = 0u;
+    const float intensity = 1.0f;                                                              // packLightColor(vec3(1)), :77-93
+    const float lr = saturatef((log2_pinned(intensity) - RT2_LIGHT_MIN_LOG2) / (RT2_LIGHT_MAX_LOG2 - RT2_LIGHT_MIN_LOG2));
+    const uint32_t packed = min((uint32_t)ceilf(lr * 65534.0f) + 1u, 0xffffu);
+    const float unpacked = unpack_light_radiance(packed);
+    li.log_radiance |= packed;
+    li.color_type_and_flags |= pack_r8g8b8(v3(saturatef(1.0f / unpacked), saturatef(1.0f / unpacked), saturatef(1.0f / unpacked)));
+    li.color_type_and_flags |= RT2_LIGHT_ENVIRONMENT << RT2_LIGHT_TYPE_SHIFT;
+    li.direction1 = 0u;                                                                        // textureIndex >= 0
+    li.scalars = (uint32_t)f32_to_f16_bits(0.25f) | (1u << 16);                                // rotation | importanceSampled
+    li.direction2 = (tex_w & 0xffffu) | (tex_h << 16);
+    return li;
+}
 __device__ __forceinline__ float light_power(const rt2_light_info& li) {                      // getPower :454-471
     if (((li.color_type_and_flags >> RT2_LIGHT_TYPE_SHIFT) & RT2_LIGHT_TYPE_MASK) != RT2_LIGHT_TRIANGLE) return 0.f;
     const TriangleLight t = create_triangle_light(li);

@@ -114,7 +114,7 @@ struct FrameBuffers {
     rt2_packed_di_reservoir* di_reservoirs = nullptr;    // arrayPitch x 2
     uint4* gi_reservoirs = nullptr;                      // 32 B x arrayPitch x 2
     uint4* secondary_gbuffer = nullptr;                  // 48 B x arrayPitch
-    uint4* di_state = nullptr;                           // 5 planes x W x H: sampler state parked between the wavefront stages of K9
+    uint4* di_state = nullptr;                           // 8 planes x W x H: sampler state parked between the wavefront stages of K9
     char2* neighbor_offsets = nullptr;                   // RT2_NEIGHBOR_OFFSET_COUNT signed byte pairs (K7)
     uint32_t reservoir_block_row_pitch = 0, reservoir_array_pitch = 0;
     uint32_t* counters = nullptr;      // [0..1] u64 rays, [2..3] u64 hits, then (count, head) per wavefront iteration
@@ -160,7 +160,8 @@ struct rt2_ctx {
     std::vector<cudaEvent_t> prof_events;   // RT2_LAUNCH_PROFILE: 3 per wavefront iteration (before trace, after trace, after shade)
     uint64_t device_bytes = 0;
     // lights / pdf textures (K10/K12)
-    rt2_light_info* light_info = nullptr; uint32_t light_capacity = 0;
+    rt2_light_info* light_info = nullptr; uint32_t light_capacity = 0;   // = the scene's light count
+    uint32_t light_records = 0;                                            // records allocated: light_capacity, + 2 with a sky (a zero record and the environment light)
     uint32_t* geom_to_light = nullptr;
     rt2_prepare_lights_task* light_tasks = nullptr; uint32_t num_light_tasks = 0;
     bool lights_prepared = false;

@@ -64,7 +64,7 @@ int restir_ensure_resources(rt2_ctx* ctx) {
         RT2_CUDA(ctx, cudaMemcpyAsync(f.neighbor_offsets, tab.data(), tab.size(), cudaMemcpyHostToDevice, ctx->stream));
         RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // `tab` is pageable host memory going out of scope
     }
-    RT2_CUDA(ctx, zalloc(ctx, &f.di_state, n * 5));                                        // K9 wavefront hand-over state, 80 B per pixel
+    RT2_CUDA(ctx, zalloc(ctx, &f.di_state, n * 8));                                        // K9 wavefront hand-over state, 80 B per pixel + 48 B for the environment reservoir
     RT2_CUDA(ctx, zalloc(ctx, &f.secondary_gbuffer, (size_t)f.reservoir_array_pitch * 3)); // 48 B x arrayPitch (block-linear addressing), :309-317
     return RT2_OK;
 }
@@ -85,7 +85,7 @@ bool pass_buffer(rt2_ctx* ctx, int which, void** ptr, size_t* bytes) {
     if (which >= RT2_BUF_ENV_PDF_MIP0 && which < RT2_BUF_ENV_PDF_MIP0 + 32)
         return mip(ctx->env_pdf, ctx->env_pdf_w, ctx->env_pdf_h, ctx->env_pdf_mips, (uint32_t)(which - RT2_BUF_ENV_PDF_MIP0), 2);
     switch (which) {
-        case RT2_BUF_LIGHT_INFO: *ptr = ctx->light_info; *bytes = (size_t)ctx->light_capacity * sizeof(rt2_light_info); return ctx->light_info && ctx->light_capacity;
+        case RT2_BUF_LIGHT_INFO: *ptr = ctx->light_info; *bytes = (size_t)ctx->light_records * sizeof(rt2_light_info); return ctx->light_info && ctx->light_records;
         case RT2_BUF_GEOM_TO_LIGHT: *ptr = ctx->geom_to_light; *bytes = (size_t)ctx->scene.num_geoms * 4; return ctx->geom_to_light && ctx->scene.num_geoms;
         case RT2_BUF_LIGHT_TASKS: *ptr = ctx->light_tasks; *bytes = (size_t)ctx->num_light_tasks * sizeof(rt2_prepare_lights_task); return ctx->light_tasks && ctx->num_light_tasks;
         case RT2_BUF_GBUFFER_DEPTH: *ptr = f.gb_depth[cur]; *bytes = n * 4; return f.gb_depth[cur] != nullptr;

@@ -72,12 +72,20 @@ __global__ void __launch_bounds__(256) k_prepare_lights(const rt2_prepare_lights
 }
 
 void presample_release(rt2_ctx* ctx);
+// the environment light at index lights + 1 (src/main.rs:383; SURVEY Q7 pinned to intent, see store_environment_light)
+__global__ void k_store_environment_light(rt2_light_info* lights, uint32_t num_lights, uint32_t tex_w, uint32_t tex_h) {
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    rt2_light_info zero; memset(&zero, 0, sizeof zero);
+    lights[num_lights] = zero;
+    lights[num_lights + 1] = store_environment_light(tex_w, tex_h);
+}
+
 void lights_release(rt2_ctx* ctx) {
     presample_release(ctx);
     void* ptrs[] = {ctx->light_info, ctx->geom_to_light, ctx->light_tasks, ctx->local_pdf, ctx->env_pdf};
     for (void* p : ptrs) if (p) cudaFree(p);
     ctx->light_info = nullptr; ctx->geom_to_light = nullptr; ctx->light_tasks = nullptr; ctx->local_pdf = nullptr; ctx->env_pdf = nullptr;
-    ctx->light_capacity = ctx->num_light_tasks = 0;
+    ctx->light_capacity = ctx->light_records = ctx->num_light_tasks = 0;
     ctx->local_pdf_w = ctx->local_pdf_h = ctx->local_pdf_mips = ctx->env_pdf_w = ctx->env_pdf_h = ctx->env_pdf_mips = 0;
     ctx->lights_prepared = false;
 }
@@ -88,18 +96,21 @@ int lights_ensure_resources(rt2_ctx* ctx) {
     if (!s.geom_tri_offset) return fail(ctx, RT2_E_STATE, "no scene: call rt2_upload_scene first");
     if (ctx->light_info) return RT2_OK;
     const uint32_t n = s.num_lights;
-    RT2_CUDA(ctx, cudaMalloc((void**)&ctx->light_info, std::max<size_t>(n, 1) * sizeof(rt2_light_info)));
+    // lights + 2 records when the scene has a sky: the environment light lives at lights + 1 (src/main.rs:383)
+    const bool env = s.sky != nullptr && s.sky_w <= 0xffffu && s.sky_h <= 0xffffu;
+    const size_t records = (size_t)n + (env ? 2 : 0);
+    RT2_CUDA(ctx, cudaMalloc((void**)&ctx->light_info, std::max<size_t>(records, 1) * sizeof(rt2_light_info)));
     RT2_CUDA(ctx, cudaMalloc((void**)&ctx->geom_to_light, std::max<size_t>(s.num_geoms, 1) * 4));
     RT2_CUDA(ctx, cudaMalloc((void**)&ctx->light_tasks, std::max<size_t>(s.num_geoms, 1) * sizeof(rt2_prepare_lights_task)));
-    ctx->light_capacity = n;
+    ctx->light_capacity = n; ctx->light_records = (uint32_t)records;
     compute_pdf_texture_size(n, &ctx->local_pdf_w, &ctx->local_pdf_h, &ctx->local_pdf_mips);
     const size_t texels = mip_chain_texels(ctx->local_pdf_w, ctx->local_pdf_h, ctx->local_pdf_mips);
     RT2_CUDA(ctx, cudaMalloc((void**)&ctx->local_pdf, texels * 4));
     // the reference never clears this image; texels no light writes are pinned to 0
     RT2_CUDA(ctx, cudaMemsetAsync(ctx->local_pdf, 0, texels * 4, ctx->stream));
-    RT2_CUDA(ctx, cudaMemsetAsync(ctx->light_info, 0, std::max<size_t>(n, 1) * sizeof(rt2_light_info), ctx->stream));
+    RT2_CUDA(ctx, cudaMemsetAsync(ctx->light_info, 0, std::max<size_t>(records, 1) * sizeof(rt2_light_info), ctx->stream));
     RT2_CUDA(ctx, cudaMemsetAsync(ctx->geom_to_light, 0xFF, std::max<size_t>(s.num_geoms, 1) * 4, ctx->stream));
-    ctx->device_bytes += std::max<size_t>(n, 1) * sizeof(rt2_light_info) + std::max<size_t>(s.num_geoms, 1) * 20 + texels * 4;
+    ctx->device_bytes += std::max<size_t>(records, 1) * sizeof(rt2_light_info) + std::max<size_t>(s.num_geoms, 1) * 20 + texels * 4;
     return RT2_OK;
 }
 
@@ -129,7 +140,11 @@ int lights_prepare(rt2_ctx* ctx) {
                                                           ctx->local_pdf, ctx->local_pdf_w, ctx->local_pdf_h);
         RT2_CUDA(ctx, cudaGetLastError());
     }
-    ctx->stats.kernel_launches = groups ? 1 : 0;
+    if (ctx->light_records == ctx->light_capacity + 2) {
+        k_store_environment_light<<<1, 32, 0, ctx->stream>>>(ctx->light_info, ctx->light_capacity, s.sky_w, s.sky_h);
+        RT2_CUDA(ctx, cudaGetLastError());
+    }
+    ctx->stats.kernel_launches = (groups ? 1 : 0) + (ctx->light_records == ctx->light_capacity + 2 ? 1 : 0);
     ctx->stats_from_counters = false;
     ctx->lights_prepared = true;
     return RT2_OK;

@@ -99,6 +99,9 @@ struct LightRefs {
     const float* pdf; uint32_t pdf_w, pdf_h, pdf_last_offset;
     // RT2_LAUNCH_PRESAMPLING: the sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1; K11's tiles for POWER_RIS
     uint32_t presampling; const uint2* ris; const uint4* ris_light_data;
+    // the environment light (RT2_LAUNCH_PRESAMPLING only; SURVEY Q7 pinned to intent): present when environmentLightParams.lightPresent
+    // is set AND the scene has a sky; env_pdf = K12's r16f pyramid, env_last_offset = the texel offset of the mip the pdf's average is read from
+    uint32_t env_present, env_index; const uint16_t* env_pdf; uint32_t env_w, env_h, env_last_offset;
 };
 
 // RAB_EvaluateLocalLightSourcePdf, bridge :420-434 (Q14 pinned to texelFetch semantics)
@@ -108,6 +111,19 @@ __device__ __forceinline__ float local_light_source_pdf(const LightRefs& a, uint
     const float texel = (x < a.pdf_w && y < a.pdf_h) ? __ldg(a.pdf + (size_t)y * a.pdf_w + x) : 0.f;
     const int last = max(0, (int)floorf(log2_pinned((float)max(a.pdf_w, a.pdf_h))));
     const float average = __ldg(a.pdf + a.pdf_last_offset);
+    const float sum = average * (float)(1u << (uint32_t)last << (uint32_t)last);
+    return texel / sum;
+}
+
+// RAB_EvaluateEnvironmentMapSamplingPdf, bridge :397-418 (the Q14 quirk again, same pin: texelFetch; uv == 1.0 reads 0)
+__device__ __forceinline__ float environment_map_sampling_pdf(const LightRefs& a, const rt2_gconst& g, V3 L) {
+    if (g.restir_di.initial_sampling_params.environment_map_importance_sampling == 0u) return 1.0f;
+    float u, v; direction_to_equirect_uv(L, &u, &v);                   // RAB_GetEnvironmentMapRandXYFromDir, bridge :389-393
+    const uint32_t sx = g.environment_pdf_texture_size[0], sy = g.environment_pdf_texture_size[1];
+    const uint32_t tx = (uint32_t)((float)sx * u), ty = (uint32_t)((float)sy * v);
+    const float texel = (tx < a.env_w && ty < a.env_h) ? f16_bits_to_f32(__ldg(a.env_pdf + (size_t)ty * a.env_w + tx)) : 0.f;
+    const int last = max(0, (int)floorf(log2_pinned((float)max(sx, sy))));
+    const float average = f16_bits_to_f32(__ldg(a.env_pdf + a.env_last_offset));
     const float sum = average * (float)(1u << (uint32_t)last << (uint32_t)last);
     return texel / sum;
 }
@@ -126,7 +142,12 @@ __device__ __forceinline__ bool visibility_ray_miss(const SceneRefs& sc, const S
 // (1) RTXDI_SampleLocalLights{,Internal}, :264-343 (uniform selection)
 // With lr.presampling and localLightSamplingMode == POWER_RIS the lights come from one of K11's tiles, chosen by the tile-coherent
 // generator (:241-254, LocalLightSelection.hlsli:43-94, RISBuffer.hlsli:22-45); tile_x/tile_y = launch pixel / RTXDI_TILE_SIZE_IN_PIXELS.
-__device__ __forceinline__ void sl_local_lights(const LightRefs& lr, const rt2_gconst& g, Rng& rng, uint32_t tile_x, uint32_t tile_y, uint32_t frame,
+struct TileRng { Rng rng; bool started; };      // the tile-coherent generator (di_fused_resampling.rgen:22): created on first use, shared by the local and environment tile draws
+__device__ __forceinline__ float tile_rng_next(TileRng& t, uint32_t tile_x, uint32_t tile_y, uint32_t frame) {
+    if (!t.started) { t.rng = rng_init(tile_x, tile_y, frame, 1u); t.started = true; }
+    return rng_next(t.rng);
+}
+__device__ __forceinline__ void sl_local_lights(const SceneRefs& sc, const LightRefs& lr, const rt2_gconst& g, Rng& rng, TileRng& tile_rng, uint32_t tile_x, uint32_t tile_y, uint32_t frame,
                                                 const Surface& surface, const SampleParams& sp,
                                                 DIReservoir* local_reservoir, LightSample* local_sample) {
     const uint32_t first_local = g.light_buffer_params.local_light_buffer_region.first_light_index;
@@ -139,8 +160,7 @@ __device__ __forceinline__ void sl_local_lights(const LightRefs& lr, const rt2_g
         uint32_t tile_offset = 0, tile_size = 0;
         if (ris_mode) {                                                // RTXDI_RandomlySelectRISTile
             const rt2_ris_buffer_segment_params& seg = g.local_lights_risbuffer_segment_params;
-            Rng tile_rng = rng_init(tile_x, tile_y, frame, 1u);
-            const uint32_t tile_index = (uint32_t)(rng_next(tile_rng) * (float)seg.tile_count);
+            const uint32_t tile_index = (uint32_t)(tile_rng_next(tile_rng, tile_x, tile_y, frame) * (float)seg.tile_count);
             tile_offset = tile_index * seg.tile_size + seg.buffer_offset;
             tile_size = seg.tile_size;
         }
@@ -163,7 +183,7 @@ __device__ __forceinline__ void sl_local_lights(const LightRefs& lr, const rt2_g
                 li = load_light_info(lr.lights, light_index);
             }
             const float uvx = rng_next(rng), uvy = rng_next(rng);
-            const LightSample cand = sample_polymorphic_light(li, surface, uvx, uvy);           // :131-156
+            const LightSample cand = sample_polymorphic_light(sc, li, surface, uvx, uvy);       // :131-156
             const float blended = light_brdf_mis_weight(surface, cand, 1.0f / inv_source_pdf, sp.local_mis_weight, false, sp);
             const float target_pdf = light_sample_target_pdf(cand, surface);
             const float ris_rnd = rng_next(rng);
@@ -175,6 +195,35 @@ __device__ __forceinline__ void sl_local_lights(const LightRefs& lr, const rt2_g
         *local_reservoir = state;
     }
 }
+// (1b) RTXDI_SampleEnvironmentMap, :465-499 (compiled with RTXDI_ENABLE_PRESAMPLING only): candidates from one of K11's environment
+// tiles; every candidate is streamed, a zero source pdf included (:441-463 has no early-out, unlike the local-light one)
+__device__ __forceinline__ void sl_environment_map(const SceneRefs& sc, const LightRefs& lr, const rt2_gconst& g, Rng& rng, TileRng& tile_rng, uint32_t tile_x, uint32_t tile_y,
+                                                   uint32_t frame, const Surface& surface, const SampleParams& sp,
+                                                   DIReservoir* env_reservoir, LightSample* env_sample) {
+    *env_sample = empty_light_sample();
+    *env_reservoir = empty_di_reservoir();
+    if (lr.presampling == 0u || lr.env_present == 0u || sp.num_env == 0u) return;
+    const rt2_ris_buffer_segment_params& seg = g.environment_light_risbuffer_segment_params;
+    const uint32_t tile_index = (uint32_t)(tile_rng_next(tile_rng, tile_x, tile_y, frame) * (float)seg.tile_count);   // RTXDI_RandomlySelectRISTile
+    const uint32_t tile_offset = tile_index * seg.tile_size + seg.buffer_offset, tile_size = seg.tile_size;
+    const rt2_light_info li = load_light_info(lr.lights, lr.env_index);
+    DIReservoir state = empty_di_reservoir();
+    for (uint32_t i = 0; i < sp.num_env; i++) {
+        const float rnd = rng_next(rng);                                // RTXDI_RandomlySelectLightDataFromRISTile, RISBuffer.hlsli:20-31
+        const uint32_t ptr = min((uint32_t)floorf(rnd * (float)tile_size), tile_size - 1u) + tile_offset;
+        const uint2 tile_data = __ldg(lr.ris + ptr);
+        const float inv_source_pdf = __uint_as_float(tile_data.y);     // RTXDI_UnpackEnvironmentLightDataFromRISData, :417-426
+        const float uvx = (float)(tile_data.x & 0xffffu) / (float)0xffff, uvy = (float)(tile_data.x >> 16) / (float)0xffff;
+        const LightSample cand = sample_polymorphic_light(sc, li, surface, uvx, uvy);
+        const float blended = light_brdf_mis_weight(surface, cand, 1.0f / inv_source_pdf, sp.env_mis_weight, true, sp);
+        const float target_pdf = light_sample_target_pdf(cand, surface);
+        const float ris_rnd = rng_next(rng);
+        if (di_stream_sample(state, lr.env_index, uvx, uvy, ris_rnd, target_pdf, 1.0f / blended)) *env_sample = cand;
+    }
+    di_finalize(state, 1.0f, (float)sp.num_mis);
+    state.M = 1;
+    *env_reservoir = state;
+}
 // (2) RTXDI_SampleBrdf, :507-591, one iteration: the ray ...
 struct BrdfProbe { bool sampled; V3 dir; float max_distance; };
 __device__ __forceinline__ BrdfProbe sl_brdf_ray(const Surface& surface, Rng& rng, const SampleParams& sp) {
@@ -184,8 +233,8 @@ __device__ __forceinline__ BrdfProbe sl_brdf_ray(const Surface& surface, Rng& rn
     return p;
 }
 // ... and what follows its hit (RAB_TraceRayForLocalLight, bridge :629-669): geom == ~0u is a miss
-__device__ __forceinline__ void sl_brdf_hit(const LightRefs& lr, Rng& rng, const Surface& surface, const SampleParams& sp, bool sampled,
-                                            uint32_t geom, uint32_t prim, float hu, float hv, DIReservoir* brdf_reservoir, LightSample* brdf_sample) {
+__device__ __forceinline__ void sl_brdf_hit(const SceneRefs& sc, const LightRefs& lr, const rt2_gconst& g, Rng& rng, const Surface& surface, const SampleParams& sp, bool sampled,
+                                            V3 sample_dir, uint32_t geom, uint32_t prim, float hu, float hv, DIReservoir* brdf_reservoir, LightSample* brdf_sample) {
     float light_source_pdf = 0;
     uint32_t light_index = RT2_INVALID_LIGHT;
     float rx = 0, ry = 0;
@@ -200,7 +249,7 @@ __device__ __forceinline__ void sl_brdf_hit(const LightRefs& lr, Rng& rng, const
             const float bx = 1 - hu - hv, bz = hv;                     // hitUVToBarycentric, randomFromBarycentric (Helpers.glsl:76-86)
             const float sqrtx = 1 - bx;
             rx = sqrtx * sqrtx; ry = bz / sqrtx;
-            cand = sample_polymorphic_light(load_light_info(lr.lights, light_index), surface, rx, ry);
+            cand = sample_polymorphic_light(sc, load_light_info(lr.lights, light_index), surface, rx, ry);
             if (sp.brdf_cutoff > 0.f) {
                 const V3 to_light = cand.position - surface.world_pos;
                 const float light_distance = length3(to_light);
@@ -209,17 +258,26 @@ __device__ __forceinline__ void sl_brdf_hit(const LightRefs& lr, Rng& rng, const
             }
             if (light_index != RT2_INVALID_LIGHT) light_source_pdf = local_light_source_pdf(lr, light_index);
         }
-        // BRDF miss + environmentLightParams.lightPresent: the environment light (index lights + 1) is never written (Q7) -> absent
+        // BRDF miss + environmentLightParams.lightPresent, :556-564: the environment light (index lights + 1) is never written by the
+        // reference (Q7) -> absent as shipped; with RT2_LAUNCH_PRESAMPLING the one K10 writes there is sampled
+        else if (geom == 0xFFFFFFFFu && lr.env_present != 0u) {
+            light_index = lr.env_index;
+            direction_to_equirect_uv(sample_dir, &rx, &ry);            // RAB_GetEnvironmentMapRandXYFromDir
+            cand = sample_polymorphic_light(sc, load_light_info(lr.lights, light_index), surface, rx, ry);
+            light_source_pdf = environment_map_sampling_pdf(lr, g, sample_dir);
+        }
     }
     if (light_source_pdf == 0) return;
+    const bool is_env = lr.env_present != 0u && light_index == lr.env_index;       // :573
     const float target_pdf = light_sample_target_pdf(cand, surface);
-    const float blended = light_brdf_mis_weight(surface, cand, light_source_pdf, sp.local_mis_weight, false, sp);
+    const float blended = light_brdf_mis_weight(surface, cand, light_source_pdf, is_env ? sp.env_mis_weight : sp.local_mis_weight, is_env, sp);
     const float ris_rnd = rng_next(rng);
     if (di_stream_sample(*brdf_reservoir, light_index, rx, ry, ris_rnd, target_pdf, 1.0f / blended)) *brdf_sample = cand;
 }
 // (3) finalize the BRDF reservoir and combine, :586-590, 637-663.  The infinite-light region is always empty
 // (src/main.rs:375-380; rejected on the host otherwise), so its reservoir and sample are the empty ones.
 __device__ __forceinline__ DIReservoir sl_combine(const LightRefs& lr, Rng& rng, const SampleParams& sp, const DIReservoir& local_reservoir, const LightSample& local_sample,
+                                                  const DIReservoir& env_reservoir, const LightSample& env_sample,
                                                   DIReservoir brdf_reservoir, const LightSample& brdf_sample, LightSample* o_light_sample) {
     di_finalize(brdf_reservoir, 1.0f, (float)sp.num_mis);
     brdf_reservoir.M = 1;
@@ -228,12 +286,13 @@ __device__ __forceinline__ DIReservoir sl_combine(const LightRefs& lr, Rng& rng,
     DIReservoir reservoir = empty_di_reservoir();
     di_combine(reservoir, local_reservoir, 0.5f, local_reservoir.target_pdf);
     const bool select_infinite = di_combine(reservoir, infinite_reservoir, rng_next(rng), infinite_reservoir.target_pdf);
-    // :641-643 — with presampling compiled in the (always empty, Q7) environment reservoir is combined too: one more draw
-    if (lr.presampling != 0u) { const DIReservoir env = empty_di_reservoir(); di_combine(reservoir, env, rng_next(rng), env.target_pdf); }
+    // :641-643 — with presampling compiled in the environment reservoir is combined too (one more draw, empty reservoir or not)
+    bool select_env = false;
+    if (lr.presampling != 0u) select_env = di_combine(reservoir, env_reservoir, rng_next(rng), env_reservoir.target_pdf);
     const bool select_brdf = di_combine(reservoir, brdf_reservoir, rng_next(rng), brdf_reservoir.target_pdf);
     di_finalize(reservoir, 1.0f, 1.0f);
     reservoir.M = 1;
-    *o_light_sample = select_brdf ? brdf_sample : (select_infinite ? infinite_sample : local_sample);
+    *o_light_sample = select_brdf ? brdf_sample : (select_env ? env_sample : (select_infinite ? infinite_sample : local_sample));
     return reservoir;
 }
 
@@ -241,7 +300,10 @@ __device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& s
                                                               uint32_t tile_x, uint32_t tile_y, uint32_t frame, const Surface& surface,
                                                               const SampleParams& sp, LightSample* o_light_sample, uint32_t& rays, uint32_t& hits) {
     LightSample local_sample; DIReservoir local_reservoir;
-    sl_local_lights(lr, g, rng, tile_x, tile_y, frame, surface, sp, &local_reservoir, &local_sample);
+    TileRng tile_rng; tile_rng.started = false;
+    sl_local_lights(sc, lr, g, rng, tile_rng, tile_x, tile_y, frame, surface, sp, &local_reservoir, &local_sample);
+    LightSample env_sample; DIReservoir env_reservoir;
+    sl_environment_map(sc, lr, g, rng, tile_rng, tile_x, tile_y, frame, surface, sp, &env_reservoir, &env_sample);
     LightSample brdf_sample = empty_light_sample();
     DIReservoir brdf_reservoir = empty_di_reservoir();
     for (uint32_t i = 0; i < sp.num_brdf; ++i) {
@@ -253,9 +315,9 @@ __device__ __noinline__ DIReservoir sample_lights_for_surface(const SceneRefs& s
             rays++;
             if (h.geom != 0xFFFFFFFFu) hits++;
         }
-        sl_brdf_hit(lr, rng, surface, sp, p.sampled, h.geom, h.prim, h.u, h.v, &brdf_reservoir, &brdf_sample);
+        sl_brdf_hit(sc, lr, g, rng, surface, sp, p.sampled, p.dir, h.geom, h.prim, h.u, h.v, &brdf_reservoir, &brdf_sample);
     }
-    return sl_combine(lr, rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, o_light_sample);
+    return sl_combine(lr, rng, sp, local_reservoir, local_sample, env_reservoir, env_sample, brdf_reservoir, brdf_sample, o_light_sample);
 }
 
 // ShadeSurfaceWithLightSample, ShadingHelpers.glsl:2-58.  Visibility reuse needs reservoir.age > 0 (DIReservoir.hlsli:186-189);
@@ -347,7 +409,7 @@ __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
 struct DIWaveArgs {
     DIArgs di;
     float4 *st_ray0, *st_ray1; float4* st_hit; const uint32_t* st_hit_inst;
-    uint4* state; uint32_t plane;          // 5 planes of `plane` uint4 each
+    uint4* state; uint32_t plane;          // 8 planes of `plane` uint4 each (5..7: the environment reservoir, di_env_store)
     const uint4* secondary;                // K5 (DI on): sample at the secondary surface instead of the G-buffer surface
     uint32_t* queue; uint32_t* count;
 };
@@ -366,6 +428,23 @@ __device__ __forceinline__ void di_state_load(const DIWaveArgs& w, uint32_t slot
     r->age = c.x; *rng_index = c.y; *flags = c.z;
     *ls = empty_light_sample();                                        // the normal is not needed past sample_polymorphic_light
     ls->light_type = c.w;
+    ls->position = v3(__uint_as_float(d.x), __uint_as_float(d.y), __uint_as_float(d.z)); ls->solid_angle_pdf = __uint_as_float(d.w);
+    ls->radiance = v3(__uint_as_float(e.x), __uint_as_float(e.y), __uint_as_float(e.z));
+}
+// the environment reservoir and its sample wait in planes 5..7 while the BRDF ray is traced (K9 only: K5 asks for no environment samples).
+// M is 1 after RTXDI_SampleEnvironmentMap's finalize; the sample's type follows from the reservoir (a selected sample set lightData).
+__device__ __forceinline__ bool di_env_active(const LightRefs& lr, const SampleParams& sp) { return lr.presampling != 0u && lr.env_present != 0u && sp.num_env != 0u; }
+__device__ __forceinline__ void di_env_store(const DIWaveArgs& w, uint32_t slot, const DIReservoir& r, const LightSample& ls) {
+    w.state[5 * (size_t)w.plane + slot] = make_uint4(r.light_data, r.uv_data, __float_as_uint(r.weight_sum), __float_as_uint(r.target_pdf));
+    w.state[6 * (size_t)w.plane + slot] = make_uint4(__float_as_uint(ls.position.x), __float_as_uint(ls.position.y), __float_as_uint(ls.position.z), __float_as_uint(ls.solid_angle_pdf));
+    w.state[7 * (size_t)w.plane + slot] = make_uint4(__float_as_uint(ls.radiance.x), __float_as_uint(ls.radiance.y), __float_as_uint(ls.radiance.z), 0u);
+}
+__device__ __forceinline__ void di_env_load(const DIWaveArgs& w, uint32_t slot, DIReservoir* r, LightSample* ls) {
+    const uint4 a = w.state[5 * (size_t)w.plane + slot], d = w.state[6 * (size_t)w.plane + slot], e = w.state[7 * (size_t)w.plane + slot];
+    *r = empty_di_reservoir();
+    r->light_data = a.x; r->uv_data = a.y; r->weight_sum = __uint_as_float(a.z); r->target_pdf = __uint_as_float(a.w); r->M = 1;
+    *ls = empty_light_sample();
+    ls->light_type = a.x != 0u ? RT2_LIGHT_ENVIRONMENT : 0u;
     ls->position = v3(__uint_as_float(d.x), __uint_as_float(d.y), __uint_as_float(d.z)); ls->solid_angle_pdf = __uint_as_float(d.w);
     ls->radiance = v3(__uint_as_float(e.x), __uint_as_float(e.y), __uint_as_float(e.z));
 }
@@ -435,7 +514,13 @@ __global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_a(DIWaveArgs w)
         const Surface surface = di_stage_surface<SEC>(w, g, lx, ly, px, py, &active);
         const SampleParams sp = di_stage_params<SEC>(g.restir_di);
         LightSample local_sample = empty_light_sample(); DIReservoir local_reservoir = empty_di_reservoir();
-        if (active) sl_local_lights(a.li, g, rng, (SEC ? lx : px) >> 4, (SEC ? ly : py) >> 4, a.frame, surface, sp, &local_reservoir, &local_sample);
+        TileRng tile_rng; tile_rng.started = false;
+        if (active) sl_local_lights(a.sc, a.li, g, rng, tile_rng, (SEC ? lx : px) >> 4, (SEC ? ly : py) >> 4, a.frame, surface, sp, &local_reservoir, &local_sample);
+        if (!SEC && di_env_active(a.li, sp)) {
+            LightSample env_sample; DIReservoir env_reservoir;
+            sl_environment_map(a.sc, a.li, g, rng, tile_rng, px >> 4, py >> 4, a.frame, surface, sp, &env_reservoir, &env_sample);
+            di_env_store(w, slot, env_reservoir, env_sample);
+        }
         uint32_t flags = active ? DIW_ACTIVE : 0u;
         if (active && sp.num_brdf != 0u) {
             const BrdfProbe p = sl_brdf_ray(surface, rng, sp);
@@ -476,7 +561,10 @@ __global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_b(DIWaveArgs w,
         if (sp.num_brdf != 0u) {
             const bool sampled = (flags & DIW_BRDF_SAMPLED) != 0u;
             uint32_t geom = 0xFFFFFFFFu, prim = 0xFFFFFFFFu; float hu = 0.f, hv = 0.f;
+            V3 sample_dir = v3(0.f, 0.f, 0.f);
             if (sampled) {
+                const float4 rd = w.st_ray1[slot];                       // the BRDF direction stage A queued (the trace kernel only reads it)
+                sample_dir = v3(rd.x, rd.y, rd.z);
                 const float4 h = w.st_hit[slot];
                 const uint32_t tri_slot = __float_as_uint(h.w);
                 if (tri_slot != 0xFFFFFFFFu) {
@@ -485,10 +573,12 @@ __global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_b(DIWaveArgs w,
                     geom = f2u(ld16f(&tp->v0).w); prim = f2u(ld16f(&tp->v1).w); hu = h.y; hv = h.z;
                 }
             }
-            sl_brdf_hit(a.li, rng, surface, sp, sampled, geom, prim, hu, hv, &brdf_reservoir, &brdf_sample);
+            sl_brdf_hit(a.sc, a.li, g, rng, surface, sp, sampled, sample_dir, geom, prim, hu, hv, &brdf_reservoir, &brdf_sample);
         }
+        LightSample env_sample = empty_light_sample(); DIReservoir env_reservoir = empty_di_reservoir();
+        if (!SEC && di_env_active(a.li, sp)) di_env_load(w, slot, &env_reservoir, &env_sample);
         LightSample light_sample;
-        DIReservoir reservoir = sl_combine(a.li, rng, sp, local_reservoir, local_sample, brdf_reservoir, brdf_sample, &light_sample);
+        DIReservoir reservoir = sl_combine(a.li, rng, sp, local_reservoir, local_sample, env_reservoir, env_sample, brdf_reservoir, brdf_sample, &light_sample);
         flags = DIW_ACTIVE;
         // K9 runs the initial-visibility test of di_fused_resampling.rgen:42-48 first; K5 shades with enableVisibilityReuse false and has none
         if (di_valid(reservoir) || SEC) {
@@ -1322,7 +1412,9 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     if (g.enable_restir_di == 1u) {
         const uint32_t num_local = g.light_buffer_params.local_light_buffer_region.num_lights;
         if (g.light_buffer_params.infinite_light_buffer_region.num_lights != 0u) return fail(ctx, RT2_E_INVALID, "infinite lights have no producer in the reference (src/main.rs:375-380)");
-        if (g.restir_di.initial_sampling_params.num_primary_environment_samples != 0u) return fail(ctx, RT2_E_INVALID, "environment RIS sampling is compiled out (RTXDI_ENABLE_PRESAMPLING 0)");
+        const uint32_t num_env = g.restir_di.initial_sampling_params.num_primary_environment_samples;
+        if (num_env != 0u && !(lp.flags & RT2_LAUNCH_PRESAMPLING))
+            return fail(ctx, RT2_E_INVALID, "environment RIS sampling is compiled out of the shipped shaders (RTXDI_ENABLE_PRESAMPLING 0): pass RT2_LAUNCH_PRESAMPLING");
         if (!pitches_ok(g.restir_di.reservoir_buffer_params)) return fail(ctx, RT2_E_INVALID, "GConst reservoir buffer parameters do not match the frame size (calculate_reservoir_buffer_parameters)");
         if (g.restir_di.buffer_indices.shading_input_buffer_index > 1u) return fail(ctx, RT2_E_INVALID, "reservoir buffer index out of range");
         if (num_local) {
@@ -1348,6 +1440,31 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
                 if (seg.tile_size == 0u || seg.tile_count == 0u || (uint64_t)seg.buffer_offset + (uint64_t)seg.tile_size * seg.tile_count > ctx->ris_entries)
                     return fail(ctx, RT2_E_INVALID, "local-light RIS segment exceeds the RIS buffer");
                 lrefs.ris = ctx->ris_buffer; lrefs.ris_light_data = ctx->ris_light_data;
+            }
+            // the environment light: environmentLightParams.lightPresent (always 1 in the reference, src/main.rs:381-386) AND a sky in the scene
+            const rt2_environment_light_buffer_params& ep = g.light_buffer_params.environment_light_params;
+            if (ep.light_present != 0u && ctx->scene.sky != nullptr) {
+                if (!ctx->lights_prepared || ctx->light_records != ctx->light_capacity + 2u)
+                    return fail(ctx, RT2_E_STATE, "the environment light is not written: call rt2_prepare_lights first");
+                if (ep.light_index != ctx->light_capacity + 1u) return fail(ctx, RT2_E_INVALID, "environment light index must be lights + 1 (src/main.rs:383): rt2_prepare_lights writes the environment light there");
+                if (!ctx->env_pdf) return fail(ctx, RT2_E_STATE, "environment PDF pyramid not built: call rt2_generate_mips(1) first");
+                if (g.environment_pdf_texture_size[0] != ctx->env_pdf_w || g.environment_pdf_texture_size[1] != ctx->env_pdf_h)
+                    return fail(ctx, RT2_E_INVALID, "GConst environment_pdf_texture_size does not match the environment PDF texture");
+                lrefs.env_present = 1u; lrefs.env_index = ep.light_index;
+                lrefs.env_pdf = ctx->env_pdf; lrefs.env_w = ctx->env_pdf_w; lrefs.env_h = ctx->env_pdf_h;
+                const uint32_t em = std::max(ctx->env_pdf_w, ctx->env_pdf_h);
+                uint32_t elast = 0; while ((2u << elast) <= em) elast++;
+                elast = std::min(elast, ctx->env_pdf_mips - 1);
+                uint32_t eoff = 0;
+                for (uint32_t k = 0; k < elast; k++) eoff += std::max(1u, ctx->env_pdf_w >> k) * std::max(1u, ctx->env_pdf_h >> k);
+                lrefs.env_last_offset = eoff;
+                if (num_env != 0u) {
+                    const rt2_ris_buffer_segment_params& seg = g.environment_light_risbuffer_segment_params;
+                    if (!ctx->ris_buffer) return fail(ctx, RT2_E_STATE, "environment-map sampling needs the presampled tiles: call rt2_presample(ctx, frame, 1) first");
+                    if (seg.tile_size == 0u || seg.tile_count == 0u || (uint64_t)seg.buffer_offset + (uint64_t)seg.tile_size * seg.tile_count > ctx->ris_entries)
+                        return fail(ctx, RT2_E_INVALID, "environment RIS segment exceeds the RIS buffer");
+                    lrefs.ris = ctx->ris_buffer;
+                }
             }
         }
     }

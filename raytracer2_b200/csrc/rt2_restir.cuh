@@ -104,9 +104,44 @@ __device__ __forceinline__ rt2_light_info load_light_info(const rt2_light_info* 
     li.ies_profile_index = li.primary_axis = li.cos_cone_angle_and_softness = li.padding = 0u;
     return li;
 }
-__device__ __forceinline__ LightSample sample_polymorphic_light(const rt2_light_info& li, const Surface& surface, float uvx, float uvy) {
+#define RT2_DISTANT_LIGHT_DISTANCE 1000.0f   /* PolymorphicLight.glsl:43 */
+// equirectUVToDirection, Helpers.glsl:334-345
+__device__ __forceinline__ V3 equirect_uv_to_direction(float u, float v, float* cos_elevation) {
+    const float azimuth = (u + 0.25f) * (2 * RT2_RTXDI_PI);
+    const float elevation = (0.5f - v) * RT2_RTXDI_PI;
+    float sa, ca, se, ce;
+    sincos_pinned(azimuth, &sa, &ca); sincos_pinned(elevation, &se, &ce);
+    *cos_elevation = ce;
+    return v3(ca * ce, se, sa * ce);
+}
+// calcEnvironmentLightSample, PolymorphicLight.glsl:368-410 (importance-sampled branch: the only kind K10 writes)
+__device__ __forceinline__ LightSample environment_light_sample(const SceneRefs& sc, const rt2_light_info& li, V3 viewer_position, float rx, float ry) {
+    LightSample out = empty_light_sample();
+    out.light_type = RT2_LIGHT_ENVIRONMENT;
+    const int texture_index = (int)li.direction1;                         // CreateEnvironmentLight, :414-426
+    const float rotation = f16_bits_to_f32((uint16_t)(li.scalars & 0xffffu));
+    const uint32_t tex_w = li.direction2 & 0xffffu, tex_h = li.direction2 >> 16;
+    const V3 radiance_scale = unpack_r8g8b8(li.color_type_and_flags) * unpack_light_radiance(li.log_radiance & 0xffffu);
+    float cos_elevation;
+    const V3 dir = equirect_uv_to_direction(rx + rotation, ry, &cos_elevation);
+    out.solid_angle_pdf = (float)(tex_w * tex_h) / (2 * RT2_RTXDI_PI * RT2_RTXDI_PI * cos_elevation);
+    V3 radiance = radiance_scale;
+    if (texture_index >= 0) radiance = radiance * sample_sky(sc, rx, ry);
+    const float sum = radiance.x + radiance.y + radiance.z;
+    if (isinf(sum) || isnan(sum)) radiance = v3(0.f, 0.f, 0.f);
+    out.position = viewer_position + dir * RT2_DISTANT_LIGHT_DISTANCE;
+    out.normal = neg3(dir);
+    out.radiance = radiance;
+    return out;
+}
+__device__ __forceinline__ LightSample sample_polymorphic_light(const SceneRefs& sc, const rt2_light_info& li, const Surface& surface, float uvx, float uvy) {
     LightSample out = empty_light_sample();
     out.light_type = (li.color_type_and_flags >> RT2_LIGHT_TYPE_SHIFT) & RT2_LIGHT_TYPE_MASK;
+    if (out.light_type == RT2_LIGHT_ENVIRONMENT && sc.sky != nullptr && (li.scalars >> 16) != 0u) {
+        out = environment_light_sample(sc, li, surface.world_pos, uvx, uvy);
+        if (out.solid_angle_pdf > 0) out.radiance = out.radiance * v3(1.0f, 1.0f, 1.0f);   // evaluateLightShaping with the shaping bit clear
+        return out;
+    }
     if (out.light_type != RT2_LIGHT_TRIANGLE) return out;
     const TriangleLight self = create_triangle_light(li);
     const float sqrtx = sqrtf(uvx);                                       // sampleTriangle, Helpers.glsl:66-74
@@ -200,11 +235,11 @@ __device__ __forceinline__ float brdf_max_distance_from_pdf(float brdf_cutoff, f
 __device__ __forceinline__ float light_brdf_mis_weight(const Surface& s, const LightSample& ls, float light_selection_pdf, float light_mis_weight,
                                                        bool is_environment_map, const SampleParams& sp) {
     const float pdf = ls.solid_angle_pdf;
-    const bool analytic = ls.light_type != RT2_LIGHT_TRIANGLE && ls.light_type != 6u;   // RAB_IsAnalyticLightSample, bridge :544-548
+    const bool analytic = ls.light_type != RT2_LIGHT_TRIANGLE && ls.light_type != RT2_LIGHT_ENVIRONMENT;   // RAB_IsAnalyticLightSample, bridge :544-548
     if (sp.brdf_mis_weight == 0 || analytic || pdf <= 0 || isinf(pdf) || isnan(pdf)) return light_mis_weight * light_selection_pdf;
-    const V3 to_light = ls.position - s.world_pos;                        // RAB_GetLightDirDistance, bridge :527-542
-    const float light_distance = length3(to_light);
-    const V3 light_dir = to_light / light_distance;
+    V3 light_dir; float light_distance;                                   // RAB_GetLightDirDistance, bridge :527-542
+    if (ls.light_type == RT2_LIGHT_ENVIRONMENT) { light_dir = neg3(ls.normal); light_distance = RT2_DISTANT_LIGHT_DISTANCE; }
+    else { const V3 to_light = ls.position - s.world_pos; light_distance = length3(to_light); light_dir = to_light / light_distance; }
     float brdf_pdf = surface_brdf_pdf(s, light_dir);
     const float max_distance = brdf_max_distance_from_pdf(sp.brdf_cutoff, brdf_pdf);
     if (!is_environment_map && light_distance > max_distance) brdf_pdf = 0.f;

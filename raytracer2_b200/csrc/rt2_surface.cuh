@@ -77,12 +77,14 @@ __device__ __forceinline__ V3 sample_texture(const uint32_t* __restrict__ texels
 
 // GetEnvironmentRadiance — bridge :618-627; directionToEquirectUV Helpers.glsl:242-248 (PI = 3.1415926,
 // common.glsl:31); sampler LINEAR / CLAMP_TO_BORDER black / normalised (src/main.rs:123-138).
-__device__ __forceinline__ V3 environment_radiance(const SceneRefs& a, const rt2_gconst& g, V3 dir) {
-    if (g.environment != 1u || a.sky == nullptr) return v3(0.f, 0.f, 0.f);
+__device__ __forceinline__ void direction_to_equirect_uv(V3 dir, float* u, float* v) {
     const float PI_ = 3.1415926f;
     // atan / asin follow the transcendental pin (binary64, rounded once), so the lookup is bit-identical to the oracle's
-    const float u = 0.5f + (float)atan2((double)dir.z, (double)dir.x) / (2.0f * PI_);
-    const float v = 0.5f - (float)asin((double)dir.y) / PI_;
+    *u = 0.5f + (float)atan2((double)dir.z, (double)dir.x) / (2.0f * PI_);
+    *v = 0.5f - (float)asin((double)dir.y) / PI_;
+}
+// texture(SkyBox, uv).rgb == textureLod(SkyBox, uv, 0).rgb in a ray-generation shader
+__device__ __forceinline__ V3 sample_sky(const SceneRefs& a, float u, float v) {
     const int W = (int)a.sky_w, H = (int)a.sky_h;
     const float x = u * (float)W - 0.5f, y = v * (float)H - 0.5f;
     const float fx = floorf(x), fy = floorf(y);
@@ -97,6 +99,11 @@ __device__ __forceinline__ V3 environment_radiance(const SceneRefs& a, const rt2
     const float ia = 1.0f - wa, ib = 1.0f - wb;
     const V3 top = t00 * ia + t10 * wa, bot = t01 * ia + t11 * wa;
     return top * ib + bot * wb;
+}
+__device__ __forceinline__ V3 environment_radiance(const SceneRefs& a, const rt2_gconst& g, V3 dir) {
+    if (g.environment != 1u || a.sky == nullptr) return v3(0.f, 0.f, 0.f);
+    float u, v; direction_to_equirect_uv(dir, &u, &v);
+    return sample_sky(a, u, v);
 }
 
 // ShadingHelpers.glsl:61-88 StoreShadingOutput: the two rgba16f images follow the shader literally

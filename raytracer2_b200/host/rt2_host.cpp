@@ -437,6 +437,23 @@ static void gen_manylight(rt2h_scene& s, float scale, uint64_t seed) {
     rt2h_camera_new(&s.cam, pos, dir, 65.0f, 16.0f / 9.0f, 0.1f, 1000.0f);
 }
 
+// procedural equirect sky: gradient + sun (width x width / 2)
+static void gen_sky(rt2h_scene& s, uint32_t width) {
+    s.sky_w = width; s.sky_h = s.sky_w / 2;
+    s.sky.resize((size_t)s.sky_w * s.sky_h * 4);
+    F3 sun = normalize(f3(0.4f, 0.6f, -0.5f));
+    for (uint32_t y = 0; y < s.sky_h; y++) for (uint32_t x = 0; x < s.sky_w; x++) {
+        float u = (x + 0.5f) / s.sky_w, v = (y + 0.5f) / s.sky_h;
+        float az = (u - 0.5f) * 6.2831853f, el = (0.5f - v) * 3.14159265f;
+        F3 d = f3(std::cos(az) * std::cos(el), std::sin(el), std::sin(az) * std::cos(el));
+        float t = 0.5f + 0.5f * d.y;
+        float sd_ = std::max(0.0f, dot(d, sun));
+        float disk = std::pow(sd_, 800.0f) * 40.0f + std::pow(sd_, 8.0f) * 0.5f;
+        float* p = &s.sky[((size_t)y * s.sky_w + x) * 4];
+        p[0] = lerp(0.6f, 0.25f, t) + disk; p[1] = lerp(0.6f, 0.45f, t) + disk * 0.9f; p[2] = lerp(0.55f, 0.9f, t) + disk * 0.7f; p[3] = 1.0f;
+    }
+}
+
 // ---- C5: instanced ------------------------------------------------------------------------------------------
 static void gen_instanced(rt2h_scene& s, float scale, uint64_t seed) {
     const uint32_t sd = (uint32_t)(0x5254325FULL + 5 + seed);
@@ -467,20 +484,7 @@ static void gen_instanced(rt2h_scene& s, float scale, uint64_t seed) {
         float rows[12] = { m[0], m[4], m[8], m[12], m[1], m[5], m[9], m[13], m[2], m[6], m[10], m[14] };
         s.instances.insert(s.instances.end(), rows, rows + 12);
     }
-    // procedural equirect sky: gradient + sun
-    s.sky_w = std::max(64u, (uint32_t)(2048 * std::min(1.0f, scale * 2))); s.sky_h = s.sky_w / 2;
-    s.sky.resize((size_t)s.sky_w * s.sky_h * 4);
-    F3 sun = normalize(f3(0.4f, 0.6f, -0.5f));
-    for (uint32_t y = 0; y < s.sky_h; y++) for (uint32_t x = 0; x < s.sky_w; x++) {
-        float u = (x + 0.5f) / s.sky_w, v = (y + 0.5f) / s.sky_h;
-        float az = (u - 0.5f) * 6.2831853f, el = (0.5f - v) * 3.14159265f;
-        F3 d = f3(std::cos(az) * std::cos(el), std::sin(el), std::sin(az) * std::cos(el));
-        float t = 0.5f + 0.5f * d.y;
-        float sd_ = std::max(0.0f, dot(d, sun));
-        float disk = std::pow(sd_, 800.0f) * 40.0f + std::pow(sd_, 8.0f) * 0.5f;
-        float* p = &s.sky[((size_t)y * s.sky_w + x) * 4];
-        p[0] = lerp(0.6f, 0.25f, t) + disk; p[1] = lerp(0.6f, 0.45f, t) + disk * 0.9f; p[2] = lerp(0.55f, 0.9f, t) + disk * 0.7f; p[3] = 1.0f;
-    }
+    gen_sky(s, std::max(64u, (uint32_t)(2048 * std::min(1.0f, scale * 2))));
     float ext = G * CELL * 0.5f;
     float pos[3] = {-ext * 0.6f, 9.0f, -ext * 0.7f}, dir[3] = {-0.6f, 0.3f, -0.74f};
     rt2h_camera_new(&s.cam, pos, dir, 65.0f, 16.0f / 9.0f, 0.1f, 1000.0f);
@@ -687,6 +691,12 @@ void rt2h_free(void* p) { std::free(p); }
 void rt2h_scene_destroy(rt2h_scene* s) { delete s; }
 const rt2_scene_desc* rt2h_scene_desc(const rt2h_scene* s) { return s ? &s->desc : nullptr; }
 void rt2h_scene_camera(const rt2h_scene* s, float aspect_ratio, rt2h_camera* out) { *out = s->cam; if (aspect_ratio > 0) out->aspect_ratio = aspect_ratio; }
+void rt2h_scene_add_procedural_sky(rt2h_scene* s, uint32_t width) {
+    if (!s) return;
+    gen_sky(*s, std::max(8u, std::min(width, 16384u)) & ~1u);
+    s->finish();
+}
+
 uint32_t rt2h_scene_num_lights(const rt2h_scene* s) {
     uint32_t lights = 0;                                                       // model.rs:411-413
     for (size_t g = 0; g < s->geoms.size(); g++) {

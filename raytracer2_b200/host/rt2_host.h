@@ -79,6 +79,9 @@ const rt2_scene_desc* rt2h_scene_desc(const rt2h_scene* s);
 void        rt2h_scene_camera(const rt2h_scene* s, float aspect_ratio, rt2h_camera* out);
 /* number of emissive triangles (Model.lights, src/model.rs:411-413) */
 uint32_t    rt2h_scene_num_lights(const rt2h_scene* s);
+/* Gives any scene the instanced scene's procedural sky (equirect gradient + sun, width x width/2): the reference always has a
+ * sky box (src/main.rs:63), the closed test scenes have none.  Invalidates nothing: the descriptor is refreshed in place. */
+void        rt2h_scene_add_procedural_sky(rt2h_scene* s, uint32_t width);
 uint64_t    rt2h_scene_num_triangles(const rt2h_scene* s);   /* instanced: BLAS tris x instances */
 
 #ifdef __cplusplus

@@ -173,7 +173,19 @@ def test_gbuffer_bit_exact(kind, scale, w, h, brute, frame):
 
 
 def _di_run(kind, scale, w, h, frame, **di):
-    sc, ctx, g, lp = _restir_setup(kind, scale, w, h)
+    sky = di.get("sky", 0)              # > 0: give the scene the procedural sky box of that width (the instanced scene has its own)
+    if sky or kind == rt.SCENE_INSTANCED:
+        sc = rt.Scene(kind, scale, 64, 0)
+        if sky:
+            sc.add_sky(sky)
+        ctx = rt.Renderer(0)
+        rt.Model.from_scene(ctx, sc)
+        d = sc.desc.contents
+        g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights, env_size=(d.sky_width, d.sky_height))
+        g.refrence_mode = 0; g.enable_restir_gi = 0; g.environment = 1
+        lp = rt.LightPasses(ctx, w, h)
+    else:
+        sc, ctx, g, lp = _restir_setup(kind, scale, w, h)
     g.enable_restir_di = 1
     isp = g.restir_di.initial_sampling_params
     isp.num_primary_local_light_samples = di.get("local", 4); isp.num_primary_brdf_samples = di.get("brdf", 1)
@@ -183,11 +195,19 @@ def _di_run(kind, scale, w, h, frame, **di):
     rt.PrepareLightsTasks(ctx).execute()
     rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
     isp.local_light_sampling_mode = di.get("mode", 0)
+    isp.num_primary_environment_samples = di.get("env", 0); isp.environment_map_importance_sampling = di.get("env_is", 0)
     lp.update_uniform(g)
     presampling = di.get("presampling", False)
-    ris = ris_data = None
-    if presampling:                 # K11 fills the tiles the POWER_RIS sampler draws from (its own parity: test_presample_local_lights_bit_exact)
-        lp.execute_presampeling(frame, False)
+    ris = ris_data = env_pdf = None
+    env_dims = (0, 0, 0)
+    has_sky = sc.desc.contents.sky_width != 0
+    if presampling and has_sky and not di.get("skip_env_mips", False):
+        rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.ENVIRONMENT).execute_mip_generation()
+        sw, sh = sc.desc.contents.sky_width, sc.desc.contents.sky_height
+        env_dims = (sw, sh, int(math.ceil(math.log2(max(sw, sh)))) + 1)
+        env_pdf = np.concatenate([m.ravel() for m in _read_mips(ctx, rt.BUF_ENV_PDF_MIP0, *env_dims, np.uint16)])
+    if presampling:                 # K11 fills the tiles the POWER_RIS / environment samplers draw from (its own parity: test_presample_*_bit_exact)
+        lp.execute_presampeling(frame, env_pdf is not None)
         ris = ctx.read(rt.BUF_RIS, np.uint32).reshape(-1, 2)
         ris_data = ctx.read(rt.BUF_RIS_LIGHT_DATA, np.uint32).reshape(-1, 8)
     if di.get("accumulate", 0):     # seed prior lighting so the accumulation branch reads something
@@ -208,7 +228,8 @@ def _di_run(kind, scale, w, h, frame, **di):
     d_in = prior.view(np.uint16).copy() if prior is not None else None
     s_in = prior.view(np.uint16).copy() if prior is not None else None
     res, d16, s16, rays = O.OracleScene(sc.desc).di_fused_resampling(g, frame, w, h, gb, lights, g2l, pdf, pw.value, ph.value, pm.value, pitch,
-                                                                     diffuse_f16=d_in, specular_f16=s_in, flags=oflags, ris=ris, ris_light_data=ris_data)
+                                                                     diffuse_f16=d_in, specular_f16=s_in, flags=oflags, ris=ris, ris_light_data=ris_data,
+                                                                     env_pdf=env_pdf, env_dims=env_dims)
     got_res = ctx.read(rt.BUF_DI_RESERVOIRS, np.uint32).reshape(-1, 6)
     got_d = ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).reshape(h, w, 4)
     got_s = ctx.read(rt.BUF_SPECULAR_F16, np.uint16).reshape(h, w, 4)
@@ -256,6 +277,81 @@ def test_di_power_ris_sampling_bit_exact(kind, scale, w, h, di):
     (res0, _, _, _), _ = _di_run(kind, scale, w, h, 3, **{**di, "presampling": False, "mode": 0})
     ndiff = int((res0[:, 0] != res[:, 0]).sum())
     assert ndiff > (nvalid // 4 if di["mode"] == 1 else 0)      # mode 0: only the environment combine's extra draw differs
+
+
+@pytest.mark.parametrize("kind,scale,w,h,di", [
+    # the instanced scene with its sky on, numPrimaryEnvironmentSamples = 4 (no local lights in this scene)
+    (rt.SCENE_INSTANCED, 0.05, 320, 180, dict(local=0, brdf=1, env=4, env_is=1, final_vis=1, oflags=0, presampling=True)),
+    (rt.SCENE_INSTANCED, 0.05, 200, 120, dict(local=0, brdf=1, env=4, env_is=0, initial_vis=1, final_vis=1, oflags=0, presampling=True)),
+    # lamp + sky: local, environment and BRDF reservoirs all populated (the open Cornell box with the procedural sky box)
+    (rt.SCENE_CORNELL, 1.0, 256, 256, dict(local=4, brdf=1, env=4, env_is=1, final_vis=1, presampling=True, mode=1, sky=256)),
+    (rt.SCENE_CORNELL, 1.0, 200, 120, dict(local=2, brdf=1, env=2, env_is=1, cutoff=0.1, initial_vis=1, final_vis=1, accumulate=1, presampling=True, sky=128)),
+    (rt.SCENE_CORNELL, 1.0, 200, 120, dict(local=2, brdf=2, env=3, env_is=1, final_vis=1, presampling=True, sky=128)),     # 2 BRDF samples: megakernel form
+    (rt.SCENE_CORNELL, 1.0, 200, 120, dict(local=4, brdf=1, env=0, env_is=1, final_vis=1, presampling=True, sky=128)),     # the sky only through BRDF misses
+    (rt.SCENE_MANYLIGHT, 0.2, 320, 180, dict(local=8, brdf=1, env=4, env_is=1, final_vis=1, oflags=0, presampling=True, mode=1, sky=512)),
+])
+def test_di_environment_map_sampling_bit_exact(kind, scale, w, h, di):
+    """SURVEY §8f N3, second half: RTXDI_SampleEnvironmentMap (InitialSamplingFunctions.hlsli:465-499) drawing from K11's environment
+    tiles, the BRDF-miss environment branch (:556-564) and RAB_EvaluateEnvironmentMapSamplingPdf (bridge :397-418), with the
+    environment light K10 writes at lights + 1 (Q7 pinned to intent)."""
+    (res, d16, s16, rays), (rres, rd16, rs16, rrays) = _di_run(kind, scale, w, h, 3, **di)
+    valid = rres[:, 0] != 0
+    nvalid = int(valid.sum())
+    assert nvalid > 0 and rays == rrays
+    tol = max(2, w * h // 20000)     # sky lookups go through atan2 / asin in binary64 on both sides: a last-bit difference moves a uv by one ulp
+    bad = np.flatnonzero((res != rres).any(axis=1))
+    assert len(bad) <= tol, f"{len(bad)} reservoirs differ (of {nvalid} valid), first {bad[:4]}"
+    assert int((d16 != rd16).any(axis=2).sum()) <= tol and int((s16 != rs16).any(axis=2).sum()) <= tol
+    f = d16.view(np.float16)[:, :, :3].astype(np.float32)
+    assert np.isfinite(f).all() and f.max() > 0
+    # the environment light is among the selected lights
+    n_lights = int(rres[valid, 0].max() & 0x7fffffff) - 1 if kind == rt.SCENE_INSTANCED else None
+    env_index = (rres[valid, 0] & 0x7fffffff).max()
+    n_env = int(((res[:, 0] & 0x7fffffff) == env_index).sum())
+    assert n_env > nvalid // 20, (n_env, nvalid)
+    if n_lights is not None:
+        assert n_lights == 0
+
+
+def test_environment_map_sampling_needs_its_inputs():
+    w, h = 96, 64
+    sc = rt.Scene(rt.SCENE_INSTANCED, 0.05, 16, 0)
+    d = sc.desc.contents
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights, env_size=(d.sky_width, d.sky_height))
+    g.refrence_mode = 0; g.enable_restir_gi = 0; g.enable_restir_di = 1; g.environment = 1
+    isp = g.restir_di.initial_sampling_params
+    isp.num_primary_local_light_samples = 0; isp.num_primary_brdf_samples = 1; isp.num_primary_environment_samples = 4
+    lp = rt.LightPasses(ctx, w, h)
+    lp.update_uniform(g)
+    pre = rt.LaunchParams(flags=rt.LAUNCH_PRESAMPLING)
+    with pytest.raises(rt.Rt2Error, match="compiled out"):
+        lp.execute(1)                                   # the shipped build has no environment reservoir
+    with pytest.raises(rt.Rt2Error, match="rt2_prepare_lights"):
+        lp.execute(1, pre)                              # K10 writes the environment light
+    rt.PrepareLightsTasks(ctx).execute()
+    lights = ctx.read(rt.BUF_LIGHT_INFO, np.uint32).reshape(-1, 12)
+    assert lights.shape[0] == sc.num_lights + 2 and lights[-1, 3] >> 24 == 6
+    ref = O.OracleScene(sc.desc).prepare_lights(0, 0, env=True)[2]
+    assert np.array_equal(lights, ref)
+    with pytest.raises(rt.Rt2Error, match="rt2_generate_mips"):
+        lp.execute(1, pre)
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.ENVIRONMENT).execute_mip_generation()
+    with pytest.raises(rt.Rt2Error, match="rt2_presample"):
+        lp.execute(1, pre)
+    lp.execute_presampeling(1, True)
+    lp.execute(1, pre)
+    g.light_buffer_params.environment_light_params.light_index = sc.num_lights + 5
+    lp.update_uniform(g)
+    with pytest.raises(rt.Rt2Error, match="lights \\+ 1"):
+        lp.execute(1, pre)
+    # lightPresent == 0: no environment light, numPrimaryEnvironmentSamples is then inert (RTXDI_SampleEnvironmentMap returns at :477)
+    g.light_buffer_params.environment_light_params.light_present = 0
+    lp.update_uniform(g)
+    lp.execute(1, pre)
+    assert not ctx.read(rt.BUF_DI_RESERVOIRS, np.uint32).reshape(-1, 6)[:, 0].any()
+    ctx.close()
 
 
 def test_power_ris_needs_presampled_tiles():

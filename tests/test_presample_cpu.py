@@ -3,6 +3,7 @@ PDF mip pyramid must draw light i with probability power_i / sum(power) and repo
 import ctypes as C
 
 import numpy as np
+import pytest
 
 import raytracer2_b200 as rt
 from oracle import oracle_ffi as O
@@ -144,3 +145,137 @@ def test_power_ris_light_sampling_is_an_unbiased_alternative_to_uniform_selectio
     r_plain = osc.di_fused_resampling(g, 1, w, h, gb, lights, g2l, packed, *dims, pitch)[0]
     r_pre = osc.di_fused_resampling(g, 1, w, h, gb, lights, g2l, packed, *dims, pitch, flags=O.ORC_PRESAMPLING)[0]
     assert not np.array_equal(r_plain, r_pre)
+
+
+def _env_inputs(sc, w, h):
+    """gconst + oracle inputs of a scene with a sky: light list with the environment light at lights + 1, both PDF pyramids."""
+    import math
+    d = sc.desc.contents
+    sw, sh = d.sky_width, d.sky_height
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights, env_size=(sw, sh))
+    g.environment = 1
+    osc = O.OracleScene(sc.desc)
+    pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
+    dims = (pw.value, ph.value, pm.value)
+    tasks, g2l, lights, pdf0 = osc.prepare_lights(dims[0], dims[1], env=True)
+    packed = np.zeros(sum(a * b for a, b in O.mip_dims(*dims)), np.float32)
+    packed[:dims[0] * dims[1]] = pdf0.ravel()
+    osc.generate_mips(0, packed, *dims)
+    emips = int(math.ceil(math.log2(max(sw, sh)))) + 1
+    epacked = np.zeros(sum(a * b for a, b in O.mip_dims(sw, sh, emips)), np.uint16)
+    osc.generate_mips(1, epacked, sw, sh, emips)
+    return g, osc, g2l, lights, packed, dims, epacked, (sw, sh, emips)
+
+
+def test_environment_light_record():
+    """The record K10 writes at lights + 1 (SURVEY Q7 pinned to intent): type kEnvironment, radiance scale 1 through packLightColor,
+    rotation 0.25 turns | importance sampled, the PDF texture's size."""
+    sc = rt.Scene(rt.SCENE_CORNELL, 1.0, 16, 0).add_sky(256)
+    g, osc, g2l, lights, packed, dims, epacked, edims = _env_inputs(sc, 32, 32)
+    assert lights.shape == (sc.num_lights + 2, 12)
+    assert g.light_buffer_params.environment_light_params.light_present == 1
+    assert g.light_buffer_params.environment_light_params.light_index == sc.num_lights + 1          # src/main.rs:381-386
+    env = lights[sc.num_lights + 1]
+    assert not lights[sc.num_lights].any()
+    assert env[3] >> 24 == 6 and env[3] & 0xffffff == 0xffffff                                       # kEnvironment, colour 1,1,1
+    assert env[4] == 0 and env[5] == 256 | (128 << 16)
+    assert env[6] == (1 << 16) | int(np.float16(0.25).view(np.uint16))
+    scale = 2.0 ** ((int(env[7]) - 1) / 65534.0 * 48.0 - 8.0)                                        # unpackLightRadiance
+    assert 1.0 <= scale < 1.001
+    # a scene without a sky gets no environment record, whatever the capacity
+    sc2 = rt.Scene(rt.SCENE_CORNELL, 1.0, 16, 0)
+    l2 = O.OracleScene(sc2.desc).prepare_lights(dims[0], dims[1], env=True)[2]
+    assert not l2[sc2.num_lights:].any()
+
+
+@pytest.mark.parametrize("scene,local", [("instanced", 0), ("cornell+sky", 2)])
+def test_environment_map_sampling_agrees_with_the_path_tracers_sky_lighting(scene, local):
+    """SURVEY §8f N3, second half: RTXDI_SampleEnvironmentMap (InitialSamplingFunctions.hlsli:465-499) fed by K11's environment tiles,
+    plus the BRDF-miss environment branch (:556-564), MIS-combined with the local-light and BRDF reservoirs.  E[DI diffuse] * albedo
+    must equal the direct lighting (emitters + sky) the brute-force path tracer K1 sees: K1(2 bounces) - K1(1 bounce) — the same
+    cross-check, with the same 5 % tolerance, as test_di_light_sampling_agrees_with_brute_force_path_tracer."""
+    if scene == "instanced":
+        w, h = 48, 27
+        sc = rt.Scene(rt.SCENE_INSTANCED, 0.125, 16, 0)
+    else:
+        w = h = 40
+        sc = rt.Scene(rt.SCENE_CORNELL, 1.0, 16, 0).add_sky(256)
+    g, osc, g2l, lights, packed, dims, epacked, edims = _env_inputs(sc, w, h)
+    gb = osc.gbuffer(g, w, h)
+    g.refrence_mode = 0; g.enable_restir_gi = 0; g.enable_restir_di = 1
+    isp = g.restir_di.initial_sampling_params
+    isp.num_primary_local_light_samples = local; isp.num_primary_brdf_samples = 1; isp.num_primary_environment_samples = 4
+    isp.environment_map_importance_sampling = 1
+    g.restir_di.shading_params.enable_final_visibility = 1
+    pitch = g.restir_di.reservoir_buffer_params.reservoir_array_pitch
+    frames = 32
+    acc = np.zeros((h, w, 3)); n_env = n_valid = 0
+    for f in range(1, frames + 1):
+        ris, data = O.presample(g, f, 0, packed, *dims, lights)
+        ris, data = O.presample(g, f, 1, epacked, *edims, ris=ris, ris_light_data=data)
+        res, d16, s16, rays = osc.di_fused_resampling(g, f, w, h, gb, lights, g2l, packed, *dims, pitch, flags=O.ORC_PRESAMPLING,
+                                                      ris=ris, ris_light_data=data, env_pdf=epacked, env_dims=edims)
+        acc += d16.view(np.float16)[:, :, :3].astype(np.float64)
+        valid = res[:, 0] != 0
+        n_valid += int(valid.sum()); n_env += int(((res[valid, 0] & 0x7fffffff) == sc.num_lights + 1).sum())
+    assert n_env > 0.3 * n_valid                          # the environment light really is selected
+    if local:
+        assert n_env < n_valid                            # ... and so are the lamp's triangles
+    L = O.lib()
+    albedo = np.zeros((h, w, 3), np.float32); tmp = np.zeros(3, np.float32)
+    for y in range(h):
+        for x in range(w):
+            L.orc_unpack_r11g11b10(int(gb["diffuse_albedo"][y, x]), tmp.ctypes.data_as(C.c_void_p)); albedo[y, x] = tmp
+    direct_di = acc / frames * albedo
+    g.refrence_mode = 1
+    k2 = np.zeros((h, w, 3)); k1 = np.zeros((h, w, 3))
+    for f in range(1, 9):
+        k2 += osc.render_reference(g, f, w, h, spp=64, max_bounces=2)[2][:, :, :3]
+        k1 += osc.render_reference(g, f, w, h, spp=1, max_bounces=1)[2][:, :, :3]
+    direct_pt = (k2 - k1) / 8
+    m = (gb["emissive"].view(np.float16)[:, :, 0] == 0) & (gb["depth"] < 1e4)
+    a, b = direct_di[m].mean(), direct_pt[m].mean()
+    assert b > 0 and abs(a - b) < 0.05 * b, (a, b)
+
+
+def test_environment_light_through_brdf_misses_only_and_rejections():
+    """numPrimaryEnvironmentSamples == 0 (what K5 passes, shade_secondary_surfaces.rgen:69): the sky is still found by BRDF rays that miss
+    (InitialSamplingFunctions.hlsli:556-564) and weighted by RAB_EvaluateEnvironmentMapSamplingPdf — same expectation, more noise."""
+    w, h = 48, 27
+    sc = rt.Scene(rt.SCENE_INSTANCED, 0.125, 16, 0)
+    g, osc, g2l, lights, packed, dims, epacked, edims = _env_inputs(sc, w, h)
+    gb = osc.gbuffer(g, w, h)
+    g.refrence_mode = 0; g.enable_restir_gi = 0; g.enable_restir_di = 1
+    isp = g.restir_di.initial_sampling_params
+    isp.num_primary_local_light_samples = 0; isp.num_primary_brdf_samples = 1; isp.num_primary_environment_samples = 0
+    g.restir_di.shading_params.enable_final_visibility = 1
+    pitch = g.restir_di.reservoir_buffer_params.reservoir_array_pitch
+    run = lambda f, **kw: osc.di_fused_resampling(g, f, w, h, gb, lights, g2l, packed, *dims, pitch, **kw)
+    acc = {0: np.zeros((h, w, 3)), 1: np.zeros((h, w, 3))}
+    for imp in (0, 1):                 # environmentMapImportanceSampling only changes the source pdf BRDF samples report (1.0 vs the texel's)
+        isp.environment_map_importance_sampling = imp
+        for f in range(1, 41):
+            res, d16, _, _ = run(f, flags=O.ORC_PRESAMPLING, env_pdf=epacked, env_dims=edims)
+            acc[imp] += d16.view(np.float16)[:, :, :3].astype(np.float64)
+            valid = res[:, 0] != 0
+            assert valid.any() and ((res[valid, 0] & 0x7fffffff) == sc.num_lights + 1).all()
+    a, b = acc[0].mean(), acc[1].mean()
+    assert a > 0 and abs(a - b) < 0.05 * a, (a, b)          # one technique only: the MIS weight cancels whatever the source pdf is
+    # as shipped (no ORC_PRESAMPLING) there is no environment light: nothing is selected in a scene without emitters (Q7)
+    res, d16, _, _ = run(1)
+    assert not res[:, 0].any() and not d16.any()
+    # environment samples need the presampling build; the environment light needs its record and its PDF pyramid
+    isp.num_primary_environment_samples = 2
+    with pytest.raises(O.OracleError) as e:
+        run(1)
+    assert e.value.args[0] == -3
+    with pytest.raises(O.OracleError) as e:
+        run(1, flags=O.ORC_PRESAMPLING)                      # no pyramid
+    assert e.value.args[0] == -5
+    with pytest.raises(O.OracleError) as e:
+        osc.di_fused_resampling(g, 1, w, h, gb, lights[:1], g2l, packed, *dims, pitch, flags=O.ORC_PRESAMPLING, env_pdf=epacked, env_dims=edims)
+    assert e.value.args[0] == -5                             # light buffer too short for index lights + 1
+    with pytest.raises(O.OracleError) as e:
+        run(1, flags=O.ORC_PRESAMPLING, env_pdf=epacked, env_dims=edims)     # environment samples without K11's tiles
+    assert e.value.args[0] == -4
