@@ -193,7 +193,10 @@ typedef struct rt2_launch_params {
 #define RT2_LAUNCH_TRIG_LIBDEVICE 1u  /* use CUDA sinf/cosf/atan2f/asinf instead of the pinned polynomials */
 #define RT2_LAUNCH_PRESAMPLING    4u  /* ReSTIR light sampler as compiled with RTXDI_ENABLE_PRESAMPLING 1 (the reference ships 0,
                                        * RtxdiApplicationBridge.glsl:12): local_light_sampling_mode 1 = POWER_RIS draws from the tiles
-                                       * rt2_presample(…, 0) filled (InitialSamplingFunctions.hlsli:241-254) */
+                                       * rt2_presample(…, 0) filled (InitialSamplingFunctions.hlsli:241-254); the environment light
+                                       * rt2_prepare_lights writes at index lights + 1 for scenes with a sky (src/main.rs:381-386) exists:
+                                       * num_primary_environment_samples candidates per pixel from the tiles rt2_presample(…, 1) filled
+                                       * (:465-499, after rt2_generate_mips(1)), and BRDF rays that miss select it (:556-564) */
 #define RT2_LAUNCH_PROFILE        2u  /* bracket every kernel launch with CUDA events (rt2_stats.trace_ns/shade_ns) */
 
 /* Buffers readable with rt2_read (all row-major W x H unless noted). */

@@ -18,11 +18,14 @@ GB_KEYS = [("depth", rt.BUF_GBUFFER_DEPTH, np.float32, 1), ("normals", rt.BUF_GB
            ("specular_rough", rt.BUF_GBUFFER_SPECULAR_ROUGH, np.uint32, 1)]
 
 
-def _ctx(kind, scale, w, h, tex=64):
+def _ctx(kind, scale, w, h, tex=64, sky=0):
     sc = rt.Scene(kind, scale, tex, 0)
+    if sky:
+        sc.add_sky(sky)
     ctx = rt.Renderer(0)
     rt.Model.from_scene(ctx, sc)
-    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+    d = sc.desc.contents
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights, env_size=(d.sky_width, d.sky_height))
     g.refrence_mode = 0
     return sc, ctx, g, rt.LightPasses(ctx, w, h)
 
@@ -39,8 +42,14 @@ def _light_inputs(sc, ctx):
             "pdf_packed": np.concatenate([m.ravel() for m in mips]), "pdf_dims": (pw.value, ph.value, pm.value)}
 
 
-def _run(kind, scale, w, h, frames=(1,), di=0, final_vis=0, mis=1, env=0, additive=1, oflags=O.ORC_BRUTE_FORCE, local=2, brdf=1):
-    sc, ctx, g, lp = _ctx(kind, scale, w, h)
+def _run(kind, scale, w, h, frames=(1,), di=0, final_vis=0, mis=1, env=0, additive=1, oflags=O.ORC_BRUTE_FORCE, local=2, brdf=1, sky=0, presampling=False,
+         env_samples=0):
+    """sky: attach the procedural sky box of that width.  presampling: K11 every frame + RT2_LAUNCH_PRESAMPLING / ORC_PRESAMPLING — the sampler's
+    RTXDI_ENABLE_PRESAMPLING 1 build, in which the environment light K10 writes at lights + 1 exists (K9 draws env_samples candidates from its tiles,
+    K5 finds it through BRDF rays that miss)."""
+    sc, ctx, g, lp = _ctx(kind, scale, w, h, sky=sky)
+    g.restir_di.initial_sampling_params.num_primary_environment_samples = env_samples
+    g.restir_di.initial_sampling_params.environment_map_importance_sampling = 1 if presampling else 0
     g.enable_restir_gi = 1; g.enable_restir_di = di; g.environment = env; g.enable_brdf_additive_blend = additive
     g.restir_gi.final_shading_params.enable_final_visibility = final_vis
     g.restir_gi.final_shading_params.enable_final_mis = mis
@@ -50,6 +59,15 @@ def _run(kind, scale, w, h, frames=(1,), di=0, final_vis=0, mis=1, env=0, additi
     if di:
         rt.PrepareLightsTasks(ctx).execute()
         rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    env_pdf, env_dims = None, (0, 0, 0)
+    if presampling:
+        oflags |= O.ORC_PRESAMPLING
+        if sc.desc.contents.sky_width:
+            import math
+            rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.ENVIRONMENT).execute_mip_generation()
+            sw, sh = sc.desc.contents.sky_width, sc.desc.contents.sky_height
+            env_dims = (sw, sh, int(math.ceil(math.log2(max(sw, sh)))) + 1)
+            env_pdf = np.concatenate([ctx.read(rt.BUF_ENV_PDF_MIP0 + k, np.uint16).ravel() for k in range(env_dims[2])])
     osc = O.OracleScene(sc.desc)
     pitch = g.restir_gi.reservoir_buffer_params.reservoir_array_pitch
     state = None
@@ -57,12 +75,17 @@ def _run(kind, scale, w, h, frames=(1,), di=0, final_vis=0, mis=1, env=0, additi
     for frame in frames:
         g.frame = frame
         lp.update_uniform(g)
-        lp.execute(frame)
+        if presampling:
+            lp.execute_presampeling(frame, env_pdf is not None)
+        lp.execute(frame, rt.LaunchParams(flags=rt.LAUNCH_PRESAMPLING) if presampling else None)
         gb = _read_gb(ctx, w, h)
         got = {"secondary": ctx.read(rt.BUF_SECONDARY_GBUFFER, np.uint32).reshape(-1, 12), "gi_reservoirs": ctx.read(rt.BUF_GI_RESERVOIRS, np.uint32).reshape(-1, 8),
                "diffuse": ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).reshape(h, w, 4), "specular": ctx.read(rt.BUF_SPECULAR_F16, np.uint16).reshape(h, w, 4)}
         st = ctx.stats()
         li = _light_inputs(sc, ctx) if di else None
+        if di and presampling:
+            li.update(ris=ctx.read(rt.BUF_RIS, np.uint32).reshape(-1, 2), ris_light_data=ctx.read(rt.BUF_RIS_LIGHT_DATA, np.uint32).reshape(-1, 8),
+                      env_pdf=env_pdf, env_dims=env_dims)
         if state is None:
             state = {"secondary": np.zeros((pitch, 12), np.uint32), "gi_reservoirs": np.zeros((pitch * 2, 8), np.uint32),
                      "diffuse": np.zeros((h, w, 4), np.uint16), "specular": np.zeros((h, w, 4), np.uint16)}
@@ -70,7 +93,8 @@ def _run(kind, scale, w, h, frames=(1,), di=0, final_vis=0, mis=1, env=0, additi
         if di:
             _, _, _, rays_di = osc.di_fused_resampling(g, frame, w, h, gb, li["lights"], li["geom_to_light"], li["pdf_packed"], *li["pdf_dims"],
                                                        g.restir_di.reservoir_buffer_params.reservoir_array_pitch,
-                                                       diffuse_f16=state["diffuse"], specular_f16=state["specular"], flags=oflags)
+                                                       diffuse_f16=state["diffuse"], specular_f16=state["specular"], flags=oflags,
+                                                       ris=li.get("ris"), ris_light_data=li.get("ris_light_data"), env_pdf=li.get("env_pdf"), env_dims=li.get("env_dims", (0, 0, 0)))
         state = osc.gi_chain(g, frame, w, h, gb, pitch, light_inputs=li, state=state, flags=oflags)
         out.append((got, {k: v.copy() for k, v in state.items() if k != "rays"}, st.rays_traced - w * h, rays_di + sum(state["rays"]), gb))
     ctx.close()
@@ -94,6 +118,9 @@ def _check(got, ref, w, h, tol):
     (rt.SCENE_INSTANCED, 0.05, 320, 180, dict(env=1, oflags=0)),                       # open scene under a sky: environment secondary surfaces
     (rt.SCENE_CORNELL, 1.0, 256, 256, dict(di=1)),                                     # DI on: K5 samples the light list at the secondary hit
     (rt.SCENE_MANYLIGHT, 0.2, 320, 180, dict(di=1, final_vis=1, oflags=0)),
+    # DI + GI under a sky with the environment light (presampling build): K9 draws environment candidates, K5's BRDF rays that miss select it
+    (rt.SCENE_CORNELL, 1.0, 200, 120, dict(di=1, env=1, sky=128, presampling=True, env_samples=2)),
+    (rt.SCENE_INSTANCED, 0.05, 320, 180, dict(di=1, env=1, oflags=0, presampling=True, env_samples=4, local=0)),
 ])
 def test_gi_chain_bit_exact(kind, scale, w, h, kw):
     (got, ref, rays, rrays, gb), = _run(kind, scale, w, h, **kw)
