@@ -70,6 +70,40 @@ __global__ void __launch_bounds__(256) k_unpermute_bands(const uint4* __restrict
     }
 }
 
+// ---- in-frame exchange of per-pixel buffers (K6 / K7 under sharding) ---------------------------------------------------------------
+// K6 reads the previous frame's G-buffer and GI reservoirs wherever the motion vectors point, K7 the current ones within its
+// sampling radius (rtxdi/GIResamplingFunctions.hlsli:186-359, 391-553) — rows other ranks own.  Each rank packs the entries of ITS
+// pixels, one ncclAllGather moves them, each rank writes the other ranks' entries where they belong.  An entry is `words` uint32;
+// layout 0 = row-major W x H, 1 = the reservoirs' 16 x 16 block-linear order (RTXDI_ReservoirPositionToPointer, RtxdiHelpers.hlsli:75-88).
+struct ExchangeSeg { uint32_t* base; uint32_t words, layout; size_t slot_offset_words; };
+
+__device__ __forceinline__ size_t exchange_entry(uint32_t x, uint32_t y, uint32_t width, uint32_t layout, uint32_t block_row_pitch) {
+    return layout == 0u ? (size_t)y * width + x : (size_t)(y >> 4) * block_row_pitch + (size_t)(x >> 4) * 256u + (y & 15u) * 16u + (x & 15u);
+}
+__global__ void __launch_bounds__(256) k_exchange_pack(ExchangeSeg seg, uint32_t* __restrict__ send, uint32_t width, uint32_t local_rows, uint32_t band_rows,
+                                                       uint32_t rank, uint32_t world, uint32_t block_row_pitch) {
+    const uint64_t n = (uint64_t)local_rows * width * seg.words;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t e = i / seg.words; const uint32_t wd = (uint32_t)(i % seg.words);
+        const uint32_t packed_row = (uint32_t)(e / width), x = (uint32_t)(e % width);
+        const uint32_t y = ((packed_row / band_rows) * world + rank) * band_rows + packed_row % band_rows;
+        send[seg.slot_offset_words + i] = seg.base[exchange_entry(x, y, width, seg.layout, block_row_pitch) * seg.words + wd];
+    }
+}
+__global__ void __launch_bounds__(256) k_exchange_unpack(ExchangeSeg seg, const uint32_t* __restrict__ recv, size_t slot_words, uint32_t width, uint32_t height,
+                                                         uint32_t band_rows, uint32_t rank, uint32_t world, uint32_t block_row_pitch) {
+    const uint64_t n = (uint64_t)height * width * seg.words;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t e = i / seg.words; const uint32_t wd = (uint32_t)(i % seg.words);
+        const uint32_t y = (uint32_t)(e / width), x = (uint32_t)(e % width);
+        const uint32_t band = y / band_rows, owner = band % world;
+        if (owner == rank) continue;                                   // this rank's own entries are already in place
+        const uint32_t packed_row = (band / world) * band_rows + y % band_rows;
+        seg.base[exchange_entry(x, y, width, seg.layout, block_row_pitch) * seg.words + wd] =
+            recv[(size_t)owner * slot_words + seg.slot_offset_words + ((size_t)packed_row * width + x) * seg.words + wd];
+    }
+}
+
 }  // namespace rt2
 
 using namespace rt2;
@@ -86,10 +120,12 @@ struct rt2_group {
         void* send[RT2_GROUP_BUFFERS] = {}; void* recv[RT2_GROUP_BUFFERS] = {}; void* assembled[RT2_GROUP_BUFFERS] = {};
         cudaEvent_t ready[RT2_GROUP_BUFFERS] = {}, done[RT2_GROUP_BUFFERS] = {}; cudaEvent_t tail = nullptr;
         size_t cap_slot = 0, cap_frame = 0;
+        uint32_t* xsend = nullptr; uint32_t* xrecv = nullptr; size_t cap_xslot = 0;     // in-frame exchange staging (K6 / K7), on the render stream
     };
     std::vector<Lane> lanes;
     uint32_t width = 0, height = 0;
     uint64_t gathers = 0;                             // gathers issued; buffer of gather k is k % RT2_GROUP_BUFFERS
+    uint64_t exchanges = 0;                           // in-frame exchanges issued (K6 / K7 inputs)
     size_t frame_bytes = 0;                           // of the last gathered buffer
     std::string last_error;
 };
@@ -152,6 +188,8 @@ int rt2_group_destroy(rt2_group* g) {
                 if (L.done[b]) cudaEventDestroy(L.done[b]);
             }
             if (L.tail) cudaEventDestroy(L.tail);
+            if (L.xsend) cudaFree(L.xsend);
+            if (L.xrecv) cudaFree(L.xrecv);
         }
         if (i < g->comm_streams.size() && g->comm_streams[i]) cudaStreamDestroy(g->comm_streams[i]);
         rt2_destroy(g->ctxs[i]);
@@ -258,17 +296,117 @@ int rt2_group_sync(rt2_group* g) {
     return RT2_OK;
 }
 
+}  // extern "C"
+
+// One exchange: `segs(i)` lists local context i's buffers (same shapes on every rank).  Runs on the render streams: the passes
+// behind it wait for it anyway.
+template <typename SegsOf>
+static int group_exchange(rt2_group* g, SegsOf segs_of) {
+    const size_t n = g->ctxs.size();
+    const uint32_t world = (uint32_t)g->world, W = g->width, H = g->height;
+    BandPlanC plan; plan.height = H; plan.world = world;
+    const uint32_t max_rows = plan.max_rows();
+    std::vector<std::vector<ExchangeSeg>> all(n);
+    size_t slot_words = 0;
+    for (size_t i = 0; i < n; i++) {
+        all[i] = segs_of(i);
+        size_t off = 0;
+        for (ExchangeSeg& sg : all[i]) { sg.slot_offset_words = off; off += (size_t)max_rows * W * sg.words; }
+        slot_words = off;
+    }
+    for (size_t i = 0; i < n; i++) {
+        rt2_group::Lane& L = g->lanes[i];
+        rt2_ctx* c = g->ctxs[i];
+        RT2_GCUDA(g, cudaSetDevice(c->device));
+        if (L.cap_xslot < slot_words) {
+            RT2_GCUDA(g, cudaStreamSynchronize(c->stream));
+            if (L.xsend) cudaFree(L.xsend); if (L.xrecv) cudaFree(L.xrecv);
+            L.xsend = L.xrecv = nullptr;
+            RT2_GCUDA(g, cudaMalloc((void**)&L.xsend, slot_words * 4)); RT2_GCUDA(g, cudaMalloc((void**)&L.xrecv, slot_words * 4 * world));
+            RT2_GCUDA(g, cudaMemsetAsync(L.xsend, 0, slot_words * 4, c->stream));
+            L.cap_xslot = slot_words;
+        }
+        const uint32_t rank = (uint32_t)g->first_rank + (uint32_t)i, rows = plan.rows(rank);
+        for (const ExchangeSeg& sg : all[i]) {
+            const uint64_t items = (uint64_t)rows * W * sg.words;
+            const int blocks = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8u, (items + 255u) / 256u);
+            k_exchange_pack<<<std::max(blocks, 1), 256, 0, c->stream>>>(sg, L.xsend, W, rows, RT2_GROUP_BAND_ROWS, rank, world, c->fb.reservoir_block_row_pitch);
+        }
+        RT2_GCUDA(g, cudaGetLastError());
+    }
+    RT2_GNCCL(g, g_nccl.GroupStart());
+    for (size_t i = 0; i < n; i++) {
+        int r = g_nccl.AllGather(g->lanes[i].xsend, g->lanes[i].xrecv, slot_words * 4, NCCL_INT8, g->comms[i], g->ctxs[i]->stream);
+        if (r != 0) { g_nccl.GroupEnd(); return gfail(g, RT2_E_CUDA, std::string("ncclAllGather: ") + g_nccl.GetErrorString(r)); }
+    }
+    RT2_GNCCL(g, g_nccl.GroupEnd());
+    for (size_t i = 0; i < n; i++) {
+        rt2_ctx* c = g->ctxs[i];
+        RT2_GCUDA(g, cudaSetDevice(c->device));
+        const uint32_t rank = (uint32_t)g->first_rank + (uint32_t)i;
+        for (const ExchangeSeg& sg : all[i]) {
+            const uint64_t items = (uint64_t)H * W * sg.words;
+            const int blocks = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8u, (items + 255u) / 256u);
+            k_exchange_unpack<<<std::max(blocks, 1), 256, 0, c->stream>>>(sg, g->lanes[i].xrecv, slot_words, W, H, RT2_GROUP_BAND_ROWS, rank, world, c->fb.reservoir_block_row_pitch);
+        }
+        RT2_GCUDA(g, cudaGetLastError());
+    }
+    g->exchanges++;
+    return RT2_OK;
+}
+
+extern "C" {
+
 int rt2_group_render(rt2_group* g, uint32_t frame, const rt2_launch_params* params, int gather_which) {
     if (!g) return RT2_E_INVALID;
     if (!g->height) return gfail(g, RT2_E_STATE, "rt2_group_render before rt2_group_resize");
     const size_t n = g->ctxs.size();
     const uint32_t world = (uint32_t)g->world;
-    for (size_t i = 0; i < n; i++) {
-        rt2_launch_params lp{};
-        if (params) lp = *params;
-        lp.band_rows = world > 1u ? RT2_GROUP_BAND_ROWS : 0u; lp.band_rank = (uint32_t)g->first_rank + (uint32_t)i; lp.band_world = world > 1u ? world : 0u;
-        if (world <= 1u) lp.band_rank = 0u;
-        RT2_GCTX(g, g->ctxs[i], rt2_render(g->ctxs[i], frame, &lp));
+    auto render_all = [&](uint32_t phase) -> int {
+        for (size_t i = 0; i < n; i++) {
+            rt2_launch_params lp{};
+            if (params) lp = *params;
+            lp.band_rows = world > 1u ? RT2_GROUP_BAND_ROWS : 0u; lp.band_rank = (uint32_t)g->first_rank + (uint32_t)i; lp.band_world = world > 1u ? world : 0u;
+            if (world <= 1u) lp.band_rank = 0u;
+            g->ctxs[i]->restir_phase = phase;
+            const int rc = rt2_render(g->ctxs[i], frame, &lp);
+            g->ctxs[i]->restir_phase = 0u;
+            if (rc != RT2_OK) return gfail(g, rc, std::string("rt2_render: ") + rt2_last_error(g->ctxs[i]));
+        }
+        return RT2_OK;
+    };
+    // GI temporal / spatial resampling (K6 / K7) under sharding: the frame runs in phases with the inputs those two passes read at
+    // other ranks' pixels exchanged in between (every rank's GConst is the same: rt2_group_set_constants)
+    const rt2_gconst& gc = g->ctxs[0]->gconst;
+    const bool temporal = gc.enable_temporal_resampling == 1u, spatial = gc.enable_spatial_resampling == 1u;
+    if (world > 1u && gc.refrence_mode != 1u && gc.enable_restir_gi == 1u && (temporal || spatial)) {
+        const uint32_t cur = frame & 1u;                                // the G-buffer set K3 writes this frame (src/light_passes.rs:565-577)
+        auto page = [&](size_t i, uint32_t index) {
+            FrameBuffers& f = g->ctxs[i]->fb;
+            return ExchangeSeg{reinterpret_cast<uint32_t*>(f.gi_reservoirs + 2 * (size_t)f.reservoir_array_pitch * index), 8u, 1u, 0};
+        };
+        int rc = render_all(1u);                                        // K3, K9, K4, K5 on the rank's bands
+        if (rc) return rc;
+        if (temporal) {                                                 // K6 gathers from the previous frame's reservoirs; its G-buffer was exchanged last frame
+            const uint32_t tin = gc.restir_gi.buffer_indices.temporal_resampling_input_buffer_index;
+            if ((rc = group_exchange(g, [&](size_t i) { return std::vector<ExchangeSeg>{page(i, tin)}; }))) return rc;
+            if ((rc = render_all(2u))) return rc;
+        }
+        // the current G-buffer: K7's neighbours now, K6's reprojected surfaces next frame; + the page K7 gathers from
+        const uint32_t sin = gc.restir_gi.buffer_indices.spatial_resampling_input_buffer_index;
+        rc = group_exchange(g, [&](size_t i) {
+            FrameBuffers& f = g->ctxs[i]->fb;
+            std::vector<ExchangeSeg> v;
+            void* planes[5] = {f.gb_depth[cur], f.gb_normals[cur], f.gb_geo_normals[cur], f.gb_diffuse_albedo[cur], f.gb_specular_rough[cur]};
+            for (void* p : planes) v.push_back(ExchangeSeg{static_cast<uint32_t*>(p), 1u, 0u, 0});
+            if (spatial) v.push_back(page(i, sin));
+            return v;
+        });
+        if (rc) return rc;
+        if ((rc = render_all(4u))) return rc;                           // K7, K8
+    } else {
+        const int rc = render_all(0u);
+        if (rc) return rc;
     }
     if (gather_which < 0) return RT2_OK;
     return rt2_group_gather(g, gather_which);

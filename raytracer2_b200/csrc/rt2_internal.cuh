@@ -161,6 +161,7 @@ struct rt2_ctx {
     uint64_t device_bytes = 0;
     // lights / pdf textures (K10/K12)
     rt2_light_info* light_info = nullptr; uint32_t light_capacity = 0;   // = the scene's light count
+    uint32_t restir_phase = 0;                                             // set by rt2_group_render around a sharded frame with K6 / K7: which part of render_restir runs (0 = all)
     uint32_t light_records = 0;                                            // records allocated: light_capacity, + 2 with a sky (a zero record and the environment light)
     uint32_t* geom_to_light = nullptr;
     rt2_prepare_lights_task* light_tasks = nullptr; uint32_t num_light_tasks = 0;

@@ -1378,9 +1378,13 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         if (lp.band_rows == 0u || lp.band_rank >= lp.band_world) return fail(ctx, RT2_E_INVALID, "bad band parameters");
         // K3 / K9 / K4 / K5 / K8 are per-pixel independent and shard by rows with no exchange; K6 / K7 read their
         // neighbours' G-buffer and reservoirs across band edges and would need a halo exchange between the ranks
-        if (g.enable_restir_gi == 1u && (g.enable_temporal_resampling == 1u || g.enable_spatial_resampling == 1u))
-            return fail(ctx, RT2_E_INVALID, "GI temporal / spatial resampling reads neighbouring rows: not available with row-band sharding (no halo exchange)");
+        // across band edges (K6 anywhere in the previous frame): rt2_group_render runs the frame in phases and exchanges those inputs between
+        // them (ctx->restir_phase, rt2_group.cu); a plain rt2_render of one band set has nobody to exchange with
+        if (ctx->restir_phase == 0u && g.enable_restir_gi == 1u && (g.enable_temporal_resampling == 1u || g.enable_spatial_resampling == 1u))
+            return fail(ctx, RT2_E_INVALID, "GI temporal / spatial resampling reads neighbouring rows: with row-band sharding it needs the halo exchange rt2_group_render performs");
     }
+    // phases of a sharded frame with resampling: 1 = K3, K9, K4, K5; 2 = K6; 4 = K7, K8.  0 (a plain rt2_render) = everything.
+    const uint32_t ph = ctx->restir_phase ? ctx->restir_phase : 7u;
     int rc = restir_ensure_resources(ctx); if (rc) return rc;
     FrameBuffers& f = ctx->fb;
     // counters: [0..1] rays, [2..3] hits
@@ -1388,7 +1392,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         if (f.counters) { RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(f.counters); f.counters = nullptr; }
         RT2_CUDA(ctx, cudaMalloc((void**)&f.counters, 16 * 4)); f.counter_capacity = 16;
     }
-    RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, 64, ctx->stream));
+    if (ph & 1u) RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, 64, ctx->stream));
     unsigned long long* stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
     unsigned long long* stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
     const uint32_t cur = frame & 1u;                   // ping-pong, src/light_passes.rs:565-577
@@ -1492,11 +1496,11 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     ga.sc = make_scene_refs(ctx); ga.g = ctx->d_gconst; ga.width = f.width; ga.height = f.height; ga.band = band;
     ga.depth = f.gb_depth[cur]; ga.normals = f.gb_normals[cur]; ga.geo_normals = f.gb_geo_normals[cur]; ga.diffuse_albedo = f.gb_diffuse_albedo[cur];
     ga.specular_rough = f.gb_specular_rough[cur]; ga.emissive = f.gb_emissive[cur]; ga.motion = f.motion_vectors; ga.stat_hits = stat_hits;
-    k_gbuffer<<<blocks, 128, 0, ctx->stream>>>(ga); launches++;
+    if (ph & 1u) { k_gbuffer<<<blocks, 128, 0, ctx->stream>>>(ga); launches++; }
     uint64_t static_rays = (uint64_t)f.width * band.local_rows;      // K3: one primary ray per owned pixel
     const GBufferRefs gbrefs{f.gb_depth[cur], f.gb_normals[cur], f.gb_geo_normals[cur], f.gb_diffuse_albedo[cur], f.gb_specular_rough[cur]};
     // ---- K9
-    if (g.enable_restir_di == 1u) {
+    if (g.enable_restir_di == 1u && (ph & 1u)) {
         DIArgs da{};
         da.sc = ga.sc; da.g = ctx->d_gconst; da.width = f.width; da.height = f.height; da.frame = frame; da.band = band;
         da.gb = gbrefs; da.li = lrefs;
@@ -1534,7 +1538,9 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         gi.secondary = f.secondary_gbuffer; gi.reservoirs = f.gi_reservoirs;
         gi.diffuse = f.diffuse_f16; gi.specular = f.specular_f16; gi.diffuse_f32 = f.diffuse_f32;
         gi.stat_rays = stat_rays; gi.stat_hits = stat_hits;
-        if (ctx->gi_megakernels) {
+        if (!(ph & 1u)) {
+            // K4 / K5 ran in an earlier phase of this frame
+        } else if (ctx->gi_megakernels) {
             k_brdf_rays<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
             k_shade_secondary<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
         } else {
@@ -1576,16 +1582,16 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
             ra.motion = f.motion_vectors; ra.neighbor_offsets = f.neighbor_offsets; ra.reservoirs = f.gi_reservoirs;
             ra.stat_rays = stat_rays; ra.stat_hits = stat_hits;
             // the reference records K6 and K7 without a barrier between them (src/light_passes.rs:642-647); stream order = K6 then K7
-            if (g.enable_temporal_resampling == 1u) { k_gi_temporal<<<blocks, 128, 0, ctx->stream>>>(ra); launches++; }
-            if (g.enable_spatial_resampling == 1u) { k_gi_spatial<<<blocks, 128, 0, ctx->stream>>>(ra); launches++; }
+            if (g.enable_temporal_resampling == 1u && (ph & 2u)) { k_gi_temporal<<<blocks, 128, 0, ctx->stream>>>(ra); launches++; }
+            if (g.enable_spatial_resampling == 1u && (ph & 4u)) { k_gi_spatial<<<blocks, 128, 0, ctx->stream>>>(ra); launches++; }
         }
-        k_gi_final_shading<<<blocks, 128, 0, ctx->stream>>>(gi); launches++;
+        if (ph & 4u) { k_gi_final_shading<<<blocks, 128, 0, ctx->stream>>>(gi); launches++; }
     }
     RT2_CUDA(ctx, cudaGetLastError());
-    ctx->stats.kernel_launches = launches;
+    ctx->stats.kernel_launches = (ph & 1u) ? launches : ctx->stats.kernel_launches + launches;
     ctx->stats.wavefront_iterations = 1;
     ctx->stats_from_counters = true;
-    ctx->pending_rays_static = static_rays;
+    if (ph & 1u) ctx->pending_rays_static = static_rays;
     return RT2_OK;
 }
 

@@ -134,36 +134,65 @@ def test_group_gathers_tonemapped_rgba8_bands():
     grp.close()
 
 
-def _rank_worker(rank, world, uid, w, h, q):
+def _gi_frames(sc, w, h, update, execute, read):
+    """three frames of the ReSTIR-GI chain with K6 + K7 on and a moving camera"""
+    cam = sc.camera(w / h)
+    g = rt.default_gconst(cam, w, h, sc.num_lights)
+    g.refrence_mode = 0; g.enable_restir_gi = 1; g.enable_restir_di = 0
+    g.enable_temporal_resampling = 1; g.enable_spatial_resampling = 1
+    g.restir_gi.spatial_resampling_params.num_spatial_samples = 2
+    out = None
+    for f in (1, 2, 3):
+        cam.position[0] += 0.02
+        rt.advance_frame(g, cam, w, h, f)
+        update(g)
+        execute(f)
+        out = read()
+    return out
+
+
+def _rank_worker(rank, world, uid, w, h, q, mode="k1"):
     import numpy as np
     import raytracer2_b200 as rt
     sc = rt.Scene(rt.SCENE_HALL, 0.125, 32, 0)
-    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
-    g.refrence_mode = 1
     grp = rt.Group.from_rank(rank, rank, world, uid)
     grp.upload_scene(sc.desc); grp.resize(w, h)
-    out = None
-    for f in (1, 2, 3):
-        g.frame = f
-        grp.update_uniform(g)
-        grp.execute(f, rt.LaunchParams(spp=4, max_bounces=3))
-        out = grp.read(np.uint32).copy()
+    if mode == "gi":        # K6 / K7: the in-frame exchanges run between the processes
+        out = _gi_frames(sc, w, h, grp.update_uniform, lambda f: grp.execute(f, None, gather=rt.BUF_DIFFUSE_F16), lambda: grp.read(np.uint32).copy())
+    else:
+        g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+        g.refrence_mode = 1
+        out = None
+        for f in (1, 2, 3):
+            g.frame = f
+            grp.update_uniform(g)
+            grp.execute(f, rt.LaunchParams(spp=4, max_bounces=3))
+            out = grp.read(np.uint32).copy()
     q.put((rank, out.tobytes(), grp.ctx(0).stats().rays_traced))
     grp.close()
 
 
-def test_one_process_per_gpu_group_equals_one_gpu_bit_for_bit():
+@pytest.mark.parametrize("mode", ["k1", "gi"])
+def test_one_process_per_gpu_group_equals_one_gpu_bit_for_bit(mode):
     n = 2
     if torch.cuda.device_count() < n:
         pytest.skip("needs 2 GPUs")
     import torch.multiprocessing as mp
     w, h = 200, 150
     sc, g = _scene(w=w, h=h)
-    want, rays = _single(sc, g, w, h, [1, 2, 3], rt.LaunchParams(spp=4, max_bounces=3))
+    if mode == "gi":
+        ctx1 = rt.Renderer(0)
+        rt.Model.from_scene(ctx1, sc)
+        lp1 = rt.LightPasses(ctx1, w, h)
+        want = [_gi_frames(sc, w, h, lp1.update_uniform, lp1.execute, lambda: ctx1.read(rt.BUF_DIFFUSE_F16, np.uint32).copy())]
+        rays = [ctx1.stats().rays_traced]
+        ctx1.close()
+    else:
+        want, rays = _single(sc, g, w, h, [1, 2, 3], rt.LaunchParams(spp=4, max_bounces=3))
     uid = rt.Group.unique_id()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_rank_worker, args=(r, n, uid, w, h, q)) for r in range(n)]
+    procs = [ctx.Process(target=_rank_worker, args=(r, n, uid, w, h, q, mode)) for r in range(n)]
     for p in procs:
         p.start()
     res = [q.get(timeout=300) for _ in range(n)]
@@ -173,3 +202,69 @@ def test_one_process_per_gpu_group_equals_one_gpu_bit_for_bit():
     for rank, buf, _ in res:
         assert np.array_equal(np.frombuffer(buf, np.uint32), want[-1]), f"rank {rank}"
     assert sum(r[2] for r in res) == rays[-1]
+
+
+def _resampling_gconst(sc, cam, w, h, temporal, spatial, bias, nspatial, permutation):
+    g = rt.default_gconst(cam, w, h, sc.num_lights)
+    g.refrence_mode = 0; g.enable_restir_gi = 1; g.enable_restir_di = 0
+    g.enable_temporal_resampling = temporal; g.enable_spatial_resampling = spatial
+    g.restir_gi.temporal_resampling_params.temporal_bias_correction_mode = bias
+    g.restir_gi.temporal_resampling_params.enable_permutation_sampling = permutation
+    g.restir_gi.spatial_resampling_params.spatial_bias_correction_mode = bias
+    g.restir_gi.spatial_resampling_params.num_spatial_samples = nspatial
+    return g
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("kind,scale,w,h,kw", [
+    (rt.SCENE_CORNELL, 1.0, 256, 256, dict()),                                                  # the reference's defaults with both passes on
+    (rt.SCENE_CORNELL, 1.0, 200, 120, dict(bias=3, nspatial=3, permutation=1)),                 # ray-traced bias correction: visibility rays inside K6 / K7
+    (rt.SCENE_HALL, 0.125, 320, 180, dict(nspatial=2)),
+    (rt.SCENE_CORNELL, 1.0, 160, 100, dict(spatial=0)),                                         # temporal alone (ragged last band: 100 rows)
+    (rt.SCENE_CORNELL, 1.0, 160, 100, dict(temporal=0, nspatial=4)),                            # spatial alone
+])
+def test_group_gi_resampling_equals_one_gpu_bit_for_bit(n, kind, scale, w, h, kw):
+    """K6 / K7 under sharding (VERDICT r1 missing 1; src/light_passes.rs:598-659, rtxdi/GIResamplingFunctions.hlsli:186-553): rt2_group_render
+    runs the frame in phases and exchanges the reservoir page K6 / K7 gather from and the G-buffer between them.  Five frames with a moving
+    camera (motion vectors, history) must equal the one-GPU frames bit for bit — lighting images and ray counts."""
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+    temporal, spatial = kw.get("temporal", 1), kw.get("spatial", 1)
+    sc = rt.Scene(kind, scale, 32, 0)
+    frames = range(1, 6)
+
+    def run(make, read):
+        cam = sc.camera(w / h)
+        g = _resampling_gconst(sc, cam, w, h, temporal, spatial, kw.get("bias", 2), kw.get("nspatial", 1), kw.get("permutation", 0))
+        target, update, execute = make()
+        out = []
+        for f in frames:
+            cam.position[0] += 0.02; cam.position[1] += 0.01
+            rt.advance_frame(g, cam, w, h, f)
+            update(g)
+            execute(f)
+            out.append(read())
+        return out
+
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, w, h)
+    want = run(lambda: (ctx, lp.update_uniform, lp.execute),
+               lambda: (ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).copy(), ctx.read(rt.BUF_SPECULAR_F16, np.uint16).copy(), ctx.stats().rays_traced))
+    ctx.close()
+
+    grp = rt.Group(list(range(n)))
+    grp.upload_scene(sc.desc); grp.resize(w, h)
+
+    def read_group():
+        d = grp.read(np.uint16).copy()
+        grp.gather(rt.BUF_SPECULAR_F16)
+        s = grp.read(np.uint16).copy()
+        return d, s, sum(grp.ctx(i).stats().rays_traced for i in range(n))
+    got = run(lambda: (grp, grp.update_uniform, lambda f: grp.execute(f, None, gather=rt.BUF_DIFFUSE_F16)), read_group)
+    grp.close()
+    for f, ((d, s, r), (wd, ws, wr)) in enumerate(zip(got, want), 1):
+        assert np.array_equal(d, wd), f"frame {f}: {int((d.reshape(-1, 4) != wd.reshape(-1, 4)).any(axis=1).sum())} diffuse pixels differ"
+        assert np.array_equal(s, ws), f"frame {f}: specular differs"
+        assert r == wr, f"frame {f}: {r} rays vs {wr}"
+    assert got[0][0].any() and not np.array_equal(got[0][0], got[-1][0])
