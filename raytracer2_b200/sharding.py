@@ -100,3 +100,35 @@ def gather_frame(plan: BandPlan, rank: int, send, recv, dist, async_op: bool = F
     else:
         h = dist.all_gather_into_tensor(recv.view(-1), send.reshape(-1), async_op=async_op)
     return h if async_op else recv
+
+
+# ---- in-frame exchange of per-pixel buffers (K6 / K7 under sharding; the host-side mirror of k_exchange_pack / k_exchange_unpack,
+# raytracer2_b200/csrc/rt2_group.cu) --------------------------------------------------------------------------------------------------
+def exchange_entry_index(width: int, height: int, layout: int, block_row_pitch: int = 0):
+    """Entry index of pixel (x, y) for every pixel, as an [H, W] int64 array.  layout 0: row-major; layout 1: the reservoirs'
+    16 x 16 block-linear order (RTXDI_ReservoirPositionToPointer, rtxdi/RtxdiHelpers.hlsli:75-88)."""
+    import numpy as np
+    y, x = np.mgrid[0:height, 0:width].astype(np.int64)
+    if layout == 0:
+        return y * width + x
+    return (y >> 4) * block_row_pitch + (x >> 4) * 256 + (y & 15) * 16 + (x & 15)
+
+
+def exchange_pack(plan: BandPlan, rank: int, buf, width: int, layout: int, block_row_pitch: int = 0):
+    """`buf`: [entries, words] array addressed by exchange_entry_index.  Returns this rank's pixels' entries, [max_rows * W, words]
+    (bands top to bottom, padded with zeros)."""
+    import numpy as np
+    idx = exchange_entry_index(width, plan.height, layout, block_row_pitch)
+    out = np.zeros((plan.max_rows * width, buf.shape[1]), buf.dtype)
+    for (y0, y1, off) in plan.pack_offsets(rank):
+        out[off * width:(off + y1 - y0) * width] = buf[idx[y0:y1].ravel()]
+    return out
+
+
+def exchange_unpack(plan: BandPlan, rank: int, gathered, buf, width: int, layout: int, block_row_pitch: int = 0):
+    """`gathered`: [world, max_rows * W, words].  Writes every OTHER rank's entries into `buf` in place; this rank's stay as they are."""
+    idx = exchange_entry_index(width, plan.height, layout, block_row_pitch)
+    for (y0, y1, r, off) in plan.scatter_index():
+        if r != rank:
+            buf[idx[y0:y1].ravel()] = gathered[r, off * width:(off + y1 - y0) * width]
+    return buf

@@ -119,3 +119,62 @@ def test_two_ranks_over_gloo_reassemble_the_whole_frame_bit_exactly(h, band_rows
     same, rays_sum, rays_whole = q.get(timeout=5)
     assert same
     assert rays_sum == rays_whole > 0           # the bands partition the work: no ray traced twice, none dropped
+
+
+def _exchange_main(rank, world, port, w, h, band_rows, q):
+    """Two ranks each hold a block-linear reservoir page and a row-major G-buffer plane that are valid only at their own pixels;
+    after the exchange (pack own -> all_gather -> scatter the others') both hold the complete buffers."""
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from raytracer2_b200.sharding import BandPlan, exchange_entry_index, exchange_pack, exchange_unpack
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        plan = BandPlan(h, band_rows, world)
+        pitch = ((w + 15) // 16) * 256                               # calculate_reservoir_buffer_parameters: blockRowPitch
+        entries = pitch * ((h + 15) // 16)
+        rng = np.random.default_rng(5)                               # same seed on every rank: the "whole frame" truth
+        truth = {"page": rng.integers(0, 2**32, (entries, 8), dtype=np.uint32), "plane": rng.integers(0, 2**32, (w * h, 1), dtype=np.uint32)}
+        owner = (np.arange(h) // band_rows) % world
+        ok = True
+        for name, layout in (("page", 1), ("plane", 0)):
+            idx = exchange_entry_index(w, h, layout, pitch)
+            mine = idx[owner == rank].ravel()
+            buf = np.full_like(truth[name], 0xDEADBEEF)
+            buf[mine] = truth[name][mine]                            # only this rank's pixels are valid
+            send = torch.from_numpy(exchange_pack(plan, rank, buf, w, layout, pitch).view(np.int32).copy())
+            chunks = [torch.zeros_like(send) for _ in range(world)]
+            dist.all_gather(chunks, send)
+            gathered = np.stack([c.numpy().view(np.uint32) for c in chunks])
+            exchange_unpack(plan, rank, gathered, buf, w, layout, pitch)
+            pix = idx.ravel()                                        # entries that belong to a pixel (block padding stays poisoned)
+            ok = ok and np.array_equal(buf[pix], truth[name][pix])
+            pad = np.setdiff1d(np.arange(len(buf)), pix)
+            ok = ok and (buf[pad] == 0xDEADBEEF).all()
+        q.put((rank, bool(ok)))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("w,h,band_rows", [(48, 40, 8), (37, 50, 8), (64, 33, 4)])
+def test_two_ranks_over_gloo_exchange_reservoir_pages_and_gbuffer_planes(w, h, band_rows):
+    """The K6 / K7 input exchange of rt2_group_render (rt2_group.cu), host-side mirror over gloo: block-linear and row-major addressing,
+    8-row bands cutting the 16 x 16 reservoir blocks in half, ragged last bands."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_exchange_main, args=(r, 2, port, w, h, band_rows, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+        assert p.exitcode == 0
+    got = sorted(q.get(timeout=5) for _ in range(2))
+    assert got == [(0, True), (1, True)]
