@@ -186,6 +186,24 @@ __global__ void k_compact(const uint32_t* clusters, const uint32_t* valid, const
         if (i == n - 1) *total = pos[i] + valid[i];
     }
 }
+// SAH-optimal collapse, bottom-up: a thread per leaf climbs; the second thread to arrive at an inner node solves it
+__global__ void k_bvh2_parents(Bvh2 b, uint32_t num_leaves, uint32_t num_nodes, uint32_t* parent) {
+    uint32_t i = num_leaves + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < num_nodes) { parent[__float_as_uint(b.lo[i].w)] = i; parent[__float_as_uint(b.hi[i].w)] = i; }
+}
+__global__ void k_dp_bottom_up(Bvh2 b, uint32_t num_leaves, const uint32_t* __restrict__ parent, uint32_t* flags, CollapseDp dp, uint32_t root) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= num_leaves) return;
+    dp_solve_leaf(dp, b, i);
+    uint32_t cur = i;
+    while (cur != root) {
+        const uint32_t p = parent[cur];
+        __threadfence();
+        if (atomicAdd(&flags[p], 1u) == 0u) return;
+        dp_solve_inner(dp, b, p);
+        cur = p;
+    }
+}
 __global__ void k_collapse(CollapseCtx c, const uint2* queue_in, uint32_t count) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) { uint2 q = queue_in[i]; collapse_node(c, q.x, q.y); }
@@ -218,6 +236,8 @@ int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, 
     uint32_t *hist = nullptr, *hist_scanned = nullptr, *scan_scratch = nullptr;
     Bvh2 b2{}; uint32_t *cl0 = nullptr, *cl1 = nullptr, *nearest = nullptr, *valid = nullptr, *pos = nullptr, *counters = nullptr;
     uint2 *q0 = nullptr, *q1 = nullptr;
+    CollapseDp dp{}; uint32_t *dp_parent = nullptr, *dp_flags = nullptr;
+    static const bool use_dp = [] { const char* e = getenv("RT2_COLLAPSE_DP"); return !e || atoi(e) != 0; }();
     uint32_t depth = 0;
     *nodes_out = nullptr; *out_prim_out = nullptr; *num_nodes_out = 0;
 
@@ -278,6 +298,15 @@ int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, 
         uint32_t root = 0;
         BCK(cudaMemcpyAsync(&root, cl0, 4, cudaMemcpyDeviceToHost, st));
         BCK(cudaStreamSynchronize(st));
+        // SAH-optimal slot distribution (rt2_build.cuh 5a): one bottom-up pass over the BVH2
+        if (use_dp) {
+            const uint32_t num_b2 = 2 * n - 1;                          // PLOC allocates inner nodes [n, 2n - 1)
+            BCK(sc.alloc(&dp.cost, (size_t)num_b2 * 7)); BCK(sc.alloc(&dp.dec, num_b2));
+            BCK(sc.alloc(&dp_parent, num_b2)); BCK(sc.alloc(&dp_flags, num_b2));
+            BCK(cudaMemsetAsync(dp_flags, 0, (size_t)num_b2 * 4, st));
+            if (n > 1) { k_bvh2_parents<<<grid(n - 1), T, 0, st>>>(b2, n, num_b2, dp_parent); lc->add(1); }
+            k_dp_bottom_up<<<grid(n), T, 0, st>>>(b2, n, dp_parent, dp_flags, dp, root); lc->add(1);
+        }
         // collapse to 8-wide
         const uint32_t max_nodes = n + 1;   // every wide node holds >= 1 primitive-bearing or >= 2 children; n+1 is a safe bound
         BCK(cudaMalloc((void**)&nodes, (size_t)max_nodes * sizeof(Node8)));
@@ -290,6 +319,7 @@ int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, 
         CollapseCtx cc{};
         cc.bvh2 = b2; cc.num_leaves = n; cc.leaf_prim = vals0; cc.nodes = nodes; cc.node_counter = counters + 2; cc.prim_counter = counters + 3;
         cc.out_prim = out_prim; cc.queue_out_count = counters + 4; cc.max_nodes = max_nodes; cc.max_prims = n;
+        cc.dp_dec = use_dp ? dp.dec : nullptr;
         while (qn) {
             depth++;
             BCK(cudaMemsetAsync(counters + 4, 0, 4, st));

@@ -60,7 +60,12 @@ static bool build_from_boxes(const std::vector<float4>& lo, const std::vector<fl
     out_prim.assign(n, 0);
     std::vector<uint2> q0(n), q1(n);
     uint32_t wide_counter = 1, prim_counter = 0, qcount = 0;
+    std::vector<float> dp_cost((size_t)node_counter * 7); std::vector<uint32_t> dp_dec(node_counter);
+    CollapseDp dp{dp_cost.data(), dp_dec.data()};
+    for (uint32_t i = 0; i < n; i++) dp_solve_leaf(dp, b2, i);
+    for (uint32_t i = n; i < node_counter; i++) dp_solve_inner(dp, b2, i);     // PLOC creates children before parents
     CollapseCtx cc{};
+    cc.dp_dec = dp_dec.data();
     cc.bvh2 = b2; cc.num_leaves = n; cc.leaf_prim = sorted.data(); cc.nodes = nodes.data(); cc.node_counter = &wide_counter;
     cc.prim_counter = &prim_counter; cc.out_prim = out_prim.data(); cc.queue_out_count = &qcount; cc.max_nodes = n + 1; cc.max_prims = n;
     q0[0] = make_uint2(root, 0u);
