@@ -313,7 +313,10 @@ template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = fals
 __global__ void __launch_bounds__(128, 6) k_trace_dyn_tlas(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, true, GENERIC>(a); }
 // flattened instancing: single-level walk over the (instance, triangle) tree
 template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false>
-__global__ void __launch_bounds__(128) k_trace_dyn_flat(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, false, GENERIC, false, true>(a); }
+#ifndef RT2_FLAT_MIN_BLOCKS
+#define RT2_FLAT_MIN_BLOCKS 7   /* 72 registers, 28 warps per SM: the flat walk is latency-bound (L2 hit 72-80 %, DRAM 2 %); 5 / 6 / 7 / 8 blocks: 1021 / 1086 / 1144 / 1096 Mrays/s on C5 */
+#endif
+__global__ void __launch_bounds__(128, RT2_FLAT_MIN_BLOCKS) k_trace_dyn_flat(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, false, GENERIC, false, true>(a); }
 
 // refrence.rgen:28-46 for the path in `slot` whose ray just came back (hit record in st_hit): emission / throughput update,
 // cosine-lobe sample, path regeneration.  Returns true while the pixel still has rays to trace (state written back), false when
