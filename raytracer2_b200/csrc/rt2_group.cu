@@ -7,8 +7,12 @@
 
 #include <dlfcn.h>
 
+#include <algorithm>
+#include <condition_variable>
+#include <functional>
 #include <mutex>
 #include <new>
+#include <thread>
 
 namespace rt2 {
 
@@ -80,27 +84,44 @@ struct ExchangeSeg { uint32_t* base; uint32_t words, layout; size_t slot_offset_
 __device__ __forceinline__ size_t exchange_entry(uint32_t x, uint32_t y, uint32_t width, uint32_t layout, uint32_t block_row_pitch) {
     return layout == 0u ? (size_t)y * width + x : (size_t)(y >> 4) * block_row_pitch + (size_t)(x >> 4) * 256u + (y & 15u) * 16u + (x & 15u);
 }
-__global__ void __launch_bounds__(256) k_exchange_pack(ExchangeSeg seg, uint32_t* __restrict__ send, uint32_t width, uint32_t local_rows, uint32_t band_rows,
-                                                       uint32_t rank, uint32_t world, uint32_t block_row_pitch) {
-    const uint64_t n = (uint64_t)local_rows * width * seg.words;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint64_t e = i / seg.words; const uint32_t wd = (uint32_t)(i % seg.words);
-        const uint32_t packed_row = (uint32_t)(e / width), x = (uint32_t)(e % width);
-        const uint32_t y = ((packed_row / band_rows) * world + rank) * band_rows + packed_row % band_rows;
-        send[seg.slot_offset_words + i] = seg.base[exchange_entry(x, y, width, seg.layout, block_row_pitch) * seg.words + wd];
+#define RT2_EXCHANGE_MAX_SEGS 6
+struct ExchangeSegs { ExchangeSeg s[RT2_EXCHANGE_MAX_SEGS]; uint32_t n; };
+
+// one thread per pixel, every segment of the exchange in one launch; 8-word entries (reservoirs) move as two uint4
+__device__ __forceinline__ void exchange_copy(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, uint32_t words) {
+    if (words == 8u) {
+        const uint4 a = reinterpret_cast<const uint4*>(src)[0], b = reinterpret_cast<const uint4*>(src)[1];
+        reinterpret_cast<uint4*>(dst)[0] = a; reinterpret_cast<uint4*>(dst)[1] = b;
+    } else {
+        for (uint32_t w = 0; w < words; w++) dst[w] = src[w];
     }
 }
-__global__ void __launch_bounds__(256) k_exchange_unpack(ExchangeSeg seg, const uint32_t* __restrict__ recv, size_t slot_words, uint32_t width, uint32_t height,
+__global__ void __launch_bounds__(256) k_exchange_pack(ExchangeSegs segs, uint32_t* __restrict__ send, uint32_t width, uint32_t local_rows, uint32_t band_rows,
+                                                       uint32_t rank, uint32_t world, uint32_t block_row_pitch) {
+    const uint32_t n = local_rows * width;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const uint32_t packed_row = e / width, x = e - packed_row * width;
+        const uint32_t y = ((packed_row / band_rows) * world + rank) * band_rows + packed_row % band_rows;
+        for (uint32_t k = 0; k < segs.n; k++) {
+            const ExchangeSeg& sg = segs.s[k];
+            exchange_copy(send + sg.slot_offset_words + (size_t)e * sg.words, sg.base + exchange_entry(x, y, width, sg.layout, block_row_pitch) * sg.words, sg.words);
+        }
+    }
+}
+__global__ void __launch_bounds__(256) k_exchange_unpack(ExchangeSegs segs, const uint32_t* __restrict__ recv, size_t slot_words, uint32_t width, uint32_t height,
                                                          uint32_t band_rows, uint32_t rank, uint32_t world, uint32_t block_row_pitch) {
-    const uint64_t n = (uint64_t)height * width * seg.words;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint64_t e = i / seg.words; const uint32_t wd = (uint32_t)(i % seg.words);
-        const uint32_t y = (uint32_t)(e / width), x = (uint32_t)(e % width);
+    const uint32_t n = height * width;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < n; e += gridDim.x * blockDim.x) {
+        const uint32_t y = e / width, x = e - y * width;
         const uint32_t band = y / band_rows, owner = band % world;
         if (owner == rank) continue;                                   // this rank's own entries are already in place
         const uint32_t packed_row = (band / world) * band_rows + y % band_rows;
-        seg.base[exchange_entry(x, y, width, seg.layout, block_row_pitch) * seg.words + wd] =
-            recv[(size_t)owner * slot_words + seg.slot_offset_words + ((size_t)packed_row * width + x) * seg.words + wd];
+        const uint32_t* slot = recv + (size_t)owner * slot_words;
+        for (uint32_t k = 0; k < segs.n; k++) {
+            const ExchangeSeg& sg = segs.s[k];
+            exchange_copy(sg.base + exchange_entry(x, y, width, sg.layout, block_row_pitch) * sg.words,
+                          slot + sg.slot_offset_words + ((size_t)packed_row * width + x) * sg.words, sg.words);
+        }
     }
 }
 
@@ -109,6 +130,25 @@ __global__ void __launch_bounds__(256) k_exchange_unpack(ExchangeSeg seg, const 
 using namespace rt2;
 
 #define RT2_GROUP_BUFFERS 2
+// One host thread per local GPU beyond the first (single-process groups): a frame is 60-270 kernel launches per GPU, and one thread
+// issuing them for 8 GPUs in turn takes longer than a GPU needs to run its share (measured: C5 on 8 GPUs 7.4 ms per frame, of which
+// ~4 ms of GPU work).  The caller's thread drives context 0 and waits for the others.
+struct GroupWorker {
+    std::thread th; std::mutex m; std::condition_variable cv;
+    std::function<int()> job; bool has_job = false, quit = false; int rc = 0;
+    void loop() {
+        for (;;) {
+            std::function<int()> j;
+            { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return has_job || quit; }); if (quit && !has_job) return; j = job; }
+            const int r = j();
+            { std::lock_guard<std::mutex> l(m); rc = r; has_job = false; }
+            cv.notify_all();
+        }
+    }
+    void start(std::function<int()> j) { { std::lock_guard<std::mutex> l(m); job = std::move(j); has_job = true; } cv.notify_all(); }
+    int wait() { std::unique_lock<std::mutex> l(m); cv.wait(l, [&] { return !has_job; }); return rc; }
+    void stop() { { std::lock_guard<std::mutex> l(m); quit = true; } cv.notify_all(); if (th.joinable()) th.join(); }
+};
 struct rt2_group {
     int world = 1, first_rank = 0;                    // this process owns ranks [first_rank, first_rank + ctxs.size())
     std::vector<rt2_ctx*> ctxs;
@@ -126,6 +166,16 @@ struct rt2_group {
     uint32_t width = 0, height = 0;
     uint64_t gathers = 0;                             // gathers issued; buffer of gather k is k % RT2_GROUP_BUFFERS
     uint64_t exchanges = 0;                           // in-frame exchanges issued (K6 / K7 inputs)
+    std::vector<GroupWorker*> workers;                // workers[i] drives ctxs[i], i >= 1 (workers[0] is null)
+    // fn(i) for every local context, in parallel; returns the first non-zero code (and its context index)
+    int each(const std::function<int(size_t)>& fn, size_t* failed = nullptr) {
+        const size_t n = ctxs.size();
+        for (size_t i = 1; i < n; i++) workers[i]->start([&fn, i] { return fn(i); });
+        int rc = fn(0); size_t who = 0;
+        for (size_t i = 1; i < n; i++) { const int r = workers[i]->wait(); if (r != 0 && rc == 0) { rc = r; who = i; } }
+        if (failed) *failed = who;
+        return rc;
+    }
     size_t frame_bytes = 0;                           // of the last gathered buffer
     std::string last_error;
 };
@@ -144,6 +194,8 @@ static int group_finish_create(rt2_group* g) {
     const size_t n = g->ctxs.size();
     g->comm_streams.assign(n, nullptr);
     g->lanes.assign(n, rt2_group::Lane());
+    g->workers.assign(n, nullptr);
+    for (size_t i = 1; i < n; i++) { g->workers[i] = new GroupWorker(); GroupWorker* w = g->workers[i]; w->th = std::thread([w] { w->loop(); }); }
     for (size_t i = 0; i < n; i++) {
         RT2_GCUDA(g, cudaSetDevice(g->ctxs[i]->device));
         RT2_GCUDA(g, cudaStreamCreateWithFlags(&g->comm_streams[i], cudaStreamNonBlocking));
@@ -168,6 +220,8 @@ const char* rt2_group_last_error(rt2_group* g) {
 
 int rt2_group_destroy(rt2_group* g) {
     if (!g) return RT2_E_INVALID;
+    for (GroupWorker* w : g->workers) if (w) { w->stop(); delete w; }
+    g->workers.clear();
     for (size_t i = 0; i < g->ctxs.size(); i++) {
         if (!g->ctxs[i]) continue;
         cudaSetDevice(g->ctxs[i]->device);
@@ -310,9 +364,11 @@ static int group_exchange(rt2_group* g, SegsOf segs_of) {
     size_t slot_words = 0;
     for (size_t i = 0; i < n; i++) {
         all[i] = segs_of(i);
+        // 8-word entries first and slots padded to 16 bytes: they move as uint4 pairs
+        std::stable_sort(all[i].begin(), all[i].end(), [](const ExchangeSeg& a, const ExchangeSeg& b) { return a.words > b.words; });
         size_t off = 0;
         for (ExchangeSeg& sg : all[i]) { sg.slot_offset_words = off; off += (size_t)max_rows * W * sg.words; }
-        slot_words = off;
+        slot_words = (off + 3u) & ~(size_t)3u;
     }
     for (size_t i = 0; i < n; i++) {
         rt2_group::Lane& L = g->lanes[i];
@@ -327,10 +383,13 @@ static int group_exchange(rt2_group* g, SegsOf segs_of) {
             L.cap_xslot = slot_words;
         }
         const uint32_t rank = (uint32_t)g->first_rank + (uint32_t)i, rows = plan.rows(rank);
-        for (const ExchangeSeg& sg : all[i]) {
-            const uint64_t items = (uint64_t)rows * W * sg.words;
+        if (all[i].size() > RT2_EXCHANGE_MAX_SEGS) return gfail(g, RT2_E_INVALID, "too many exchange segments");
+        ExchangeSegs segs{}; segs.n = (uint32_t)all[i].size();
+        for (size_t k = 0; k < all[i].size(); k++) segs.s[k] = all[i][k];
+        {
+            const uint64_t items = (uint64_t)rows * W;
             const int blocks = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8u, (items + 255u) / 256u);
-            k_exchange_pack<<<std::max(blocks, 1), 256, 0, c->stream>>>(sg, L.xsend, W, rows, RT2_GROUP_BAND_ROWS, rank, world, c->fb.reservoir_block_row_pitch);
+            k_exchange_pack<<<std::max(blocks, 1), 256, 0, c->stream>>>(segs, L.xsend, W, rows, RT2_GROUP_BAND_ROWS, rank, world, c->fb.reservoir_block_row_pitch);
         }
         RT2_GCUDA(g, cudaGetLastError());
     }
@@ -344,10 +403,12 @@ static int group_exchange(rt2_group* g, SegsOf segs_of) {
         rt2_ctx* c = g->ctxs[i];
         RT2_GCUDA(g, cudaSetDevice(c->device));
         const uint32_t rank = (uint32_t)g->first_rank + (uint32_t)i;
-        for (const ExchangeSeg& sg : all[i]) {
-            const uint64_t items = (uint64_t)H * W * sg.words;
+        ExchangeSegs segs{}; segs.n = (uint32_t)all[i].size();
+        for (size_t k = 0; k < all[i].size(); k++) segs.s[k] = all[i][k];
+        {
+            const uint64_t items = (uint64_t)H * W;
             const int blocks = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8u, (items + 255u) / 256u);
-            k_exchange_unpack<<<std::max(blocks, 1), 256, 0, c->stream>>>(sg, g->lanes[i].xrecv, slot_words, W, H, RT2_GROUP_BAND_ROWS, rank, world, c->fb.reservoir_block_row_pitch);
+            k_exchange_unpack<<<std::max(blocks, 1), 256, 0, c->stream>>>(segs, g->lanes[i].xrecv, slot_words, W, H, RT2_GROUP_BAND_ROWS, rank, world, c->fb.reservoir_block_row_pitch);
         }
         RT2_GCUDA(g, cudaGetLastError());
     }
@@ -363,16 +424,18 @@ int rt2_group_render(rt2_group* g, uint32_t frame, const rt2_launch_params* para
     const size_t n = g->ctxs.size();
     const uint32_t world = (uint32_t)g->world;
     auto render_all = [&](uint32_t phase) -> int {
-        for (size_t i = 0; i < n; i++) {
+        size_t who = 0;
+        const int rc = g->each([&](size_t i) {
             rt2_launch_params lp{};
             if (params) lp = *params;
             lp.band_rows = world > 1u ? RT2_GROUP_BAND_ROWS : 0u; lp.band_rank = (uint32_t)g->first_rank + (uint32_t)i; lp.band_world = world > 1u ? world : 0u;
             if (world <= 1u) lp.band_rank = 0u;
             g->ctxs[i]->restir_phase = phase;
-            const int rc = rt2_render(g->ctxs[i], frame, &lp);
+            const int r = rt2_render(g->ctxs[i], frame, &lp);
             g->ctxs[i]->restir_phase = 0u;
-            if (rc != RT2_OK) return gfail(g, rc, std::string("rt2_render: ") + rt2_last_error(g->ctxs[i]));
-        }
+            return r;
+        }, &who);
+        if (rc != RT2_OK) return gfail(g, rc, std::string("rt2_render: ") + rt2_last_error(g->ctxs[who]));
         return RT2_OK;
     };
     // GI temporal / spatial resampling (K6 / K7) under sharding: the frame runs in phases with the inputs those two passes read at

@@ -7,6 +7,7 @@ import raytracer2_b200 as rt
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--frames", type=int, default=6); ap.add_argument("--overhead", action="store_true"); ap.add_argument("--scale", type=float, default=1.0)
+ap.add_argument("--band-world", type=int, default=0, help="render only rank 0's 8-row bands of this many ranks (one rank of N, emulated)")
 a = ap.parse_args()
 W, H = 1920, 1080
 sc = rt.Scene(rt.SCENE_INSTANCED, a.scale, 512, 0)
@@ -19,7 +20,7 @@ rt.Model.from_scene(ctx, sc)
 lp = rt.LightPasses(ctx, W, H); lp.update_uniform(g)
 rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.ENVIRONMENT).execute_mip_generation()
 post = rt.PostProcessPass(ctx)
-p = rt.LaunchParams(spp=4, max_bounces=4)
+p = rt.LaunchParams(spp=4, max_bounces=4, band_rows=8 if a.band_world > 1 else 0, band_rank=0, band_world=a.band_world if a.band_world > 1 else 0)
 out = []
 for f in range(1, a.frames + 1):
     ctx.sync(); t0 = time.perf_counter()
