@@ -1,7 +1,9 @@
 // rt2_build.cu — device BVH builder: kernels + host orchestration.  See rt2_build.cuh.
 #include "rt2_internal.cuh"
 #include "rt2_build.cuh"
+#include "rt2_reinsert.cuh"
 
+#include <cstdio>
 #include <vector>
 
 namespace rt2 {
@@ -204,6 +206,35 @@ __global__ void k_dp_bottom_up(Bvh2 b, uint32_t num_leaves, const uint32_t* __re
         cur = p;
     }
 }
+// insertion-based optimisation of the BVH2 (rt2_reinsert.cuh): one iteration = find, lock, check, apply, refit
+__global__ void __launch_bounds__(128) k_reinsert_find(Reinsert r) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < r.num_nodes) { r.lock[i] = 0ull; r.pass[i] = 0ull; reinsert_find(r, i); }
+}
+__global__ void k_reinsert_lock(Reinsert r) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < r.num_nodes) reinsert_lock(r, i);
+}
+__global__ void k_reinsert_check(Reinsert r, uint32_t* win, uint32_t* applied) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < r.num_nodes) { const bool w = reinsert_check(r, i); win[i] = w ? 1u : 0u; if (w) atomicAdd(applied, 1u); }
+}
+__global__ void k_reinsert_apply(Reinsert r, const uint32_t* win) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < r.num_nodes && win[i]) reinsert_apply(r, i, r.target[i]);
+}
+__global__ void k_refit_bottom_up(Bvh2 b, uint32_t num_leaves, const uint32_t* __restrict__ parent, uint32_t* flags, uint32_t root) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= num_leaves) return;
+    uint32_t cur = i;
+    while (cur != root) {
+        const uint32_t p = parent[cur];
+        __threadfence();
+        if (atomicAdd(&flags[p], 1u) == 0u) return;
+        reinsert_refit_node(b, p);
+        cur = p;
+    }
+}
 __global__ void k_collapse(CollapseCtx c, const uint2* queue_in, uint32_t count) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) { uint2 q = queue_in[i]; collapse_node(c, q.x, q.y); }
@@ -238,6 +269,8 @@ int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, 
     uint2 *q0 = nullptr, *q1 = nullptr;
     CollapseDp dp{}; uint32_t *dp_parent = nullptr, *dp_flags = nullptr;
     static const bool use_dp = [] { const char* e = getenv("RT2_COLLAPSE_DP"); return !e || atoi(e) != 0; }();
+    static const bool build_verbose = getenv("RT2_BUILD_VERBOSE") != nullptr;
+    static const int reinsert_iters = [] { const char* e = getenv("RT2_REINSERT_ITERS"); return e ? atoi(e) : 12; }();
     uint32_t depth = 0;
     *nodes_out = nullptr; *out_prim_out = nullptr; *num_nodes_out = 0;
 
@@ -298,13 +331,39 @@ int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, 
         uint32_t root = 0;
         BCK(cudaMemcpyAsync(&root, cl0, 4, cudaMemcpyDeviceToHost, st));
         BCK(cudaStreamSynchronize(st));
+        const uint32_t num_b2 = 2 * n - 1;                              // PLOC allocates inner nodes [n, 2n - 1)
+        if (use_dp || reinsert_iters > 0) {
+            BCK(sc.alloc(&dp_parent, num_b2)); BCK(sc.alloc(&dp_flags, num_b2));
+            BCK(cudaMemsetAsync(dp_parent, 0xFF, (size_t)num_b2 * 4, st));
+            if (n > 1) { k_bvh2_parents<<<grid(n - 1), T, 0, st>>>(b2, n, num_b2, dp_parent); lc->add(1); }
+        }
+        // insertion-based optimisation of the BVH2 (rt2_reinsert.cuh)
+        if (reinsert_iters > 0 && n >= 16) {
+            Reinsert r{}; uint32_t* win = nullptr;
+            r.b = b2; r.parent = dp_parent; r.root = root; r.num_leaves = n; r.num_nodes = num_b2;
+            BCK(sc.alloc(&r.target, num_b2)); BCK(sc.alloc(&r.lca, num_b2)); BCK(sc.alloc(&r.gain, num_b2));
+            BCK(sc.alloc(&r.lock, num_b2)); BCK(sc.alloc(&r.pass, num_b2)); BCK(sc.alloc(&win, num_b2));
+            // big trees: fewer rounds (a round costs a branch-and-bound search per node)
+            const int iters = n > (4u << 20) ? std::max(1, reinsert_iters / 2) : reinsert_iters;
+            for (int it = 0; it < iters; it++) {
+                BCK(cudaMemsetAsync(counters + 5, 0, 4, st));
+                k_reinsert_find<<<(num_b2 + 127) / 128, 128, 0, st>>>(r); lc->add(1);
+                k_reinsert_lock<<<grid(num_b2), T, 0, st>>>(r); lc->add(1);
+                k_reinsert_check<<<grid(num_b2), T, 0, st>>>(r, win, counters + 5); lc->add(1);
+                k_reinsert_apply<<<grid(num_b2), T, 0, st>>>(r, win); lc->add(1);
+                BCK(cudaMemsetAsync(dp_flags, 0, (size_t)num_b2 * 4, st));
+                k_refit_bottom_up<<<grid(n), T, 0, st>>>(b2, n, dp_parent, dp_flags, root); lc->add(1);
+                uint32_t applied = 0;
+                BCK(cudaMemcpyAsync(&applied, counters + 5, 4, cudaMemcpyDeviceToHost, st));
+                BCK(cudaStreamSynchronize(st));
+                if (build_verbose) fprintf(stderr, "[rt2 build] %u leaves, reinsertion round %d: %u moves applied\n", n, it, applied);
+                if (applied * 2000ull < n) break;                       // fewer than 0.05 % of the leaves moved: converged
+            }
+        }
         // SAH-optimal slot distribution (rt2_build.cuh 5a): one bottom-up pass over the BVH2
         if (use_dp) {
-            const uint32_t num_b2 = 2 * n - 1;                          // PLOC allocates inner nodes [n, 2n - 1)
             BCK(sc.alloc(&dp.cost, (size_t)num_b2 * 7)); BCK(sc.alloc(&dp.dec, num_b2));
-            BCK(sc.alloc(&dp_parent, num_b2)); BCK(sc.alloc(&dp_flags, num_b2));
             BCK(cudaMemsetAsync(dp_flags, 0, (size_t)num_b2 * 4, st));
-            if (n > 1) { k_bvh2_parents<<<grid(n - 1), T, 0, st>>>(b2, n, num_b2, dp_parent); lc->add(1); }
             k_dp_bottom_up<<<grid(n), T, 0, st>>>(b2, n, dp_parent, dp_flags, dp, root); lc->add(1);
         }
         // collapse to 8-wide

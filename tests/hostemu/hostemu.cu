@@ -2,7 +2,7 @@
 // (raytracer2_b200/csrc/rt2_build.cuh, rt2_bvh.cuh) serially on the CPU so that the BVH build,
 // the Node8 encoding and the CWBVH traversal can be checked against the oracle without a GPU.
 // Not linked into librt2cuda.so; the product has no CPU path.
-#include "../../raytracer2_b200/csrc/rt2_build.cuh"
+#include "../../raytracer2_b200/csrc/rt2_reinsert.cuh"
 #include "../../include/rt2_gconst.h"
 
 #include <algorithm>
@@ -60,10 +60,36 @@ static bool build_from_boxes(const std::vector<float4>& lo, const std::vector<fl
     out_prim.assign(n, 0);
     std::vector<uint2> q0(n), q1(n);
     uint32_t wide_counter = 1, prim_counter = 0, qcount = 0;
+    // insertion-based optimisation (rt2_reinsert.cuh), phase by phase as the kernels of rt2_build.cu run it
+    std::vector<uint32_t> parent(node_counter, 0xFFFFFFFFu);
+    for (uint32_t i = n; i < node_counter; i++) { parent[f2u(blo[i].w)] = i; parent[f2u(bhi[i].w)] = i; }
+    auto post_order = [&]() {
+        std::vector<uint32_t> order; order.reserve(node_counter); std::vector<uint32_t> st{root};
+        while (!st.empty()) { uint32_t x = st.back(); st.pop_back(); order.push_back(x); if (x >= n) { st.push_back(f2u(blo[x].w)); st.push_back(f2u(bhi[x].w)); } }
+        std::reverse(order.begin(), order.end());
+        return order;
+    };
+    if (n >= 16) {
+        std::vector<uint32_t> target(node_counter), lca(node_counter); std::vector<float> gain(node_counter);
+        std::vector<unsigned long long> lock(node_counter), pass(node_counter); std::vector<uint8_t> win(node_counter);
+        Reinsert r{b2, parent.data(), root, n, node_counter, target.data(), lca.data(), gain.data(), lock.data(), pass.data()};
+        const int iters = n > (4u << 20) ? 6 : 12;
+        for (int it = 0; it < iters; it++) {
+            std::fill(lock.begin(), lock.end(), 0ull); std::fill(pass.begin(), pass.end(), 0ull);
+            for (uint32_t i = 0; i < node_counter; i++) reinsert_find(r, i);
+            for (uint32_t i = 0; i < node_counter; i++) reinsert_lock(r, i);
+            uint32_t applied = 0;
+            for (uint32_t i = 0; i < node_counter; i++) { win[i] = reinsert_check(r, i) ? 1 : 0; applied += win[i]; }
+            for (uint32_t i = 0; i < node_counter; i++) if (win[i]) reinsert_apply(r, i, target[i]);
+            const std::vector<uint32_t> order = post_order();
+            if (order.size() != node_counter) return false;
+            for (uint32_t x : order) if (x >= n) reinsert_refit_node(b2, x);
+            if (applied * 2000ull < n) break;
+        }
+    }
     std::vector<float> dp_cost((size_t)node_counter * 7); std::vector<uint32_t> dp_dec(node_counter);
     CollapseDp dp{dp_cost.data(), dp_dec.data()};
-    for (uint32_t i = 0; i < n; i++) dp_solve_leaf(dp, b2, i);
-    for (uint32_t i = n; i < node_counter; i++) dp_solve_inner(dp, b2, i);     // PLOC creates children before parents
+    for (uint32_t x : post_order()) { if (x < n) dp_solve_leaf(dp, b2, x); else dp_solve_inner(dp, b2, x); }
     CollapseCtx cc{};
     cc.dp_dec = dp_dec.data();
     cc.bvh2 = b2; cc.num_leaves = n; cc.leaf_prim = sorted.data(); cc.nodes = nodes.data(); cc.node_counter = &wide_counter;

@@ -16,7 +16,9 @@ cam = rt.overhead_camera(sc, W / H) if a.overhead else sc.camera(W / H)
 g = rt.default_gconst(cam, W, H, sc.num_lights, env_size=(d.sky_width, d.sky_height))
 g.refrence_mode = 1; g.environment = 1
 ctx = rt.Renderer(0)
-rt.Model.from_scene(ctx, sc)
+t0 = time.perf_counter()
+rt.Model.from_scene(ctx, sc); ctx.sync()
+print(f"upload + BVH build: {time.perf_counter() - t0:.2f} s", flush=True)
 lp = rt.LightPasses(ctx, W, H); lp.update_uniform(g)
 rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.ENVIRONMENT).execute_mip_generation()
 post = rt.PostProcessPass(ctx)

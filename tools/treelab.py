@@ -20,6 +20,8 @@ def lib():
     L = C.CDLL(so)
     L.treelab_build.restype = C.c_void_p
     L.treelab_build.argtypes = [C.c_void_p, C.c_int, C.c_float, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    L.treelab_build_soup.restype = C.c_void_p
+    L.treelab_build_soup.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_float, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     L.treelab_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_float, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
     L.treelab_destroy.argtypes = [C.c_void_p]
     return L
@@ -42,7 +44,11 @@ def world_triangles(sc):
         p = pos[ii].astype(np.float64)
         pw = p @ M[:3, :3].T + M[:3, 3]
         tris.append(pw.reshape(-1, 3, 3))
-    return np.concatenate(tris)
+    tris = np.concatenate(tris)
+    if d.num_instances:                                                          # flattened instancing: every (instance, triangle) pair in world space
+        m = np.ctypeslib.as_array(C.cast(d.instance_transforms, C.POINTER(C.c_float)), shape=(d.num_instances, 3, 4)).astype(np.float64)
+        tris = np.concatenate([tris @ m[i, :, :3].T + m[i, :, 3] for i in range(d.num_instances)])
+    return tris
 
 
 def bounce_rays(tris, n, seed=1):
@@ -84,7 +90,7 @@ def main():
     ap.add_argument("--fraction", type=float, default=1.0)
     ap.add_argument("--collapse", default="0", help="comma list of collapse modes (0 = product: largest area first)")
     a = ap.parse_args()
-    kind = {"hall": rt.SCENE_HALL, "manylight": rt.SCENE_MANYLIGHT, "cornell": rt.SCENE_CORNELL, "random": rt.SCENE_RANDOM}[a.scene]
+    kind = {"hall": rt.SCENE_HALL, "manylight": rt.SCENE_MANYLIGHT, "cornell": rt.SCENE_CORNELL, "random": rt.SCENE_RANDOM, "instanced": rt.SCENE_INSTANCED}[a.scene]
     sc = rt.Scene(kind, a.scale, 16, 0)
     tris = world_triangles(sc)
     print(f"scene {a.scene} scale {a.scale}: {len(tris)} triangles")
@@ -96,7 +102,11 @@ def main():
       for cmode in [int(c) for c in a.collapse.split(",")]:
         sb, sa, wn, dp = C.c_double(), C.c_double(), C.c_uint32(), C.c_uint32()
         t0 = time.time()
-        hnd = L.treelab_build(C.cast(sc.desc, C.c_void_p), passes, a.fraction, cmode, C.byref(sb), C.byref(sa), C.byref(wn), C.byref(dp))
+        if sc.desc.contents.num_instances:
+            soup = np.ascontiguousarray(tris.reshape(-1, 9), np.float32)
+            hnd = L.treelab_build_soup(soup.ctypes.data_as(C.c_void_p), len(soup), passes, a.fraction, cmode, C.byref(sb), C.byref(sa), C.byref(wn), C.byref(dp))
+        else:
+            hnd = L.treelab_build(C.cast(sc.desc, C.c_void_p), passes, a.fraction, cmode, C.byref(sb), C.byref(sa), C.byref(wn), C.byref(dp))
         tb = time.time() - t0
         assert hnd
         row = [f"passes {passes} collapse {cmode}: SAH(node) {sb.value:.2f} -> {sa.value:.2f}, {wn.value} wide nodes, depth {dp.value}, build {tb:.1f} s"]

@@ -2,9 +2,11 @@
 // __host__ __device__ builder functions (rt2_build.cuh) with optional tree-quality passes between PLOC and the collapse, and
 // counts node steps and triangle tests per ray with the product's traversal (rt2_bvh.cuh).  Used to decide whether a SAH
 // optimisation pass is worth building on the device (VERDICT r1 task 6); results in profiles/r02_tree_quality.txt.
-#include "../../raytracer2_b200/csrc/rt2_build.cuh"
+#include "../../raytracer2_b200/csrc/rt2_reinsert.cuh"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <queue>
 #include <vector>
@@ -180,6 +182,28 @@ struct DpCollapse {
     }
 };
 
+// The product's parallel reinsertion (rt2_reinsert.cuh), phases run one after the other over all nodes as the kernels do
+static void parallel_reinsertion(Tree2& t, int iterations, int mod, bool verbose) {
+    const uint32_t N = (uint32_t)t.lo.size();
+    std::vector<uint32_t> target(N), lca(N), flags(N); std::vector<float> gain(N); std::vector<unsigned long long> lock(N), pass(N);
+    std::vector<uint8_t> winner(N);
+    for (int it = 0; it < iterations; it++) {
+        Reinsert r{Bvh2{t.lo.data(), t.hi.data(), t.count.data()}, t.parent.data(), t.root, t.nleaves, N, target.data(), lca.data(), gain.data(), lock.data(), pass.data()};
+        std::fill(lock.begin(), lock.end(), 0ull); std::fill(pass.begin(), pass.end(), 0ull);
+        uint32_t wanted = 0, applied = 0;
+        for (uint32_t i = 0; i < N; i++) { if (mod > 1 && (int)((i + it) % mod) != 0) { target[i] = 0xFFFFFFFFu; continue; } reinsert_find(r, i); if (target[i] != 0xFFFFFFFFu) wanted++; }
+        for (uint32_t i = 0; i < N; i++) reinsert_lock(r, i);
+        for (uint32_t i = 0; i < N; i++) winner[i] = reinsert_check(r, i) ? 1 : 0;
+        for (uint32_t i = 0; i < N; i++) if (winner[i]) { reinsert_apply(r, i, target[i]); applied++; }
+        // refit bottom-up: post-order from the root
+        std::vector<uint32_t> order; order.reserve(N); std::vector<uint32_t> st{t.root};
+        while (!st.empty()) { uint32_t x = st.back(); st.pop_back(); order.push_back(x); if (!t.leaf(x)) { st.push_back(t.left(x)); st.push_back(t.right(x)); } }
+        if (order.size() != N) { fprintf(stderr, "reinsertion broke the tree: %zu of %u nodes reachable\n", order.size(), N); abort(); }
+        for (size_t k = order.size(); k-- > 0;) if (!t.leaf(order[k])) reinsert_refit_node(r.b, order[k]);
+        if (verbose) fprintf(stderr, "  iteration %d: %u moves wanted, %u applied, SAH %.3f\n", it, wanted, applied, t.sah());
+    }
+}
+
 struct Lab {
     std::vector<Node8> nodes; std::vector<TriPos> tris; std::vector<uint32_t> slot_to_prim;
     double sah_before = 0, sah_after = 0; uint32_t depth = 0;
@@ -226,7 +250,8 @@ static bool build(Lab& L, const std::vector<float4>& lo, const std::vector<float
     t.parent.assign(node_counter, 0xFFFFFFFFu);
     for (uint32_t i = n; i < node_counter; i++) { t.parent[t.left(i)] = i; t.parent[t.right(i)] = i; }
     L.sah_before = t.sah();
-    for (int k = 0; k < passes; k++) reinsertion_pass(t, fraction);
+    if (collapse_mode & 32) parallel_reinsertion(t, passes, (collapse_mode >> 16) & 0xff, true);
+    else for (int k = 0; k < passes; k++) reinsertion_pass(t, fraction);
     L.sah_after = t.sah();
     b2 = Bvh2{t.lo.data(), t.hi.data(), t.count.data()};
     DpCollapse dp; const bool dp_on = (collapse_mode & 1) != 0;
@@ -264,6 +289,22 @@ void* treelab_build(const rt2_scene_desc* d, int reinsertion_passes, float fract
     BuildInput in{d->vertices, d->indices, d->geometries, offs.data(), d->num_geometries, n};
     std::vector<TriPos> tris_in(n); std::vector<float4> lo(n), hi(n);
     for (uint32_t i = 0; i < n; i++) build_triangle(in, i, tris_in.data(), lo.data(), hi.data());
+    if (!build(*L, lo, hi, reinsertion_passes, fraction, collapse_mode)) { delete L; return nullptr; }
+    L->tris.resize(n);
+    for (uint32_t s = 0; s < n; s++) L->tris[s] = tris_in[L->slot_to_prim[s]];
+    *sah_before = L->sah_before; *sah_after = L->sah_after; *wide_nodes = (uint32_t)L->nodes.size(); *depth = L->depth;
+    return L;
+}
+// a world-space triangle soup (9 floats per triangle): the flattened-instancing tree of an instanced scene has exactly these leaves
+void* treelab_build_soup(const float* tris9, uint32_t n, int reinsertion_passes, float fraction, int collapse_mode, double* sah_before, double* sah_after, uint32_t* wide_nodes, uint32_t* depth) {
+    Lab* L = new Lab();
+    std::vector<TriPos> tris_in(n); std::vector<float4> lo(n), hi(n);
+    for (uint32_t i = 0; i < n; i++) {
+        const float* t = tris9 + 9 * (size_t)i;
+        tris_in[i].v0 = make_float4(t[0], t[1], t[2], u2f(0u)); tris_in[i].v1 = make_float4(t[3], t[4], t[5], u2f(i)); tris_in[i].v2 = make_float4(t[6], t[7], t[8], 0.f);
+        lo[i] = make_float4(fminf(t[0], fminf(t[3], t[6])), fminf(t[1], fminf(t[4], t[7])), fminf(t[2], fminf(t[5], t[8])), u2f(0xFFFFFFFFu));
+        hi[i] = make_float4(fmaxf(t[0], fmaxf(t[3], t[6])), fmaxf(t[1], fmaxf(t[4], t[7])), fmaxf(t[2], fmaxf(t[5], t[8])), u2f(0xFFFFFFFFu));
+    }
     if (!build(*L, lo, hi, reinsertion_passes, fraction, collapse_mode)) { delete L; return nullptr; }
     L->tris.resize(n);
     for (uint32_t s = 0; s < n; s++) L->tris[s] = tris_in[L->slot_to_prim[s]];
