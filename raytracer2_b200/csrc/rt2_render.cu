@@ -929,6 +929,13 @@ static const trace_kernel_t g_trace_variants[] = {
     k_trace_dyn<12, 4, 8>,     // 12
     k_trace_dyn<20, 6, 6>,     // 13
     k_trace_dyn<20, 3, 6>,     // 14
+    k_trace_dyn<30, 4, 4>,     // 15 (r02b re-sweep after the tree-quality work: shorter walks favour checking more often)
+    k_trace_dyn<25, 6, 6>,     // 16
+    k_trace_dyn<30, 6, 6>,     // 17
+    k_trace_dyn<25, 4, 6>,     // 18
+    k_trace_dyn<30, 6, 4>,     // 19
+    k_trace_dyn<35, 4, 4>,     // 20
+    k_trace_dyn<25, 8, 4>,     // 21
 };
 static const int g_num_trace_variants = (int)(sizeof(g_trace_variants) / sizeof(g_trace_variants[0]));
 

@@ -46,7 +46,7 @@ __device__ __forceinline__ void setup_primary_ray(const rt2_planar_view_constant
 
 #define RT2_BACKGROUND_DEPTH 100000.0f   /* ShaderParameters.glsl:12 */
 #define RT2_K1_TMIN 0.001f               /* refrence.rgen:27 */
-#define RT2_DEFAULT_TRACE_VARIANT 5
+#define RT2_DEFAULT_TRACE_VARIANT 16
 
 // texture(textures[idx], uv).rgb at implicit LOD 0 — Hit.glsl:35-37; R8G8B8A8_SRGB, REPEAT; pinned
 // filter identical to the oracle's sample_texture.
