@@ -173,9 +173,9 @@ __global__ void k_init_leaves(const float4* lo, const float4* hi, const uint32_t
         b.lo[i] = l; b.hi[i] = h; b.count[i] = 1u; clusters[i] = i;
     }
 }
-__global__ void k_ploc_nearest(Bvh2 b, const uint32_t* clusters, uint32_t n, uint32_t* nearest) {
+__global__ void k_ploc_nearest(Bvh2 b, const uint32_t* clusters, uint32_t n, uint32_t* nearest, uint32_t radius) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) nearest[i] = ploc_nearest(b, clusters, n, i);
+    if (i < n) nearest[i] = ploc_nearest(b, clusters, n, i, radius);
 }
 __global__ void k_ploc_merge(Bvh2 b, uint32_t* clusters, const uint32_t* nearest, uint32_t n, uint32_t* node_counter, uint32_t* valid) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -258,7 +258,7 @@ struct Scratch {
 // Build a CWBVH over `n` boxed primitives (lo/hi on device). Produces nodes (cudaMalloc'd, owned by
 // caller) and out_prim (slot -> primitive id, cudaMalloc'd, owned by caller).
 int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, uint32_t n, Node8** nodes_out, uint32_t* num_nodes_out,
-                           uint32_t** out_prim_out, uint32_t* depth_out, LaunchCounter* lc, std::string& err) {
+                           uint32_t** out_prim_out, uint32_t* depth_out, LaunchCounter* lc, std::string& err, uint32_t ploc_radius) {
     Scratch sc;
     Node8* nodes = nullptr; uint32_t* out_prim = nullptr;
     const uint32_t T = 256;
@@ -317,7 +317,7 @@ int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, 
         uint32_t cur = n;
         int guard = 0;
         while (cur > 1) {
-            k_ploc_nearest<<<grid(cur), T, 0, st>>>(b2, cl0, cur, nearest); lc->add(1);
+            k_ploc_nearest<<<grid(cur), T, 0, st>>>(b2, cl0, cur, nearest, ploc_radius); lc->add(1);
             k_ploc_merge<<<grid(cur), T, 0, st>>>(b2, cl0, nearest, cur, counters + 0, valid); lc->add(1);
             exclusive_scan(st, valid, pos, cur, scan_scratch, lc);
             k_compact<<<grid(cur), T, 0, st>>>(cl0, valid, pos, cur, cl1, counters + 1); lc->add(1);
@@ -418,7 +418,7 @@ int build_blas(cudaStream_t st, const BuildInput& in, Accel* out, LaunchCounter*
         BCK(cudaMemcpyAsync(bounds, init_bounds, sizeof init_bounds, cudaMemcpyHostToDevice, st));
         k_build_triangles<<<(n + T - 1) / T, T, 0, st>>>(in, tris_in, lo, hi, bounds); lc->add(1);
     }
-    rc = build_cwbvh_from_boxes(st, lo, hi, n, &nodes, &num_nodes, &out_prim, &depth, lc, err);
+    rc = build_cwbvh_from_boxes(st, lo, hi, n, &nodes, &num_nodes, &out_prim, &depth, lc, err, RT2_PLOC_RADIUS_TRIANGLES);
     if (rc != RT2_OK) return rc;
     BCK(cudaMalloc((void**)&tris, std::max<size_t>(n, 1) * sizeof(TriPos)));
     if (n) { k_permute_tris<<<(n + T - 1) / T, T, 0, st>>>(tris_in, out_prim, n, tris); lc->add(1); }

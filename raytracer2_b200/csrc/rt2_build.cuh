@@ -91,15 +91,21 @@ RT2_HD float box_half_area(float lx, float ly, float lz, float hx, float hy, flo
 
 // 4a. PLOC nearest-neighbour search for cluster position i (radius R). Distance = half area of the
 // union box; ties are broken by (min index, max index) so the globally best pair is always mutual.
+// Search radius: 16 for trees over instance-level boxes (TLAS, flattened instancing: heavily overlapping leaves), 8 for triangle
+// BLASes — with the reinsertion rounds behind it a narrower search gives the better triangle tree (C2: radius 2 / 4 / 6 / 8 / 16 / 32 ->
+// 2774 / 2796 / 2770 / 2805 / 2761 / 2738 Mrays/s; C5's flat tree: 955 / 998 / 1081 / 1016 / 1145 / -, profiles/r02b_trace_variant_sweep.txt)
 #ifndef RT2_PLOC_RADIUS
 #define RT2_PLOC_RADIUS 16
 #endif
-RT2_HD uint32_t ploc_nearest(const Bvh2& b, const uint32_t* clusters, uint32_t n, uint32_t i) {
+#ifndef RT2_PLOC_RADIUS_TRIANGLES
+#define RT2_PLOC_RADIUS_TRIANGLES 8
+#endif
+RT2_HD uint32_t ploc_nearest(const Bvh2& b, const uint32_t* clusters, uint32_t n, uint32_t i, uint32_t radius = RT2_PLOC_RADIUS) {
     const uint32_t ci = clusters[i];
     const float4 li = b.lo[ci], hi_ = b.hi[ci];
     float best = INFINITY; uint32_t best_j = 0xFFFFFFFFu;
-    uint32_t j0 = i > RT2_PLOC_RADIUS ? i - RT2_PLOC_RADIUS : 0u;
-    uint32_t j1 = i + RT2_PLOC_RADIUS + 1u < n ? i + RT2_PLOC_RADIUS + 1u : n;
+    uint32_t j0 = i > radius ? i - radius : 0u;
+    uint32_t j1 = i + radius + 1u < n ? i + radius + 1u : n;
     for (uint32_t j = j0; j < j1; j++) {
         if (j == i) continue;
         const uint32_t cj = clusters[j];

@@ -182,7 +182,7 @@ int fail(rt2_ctx* ctx, int code, const std::string& msg);
 struct BuildInput;
 int build_blas(cudaStream_t st, const BuildInput& in, Accel* out, LaunchCounter* lc, std::string& err);
 int build_cwbvh_from_boxes(cudaStream_t st, const float4* lo, const float4* hi, uint32_t n, Node8** nodes_out, uint32_t* num_nodes_out,
-                           uint32_t** out_prim_out, uint32_t* depth_out, LaunchCounter* lc, std::string& err);
+                           uint32_t** out_prim_out, uint32_t* depth_out, LaunchCounter* lc, std::string& err, uint32_t ploc_radius = 16u /* RT2_PLOC_RADIUS: instance-level boxes */);
 // rt2_scene.cu
 int scene_upload(rt2_ctx* ctx, const rt2_scene_desc* d);
 int scene_build_accel(rt2_ctx* ctx);

@@ -19,7 +19,7 @@ struct HostAccel {
 };
 
 static bool build_from_boxes(const std::vector<float4>& lo, const std::vector<float4>& hi, std::vector<Node8>& nodes,
-                             std::vector<uint32_t>& out_prim, uint32_t* depth_out) {
+                             std::vector<uint32_t>& out_prim, uint32_t* depth_out, uint32_t ploc_radius = RT2_PLOC_RADIUS) {
     const uint32_t n = (uint32_t)lo.size();
     if (n == 0) { nodes.assign(1, Node8{}); memset(nodes.data(), 0, sizeof(Node8)); return true; }
     V3 slo = v3(INFINITY, INFINITY, INFINITY), shi = v3(-INFINITY, -INFINITY, -INFINITY);
@@ -42,7 +42,7 @@ static bool build_from_boxes(const std::vector<float4>& lo, const std::vector<fl
     }
     uint32_t node_counter = n, cur = n;
     while (cur > 1) {
-        for (uint32_t i = 0; i < cur; i++) nearest[i] = ploc_nearest(b2, cl0.data(), cur, i);
+        for (uint32_t i = 0; i < cur; i++) nearest[i] = ploc_nearest(b2, cl0.data(), cur, i, ploc_radius);
         // emulate the parallel kernel: every "thread" reads the pre-merge cluster array
         std::vector<uint32_t> snapshot(cl0.begin(), cl0.begin() + cur);
         for (uint32_t i = 0; i < cur; i++) {
@@ -138,7 +138,7 @@ void* hostemu_build(const rt2_scene_desc* d) {
     BuildInput in{d->vertices, d->indices, d->geometries, offs.data(), d->num_geometries, n};
     std::vector<TriPos> tris_in(n); std::vector<float4> lo(n), hi(n);
     for (uint32_t i = 0; i < n; i++) build_triangle(in, i, tris_in.data(), lo.data(), hi.data());
-    if (!build_from_boxes(lo, hi, hs->blas.nodes, hs->blas.slot_to_prim, &hs->blas.depth)) { delete hs; return nullptr; }
+    if (!build_from_boxes(lo, hi, hs->blas.nodes, hs->blas.slot_to_prim, &hs->blas.depth, RT2_PLOC_RADIUS_TRIANGLES)) { delete hs; return nullptr; }
     hs->blas.tris.resize(n);
     for (uint32_t s = 0; s < n; s++) hs->blas.tris[s] = tris_in[hs->blas.slot_to_prim[s]];
     if (d->num_instances && d->instance_transforms) {
