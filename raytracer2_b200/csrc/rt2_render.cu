@@ -313,6 +313,16 @@ template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = fals
 __global__ void __launch_bounds__(128, 6) k_trace_dyn_tlas(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, true, GENERIC>(a); }
 // flattened instancing: single-level walk over the (instance, triangle) tree
 template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false>
+#ifndef RT2_FLAT_POSTPONE
+#define RT2_FLAT_POSTPONE 30   /* 20 / 25 / 30: 1143 / 1152 (with refill 6, check 6) / 1154 Mrays/s on C5 */
+#endif
+#ifndef RT2_FLAT_REFILL
+#define RT2_FLAT_REFILL 4
+#endif
+#ifndef RT2_FLAT_CHECK
+#define RT2_FLAT_CHECK 8
+#endif
+#define RT2_FLAT_PARAMS RT2_FLAT_POSTPONE, RT2_FLAT_REFILL, RT2_FLAT_CHECK     /* POSTPONE_PCT, REFILL_MIN, CHECK_EVERY of the flat walk */
 #ifndef RT2_FLAT_MIN_BLOCKS
 #define RT2_FLAT_MIN_BLOCKS 7   /* 72 registers, 28 warps per SM: the flat walk is latency-bound (L2 hit 72-80 %, DRAM 2 %); 5 / 6 / 7 / 8 blocks: 1021 / 1086 / 1144 / 1096 Mrays/s on C5 */
 #endif
@@ -1081,7 +1091,7 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
                 if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], st));
                 t.queue = k.q[it & 1]; t.count = k.cnt + 2 * it; t.head = k.cnt + 2 * it + 1;
                 if (flat) {
-                    k_trace_dyn_flat<20, 4, 8><<<k.trace_blocks, 128, 0, st>>>(t);
+                    k_trace_dyn_flat<RT2_FLAT_PARAMS><<<k.trace_blocks, 128, 0, st>>>(t);
                 } else if (s.num_instances) {
                     // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
                     const bool unified = ctx->trace_variant != 0 && unified_walk_fits(s);
@@ -1112,7 +1122,7 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
 // ------------------------------------------------------------------------------------------------
 static void launch_trace_kernel(rt2_ctx* ctx, const TraceArgs& t, bool flat, int blocks, cudaStream_t st) {
     const DeviceScene& s = ctx->scene;
-    if (flat) k_trace_dyn_flat<20, 4, 8><<<blocks, 128, 0, st>>>(t);
+    if (flat) k_trace_dyn_flat<RT2_FLAT_PARAMS><<<blocks, 128, 0, st>>>(t);
     else if (s.num_instances) {
         if (ctx->trace_variant != 0 && unified_walk_fits(s)) k_trace_dyn_tlas<20, 4, 8><<<blocks, 128, 0, st>>>(t);
         else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, st>>>(t);
@@ -1353,7 +1363,7 @@ int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* cou
     TraceArgs t = make_trace_args(ctx);
     t.queue = queue; t.count = count; t.head = head; t.stat_rays = stat_rays;
     if (t.flat_nodes) {
-        k_trace_dyn_flat<20, 4, 8, true><<<ctx->trace_blocks_per_sm[3] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        k_trace_dyn_flat<RT2_FLAT_PARAMS, true><<<ctx->trace_blocks_per_sm[3] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
     } else if (s.num_instances) {
         if (unified_walk_fits(s)) k_trace_dyn_tlas<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
         else k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
@@ -1384,7 +1394,7 @@ int render_init(rt2_ctx* ctx) {
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p0, k_path_warp<false>, 128, 0));
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p1, k_path_warp<true>, 128, 0));
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2, k_path_warp<false, true>, 128, 0));
-    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, k_trace_dyn_flat<20, 4, 8>, 128, 0));
+    RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, k_trace_dyn_flat<RT2_FLAT_PARAMS>, 128, 0));
     ctx->path_blocks_per_sm[0] = std::max(p0, 1); ctx->path_blocks_per_sm[1] = std::max(p1, 1); ctx->path_blocks_per_sm[2] = std::max(p2, 1);
     ctx->trace_blocks_per_sm[3] = std::max(b3, 1);
     if (const char* e = getenv("RT2_USE_FLAT")) ctx->use_flat = atoi(e) != 0;
