@@ -32,7 +32,7 @@ def hostemu():
     d = os.path.join(ROOT, "tests", "hostemu")
     so = os.path.join(d, "libhostemu.so")
     src = os.path.join(d, "hostemu.cu")
-    deps = [src] + [os.path.join(ROOT, "raytracer2_b200", "csrc", f) for f in ("rt2_build.cuh", "rt2_bvh.cuh", "rt2_math.cuh")]
+    deps = [src] + [os.path.join(ROOT, "raytracer2_b200", "csrc", f) for f in ("rt2_build.cuh", "rt2_reinsert.cuh", "rt2_bvh.cuh", "rt2_math.cuh")]
     if not os.path.exists(so) or any(os.path.getmtime(p) > os.path.getmtime(so) for p in deps):
         nvcc = "/usr/local/cuda/bin/nvcc"
         if not os.path.exists(nvcc):
@@ -46,6 +46,7 @@ def hostemu():
     L.hostemu_trace_primary.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]
     L.hostemu_trace_rays.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_float, C.c_float, C.c_void_p, C.POINTER(C.c_uint64)]
     L.hostemu_info.argtypes = [C.c_void_p] + [C.POINTER(C.c_uint32)] * 3
+    L.hostemu_reinsertion_probe.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double)]
     return L
 
 

@@ -164,6 +164,73 @@ void* hostemu_build(const rt2_scene_desc* d) {
     return hs;
 }
 void hostemu_destroy(void* p) { delete (HostScene*)p; }
+
+// PLOC BVH2 of the scene's triangles + `iters` reinsertion rounds (rt2_reinsert.cuh), checking after every round that the result is
+// still a binary tree over the same leaves with consistent parent pointers, enclosing boxes and additive counts.
+// out[0] = SAH (sum of inner-node areas / root area) before, out[1] = after, out[2] = moves applied, out[3] = 1 if every check held.
+void hostemu_reinsertion_probe(const rt2_scene_desc* d, int iters, double* out) {
+    std::vector<uint32_t> offs(d->num_geometries + 1, 0);
+    for (uint32_t g = 0; g < d->num_geometries; g++) offs[g + 1] = offs[g] + d->index_counts[g] / 3;
+    const uint32_t n = offs[d->num_geometries];
+    BuildInput in{d->vertices, d->indices, d->geometries, offs.data(), d->num_geometries, n};
+    std::vector<TriPos> tris_in(n); std::vector<float4> lo(n), hi(n);
+    for (uint32_t i = 0; i < n; i++) build_triangle(in, i, tris_in.data(), lo.data(), hi.data());
+    V3 slo = v3(INFINITY, INFINITY, INFINITY), shi = v3(-INFINITY, -INFINITY, -INFINITY);
+    for (uint32_t i = 0; i < n; i++) { slo = v3(fminf(slo.x, lo[i].x), fminf(slo.y, lo[i].y), fminf(slo.z, lo[i].z)); shi = v3(fmaxf(shi.x, hi[i].x), fmaxf(shi.y, hi[i].y), fmaxf(shi.z, hi[i].z)); }
+    std::vector<std::pair<uint64_t, uint32_t>> kv(n);
+    for (uint32_t i = 0; i < n; i++) kv[i] = {morton_key(lo[i], hi[i], slo, shi), i};
+    std::stable_sort(kv.begin(), kv.end(), [](auto& a, auto& b) { return a.first < b.first; });
+    std::vector<float4> blo(2 * (size_t)n), bhi(2 * (size_t)n);
+    std::vector<uint32_t> bcount(2 * (size_t)n), cl0(n), cl1(n), nearest(n), valid(n);
+    Bvh2 b2{blo.data(), bhi.data(), bcount.data()};
+    for (uint32_t i = 0; i < n; i++) { float4 l = lo[kv[i].second], h = hi[kv[i].second]; l.w = u2f(0xFFFFFFFFu); h.w = u2f(0xFFFFFFFFu); blo[i] = l; bhi[i] = h; bcount[i] = 1; cl0[i] = i; }
+    uint32_t node_counter = n, cur = n;
+    while (cur > 1) {
+        for (uint32_t i = 0; i < cur; i++) nearest[i] = ploc_nearest(b2, cl0.data(), cur, i, RT2_PLOC_RADIUS_TRIANGLES);
+        for (uint32_t i = 0; i < cur; i++) valid[i] = ploc_merge(b2, cl0.data(), nearest.data(), cur, i, &node_counter);
+        uint32_t m = 0;
+        for (uint32_t i = 0; i < cur; i++) if (valid[i]) cl1[m++] = cl0[i];
+        cur = m; std::swap(cl0, cl1);
+    }
+    const uint32_t root = cl0[0], N = node_counter;
+    std::vector<uint32_t> parent(N, 0xFFFFFFFFu);
+    for (uint32_t i = n; i < N; i++) { parent[f2u(blo[i].w)] = i; parent[f2u(bhi[i].w)] = i; }
+    auto sah = [&]() { double s = 0; for (uint32_t i = n; i < N; i++) s += bvh2_half_area(b2, i); return s / bvh2_half_area(b2, root); };
+    auto check = [&]() -> bool {
+        std::vector<uint8_t> seen(N, 0); std::vector<uint32_t> st{root}; uint32_t reached = 0, leaves = 0;
+        if (parent[root] != 0xFFFFFFFFu) return false;
+        while (!st.empty()) {
+            const uint32_t x = st.back(); st.pop_back();
+            if (x >= N || seen[x]) return false;
+            seen[x] = 1; reached++;
+            if (x < n) { leaves++; if (bcount[x] != 1) return false; continue; }
+            const uint32_t l = f2u(blo[x].w), r = f2u(bhi[x].w);
+            if (l >= N || r >= N || l == r || parent[l] != x || parent[r] != x) return false;
+            if (bcount[x] != bcount[l] + bcount[r]) return false;
+            const float4 ll = blo[l], lh = bhi[l], rl = blo[r], rh = bhi[r];
+            if (blo[x].x != fminf(ll.x, rl.x) || blo[x].y != fminf(ll.y, rl.y) || blo[x].z != fminf(ll.z, rl.z)) return false;
+            if (bhi[x].x != fmaxf(lh.x, rh.x) || bhi[x].y != fmaxf(lh.y, rh.y) || bhi[x].z != fmaxf(lh.z, rh.z)) return false;
+            st.push_back(l); st.push_back(r);
+        }
+        return reached == N && leaves == n && bcount[root] == n;
+    };
+    out[0] = sah(); out[2] = 0; out[3] = check() ? 1.0 : 0.0;
+    std::vector<uint32_t> target(N), lca(N); std::vector<float> gain(N); std::vector<unsigned long long> lock(N), pass(N); std::vector<uint8_t> win(N);
+    Reinsert r{b2, parent.data(), root, n, N, target.data(), lca.data(), gain.data(), lock.data(), pass.data()};
+    for (int it = 0; it < iters && out[3] == 1.0; it++) {
+        std::fill(lock.begin(), lock.end(), 0ull); std::fill(pass.begin(), pass.end(), 0ull);
+        for (uint32_t i = 0; i < N; i++) reinsert_find(r, i);
+        for (uint32_t i = 0; i < N; i++) reinsert_lock(r, i);
+        for (uint32_t i = 0; i < N; i++) win[i] = reinsert_check(r, i) ? 1 : 0;
+        for (uint32_t i = 0; i < N; i++) if (win[i]) { reinsert_apply(r, i, target[i]); out[2] += 1; }
+        std::vector<uint32_t> order; std::vector<uint32_t> st{root};
+        while (!st.empty() && order.size() <= N) { uint32_t x = st.back(); st.pop_back(); order.push_back(x); if (x >= n && x < N) { st.push_back(f2u(blo[x].w)); st.push_back(f2u(bhi[x].w)); } }
+        if (order.size() != N) { out[3] = 0.0; break; }
+        for (size_t k = order.size(); k-- > 0;) if (order[k] >= n) reinsert_refit_node(b2, order[k]);
+        if (!check()) out[3] = 0.0;
+    }
+    out[1] = sah();
+}
 void hostemu_info(void* p, uint32_t* nodes, uint32_t* depth, uint32_t* tlas_nodes) {
     HostScene* hs = (HostScene*)p; *nodes = (uint32_t)hs->blas.nodes.size(); *depth = hs->blas.depth; *tlas_nodes = (uint32_t)hs->tlas_nodes.size();
 }

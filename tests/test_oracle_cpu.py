@@ -225,3 +225,19 @@ def test_axis_aligned_rays_do_not_walk_the_whole_tree(hostemu):
     assert v_axis.value <= 2 * v_tilt.value, (v_axis.value, v_tilt.value)
     assert v_axis.value / n < 200
     assert (out[:, 1] != 0xFFFFFFFF).mean() > 0.9      # closed hall: nearly every ray hits
+
+
+@pytest.mark.parametrize("kind,scale,seed", [(rt.SCENE_HALL, 0.25, 0), (rt.SCENE_MANYLIGHT, 0.1, 0), (rt.SCENE_RANDOM, 1.0, 3), (rt.SCENE_CORNELL, 1.0, 0)])
+def test_parallel_reinsertion_keeps_a_valid_tree_and_lowers_the_sah_cost(hostemu, kind, scale, seed):
+    """rt2_reinsert.cuh (the functions the device kernels wrap), round by round on the CPU: after every round the BVH2 is still a binary
+    tree over the same leaves — every node reached exactly once, parent pointers consistent, boxes exactly the union of their children,
+    counts additive — and the node-area cost the moves were chosen to reduce goes down."""
+    sc = rt.Scene(kind, scale, 16, seed)
+    out = (C.c_double * 4)()
+    hostemu.hostemu_reinsertion_probe(C.cast(sc.desc, C.c_void_p), 6, out)
+    before, after, moves, ok = out[0], out[1], int(out[2]), out[3]
+    assert ok == 1.0, "the tree broke"
+    if sc.num_triangles >= 1000:
+        assert moves > 0 and after < before * 0.995, (before, after, moves)
+    else:
+        assert after <= before * (1 + 1e-6)
