@@ -84,6 +84,10 @@ typedef struct rt2_texture_desc {
 /* What `Model::from_gltf(ctx, gltf::Model)` consumes (src/model.rs:185-476) plus the sky box
  * (src/main.rs:63,145) and the TLAS instance list (src/main.rs:153-191; the reference always has
  * exactly one identity instance — more than one is the documented extension of SURVEY.md §8a A2).
+ * Single-BLAS by design: the reference builds ONE bottom-level structure holding every geometry of the model
+ * (src/model.rs:379-459) and instances it once (src/model.rs:63-75); the extension keeps that shape — every
+ * instance is a transform of that one BLAS, there is no per-instance BLAS index.  A scene made of several
+ * different meshes is, as in the reference, several geometries of the one BLAS.
  */
 typedef struct rt2_scene_desc {
     const rt2_vertex*        vertices;       uint64_t num_vertices;
