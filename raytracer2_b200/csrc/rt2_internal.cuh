@@ -145,6 +145,7 @@ struct rt2_ctx {
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
     int trace_blocks_per_sm[4] = {1, 1, 1, 1};          // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level, [3] flattened instancing
+    int trace_queue_blocks_per_sm = 1;       // resident blocks of k_trace_queue (the ReSTIR passes' ray-queue kernel)
     bool use_flat = true;                                // trace instanced scenes through the flattened tree when it was built (RT2_USE_FLAT=0: two-level walk)
     int trace_variant = 0;
     // K1 sample schedule: speculate = -1 auto (from the previous frame's miss statistics, read back without a sync), 0 never, 1 whenever

@@ -328,6 +328,24 @@ template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = fals
 #endif
 __global__ void __launch_bounds__(128, RT2_FLAT_MIN_BLOCKS) k_trace_dyn_flat(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, false, GENERIC, false, true>(a); }
 
+// The ray-queue kernel of the ReSTIR passes (GENERIC rays: origin | tmin, direction | tmax per slot) on single-level scenes: an entry
+// point of its own so that its register cap and refill cadence can differ from K1's (80 registers / 36 % occupancy without the cap)
+#ifndef RT2_GENERIC_POSTPONE
+#define RT2_GENERIC_POSTPONE 25
+#endif
+#ifndef RT2_GENERIC_REFILL
+#define RT2_GENERIC_REFILL 6
+#endif
+#ifndef RT2_GENERIC_CHECK
+#define RT2_GENERIC_CHECK 6
+#endif
+#ifndef RT2_GENERIC_MIN_BLOCKS
+#define RT2_GENERIC_MIN_BLOCKS 7
+#endif
+__global__ void __launch_bounds__(128, RT2_GENERIC_MIN_BLOCKS) k_trace_queue(TraceArgs a) {
+    trace_dyn_body<RT2_GENERIC_POSTPONE, RT2_GENERIC_REFILL, RT2_GENERIC_CHECK, false, true>(a);
+}
+
 // refrence.rgen:28-46 for the path in `slot` whose ray just came back (hit record in st_hit): emission / throughput update,
 // cosine-lobe sample, path regeneration.  Returns true while the pixel still has rays to trace (state written back), false when
 // its last sample finished (radiance stored).
@@ -1368,7 +1386,7 @@ int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* cou
         if (unified_walk_fits(s)) k_trace_dyn_tlas<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
         else k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
     } else {
-        k_trace_dyn<20, 4, 8, false, true><<<ctx->trace_blocks_per_sm[0] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        k_trace_queue<<<ctx->trace_queue_blocks_per_sm * ctx->num_sms, 128, 0, ctx->stream>>>(t);
     }
     RT2_CUDA(ctx, cudaGetLastError());
     return RT2_OK;
@@ -1397,6 +1415,7 @@ int render_init(rt2_ctx* ctx) {
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, k_trace_dyn_flat<RT2_FLAT_PARAMS>, 128, 0));
     ctx->path_blocks_per_sm[0] = std::max(p0, 1); ctx->path_blocks_per_sm[1] = std::max(p1, 1); ctx->path_blocks_per_sm[2] = std::max(p2, 1);
     ctx->trace_blocks_per_sm[3] = std::max(b3, 1);
+    { int bq = 0; RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bq, k_trace_queue, 128, 0)); ctx->trace_queue_blocks_per_sm = std::max(bq, 1); }
     if (const char* e = getenv("RT2_USE_FLAT")) ctx->use_flat = atoi(e) != 0;
     ctx->trace_blocks_per_sm[0] = std::max(b0, 1); ctx->trace_blocks_per_sm[1] = std::max(b1, 1); ctx->trace_blocks_per_sm[2] = std::max(b2, 1);
     return RT2_OK;

@@ -6,7 +6,10 @@ import csv, io, json, subprocess, sys
 
 rep, out, note = sys.argv[1], sys.argv[2], (sys.argv[3] if len(sys.argv) > 3 else "")
 rays_per_launch = float(sys.argv[4]) if len(sys.argv) > 4 else None      # rays one captured launch traces (from the same run's stats)
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+if rep.endswith(".csv"):        # the raw page already exported on the GPU box (reports above gpurun's 64 MB limit)
+    raw = open(rep).read()
+else:
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
 open(out + "_full_raw.csv", "w").write(raw)
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, data = rows[0], rows[2:]
