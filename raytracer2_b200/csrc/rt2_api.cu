@@ -64,6 +64,7 @@ int rt2_create(int cuda_device, rt2_ctx** out) {
     if (e != cudaSuccess) { std::string m = cudaGetErrorString(e); rt2_destroy(ctx); return fail(nullptr, RT2_E_CUDA, m); }
     int rc = render_init(ctx);
     if (rc == RT2_OK) rc = noalloc_init(ctx);
+    if (rc == RT2_OK) rc = codec_luts_init(ctx);
     if (rc != RT2_OK) { std::string m = ctx->last_error; rt2_destroy(ctx); return fail(nullptr, rc, m); }
     *out = ctx;
     return RT2_OK;
@@ -82,6 +83,7 @@ int rt2_destroy(rt2_ctx* ctx) {
     }
     if (ctx->h_gconst_ring) cudaFreeHost(ctx->h_gconst_ring);
     if (ctx->h_k1_stats) cudaFreeHost(ctx->h_k1_stats);
+    if (ctx->codec_luts) cudaFree(ctx->codec_luts);
     if (ctx->k1_stats_ready) cudaEventDestroy(ctx->k1_stats_ready);
     scene_release(ctx); frame_release(ctx); passes_release(ctx);
     for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);

@@ -13,6 +13,10 @@ namespace rt2 {
 __device__ __forceinline__ float log2_pinned(float x) { return (float)log2((double)x); }
 __device__ __forceinline__ float exp2_pinned(float x) { return (float)exp2((double)x); }
 __device__ __forceinline__ float pow_pinned(float x, float y) { return (float)pow((double)x, (double)y); }
+// pow(x, 5.0) under the same pin (binary64, rounded once to binary32): four binary64 multiplications carry <= 2 ulp(binary64) of error,
+// as libm's pow does, so the binary32 result differs from it only when x^5 lies within ~2^-52 of a rounding boundary (once in ~10^8
+// evaluations: inside the tolerance the reservoir parity tests state for the binary64 transcendentals)
+__device__ __forceinline__ float pow5_pinned(float x) { const double d = (double)x, d2 = d * d; return (float)(d2 * d2 * d); }
 __device__ __forceinline__ float cos_pinned(float a) { float s, c; sincos_pinned(a, &s, &c); return c; }
 __device__ __forceinline__ float sin_pinned(float a) { float s, c; sincos_pinned(a, &s, &c); return s; }
 __device__ __forceinline__ float length3(V3 v) { return sqrtf(dot3(v, v)); }
@@ -37,9 +41,13 @@ __device__ __forceinline__ uint32_t pack_rgba8_gamma(float r, float g, float b, 
     b = pow_pinned(clampf(b, 0.f, 1.f), ig); a = pow_pinned(clampf(a, 0.f, 1.f), ig);
     return pack_ufloat(r, 8, 0.5f) | (pack_ufloat(g, 8, 0.5f) << 8) | (pack_ufloat(b, 8, 0.5f) << 16) | (pack_ufloat(a, 8, 0.5f) << 24);
 }
-__device__ __forceinline__ float4 unpack_rgba8_gamma(uint32_t p) {
-    return make_float4(pow_pinned(saturatef(unpack_ufloat(p, 8)), 2.2f), pow_pinned(saturatef(unpack_ufloat(p >> 8, 8)), 2.2f),
-                       pow_pinned(saturatef(unpack_ufloat(p >> 16, 8)), 2.2f), pow_pinned(saturatef(unpack_ufloat(p >> 24, 8)), 2.2f));
+__device__ __forceinline__ float gamma22_decode(uint32_t byte) { return pow_pinned(saturatef(unpack_ufloat(byte, 8)), 2.2f); }
+// `lut` = CodecLuts::gamma22 (the 256 values of gamma22_decode, tabulated on this device by k_build_codec_luts): the G-buffer's
+// specular/roughness word is decoded at every stage of every ReSTIR pass and for every neighbour K6 / K7 look at — four binary64
+// pow() per decode otherwise.  Bit-identical to the inline form by construction.
+__device__ __forceinline__ float4 unpack_rgba8_gamma(uint32_t p, const float* __restrict__ lut = nullptr) {
+    if (lut) return make_float4(__ldg(lut + (p & 0xffu)), __ldg(lut + ((p >> 8) & 0xffu)), __ldg(lut + ((p >> 16) & 0xffu)), __ldg(lut + (p >> 24)));
+    return make_float4(gamma22_decode(p), gamma22_decode(p >> 8), gamma22_decode(p >> 16), gamma22_decode(p >> 24));
 }
 __device__ __forceinline__ V3 unpack_r8g8b8(uint32_t p) { return v3(unpack_ufloat(p, 8), unpack_ufloat(p >> 8, 8), unpack_ufloat(p >> 16, 8)); }
 __device__ __forceinline__ uint32_t pack_r8g8b8(V3 c) { return pack_ufloat(c.x, 8, 0.5f) | (pack_ufloat(c.y, 8, 0.5f) << 8) | (pack_ufloat(c.z, 8, 0.5f) << 16); }
@@ -76,17 +84,19 @@ __device__ __forceinline__ V3 oct_to_ndir_unorm32(uint32_t p) {
 #define RT2_LIGHT_MIN_LOG2 (-8.f)
 #define RT2_LIGHT_MAX_LOG2 (40.f)
 __device__ __forceinline__ float calc_luminance(V3 c) { return dot3(c, v3(0.299f, 0.587f, 0.114f)); }
-__device__ __forceinline__ float unpack_light_radiance(uint32_t lr) {                          // :65-68
+// `lut` = CodecLuts::light_radiance: the function below for all 65536 codes (a binary64 exp2 per light candidate otherwise)
+__device__ __forceinline__ float unpack_light_radiance(uint32_t lr, const float* __restrict__ lut = nullptr) {   // :65-68
+    if (lut) return __ldg(lut + (lr & 0xffffu));
     if (lr == 0u) return 0.f;
     return exp2_pinned(((float)(lr - 1u) / 65534.0f) * (RT2_LIGHT_MAX_LOG2 - RT2_LIGHT_MIN_LOG2) + RT2_LIGHT_MIN_LOG2);
 }
 struct TriangleLight { V3 base, edge1, edge2, radiance, normal; float surface_area; };
-__device__ __forceinline__ TriangleLight create_triangle_light(const rt2_light_info& li) {    // :320-343
+__device__ __forceinline__ TriangleLight create_triangle_light(const rt2_light_info& li, const float* __restrict__ radiance_lut = nullptr) {    // :320-343
     TriangleLight t;
     t.edge1 = oct_to_ndir_unorm32(li.direction1) * f16_bits_to_f32((uint16_t)(li.scalars & 0xffffu));
     t.edge2 = oct_to_ndir_unorm32(li.direction2) * f16_bits_to_f32((uint16_t)(li.scalars >> 16));
     t.base = v3(li.center[0], li.center[1], li.center[2]) - (t.edge1 + t.edge2) / 3.0f;
-    t.radiance = unpack_r8g8b8(li.color_type_and_flags) * unpack_light_radiance(li.log_radiance & 0xffffu);
+    t.radiance = unpack_r8g8b8(li.color_type_and_flags) * unpack_light_radiance(li.log_radiance & 0xffffu, radiance_lut);
     const V3 ln = cross3(t.edge1, t.edge2);
     const float len = length3(ln);
     if (len > 0.0f) { t.surface_area = 0.5f * len; t.normal = ln / len; }

@@ -162,6 +162,7 @@ struct rt2_ctx {
     uint64_t device_bytes = 0;
     // lights / pdf textures (K10/K12)
     rt2_light_info* light_info = nullptr; uint32_t light_capacity = 0;   // = the scene's light count
+    float* codec_luts = nullptr;                                           // [0,256): gamma22_decode(byte); [256, 256 + 65536): unpack_light_radiance(code); then 16384 x logluv_luminance(exponent) — built on this device at rt2_create
     uint32_t restir_phase = 0;                                             // set by rt2_group_render around a sharded frame with K6 / K7: which part of render_restir runs (0 = all)
     uint32_t light_records = 0;                                            // records allocated: light_capacity, + 2 with a sky (a zero record and the environment light)
     uint32_t* geom_to_light = nullptr;
@@ -195,6 +196,7 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp);
 int render_primary(rt2_ctx* ctx, const rt2_launch_params& lp);
 int render_init(rt2_ctx* ctx);
 // rt2_noalloc.cu
+int codec_luts_init(rt2_ctx* ctx);                 // rt2_passes_common.cu: tabulates the two byte/half-word decoders that cost a binary64 transcendental each
 int noalloc_init(rt2_ctx* ctx);                    // resolves the static scratch's device address, once per device (cudaGetSymbolAddress)
 
 }  // namespace rt2

@@ -2,8 +2,26 @@
 // read-out through rt2_read (RenderResources, src/render_resources.rs:130-341).
 #include <vector>
 #include "rt2_internal.cuh"
+#include "rt2_restir.cuh"
 
 namespace rt2 {
+
+// The two decoders that cost a binary64 transcendental per call, tabulated with the very functions they replace (so a lookup is the
+// same bits as the inline form): the gamma-2.2 byte of the G-buffer's specular/roughness word (256 values) and the 16-bit log radiance
+// of a light record (65536 values); plus the luminance of a LogLuv exponent field (16384 values), decoded for every GI reservoir K6 / K7 / K8 load.
+__global__ void k_build_codec_luts(float* luts) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < 256u) luts[i] = gamma22_decode(i);
+    if (i < 65536u) luts[256u + i] = unpack_light_radiance(i);
+    if (i < 16384u) luts[256u + 65536u + i] = logluv_luminance(i);
+}
+int codec_luts_init(rt2_ctx* ctx) {
+    if (ctx->codec_luts) return RT2_OK;
+    RT2_CUDA(ctx, cudaMalloc((void**)&ctx->codec_luts, (256 + 65536 + 16384) * sizeof(float)));
+    k_build_codec_luts<<<65536 / 256, 256, 0, ctx->stream>>>(ctx->codec_luts);
+    RT2_CUDA(ctx, cudaGetLastError());
+    return RT2_OK;
+}
 
 void lights_release(rt2_ctx* ctx);
 size_t mip_chain_texels(uint32_t w, uint32_t h, uint32_t mips);

@@ -17,6 +17,7 @@ struct PostArgs {
     float4* motion_vectors;
     const float4* sky; uint32_t sky_w, sky_h;
     uchar4* out;
+    const float* gamma_lut;      // CodecLuts::gamma22
 };
 
 __device__ __forceinline__ float agx_contrast(float x) {          // agxDefaultContrastApprox, :47-58
@@ -88,7 +89,7 @@ __global__ void __launch_bounds__(256) k_postprocess(PostArgs a) {
         col = h3(a.diffuse[i]);                                                         // :156-157
     } else if (a.gb_depth[i] != 100000.0f) {                                            // :158-174
         const V3 albedo = unpack_r11g11b10(a.gb_diffuse_albedo[i]);
-        const float4 sf = unpack_rgba8_gamma(a.gb_specular_rough[i]);
+        const float4 sf = unpack_rgba8_gamma(a.gb_specular_rough[i], a.gamma_lut);
         const V3 emissive = h3(a.gb_emissive[i]);
         V3 di = h3(a.diffuse[i]), si = h3(a.specular[i]);
         if (g.textures == 1u) { di = di * albedo; si = si * v3(fmaxf(0.01f, sf.x), fmaxf(0.01f, sf.y), fmaxf(0.01f, sf.z)); }
@@ -122,7 +123,7 @@ int post_process(rt2_ctx* ctx, uint32_t frame) {
     PostArgs a{};
     a.g = ctx->d_gconst; a.width = f.width; a.height = f.height;
     a.diffuse = f.diffuse_f16; a.specular = f.specular_f16; a.out = f.output_rgba8;
-    a.sky = ctx->scene.sky; a.sky_w = ctx->scene.sky_w; a.sky_h = ctx->scene.sky_h;
+    a.sky = ctx->scene.sky; a.sky_w = ctx->scene.sky_w; a.sky_h = ctx->scene.sky_h; a.gamma_lut = ctx->codec_luts;
     if (ctx->gconst.refrence_mode != 1u) {
         if (!f.gb_depth[0]) return fail(ctx, RT2_E_STATE, "no G-buffer: run rt2_render in ReSTIR mode first");
         const uint32_t cur = frame & 1u;           // source_descriptors[frame % 2], src/postprocess.rs:284

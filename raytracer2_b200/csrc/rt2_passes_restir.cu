@@ -486,7 +486,7 @@ __device__ __forceinline__ Surface di_stage_surface(const DIWaveArgs& w, const r
     sec.normal = oct_to_ndir_unorm32(s0.w);
     sec.geo_normal = sec.normal;
     sec.diffuse_albedo = unpack_r11g11b10(s1.z);
-    const float4 sr = unpack_rgba8_gamma(s1.w);
+    const float4 sr = unpack_rgba8_gamma(s1.w, a.sc.gamma_lut);
     sec.specular_f0 = v3(sr.x, sr.y, sr.z);
     sec.roughness = sr.w;
     sec.diffuse_probability = 1.0f;
@@ -802,7 +802,7 @@ __global__ void __launch_bounds__(128) k_shade_secondary(GIArgs a) {
     sec.normal = oct_to_ndir_unorm32(s0.w);
     sec.geo_normal = sec.normal;
     sec.diffuse_albedo = unpack_r11g11b10(s1.z);
-    const float4 sr = unpack_rgba8_gamma(s1.w);
+    const float4 sr = unpack_rgba8_gamma(s1.w, a.sc.gamma_lut);
     sec.specular_f0 = v3(sr.x, sr.y, sr.z);
     sec.roughness = sr.w;
     sec.diffuse_probability = 1.0f;
@@ -869,7 +869,7 @@ __global__ void __launch_bounds__(128, RT2_K8_BLOCKS) k_gi_final_shading(GIArgs 
     const uint32_t rx = g.runtime_params.active_checkerboard_field != 0u ? (px >> 1) : px;
     const uint32_t row_pitch = g.restir_gi.reservoir_buffer_params.reservoir_block_row_pitch, array_pitch = g.restir_gi.reservoir_buffer_params.reservoir_array_pitch;
     // sic: reads the K5 output page, not finalShadingInputBufferIndex (:50)
-    const GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, g.restir_gi.buffer_indices.secondary_surface_restirdi_output_buffer_index));
+    const GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, g.restir_gi.buffer_indices.secondary_surface_restirdi_output_buffer_index), a.sc.logluv_lut);
     V3 diffuse = v3(0.f, 0.f, 0.f), specular = v3(0.f, 0.f, 0.f);
     if (reservoir.M != 0u) {
         V3 radiance = reservoir.radiance * reservoir.weight_sum;
@@ -1035,7 +1035,7 @@ __global__ void __launch_bounds__(128) k_brdf_rays_shade(GIWaveArgs w) {
             const V3 diffuse = is_specular_ray ? v3(0.f, 0.f, 0.f) : radiance * brdf_over_pdf;
             V3 specular = is_specular_ray ? radiance * brdf_over_pdf : v3(0.f, 0.f, 0.f);
             V3 f0 = v3(0.f, 0.f, 0.f);                                 // the primary surface's specularF0 is all the shading tail needs
-            if ((float)px < g.view.viewport_size[0] && (float)py < g.view.viewport_size[1]) { const float4 sr = unpack_rgba8_gamma(a.gb.specular_rough[(size_t)py * a.width + px]); f0 = v3(sr.x, sr.y, sr.z); }
+            if ((float)px < g.view.viewport_size[0] && (float)py < g.view.viewport_size[1]) { const float4 sr = unpack_rgba8_gamma(a.gb.specular_rough[(size_t)py * a.width + px], a.gb.gamma_lut); f0 = v3(sr.x, sr.y, sr.z); }
             specular = demodulate_specular(f0, specular);
             if (px < a.width) store_shading_output(g, (size_t)py * a.width + px, diffuse, specular, false, a.diffuse, a.specular, a.diffuse_f32);
         }
@@ -1205,7 +1205,7 @@ __global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_temporal(GIResample
     const uint32_t field = g.runtime_params.active_checkerboard_field;
     const uint32_t rx = field != 0u ? (px >> 1) : px;
     const uint32_t row_pitch = gi.reservoir_buffer_params.reservoir_block_row_pitch, array_pitch = gi.reservoir_buffer_params.reservoir_array_pitch;
-    GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, gi.buffer_indices.secondary_surface_restirdi_output_buffer_index));
+    GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, gi.buffer_indices.secondary_surface_restirdi_output_buffer_index), a.sc.logluv_lut);
     V3 motion = v3(0.f, 0.f, 0.f);
     if (px < a.width && py < a.height) { const float4 m = a.motion[(size_t)py * a.width + px]; motion = v3(m.x, m.y, m.z); }
     {   // convertMotionVectorToPixelSpace, GBufferHelpers.glsl:69-80
@@ -1242,7 +1242,7 @@ __global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_temporal(GIResample
             if (!is_fallback && !is_valid_neighbor(surface.normal, temporal_surface.normal, expected_prev_depth, temporal_surface.view_depth, tp.normal_threshold, tp.depth_threshold)) continue;
             if (!materials_similar(surface, temporal_surface)) continue;
             const uint32_t prx = field != 0u ? ((uint32_t)ix >> 1) : (uint32_t)ix;
-            temporal = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, prx, (uint32_t)iy, gi.buffer_indices.temporal_resampling_input_buffer_index));
+            temporal = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, prx, (uint32_t)iy, gi.buffer_indices.temporal_resampling_input_buffer_index), a.sc.logluv_lut);
             if (temporal.M == 0u) continue;
             found = true;
             break;
@@ -1308,7 +1308,7 @@ __global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_spatial(GIResampleA
     const uint32_t rx = field != 0u ? (px >> 1) : px;
     const uint32_t row_pitch = gi.reservoir_buffer_params.reservoir_block_row_pitch, array_pitch = gi.reservoir_buffer_params.reservoir_array_pitch;
     const uint32_t src = gi.buffer_indices.spatial_resampling_input_buffer_index;
-    GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, src));
+    GIReservoir reservoir = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, rx, py, src), a.sc.logluv_lut);
     if (surface.view_depth != RT2_BACKGROUND_DEPTH) {
         const rt2_restirgi_spatial_params& sp = gi.spatial_resampling_params;
         const int num_samples = (int)sp.num_spatial_samples;
@@ -1331,7 +1331,7 @@ __global__ void __launch_bounds__(128, RT2_GIRS_BLOCKS) k_gi_spatial(GIResampleA
             if (!is_valid_neighbor(surface.normal, ns.normal, surface.view_depth, ns.view_depth, sp.spatial_normal_threshold, sp.spatial_depth_threshold)) continue;
             if (!materials_similar(surface, ns)) continue;
             const uint32_t nrx = field != 0u ? ((uint32_t)ix >> 1) : (uint32_t)ix;
-            const GIReservoir nr = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, nrx, (uint32_t)iy, src));
+            const GIReservoir nr = load_gi_reservoir(a.reservoirs, reservoir_pointer(row_pitch, array_pitch, nrx, (uint32_t)iy, src), a.sc.logluv_lut);
             if (nr.M == 0u) continue;
             float jacobian = gi_jacobian(surface.world_pos, ns.world_pos, nr);
             const float target_pdf = gi_target_pdf(nr.position, nr.radiance, surface);
@@ -1498,7 +1498,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     ga.specular_rough = f.gb_specular_rough[cur]; ga.emissive = f.gb_emissive[cur]; ga.motion = f.motion_vectors; ga.stat_hits = stat_hits;
     if (ph & 1u) { k_gbuffer<<<blocks, 128, 0, ctx->stream>>>(ga); launches++; }
     uint64_t static_rays = (uint64_t)f.width * band.local_rows;      // K3: one primary ray per owned pixel
-    const GBufferRefs gbrefs{f.gb_depth[cur], f.gb_normals[cur], f.gb_geo_normals[cur], f.gb_diffuse_albedo[cur], f.gb_specular_rough[cur]};
+    const GBufferRefs gbrefs{f.gb_depth[cur], f.gb_normals[cur], f.gb_geo_normals[cur], f.gb_diffuse_albedo[cur], f.gb_specular_rough[cur], ctx->codec_luts};
     // ---- K9
     if (g.enable_restir_di == 1u && (ph & 1u)) {
         DIArgs da{};
@@ -1578,7 +1578,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
             GIResampleArgs ra{};
             ra.sc = ga.sc; ra.g = ctx->d_gconst; ra.width = f.width; ra.height = f.height; ra.frame = frame; ra.band = band;
             ra.gb = gbrefs;
-            ra.gb_prev = GBufferRefs{f.gb_depth[prev], f.gb_normals[prev], f.gb_geo_normals[prev], f.gb_diffuse_albedo[prev], f.gb_specular_rough[prev]};
+            ra.gb_prev = GBufferRefs{f.gb_depth[prev], f.gb_normals[prev], f.gb_geo_normals[prev], f.gb_diffuse_albedo[prev], f.gb_specular_rough[prev], ctx->codec_luts};
             ra.motion = f.motion_vectors; ra.neighbor_offsets = f.neighbor_offsets; ra.reservoirs = f.gi_reservoirs;
             ra.stat_rays = stat_rays; ra.stat_hits = stat_hits;
             // the reference records K6 and K7 without a barrier between them (src/light_passes.rs:642-647); stream order = K6 then K7

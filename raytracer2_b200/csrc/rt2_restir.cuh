@@ -20,7 +20,8 @@ __device__ __forceinline__ Surface empty_surface() {
     s.roughness = s.diffuse_probability = 0.f; s.view_depth = RT2_BACKGROUND_DEPTH;
     return s;
 }
-struct GBufferRefs { const float* depth; const uint32_t* normals; const uint32_t* geo_normals; const uint32_t* diffuse_albedo; const uint32_t* specular_rough; };
+struct GBufferRefs { const float* depth; const uint32_t* normals; const uint32_t* geo_normals; const uint32_t* diffuse_albedo; const uint32_t* specular_rough;
+                     const float* gamma_lut; /* CodecLuts::gamma22, may be null */ };
 // GetGBufferSurface, bridge :296-323; viewDepthToWorldPos, GBufferHelpers.glsl:54-67
 __device__ __forceinline__ Surface gbuffer_surface(const GBufferRefs& gb, uint32_t width, int px, int py, const rt2_planar_view_constants& view) {
     Surface s = empty_surface();
@@ -32,7 +33,7 @@ __device__ __forceinline__ Surface gbuffer_surface(const GBufferRefs& gb, uint32
     s.normal = oct_to_ndir_unorm32(gb.normals[i]);
     s.geo_normal = oct_to_ndir_unorm32(gb.geo_normals[i]);
     s.diffuse_albedo = unpack_r11g11b10(gb.diffuse_albedo[i]);
-    const float4 sr = unpack_rgba8_gamma(gb.specular_rough[i]);
+    const float4 sr = unpack_rgba8_gamma(gb.specular_rough[i], gb.gamma_lut);
     s.specular_f0 = v3(sr.x, sr.y, sr.z); s.roughness = sr.w;
     V3 o, d;
     setup_primary_ray(view, (uint32_t)px, (uint32_t)py, &o, &d);
@@ -66,7 +67,7 @@ __device__ __forceinline__ V3 ggx_times_ndotl(V3 V, V3 L, V3 N, float roughness,
         const float G = g_smith_over_ndotv(roughness, NoV, NoL);
         const float alpha = roughness * roughness;
         const float D = ggx_d_literal(alpha, NoH);
-        const float p = pow_pinned(fmaxf(1 - VoH, 0.f), 5.0f);            // Schlick_Fresnel
+        const float p = pow5_pinned(fmaxf(1 - VoH, 0.f));                 // Schlick_Fresnel
         const V3 F = v3(F0.x + (1 - F0.x) * p, F0.y + (1 - F0.y) * p, F0.z + (1 - F0.z) * p);
         return F * (D * G / 4);
     }
@@ -121,7 +122,7 @@ __device__ __forceinline__ LightSample environment_light_sample(const SceneRefs&
     const int texture_index = (int)li.direction1;                         // CreateEnvironmentLight, :414-426
     const float rotation = f16_bits_to_f32((uint16_t)(li.scalars & 0xffffu));
     const uint32_t tex_w = li.direction2 & 0xffffu, tex_h = li.direction2 >> 16;
-    const V3 radiance_scale = unpack_r8g8b8(li.color_type_and_flags) * unpack_light_radiance(li.log_radiance & 0xffffu);
+    const V3 radiance_scale = unpack_r8g8b8(li.color_type_and_flags) * unpack_light_radiance(li.log_radiance & 0xffffu, sc.radiance_lut);
     float cos_elevation;
     const V3 dir = equirect_uv_to_direction(rx + rotation, ry, &cos_elevation);
     out.solid_angle_pdf = (float)(tex_w * tex_h) / (2 * RT2_RTXDI_PI * RT2_RTXDI_PI * cos_elevation);
@@ -143,7 +144,7 @@ __device__ __forceinline__ LightSample sample_polymorphic_light(const SceneRefs&
         return out;
     }
     if (out.light_type != RT2_LIGHT_TRIANGLE) return out;
-    const TriangleLight self = create_triangle_light(li);
+    const TriangleLight self = create_triangle_light(li, sc.radiance_lut);
     const float sqrtx = sqrtf(uvx);                                       // sampleTriangle, Helpers.glsl:66-74
     const float by = sqrtx * (1 - uvy), bz = sqrtx * uvy;
     out.position = (self.base + self.edge1 * by) + self.edge2 * bz;
@@ -261,7 +262,7 @@ __device__ __forceinline__ V3 demodulate_specular(V3 f0, V3 specular) {
     return v3(specular.x / fmaxf(0.01f, f0.x), specular.y / fmaxf(0.01f, f0.y), specular.z / fmaxf(0.01f, f0.z));
 }
 __device__ __forceinline__ V3 schlick_fresnel(V3 F0, float VdotH) {                      // Helpers.glsl:199-202
-    const float p = pow_pinned(fmaxf(1 - VdotH, 0.f), 5.0f);
+    const float p = pow5_pinned(fmaxf(1 - VdotH, 0.f));
     return v3(F0.x + (1 - F0.x) * p, F0.y + (1 - F0.y) * p, F0.z + (1 - F0.z) * p);
 }
 
@@ -329,11 +330,15 @@ __device__ __forceinline__ uint32_t encode_logluv(V3 c) {
     const uint32_t ue = isnan(cu) ? 0u : (uint32_t)cu, ve = isnan(cv) ? 0u : (uint32_t)cv;
     return (Le << 18) | (ue << 9) | ve;
 }
-__device__ __forceinline__ V3 decode_logluv(uint32_t packed) {
+// the luminance of a 14-bit LogLuv exponent field (tabulated as CodecLuts::logluv_y)
+__device__ __forceinline__ float logluv_luminance(uint32_t Le) {
+    const float logY = ((float)Le + 0.5f) / 409.6f - 20.0f;
+    return exp2_pinned(logY);                                              // pow(2.0, logY), same pin (binary64, rounded once)
+}
+__device__ __forceinline__ V3 decode_logluv(uint32_t packed, const float* __restrict__ y_lut = nullptr) {
     const uint32_t Le = packed >> 18;
     if (Le == 0u) return v3(0.f, 0.f, 0.f);
-    const float logY = ((float)Le + 0.5f) / 409.6f - 20.0f;
-    const float Y = pow_pinned(2.0f, logY);
+    const float Y = y_lut ? __ldg(y_lut + Le) : logluv_luminance(Le);
     const uint32_t ue = (packed >> 9) & 0x1ffu, ve = packed & 0x1ffu;
     const float u = ((float)ue + 0.5f) / 820.0f, v = ((float)ve + 0.5f) / 820.0f;
     const float inv_denom = 1.0f / ((6.0f * u - 16.0f * v) + 12.0f);
@@ -362,12 +367,12 @@ __device__ __forceinline__ void store_gi_reservoir(uint4* buf, uint32_t ptr, con
     buf[2 * (size_t)ptr] = make_uint4(__float_as_uint(r.position.x), __float_as_uint(r.position.y), __float_as_uint(r.position.z), mam);
     buf[2 * (size_t)ptr + 1] = make_uint4(encode_logluv(r.radiance), __float_as_uint(r.weight_sum), encode_snorm_oct(r.normal), 0u);
 }
-__device__ __forceinline__ GIReservoir load_gi_reservoir(const uint4* buf, uint32_t ptr) {
+__device__ __forceinline__ GIReservoir load_gi_reservoir(const uint4* buf, uint32_t ptr, const float* __restrict__ y_lut = nullptr) {
     const uint4 a = buf[2 * (size_t)ptr], b = buf[2 * (size_t)ptr + 1];
     GIReservoir r;
     r.position = v3(__uint_as_float(a.x), __uint_as_float(a.y), __uint_as_float(a.z));
     r.normal = decode_snorm_oct(b.z);
-    r.radiance = decode_logluv(b.x);
+    r.radiance = decode_logluv(b.x, y_lut);
     r.weight_sum = __uint_as_float(b.y);
     r.M = a.w & 0xffu; r.age = (a.w >> 8) & 0xffu;
     return r;

@@ -15,6 +15,7 @@ struct SceneRefs {
     const TriShade* tri_shade; const GeomShade* geom_shade;
     const uint32_t* texels; const TextureRec* textures; const float* srgb_lut;
     const float4* sky; uint32_t sky_w, sky_h;
+    const float* gamma_lut; const float* radiance_lut; const float* logluv_lut;   // CodecLuts (rt2_internal.cuh): tabulated decoders, may be null
 };
 inline SceneRefs make_scene_refs(const rt2_ctx* ctx) {
     const DeviceScene& s = ctx->scene;
@@ -24,6 +25,7 @@ inline SceneRefs make_scene_refs(const rt2_ctx* ctx) {
     if (s.flat.nodes && ctx->use_flat) { r.flat_nodes = s.flat.nodes; r.flat_leaf = s.flat_leaf; }
     r.tri_shade = s.tri_shade; r.geom_shade = s.geom_shade;
     r.texels = s.texels; r.textures = s.textures; r.srgb_lut = s.srgb_lut; r.sky = s.sky; r.sky_w = s.sky_w; r.sky_h = s.sky_h;
+    r.gamma_lut = ctx->codec_luts; r.radiance_lut = ctx->codec_luts ? ctx->codec_luts + 256 : nullptr; r.logluv_lut = ctx->codec_luts ? ctx->codec_luts + 256 + 65536 : nullptr;
     return r;
 }
 
