@@ -37,8 +37,10 @@ __device__ __forceinline__ V3 unpack_r11g11b10(uint32_t p) { return v3(unpack_uf
 __device__ __forceinline__ uint32_t pack_r11g11b10(V3 c) { return pack_ufloat(c.x, 11, 0.5f) | (pack_ufloat(c.y, 11, 0.5f) << 11) | (pack_ufloat(c.z, 10, 0.5f) << 22); }
 __device__ __forceinline__ uint32_t pack_rgba8_gamma(float r, float g, float b, float a) {
     const float ig = 1.0f / 2.2f;
-    r = pow_pinned(clampf(r, 0.f, 1.f), ig); g = pow_pinned(clampf(g, 0.f, 1.f), ig);
-    b = pow_pinned(clampf(b, 0.f, 1.f), ig); a = pow_pinned(clampf(a, 0.f, 1.f), ig);
+    // pow(0, y) = 0 and pow(1, y) = 1 exactly: dielectrics have F0 = 0 and the reference's roughness is the constant 1 (Hit.glsl:40), so
+    // most G-buffer pixels never need the binary64 pow
+    auto enc = [&](float x) { x = clampf(x, 0.f, 1.f); return x == 0.f ? 0.f : (x == 1.f ? 1.f : pow_pinned(x, ig)); };
+    r = enc(r); g = enc(g); b = enc(b); a = enc(a);
     return pack_ufloat(r, 8, 0.5f) | (pack_ufloat(g, 8, 0.5f) << 8) | (pack_ufloat(b, 8, 0.5f) << 16) | (pack_ufloat(a, 8, 0.5f) << 24);
 }
 __device__ __forceinline__ float gamma22_decode(uint32_t byte) { return pow_pinned(saturatef(unpack_ufloat(byte, 8)), 2.2f); }
