@@ -145,9 +145,6 @@ struct rt2_ctx {
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
     int trace_blocks_per_sm[4] = {1, 1, 1, 1};          // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level, [3] flattened instancing
-    int coop_blocks_per_sm[4] = {1, 1, 1, 1};  // resident blocks of k_trace_coop<FLAT, GENERIC>
-    int coop_mode = 0;                         // RT2_COOP: 0 lane-per-ray always, 1 eight-lanes-per-ray always, 2 by the launch's size
-    uint64_t coop_max_rays = 400000;            // RT2_COOP_MAX_RAYS: mode 2 uses the cooperative walk for launches of at most this many rays
     int trace_queue_blocks_per_sm = 1;       // resident blocks of k_trace_queue (the ReSTIR passes' ray-queue kernel)
     bool use_flat = true;                                // trace instanced scenes through the flattened tree when it was built (RT2_USE_FLAT=0: two-level walk)
     int trace_variant = 0;

@@ -13,7 +13,7 @@ namespace rt2 {
 
 int restir_ensure_resources(rt2_ctx* ctx);
 int lights_ensure_resources(rt2_ctx* ctx);
-int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays, uint64_t max_rays);
+int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays);
 
 // interleaved row bands (the same rule as rt2_render.cu's Band): the passes below are per-pixel independent, every buffer
 // stays full-frame and addressed by absolute pixel, a rank just visits its own rows
@@ -1518,14 +1518,14 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
             const bool final_vis = g.restir_di.shading_params.enable_final_visibility == 1u;
             k_di_stage_a<false><<<blocks, 128, 0, ctx->stream>>>(dw); launches++;
             if (g.restir_di.initial_sampling_params.num_primary_brdf_samples != 0u) {
-                if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 8, f.counters + 9, stat_rays, static_rays))) return rc;
+                if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 8, f.counters + 9, stat_rays))) return rc;
                 launches++;
             }
             k_di_stage_b<false><<<blocks, 128, 0, ctx->stream>>>(dw, f.queue1, f.counters + 10); launches++;
-            if (initial_vis || final_vis) { if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 10, f.counters + 11, stat_rays, static_rays))) return rc; launches++; }
+            if (initial_vis || final_vis) { if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 10, f.counters + 11, stat_rays))) return rc; launches++; }
             if (initial_vis) {
                 k_di_stage_c<<<blocks, 128, 0, ctx->stream>>>(dw, f.queue0, f.counters + 12); launches++;
-                if (final_vis) { if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 12, f.counters + 13, stat_rays, static_rays))) return rc; launches++; }
+                if (final_vis) { if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 12, f.counters + 13, stat_rays))) return rc; launches++; }
             }
             k_di_stage_d<<<blocks, 128, 0, ctx->stream>>>(dw, final_vis ? 1u : 0u); launches++;
         }
@@ -1549,7 +1549,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
             wa.gi = gi; wa.st_ray0 = f.st_ray0; wa.st_ray1 = f.st_ray1; wa.st_acc = f.st_acc; wa.st_misc = f.st_misc; wa.st_hit = f.st_hit; wa.st_hit_inst = f.st_hit_inst;
             wa.queue = f.queue0; wa.count = f.counters + 4;
             k_brdf_rays_gen<<<blocks, 128, 0, ctx->stream>>>(wa);
-            if ((rc = trace_queue_generic(ctx, wa.queue, wa.count, f.counters + 5, stat_rays, static_rays))) return rc;
+            if ((rc = trace_queue_generic(ctx, wa.queue, wa.count, f.counters + 5, stat_rays))) return rc;
             k_brdf_rays_shade<<<blocks, 128, 0, ctx->stream>>>(wa); launches += 3;
             if (g.enable_restir_di == 1u) {                            // K5 samples the light list at the secondary surface: the K9 stages, pointed at SecondaryGBufferData
                 DIWaveArgs dw{};
@@ -1559,17 +1559,17 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
                 dw.state = f.di_state; dw.plane = (uint32_t)((size_t)f.width * f.height); dw.secondary = f.secondary_gbuffer;
                 dw.queue = f.queue1; dw.count = f.counters + 6;
                 k_di_stage_a<true><<<blocks, 128, 0, ctx->stream>>>(dw);
-                if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 6, f.counters + 7, stat_rays, static_rays))) return rc;
+                if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 6, f.counters + 7, stat_rays))) return rc;
                 k_di_stage_b<true><<<blocks, 128, 0, ctx->stream>>>(dw, f.queue0, f.counters + 14); launches += 3;
                 if (g.restir_di.shading_params.enable_final_visibility == 1u) {
-                    if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 14, f.counters + 15, stat_rays, static_rays))) return rc;
+                    if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 14, f.counters + 15, stat_rays))) return rc;
                     launches++;
                 }
                 k_shade_secondary_stage_d<<<blocks, 128, 0, ctx->stream>>>(dw, gi); launches++;
             } else {
                 wa.queue = f.queue1; wa.count = f.counters + 6;
                 k_shade_secondary_gen<<<blocks, 128, 0, ctx->stream>>>(wa);
-                if ((rc = trace_queue_generic(ctx, wa.queue, wa.count, f.counters + 7, stat_rays, static_rays))) return rc;
+                if ((rc = trace_queue_generic(ctx, wa.queue, wa.count, f.counters + 7, stat_rays))) return rc;
                 k_shade_secondary_shade<<<blocks, 128, 0, ctx->stream>>>(wa); launches += 3;
             }
         }

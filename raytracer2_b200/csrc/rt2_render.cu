@@ -346,17 +346,6 @@ __global__ void __launch_bounds__(128, RT2_GENERIC_MIN_BLOCKS) k_trace_queue(Tra
     trace_dyn_body<RT2_GENERIC_POSTPONE, RT2_GENERIC_REFILL, RT2_GENERIC_CHECK, false, true>(a);
 }
 
-#include "rt2_trace_coop.cuh"
-
-// Lane-per-ray or eight-lanes-per-ray?  `rays` = an upper bound of the launch's queue length known on the host.  The cooperative
-// walk wins when the launch cannot give every resident lane several rays (ctx->coop_max_rays, RT2_COOP_MAX_RAYS; RT2_COOP=0 / 1
-// forces never / always).
-static inline bool use_coop(const rt2_ctx* ctx, uint64_t rays) {
-    if (ctx->coop_mode == 0) return false;
-    if (ctx->coop_mode == 1) return true;
-    return rays <= ctx->coop_max_rays;
-}
-
 // refrence.rgen:28-46 for the path in `slot` whose ray just came back (hit record in st_hit): emission / throughput update,
 // cosine-lobe sample, path regeneration.  Returns true while the pixel still has rays to trace (state written back), false when
 // its last sample finished (radiance stored).
@@ -1119,17 +1108,13 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
                 cudaStream_t st = k.st;
                 if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], st));
                 t.queue = k.q[it & 1]; t.count = k.cnt + 2 * it; t.head = k.cnt + 2 * it + 1;
-                const bool coop = use_coop(ctx, k.end - k.first);
                 if (flat) {
-                    if (coop) k_trace_coop<true, false><<<ctx->coop_blocks_per_sm[1] * ctx->num_sms, 32 * RT2_COOP_WARPS, 0, st>>>(t);
-                    else k_trace_dyn_flat<RT2_FLAT_PARAMS><<<k.trace_blocks, 128, 0, st>>>(t);
+                    k_trace_dyn_flat<RT2_FLAT_PARAMS><<<k.trace_blocks, 128, 0, st>>>(t);
                 } else if (s.num_instances) {
                     // one-loop TLAS/BLAS walk unless the two trees together could overflow the shared stack (then: nested loops, own stack each)
                     const bool unified = ctx->trace_variant != 0 && unified_walk_fits(s);
                     if (unified) k_trace_dyn_tlas<20, 4, 8><<<k.trace_blocks, 128, 0, st>>>(t);
                     else k_trace<true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, st>>>(t);
-                } else if (coop) {
-                    k_trace_coop<false, false><<<ctx->coop_blocks_per_sm[0] * ctx->num_sms, 32 * RT2_COOP_WARPS, 0, st>>>(t);
                 } else {
                     g_trace_variants[ctx->trace_variant]<<<k.trace_blocks, 128, 0, st>>>(t);
                 }
@@ -1391,16 +1376,12 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
 
 // Traces a queue of GENERIC rays (st_ray0 = o|tmin, st_ray1 = d|tmax, slot = pixel-linear index) into st_hit / st_hit_inst:
 // the ReSTIR passes hand their incoherent rays to the same postponing/refilling kernel the path tracer uses.
-int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays, uint64_t max_rays) {
+int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays) {
     const DeviceScene& s = ctx->scene;
     TraceArgs t = make_trace_args(ctx);
     t.queue = queue; t.count = count; t.head = head; t.stat_rays = stat_rays;
-    const bool coop = use_coop(ctx, max_rays);
     if (t.flat_nodes) {
-        if (coop) k_trace_coop<true, true><<<ctx->coop_blocks_per_sm[3] * ctx->num_sms, 32 * RT2_COOP_WARPS, 0, ctx->stream>>>(t);
-        else k_trace_dyn_flat<RT2_FLAT_PARAMS, true><<<ctx->trace_blocks_per_sm[3] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
-    } else if (!s.num_instances && coop) {
-        k_trace_coop<false, true><<<ctx->coop_blocks_per_sm[2] * ctx->num_sms, 32 * RT2_COOP_WARPS, 0, ctx->stream>>>(t);
+        k_trace_dyn_flat<RT2_FLAT_PARAMS, true><<<ctx->trace_blocks_per_sm[3] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
     } else if (s.num_instances) {
         if (unified_walk_fits(s)) k_trace_dyn_tlas<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
         else k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
@@ -1435,16 +1416,6 @@ int render_init(rt2_ctx* ctx) {
     ctx->path_blocks_per_sm[0] = std::max(p0, 1); ctx->path_blocks_per_sm[1] = std::max(p1, 1); ctx->path_blocks_per_sm[2] = std::max(p2, 1);
     ctx->trace_blocks_per_sm[3] = std::max(b3, 1);
     { int bq = 0; RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bq, k_trace_queue, 128, 0)); ctx->trace_queue_blocks_per_sm = std::max(bq, 1); }
-    {   // eight-lanes-per-ray kernels: [0] single-level K1, [1] flat K1, [2] single-level generic, [3] flat generic
-        int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-        RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c0, k_trace_coop<false, false>, 32 * RT2_COOP_WARPS, 0));
-        RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c1, k_trace_coop<true, false>, 32 * RT2_COOP_WARPS, 0));
-        RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c2, k_trace_coop<false, true>, 32 * RT2_COOP_WARPS, 0));
-        RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c3, k_trace_coop<true, true>, 32 * RT2_COOP_WARPS, 0));
-        ctx->coop_blocks_per_sm[0] = std::max(c0, 1); ctx->coop_blocks_per_sm[1] = std::max(c1, 1); ctx->coop_blocks_per_sm[2] = std::max(c2, 1); ctx->coop_blocks_per_sm[3] = std::max(c3, 1);
-        if (const char* e = getenv("RT2_COOP")) ctx->coop_mode = atoi(e);
-        if (const char* e = getenv("RT2_COOP_MAX_RAYS")) ctx->coop_max_rays = (uint64_t)atoll(e);
-    }
     if (const char* e = getenv("RT2_USE_FLAT")) ctx->use_flat = atoi(e) != 0;
     ctx->trace_blocks_per_sm[0] = std::max(b0, 1); ctx->trace_blocks_per_sm[1] = std::max(b1, 1); ctx->trace_blocks_per_sm[2] = std::max(b2, 1);
     return RT2_OK;
