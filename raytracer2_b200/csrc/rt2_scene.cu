@@ -211,12 +211,12 @@ int scene_build_accel(rt2_ctx* ctx) {
         if (rc != RT2_OK) return fail(ctx, rc, "TLAS build: " + err);
         s.tlas.num_prims = s.num_instances;
         // Flattened instancing when it fits: n = instances x triangles primitives cost ~40 B each when built (80-byte node per ~3.7
-        // primitives + 8-byte leaf record) and ~300 B each of build scratch.  RT2_FLATTEN=0 keeps the two-level walk only,
+        // primitives + 8-byte leaf record) and ~450 B each of build scratch (sort keys, BVH2, the reinsertion rounds' and the collapse's per-node state).  RT2_FLATTEN=0 keeps the two-level walk only,
         // RT2_FLATTEN=1 forces the attempt; the default takes it when the scratch fits in half of the free device memory.
         const uint64_t n_flat = (uint64_t)s.num_instances * s.num_tris;
         size_t free_b = 0, total_b = 0;
         cudaMemGetInfo(&free_b, &total_b);
-        int want = n_flat > 0 && n_flat < 0x7FFFFFF0ull && n_flat * 320ull < free_b / 2 ? 1 : 0;
+        int want = n_flat > 0 && n_flat < 0x7FFFFFF0ull && n_flat * 480ull < free_b / 2 ? 1 : 0;
         if (const char* e = getenv("RT2_FLATTEN")) want = atoi(e) != 0 && n_flat > 0 && n_flat < 0x7FFFFFF0ull;
         if (want) {
             RT2_CUDA(ctx, cudaMalloc((void**)&lo, n_flat * 16));
