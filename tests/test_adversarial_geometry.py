@@ -130,3 +130,61 @@ def test_gpu_matches_brute_force_on_adversarial_geometry(tmp_path):
     assert np.array_equal(d32, ref[2].view(np.uint32))
     assert (ref[2][:, :, :3] > 0).mean() > 0.1
     ctx.close()
+
+
+def _soup_scene(tmp_path, k, seed):
+    """k random triangles in front of the camera (some overlapping, some sharing a vertex), one geometry"""
+    rng = np.random.default_rng(seed)
+    c = rng.uniform(-1.5, 1.5, (k, 1, 3)) * np.array([1.0, 1.0, 0.6])
+    pos = (c + rng.normal(0, 0.5, (k, 3, 3))).reshape(-1, 3)
+    if k >= 2:
+        pos[3] = pos[0]                                        # two triangles share a vertex
+    b = GltfBuilder()
+    _add_mesh(b, pos, np.arange(3 * k).reshape(-1, 3), material={"pbrMetallicRoughness": {"baseColorFactor": [0.7, 0.6, 0.5, 1.0]}})
+    p = tmp_path / f"soup{k}.glb"
+    p.write_bytes(b.glb())
+    sc = rt.Scene.from_gltf(str(p))
+    cam = rt.Camera()
+    posv, dirv = (C.c_float * 3)(0.0, 0.0, 6.0), (C.c_float * 3)(0.0, 0.0, 1.0)
+    _ffi.host_lib().rt2h_camera_new(C.byref(cam), posv, dirv, 50.0, 1.0, 0.1, 1000.0)
+    g = rt.default_gconst(cam, 96, 96, sc.num_lights)
+    g.refrence_mode = 1
+    return sc, g
+
+
+TINY = [1, 2, 3, 4, 8, 15, 16, 17, 31, 33, 100]        # around RT2_LEAF_MAX, one wide node, and the 16-leaf threshold of the reinsertion rounds
+
+
+@pytest.mark.parametrize("k", TINY)
+def test_tiny_trees_on_the_cpu_emulation(tmp_path, hostemu, k):
+    """The builder's passes (PLOC, reinsertion from 16 leaves, SAH-optimal collapse) on trees of a handful of leaves: the product's
+    builder + traversal functions on the CPU reproduce the brute-force intersector's hit records bit for bit."""
+    sc, g = _soup_scene(tmp_path, k, 100 + k)
+    ids = O.OracleScene(sc.desc).trace_primary(g, 96, 96, flags=O.ORC_BRUTE_FORCE)
+    hs = hostemu.hostemu_build(C.cast(sc.desc, C.c_void_p))
+    assert hs
+    out = np.zeros((96 * 96, 8), np.uint32)
+    hostemu.hostemu_trace_primary(hs, C.cast(C.byref(g), C.c_void_p), 96, 96, out.ctypes.data_as(C.c_void_p), None)
+    hostemu.hostemu_destroy(hs)
+    assert np.array_equal(out.reshape(96, 96, 8), ids)
+    assert (ids[:, :, 1] != 0xFFFFFFFF).any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k", TINY)
+def test_tiny_trees_on_the_gpu(tmp_path, k):
+    sc, g = _soup_scene(tmp_path, k, 100 + k)
+    ids = O.OracleScene(sc.desc).trace_primary(g, 96, 96, flags=O.ORC_BRUTE_FORCE)
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, 96, 96)
+    lp.update_uniform(g)
+    lp.trace_primary()
+    got = ctx.read(rt.BUF_HIT_IDS, np.uint32).reshape(96, 96, 8)
+    assert np.array_equal(got, ids)
+    # and a short path-traced frame through the same tree
+    lp.execute(1, rt.LaunchParams(spp=2, max_bounces=3))
+    d32 = ctx.read(rt.BUF_DIFFUSE_F32, np.uint32).reshape(96, 96, 4)
+    ref = O.OracleScene(sc.desc).render_reference(g, 1, 96, 96, spp=2, max_bounces=3)[2].view(np.uint32)
+    assert np.array_equal(d32, ref)
+    ctx.close()
