@@ -367,7 +367,10 @@ int  rt2_group_prepare_lights(rt2_group* g);                                   /
 int  rt2_group_generate_mips(rt2_group* g, int which);                         /* replicated: K12 (src/mip_pass.rs:122)              */
 /* LightPasses::execute (src/light_passes.rs:550-663) on every rank's bands (params->band_* are filled in by the group), then,
  * if gather_which >= 0 (an rt2_buffer id of a W x H frame buffer, e.g. RT2_BUF_DIFFUSE_F32), pack + ncclAllGather +
- * un-permute of that buffer on the group's communication stream: the gather of frame n overlaps the render of frame n + 1. */
+ * un-permute of that buffer on the group's communication stream: the gather of frame n overlaps the render of frame n + 1.
+ * With GI temporal / spatial resampling on (K6 / K7, src/light_passes.rs:642-647) the frame runs in phases and the reservoir page and
+ * G-buffer those passes read at other ranks' pixels are exchanged in place between them (ncclAllGather on the render streams); the
+ * frames stay bit-identical to one GPU's.  In a single-process group every local GPU's launches are issued by a host thread of its own. */
 int  rt2_group_render(rt2_group* g, uint32_t frame, const rt2_launch_params* params, int gather_which);
 /* the gather step alone (e.g. RT2_BUF_OUTPUT_RGBA8 after rt2_group_postprocess: sharded K13 + gather of RGBA8) */
 int  rt2_group_gather(rt2_group* g, int which);
