@@ -332,7 +332,18 @@ int rt2_group_build_accel(rt2_group* g) { RT2_GROUP_EACH(g, rt2_build_accel(c));
 int rt2_group_set_constants(rt2_group* g, const void* gconst, size_t nbytes) { RT2_GROUP_EACH(g, rt2_set_constants(c, gconst, nbytes)); }
 int rt2_group_prepare_lights(rt2_group* g) { RT2_GROUP_EACH(g, rt2_prepare_lights(c)); }
 int rt2_group_generate_mips(rt2_group* g, int which) { RT2_GROUP_EACH(g, rt2_generate_mips(c, which)); }
-int rt2_group_postprocess(rt2_group* g, uint32_t frame) { RT2_GROUP_EACH(g, rt2_postprocess(c, frame)); }
+int rt2_group_postprocess(rt2_group* g, uint32_t frame) {
+    if (!g) return RT2_E_INVALID;
+    for (size_t i = 0; i < g->ctxs.size(); i++) {
+        rt2_ctx* c = g->ctxs[i];
+        // K13 is per pixel: every rank tonemaps the rows of its own bands only (the others hold stale lighting anyway)
+        c->post_band[0] = g->world > 1 ? RT2_GROUP_BAND_ROWS : 0u; c->post_band[1] = (uint32_t)g->first_rank + (uint32_t)i; c->post_band[2] = (uint32_t)g->world;
+        const int rc = rt2_postprocess(c, frame);
+        c->post_band[0] = 0u;
+        if (rc != RT2_OK) return gfail(g, rc, std::string("rt2_postprocess: ") + rt2_last_error(c));
+    }
+    return RT2_OK;
+}
 
 int rt2_group_resize(rt2_group* g, uint32_t width, uint32_t height) {
     if (!g) return RT2_E_INVALID;

@@ -163,6 +163,7 @@ struct rt2_ctx {
     // lights / pdf textures (K10/K12)
     rt2_light_info* light_info = nullptr; uint32_t light_capacity = 0;   // = the scene's light count
     float* codec_luts = nullptr;                                           // [0,256): gamma22_decode(byte); [256, 256 + 65536): unpack_light_radiance(code); then 16384 x logluv_luminance(exponent) — built on this device at rt2_create
+    uint32_t post_band[3] = {0, 0, 0};                                     // set by rt2_group_postprocess: {band_rows, rank, world}; K13 then visits this rank's rows only
     uint32_t restir_phase = 0;                                             // set by rt2_group_render around a sharded frame with K6 / K7: which part of render_restir runs (0 = all)
     uint32_t light_records = 0;                                            // records allocated: light_capacity, + 2 with a sky (a zero record and the environment light)
     uint32_t* geom_to_light = nullptr;

@@ -18,6 +18,7 @@ struct PostArgs {
     const float4* sky; uint32_t sky_w, sky_h;
     uchar4* out;
     const float* gamma_lut;      // CodecLuts::gamma22
+    uint32_t band_rows, band_rank, band_world;   // band_world > 1: only the rows of this rank's bands (rt2_group_postprocess)
 };
 
 __device__ __forceinline__ float agx_contrast(float x) {          // agxDefaultContrastApprox, :47-58
@@ -82,6 +83,7 @@ __device__ __forceinline__ V3 post_environment(const PostArgs& a, V3 dir) {
 __global__ void __launch_bounds__(256) k_postprocess(PostArgs a) {
     const uint32_t x = blockIdx.x * 32u + (threadIdx.x & 31u), y = blockIdx.y * 8u + (threadIdx.x >> 5);
     if (x >= a.width || y >= a.height) return;
+    if (a.band_world > 1u && (y / a.band_rows) % a.band_world != a.band_rank) return;
     const size_t i = (size_t)y * a.width + x;
     const rt2_gconst& g = *a.g;
     V3 col = v3(0.f, 0.f, 0.f);
@@ -124,6 +126,7 @@ int post_process(rt2_ctx* ctx, uint32_t frame) {
     a.g = ctx->d_gconst; a.width = f.width; a.height = f.height;
     a.diffuse = f.diffuse_f16; a.specular = f.specular_f16; a.out = f.output_rgba8;
     a.sky = ctx->scene.sky; a.sky_w = ctx->scene.sky_w; a.sky_h = ctx->scene.sky_h; a.gamma_lut = ctx->codec_luts;
+    a.band_rows = ctx->post_band[0]; a.band_rank = ctx->post_band[1]; a.band_world = ctx->post_band[0] ? ctx->post_band[2] : 0u;
     if (ctx->gconst.refrence_mode != 1u) {
         if (!f.gb_depth[0]) return fail(ctx, RT2_E_STATE, "no G-buffer: run rt2_render in ReSTIR mode first");
         const uint32_t cur = frame & 1u;           // source_descriptors[frame % 2], src/postprocess.rs:284
