@@ -13,6 +13,7 @@ import ctypes as C
 import os
 import sys
 
+import zlib
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -73,6 +74,48 @@ def k9(name, frame):
                         reservoirs=res, diffuse_f16=d16, specular_f16=s16, rays=np.uint64(rays))
 
 
+def env_inputs(sc, osc, g, frame, lights, packed, dims):
+    """K12 environment pyramid + K11 tiles of both segments (the presampling build's inputs)."""
+    import math
+    d = sc.desc.contents
+    sw, sh = d.sky_width, d.sky_height
+    emips = int(math.ceil(math.log2(max(sw, sh)))) + 1
+    epacked = np.zeros(sum(a * b for a, b in O.mip_dims(sw, sh, emips)), np.uint16)
+    osc.generate_mips(1, epacked, sw, sh, emips)
+    ris, data = O.presample(g, frame, 0, packed, *dims, lights)
+    ris, data = O.presample(g, frame, 1, epacked, sw, sh, emips, ris=ris, ris_light_data=data)
+    return epacked, (sw, sh, emips), ris, data
+
+
+def k9_env(frame, sky=128, local=2, env=3, w=64, h=64):
+    """K9 as compiled with RTXDI_ENABLE_PRESAMPLING 1 under a sky: POWER_RIS local lights, environment-map importance sampling from
+    K11's environment tiles, BRDF rays that miss select the environment light K10 writes at lights + 1 (SURVEY Q7 pinned to intent)."""
+    sc = rt.Scene(rt.SCENE_CORNELL, 1.0, 64, 0).add_sky(sky)
+    d = sc.desc.contents
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights, env_size=(d.sky_width, d.sky_height))
+    osc = O.OracleScene(sc.desc)
+    g.refrence_mode = 0; g.enable_restir_gi = 0; g.enable_restir_di = 1; g.environment = 1
+    isp = g.restir_di.initial_sampling_params
+    isp.num_primary_local_light_samples = local; isp.num_primary_brdf_samples = 1; isp.num_primary_environment_samples = env
+    isp.environment_map_importance_sampling = 1; isp.local_light_sampling_mode = 1; isp.enable_initial_visibility = 1
+    g.restir_di.shading_params.enable_final_visibility = 1
+    gb = osc.gbuffer(g, w, h, flags=O.ORC_BRUTE_FORCE)
+    pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
+    dims = (pw.value, ph.value, pm.value)
+    tasks, g2l, lights, pdf0 = osc.prepare_lights(dims[0], dims[1], env=True)
+    packed = np.zeros(sum(a * b for a, b in O.mip_dims(*dims)), np.float32)
+    packed[:dims[0] * dims[1]] = pdf0.ravel()
+    osc.generate_mips(0, packed, *dims)
+    epacked, edims, ris, data = env_inputs(sc, osc, g, frame, lights, packed, dims)
+    pitch = g.restir_di.reservoir_buffer_params.reservoir_array_pitch
+    res, d16, s16, rays = osc.di_fused_resampling(g, frame, w, h, gb, lights, g2l, packed, *dims, pitch, flags=O.ORC_BRUTE_FORCE | O.ORC_PRESAMPLING,
+                                                  ris=ris, ris_light_data=data, env_pdf=epacked, env_dims=edims)
+    np.savez_compressed(os.path.join(OUT, "k9_env_cornell_sky.npz"), frame=frame, sky=sky, local=local, env=env, width=w, height=h, lights=lights,
+                        env_pdf_mip0=epacked[:edims[0] * edims[1]], ris_head=ris[:1024], ris_tail=ris[-1024:], ris_crc=np.uint32(zlib.crc32(ris.tobytes())), reservoirs=res, diffuse_f16=d16, specular_f16=s16, rays=np.uint64(rays))
+    return sc, g, osc, gb, lights, g2l, packed, dims, epacked, edims, ris, data
+
+
 def gi(name, frame):
     """The default frame K3 -> K4 -> K5 -> K8 (src/main.rs:391-394: ReSTIR GI on, DI off, no resampling)."""
     sc, g, osc, w, h = scene(name)
@@ -110,6 +153,7 @@ if __name__ == "__main__":
     k1("hall", 3, 2, 3)
     k1("instanced", 2, 2, 3, env=1)
     k9("cornell", 1)
+    k9_env(2)
     gi("cornell", 1)
     gi("hall", 2)
     codecs()

@@ -48,6 +48,52 @@ def test_oracle_k9_reproduces_golden():
     assert np.array_equal(d16, z["diffuse_f16"]) and np.array_equal(s16, z["specular_f16"])
 
 
+def _ris_matches(ris, z):
+    """K11's tiles against the fixture (2 MB of tiles: the fixture keeps both ends and a CRC-32 of the whole)."""
+    import zlib
+    return np.array_equal(ris[:1024], z["ris_head"]) and np.array_equal(ris[-1024:], z["ris_tail"]) and zlib.crc32(np.ascontiguousarray(ris).tobytes()) == int(z["ris_crc"])
+
+
+def _k9_env_gconst(z):
+    w, h = int(z["width"]), int(z["height"])
+    sc = rt.Scene(rt.SCENE_CORNELL, 1.0, 64, 0).add_sky(int(z["sky"]))
+    d = sc.desc.contents
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights, env_size=(d.sky_width, d.sky_height))
+    g.refrence_mode = 0; g.enable_restir_gi = 0; g.enable_restir_di = 1; g.environment = 1
+    isp = g.restir_di.initial_sampling_params
+    isp.num_primary_local_light_samples = int(z["local"]); isp.num_primary_brdf_samples = 1; isp.num_primary_environment_samples = int(z["env"])
+    isp.environment_map_importance_sampling = 1; isp.local_light_sampling_mode = 1; isp.enable_initial_visibility = 1
+    g.restir_di.shading_params.enable_final_visibility = 1
+    return sc, g, w, h
+
+
+def test_oracle_k9_environment_sampling_reproduces_golden():
+    """The presampling build of the sampler under a sky (environment light at lights + 1, K11 tiles, BRDF-miss branch): the oracle's BVH walk
+    against the fixture its brute-force intersector wrote."""
+    z = _load("k9_env_cornell_sky")
+    sc, g, w, h = _k9_env_gconst(z)
+    osc = O.OracleScene(sc.desc)
+    gb = osc.gbuffer(g, w, h)
+    import ctypes as C
+    pw, ph, pm = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    rt._ffi.host_lib().rt2h_compute_pdf_texture_size(sc.num_lights, C.byref(pw), C.byref(ph), C.byref(pm))
+    dims = (pw.value, ph.value, pm.value)
+    tasks, g2l, lights, pdf0 = osc.prepare_lights(dims[0], dims[1], env=True)
+    assert np.array_equal(lights, z["lights"])
+    packed = np.zeros(sum(a * b for a, b in O.mip_dims(*dims)), np.float32)
+    packed[:dims[0] * dims[1]] = pdf0.ravel()
+    osc.generate_mips(0, packed, *dims)
+    epacked, edims, ris, data = MG.env_inputs(sc, osc, g, int(z["frame"]), lights, packed, dims)
+    assert np.array_equal(epacked[:edims[0] * edims[1]], z["env_pdf_mip0"]) and _ris_matches(ris, z)
+    pitch = g.restir_di.reservoir_buffer_params.reservoir_array_pitch
+    res, d16, s16, rays = osc.di_fused_resampling(g, int(z["frame"]), w, h, gb, lights, g2l, packed, *dims, pitch, flags=O.ORC_PRESAMPLING,
+                                                  ris=ris, ris_light_data=data, env_pdf=epacked, env_dims=edims)
+    assert rays == int(z["rays"]) and np.array_equal(res, z["reservoirs"])
+    assert np.array_equal(d16, z["diffuse_f16"]) and np.array_equal(s16, z["specular_f16"])
+    chosen = res[res[:, 0] != 0, 0] & 0x7fffffff
+    assert (chosen == sc.num_lights + 1).any() and (chosen < sc.num_lights).any()      # both the sky and the lamp are selected somewhere
+
+
 @pytest.mark.parametrize("name", ["cornell", "hall"])
 def test_oracle_gi_chain_reproduces_golden(name):
     z = _load("gi_" + name)
@@ -115,6 +161,29 @@ def test_gpu_k9_reproduces_golden():
     lp.update_uniform(g)
     lp.execute(int(z["frame"]))
     assert np.array_equal(ctx.read(rt.BUF_GBUFFER_DEPTH, np.uint32).reshape(h, w), z["depth_bits"])
+    assert ctx.stats().rays_traced - w * h == int(z["rays"])
+    res = ctx.read(rt.BUF_DI_RESERVOIRS, np.uint32).reshape(-1, 6)
+    assert int((res != z["reservoirs"]).any(axis=1).sum()) <= 2
+    assert int((ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).reshape(h, w, 4) != z["diffuse_f16"]).any(axis=2).sum()) <= 2
+    assert int((ctx.read(rt.BUF_SPECULAR_F16, np.uint16).reshape(h, w, 4) != z["specular_f16"]).any(axis=2).sum()) <= 2
+    ctx.close()
+
+
+@pytest.mark.gpu
+def test_gpu_k9_environment_sampling_reproduces_golden():
+    z = _load("k9_env_cornell_sky")
+    sc, g, w, h = _k9_env_gconst(z)
+    ctx = rt.Renderer(0)
+    rt.Model.from_scene(ctx, sc)
+    lp = rt.LightPasses(ctx, w, h)
+    rt.PrepareLightsTasks(ctx).execute()
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+    rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.ENVIRONMENT).execute_mip_generation()
+    lp.update_uniform(g)
+    lp.execute_presampeling(int(z["frame"]), True)
+    assert np.array_equal(ctx.read(rt.BUF_LIGHT_INFO, np.uint32).reshape(-1, 12), z["lights"])
+    assert _ris_matches(ctx.read(rt.BUF_RIS, np.uint32).reshape(-1, 2), z)
+    lp.execute(int(z["frame"]), rt.LaunchParams(flags=rt.LAUNCH_PRESAMPLING))
     assert ctx.stats().rays_traced - w * h == int(z["rays"])
     res = ctx.read(rt.BUF_DI_RESERVOIRS, np.uint32).reshape(-1, 6)
     assert int((res != z["reservoirs"]).any(axis=1).sum()) <= 2
