@@ -232,7 +232,7 @@ pub struct rt2_stats {
     pub shade_ns: u64,
     pub trace_launches: u64,
     pub sample_schedule: u64,
-    pub _reserved: [u64; 1],
+    pub rays_walked: u64,
 }
 
 #[repr(C)]

@@ -249,7 +249,9 @@ typedef struct rt2_stats {
     uint64_t shade_ns;         /* with RT2_LAUNCH_PROFILE: summed CUDA-event time of the shading kernel launches   */
     uint64_t trace_launches;   /* with RT2_LAUNCH_PROFILE: traversal kernel launches that had rays to trace         */
     uint64_t sample_schedule;  /* K1: 0 = one launch pair per (sample, bounce); 1 = speculative sample parallelism (every sample its own path) */
-    uint64_t _reserved[1];
+    uint64_t rays_walked;      /* BVH walks behind rays_traced.  K1's primary ray has no jitter (refrence.rgen:26, GBufferHelpers.glsl:12-27), so the
+                                  spp samples of a pixel issue the same trace() spp times: it is walked once and its hit record consumed spp
+                                  times (RT2_PRIMARY_REUSE=0 walks every one).  Equal to rays_traced for every other pass. */
 } rt2_stats;
 
 typedef struct rt2_ctx rt2_ctx;

@@ -64,7 +64,7 @@ class LaunchParams(C.Structure):
 
 
 class Stats(C.Structure):
-    _fields_ = _fields("rays_traced rays_hit kernel_launches wavefront_iterations bvh_nodes bvh_triangles device_bytes trace_ns shade_ns trace_launches sample_schedule _r1", u64)
+    _fields_ = _fields("rays_traced rays_hit kernel_launches wavefront_iterations bvh_nodes bvh_triangles device_bytes trace_ns shade_ns trace_launches sample_schedule rays_walked", u64)
 
 
 # ---- GConst (include/rt2_gconst.h; src/shader_params.rs) ----------------------------------------------

@@ -289,11 +289,12 @@ int rt2_get_stats(rt2_ctx* ctx, rt2_stats* out) {
     RT2_GUARD(ctx);
     if (!out) return fail(ctx, RT2_E_INVALID, "out is NULL");
     if (ctx->stats_from_counters && ctx->fb.counters) {
-        unsigned long long c[2] = {0, 0};
-        RT2_CUDA(ctx, cudaMemcpyAsync(c, ctx->fb.counters, 16, cudaMemcpyDeviceToHost, ctx->stream));
+        unsigned long long c[3] = {0, 0, 0};
+        RT2_CUDA(ctx, cudaMemcpyAsync(c, ctx->fb.counters, 24, cudaMemcpyDeviceToHost, ctx->stream));
         RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         ctx->stats.rays_traced = c[0] + ctx->pending_rays_static;
         ctx->stats.rays_hit = c[1];
+        ctx->stats.rays_walked = ctx->stats_walks_counted ? c[2] : ctx->stats.rays_traced;
     }
     ctx->stats.trace_ns = ctx->stats.shade_ns = ctx->stats.trace_launches = 0;
     if (!ctx->prof_events.empty()) {

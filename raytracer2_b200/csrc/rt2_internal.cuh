@@ -94,6 +94,8 @@ struct FrameBuffers {
     uint4* st_misc = nullptr;
     float4* st_hit = nullptr;
     uint32_t* st_hit_inst = nullptr;
+    float4* st_hit0 = nullptr;         // K1 primary-hit reuse: the hit record of the pixel's primary ray (k1_shade_step)
+    uint32_t* st_hit_inst0 = nullptr;
     uint32_t *queue0 = nullptr, *queue1 = nullptr;
     // speculative sample parallelism (render_reference_spec): one path per (pixel, sample); allocated on first use, grow-only
     struct Spec {
@@ -117,7 +119,7 @@ struct FrameBuffers {
     uint4* di_state = nullptr;                           // 8 planes x W x H: sampler state parked between the wavefront stages of K9
     char2* neighbor_offsets = nullptr;                   // RT2_NEIGHBOR_OFFSET_COUNT signed byte pairs (K7)
     uint32_t reservoir_block_row_pitch = 0, reservoir_array_pitch = 0;
-    uint32_t* counters = nullptr;      // [0..1] u64 rays, [2..3] u64 hits, then (count, head) per wavefront iteration
+    uint32_t* counters = nullptr;      // [0..1] u64 rays, [2..3] u64 hits, [4..5] u64 walks (K1), then (count, head) per wavefront iteration
     size_t counter_capacity = 0;
 };
 
@@ -143,6 +145,8 @@ struct rt2_ctx {
     cudaEvent_t snap_ready[RT2_FRAMES_IN_FLIGHT] = {}, read_done[RT2_FRAMES_IN_FLIGHT] = {}; uint32_t snap_next = 0; bool reads_pending = false;
     rt2_stats stats{};
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
+    bool stats_walks_counted = false;   // ... and fb.counters[4..5] holds the walks (K1); otherwise rays_walked = rays_traced
+    bool primary_reuse = true;          // K1: walk a pixel's primary ray once for all its samples (RT2_PRIMARY_REUSE=0: every sample walks its own)
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)
     int trace_blocks_per_sm[4] = {1, 1, 1, 1};          // [0] single-level queue kernel, [1] unified two-level, [2] nested two-level, [3] flattened instancing
     int trace_queue_blocks_per_sm = 1;       // resident blocks of k_trace_queue (the ReSTIR passes' ray-queue kernel)

@@ -1591,6 +1591,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     ctx->stats.kernel_launches = (ph & 1u) ? launches : ctx->stats.kernel_launches + launches;
     ctx->stats.wavefront_iterations = 1;
     ctx->stats_from_counters = true;
+    ctx->stats_walks_counted = false;
     if (ph & 1u) ctx->pending_rays_static = static_rays;
     return RT2_OK;
 }

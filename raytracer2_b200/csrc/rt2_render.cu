@@ -57,6 +57,9 @@ struct ShadeArgs {
     uint32_t* queue_out; uint32_t* count_out;
     ushort4* diffuse_f16; ushort4* specular_f16; float4* diffuse_f32;
     unsigned long long* stat_hits;
+    // primary-hit reuse (see k1_shade_step): the pixel's primary hit record, kept for its later samples; stat_rays counts the
+    // hit records the shader consumes (= its trace() calls), the trace kernels count the walks
+    float4* st_hit0; uint32_t* st_hit_inst0; unsigned long long* stat_rays; uint32_t primary_reuse;
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -170,6 +173,9 @@ __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a, const uint32_
     V3 dobj = v3(1.f, 1.f, 1.f);
     bool sh_pending = false;
     V3 oobj = v3(0.f, 0.f, 0.f);              // FLAT: origin in the object space of instance `inst`
+#ifdef RT2_DEBUG_STEP_CAP
+    int dbg_steps = 0;
+#endif
     for (;;) {
         const uint32_t need = __ballot_sync(0xFFFFFFFFu, !active);
         if (!exhausted && (need == 0xFFFFFFFFu || (REFILL_MIN > 0 && __popc(need) >= REFILL_MIN))) {
@@ -284,6 +290,9 @@ __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a, const uint32_
                         }
                     }
                 }
+#ifdef RT2_DEBUG_STEP_CAP   // measurement only (wrong images): what would a launch cost if no ray walked more than this many rounds?
+                if (++dbg_steps > RT2_DEBUG_STEP_CAP) { sp = 0; inst_sp = 0; ngroup.y = 0u; tgroup.y = 0u; dbg_steps = 0; }
+#endif
                 if (ngroup.y <= 0x00FFFFFFu) {
                     if (INSTANCED && inst != 0xFFFFFFFFu && sp == inst_sp) {    // this instance is done: back to the top level, world-space ray
                         inst = 0xFFFFFFFFu;
@@ -349,39 +358,51 @@ __global__ void __launch_bounds__(128, RT2_GENERIC_MIN_BLOCKS) k_trace_queue(Tra
 // refrence.rgen:28-46 for the path in `slot` whose ray just came back (hit record in st_hit): emission / throughput update,
 // cosine-lobe sample, path regeneration.  Returns true while the pixel still has rays to trace (state written back), false when
 // its last sample finished (radiance stored).
-__device__ __forceinline__ bool k1_shade_step(const ShadeArgs& a, const float* lut, uint32_t slot, uint32_t* hits) {
+// Primary-hit reuse: setupPrimaryRay has no jitter (GBufferHelpers.glsl:12-27: the pixel centre) and refrence.rgen:26 calls it anew
+// for every sample, so the spp samples of a pixel issue the SAME first trace().  Its hit record is kept (st_hit0) when it comes back
+// and the later samples consume it right here instead of walking the tree again: a sample costs max_bounces - 1 walks after the
+// first, a sky pixel one walk altogether.  Same hit record => same image, bit for bit; `rays` counts every record consumed (the
+// shader's trace() calls), the trace kernels count the walks (rt2_stats.rays_walked).
+__device__ __forceinline__ bool k1_shade_step(const ShadeArgs& a, const float* lut, uint32_t slot, uint32_t* hits, uint32_t* rays) {
     const float4 r0 = a.st_ray0[slot], r1 = a.st_ray1[slot], ac = a.st_acc[slot];
     const uint4 misc = a.st_misc[slot];
-    const float4 h = a.st_hit[slot];
+    float4 h = a.st_hit[slot];
+    uint32_t h_inst = a.sc.instances ? a.st_hit_inst[slot] : 0u;
     const uint32_t x = slot % a.band.width, ly = slot / a.band.width;
     const uint32_t y = band_local_to_global(a.band, ly);
     V3 o = v3(r0.x, r0.y, r0.z), d = v3(r0.w, r1.x, r1.y);
     V3 thr = v3(r1.z, r1.w, ac.x), rad = v3(ac.y, ac.z, ac.w);
     Rng rng; rng.index = misc.x; rng.seed = jenkins_hash(zcurve_to_linear(x, y)) + (a.frame + 13u);
     uint32_t sample = misc.y & 0xFFFFu, bounce = misc.y >> 16;
-    const uint32_t tri_slot = __float_as_uint(h.w);
-    bool next_sample;
-    if (tri_slot == 0xFFFFFFFFu) {                         // refrence.rgen:32-36
-        const V3 emission = environment_radiance(a.sc, *a.g, d);
-        rad = rad + thr * emission;
-        next_sample = true;
-    } else {
-        (*hits)++;
-        const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? a.st_hit_inst[slot] : 0u, h.y, h.z);
-        const V3 n = sf.normal, color = sf.color;
-        rad = rad + thr * sf.emission;                          // refrence.rgen:38
-        thr = thr * color;                                   // refrence.rgen:39
-        // RAB_GetSurfaceBrdfSample, bridge :437-461 (diffuseProbability == 1: cosine lobe only)
-        const float rx = rng_next(rng), ry = rng_next(rng), rz = rng_next(rng);
-        (void)rx;
-        const V3 hvec = sample_cos_hemisphere(ry, rz, (a.flags & RT2_LAUNCH_TRIG_LIBDEVICE) != 0u);
-        const V3 world_pos = o + d * h.x;                    // Hit.glsl:67
-        d = tangent_to_world(n, hvec);
-        o = world_pos;                                       // refrence.rgen:42
-        bounce++;
-        next_sample = bounce >= a.max_bounces;
+    if (a.primary_reuse && bounce == 0u) {                    // the one primary ray of this pixel that is walked
+        a.st_hit0[slot] = h;
+        if (a.sc.instances) a.st_hit_inst0[slot] = h_inst;
     }
-    if (next_sample) {
+    for (;;) {
+        (*rays)++;
+        const uint32_t tri_slot = __float_as_uint(h.w);
+        bool next_sample;
+        if (tri_slot == 0xFFFFFFFFu) {                         // refrence.rgen:32-36
+            const V3 emission = environment_radiance(a.sc, *a.g, d);
+            rad = rad + thr * emission;
+            next_sample = true;
+        } else {
+            (*hits)++;
+            const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, h_inst, h.y, h.z);
+            const V3 n = sf.normal, color = sf.color;
+            rad = rad + thr * sf.emission;                          // refrence.rgen:38
+            thr = thr * color;                                   // refrence.rgen:39
+            // RAB_GetSurfaceBrdfSample, bridge :437-461 (diffuseProbability == 1: cosine lobe only)
+            const float rx = rng_next(rng), ry = rng_next(rng), rz = rng_next(rng);
+            (void)rx;
+            const V3 hvec = sample_cos_hemisphere(ry, rz, (a.flags & RT2_LAUNCH_TRIG_LIBDEVICE) != 0u);
+            const V3 world_pos = o + d * h.x;                    // Hit.glsl:67
+            d = tangent_to_world(n, hvec);
+            o = world_pos;                                       // refrence.rgen:42
+            bounce++;
+            next_sample = bounce >= a.max_bounces;
+        }
+        if (!next_sample) break;
         sample++; bounce = 0;
         if (sample >= a.spp) {
             // refrence.rgen:46
@@ -392,6 +413,9 @@ __device__ __forceinline__ bool k1_shade_step(const ShadeArgs& a, const float* l
         }
         thr = v3(1.f, 1.f, 1.f);
         setup_primary_ray(a.g->view, x, y, &o, &d);
+        if (!a.primary_reuse) break;
+        h = a.st_hit0[slot];                                      // the next sample's first trace(): same ray, same record
+        if (a.sc.instances) h_inst = a.st_hit_inst0[slot];
     }
     a.st_ray0[slot] = make_float4(o.x, o.y, o.z, d.x);
     a.st_ray1[slot] = make_float4(d.y, d.z, thr.x, thr.y);
@@ -437,7 +461,7 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_k1_shade(ShadeArg
     __shared__ uint32_t s_off[18];
     const uint32_t count = *a.count_in;
     const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t hits = 0, parity = 0;
+    uint32_t hits = 0, seen = 0, parity = 0;
     // all threads of a block iterate together (block_append_index uses block barriers)
     // the queue entry of the next iteration is fetched one iteration ahead: one dependent memory round trip less per ray
     uint32_t b0 = blockIdx.x * blockDim.x;
@@ -447,11 +471,12 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_k1_shade(ShadeArg
         bool alive = false;
         const uint32_t slot = slot_ahead;
         if (i + stride < count) slot_ahead = a.queue_in[i + stride];
-        if (i < count) alive = k1_shade_step(a, lut, slot, &hits);
+        if (i < count) alive = k1_shade_step(a, lut, slot, &hits, &seen);
         const uint32_t at = block_append_index(alive, a.count_out, s_off, parity);
         if (alive) a.queue_out[at] = slot;
     }
     warp_flush_counter(a.stat_hits, hits);
+    warp_flush_counter(a.stat_rays, seen);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -480,7 +505,7 @@ __device__ __forceinline__ void path_warp_body(const TraceArgs& t, const ShadeAr
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     uint32_t* q = w.pop + (size_t)warp * w.P;
     const uint32_t tiles_x = (a.band.width + 7u) >> 3;
-    uint32_t n = 0, rays = 0, hits = 0;
+    uint32_t n = 0, rays = 0, hits = 0, seen = 0;
     bool exhausted = false;
     for (;;) {
         // ---- shade phase: every path of the population has a hit record waiting --------------------------------
@@ -489,7 +514,7 @@ __device__ __forceinline__ void path_warp_body(const TraceArgs& t, const ShadeAr
             const uint32_t i = i0 + lane;
             bool alive = false;
             uint32_t slot = 0;
-            if (i < n) { slot = q[i]; alive = k1_shade_step(a, lut, slot, &hits); }
+            if (i < n) { slot = q[i]; alive = k1_shade_step(a, lut, slot, &hits, &seen); }
             const uint32_t m = __ballot_sync(0xFFFFFFFFu, alive);      // also orders this batch's queue reads before its writes
             if (alive) q[wr + __popc(m & ((1u << lane) - 1u))] = slot;
             wr += __popc(m);
@@ -551,8 +576,9 @@ __device__ __forceinline__ void path_warp_body(const TraceArgs& t, const ShadeAr
         rays += n;
         __syncwarp();
     }
-    if (lane == 0) { if (rays) atomicAdd(t.stat_rays, (unsigned long long)rays); }
+    if (lane == 0) { if (rays) atomicAdd(t.stat_rays, (unsigned long long)rays); }     // walks
     warp_flush_counter(a.stat_hits, hits);
+    warp_flush_counter(a.stat_rays, seen);                                                // hit records consumed = the shader's trace() calls
 }
 
 template <bool INSTANCED, bool FLAT = false>
@@ -610,20 +636,26 @@ __device__ __forceinline__ bool spec_pixel(const SpecArgs& a, const uint32_t* li
 // the samples in between.  Round 0 predicts max_bounces hits per sample (a path that never misses); a fix-up round predicts what
 // the previous round observed for that sample — its path came from a wrong position, but what makes a sample short is mostly
 // geometry (a primary ray that leaves through a crack misses whatever the random numbers are).
+// Primary-hit reuse (k1_shade_step): the paths of a pixel start with the same primary ray, so only the first of them — the
+// representative — is queued for the first walk (queue_rep), and bounce 0 of every path reads the representative's hit record.  The
+// paths of a pixel are consecutive threads and alive as a prefix (sample < spp), block_append_index hands out consecutive places in
+// thread order, so a path's representative sits `back` = min(j, threadIdx.x) places before it (a pixel whose paths straddle a block
+// has one representative per part); `back` travels in the upper half of misc.y until bounce 0 is shaded.  queue_rep == nullptr: off.
 template <bool IMPLICIT>
 __global__ void __launch_bounds__(256) k_spec_gen(SpecArgs a, const uint32_t* list, const uint32_t* list_count, uint32_t first, uint32_t lanes,
-                                                  uint32_t* queue_out, uint32_t* count_out, uint32_t path_base) {
+                                                  uint32_t* queue_out, uint32_t* count_out, uint32_t path_base, uint32_t* queue_rep, uint32_t* count_rep) {
     const uint32_t n_list = IMPLICIT ? lanes : *list_count;
     const uint64_t n_items = (uint64_t)n_list * a.spp;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    __shared__ uint32_t s_off[18];
+    __shared__ uint32_t s_off[18], s_rep[18];
     uint32_t parity = 0;
     for (uint64_t b0 = (uint64_t)blockIdx.x * blockDim.x; b0 < n_items; b0 += stride, parity ^= 1u) {
         const uint64_t i = b0 + threadIdx.x;
         bool alive = false;
-        uint32_t slot = 0, sample = 0, index = 0, x = 0, ly = 0;
+        uint32_t slot = 0, sample = 0, index = 0, x = 0, ly = 0, back = 0;
         if (i < n_items) {
             const uint32_t k = (uint32_t)(i / a.spp), j = (uint32_t)(i % a.spp);
+            if (queue_rep) back = min(j, threadIdx.x);
             if (spec_pixel<IMPLICIT>(a, list, first, k, &slot)) {
                 uint2 pr = make_uint2(0u, 1u);                 // refrence.rgen:21: a fresh pixel starts sample 0 at position 1
                 if (IMPLICIT) { if (j == 0u) { a.px_prog[slot] = pr; a.px_rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f); } }
@@ -638,21 +670,25 @@ __global__ void __launch_bounds__(256) k_spec_gen(SpecArgs a, const uint32_t* li
             }
         }
         const uint32_t p = block_append_index(alive, count_out, s_off, parity);
+        uint32_t rep_at = 0;
+        if (queue_rep) rep_at = block_append_index(alive && back == 0u, count_rep, s_rep, parity);
         if (alive) {
             V3 o, d;
             setup_primary_ray(a.g->view, x, band_local_to_global(a.band, ly), &o, &d);
             a.ray0[path_base + p] = make_float4(o.x, o.y, o.z, d.x);
             a.ray1[path_base + p] = make_float4(d.y, d.z, 1.0f, 1.0f);
-            a.misc[path_base + p] = make_uint4(index, 0u, slot * a.spp + sample, __float_as_uint(1.0f));
+            a.misc[path_base + p] = make_uint4(index, back << 16, slot * a.spp + sample, __float_as_uint(1.0f));
             a.start_index[slot * a.spp + sample] = index;
             queue_out[p] = path_base + p;
+            if (queue_rep && back == 0u) queue_rep[rep_at] = path_base + p;
         }
     }
 }
 
 // refrence.rgen:28-42 for one traced ray of each queued path; a path is one sample and ends with it
+// shared_primary: this launch shades bounce 0 and the hit record is the representative's (k_spec_gen)
 __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_spec_shade(SpecArgs a, const uint32_t* queue_in, const uint32_t* count_in,
-                                                                          uint32_t* queue_out, uint32_t* count_out) {
+                                                                          uint32_t* queue_out, uint32_t* count_out, uint32_t shared_primary) {
     __shared__ float lut[256];
     lut[threadIdx.x] = a.sc.srgb_lut[threadIdx.x];
     __syncthreads();
@@ -669,13 +705,14 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_spec_shade(SpecAr
         if (i < count) {
             const float4 r0 = a.ray0[p], r1 = a.ray1[p];
             const uint4 misc = a.misc[p];
-            const float4 h = a.hit[p];
+            const uint32_t hp = shared_primary ? p - (misc.y >> 16) : p;
+            const float4 h = a.hit[hp];
             const uint32_t ps = misc.z, slot = a.cand_list ? a.cand_list[(ps - a.path_base) / a.cand_K] : ps / a.spp;
             const uint32_t x = slot % a.band.width, y = band_local_to_global(a.band, slot / a.band.width);
             V3 o = v3(r0.x, r0.y, r0.z), d = v3(r0.w, r1.x, r1.y);
             V3 thr = v3(r1.z, r1.w, __uint_as_float(misc.w));
             Rng rng; rng.index = misc.x; rng.seed = jenkins_hash(zcurve_to_linear(x, y)) + (a.frame + 13u);
-            uint32_t bounce = misc.y;
+            uint32_t bounce = misc.y & 0xFFFFu;
             const uint32_t tri_slot = __float_as_uint(h.w);
             float4* c = a.contrib + ((size_t)ps * a.max_bounces + bounce);
             if (tri_slot == 0xFFFFFFFFu) {                         // refrence.rgen:32-36
@@ -683,7 +720,7 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_spec_shade(SpecAr
                 *c = make_float4(e.x, e.y, e.z, 0.f);
                 a.nhits[ps] = (uint8_t)(bounce | 0x80u);
             } else {
-                const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? a.hit_inst[p] : 0u, h.y, h.z);
+                const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? a.hit_inst[hp] : 0u, h.y, h.z);
                 const V3 e = thr * sf.emission;                    // refrence.rgen:38
                 *c = make_float4(e.x, e.y, e.z, 0.f);
                 thr = thr * sf.color;                              // refrence.rgen:39
@@ -756,8 +793,8 @@ __global__ void __launch_bounds__(256) k_spec_reduce(SpecArgs a, const uint32_t*
 // frame — and the remaining samples can only start at idx0 + 3 m, m = 0 .. max_bounces x (remaining - 1).  So ALL those
 // candidate paths are traced in one parallel round, and k_spec_reduce_cand walks the chain m -> m + hits(m) in order.
 __global__ void __launch_bounds__(256) k_spec_gen_cand(SpecArgs a, const uint32_t* list, const uint32_t* list_count, uint32_t max_pixels,
-                                                       uint32_t* queue_out, uint32_t* count_out) {
-    __shared__ uint32_t s_off[18];
+                                                       uint32_t* queue_out, uint32_t* count_out, uint32_t* queue_rep, uint32_t* count_rep) {
+    __shared__ uint32_t s_off[18], s_rep[18];
     const uint32_t n_list = min(*list_count, max_pixels);
     const uint64_t n_items = (uint64_t)n_list * a.cand_K;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
@@ -765,21 +802,25 @@ __global__ void __launch_bounds__(256) k_spec_gen_cand(SpecArgs a, const uint32_
     for (uint64_t b0 = (uint64_t)blockIdx.x * blockDim.x; b0 < n_items; b0 += stride, parity ^= 1u) {
         const uint64_t i = b0 + threadIdx.x;
         bool alive = false;
-        uint32_t slot = 0, index = 0;
+        uint32_t slot = 0, index = 0, back = 0;
         if (i < n_items) {
             const uint32_t k = (uint32_t)(i / a.cand_K), m = (uint32_t)(i % a.cand_K);
+            if (queue_rep) back = min(m, threadIdx.x);            // the candidates of a pixel are alive as a prefix in m
             slot = list[k];
             const uint2 pr = a.px_prog[slot];
             if (pr.x < a.spp && m <= a.max_bounces * (a.spp - pr.x - 1u)) { alive = true; index = pr.y + 3u * m; }
         }
         const uint32_t p = block_append_index(alive, count_out, s_off, parity);
+        uint32_t rep_at = 0;
+        if (queue_rep) rep_at = block_append_index(alive && back == 0u, count_rep, s_rep, parity);
         if (alive) {
             V3 o, d;
             setup_primary_ray(a.g->view, slot % a.band.width, band_local_to_global(a.band, slot / a.band.width), &o, &d);
             a.ray0[a.path_base + p] = make_float4(o.x, o.y, o.z, d.x);
             a.ray1[a.path_base + p] = make_float4(d.y, d.z, 1.0f, 1.0f);
-            a.misc[a.path_base + p] = make_uint4(index, 0u, a.path_base + (uint32_t)i, __float_as_uint(1.0f));
+            a.misc[a.path_base + p] = make_uint4(index, back << 16, a.path_base + (uint32_t)i, __float_as_uint(1.0f));
             queue_out[p] = a.path_base + p;
+            if (queue_rep && back == 0u) queue_rep[rep_at] = a.path_base + p;
         }
     }
 }
@@ -860,7 +901,7 @@ static cudaError_t dev_alloc(rt2_ctx* ctx, T** p, size_t n) {
 void frame_release(rt2_ctx* ctx) {
     FrameBuffers& f = ctx->fb;
     void* ptrs[] = {f.diffuse_f16, f.specular_f16, f.diffuse_f32, f.hit_ids, f.output_rgba8, f.st_ray0, f.st_ray1, f.st_acc, f.st_misc,
-                    f.st_hit, f.st_hit_inst, f.queue0, f.queue1, f.counters, f.warp_pop,
+                    f.st_hit, f.st_hit_inst, f.st_hit0, f.st_hit_inst0, f.queue0, f.queue1, f.counters, f.warp_pop,
                     f.spec.ray0, f.spec.ray1, f.spec.hit, f.spec.contrib, f.spec.px_rad, f.spec.misc, f.spec.hit_inst, f.spec.queue0, f.spec.queue1,
                     f.spec.pending0, f.spec.pending1, f.spec.counters, f.spec.nhits, f.spec.px_prog, f.spec.start_index};
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -885,6 +926,8 @@ int frame_resize(rt2_ctx* ctx, uint32_t w, uint32_t h) {
     RT2_CUDA(ctx, dev_alloc(ctx, &f.st_misc, n));
     RT2_CUDA(ctx, dev_alloc(ctx, &f.st_hit, n));
     RT2_CUDA(ctx, dev_alloc(ctx, &f.st_hit_inst, n));
+    RT2_CUDA(ctx, dev_alloc(ctx, &f.st_hit0, n));
+    RT2_CUDA(ctx, dev_alloc(ctx, &f.st_hit_inst0, n));
     // queues are indexed in the padded 8x4-tile lane range: a wavefront chain's window starts at its first padded lane, so
     // dead lanes of earlier chains shift later windows past w*h when w is not a multiple of 8 (or rows of 4)
     const size_t padded = (size_t)((w + 7u) / 8u) * ((h + 3u) / 4u) * 32u;
@@ -923,16 +966,19 @@ static TraceArgs make_trace_args(rt2_ctx* ctx) {
     return t;
 }
 
-// counters layout: [0..1] u64 rays, [2..3] u64 hits, then per iteration it: count at 4 + 2*it, head at 5 + 2*it
+// counters layout: [0..1] u64 rays (the shader's trace() calls), [2..3] u64 hits, [4..5] u64 walks (K1: primary-hit reuse makes them
+// fewer than the rays), then per iteration it: count at RT2_COUNTER_BASE + 2*it, head one after
+#define RT2_COUNTER_BASE 6
 static int ensure_counters(rt2_ctx* ctx, uint32_t iterations) {
     FrameBuffers& f = ctx->fb;
-    const size_t need = 4 + RT2_MAX_CHAINS * 2 * ((size_t)iterations + 2);     // per chain and iteration: count, head
+    const size_t need = RT2_COUNTER_BASE + RT2_MAX_CHAINS * 2 * ((size_t)iterations + 2);     // per chain and iteration: count, head
     if (f.counter_capacity < need) {
         if (f.counters) { RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(f.counters); f.counters = nullptr; }
         RT2_CUDA(ctx, cudaMalloc((void**)&f.counters, need * 4));
         f.counter_capacity = need;
     }
     RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, need * 4, ctx->stream));
+    ctx->stats_walks_counted = false;
     return RT2_OK;
 }
 
@@ -997,7 +1043,9 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
     const uint32_t spp = lp.spp ? lp.spp : 12u;                    // refrence.rgen:17
     const uint32_t bounces = lp.max_bounces ? lp.max_bounces : 5u; // refrence.rgen:16
     if (spp > 65535u || bounces > 65535u || (uint64_t)spp * bounces > (1u << 22)) return fail(ctx, RT2_E_INVALID, "spp x bounces too large");
-    const uint32_t iterations = spp * bounces;
+    // a pixel is a chain of spp x bounces dependent rays; with primary-hit reuse only the first sample walks its primary ray
+    const bool reuse = ctx->primary_reuse;
+    const uint32_t iterations = reuse ? 1u + spp * (bounces - 1u) : spp * bounces;
     if ((rc = ensure_counters(ctx, iterations))) return rc;
     const Band band = make_band(f.width, f.height, lp);
     const uint32_t tiles_x = (band.width + 7) / 8, tiles_y = (band.local_rows + 3) / 4;
@@ -1009,8 +1057,11 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
     a.st_ray0 = f.st_ray0; a.st_ray1 = f.st_ray1; a.st_acc = f.st_acc; a.st_misc = f.st_misc; a.st_hit = f.st_hit; a.st_hit_inst = f.st_hit_inst;
     a.diffuse_f16 = f.diffuse_f16; a.specular_f16 = f.specular_f16; a.diffuse_f32 = f.diffuse_f32;
     a.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
+    a.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
+    a.st_hit0 = f.st_hit0; a.st_hit_inst0 = f.st_hit_inst0; a.primary_reuse = reuse ? 1u : 0u;
     TraceArgs t = make_trace_args(ctx);
-    t.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
+    t.stat_rays = reinterpret_cast<unsigned long long*>(f.counters + 4);
+    ctx->stats_walks_counted = true;
     if (padded) {
         const int shade_blocks_full = ctx->num_sms * 8;
         const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
@@ -1051,7 +1102,7 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
                 RT2_CUDA(ctx, cudaMalloc((void**)&f.warp_pop, need * 4));
                 f.warp_pop_cap = need; ctx->device_bytes += need * 4;
             }
-            WarpPathArgs w{f.warp_pop, P, f.counters + 4, 0u, padded};
+            WarpPathArgs w{f.warp_pop, P, f.counters + RT2_COUNTER_BASE, 0u, padded};
             if (profile) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[0], ctx->stream));
             if (flat) k_path_warp<false, true><<<blocks, 128, 0, ctx->stream>>>(t, a, w);
             else if (s.num_instances) k_path_warp<true><<<blocks, 128, 0, ctx->stream>>>(t, a, w);
@@ -1092,7 +1143,7 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
             k.st = c == 0 ? ctx->stream : ctx->chain_streams[c];
             if (c != 0) RT2_CUDA(ctx, cudaStreamWaitEvent(k.st, ctx->chain_fork, 0));
             k.first = c * per; k.end = std::min(padded, k.first + per);
-            k.cnt = f.counters + 4 + c * counter_stride;
+            k.cnt = f.counters + RT2_COUNTER_BASE + c * counter_stride;
             k.q[0] = f.queue0 + k.first; k.q[1] = f.queue1 + k.first;
             k.shade_blocks = std::max(1, std::min(shade_blocks_full, (int)((k.end - k.first + 255u) / 256u)));
             // persistent grid: every resident slot, unless the chain is so small that each lane would get fewer than
@@ -1175,7 +1226,8 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
     const size_t band_pixels = (size_t)band.width * band.local_rows;
     const size_t paths = band_pixels * spp, contribs = paths * bounces;
     const uint32_t rounds = 1u + (uint32_t)std::max(0, ctx->spec_rounds);
-    const uint32_t RB = 2u * (bounces + 1u) + 2u;                 // per round: (count, head) x (bounces + 1), pending count, pad
+    const uint32_t RB = 2u * (bounces + 1u) + 4u;                 // per round: (count, head) x (bounces + 1), (count, head) of the representatives' queue, pending count, pad
+    const bool reuse = ctx->primary_reuse;
     const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
     // two wavefront chains once a chain still gets >= 1 M paths (measured like the sequential form's rule); RT2_CHAINS overrides
     uint32_t nch = profile ? 1u : (ctx->chains ? std::min(ctx->chains, RT2_MAX_CHAINS) : (paths >= (2u << 20) ? 2u : 1u));
@@ -1221,6 +1273,8 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
         a.diffuse_f16 = f.diffuse_f16; a.specular_f16 = f.specular_f16; a.diffuse_f32 = f.diffuse_f32;
         a.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);           // valid samples only (k_spec_reduce)
         a.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
+        unsigned long long* stat_walks = reinterpret_cast<unsigned long long*>(f.counters + 4);   // every walk, speculation losses included
+        ctx->stats_walks_counted = true;
         TraceArgs t = make_trace_args(ctx);
         t.st_ray0 = sp.ray0; t.st_ray1 = sp.ray1; t.st_hit = sp.hit; t.st_hit_inst = sp.hit_inst;
         for (cudaEvent_t e : ctx->prof_events) cudaEventDestroy(e);
@@ -1264,8 +1318,10 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
                 uint32_t* cnt = round_counters(k, r);
                 const int gen_blocks = r ? ctx->num_sms * 2 : (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)ctx->num_sms * 16, ((uint64_t)k.lanes * spp + 255) / 256));
                 SpecArgs ca = a; ca.path_base = k.base;
-                if (r == 0) k_spec_gen<true><<<gen_blocks, 256, 0, k.st>>>(ca, nullptr, nullptr, k.first, k.lanes, k.q[0], cnt, k.base);
-                else k_spec_gen<false><<<gen_blocks, 256, 0, k.st>>>(ca, k.pend[(r - 1) & 1], round_counters(k, r - 1) + (RB - 2), 0u, 0u, k.q[0], cnt, k.base);
+                // with primary-hit reuse the first walk of the round runs over the pixels' representatives, queued in q[1] (free until shade 0 writes it)
+                uint32_t* q_rep = reuse ? k.q[1] : nullptr; uint32_t* c_rep = reuse ? cnt + (RB - 4) : nullptr;
+                if (r == 0) k_spec_gen<true><<<gen_blocks, 256, 0, k.st>>>(ca, nullptr, nullptr, k.first, k.lanes, k.q[0], cnt, k.base, q_rep, c_rep);
+                else k_spec_gen<false><<<gen_blocks, 256, 0, k.st>>>(ca, k.pend[(r - 1) & 1], round_counters(k, r - 1) + (RB - 2), 0u, 0u, k.q[0], cnt, k.base, q_rep, c_rep);
                 launches++;
             }
             for (uint32_t it = 0; it < bounces; it++) {
@@ -1276,10 +1332,11 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
                     const int shade_blocks = r ? ctx->num_sms : (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)full_shade, (k.cap_paths + 255) / 256));
                     if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it], k.st));
                     t.queue = k.q[it & 1]; t.count = cnt + 2 * it; t.head = cnt + 2 * it + 1;
-                    t.stat_rays = reinterpret_cast<unsigned long long*>(k.cnt);          // every ray traced, speculation losses included (diagnostic)
+                    if (reuse && it == 0) { t.queue = k.q[1]; t.count = cnt + (RB - 4); t.head = cnt + (RB - 3); }
+                    t.stat_rays = stat_walks;
                     launch_trace_kernel(ctx, t, flat, trace_blocks, k.st);
                     if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 1], k.st));
-                    k_spec_shade<<<shade_blocks, 256, 0, k.st>>>(a, k.q[it & 1], cnt + 2 * it, k.q[(it + 1) & 1], cnt + 2 * (it + 1));
+                    k_spec_shade<<<shade_blocks, 256, 0, k.st>>>(a, k.q[it & 1], cnt + 2 * it, k.q[(it + 1) & 1], cnt + 2 * (it + 1), reuse && it == 0 ? 1u : 0u);
                     if (profile && r == 0) RT2_CUDA(ctx, cudaEventRecord(ctx->prof_events[3 * it + 2], k.st));
                     launches += 2;
                 }
@@ -1300,8 +1357,10 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
         sa.st_ray0 = f.st_ray0; sa.st_ray1 = f.st_ray1; sa.st_acc = f.st_acc; sa.st_misc = f.st_misc; sa.st_hit = f.st_hit; sa.st_hit_inst = f.st_hit_inst;
         sa.diffuse_f16 = f.diffuse_f16; sa.specular_f16 = f.specular_f16; sa.diffuse_f32 = f.diffuse_f32;
         sa.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
+        sa.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
+        sa.st_hit0 = f.st_hit0; sa.st_hit_inst0 = f.st_hit_inst0; sa.primary_reuse = reuse ? 1u : 0u;
         TraceArgs ts = make_trace_args(ctx);
-        ts.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
+        ts.stat_rays = stat_walks;
         const uint32_t K = bounces * (spp - 1u) + 1u;
         for (uint32_t c = 0; c < nch; c++) {
             const Chain& k = ch[c];
@@ -1312,13 +1371,14 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
             const uint32_t max_pixels = (uint32_t)std::min<size_t>(k.cap_paths / K, 0x7FFFFFFFu / K);
             SpecArgs ca = a;
             ca.cand_list = pend_list; ca.cand_K = K; ca.path_base = k.base;
-            k_spec_gen_cand<<<ctx->num_sms * 2, 256, 0, k.st>>>(ca, pend_list, pend_count, max_pixels, k.q[0], ccnt);
+            k_spec_gen_cand<<<ctx->num_sms * 2, 256, 0, k.st>>>(ca, pend_list, pend_count, max_pixels, k.q[0], ccnt, reuse ? k.q[1] : nullptr, reuse ? ccnt + (RB - 4) : nullptr);
             launches++;
             for (uint32_t it = 0; it < bounces; it++) {
                 t.queue = k.q[it & 1]; t.count = ccnt + 2 * it; t.head = ccnt + 2 * it + 1;
-                t.stat_rays = reinterpret_cast<unsigned long long*>(k.cnt);
+                if (reuse && it == 0) { t.queue = k.q[1]; t.count = ccnt + (RB - 4); t.head = ccnt + (RB - 3); }
+                t.stat_rays = stat_walks;
                 launch_trace_kernel(ctx, t, flat, ctx->num_sms * 2, k.st);
-                k_spec_shade<<<ctx->num_sms, 256, 0, k.st>>>(ca, k.q[it & 1], ccnt + 2 * it, k.q[(it + 1) & 1], ccnt + 2 * (it + 1));
+                k_spec_shade<<<ctx->num_sms, 256, 0, k.st>>>(ca, k.q[it & 1], ccnt + 2 * it, k.q[(it + 1) & 1], ccnt + 2 * (it + 1), reuse && it == 0 ? 1u : 0u);
                 launches += 2;
             }
             k_spec_reduce_cand<<<ctx->num_sms, 256, 0, k.st>>>(ca, pend_list, pend_count, max_pixels, overflow_list, ccnt + (RB - 2));
@@ -1406,6 +1466,7 @@ int render_init(rt2_ctx* ctx) {
     if (const char* e = getenv("RT2_SPECULATE")) ctx->speculate = atoi(e);
     if (const char* e = getenv("RT2_SPEC_ROUNDS")) { int v = atoi(e); if (v >= 0 && v <= 16) ctx->spec_rounds = v; }
     if (const char* e = getenv("RT2_PATH_MODE")) ctx->path_mode = atoi(e);
+    if (const char* e = getenv("RT2_PRIMARY_REUSE")) ctx->primary_reuse = atoi(e) != 0;
     if (const char* e = getenv("RT2_WARP_P")) { int v = atoi(e); if (v >= 32 && v <= 4096) ctx->warp_paths = (uint32_t)v; }
     if (const char* e = getenv("RT2_WARP_BLOCKS")) { int v = atoi(e); if (v >= 1 && v <= 16) ctx->warp_blocks_per_sm = v; }
     int p0 = 0, p1 = 0, p2 = 0, b3 = 0;

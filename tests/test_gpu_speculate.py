@@ -114,13 +114,13 @@ def test_auto_policy_speculates_in_closed_scenes_only(monkeypatch):
         for frame in range(1, 5):
             lp.execute(frame, rt.LaunchParams(spp=4, max_bounces=4))
             ctx.sync()
-            launches.append(ctx.stats().kernel_launches)
+            launches.append((ctx.stats().kernel_launches, ctx.stats().sample_schedule))
             got = ctx.read(rt.BUF_DIFFUSE_F32, np.uint32).reshape(h, w, 4)
             ref = osc.render_reference(g, frame, w, h, spp=4, max_bounces=4)[2].view(np.uint32)
             assert np.array_equal(got, ref), (kind, frame)
-        assert launches[0] >= 2 * 16                      # sequential: a launch pair per (sample, bounce)
+        assert launches[0] == (2 * (1 + 4 * 3) + 1, 0)    # sequential: a launch pair per walked (sample, bounce) — the primary ray once — and the init
         if closed:
-            assert launches[-1] < launches[0], launches   # speculation took over
+            assert launches[-1][1] == 1, launches         # speculation took over
         else:
             assert launches[-1] == launches[0], launches
         ctx.close()
