@@ -212,8 +212,8 @@ def run_extra(rt, torch, device):
         h = st.rays_hit / max(st.rays_traced, 1)
         b_ray = depth_bytes + 96 + h * shade_bytes
         mrays = st.rays_traced / ms / 1e3
-        return {"workload": name, "ms_per_frame": ms, "Mrays_s": mrays, "rays_per_frame": st.rays_traced, "hit_fraction": h, "B_ray": b_ray,
-                "roofline_frac_hbm_nominal": mrays * 1e6 * b_ray / 1e9 / peak, "kernel_launches": st.kernel_launches, "clocks": clocks, "note": note}
+        return {"workload": name, "ms_per_frame": ms, "Mrays_s": mrays, "rays_per_frame": st.rays_traced, "walks_per_frame": st.rays_walked, "hit_fraction": h, "B_ray": b_ray,
+                "roofline_frac_hbm_nominal": (st.rays_walked * (depth_bytes + 96) + st.rays_traced * h * shade_bytes) / (ms * 1e-3) / 1e9 / peak, "kernel_launches": st.kernel_launches, "clocks": clocks, "note": note}
 
     def small(name, us, units, bytes_per_unit, unit_name):
         gbs = units * bytes_per_unit / (us * 1e-6) / 1e9 if us > 0 else 0.0
@@ -388,7 +388,8 @@ def main():
     grp.sync()
     ms = ev0.elapsed_time(ev1)
     st = ctx.stats()
-    rays_per_step = st.rays_traced
+    rays_per_step = st.rays_traced           # the shader's trace() calls (refrence.rgen:30), what the oracle counts too
+    walks_per_step = st.rays_walked          # BVH walks behind them: a pixel's samples share their unjittered primary ray (rt2_stats.rays_walked)
     hits_per_step = st.rays_hit
     launches = (st.kernel_launches + (1 if world > 1 else 0)) * args.steps       # + the un-permute kernel
     if dist:
@@ -402,6 +403,30 @@ def main():
     grp.sync()
     pst = ctx.stats()
     trace_ms, shade_ms, trace_launches = pst.trace_ns / 1e6, pst.shade_ns / 1e6, max(1, pst.trace_launches)
+    walks_profiled = pst.rays_walked
+
+    # the same step with every trace() call walked (RT2_PRIMARY_REUSE=0), N = 1 only: reported beside `value`, never instead of it
+    value_every_ray_walked = None
+    if world == 1:
+        os.environ["RT2_PRIMARY_REUSE"] = "0"
+        try:
+            grp0 = rt.Group.from_rank(local_rank, rank, world, uid)
+            grp0.ctx(0).set_stream(stream.cuda_stream)
+            grp0.upload_scene(sc.desc); grp0.resize(W, H); grp0.update_uniform(g)
+            for i in range(args.warmup):
+                grp0.execute(1 + i, params, gather=GATHER); grp0.sync()
+            torch.cuda.synchronize()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record()
+            for i in range(args.steps):
+                grp0.execute(100 + i, params, gather=GATHER)
+            grp0.wait_gather(); f1.record(); torch.cuda.synchronize(); grp0.sync()
+            st0 = grp0.ctx(0).stats()
+            assert st0.rays_walked >= st0.rays_traced
+            value_every_ray_walked = st0.rays_traced * args.steps / (f0.elapsed_time(f1) * 1e-3) / 1e6
+            grp0.close()
+        finally:
+            os.environ.pop("RT2_PRIMARY_REUSE", None)
 
     # ---- e2e through the C ABI with host buffers --------------------------------------------------------------
     # Two frames in flight, as the reference's swapchain loop has (src/context.rs:30,639-694): the ASSEMBLED frame n travels to
@@ -431,19 +456,19 @@ def main():
     e2e_ms = e0.elapsed_time(e1)
     frame_ok = bool(torch.isfinite(host_out[(args.steps - 1) & 1].float()).all().item()) and float(host_out[(args.steps - 1) & 1].float().abs().sum()) > 0 if rank == 0 else True
 
-    t = torch.tensor([ms, e2e_ms, float(rays_per_step), float(launches), trace_ms, shade_ms, float(hits_per_step)], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms, e2e_ms, float(rays_per_step), float(launches), trace_ms, shade_ms, float(hits_per_step), float(walks_per_step)], dtype=torch.float64, device="cuda")
     if dist:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         ms, e2e_ms = tmax[0].item(), tmax[1].item()
-        total_rays_step, launches, total_hits_step = tsum[2].item(), int(tsum[3].item()), tsum[6].item()
+        total_rays_step, launches, total_hits_step, total_walks_step = tsum[2].item(), int(tsum[3].item()), tsum[6].item(), tsum[7].item()
     else:
-        total_rays_step, total_hits_step = float(rays_per_step), float(hits_per_step)
+        total_rays_step, total_hits_step, total_walks_step = float(rays_per_step), float(hits_per_step), float(walks_per_step)
     value = total_rays_step * args.steps / (ms * 1e-3) / 1e6
     e2e_value = total_rays_step * args.steps / (e2e_ms * 1e-3) / 1e6
     if rank == 0:
         peak, peak_kind = measured_peak_hbm()
-        rays_per_launch = rays_per_step / trace_launches
+        rays_per_launch = walks_profiled / trace_launches       # what the trace kernel actually walks
         achieved = rays_per_launch * B_TRAVERSE / (trace_ms / trace_launches * 1e-3) / 1e9
         ncu = ncu_summary()
         k0 = (ncu.get("launches") or [{}])[0]
@@ -456,7 +481,12 @@ def main():
                        "sharding": "whole frame (rt2_group of one)" if n_gpus == 1 else f"{BAND_ROWS}-row bands interleaved over {n_gpus} ranks, scene replicated; band plan + ncclAllGather of the rgba16f bands + un-permute inside librt2cuda.so (rt2_group_*), every step",
                        "schedule": "speculative sample parallelism (every sample of a pixel is its own path; validated + summed in shader order), 2 wavefront chains" if st.sample_schedule == 1 else "one launch pair per (sample, bounce), wavefront chains",
                        "l2": "no flush: working set (BVH+triangles+shading records+textures+path state ~1 GB) exceeds the 126 MB L2",
-                       "rays_per_step": total_rays_step, "hit_fraction": total_hits_step / max(total_rays_step, 1.0)},
+                       "rays_per_step": total_rays_step, "hit_fraction": total_hits_step / max(total_rays_step, 1.0),
+                       "primary_hit_reuse": "rays = the shader's trace() calls (refrence.rgen:30; the CPU oracle counts the same). setupPrimaryRay has no jitter "
+                                            "(GBufferHelpers.glsl:12-27), so a pixel's spp samples issue the same first trace(): walked once, its hit record consumed spp times, "
+                                            "image and counts bit-identical (tests/test_gpu_primary_reuse.py); RT2_PRIMARY_REUSE=0 walks every one",
+                       "walks_per_step": total_walks_step, "value_in_walks": total_walks_step * args.steps / (ms * 1e-3) / 1e6,
+                       "value_every_ray_walked": value_every_ray_walked},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 1424, "d2h_bytes_per_step": frame_bytes, "ms_per_step": e2e_ms / args.steps,
                     "delivers": "assembled W x H rgba16f frame in pinned host memory on rank 0 (gather + un-permute + D2H inside the timed region)", "frame_finite_nonzero": frame_ok},
@@ -470,7 +500,10 @@ def main():
                          "issue": {"issue_active_pct": k0.get("issue_active_pct"), "lanes_per_inst": k0.get("threads_per_inst"),
                                    "warp_insts_per_ray": (k0.get("inst_executed") / k0["rays"]) if k0.get("inst_executed") and k0.get("rays") else None,
                                    "source": ncu.get("source")},
-                         "whole_step": {"bytes_per_ray": B_RAY, "achieved": value * 1e6 / n_gpus * B_RAY / 1e9, "frac": value * 1e6 / n_gpus * B_RAY / 1e9 / peak}},
+                         # traversal bytes for the walks, shading bytes for every ray
+                         "whole_step": {"bytes_per_ray": B_RAY, "bytes_per_walk": B_TRAVERSE,
+                                        "achieved": (total_walks_step * B_TRAVERSE + total_rays_step * (B_RAY - B_TRAVERSE)) * args.steps / n_gpus / (ms * 1e-3) / 1e9,
+                                        "frac": (total_walks_step * B_TRAVERSE + total_rays_step * (B_RAY - B_TRAVERSE)) * args.steps / n_gpus / (ms * 1e-3) / 1e9 / peak}},
         }
         if n_gpus == 1 and not args.no_cpu_baseline:
             v, crays, dt, cores, _ = cpu_oracle_run(1, BOUNCES)                 # probe: one sample per pixel

@@ -118,7 +118,8 @@ def test_auto_policy_speculates_in_closed_scenes_only(monkeypatch):
             got = ctx.read(rt.BUF_DIFFUSE_F32, np.uint32).reshape(h, w, 4)
             ref = osc.render_reference(g, frame, w, h, spp=4, max_bounces=4)[2].view(np.uint32)
             assert np.array_equal(got, ref), (kind, frame)
-        assert launches[0] == (2 * (1 + 4 * 3) + 1, 0)    # sequential: a launch pair per walked (sample, bounce) — the primary ray once — and the init
+        # sequential: per wavefront chain a launch pair per walked (sample, bounce) — the primary ray once — and the init
+        assert launches[0][1] == 0 and launches[0][0] % (2 * (1 + 4 * 3) + 1) == 0, launches
         if closed:
             assert launches[-1][1] == 1, launches         # speculation took over
         else:
