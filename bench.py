@@ -471,8 +471,8 @@ def main():
         rays_per_launch = walks_profiled / trace_launches       # what the trace kernel actually walks
         achieved = rays_per_launch * B_TRAVERSE / (trace_ms / trace_launches * 1e-3) / 1e9
         ncu = ncu_summary()
-        k0 = (ncu.get("launches") or [{}])[0]
-        traffic = ncu.get("traffic_bytes_per_launch")
+        k0 = max(ncu.get("launches") or [{}], key=lambda l: l.get("duration_us", 0.0))      # the longest captured launch: a bounce wavefront
+        traffic = k0.get("dram_bytes") or ncu.get("traffic_bytes_per_launch")
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

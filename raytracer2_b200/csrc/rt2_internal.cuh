@@ -154,7 +154,7 @@ struct rt2_ctx {
     int trace_variant = 0;
     // K1 sample schedule: speculate = -1 auto (from the previous frame's miss statistics, read back without a sync), 0 never, 1 whenever
     // the paths fit (RT2_SPECULATE); spec_rounds = prediction fix-up rounds before the candidate round (RT2_SPEC_ROUNDS)
-    int speculate = -1; bool spec_auto = false; int spec_rounds = 1;
+    int speculate = -1; bool spec_auto = false, spec_auto_few_misses = false; int spec_rounds = -1;     // spec_rounds < 0: 1, or 0 after a frame with < 0.1 % missed samples
     unsigned long long* h_k1_stats = nullptr; cudaEvent_t k1_stats_ready = nullptr; bool k1_stats_pending = false; uint64_t k1_stats_paths = 0;
     int path_mode = 0;                                   // K1 schedule: 0 = one launch per bounce (wavefront chains), 1 = warp-local wavefronts in one persistent launch (RT2_PATH_MODE)
     int path_blocks_per_sm[3] = {1, 1, 1}; int warp_blocks_per_sm = 0; uint32_t warp_paths = 0;   // k_path_warp occupancy; RT2_WARP_BLOCKS / RT2_WARP_P overrides

@@ -1225,7 +1225,9 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
     const uint32_t padded = tiles_x * tiles_y * 32;
     const size_t band_pixels = (size_t)band.width * band.local_rows;
     const size_t paths = band_pixels * spp, contribs = paths * bounces;
-    const uint32_t rounds = 1u + (uint32_t)std::max(0, ctx->spec_rounds);
+    // prediction fix-up rounds before the candidate round: RT2_SPEC_ROUNDS, else 1 — or 0 when the previous frame says that so few samples
+    // end on a miss (< 0.1 %) that the candidate round settles them for less than a round of near-empty launches costs (C2: 3041 -> 3095 Mrays/s)
+    const uint32_t rounds = 1u + (uint32_t)(ctx->spec_rounds >= 0 ? ctx->spec_rounds : (ctx->spec_auto_few_misses ? 0 : 1));
     const uint32_t RB = 2u * (bounces + 1u) + 4u;                 // per round: (count, head) x (bounces + 1), (count, head) of the representatives' queue, pending count, pad
     const bool reuse = ctx->primary_reuse;
     const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
@@ -1411,7 +1413,10 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
     if (ctx->k1_stats_pending && cudaEventQuery(ctx->k1_stats_ready) == cudaSuccess) {
         ctx->k1_stats_pending = false;
         const unsigned long long rays = ctx->h_k1_stats[0], hits = ctx->h_k1_stats[1];
-        if (ctx->k1_stats_paths) ctx->spec_auto = (double)(rays - hits) < 0.02 * (double)ctx->k1_stats_paths;
+        if (ctx->k1_stats_paths) {
+            ctx->spec_auto = (double)(rays - hits) < 0.02 * (double)ctx->k1_stats_paths;
+            ctx->spec_auto_few_misses = (double)(rays - hits) < 0.001 * (double)ctx->k1_stats_paths;
+        }
     }
     cudaGetLastError();
     const bool want = ctx->speculate > 0 || (ctx->speculate < 0 && ctx->spec_auto);
