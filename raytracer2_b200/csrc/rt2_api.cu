@@ -295,6 +295,12 @@ int rt2_get_stats(rt2_ctx* ctx, rt2_stats* out) {
         ctx->stats.rays_traced = c[0] + ctx->pending_rays_static;
         ctx->stats.rays_hit = c[1];
         ctx->stats.rays_walked = ctx->stats_walks_counted ? c[2] : ctx->stats.rays_traced;
+        if (ctx->stats_reused_counted && !ctx->stats_walks_counted) {
+            unsigned long long reused = 0;
+            RT2_CUDA(ctx, cudaMemcpyAsync(&reused, ctx->fb.counters + 16, 8, cudaMemcpyDeviceToHost, ctx->stream));
+            RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            ctx->stats.rays_walked = ctx->stats.rays_traced - reused;
+        }
     }
     ctx->stats.trace_ns = ctx->stats.shade_ns = ctx->stats.trace_launches = 0;
     if (!ctx->prof_events.empty()) {

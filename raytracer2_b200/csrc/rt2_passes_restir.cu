@@ -362,6 +362,8 @@ struct DIArgs {
     LightRefs li;
     rt2_packed_di_reservoir* reservoirs; ushort4* diffuse; ushort4* specular; float4* diffuse_f32;
     unsigned long long* stat_rays; unsigned long long* stat_hits;
+    // K9 visibility reuse (k_di_stage_c): trace() calls answered without a walk are counted here (rt2_stats.rays_walked = rays_traced - these)
+    unsigned long long* stat_reused; uint32_t visibility_reuse;
 };
 
 __global__ void __launch_bounds__(128) k_di_fused(DIArgs a) {
@@ -593,13 +595,18 @@ __global__ void __launch_bounds__(128, RT2_DI_BLOCKS) k_di_stage_b(DIWaveArgs w,
     flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
 }
 
-// C (only when initial visibility is on): di_fused_resampling.rgen:42-48, then queue the final-visibility ray
+// C (only when initial visibility is on): di_fused_resampling.rgen:42-48, then queue the final-visibility ray.
+// Visibility reuse: the final-visibility ray (ShadingHelpers.glsl:35, offset 0.01) has the origin and direction of the initial one
+// (bridge :218-222, offset 0.001) — same surface, same light sample — and its interval [0.01, max(0.01, |L| - 0.02)] lies inside
+// [0.001, max(0.001, |L| - 0.002)] unless |L| < 0.012.  A triangle's t does not depend on the interval, so an initial ray that came
+// back without a hit proves the final one has none either: it is answered "visible" here, counted as the trace() call it is (and in
+// stat_reused as a walk saved), and only the degenerate short rays are queued.  Same reservoirs and images, bit for bit.
 __global__ void __launch_bounds__(128) k_di_stage_c(DIWaveArgs w, uint32_t* queue_out, uint32_t* count_out) {
     const DIArgs& a = w.di;
     uint32_t lx, ly;
     const bool inside = tile_pixel(blockIdx.x * blockDim.x + threadIdx.x, a.width, a.band, &lx, &ly);
     bool traced = false;
-    uint32_t slot = 0, hits = 0;
+    uint32_t slot = 0, hits = 0, reused = 0;
     if (inside) {
         slot = ly * a.width + lx;
         const rt2_gconst& g = *a.g;
@@ -607,19 +614,30 @@ __global__ void __launch_bounds__(128) k_di_stage_c(DIWaveArgs w, uint32_t* queu
         uint32_t px, py; launch_to_pixel(g, lx, ly, &px, &py);
         DIReservoir reservoir; LightSample light_sample; uint32_t flags, rng_index;
         di_state_load(w, slot, &reservoir, &light_sample, &rng_index, &flags);
+        bool initial_clear = false;                       // the initial-visibility ray was traced and found nothing
         if (flags & DIW_RAY_PENDING) {
             if (__float_as_uint(w.st_hit[slot].w) != 0xFFFFFFFFu) { hits++; di_store_visibility(reservoir, v3(0.f, 0.f, 0.f), true); }
+            else initial_clear = true;
         }
         flags = 0u;
         if (di_valid(reservoir) && !(light_sample.solid_angle_pdf <= 0) && di.shading_params.enable_final_visibility == 1u) {
             const Surface surface = gbuffer_surface(a.gb, a.width, (int)px, (int)py, g.view);
-            write_visibility_ray(w, slot, surface, light_sample.position, 0.01f);
-            traced = true; flags |= DIW_RAY_PENDING;
+            const float len = length3(light_sample.position - surface.world_pos);
+            const bool inside_initial = fmaxf(0.01f, len - 0.01f * 2) <= fmaxf(0.001f, len - 0.001f * 2);     // the two tmax of setupVisibilityRay
+            if (a.visibility_reuse && initial_clear && inside_initial) reused = 1u;          // visible: stage D reads "no ray pending" as that
+            else {
+                write_visibility_ray(w, slot, surface, light_sample.position, 0.01f);
+                traced = true; flags |= DIW_RAY_PENDING;
+            }
         }
         di_state_store(w, slot, reservoir, light_sample, rng_index, flags);
     }
     warp_append(traced, slot, queue_out, count_out);
-    flush_ray_stats(a.stat_rays, a.stat_hits, 0u, hits);
+    flush_ray_stats(a.stat_rays, a.stat_hits, reused, hits);
+    if (a.visibility_reuse) {
+        const uint32_t am = __activemask(), wr = __reduce_add_sync(am, reused);
+        if (wr && (threadIdx.x & 31u) == (uint32_t)(__ffs(am) - 1)) atomicAdd(a.stat_reused, (unsigned long long)wr);
+    }
 }
 
 // D: ShadeSurfaceWithLightSample with the traced final visibility, DemodulateSpecular, stores (di_fused_resampling.rgen:50-92)
@@ -1388,11 +1406,12 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     int rc = restir_ensure_resources(ctx); if (rc) return rc;
     FrameBuffers& f = ctx->fb;
     // counters: [0..1] rays, [2..3] hits
-    if (f.counter_capacity < 16) {
+    // ... [4..15] the ray queues' (count, head) pairs, [16..17] u64 trace() calls answered without a walk (K9 visibility reuse)
+    if (f.counter_capacity < 20) {
         if (f.counters) { RT2_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(f.counters); f.counters = nullptr; }
-        RT2_CUDA(ctx, cudaMalloc((void**)&f.counters, 16 * 4)); f.counter_capacity = 16;
+        RT2_CUDA(ctx, cudaMalloc((void**)&f.counters, 20 * 4)); f.counter_capacity = 20;
     }
-    if (ph & 1u) RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, 64, ctx->stream));
+    if (ph & 1u) RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, 80, ctx->stream));
     unsigned long long* stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
     unsigned long long* stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
     const uint32_t cur = frame & 1u;                   // ping-pong, src/light_passes.rs:565-577
@@ -1506,6 +1525,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
         da.gb = gbrefs; da.li = lrefs;
         da.reservoirs = f.di_reservoirs; da.diffuse = f.diffuse_f16; da.specular = f.specular_f16; da.diffuse_f32 = f.diffuse_f32;
         da.stat_rays = stat_rays; da.stat_hits = stat_hits;
+        da.stat_reused = reinterpret_cast<unsigned long long*>(f.counters + 16); da.visibility_reuse = ctx->visibility_reuse ? 1u : 0u;
         if (ctx->gi_megakernels || g.restir_di.initial_sampling_params.num_primary_brdf_samples > 1u) {
             k_di_fused<<<blocks, 128, 0, ctx->stream>>>(da); launches++;
         } else {
@@ -1592,6 +1612,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
     ctx->stats.wavefront_iterations = 1;
     ctx->stats_from_counters = true;
     ctx->stats_walks_counted = false;
+    ctx->stats_reused_counted = true;
     if (ph & 1u) ctx->pending_rays_static = static_rays;
     return RT2_OK;
 }

@@ -978,7 +978,7 @@ static int ensure_counters(rt2_ctx* ctx, uint32_t iterations) {
         f.counter_capacity = need;
     }
     RT2_CUDA(ctx, cudaMemsetAsync(f.counters, 0, need * 4, ctx->stream));
-    ctx->stats_walks_counted = false;
+    ctx->stats_walks_counted = false; ctx->stats_reused_counted = false;
     return RT2_OK;
 }
 
@@ -1472,6 +1472,7 @@ int render_init(rt2_ctx* ctx) {
     if (const char* e = getenv("RT2_SPEC_ROUNDS")) { int v = atoi(e); if (v >= 0 && v <= 16) ctx->spec_rounds = v; }
     if (const char* e = getenv("RT2_PATH_MODE")) ctx->path_mode = atoi(e);
     if (const char* e = getenv("RT2_PRIMARY_REUSE")) ctx->primary_reuse = atoi(e) != 0;
+    if (const char* e = getenv("RT2_VISIBILITY_REUSE")) ctx->visibility_reuse = atoi(e) != 0;
     if (const char* e = getenv("RT2_WARP_P")) { int v = atoi(e); if (v >= 32 && v <= 4096) ctx->warp_paths = (uint32_t)v; }
     if (const char* e = getenv("RT2_WARP_BLOCKS")) { int v = atoi(e); if (v >= 1 && v <= 16) ctx->warp_blocks_per_sm = v; }
     int p0 = 0, p1 = 0, p2 = 0, b3 = 0;

@@ -74,3 +74,38 @@ def test_primary_hit_reuse_under_row_bands(monkeypatch):
             assert np.array_equal(part[0][rows].view(np.uint32), whole[0][rows].view(np.uint32)), (rank, name)
         rays += part[2]
     assert rays == whole[2]
+
+
+@pytest.mark.parametrize("kind,scale,sky", [(rt.SCENE_MANYLIGHT, 0.1, 0), (rt.SCENE_CORNELL, 1.0, 0), (rt.SCENE_HALL, 0.125, 0)])
+def test_k9_final_visibility_is_answered_by_a_clear_initial_ray(monkeypatch, kind, scale, sky):
+    """K9 with both visibility tests on (di_fused_resampling.rgen:40-48, ShadingHelpers.glsl:33-38): the final ray has the initial ray's origin
+    and direction and a t-interval inside the initial one, so a clear initial ray answers it (k_di_stage_c).  Reservoirs, both lighting images
+    and the trace() count equal the every-ray-walked run's and the oracle's; rays_walked drops by the final rays that were not walked."""
+    w, h, frame = 192, 108, 2
+    out = {}
+    for reuse in (0, 1):
+        monkeypatch.setenv("RT2_VISIBILITY_REUSE", str(reuse))
+        sc = rt.Scene(kind, scale, 32, 0)
+        ctx = rt.Renderer(0)
+        rt.Model.from_scene(ctx, sc)
+        g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+        g.refrence_mode = 0; g.enable_restir_gi = 0; g.enable_restir_di = 1
+        isp = g.restir_di.initial_sampling_params
+        isp.num_primary_local_light_samples = 4; isp.num_primary_brdf_samples = 1; isp.enable_initial_visibility = 1
+        g.restir_di.shading_params.enable_final_visibility = 1
+        lp = rt.LightPasses(ctx, w, h)
+        rt.PrepareLightsTasks(ctx).execute()
+        rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+        lp.update_uniform(g)
+        lp.execute(frame)
+        st = ctx.stats()
+        out[reuse] = (ctx.read(rt.BUF_DI_RESERVOIRS, np.uint32).copy(), ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).copy(), ctx.read(rt.BUF_SPECULAR_F16, np.uint16).copy(),
+                      st.rays_traced, st.rays_hit, st.rays_walked)
+        ctx.close()
+    off, on = out[0], out[1]
+    for k in range(3):
+        assert np.array_equal(on[k], off[k])
+    assert on[3] == off[3] and on[4] == off[4]
+    assert off[5] == off[3], "without reuse every trace() is a walk"
+    valid = int((on[0].reshape(-1, 6)[:, 0] != 0).sum())           # reservoirs that kept a light: their initial ray was clear
+    assert 0.5 * valid <= on[3] - on[5] <= valid and valid > 0, (on[3], on[5], valid)
