@@ -251,7 +251,8 @@ typedef struct rt2_stats {
     uint64_t sample_schedule;  /* K1: 0 = one launch pair per (sample, bounce); 1 = speculative sample parallelism (every sample its own path) */
     uint64_t rays_walked;      /* BVH walks behind rays_traced.  K1's primary ray has no jitter (refrence.rgen:26, GBufferHelpers.glsl:12-27), so the
                                   spp samples of a pixel issue the same trace() spp times: it is walked once and its hit record consumed spp
-                                  times (RT2_PRIMARY_REUSE=0 walks every one).  Equal to rays_traced for every other pass. */
+                                  times (RT2_PRIMARY_REUSE=0 walks every one).  K9 with both visibility tests on: a clear initial-visibility ray answers the
+                                  final one (RT2_VISIBILITY_REUSE=0 walks both).  Equal to rays_traced everywhere else. */
 } rt2_stats;
 
 typedef struct rt2_ctx rt2_ctx;
