@@ -147,6 +147,7 @@ struct rt2_ctx {
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
     bool stats_walks_counted = false;   // ... and fb.counters[4..5] holds the walks (K1); otherwise rays_walked = rays_traced
     bool stats_reused_counted = false;  // ... and fb.counters[16..17] holds trace() calls answered without a walk (ReSTIR frames): rays_walked = rays_traced - that
+    bool any_hit = true;                // visibility-ray batches of the ReSTIR passes end a walk at its first hit (RT2_ANY_HIT=0: closest hit always)
     bool visibility_reuse = true;       // K9: a clear initial-visibility ray answers the final one (RT2_VISIBILITY_REUSE=0: both are walked)
     bool primary_reuse = true;          // K1: walk a pixel's primary ray once for all its samples (RT2_PRIMARY_REUSE=0: every sample walks its own)
     uint64_t pending_rays_static = 0;   // rays known on the host (primary probe)

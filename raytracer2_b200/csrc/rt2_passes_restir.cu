@@ -13,7 +13,7 @@ namespace rt2 {
 
 int restir_ensure_resources(rt2_ctx* ctx);
 int lights_ensure_resources(rt2_ctx* ctx);
-int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays);
+int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays, bool any_hit = false);
 
 // interleaved row bands (the same rule as rt2_render.cu's Band): the passes below are per-pixel independent, every buffer
 // stays full-frame and addressed by absolute pixel, a rank just visits its own rows
@@ -1542,10 +1542,10 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
                 launches++;
             }
             k_di_stage_b<false><<<blocks, 128, 0, ctx->stream>>>(dw, f.queue1, f.counters + 10); launches++;
-            if (initial_vis || final_vis) { if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 10, f.counters + 11, stat_rays))) return rc; launches++; }
+            if (initial_vis || final_vis) { if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 10, f.counters + 11, stat_rays, true))) return rc; launches++; }
             if (initial_vis) {
                 k_di_stage_c<<<blocks, 128, 0, ctx->stream>>>(dw, f.queue0, f.counters + 12); launches++;
-                if (final_vis) { if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 12, f.counters + 13, stat_rays))) return rc; launches++; }
+                if (final_vis) { if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 12, f.counters + 13, stat_rays, true))) return rc; launches++; }
             }
             k_di_stage_d<<<blocks, 128, 0, ctx->stream>>>(dw, final_vis ? 1u : 0u); launches++;
         }
@@ -1582,7 +1582,7 @@ int render_restir(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) {
                 if ((rc = trace_queue_generic(ctx, f.queue1, f.counters + 6, f.counters + 7, stat_rays))) return rc;
                 k_di_stage_b<true><<<blocks, 128, 0, ctx->stream>>>(dw, f.queue0, f.counters + 14); launches += 3;
                 if (g.restir_di.shading_params.enable_final_visibility == 1u) {
-                    if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 14, f.counters + 15, stat_rays))) return rc;
+                    if ((rc = trace_queue_generic(ctx, f.queue0, f.counters + 14, f.counters + 15, stat_rays, true))) return rc;
                     launches++;
                 }
                 k_shade_secondary_stage_d<<<blocks, 128, 0, ctx->stream>>>(dw, gi); launches++;

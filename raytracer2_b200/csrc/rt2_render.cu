@@ -148,7 +148,9 @@ __device__ __forceinline__ float4 ld16f_stream(const void* p) {
 // register instead of a global atomic.
 // FLAT (with INSTANCED = false): one tree over every (instance, triangle) pair walked with the world-space ray; the lane re-expresses
 // its ray in an instance's object space only when a leaf of another instance comes up (rt2_bvh.cuh, flat_closest_hit).
-template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED, bool GENERIC, bool LOCALQ = false, bool FLAT = false>
+// ANYHIT (GENERIC visibility rays): the caller reads only "hit or not" (p.geometryIndex == ~0u after trace(), bridge :218-231,
+// ShadingHelpers.glsl:35-37), so the first triangle hit inside [tmin, tmax] ends the walk.  The record then names some hit, not the closest.
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED, bool GENERIC, bool LOCALQ = false, bool FLAT = false, bool ANYHIT = false>
 __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a, const uint32_t* lq = nullptr, uint32_t lcount = 0u) {
     const uint32_t count = LOCALQ ? lcount : *a.count;
     const uint32_t* queue = LOCALQ ? lq : a.queue;      // no __restrict__: a warp-local queue was written earlier in this kernel
@@ -286,6 +288,7 @@ __device__ __forceinline__ void trace_dyn_body(const TraceArgs& a, const uint32_
                             if (hit_closer(t, hi, geom, prim, best)) {
                                 best.t = t; best.u = u; best.v = v; best.inst = hi; best.geom = geom; best.prim = prim;
                                 tri_slot = s;
+                                if (ANYHIT) { tgroup.y = 0u; ngroup = make_uint2(0u, 0u); sp = 0; inst_sp = 0; }      // nothing left to visit: the ray retires below
                             }
                         }
                     }
@@ -318,10 +321,10 @@ template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool INSTANCED = fa
 __global__ void __launch_bounds__(128) k_trace_dyn(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, INSTANCED, GENERIC>(a); }
 // The two-level walk at 6 blocks/SM (80 registers; ptxas picks 96 = 5 blocks on its own): C5 619 -> 659 Mrays/s.  A separate
 // entry point because __launch_bounds__(128, n) on the single-level kernels changes their code (C2 -0.4 % at n = 7).
-template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false>
-__global__ void __launch_bounds__(128, 6) k_trace_dyn_tlas(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, true, GENERIC>(a); }
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false, bool ANYHIT = false>
+__global__ void __launch_bounds__(128, 6) k_trace_dyn_tlas(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, true, GENERIC, false, false, ANYHIT>(a); }
 // flattened instancing: single-level walk over the (instance, triangle) tree
-template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false>
+template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = false, bool ANYHIT = false>
 #ifndef RT2_FLAT_POSTPONE
 #define RT2_FLAT_POSTPONE 30   /* 20 / 25 / 30: 1143 / 1152 (with refill 6, check 6) / 1154 Mrays/s on C5 */
 #endif
@@ -335,7 +338,7 @@ template <int POSTPONE_PCT, int REFILL_MIN, int CHECK_EVERY, bool GENERIC = fals
 #ifndef RT2_FLAT_MIN_BLOCKS
 #define RT2_FLAT_MIN_BLOCKS 7   /* 72 registers, 28 warps per SM: the flat walk is latency-bound (L2 hit 72-80 %, DRAM 2 %); 5 / 6 / 7 / 8 blocks: 1021 / 1086 / 1144 / 1096 Mrays/s on C5 */
 #endif
-__global__ void __launch_bounds__(128, RT2_FLAT_MIN_BLOCKS) k_trace_dyn_flat(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, false, GENERIC, false, true>(a); }
+__global__ void __launch_bounds__(128, RT2_FLAT_MIN_BLOCKS) k_trace_dyn_flat(TraceArgs a) { trace_dyn_body<POSTPONE_PCT, REFILL_MIN, CHECK_EVERY, false, GENERIC, false, true, ANYHIT>(a); }
 
 // The ray-queue kernel of the ReSTIR passes (GENERIC rays: origin | tmin, direction | tmax per slot) on single-level scenes: an entry
 // point of its own so that its register cap and refill cadence can differ from K1's (80 registers / 36 % occupancy without the cap)
@@ -351,8 +354,9 @@ __global__ void __launch_bounds__(128, RT2_FLAT_MIN_BLOCKS) k_trace_dyn_flat(Tra
 #ifndef RT2_GENERIC_MIN_BLOCKS
 #define RT2_GENERIC_MIN_BLOCKS 7
 #endif
+template <bool ANYHIT>
 __global__ void __launch_bounds__(128, RT2_GENERIC_MIN_BLOCKS) k_trace_queue(TraceArgs a) {
-    trace_dyn_body<RT2_GENERIC_POSTPONE, RT2_GENERIC_REFILL, RT2_GENERIC_CHECK, false, true>(a);
+    trace_dyn_body<RT2_GENERIC_POSTPONE, RT2_GENERIC_REFILL, RT2_GENERIC_CHECK, false, true, false, false, ANYHIT>(a);
 }
 
 // refrence.rgen:28-46 for the path in `slot` whose ray just came back (hit record in st_hit): emission / throughput update,
@@ -1441,17 +1445,25 @@ int render_reference(rt2_ctx* ctx, uint32_t frame, const rt2_launch_params& lp) 
 
 // Traces a queue of GENERIC rays (st_ray0 = o|tmin, st_ray1 = d|tmax, slot = pixel-linear index) into st_hit / st_hit_inst:
 // the ReSTIR passes hand their incoherent rays to the same postponing/refilling kernel the path tracer uses.
-int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays) {
+// any_hit: the rays are visibility tests — the consumer reads "hit or not" only — so a walk ends at its first hit (RT2_ANY_HIT=0: closest hit always)
+int trace_queue_generic(rt2_ctx* ctx, const uint32_t* queue, const uint32_t* count, uint32_t* head, unsigned long long* stat_rays, bool any_hit) {
     const DeviceScene& s = ctx->scene;
     TraceArgs t = make_trace_args(ctx);
     t.queue = queue; t.count = count; t.head = head; t.stat_rays = stat_rays;
+    any_hit = any_hit && ctx->any_hit;
     if (t.flat_nodes) {
-        k_trace_dyn_flat<RT2_FLAT_PARAMS, true><<<ctx->trace_blocks_per_sm[3] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        const int blocks = ctx->trace_blocks_per_sm[3] * ctx->num_sms;
+        if (any_hit) k_trace_dyn_flat<RT2_FLAT_PARAMS, true, true><<<blocks, 128, 0, ctx->stream>>>(t);
+        else k_trace_dyn_flat<RT2_FLAT_PARAMS, true><<<blocks, 128, 0, ctx->stream>>>(t);
     } else if (s.num_instances) {
-        if (unified_walk_fits(s)) k_trace_dyn_tlas<20, 4, 8, true><<<ctx->trace_blocks_per_sm[1] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
-        else k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        const int blocks = ctx->trace_blocks_per_sm[1] * ctx->num_sms;
+        if (!unified_walk_fits(s)) k_trace<true, true><<<ctx->trace_blocks_per_sm[2] * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        else if (any_hit) k_trace_dyn_tlas<20, 4, 8, true, true><<<blocks, 128, 0, ctx->stream>>>(t);
+        else k_trace_dyn_tlas<20, 4, 8, true><<<blocks, 128, 0, ctx->stream>>>(t);
     } else {
-        k_trace_queue<<<ctx->trace_queue_blocks_per_sm * ctx->num_sms, 128, 0, ctx->stream>>>(t);
+        const int blocks = ctx->trace_queue_blocks_per_sm * ctx->num_sms;
+        if (any_hit) k_trace_queue<true><<<blocks, 128, 0, ctx->stream>>>(t);
+        else k_trace_queue<false><<<blocks, 128, 0, ctx->stream>>>(t);
     }
     RT2_CUDA(ctx, cudaGetLastError());
     return RT2_OK;
@@ -1473,6 +1485,7 @@ int render_init(rt2_ctx* ctx) {
     if (const char* e = getenv("RT2_PATH_MODE")) ctx->path_mode = atoi(e);
     if (const char* e = getenv("RT2_PRIMARY_REUSE")) ctx->primary_reuse = atoi(e) != 0;
     if (const char* e = getenv("RT2_VISIBILITY_REUSE")) ctx->visibility_reuse = atoi(e) != 0;
+    if (const char* e = getenv("RT2_ANY_HIT")) ctx->any_hit = atoi(e) != 0;
     if (const char* e = getenv("RT2_WARP_P")) { int v = atoi(e); if (v >= 32 && v <= 4096) ctx->warp_paths = (uint32_t)v; }
     if (const char* e = getenv("RT2_WARP_BLOCKS")) { int v = atoi(e); if (v >= 1 && v <= 16) ctx->warp_blocks_per_sm = v; }
     int p0 = 0, p1 = 0, p2 = 0, b3 = 0;
@@ -1482,7 +1495,7 @@ int render_init(rt2_ctx* ctx) {
     RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, k_trace_dyn_flat<RT2_FLAT_PARAMS>, 128, 0));
     ctx->path_blocks_per_sm[0] = std::max(p0, 1); ctx->path_blocks_per_sm[1] = std::max(p1, 1); ctx->path_blocks_per_sm[2] = std::max(p2, 1);
     ctx->trace_blocks_per_sm[3] = std::max(b3, 1);
-    { int bq = 0; RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bq, k_trace_queue, 128, 0)); ctx->trace_queue_blocks_per_sm = std::max(bq, 1); }
+    { int bq = 0; RT2_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bq, k_trace_queue<false>, 128, 0)); ctx->trace_queue_blocks_per_sm = std::max(bq, 1); }
     if (const char* e = getenv("RT2_USE_FLAT")) ctx->use_flat = atoi(e) != 0;
     ctx->trace_blocks_per_sm[0] = std::max(b0, 1); ctx->trace_blocks_per_sm[1] = std::max(b1, 1); ctx->trace_blocks_per_sm[2] = std::max(b2, 1);
     return RT2_OK;

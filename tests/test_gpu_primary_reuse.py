@@ -109,3 +109,41 @@ def test_k9_final_visibility_is_answered_by_a_clear_initial_ray(monkeypatch, kin
     assert off[5] == off[3], "without reuse every trace() is a walk"
     valid = int((on[0].reshape(-1, 6)[:, 0] != 0).sum())           # reservoirs that kept a light: their initial ray was clear
     assert 0.5 * valid <= on[3] - on[5] <= valid and valid > 0, (on[3], on[5], valid)
+
+
+@pytest.mark.parametrize("kind,scale", [(rt.SCENE_MANYLIGHT, 0.1), (rt.SCENE_INSTANCED, 0.05), (rt.SCENE_HALL, 0.125)])
+def test_visibility_ray_batches_end_at_their_first_hit(monkeypatch, kind, scale):
+    """The visibility-ray batches of K9 / K5 (consumers read `p.geometryIndex == ~0u` only: bridge :218-231, ShadingHelpers.glsl:35-37) end a walk at
+    its first hit (trace_dyn_body<ANYHIT>).  Nothing the passes write may depend on it: RT2_ANY_HIT=0 (closest hit always) gives the same reservoirs,
+    images, ray and hit counts — with the visibility reuse off, so that every visibility ray is really walked."""
+    w, h = 192, 108
+    monkeypatch.setenv("RT2_VISIBILITY_REUSE", "0")
+    out = {}
+    for any_hit in (0, 1):
+        monkeypatch.setenv("RT2_ANY_HIT", str(any_hit))
+        sc = rt.Scene(kind, scale, 32, 0)
+        ctx = rt.Renderer(0)
+        rt.Model.from_scene(ctx, sc)
+        d = sc.desc.contents
+        g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights, env_size=(d.sky_width, d.sky_height))
+        g.refrence_mode = 0; g.enable_restir_gi = 1; g.enable_restir_di = 1; g.environment = 1 if d.sky_width else 0
+        isp = g.restir_di.initial_sampling_params
+        isp.num_primary_local_light_samples = 4; isp.num_primary_brdf_samples = 1; isp.enable_initial_visibility = 1
+        g.restir_di.shading_params.enable_final_visibility = 1
+        lp = rt.LightPasses(ctx, w, h)
+        rt.PrepareLightsTasks(ctx).execute()
+        rt.GenerateMipsPass(ctx, rt.GenerateMipsPass.LOCAL_LIGHTS).execute_mip_generation()
+        frames = []
+        for frame in (1, 2):
+            lp.update_uniform(g)
+            lp.execute(frame)
+            st = ctx.stats()
+            frames.append((ctx.read(rt.BUF_DI_RESERVOIRS, np.uint32).copy(), ctx.read(rt.BUF_GI_RESERVOIRS, np.uint32).copy(), ctx.read(rt.BUF_DIFFUSE_F16, np.uint16).copy(),
+                           ctx.read(rt.BUF_SPECULAR_F16, np.uint16).copy(), st.rays_traced, st.rays_hit))
+        out[any_hit] = frames
+        ctx.close()
+    for a, b in zip(out[0], out[1]):
+        for k in range(4):
+            assert np.array_equal(a[k], b[k]), k
+        assert a[4] == b[4] and a[5] == b[5]
+        assert a[5] > 0
