@@ -479,8 +479,17 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_k1_shade(ShadeArg
         const uint32_t at = block_append_index(alive, a.count_out, s_off, parity);
         if (alive) a.queue_out[at] = slot;
     }
-    warp_flush_counter(a.stat_hits, hits);
-    warp_flush_counter(a.stat_rays, seen);
+    // one atomic pair per block (a launch over 262 k pixels has 8 k warps: same-address atomics serialise in the L2)
+    __shared__ uint32_t s_cnt[2][8];
+    const uint32_t wh = __reduce_add_sync(0xFFFFFFFFu, hits), ws = __reduce_add_sync(0xFFFFFFFFu, seen);
+    if ((threadIdx.x & 31u) == 0u) { s_cnt[0][threadIdx.x >> 5] = wh; s_cnt[1][threadIdx.x >> 5] = ws; }
+    __syncthreads();
+    if (threadIdx.x < 2u) {
+        uint32_t sum = 0;
+        for (uint32_t w = 0; w < (blockDim.x >> 5); w++) sum += s_cnt[threadIdx.x][w];
+        unsigned long long* dst = threadIdx.x == 0u ? a.stat_hits : a.stat_rays;
+        if (sum && dst) atomicAdd(dst, (unsigned long long)sum);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -582,7 +591,7 @@ __device__ __forceinline__ void path_warp_body(const TraceArgs& t, const ShadeAr
     }
     if (lane == 0) { if (rays) atomicAdd(t.stat_rays, (unsigned long long)rays); }     // walks
     warp_flush_counter(a.stat_hits, hits);
-    warp_flush_counter(a.stat_rays, seen);                                                // hit records consumed = the shader's trace() calls
+    if (a.stat_rays) warp_flush_counter(a.stat_rays, seen);                               // hit records consumed = the shader's trace() calls
 }
 
 template <bool INSTANCED, bool FLAT = false>
@@ -1048,7 +1057,7 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
     const uint32_t bounces = lp.max_bounces ? lp.max_bounces : 5u; // refrence.rgen:16
     if (spp > 65535u || bounces > 65535u || (uint64_t)spp * bounces > (1u << 22)) return fail(ctx, RT2_E_INVALID, "spp x bounces too large");
     // a pixel is a chain of spp x bounces dependent rays; with primary-hit reuse only the first sample walks its primary ray
-    const bool reuse = ctx->primary_reuse;
+    const bool reuse = ctx->primary_reuse && spp > 1u;
     const uint32_t iterations = reuse ? 1u + spp * (bounces - 1u) : spp * bounces;
     if ((rc = ensure_counters(ctx, iterations))) return rc;
     const Band band = make_band(f.width, f.height, lp);
@@ -1061,11 +1070,12 @@ static int render_reference_seq(rt2_ctx* ctx, uint32_t frame, const rt2_launch_p
     a.st_ray0 = f.st_ray0; a.st_ray1 = f.st_ray1; a.st_acc = f.st_acc; a.st_misc = f.st_misc; a.st_hit = f.st_hit; a.st_hit_inst = f.st_hit_inst;
     a.diffuse_f16 = f.diffuse_f16; a.specular_f16 = f.specular_f16; a.diffuse_f32 = f.diffuse_f32;
     a.stat_hits = reinterpret_cast<unsigned long long*>(f.counters + 2);
-    a.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);
+    // with reuse the shade steps count the trace() calls (hit records consumed) and the trace kernels the walks; without it they are the same number
+    a.stat_rays = reuse ? reinterpret_cast<unsigned long long*>(f.counters) : nullptr;
     a.st_hit0 = f.st_hit0; a.st_hit_inst0 = f.st_hit_inst0; a.primary_reuse = reuse ? 1u : 0u;
     TraceArgs t = make_trace_args(ctx);
-    t.stat_rays = reinterpret_cast<unsigned long long*>(f.counters + 4);
-    ctx->stats_walks_counted = true;
+    t.stat_rays = reinterpret_cast<unsigned long long*>(f.counters + (reuse ? 4 : 0));
+    ctx->stats_walks_counted = reuse;
     if (padded) {
         const int shade_blocks_full = ctx->num_sms * 8;
         const bool profile = (lp.flags & RT2_LAUNCH_PROFILE) != 0u;
