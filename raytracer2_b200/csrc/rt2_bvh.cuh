@@ -215,9 +215,10 @@ RT2_HD void cwbvh_node_step(const Node8* __restrict__ nodes, const RayPrep& rp, 
 
 // Generic CWBVH stack traversal.  `leaf(slot)` is called for every leaf primitive whose (padded)
 // box the ray touches within [tmin, min(tmax, *t_limit)]; it may lower *t_limit (closest hit).
+// `stop` (optional): the walk ends as soon as *stop is set by `leaf` — visibility tests that only ask "hit or not" (any-hit).
 template <class LeafFn>
 RT2_HD void cwbvh_traverse(const Node8* __restrict__ nodes, const TraceRay& ray, const float* t_limit, LeafFn&& leaf,
-                           uint32_t* node_visits = nullptr) {
+                           uint32_t* node_visits = nullptr, const bool* stop = nullptr) {
     const RayPrep rp = make_ray_prep(ray.o, ray.d);
     uint2 stack[RT2_STACK_SIZE];
     int sp = 0;
@@ -236,6 +237,7 @@ RT2_HD void cwbvh_traverse(const Node8* __restrict__ nodes, const TraceRay& ray,
             const uint32_t ti = rt2_fhs(tgroup.y);
             tgroup.y &= ~(1u << ti);
             leaf(tgroup.x + ti);
+            if (stop && *stop) return;
         }
         if (ngroup.y <= 0x00FFFFFFu) {
             if (sp == 0) break;
@@ -246,9 +248,11 @@ RT2_HD void cwbvh_traverse(const Node8* __restrict__ nodes, const TraceRay& ray,
 
 // Closest hit over one triangle CWBVH.  `inst` is written into the hit record (0 for the
 // single-level case).  Caller initialises best.t = +inf and ids = ~0u.
+// `any` (here and in the two functions below): stop at the first accepted hit — `best` then names some hit, not the closest.
 RT2_HD void cwbvh_closest_hit(const Node8* __restrict__ nodes, const TriPos* __restrict__ tris,
-                              const TraceRay& ray, uint32_t inst, Hit& best, uint32_t* slot_out, uint32_t* node_visits = nullptr) {
+                              const TraceRay& ray, uint32_t inst, Hit& best, uint32_t* slot_out, uint32_t* node_visits = nullptr, bool any = false) {
     const RayShear sh = make_shear(ray.d);
+    bool found = false;
     cwbvh_traverse(nodes, ray, &best.t, [&](uint32_t slot) {
         const TriPos* tp = tris + slot;
         const float4 a = ld16f(&tp->v0), b = ld16f(&tp->v1), c = ld16f(&tp->v2);
@@ -258,9 +262,10 @@ RT2_HD void cwbvh_closest_hit(const Node8* __restrict__ nodes, const TriPos* __r
             if (hit_closer(t, inst, geom, prim, best)) {
                 best.t = t; best.u = u; best.v = v; best.inst = inst; best.geom = geom; best.prim = prim;
                 if (slot_out) *slot_out = slot;
+                found = true;
             }
         }
-    }, node_visits);
+    }, node_visits, any ? &found : nullptr);
 }
 
 // Instance record of the TLAS (A2 extension): world->object 3x4, object->world 3x4. 96 bytes.
@@ -271,7 +276,8 @@ struct __align__(16) InstanceRec { float inv[12]; float fwd[12]; };
 RT2_HD void tlas_closest_hit(const Node8* __restrict__ tlas_nodes, const uint32_t* __restrict__ tlas_slot_to_inst,
                              const InstanceRec* __restrict__ instances, const Node8* __restrict__ blas_nodes,
                              const TriPos* __restrict__ tris, const TraceRay& ray, Hit& best, uint32_t* slot_out,
-                             uint32_t* node_visits = nullptr) {
+                             uint32_t* node_visits = nullptr, bool any = false) {
+    bool found = false;
     cwbvh_traverse(tlas_nodes, ray, &best.t, [&](uint32_t slot) {
         const uint32_t inst = tlas_slot_to_inst[slot];
         const InstanceRec* ir = instances + inst;
@@ -280,8 +286,9 @@ RT2_HD void tlas_closest_hit(const Node8* __restrict__ tlas_nodes, const uint32_
         for (int k = 0; k < 3; k++) { float4 r = ld16f(ir->inv + 4 * k); m[4 * k] = r.x; m[4 * k + 1] = r.y; m[4 * k + 2] = r.z; m[4 * k + 3] = r.w; }
         TraceRay lr;
         lr.o = xform_point(m, ray.o); lr.d = xform_vector(m, ray.d); lr.tmin = ray.tmin; lr.tmax = ray.tmax;
-        cwbvh_closest_hit(blas_nodes, tris, lr, inst, best, slot_out, node_visits);
-    }, node_visits);
+        cwbvh_closest_hit(blas_nodes, tris, lr, inst, best, slot_out, node_visits, any);
+        if (any && best.geom != 0xFFFFFFFFu) found = true;
+    }, node_visits, any ? &found : nullptr);
 }
 
 // Flattened instancing (B200: 180 GB of HBM makes the memory a non-issue): ONE CWBVH over the world-space boxes of every
@@ -293,10 +300,12 @@ RT2_HD void tlas_closest_hit(const Node8* __restrict__ tlas_nodes, const uint32_
 struct FlatLeaf { uint32_t inst, tri; };      // tri = BLAS leaf slot (index into the object-space TriPos array)
 
 RT2_HD void flat_closest_hit(const Node8* __restrict__ nodes, const FlatLeaf* __restrict__ leaves, const InstanceRec* __restrict__ instances,
-                             const TriPos* __restrict__ tris, const TraceRay& ray, Hit& best, uint32_t* slot_out, uint32_t* node_visits = nullptr) {
+                             const TriPos* __restrict__ tris, const TraceRay& ray, Hit& best, uint32_t* slot_out, uint32_t* node_visits = nullptr,
+                             bool any = false) {
     uint32_t cur = 0xFFFFFFFFu;
     V3 oo = ray.o;
     RayShear sh = make_shear(ray.d);
+    bool found = false;
     cwbvh_traverse(nodes, ray, &best.t, [&](uint32_t slot) {
         const FlatLeaf lf = leaves[slot];
         if (lf.inst != cur) {
@@ -316,9 +325,10 @@ RT2_HD void flat_closest_hit(const Node8* __restrict__ nodes, const FlatLeaf* __
             if (hit_closer(t, cur, geom, prim, best)) {
                 best.t = t; best.u = u; best.v = v; best.inst = cur; best.geom = geom; best.prim = prim;
                 if (slot_out) *slot_out = lf.tri;
+                found = true;
             }
         }
-    }, node_visits);
+    }, node_visits, any ? &found : nullptr);
 }
 
 }  // namespace rt2

@@ -132,7 +132,7 @@ __device__ __forceinline__ bool visibility_ray_miss(const SceneRefs& sc, const S
     const V3 L = sample_position - s.world_pos;                        // setupVisibilityRay, bridge :191-218
     const float tmax = fmaxf(offset, length3(L) - offset * 2);
     uint32_t slot;
-    const Hit h = trace_closest(sc, s.world_pos, normalize3(L), offset, tmax, &slot);
+    const Hit h = trace_closest(sc, s.world_pos, normalize3(L), offset, tmax, &slot, true);       // "hit or not" is all the shader reads (bridge :218-231)
     (*rays)++;
     return h.geom == 0xFFFFFFFFu;
 }

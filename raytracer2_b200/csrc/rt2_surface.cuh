@@ -16,6 +16,7 @@ struct SceneRefs {
     const uint32_t* texels; const TextureRec* textures; const float* srgb_lut;
     const float4* sky; uint32_t sky_w, sky_h;
     const float* gamma_lut; const float* radiance_lut; const float* logluv_lut;   // CodecLuts (rt2_internal.cuh): tabulated decoders, may be null
+    uint32_t any_hit;            // inlined visibility rays stop at their first hit (rt2_ctx::any_hit)
 };
 inline SceneRefs make_scene_refs(const rt2_ctx* ctx) {
     const DeviceScene& s = ctx->scene;
@@ -25,6 +26,7 @@ inline SceneRefs make_scene_refs(const rt2_ctx* ctx) {
     if (s.flat.nodes && ctx->use_flat) { r.flat_nodes = s.flat.nodes; r.flat_leaf = s.flat_leaf; }
     r.tri_shade = s.tri_shade; r.geom_shade = s.geom_shade;
     r.texels = s.texels; r.textures = s.textures; r.srgb_lut = s.srgb_lut; r.sky = s.sky; r.sky_w = s.sky_w; r.sky_h = s.sky_h;
+    r.any_hit = ctx->any_hit ? 1u : 0u;
     r.gamma_lut = ctx->codec_luts; r.radiance_lut = ctx->codec_luts ? ctx->codec_luts + 256 : nullptr; r.logluv_lut = ctx->codec_luts ? ctx->codec_luts + 256 + 65536 : nullptr;
     return r;
 }
@@ -136,13 +138,15 @@ __device__ __forceinline__ void store_shading_output(const rt2_gconst& g, size_t
 
 // trace(ray): traceRayEXT(SceneBVH, opaque, 0xff, ...) — bridge :74-81, rayhit.rchit:60-66, raymiss.rmiss:12-17.
 // A miss leaves geom = prim = inst = ~0u and *tri_slot = ~0u.
-__device__ __forceinline__ Hit trace_closest(const SceneRefs& sc, V3 o, V3 d, float tmin, float tmax, uint32_t* tri_slot) {
+// any = true: the caller only asks "hit or not" (visibility tests) — the walk stops at the first hit (sc.any_hit; RT2_ANY_HIT=0 turns it off)
+__device__ __forceinline__ Hit trace_closest(const SceneRefs& sc, V3 o, V3 d, float tmin, float tmax, uint32_t* tri_slot, bool any = false) {
     TraceRay ray; ray.o = o; ray.d = d; ray.tmin = tmin; ray.tmax = tmax;
     Hit best; best.t = INFINITY; best.u = best.v = 0.f; best.inst = best.geom = best.prim = 0xFFFFFFFFu;
     *tri_slot = 0xFFFFFFFFu;
-    if (sc.flat_nodes) flat_closest_hit(sc.flat_nodes, sc.flat_leaf, sc.instances, sc.tris, ray, best, tri_slot);
-    else if (sc.instances) tlas_closest_hit(sc.tlas_nodes, sc.tlas_slot_to_inst, sc.instances, sc.blas_nodes, sc.tris, ray, best, tri_slot);
-    else cwbvh_closest_hit(sc.blas_nodes, sc.tris, ray, 0u, best, tri_slot);
+    any = any && sc.any_hit != 0u;
+    if (sc.flat_nodes) flat_closest_hit(sc.flat_nodes, sc.flat_leaf, sc.instances, sc.tris, ray, best, tri_slot, nullptr, any);
+    else if (sc.instances) tlas_closest_hit(sc.tlas_nodes, sc.tlas_slot_to_inst, sc.instances, sc.blas_nodes, sc.tris, ray, best, tri_slot, nullptr, any);
+    else cwbvh_closest_hit(sc.blas_nodes, sc.tris, ray, 0u, best, tri_slot, nullptr, any);
     return best;
 }
 
