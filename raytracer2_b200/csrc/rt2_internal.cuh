@@ -101,7 +101,7 @@ struct FrameBuffers {
     struct Spec {
         float4 *ray0 = nullptr, *ray1 = nullptr, *hit = nullptr, *contrib = nullptr, *px_rad = nullptr;
         uint4* misc = nullptr; uint32_t *hit_inst = nullptr, *queue0 = nullptr, *queue1 = nullptr, *pending0 = nullptr, *pending1 = nullptr, *counters = nullptr, *start_index = nullptr;
-        uint8_t* nhits = nullptr; uint2* px_prog = nullptr;
+        uint16_t* nhits = nullptr; uint2* px_prog = nullptr;
         size_t cap_paths = 0, cap_contrib = 0, cap_pixels = 0, cap_counters = 0;
     } spec;
     uint32_t* warp_pop = nullptr; size_t warp_pop_cap = 0;   // k_path_warp: warp-private slot queues (num_warps x P)
@@ -147,6 +147,7 @@ struct rt2_ctx {
     bool stats_from_counters = false;   // rays/hits of the last render still live in fb.counters
     bool stats_walks_counted = false;   // ... and fb.counters[4..5] holds the walks (K1); otherwise rays_walked = rays_traced
     bool stats_reused_counted = false;  // ... and fb.counters[16..17] holds trace() calls answered without a walk (ReSTIR frames): rays_walked = rays_traced - that
+    bool sparse_contrib = true;         // speculative K1: contributions that are +0 are neither stored nor added (RT2_SPARSE_CONTRIB=0: all of them)
     bool any_hit = true;                // visibility-ray batches of the ReSTIR passes end a walk at its first hit (RT2_ANY_HIT=0: closest hit always)
     bool visibility_reuse = true;       // K9: a clear initial-visibility ray answers the final one (RT2_VISIBILITY_REUSE=0: both are walked)
     bool primary_reuse = true;          // K1: walk a pixel's primary ray once for all its samples (RT2_PRIMARY_REUSE=0: every sample walks its own)

@@ -622,7 +622,10 @@ struct SpecArgs {
     float4 *ray0, *ray1; uint4* misc;                 // per path: o|d.x, d.yz|thr.xy, {rng index, bounce, pixel_slot * spp + sample, thr.z}
     const float4* hit; const uint32_t* hit_inst;
     float4* contrib;                                  // per (pixel, sample, bounce): thr * emission of that event
-    uint8_t* nhits;                                   // per (pixel, sample): hits | 0x80 if the sample ended on a miss
+    uint16_t* nhits;                                  // per (pixel, sample): hits | 0x80 if the sample ended on a miss | which bounces left a contribution << 8
+    // sparse contributions (max_bounces <= 8): a contribution that is +0 in every component is neither stored nor added — x + (+0) == x bit for
+    // bit for every x the sum can hold (it starts at +0 and only a (-0) + (-0) could make it -0) — and in a closed scene almost all of them are
+    uint32_t sparse;
     uint32_t* start_index;                            // per (pixel, sample): the RNG position the sample's path was started from
     // candidate round: misc.z / contrib / nhits are indexed by (pending-list position, candidate) = k * cand_K + m instead of
     // (pixel, sample), and the pixel is cand_list[k]
@@ -718,7 +721,7 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_spec_shade(SpecAr
         if (i < count) {
             const float4 r0 = a.ray0[p], r1 = a.ray1[p];
             const uint4 misc = a.misc[p];
-            const uint32_t hp = shared_primary ? p - (misc.y >> 16) : p;
+            const uint32_t hp = shared_primary ? p - ((misc.y >> 16) & 0xFFu) : p;
             const float4 h = a.hit[hp];
             const uint32_t ps = misc.z, slot = a.cand_list ? a.cand_list[(ps - a.path_base) / a.cand_K] : ps / a.spp;
             const uint32_t x = slot % a.band.width, y = band_local_to_global(a.band, slot / a.band.width);
@@ -726,16 +729,17 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_spec_shade(SpecAr
             V3 thr = v3(r1.z, r1.w, __uint_as_float(misc.w));
             Rng rng; rng.index = misc.x; rng.seed = jenkins_hash(zcurve_to_linear(x, y)) + (a.frame + 13u);
             uint32_t bounce = misc.y & 0xFFFFu;
+            uint32_t cmask = misc.y >> 24;                         // bounces of this path that left a contribution (bits 16..23 hold `back` at bounce 0)
             const uint32_t tri_slot = __float_as_uint(h.w);
             float4* c = a.contrib + ((size_t)ps * a.max_bounces + bounce);
             if (tri_slot == 0xFFFFFFFFu) {                         // refrence.rgen:32-36
                 const V3 e = thr * environment_radiance(a.sc, *a.g, d);
-                *c = make_float4(e.x, e.y, e.z, 0.f);
-                a.nhits[ps] = (uint8_t)(bounce | 0x80u);
+                if (!a.sparse || (__float_as_uint(e.x) | __float_as_uint(e.y) | __float_as_uint(e.z)) != 0u) { *c = make_float4(e.x, e.y, e.z, 0.f); if (a.sparse) cmask |= 1u << bounce; }
+                a.nhits[ps] = (uint16_t)(bounce | 0x80u | (cmask << 8));
             } else {
                 const SurfaceFetch sf = get_geometry_from_hit(a.sc, lut, tri_slot, a.sc.instances ? a.hit_inst[hp] : 0u, h.y, h.z);
                 const V3 e = thr * sf.emission;                    // refrence.rgen:38
-                *c = make_float4(e.x, e.y, e.z, 0.f);
+                if (!a.sparse || (__float_as_uint(e.x) | __float_as_uint(e.y) | __float_as_uint(e.z)) != 0u) { *c = make_float4(e.x, e.y, e.z, 0.f); if (a.sparse) cmask |= 1u << bounce; }
                 thr = thr * sf.color;                              // refrence.rgen:39
                 const float rx = rng_next(rng), ry = rng_next(rng), rz = rng_next(rng);
                 (void)rx;
@@ -744,12 +748,12 @@ __global__ void __launch_bounds__(256, RT2_SHADE_MIN_BLOCKS) k_spec_shade(SpecAr
                 d = tangent_to_world(sf.normal, hvec);
                 o = world_pos;                                     // refrence.rgen:42
                 bounce++;
-                if (bounce >= a.max_bounces) a.nhits[ps] = (uint8_t)bounce;
+                if (bounce >= a.max_bounces) a.nhits[ps] = (uint16_t)(bounce | (cmask << 8));
                 else {
                     alive = true;
                     a.ray0[p] = make_float4(o.x, o.y, o.z, d.x);
                     a.ray1[p] = make_float4(d.y, d.z, thr.x, thr.y);
-                    a.misc[p] = make_uint4(rng.index, bounce, ps, __float_as_uint(thr.z));
+                    a.misc[p] = make_uint4(rng.index, bounce | (cmask << 24), ps, __float_as_uint(thr.z));
                 }
             }
         }
@@ -779,9 +783,9 @@ __global__ void __launch_bounds__(256) k_spec_reduce(SpecArgs a, const uint32_t*
             while (sample < a.spp) {
                 const uint32_t ps = slot * a.spp + sample;
                 if (a.start_index[ps] != index) break;
-                const uint32_t nh = a.nhits[ps], h = nh & 0x7Fu, missed = nh >> 7;
+                const uint32_t nh = a.nhits[ps], h = nh & 0x7Fu, missed = (nh >> 7) & 1u, cm = a.sparse ? nh >> 8 : 0xFFFFFFFFu;
                 const float4* c = a.contrib + (size_t)ps * a.max_bounces;
-                for (uint32_t b = 0; b < h + missed; b++) { const float4 e = c[b]; rad = rad + v3(e.x, e.y, e.z); }
+                for (uint32_t b = 0; b < h + missed; b++) if ((cm >> (b & 31u)) & 1u) { const float4 e = c[b]; rad = rad + v3(e.x, e.y, e.z); }
                 index += 3u * h; rays += h + missed; hits += h;
                 sample++;
             }
@@ -857,9 +861,9 @@ __global__ void __launch_bounds__(256) k_spec_reduce_cand(SpecArgs a, const uint
                 uint32_t m = 0;
                 for (uint32_t sample = pr.x; sample < a.spp; sample++) {
                     const size_t cps = (size_t)a.path_base + (size_t)k * a.cand_K + m;
-                    const uint32_t nh = a.nhits[cps], h = nh & 0x7Fu, missed = nh >> 7;
+                    const uint32_t nh = a.nhits[cps], h = nh & 0x7Fu, missed = (nh >> 7) & 1u, cm = a.sparse ? nh >> 8 : 0xFFFFFFFFu;
                     const float4* c = a.contrib + cps * a.max_bounces;
-                    for (uint32_t b = 0; b < h + missed; b++) { const float4 e = c[b]; rad = rad + v3(e.x, e.y, e.z); }
+                    for (uint32_t b = 0; b < h + missed; b++) if ((cm >> (b & 31u)) & 1u) { const float4 e = c[b]; rad = rad + v3(e.x, e.y, e.z); }
                     m += h; rays += h + missed; hits += h;
                 }
                 a.px_prog[slot] = make_uint2(a.spp, pr.y + 3u * m);
@@ -1285,6 +1289,7 @@ static int render_reference_spec(rt2_ctx* ctx, uint32_t frame, const rt2_launch_
         a.band = band; a.g = ctx->d_gconst; a.frame = frame; a.spp = spp; a.max_bounces = bounces; a.flags = lp.flags;
         a.sc = make_scene_refs(ctx);
         a.ray0 = sp.ray0; a.ray1 = sp.ray1; a.misc = sp.misc; a.hit = sp.hit; a.hit_inst = sp.hit_inst;
+        a.sparse = bounces <= 8u && ctx->sparse_contrib ? 1u : 0u;
         a.contrib = sp.contrib; a.nhits = sp.nhits; a.start_index = sp.start_index; a.px_prog = sp.px_prog; a.px_rad = sp.px_rad;
         a.diffuse_f16 = f.diffuse_f16; a.specular_f16 = f.specular_f16; a.diffuse_f32 = f.diffuse_f32;
         a.stat_rays = reinterpret_cast<unsigned long long*>(f.counters);           // valid samples only (k_spec_reduce)
@@ -1496,6 +1501,7 @@ int render_init(rt2_ctx* ctx) {
     if (const char* e = getenv("RT2_PRIMARY_REUSE")) ctx->primary_reuse = atoi(e) != 0;
     if (const char* e = getenv("RT2_VISIBILITY_REUSE")) ctx->visibility_reuse = atoi(e) != 0;
     if (const char* e = getenv("RT2_ANY_HIT")) ctx->any_hit = atoi(e) != 0;
+    if (const char* e = getenv("RT2_SPARSE_CONTRIB")) ctx->sparse_contrib = atoi(e) != 0;
     if (const char* e = getenv("RT2_WARP_P")) { int v = atoi(e); if (v >= 32 && v <= 4096) ctx->warp_paths = (uint32_t)v; }
     if (const char* e = getenv("RT2_WARP_BLOCKS")) { int v = atoi(e); if (v >= 1 && v <= 16) ctx->warp_blocks_per_sm = v; }
     int p0 = 0, p1 = 0, p2 = 0, b3 = 0;

@@ -147,3 +147,22 @@ def test_visibility_ray_batches_end_at_their_first_hit(monkeypatch, kind, scale)
             assert np.array_equal(a[k], b[k]), k
         assert a[4] == b[4] and a[5] == b[5]
         assert a[5] > 0
+
+
+@pytest.mark.parametrize("kind,scale,env", [(rt.SCENE_CORNELL, 1, 0), (rt.SCENE_HALL, 0.125, 0), (rt.SCENE_INSTANCED, 0.05, 1)])
+def test_sparse_contributions_change_nothing(monkeypatch, kind, scale, env):
+    """Speculative schedule: a per-bounce contribution that is +0 in every component is neither stored nor added (k_spec_shade / k_spec_reduce).
+    x + (+0) == x bit for bit, so the image must equal the one with every contribution stored (RT2_SPARSE_CONTRIB=0) and the oracle's."""
+    w, h, spp, bounces = 160, 96, 5, 4
+    sc = rt.Scene(kind, scale, 32, 0)
+    g = rt.default_gconst(sc.camera(w / h), w, h, sc.num_lights)
+    g.refrence_mode = 1; g.environment = env
+    out = []
+    for sparse in ("0", "1"):
+        monkeypatch.setenv("RT2_SPARSE_CONTRIB", sparse)
+        out.append(_frame(monkeypatch, SCHEDULES["speculative"], True, sc, g, w, h, spp, bounces))
+    assert np.array_equal(out[0][0].view(np.uint32), out[1][0].view(np.uint32)) and np.array_equal(out[0][1], out[1][1])
+    assert out[0][2] == out[1][2] and out[0][3] == out[1][3]
+    ref = O.OracleScene(sc.desc).render_reference(g, 3, w, h, spp=spp, max_bounces=bounces)
+    nbad = int((out[1][0].view(np.uint32) != ref[2].view(np.uint32)).any(axis=2).sum())
+    assert nbad <= (2 if env else 0) and out[1][2] == ref[3]
